@@ -1,0 +1,511 @@
+/*
+ * fec_oracle.c — scalar C restatement of the reference decode path (see fec_oracle.h for status).
+ * TEST INFRASTRUCTURE ONLY; never linked into the product.
+ *
+ * Written from the algorithm description in SURVEY.md section 8 and 3GPP TS 36.212 (5.1.1 CRC, 5.1.2
+ * segmentation, 5.1.3.2 turbo code/QPP, 5.1.4.1 rate matching); each function names the reference
+ * file:line whose behaviour it restates and is checked bit-for-bit against it.
+ */
+#define _GNU_SOURCE
+#include "fec_oracle.h"
+#include "lte_qpp_table.h"
+#include <math.h>
+#include <pthread.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <time.h>
+
+/* ------------------------------------------------------------------ sizes / segmentation ---- */
+
+int orc_cb_index(int K)
+{   /* first table entry >= K (cbsegm.c:116-127) */
+  for (int i = 0; i < LTE_NOF_CB_SIZES; i++) if (lte_qpp_table[i][0] >= K) return i;
+  return -1;
+}
+int orc_cb_size(int idx) { return (idx >= 0 && idx < LTE_NOF_CB_SIZES) ? lte_qpp_table[idx][0] : -1; }
+
+int orc_subblocks(int K)
+{   /* turbodecoder.c:364-376 with LV_HAVE_AVX2 */
+  if (K % 16 == 0 && K > 800) return 16;
+  if (K % 8 == 0 && K > 400) return 8;
+  return 0;
+}
+
+int orc_cbsegm(uint32_t tbs, uint32_t *o)
+{   /* cbsegm.c:58-108; o = {F,C,K1,K2,K1_idx,K2_idx,C1,C2,tbs} */
+  memset(o, 0, 9 * sizeof(uint32_t));
+  if (tbs == 0) return 0;
+  uint32_t B = tbs + 24, C, Bp;
+  if (B <= 6144) { C = 1; Bp = B; }
+  else { C = (uint32_t)ceilf((float)B / (6144 - 24)); Bp = B + 24 * C; }
+  int i1 = orc_cb_index((int)((Bp - 1) / C + 1));
+  if (i1 < 0) return -1;
+  uint32_t K1 = lte_qpp_table[i1][0], K2 = 0, K2i = 0, C1 = 1, C2 = 0;
+  if (C > 1) {
+    K2i = i1 - 1; K2 = lte_qpp_table[K2i][0];
+    C2 = (C * K1 - Bp) / (K1 - K2); C1 = C - C2;
+  }
+  o[0] = C1 * K1 + C2 * K2 - Bp; o[1] = C; o[2] = K1; o[3] = K2; o[4] = i1; o[5] = K2i; o[6] = C1; o[7] = C2; o[8] = tbs;
+  return 0;
+}
+
+/* ------------------------------------------------------------------ CRC ---- */
+/* MSB-first, zero init, no reflection, no final xor (crc.c:74-101,144-158). Like
+ * srslte_crc_checksum_byte, only the nbits/8 WHOLE bytes are consumed ("len is multiple of 8",
+ * crc.c:143); every length on this path (K, tbs, tbs+24) is a multiple of 8. */
+uint32_t orc_crc(int type, const uint8_t *bytes, int nbits)
+{
+  const uint32_t poly = type ? 0x1800063u : 0x1864CFBu;
+  uint32_t r = 0;
+  nbits &= ~7;
+  for (int i = 0; i < nbits; i++) {
+    uint32_t bit = (bytes[i >> 3] >> (7 - (i & 7))) & 1u;
+    r = (r << 1) | bit;            /* message bit enters at the bottom of a 25-bit register */
+    if (r & 0x1000000u) r ^= poly;
+  }
+  for (int i = 0; i < 24; i++) {   /* flush 24 zero bits = multiply by x^24 */
+    r <<= 1;
+    if (r & 0x1000000u) r ^= poly;
+  }
+  return r & 0xFFFFFFu;
+}
+
+/* ------------------------------------------------------------------ QPP interleaver ---- */
+int orc_qpp(int K, uint16_t *fwd, uint16_t *rev)
+{
+  int idx = orc_cb_index(K);
+  if (idx < 0 || lte_qpp_table[idx][0] != K) return -1;
+  uint64_t f1 = lte_qpp_table[idx][1], f2 = lte_qpp_table[idx][2];
+  for (uint64_t i = 0; i < (uint64_t)K; i++) {
+    uint64_t j = (f1 * i + f2 * i * i) % (uint64_t)K;
+    fwd[i] = (uint16_t)j; rev[j] = (uint16_t)i;
+  }
+  return 0;
+}
+
+int orc_sb_pos(int x, int K, int P)
+{
+  if (P <= 1) return x;
+  int L = K / P;
+  return (x % L) * P + x / L;
+}
+
+int orc_qpp_sb(int K, int P, uint16_t *fwd, uint16_t *rev)
+{   /* tc_interl_lte.c:104-112: tables re-indexed into the sb domain */
+  static __thread uint16_t f[ORC_MAX_K], r[ORC_MAX_K];
+  if (orc_qpp(K, f, r)) return -1;
+  if (P <= 1) { memcpy(fwd, f, 2 * K); memcpy(rev, r, 2 * K); return 0; }
+  int L = K / P;
+  for (int pos = 0; pos < K; pos++) {
+    int nat = (pos % P) * L + pos / P;
+    fwd[pos] = (uint16_t)orc_sb_pos(f[nat], K, P);
+    rev[pos] = (uint16_t)orc_sb_pos(r[nat], K, P);
+  }
+  return 0;
+}
+
+/* ------------------------------------------------------------------ rate de-matching ---- */
+static const uint8_t RM_COLPERM[32] = {0, 16, 8, 24, 4, 20, 12, 28, 2, 18, 10, 26, 6, 22, 14, 30,
+                                       1, 17, 9, 25, 5, 21, 13, 29, 3, 19, 11, 27, 7, 23, 15, 31};
+
+/* tab[i] = natural position (3*idx+stream, tail included) of the i-th transmitted bit for this rv,
+ * i in [0, 3K+12). 36.212 5.1.4.1.1-2; restates rm_turbo.c:164-238. */
+int orc_rm_table(int K, int rv, uint16_t *tab)
+{
+  const int D = K + 4, R = (D - 1) / 32 + 1, KP = 32 * R, ND = KP - D, NCB = 3 * KP;
+  const int k0 = R * (2 * (int)ceilf((float)NCB / (float)(8 * R)) * rv + 2);
+  int n = 0;
+  for (int j = 0; n < 3 * D; j++) {
+    int w = (k0 + j) % NCB, y, stream;
+    if (w < KP)                { stream = 0; y = (w % R) * 32 + RM_COLPERM[w / R]; }
+    else if (((w - KP) & 1) == 0) { int m = (w - KP) / 2; stream = 1; y = (m % R) * 32 + RM_COLPERM[m / R]; }
+    else { int m = (w - KP) / 2; stream = 2; y = (RM_COLPERM[m / R] + 32 * (m % R) + 1) % KP; }
+    if (y < ND) continue;          /* <NULL> dummy bit */
+    tab[n++] = (uint16_t)(3 * (y - ND) + stream);
+  }
+  return 0;
+}
+
+/* natural coded position t -> index in the reference soft buffer (rm_turbo.c:250-264) */
+int orc_rm_soft_index(int t, int K, int P)
+{
+  if (P == 0) return t;
+  if (t < 3 * K) return (t % 3) * (K + 32) + orc_sb_pos(t / 3, K, P);
+  return 3 * (K + 32) + (t - 3 * K);
+}
+
+int orc_rm_rx(const int16_t *in, int E, int K, int rv, int sb_layout, int16_t *soft)
+{   /* soft[deinter[i % (3K+12)]] += e[i], wrapping int16 (rm_turbo.c:378-430) */
+  static __thread uint16_t tab[3 * ORC_MAX_K + 12];
+  if (rv < 0 || rv > 3 || orc_cb_index(K) < 0 || orc_cb_size(orc_cb_index(K)) != K) return -2;
+  orc_rm_table(K, rv, tab);
+  int P = sb_layout ? orc_subblocks(K) : 0, n = 3 * K + 12;
+  for (int i = 0; i < E; i++) {
+    int pos = orc_rm_soft_index(tab[i % n], K, P);
+    soft[pos] = (int16_t)(soft[pos] + in[i]);
+  }
+  return 0;
+}
+
+/* ------------------------------------------------------------------ constituent MAP decoders ---- */
+#define NEG_INF (-10000)
+static inline int16_t sat16(int v) { return (int16_t)(v > 32767 ? 32767 : (v < -32768 ? -32768 : v)); }
+static inline int16_t adds(int16_t a, int16_t b) { return sat16((int)a + (int)b); }
+static inline int16_t subs(int16_t a, int16_t b) { return sat16((int)a - (int)b); }
+static inline int16_t wrap16(int v) { return (int16_t)(uint16_t)v; }
+static inline int16_t maxs(int16_t a, int16_t b) { return a > b ? a : b; }
+
+/* backward (beta) step of the windowed decoder: o <- max(m,n) (turbodecoder_win.h:397-418) */
+static void win_beta_step(int16_t o[8], int16_t x, int16_t y, int saturate)
+{
+  int16_t xy, m[8], n[8];
+  if (saturate) {
+    xy = adds(x, y);
+    m[0] = adds(o[4], xy); m[1] = o[4];          m[2] = adds(o[5], y);  m[3] = adds(o[5], x);
+    m[4] = adds(o[6], x);  m[5] = adds(o[6], y); m[6] = o[7];           m[7] = adds(o[7], xy);
+    n[0] = o[0];           n[1] = adds(o[0], xy); n[2] = adds(o[1], x);  n[3] = adds(o[1], y);
+    n[4] = adds(o[2], y);  n[5] = adds(o[2], x); n[6] = adds(o[3], xy); n[7] = o[3];
+  } else {   /* tail trellis uses plain (wrapping) adds: turbodecoder_win.h:235-242,263-307 */
+    xy = wrap16(x + y);
+    m[0] = wrap16(o[4] + xy); m[1] = o[4];             m[2] = wrap16(o[5] + y);  m[3] = wrap16(o[5] + x);
+    m[4] = wrap16(o[6] + x);  m[5] = wrap16(o[6] + y); m[6] = o[7];              m[7] = wrap16(o[7] + xy);
+    n[0] = o[0];              n[1] = wrap16(o[0] + xy); n[2] = wrap16(o[1] + x);  n[3] = wrap16(o[1] + y);
+    n[4] = wrap16(o[2] + y);  n[5] = wrap16(o[2] + x); n[6] = wrap16(o[3] + xy); n[7] = o[3];
+  }
+  for (int i = 0; i < 8; i++) o[i] = maxs(m[i], n[i]);
+}
+
+static void win_alpha_branches(const int16_t o[8], int16_t x, int16_t y, int16_t m[8], int16_t n[8])
+{   /* turbodecoder_win.h:521-539: m = hypothesis bit 0, n = hypothesis bit 1 */
+  int16_t xy = adds(x, y);
+  m[0] = o[0];           m[1] = adds(o[3], y); m[2] = adds(o[4], y); m[3] = o[7];
+  m[4] = o[1];           m[5] = adds(o[2], y); m[6] = adds(o[5], y); m[7] = o[6];
+  n[0] = adds(o[1], xy); n[1] = adds(o[2], x); n[2] = adds(o[5], x); n[3] = adds(o[6], xy);
+  n[4] = adds(o[0], xy); n[5] = adds(o[3], x); n[6] = adds(o[4], x); n[7] = adds(o[7], xy);
+}
+
+static inline void win_normalize(int k, int16_t o[8])
+{   /* turbodecoder_win.h:244-261 with normalize_period 2 */
+  if ((k % 2) == 0 && k != 0) {
+    for (int i = 1; i < 8; i++) o[i] = subs(o[i], o[0]);
+    o[0] = 0;
+  }
+}
+
+/* windowed max-log-MAP, P sub-blocks of L=K/P, natural indexing (lane d, step k <-> d*L+k).
+ * Restates tdec_win{sse16,avx16}_dec = beta then alpha (turbodecoder_win.h:310-435,438-586). */
+static void map_windowed(int K, int P, const int16_t *in, const int16_t *app, const int16_t *par,
+                         const int16_t *tail_x, const int16_t *tail_p, int16_t *out)
+{
+  const int L = K / P, W = 40;
+  static __thread int16_t X[ORC_MAX_K];
+  static __thread int16_t B[16][ORC_MAX_K / 8 + 1][8];   /* beta store, (L+1) x 8 per lane; L <= 768 (K=6144,P=8 manual) */
+  int16_t warm[16][8], o[8];
+  for (int i = 0; i < K; i++) X[i] = app ? adds(app[i], in[i]) : in[i];
+
+  /* beta warm-up over the FIRST 40 symbols of every sub-block */
+  for (int d = 0; d < P; d++) {
+    for (int i = 0; i < 8; i++) o[i] = NEG_INF;
+    for (int k = W - 1; k >= 0; k--) { win_beta_step(o, X[d * L + k], par[d * L + k], 1); win_normalize(k, o); }
+    memcpy(warm[d], o, sizeof(o));
+  }
+  for (int d = 0; d < P; d++) {
+    if (d < P - 1) memcpy(o, warm[d + 1], sizeof(o));
+    else {   /* last lane: known end state through the 3 tail steps, no apriori, wrapping adds */
+      o[0] = 0; for (int i = 1; i < 8; i++) o[i] = NEG_INF;
+      for (int k = 2; k >= 0; k--) win_beta_step(o, tail_x[k], tail_p[k], 0);
+    }
+    memcpy(B[d][L], o, sizeof(o));
+    for (int k = L - 1; k >= 0; k--) {
+      win_beta_step(o, X[d * L + k], par[d * L + k], 1);
+      memcpy(B[d][k], o, sizeof(o));     /* stored BEFORE normalisation */
+      win_normalize(k, o);
+    }
+  }
+  /* alpha warm-up over the LAST 40 symbols of every sub-block */
+  for (int d = 0; d < P; d++) {
+    int16_t m[8], n[8];
+    for (int i = 0; i < 8; i++) o[i] = NEG_INF;
+    for (int k = 0; k < W; k++) {
+      int idx = d * L + L - W + k;
+      win_alpha_branches(o, X[idx], par[idx], m, n);
+      for (int i = 0; i < 8; i++) o[i] = maxs(m[i], n[i]);
+      win_normalize(k, o);
+    }
+    memcpy(warm[d], o, sizeof(o));
+  }
+  for (int d = 0; d < P; d++) {
+    int16_t m[8], n[8];
+    if (d > 0) memcpy(o, warm[d - 1], sizeof(o));
+    else { o[0] = 0; for (int i = 1; i < 8; i++) o[i] = NEG_INF; }
+    for (int k = 0; k < L; k++) {
+      int idx = d * L + k;
+      win_alpha_branches(o, X[idx], par[idx], m, n);
+      const int16_t *b = B[d][k + 1];
+      int16_t m0 = adds(b[0], m[0]), m1 = adds(b[0], n[0]);
+      for (int i = 1; i < 8; i++) { m0 = maxs(m0, adds(b[i], m[i])); m1 = maxs(m1, adds(b[i], n[i])); }
+      int16_t r = subs(m1, m0);
+      if (P == 8) r = (int16_t)(r >> 1);   /* divide_output exists for sse16 only (turbodecoder_win.h:61,565-567) */
+      out[idx] = r;
+      for (int i = 0; i < 8; i++) o[i] = maxs(m[i], n[i]);
+      win_normalize(k, o);
+    }
+  }
+}
+
+/* non-windowed SSE decoder, wrapping int16 (turbodecoder_sse.c:105-206,211-297,300-353) */
+static void map_sse(int K, const int16_t *in, const int16_t *app, const int16_t *par,
+                    const int16_t *tail_x, const int16_t *tail_p, int16_t *out)
+{
+  static __thread int16_t g0[ORC_MAX_K + 3], g1[ORC_MAX_K + 3], A[ORC_MAX_K + 4][8];
+  static const int SP[8] = {1, 2, 5, 6, 0, 3, 4, 7}, SN[8] = {0, 3, 4, 7, 1, 2, 5, 6};
+  static const int BP[8] = {4, 0, 1, 5, 6, 2, 3, 7}, BN[8] = {0, 4, 5, 1, 2, 6, 7, 3};
+  static const int GA[8] = {1, 1, 0, 0, 0, 0, 1, 1}, GB[8] = {1, 0, 0, 1, 1, 0, 0, 1};
+  for (int k = 0; k < K; k++) {
+    int16_t x = app ? wrap16(app[k] + in[k]) : in[k];
+    g1[k] = (int16_t)(wrap16(x + par[k]) >> 1);
+    g0[k] = (int16_t)(wrap16(x - par[k]) >> 1);
+  }
+  for (int k = 0; k < 3; k++) {   /* tail: C integer division, truncating (turbodecoder_sse.c:349-352) */
+    g0[K + k] = (int16_t)(((int)tail_x[k] - (int)tail_p[k]) / 2);
+    g1[K + k] = (int16_t)(((int)tail_x[k] + (int)tail_p[k]) / 2);
+  }
+  int16_t a[8], t[8];
+  a[0] = 0; for (int i = 1; i < 8; i++) a[i] = NEG_INF;
+  memcpy(A[0], a, sizeof(a));
+  for (int k = 0; k < K; k++) {
+    int16_t ap[8], an[8];
+    for (int i = 0; i < 8; i++) { int16_t g = GA[i] ? g1[k] : g0[k]; ap[i] = wrap16(a[i] + g); an[i] = wrap16(a[i] - g); }
+    for (int j = 0; j < 8; j++) t[j] = maxs(ap[SP[j]], an[SN[j]]);
+    memcpy(a, t, sizeof(a));
+    memcpy(A[k + 1], a, sizeof(a));          /* stored before normalisation */
+    if ((k % 4) == 3) { int16_t z = a[0]; for (int i = 0; i < 8; i++) a[i] = wrap16(a[i] - z); }
+  }
+  int16_t b[8];
+  b[0] = 0; for (int i = 1; i < 8; i++) b[i] = NEG_INF;
+  int cnt = 0;
+  for (int k = K + 2; k >= 0; k--) {
+    int16_t bp[8], bn[8], sp[8], sn[8];
+    for (int i = 0; i < 8; i++) { int16_t g = GB[i] ? g1[k] : g0[k]; bp[i] = wrap16(b[i] + g); bn[i] = wrap16(b[i] - g); }
+    for (int j = 0; j < 8; j++) { sp[j] = bp[BP[j]]; sn[j] = bn[BN[j]]; b[j] = maxs(sp[j], sn[j]); }
+    if (k < K) {
+      int16_t mp = wrap16(sp[0] + A[k][0]), mn = wrap16(sn[0] + A[k][0]);
+      for (int j = 1; j < 8; j++) { mp = maxs(mp, wrap16(sp[j] + A[k][j])); mn = maxs(mn, wrap16(sn[j] + A[k][j])); }
+      out[k] = wrap16((int)mp - (int)mn);    /* hMax() returns 0x7FFF-max, so hMax(bn)-hMax(bp) = max(bp)-max(bn) (turbodecoder_sse.c:97-102,178) */
+      if (++cnt == 4) { cnt = 0; int16_t z = b[0]; for (int i = 0; i < 8; i++) b[i] = wrap16(b[i] - z); }
+    }
+  }
+}
+
+void orc_map(int K, int P, const int16_t *x, const int16_t *app, const int16_t *par,
+             const int16_t *tail_x, const int16_t *tail_p, int16_t *out)
+{
+  if (P == 0) map_sse(K, x, app, par, tail_x, tail_p, out);
+  else map_windowed(K, P, x, app, par, tail_x, tail_p, out);
+}
+
+/* ------------------------------------------------------------------ half-iteration driver ---- */
+static int tdec_setup(orc_tdec_t *h, int K)
+{
+  int idx = orc_cb_index(K);
+  if (K > ORC_MAX_K || idx < 0 || orc_cb_size(idx) != K) return -1;
+  h->K = K; h->P = orc_subblocks(K); h->n_iter = 0;
+  return orc_qpp(K, h->fwd, h->rev);
+}
+
+static void tdec_tails(orc_tdec_t *h, const int16_t *t)
+{   /* turbodecoder_iter.h:61-70 / turbodecoder_win.h:667-673 / turbodecoder_sse.c:486-492 */
+  for (int i = 0; i < 3; i++) {
+    h->t_syst[i] = t[2 * i]; h->t_p0[i] = t[2 * i + 1];
+    h->t_app2[i] = t[6 + 2 * i]; h->t_p1[i] = t[6 + 2 * i + 1];
+  }
+}
+
+int orc_tdec_new_cb_natural(orc_tdec_t *h, int K, const int16_t *in)
+{
+  if (tdec_setup(h, K)) return -1;
+  for (int i = 0; i < K; i++) { h->syst[i] = in[3 * i]; h->p0[i] = in[3 * i + 1]; h->p1[i] = in[3 * i + 2]; }
+  tdec_tails(h, in + 3 * K);
+  return 0;
+}
+
+int orc_tdec_new_cb_soft(orc_tdec_t *h, int K, const int16_t *soft)
+{
+  if (tdec_setup(h, K)) return -1;
+  if (h->P == 0) return orc_tdec_new_cb_natural(h, K, soft);
+  for (int x = 0; x < K; x++) {
+    int pos = orc_sb_pos(x, K, h->P);
+    h->syst[x] = soft[pos]; h->p0[x] = soft[K + 32 + pos]; h->p1[x] = soft[2 * (K + 32) + pos];
+  }
+  tdec_tails(h, soft + 3 * (K + 32));
+  return 0;
+}
+
+void orc_tdec_iteration(orc_tdec_t *h, uint8_t *out_bytes, int16_t *llr_nat)
+{   /* run_tdec_iteration_16bit (turbodecoder_iter.h:73-147) + tdec_decision_byte (turbodecoder.c:353-360) */
+  const int K = h->K, n = h->n_iter;
+  if ((n % 2) == 0) {
+    if (n) for (int i = 0; i < K; i++) h->app1[i] = wrap16(h->app1[i] - h->ext1[i]);
+    orc_map(K, h->P, h->syst, n ? h->app1 : NULL, h->p0, h->t_syst, h->t_p0, h->ext1);
+  } else {
+    if (n > 1) for (int i = 0; i < K; i++) h->ext1[i] = wrap16(h->ext1[i] - h->app1[i]);
+    for (int i = 0; i < K; i++) h->app2[h->rev[i]] = h->ext1[i];
+    orc_map(K, h->P, h->app2, NULL, h->p1, h->t_app2, h->t_p1, h->ext2);
+    for (int i = 0; i < K; i++) h->app1[h->fwd[i]] = h->ext2[i];
+  }
+  h->n_iter++;
+  const int16_t *A = (h->n_iter % 2) ? h->ext1 : h->app1;
+  if (out_bytes) {
+    memset(out_bytes, 0, K / 8);
+    for (int x = 0; x < K; x++) if (A[x] > 0) out_bytes[x >> 3] |= (uint8_t)(0x80u >> (x & 7));
+  }
+  if (llr_nat) memcpy(llr_nat, A, sizeof(int16_t) * K);
+}
+
+int orc_tdec_halfits(int K, const int16_t *in_nat, int nof, uint8_t *out_bytes, int16_t *llr_nat)
+{
+  orc_tdec_t *h = malloc(sizeof(*h));
+  int r = orc_tdec_new_cb_natural(h, K, in_nat);
+  for (int n = 0; n < nof && !r; n++)
+    orc_tdec_iteration(h, out_bytes + (size_t)n * (K / 8), llr_nat ? llr_nat + (size_t)n * K : NULL);
+  free(h);
+  return r;
+}
+
+static int decode_cb_h(orc_tdec_t *h, int max_its, int crc_type, int crc_bits, uint8_t *out_bytes, int *nits)
+{   /* sch.c:361-391 */
+  int n = 0, ok = 0;
+  do {
+    orc_tdec_iteration(h, out_bytes, NULL);
+    n++;
+    if (!orc_crc(crc_type, out_bytes, crc_bits)) ok = 1;
+  } while (n < max_its && !ok);
+  *nits = n;
+  return ok;
+}
+
+int orc_decode_cb(const int16_t *soft, int K, int max_its, int crc_type, uint8_t *out_bytes, int *nits)
+{
+  orc_tdec_t *h = malloc(sizeof(*h));
+  if (orc_tdec_new_cb_soft(h, K, soft)) { free(h); return -1; }
+  int ok = decode_cb_h(h, max_its, crc_type, K, out_bytes, nits);
+  free(h);
+  return ok;
+}
+
+/* ------------------------------------------------------------------ transport block ---- */
+typedef struct { orc_softbuffer_t sb; orc_tdec_t dec; } orc_tb_t;
+
+void *orc_tb_new(void) { orc_tb_t *t = calloc(1, sizeof(orc_tb_t)); if (t) t->sb.max_cb = ORC_MAX_CB; return t; }
+void  orc_tb_free(void *p) { free(p); }
+
+void orc_tb_reset(void *p, uint32_t tbs)
+{
+  orc_tb_t *t = p;
+  int n = (int)((tbs + 24) / (6144 - 24) + 1);
+  if (n > t->sb.max_cb) n = t->sb.max_cb;
+  for (int i = 0; i < n; i++) memset(t->sb.soft[i], 0, sizeof(t->sb.soft[i]));
+  memset(t->sb.cb_crc, 0, sizeof(t->sb.cb_crc));
+}
+
+void orc_tb_get_soft(void *p, int cb, int16_t *out) { memcpy(out, ((orc_tb_t *)p)->sb.soft[cb], sizeof(int16_t) * ORC_SOFT_SIZE); }
+
+/* decode_tb + decode_tb_cb (sch.c:307-498). Returns 0 OK, -1 CRC fail, -2 invalid. data needs
+ * tbs/8 + 3 bytes plus K/8 slack for the last CB's write. */
+int orc_tb_decode(void *p, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits, const int16_t *e_bits,
+                  uint32_t max_its, uint8_t *data, uint8_t *cb_crc_out, uint32_t *cb_its)
+{
+  orc_tb_t *t = p;
+  uint32_t s[9];
+  if (!t || !data || !e_bits) return -2;
+  if (orc_cbsegm(tbs, s)) return -2;
+  const uint32_t F = s[0], C = s[1], K1 = s[2], K2 = s[3], C1 = s[6];
+  if (tbs == 0 || C == 0) return 0;
+  if (F) return -2;
+  if (C > (uint32_t)t->sb.max_cb) return -2;
+  data[tbs / 8] = 0; data[tbs / 8 + 1] = 0; data[tbs / 8 + 2] = 0;
+  for (uint32_t cb = 0; cb < C; cb++) {
+    uint32_t K = cb < C1 ? K1 : K2, rlen = C == 1 ? K : K - 24;
+    if (cb_its) cb_its[cb] = 0;
+    if (!t->sb.cb_crc[cb]) {
+      uint32_t Gp = nof_e_bits / Qm, gamma = Gp % C, n_e = Qm * (Gp / C), rp = cb * n_e, E = n_e;
+      if (cb > C - gamma) { E = n_e + Qm; rp = (C - gamma) * n_e + (cb - (C - gamma)) * E; }   /* sch.c:339 quirk */
+      if (orc_rm_rx(e_bits + rp, (int)E, (int)K, (int)rv, 1, t->sb.soft[cb])) return -1;
+      orc_tdec_new_cb_soft(&t->dec, (int)K, t->sb.soft[cb]);
+      int nits = 0;
+      int ok = decode_cb_h(&t->dec, (int)max_its, C > 1 ? 1 : 0, C > 1 ? (int)K : (int)tbs + 24, &data[cb * rlen / 8], &nits);
+      if (ok) t->sb.cb_crc[cb] = 1;
+      if (cb_its) cb_its[cb] = (uint32_t)nits;
+    } else {
+      memcpy(&data[cb * rlen / 8], t->sb.data[cb], rlen / 8);
+    }
+  }
+  t->sb.tb_crc = 1;
+  for (uint32_t i = 0; i < C; i++) if (!t->sb.cb_crc[i]) { t->sb.tb_crc = 0; break; }
+  if (!t->sb.tb_crc)
+    for (uint32_t i = 0; i < C; i++) if (t->sb.cb_crc[i]) {
+      uint32_t K = i < C1 ? K1 : K2, rlen = C == 1 ? K : K - 24;
+      memcpy(t->sb.data[i], &data[i * rlen / 8], rlen / 8);
+    }
+  for (uint32_t i = 0; i < C && cb_crc_out; i++) cb_crc_out[i] = t->sb.cb_crc[i];
+  if (!t->sb.tb_crc) return -1;
+  uint32_t par_rx = orc_crc(0, data, (int)tbs);
+  uint32_t par_tx = ((uint32_t)data[tbs / 8] << 16) | ((uint32_t)data[tbs / 8 + 1] << 8) | data[tbs / 8 + 2];
+  return (par_rx == par_tx && par_rx) ? 0 : -1;
+}
+
+/* ------------------------------------------------------------------ multithreaded timing harness ---- */
+typedef struct {
+  int tid, nthreads, ntb, reps;
+  uint32_t tbs, Qm, rv, nof_e_bits, max_its;
+  const int16_t *e;
+  pthread_barrier_t *bar;
+  uint64_t n_tb, n_ok, its;
+  struct timespec t0, t1;
+} orc_mt_t;
+
+static void *orc_mt_worker(void *a_)
+{
+  orc_mt_t *a = a_;
+  void *tb = orc_tb_new();
+  uint8_t *data = malloc(a->tbs / 8 + 3 + 1024), crc[ORC_MAX_CB];
+  uint32_t its[ORC_MAX_CB];
+  pthread_barrier_wait(a->bar);
+  clock_gettime(CLOCK_MONOTONIC, &a->t0);
+  for (int r = 0; r < a->reps; r++)
+    for (int i = a->tid; i < a->ntb; i += a->nthreads) {
+      orc_tb_reset(tb, a->tbs);
+      int ret = orc_tb_decode(tb, a->tbs, a->Qm, a->rv, a->nof_e_bits, a->e + (size_t)i * a->nof_e_bits, a->max_its, data, crc, its);
+      a->n_tb++; if (ret == 0) a->n_ok++;
+      for (int c = 0; c < ORC_MAX_CB; c++) a->its += its[c];
+    }
+  clock_gettime(CLOCK_MONOTONIC, &a->t1);
+  free(data); orc_tb_free(tb);
+  return NULL;
+}
+
+/* out3 = {TBs decoded, TBs OK, total CB half-iterations}; returns wall seconds */
+double orc_bench_tb_mt(int nthreads, int ntb, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits,
+                       const int16_t *e_bits_all, uint32_t max_its, int reps, uint64_t *out3)
+{
+  pthread_t th[256]; orc_mt_t a[256]; pthread_barrier_t bar;
+  if (nthreads > 256) nthreads = 256;
+  pthread_barrier_init(&bar, NULL, nthreads);
+  for (int t = 0; t < nthreads; t++) {
+    a[t] = (orc_mt_t){.tid = t, .nthreads = nthreads, .ntb = ntb, .reps = reps, .tbs = tbs, .Qm = Qm, .rv = rv,
+                      .nof_e_bits = nof_e_bits, .max_its = max_its, .e = e_bits_all, .bar = &bar};
+    pthread_create(&th[t], NULL, orc_mt_worker, &a[t]);
+  }
+  double t0 = 1e300, t1 = 0;
+  out3[0] = out3[1] = out3[2] = 0;
+  for (int t = 0; t < nthreads; t++) {
+    pthread_join(th[t], NULL);
+    double s = a[t].t0.tv_sec + 1e-9 * a[t].t0.tv_nsec, e = a[t].t1.tv_sec + 1e-9 * a[t].t1.tv_nsec;
+    if (s < t0) t0 = s;
+    if (e > t1) t1 = e;
+    out3[0] += a[t].n_tb; out3[1] += a[t].n_ok; out3[2] += a[t].its;
+  }
+  pthread_barrier_destroy(&bar);
+  return t1 - t0;
+}

@@ -1,0 +1,72 @@
+/*
+ * fec_oracle.h — CPU restatement of the reference's transport-block decode path.
+ *
+ * TEST INFRASTRUCTURE ONLY. Nothing under oracle/ is product code: only tests/, __graft_entry__.smoke()
+ * and bench.py's cpu_baseline leg may load it, and only as the checker. The product library
+ * (libsrslte_fec_cuda.so) never links or calls it and has no CPU fallback.
+ *
+ * Parity status: PINNED. Every function here is checked (tests/test_oracle_vs_ref.py, run wherever
+ * /root/reference is mounted) against the unmodified reference objects in oracle/_ref, and on any box
+ * against golden vectors under tests/golden/ that were produced by those objects (oracle/gen_golden.py).
+ *
+ * All arrays are in NATURAL bit order (index x = bit position in the code block); the reference's
+ * sub-block-interleaved ("sb") layout is only an addressing convention (element k of sub-block d at
+ * k*P+d) and is converted at the edges by orc_sb_pos().
+ */
+#ifndef FEC_ORACLE_H
+#define FEC_ORACLE_H
+#include <stdint.h>
+
+#define ORC_MAX_K       6144
+#define ORC_SOFT_SIZE   18600      /* reference softbuffer.h:55 */
+#define ORC_MAX_CB      13
+
+int      orc_cb_index(int K);                      /* cbsegm.c:116-127 */
+int      orc_cb_size(int idx);                     /* cbsegm.c:134-141 */
+int      orc_subblocks(int K);                     /* turbodecoder.c:364-376 (AVX2 build) */
+int      orc_cbsegm(uint32_t tbs, uint32_t *out9); /* cbsegm.c:58-108 */
+uint32_t orc_crc(int type, const uint8_t *bytes, int nbits);        /* crc.c:144-158, crc.h:68-80 */
+int      orc_qpp(int K, uint16_t *fwd, uint16_t *rev);              /* tc_interl_lte.c:78-103 */
+int      orc_qpp_sb(int K, int P, uint16_t *fwd, uint16_t *rev);    /* tc_interl_lte.c:104-112 */
+int      orc_sb_pos(int x, int K, int P);                           /* natural x -> sb position */
+int      orc_rm_table(int K, int rv, uint16_t *tab);                /* rm_turbo.c:164-238 (natural) */
+int      orc_rm_soft_index(int t, int K, int P);                    /* rm_turbo.c:250-264 */
+int      orc_rm_rx(const int16_t *in, int E, int K, int rv, int sb_layout, int16_t *soft); /* rm_turbo.c:378-430 */
+
+/* one constituent MAP decoder run, natural order. tail_x/tail_p: the 3 tail LLRs of this decoder. */
+void orc_map(int K, int P, const int16_t *x, const int16_t *app, const int16_t *par,
+             const int16_t *tail_x, const int16_t *tail_p, int16_t *out);
+
+typedef struct {
+  int      K, P, n_iter;
+  int16_t  syst[ORC_MAX_K + 4], p0[ORC_MAX_K + 4], p1[ORC_MAX_K + 4];
+  int16_t  t_syst[3], t_p0[3], t_app2[3], t_p1[3];
+  int16_t  app1[ORC_MAX_K], app2[ORC_MAX_K], ext1[ORC_MAX_K], ext2[ORC_MAX_K];
+  uint16_t fwd[ORC_MAX_K], rev[ORC_MAX_K];
+} orc_tdec_t;
+
+int  orc_tdec_new_cb_natural(orc_tdec_t *h, int K, const int16_t *in_nat);        /* [s p p']xK + 12 tail */
+int  orc_tdec_new_cb_soft(orc_tdec_t *h, int K, const int16_t *soft);             /* reference soft-buffer layout */
+void orc_tdec_iteration(orc_tdec_t *h, uint8_t *out_bytes, int16_t *llr_nat);     /* turbodecoder_iter.h:73-147 */
+int  orc_tdec_halfits(int K, const int16_t *in_nat, int nof, uint8_t *out_bytes, int16_t *llr_nat);
+int  orc_decode_cb(const int16_t *soft, int K, int max_its, int crc_type, uint8_t *out_bytes, int *nits);
+
+typedef struct {
+  int      max_cb;
+  int16_t  soft[ORC_MAX_CB][ORC_SOFT_SIZE];
+  uint8_t  data[ORC_MAX_CB][ORC_MAX_K / 8];
+  uint8_t  cb_crc[ORC_MAX_CB];
+  uint8_t  tb_crc;
+} orc_softbuffer_t;
+
+void *orc_tb_new(void);
+void  orc_tb_free(void *p);
+void  orc_tb_reset(void *p, uint32_t tbs);                                        /* softbuffer.c:128-151 */
+int   orc_tb_decode(void *p, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits, const int16_t *e_bits,
+                    uint32_t max_its, uint8_t *data, uint8_t *cb_crc_out, uint32_t *cb_its); /* sch.c:307-498 */
+void  orc_tb_get_soft(void *p, int cb, int16_t *out);
+
+/* multithreaded timing harness for bench.py's cpu_baseline leg ("port") */
+double orc_bench_tb_mt(int nthreads, int ntb, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits,
+                       const int16_t *e_bits_all, uint32_t max_its, int reps, uint64_t *out3);
+#endif

@@ -1,0 +1,150 @@
+#!/usr/bin/env python
+"""Generate tests/golden/*.npz from the UNMODIFIED reference objects (oracle/_ref/libsrslte_ref.so).
+
+Run in the container where /root/reference is mounted:   python oracle/gen_golden.py
+Inputs are derived from integer-only generators in tests/_libs.py (bit-identical on every box), so the
+fixtures only need to hold the reference's OUTPUTS (plus encoder bits, which need the reference encoder).
+"""
+import ctypes as C
+import os
+import sys
+import zlib
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+from _libs import ALL_K, P, int_awgn_llr, int_gauss, ref  # noqa: E402
+
+R = ref()
+assert R is not None, "needs oracle/_ref (make -C oracle ref)"
+OUT = os.path.join(ROOT, "tests", "golden")
+os.makedirs(OUT, exist_ok=True)
+
+
+def crc32(a):
+    return zlib.crc32(np.ascontiguousarray(a).tobytes()) & 0xFFFFFFFF
+
+
+def gen_tdec():
+    """srslte_tdec_iteration snapshots on natural-layout inputs (turbodecoder_test path, AUTO impl)."""
+    out = {}
+    cases = []
+    for K, kind, par, nof in [(40, "awgn", 900, 6), (104, "rand", 600, 8), (400, "awgn", 800, 8), (408, "awgn", 700, 8),
+                              (512, "rand", 6000, 8), (800, "awgn", 900, 8), (816, "awgn", 800, 8), (1024, "rand", 30000, 8),
+                              (2048, "awgn", 700, 8), (5824, "awgn", 620, 8), (6144, "awgn", 1540, 4), (6144, "awgn", 800, 8),
+                              (6144, "rand", 30000, 8)]:
+        seed = 1000 + len(cases)
+        if kind == "awgn":
+            bits = (int_gauss(K, seed) & 1).astype(np.uint8)
+            coded = np.zeros(3 * K + 12, np.uint8)
+            R.ref_encode_cb(K, P(bits), P(coded))
+            inp = int_awgn_llr(coded, par, seed + 1)
+            out[f"coded_{len(cases)}"] = np.packbits(coded)
+        else:
+            inp = (int_gauss(3 * K + 12, seed) % (2 * par + 1) - par).astype(np.int16)
+        ob = np.zeros((nof, K // 8), np.uint8)
+        ol = np.zeros((nof, K), np.int16)
+        assert R.ref_tdec_halfits(K, P(inp), nof, 0, P(ob), P(ol)) == 0
+        out[f"bytes_{len(cases)}"] = ob
+        out[f"llrcrc_{len(cases)}"] = np.array([crc32(ol[n]) for n in range(nof)], np.uint32)
+        if K <= 1024:
+            out[f"llr_{len(cases)}"] = ol
+        out[f"incrc_{len(cases)}"] = np.array([crc32(inp)], np.uint32)
+        cases.append((K, 0 if kind == "awgn" else 1, par, nof, seed))
+    out["cases"] = np.array(cases, np.int64)
+    np.savez_compressed(os.path.join(OUT, "tdec.npz"), **out)
+
+
+def gen_tables():
+    """CRC KATs, QPP and RM tables as checksums over all 188 K (x 4 rv)."""
+    out = {}
+    qpp = []
+    for K in ALL_K:
+        for Pn in (1, 8, 16):
+            if Pn > 1 and K % Pn:
+                continue
+            f, r = np.zeros(K, np.uint16), np.zeros(K, np.uint16)
+            R.ref_interleaver(K, Pn, P(f), P(r))
+            qpp.append((K, Pn, crc32(f), crc32(r)))
+    out["qpp"] = np.array(qpp, np.int64)
+    rm = []
+    for K in ALL_K:
+        idx = R.ref_cb_index(K)
+        for rv in range(4):
+            for sb in (0, 1):
+                for E in (3 * K + 12, 2 * K + 6, 5 * K):
+                    e = (int_gauss(E, K * 8 + rv) % 2001 - 1000).astype(np.int16)
+                    s = (int_gauss(18600, K) % 20001 - 10000).astype(np.int16)
+                    assert R.ref_rm_rx(P(e), E, idx, rv, sb, P(s)) == 0
+                    rm.append((K, rv, sb, E, crc32(s)))
+    out["rm"] = np.array(rm, np.int64)
+    crc = []
+    for n in (8, 24, 40, 5000, 5824, 6144, 75376, 75400):
+        d = (int_gauss(n // 8, n) & 255).astype(np.uint8)
+        crc.append((n, R.ref_crc(0, P(d), n), R.ref_crc(1, P(d), n)))
+    out["crc"] = np.array(crc, np.int64)
+    seg = []
+    for tbs in list(range(16, 3000, 8)) + list(range(3000, 150000, 104)) + [75376, 149776]:
+        o = np.zeros(9, np.uint32)
+        ret = R.ref_cbsegm(tbs, P(o))
+        seg.append([tbs, ret] + [int(x) for x in o])
+    out["cbsegm"] = np.array(seg, np.int64)
+    np.savez_compressed(os.path.join(OUT, "tables.npz"), **out)
+
+
+def gen_tb():
+    """srslte_dlsch_encode -> integer AWGN -> srslte_dlsch_decode sequences (HARQ rv order 0,2,3,1)."""
+    out = {}
+    cases = []
+    for tbs, Qm, nbits, sigma, max_its, ntx in [(75376, 6, 90000, 450, 8, 1), (75376, 6, 90000, 620, 8, 4),
+                                                (75376, 6, 86400, 500, 8, 2), (75376, 6, 90000, 0, 10, 1),
+                                                (1000, 2, 2400, 700, 8, 2), (16, 2, 288, 900, 10, 1),
+                                                (6200, 4, 9600, 750, 8, 2), (12216, 2, 14400, 950, 8, 4),
+                                                (3240, 2, 14400, 1300, 8, 3)]:
+        ci = len(cases)
+        seed = 5000 + 10 * ci
+        t = C.c_void_p(R.ref_tb_new(100))
+        data = np.zeros(tbs // 8 + 3 + 1024, np.uint8)
+        data[: tbs // 8] = (int_gauss(tbs // 8, seed) & 255).astype(np.uint8)
+        R.ref_tb_reset(t, tbs)
+        ntx_done = 0
+        for tx, rv in enumerate([0, 2, 3, 1][:ntx]):
+            e = np.zeros(nbits, np.uint8)
+            assert R.ref_tb_encode(t, tbs, Qm, rv, nbits, P(data), P(e)) == 0
+            llr = int_awgn_llr(e, sigma, seed + 1 + tx) if sigma else (700 * (2 * e.astype(np.int16) - 1)).astype(np.int16)
+            d = np.zeros(tbs // 8 + 3 + 1024, np.uint8)
+            crc, its = np.zeros(13, np.uint8), np.zeros(13, np.uint32)
+            d2 = np.zeros_like(d)
+            ret = R.ref_tb_decode_detail(t, tbs, Qm, rv, nbits, P(llr), max_its, P(d), P(crc), P(its))
+            out[f"e_{ci}_{tx}"] = np.packbits(e)
+            out[f"data_{ci}_{tx}"] = d[: tbs // 8 + 3].copy()
+            out[f"crc_{ci}_{tx}"] = crc
+            out[f"its_{ci}_{tx}"] = its
+            out[f"ret_{ci}_{tx}"] = np.array([ret], np.int64)
+            seg = np.zeros(9, np.uint32)
+            R.ref_cbsegm(tbs, P(seg))
+            sc = []
+            for cb in range(int(seg[1])):
+                s = np.zeros(18600, np.int16)
+                R.ref_tb_get_soft(t, cb, P(s))
+                K = int(seg[2]) if cb < int(seg[6]) else int(seg[3])
+                sc.append(crc32(s[:3 * K + 12]) if R.ref_subblocks(K) == 0 else
+                          crc32(np.concatenate([s[0:K], s[K + 32:2 * K + 32], s[2 * K + 64:3 * K + 64], s[3 * K + 96:3 * K + 108]])))
+            out[f"softcrc_{ci}_{tx}"] = np.array(sc, np.uint32)
+            ntx_done += 1
+            if ret == 0:
+                break
+        out[f"tbdata_{ci}"] = data[: tbs // 8].copy()
+        cases.append((tbs, Qm, nbits, sigma, max_its, ntx_done, seed))
+        R.ref_tb_free(t)
+    out["cases"] = np.array(cases, np.int64)
+    np.savez_compressed(os.path.join(OUT, "tb.npz"), **out)
+
+
+if __name__ == "__main__":
+    gen_tdec()
+    gen_tables()
+    gen_tb()
+    for f in sorted(os.listdir(OUT)):
+        print(f, os.path.getsize(os.path.join(OUT, f)))

@@ -144,14 +144,18 @@ int ref_tdec_halfits(int K, const int16_t *in_nat, int nof, int mode, uint8_t *o
  * Returns 1 if CRC OK else 0; *nits = half-iterations run. */
 int ref_decode_cb(int16_t *soft, int K, int max_its, int crc_type, uint8_t *out_bytes, int *nits)
 {
+  int16_t *al = srslte_vec_malloc(sizeof(int16_t) * SOFTBUFFER_SIZE);   /* the decoder uses aligned SIMD loads */
+  memcpy(al, soft, sizeof(int16_t) * SOFTBUFFER_SIZE);
   srslte_tdec_new_cb(&g_tdec, (uint32_t)K);
   int n = 0, ok = 0;
   do {
-    srslte_tdec_iteration(&g_tdec, soft, out_bytes);
+    srslte_tdec_iteration(&g_tdec, al, out_bytes);
     n++;
     if (!srslte_crc_checksum_byte(&g_crc[crc_type ? 1 : 0], out_bytes, K)) ok = 1;
   } while (n < max_its && !ok);
   *nits = n;
+  memcpy(soft, al, sizeof(int16_t) * SOFTBUFFER_SIZE);
+  free(al);
   return ok;
 }
 

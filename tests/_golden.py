@@ -1,0 +1,54 @@
+"""Readers for tests/golden/*.npz (produced by oracle/gen_golden.py from the unmodified reference)."""
+import os
+import zlib
+
+import numpy as np
+
+from _libs import int_awgn_llr, int_gauss
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def crc32(a):
+    return zlib.crc32(np.ascontiguousarray(a).tobytes()) & 0xFFFFFFFF
+
+
+def tdec_cases():
+    """yield dict(K, inp int16[3K+12], nof, bytes[nof][K/8], llrcrc[nof], llr or None)"""
+    z = np.load(os.path.join(GOLD, "tdec.npz"))
+    for i, (K, kind, par, nof, seed) in enumerate(z["cases"]):
+        K, par, nof, seed = int(K), int(par), int(nof), int(seed)
+        if kind == 0:
+            coded = np.unpackbits(z[f"coded_{i}"])[: 3 * K + 12]
+            inp = int_awgn_llr(coded, par, seed + 1)
+        else:
+            inp = (int_gauss(3 * K + 12, seed) % (2 * par + 1) - par).astype(np.int16)
+        assert crc32(inp) == int(z[f"incrc_{i}"][0]), "input generator drifted"
+        yield dict(K=K, inp=inp, nof=nof, bytes=z[f"bytes_{i}"], llrcrc=z[f"llrcrc_{i}"],
+                   llr=z[f"llr_{i}"] if f"llr_{i}" in z.files else None, id=f"K{K}-{'awgn' if kind == 0 else 'rand'}{par}")
+
+
+def tb_cases():
+    """yield dict(tbs,Qm,nbits,max_its, tx=[dict(rv, llr, data, crc, its, ret, softcrc)], tbdata)"""
+    z = np.load(os.path.join(GOLD, "tb.npz"))
+    for ci, (tbs, Qm, nbits, sigma, max_its, ntx, seed) in enumerate(z["cases"]):
+        tbs, Qm, nbits, sigma, max_its, ntx, seed = (int(v) for v in (tbs, Qm, nbits, sigma, max_its, ntx, seed))
+        txs = []
+        for tx in range(ntx):
+            e = np.unpackbits(z[f"e_{ci}_{tx}"])[:nbits]
+            llr = int_awgn_llr(e, sigma, seed + 1 + tx) if sigma else (700 * (2 * e.astype(np.int16) - 1)).astype(np.int16)
+            txs.append(dict(rv=[0, 2, 3, 1][tx], llr=llr, data=z[f"data_{ci}_{tx}"], crc=z[f"crc_{ci}_{tx}"],
+                            its=z[f"its_{ci}_{tx}"], ret=int(z[f"ret_{ci}_{tx}"][0]), softcrc=z[f"softcrc_{ci}_{tx}"]))
+        yield dict(tbs=tbs, Qm=Qm, nbits=nbits, max_its=max_its, tx=txs, tbdata=z[f"tbdata_{ci}"],
+                   id=f"tbs{tbs}-s{sigma}-n{nbits}")
+
+
+def tables():
+    return np.load(os.path.join(GOLD, "tables.npz"))
+
+
+def soft_crc_ref_layout(s, K, P):
+    """checksum of a reference-layout soft buffer over LUT-addressed positions only (SURVEY trap 7)"""
+    if P == 0:
+        return crc32(s[: 3 * K + 12])
+    return crc32(np.concatenate([s[0:K], s[K + 32:2 * K + 32], s[2 * K + 64:3 * K + 64], s[3 * K + 96:3 * K + 108]]))
