@@ -1,0 +1,179 @@
+"""empower-srslte_b200 — Python host mirror of libsrslte_fec_cuda (ctypes over the C ABI in include/).
+
+The package holds only what the hot path needs: ``csrc/`` (CUDA kernels + C ABI) and this thin binding,
+which mirrors the reference's operator interface for the path (``srslte_dlsch_decode`` ->
+:meth:`FecCuda.decode_tbs`, ``srslte_tdec_run_all`` -> :meth:`FecCuda.decode_cbs`,
+``srslte_rm_turbo_rx_lut_`` -> :meth:`FecCuda.rm_rx`). There is no CPU fallback: constructing
+:class:`FecCuda` without the built extension or without a B200 raises.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libsrslte_fec_cuda.so")
+CSRC = os.path.join(HERE, "csrc")
+SOURCES = ["fec_kernels.cu", "fec_cuda_api.cu", "fec_compat.cu", "fec_tables.c"]
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-Xcompiler", "-fPIC", "-shared"]
+
+MAX_CB = 13
+F_DEVICE_IO = 1
+F_NO_EARLY_STOP = 2
+
+
+class TbDesc(C.Structure):
+    """fec_cuda_tb_t (include/srslte_fec_cuda.h)"""
+    _fields_ = [("tbs", C.c_uint32), ("Qm", C.c_uint32), ("rv", C.c_uint32), ("nof_e_bits", C.c_uint32),
+                ("max_its", C.c_uint32), ("softbuffer", C.c_uint32), ("new_data", C.c_uint32), ("reserved", C.c_uint32),
+                ("e_bits", C.c_void_p), ("data", C.c_void_p),
+                ("ret", C.c_int32), ("avg_its", C.c_uint32),
+                ("cb_crc", C.c_uint8 * MAX_CB), ("cb_its", C.c_uint8 * MAX_CB), ("pad", C.c_uint8 * 6)]
+
+
+class CbDesc(C.Structure):
+    """fec_cuda_cb_t"""
+    _fields_ = [("K", C.c_uint32), ("max_its", C.c_uint32), ("crc_type", C.c_uint32), ("reserved", C.c_uint32),
+                ("llr", C.c_void_p), ("out", C.c_void_p), ("its", C.c_uint32), ("crc_ok", C.c_uint32)]
+
+
+def build(force=False):
+    """Compile every CUDA source for sm_100a into the in-tree shared library (nvcc cross-compiles on CPU)."""
+    srcs = [os.path.join(CSRC, s) for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
+    deps = srcs + [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))]
+    deps.append(os.path.join(os.path.dirname(HERE), "include", "srslte_fec_cuda.h"))
+    if not force and os.path.exists(LIB_PATH) and all(os.path.getmtime(d) <= os.path.getmtime(LIB_PATH) for d in deps if os.path.exists(d)):
+        return LIB_PATH
+    subprocess.check_call(["nvcc"] + NVCC_FLAGS + ["-o", LIB_PATH] + srcs)
+    return LIB_PATH
+
+
+_lib = None
+
+
+def load():
+    """dlopen the C-ABI library; raises if it has not been built (no fallback of any kind)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(f"{LIB_PATH} missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                               "(the CUDA extension is mandatory, there is no CPU path)")
+        lib = C.CDLL(LIB_PATH)
+        lib.fec_cuda_create.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_uint32]
+        lib.fec_cuda_destroy.argtypes = [C.c_void_p]
+        lib.fec_cuda_last_error.argtypes = [C.c_void_p]
+        lib.fec_cuda_last_error.restype = C.c_char_p
+        lib.fec_cuda_stream.argtypes = [C.c_void_p]
+        lib.fec_cuda_stream.restype = C.c_void_p
+        lib.fec_cuda_launch_count.argtypes = [C.c_void_p]
+        lib.fec_cuda_launch_count.restype = C.c_uint64
+        lib.fec_cuda_softbuffer_alloc.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_uint32)]
+        lib.fec_cuda_softbuffer_reset.argtypes = [C.c_void_p, C.c_uint32]
+        lib.fec_cuda_softbuffer_read_ref_layout.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]
+        lib.fec_cuda_decode_tbs.argtypes = [C.c_void_p, C.POINTER(TbDesc), C.c_uint32, C.c_uint32]
+        lib.fec_cuda_decode_cbs.argtypes = [C.c_void_p, C.POINTER(CbDesc), C.c_uint32, C.c_uint32]
+        lib.fec_cuda_rm_rx.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p]
+        lib.fec_cuda_cbsegm.argtypes = [C.c_uint32, C.POINTER(C.c_uint32)]
+        _lib = lib
+    return _lib
+
+
+def cbsegm(tbs):
+    """srslte_cbsegm: dict(F,C,K1,K2,K1_idx,K2_idx,C1,C2,tbs) or None on error"""
+    o = (C.c_uint32 * 9)()
+    if load().fec_cuda_cbsegm(tbs, o):
+        return None
+    return dict(zip(("F", "C", "K1", "K2", "K1_idx", "K2_idx", "C1", "C2", "tbs"), [int(v) for v in o]))
+
+
+class FecCuda:
+    """One decode context = one CUDA device + one stream (mirrors one srslte_sch_t per worker thread)."""
+
+    def __init__(self, device=0, max_tbs=1024):
+        self.lib = load()
+        self.h = C.c_void_p()
+        rc = self.lib.fec_cuda_create(C.byref(self.h), device, max_tbs)
+        if rc != 0:
+            raise RuntimeError(f"fec_cuda_create failed ({rc}): no usable sm_100a device; this library has no CPU path")
+
+    def close(self):
+        if self.h:
+            self.lib.fec_cuda_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def stream(self):
+        return self.lib.fec_cuda_stream(self.h)
+
+    @property
+    def launches(self):
+        return int(self.lib.fec_cuda_launch_count(self.h))
+
+    def error(self):
+        return self.lib.fec_cuda_last_error(self.h).decode()
+
+    def softbuffer_alloc(self, n):
+        first = C.c_uint32()
+        rc = self.lib.fec_cuda_softbuffer_alloc(self.h, n, C.byref(first))
+        if rc:
+            raise RuntimeError(f"softbuffer_alloc: {rc} {self.error()}")
+        return int(first.value)
+
+    def softbuffer_reset(self, sb):
+        return self.lib.fec_cuda_softbuffer_reset(self.h, sb)
+
+    def softbuffer_read(self, sb, cb, K):
+        out = np.zeros(18600, np.int16)
+        rc = self.lib.fec_cuda_softbuffer_read_ref_layout(self.h, sb, cb, K, out.ctypes.data_as(C.c_void_p))
+        if rc:
+            raise RuntimeError(f"softbuffer_read: {rc} {self.error()}")
+        return out
+
+    def decode_tbs(self, descs, flags=0):
+        """descs: ctypes array of TbDesc (filled in place). Raises on a batch-level failure."""
+        rc = self.lib.fec_cuda_decode_tbs(self.h, descs, len(descs), flags)
+        if rc:
+            raise RuntimeError(f"fec_cuda_decode_tbs: {rc} {self.error()}")
+        return descs
+
+    def decode_tb(self, tbs, Qm, rv, e_bits, softbuffer, new_data, max_its=8, flags=0):
+        """single transport block convenience (the srslte_dlsch_decode call shape). e_bits: int16 numpy."""
+        e = np.ascontiguousarray(e_bits, dtype=np.int16)
+        data = np.zeros(tbs // 8 + 3 + 768, np.uint8)
+        d = (TbDesc * 1)()
+        d[0].tbs, d[0].Qm, d[0].rv, d[0].nof_e_bits, d[0].max_its = tbs, Qm, rv, e.size, max_its
+        d[0].softbuffer, d[0].new_data = softbuffer, int(new_data)
+        d[0].e_bits, d[0].data = e.ctypes.data, data.ctypes.data
+        self.decode_tbs(d, flags)
+        Cn = cbsegm(tbs)["C"] if tbs else 0
+        return dict(ret=int(d[0].ret), data=data[: tbs // 8 + 3], avg_its=int(d[0].avg_its),
+                    cb_crc=np.array(d[0].cb_crc[:Cn], np.uint8), cb_its=np.array(d[0].cb_its[:Cn], np.uint32))
+
+    def decode_cbs(self, K_list, llr_list, max_its, crc_type=1, early_stop=True):
+        """bare code blocks from natural-layout LLRs; returns list of dict(out, its, crc_ok)"""
+        n = len(K_list)
+        d = (CbDesc * n)()
+        keep = []
+        for i, (K, llr) in enumerate(zip(K_list, llr_list)):
+            a = np.ascontiguousarray(llr, dtype=np.int16)
+            o = np.zeros(K // 8, np.uint8)
+            keep.append((a, o))
+            d[i].K, d[i].max_its, d[i].crc_type = K, max_its, crc_type
+            d[i].llr, d[i].out = a.ctypes.data, o.ctypes.data
+        rc = self.lib.fec_cuda_decode_cbs(self.h, d, n, 0 if early_stop else F_NO_EARLY_STOP)
+        if rc:
+            raise RuntimeError(f"fec_cuda_decode_cbs: {rc} {self.error()}")
+        return [dict(out=keep[i][1], its=int(d[i].its), crc_ok=int(d[i].crc_ok)) for i in range(n)]
+
+    def rm_rx(self, e, cb_idx, rv, soft, sb_layout=True):
+        """srslte_rm_turbo_rx_lut_(in, soft, E, cb_idx, rv, enable_input_tdec): soft (18600 int16) updated in place"""
+        e = np.ascontiguousarray(e, dtype=np.int16)
+        assert soft.dtype == np.int16 and soft.size >= 18600 and soft.flags.c_contiguous
+        return self.lib.fec_cuda_rm_rx(self.h, e.ctypes.data, e.size, cb_idx, rv, int(sb_layout), soft.ctypes.data)

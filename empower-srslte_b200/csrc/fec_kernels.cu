@@ -1,0 +1,632 @@
+/*
+ * fec_kernels.cu — hand-written sm_100a kernels of the transport-block decode path.
+ *
+ *   fec_tdec_win_kernel<P>   windowed max-log-MAP turbo decoder with in-kernel half-iteration driver,
+ *                            QPP (de)interleaving, hard decision, fused CRC and early stop
+ *                            (replaces tdec_win{sse16,avx16}_dec + run_tdec_iteration_16bit + the CRC loop
+ *                             of decode_tb_cb: turbodecoder_win.h:310-586, turbodecoder_iter.h:73-147, sch.c:361-391)
+ *   fec_tdec_small_kernel    non-windowed wrapping decoder for K<=400 (turbodecoder_sse.c:105-353)
+ *   fec_rm_rx_kernel         rate de-matching + HARQ combine as a gather (rm_turbo.c:378-430)
+ *   fec_extract_kernel       natural [s p p'] input -> device layout (turbodecoder_win.h:634-674)
+ *   fec_tb_assemble_kernel   code-block concatenation + CRC24A (sch.c:396-418, 478-485)
+ *
+ * Arithmetic contract (bit-exact with the reference's AVX2 build): see DESIGN.md section 3.
+ * State metrics are kept as BIASED 32-bit values u = v + 32768 in [0,65535] so that the reference's
+ * saturating int16 add is ONE instruction: VIADDMNMX.RELU (max(min(u+g,65535),0)).
+ */
+#include "fec_kernels.cuh"
+#include <stdio.h>
+
+#define BIAS   32768
+#define NEGINF (BIAS - 10000)
+#define S_CH   FEC_WIN_CHUNK
+
+__device__ __forceinline__ int sadd(int u, int g) { return __viaddmin_s32_relu(u, g, 65535); }
+__device__ __forceinline__ int sat16(int v) { return max(min(v, 32767), -32768); }
+__device__ __forceinline__ int max8(const int *v)
+{
+  return max(__vimax3_s32(v[0], v[1], v[2]), __vimax3_s32(__vimax3_s32(v[3], v[4], v[5]), v[6], v[7]));
+}
+
+/* pack 8 biased metrics as 8 true int16 (u ^ 0x8000 is the two's-complement int16 of u-32768) */
+__device__ __forceinline__ uint4 pack8(const int *o)
+{
+  uint4 r;
+  r.x = __byte_perm(o[0], o[1], 0x5410) ^ 0x80008000u;
+  r.y = __byte_perm(o[2], o[3], 0x5410) ^ 0x80008000u;
+  r.z = __byte_perm(o[4], o[5], 0x5410) ^ 0x80008000u;
+  r.w = __byte_perm(o[6], o[7], 0x5410) ^ 0x80008000u;
+  return r;
+}
+/* sign-extend the low int16 of a word: PRMT with the sign-replicate selector bit (__byte_perm masks it off) */
+__device__ __forceinline__ int sext_lo(uint32_t w)
+{
+  int r;
+  asm("prmt.b32 %0, %1, 0, 0x9910;" : "=r"(r) : "r"(w));
+  return r;
+}
+/* unpack to TRUE signed values */
+__device__ __forceinline__ void unpack8_true(uint4 p, int *b)
+{
+  b[0] = sext_lo(p.x); b[1] = ((int)p.x) >> 16;
+  b[2] = sext_lo(p.y); b[3] = ((int)p.y) >> 16;
+  b[4] = sext_lo(p.z); b[5] = ((int)p.z) >> 16;
+  b[6] = sext_lo(p.w); b[7] = ((int)p.w) >> 16;
+}
+
+/* turbodecoder_win.h:244-261 (normalize_period 2): every even k != 0, subtract state 0, saturating */
+__device__ __forceinline__ void win_norm(int k, int *o)
+{
+  if (((k & 1) == 0) && k != 0) {
+    const int t = BIAS - o[0];
+#pragma unroll
+    for (int i = 1; i < 8; i++) o[i] = sadd(o[i], t);
+    o[0] = BIAS;
+  }
+}
+
+/* backward step (turbodecoder_win.h:397-418); x,y,xy are TRUE signed branch metrics */
+__device__ __forceinline__ void win_beta_step(int *o, int x, int y)
+{
+  const int xy = sat16(x + y);
+  int n[8];
+  n[0] = max(sadd(o[4], xy), o[0]);
+  n[1] = max(o[4], sadd(o[0], xy));
+  n[2] = max(sadd(o[5], y), sadd(o[1], x));
+  n[3] = max(sadd(o[5], x), sadd(o[1], y));
+  n[4] = max(sadd(o[6], x), sadd(o[2], y));
+  n[5] = max(sadd(o[6], y), sadd(o[2], x));
+  n[6] = max(o[7], sadd(o[3], xy));
+  n[7] = max(sadd(o[7], xy), o[3]);
+#pragma unroll
+  for (int i = 0; i < 8; i++) o[i] = n[i];
+}
+
+/* forward branches (turbodecoder_win.h:521-539): m = bit 0 hypothesis, n = bit 1 hypothesis */
+__device__ __forceinline__ void win_alpha_branches(const int *o, int x, int y, int *m, int *n)
+{
+  const int xy = sat16(x + y);
+  m[0] = o[0];           m[1] = sadd(o[3], y); m[2] = sadd(o[4], y); m[3] = o[7];
+  m[4] = o[1];           m[5] = sadd(o[2], y); m[6] = sadd(o[5], y); m[7] = o[6];
+  n[0] = sadd(o[1], xy); n[1] = sadd(o[2], x); n[2] = sadd(o[5], x); n[3] = sadd(o[6], xy);
+  n[4] = sadd(o[0], xy); n[5] = sadd(o[3], x); n[6] = sadd(o[4], x); n[7] = sadd(o[7], xy);
+}
+
+struct WinLane {           /* per-lane view of one half-iteration */
+  const int16_t  *S;       /* systematic stream of this lane (ignored when smask == 0) */
+  const int16_t  *Y;       /* parity stream of this lane */
+  const uint32_t *T;       /* step table of this lane and parity */
+  int16_t        *E;       /* extrinsic array of this code block (shared memory) */
+  int             smask;   /* -1: x = sat(S + E) (decoder 1);  0: x = E (decoder 2) */
+};
+
+__device__ __forceinline__ void win_load_xy(const WinLane &w, int k, int &x, int &y)
+{
+  const uint32_t t = __ldg(w.T + k);
+  const int e = w.E[t & 0xFFFFu];
+  const int s = (int)__ldg(w.S + k) & w.smask;
+  x = sat16(s + e);
+  y = (int)__ldg(w.Y + k);
+}
+
+size_t fec_win_smem_bytes(const fec_geom_t *g, uint32_t slots)
+{
+  const size_t nthr = (size_t)slots * g->P;
+  const size_t nck = (g->L + S_CH - 1) / S_CH, nw = (g->L + 31) / 32;
+  size_t b = 0;
+  b += (((size_t)slots * g->P * g->LpE * 2) + 15) & ~(size_t)15;   /* E */
+  b += nck * nthr * 16;                                            /* beta checkpoints */
+  b += (size_t)(S_CH - 1) * nthr * 16;                             /* beta chunk buffer */
+  b += nw * nthr * 4;                                              /* decision words per lane */
+  b += (size_t)slots * ((g->K + 31) / 32) * 4;                     /* output assembly */
+  return b;
+}
+
+uint32_t fec_win_pick_slots(const fec_geom_t *g)
+{
+  uint32_t s = FEC_WIN_THREADS / g->P;
+  while (s > 1 && fec_win_smem_bytes(g, s) > 220 * 1024) s--;
+  return s;
+}
+
+template <int P>
+__global__ void __launch_bounds__(FEC_WIN_THREADS, 1) fec_tdec_win_kernel(const FecDecodeArgs a)
+{
+  extern __shared__ __align__(16) unsigned char smem[];
+  __shared__ int s_cb[FEC_WIN_THREADS / 8], s_n[FEC_WIN_THREADS / 8], s_fresh[FEC_WIN_THREADS / 8];
+  __shared__ int s_empty;
+
+  const int tid = threadIdx.x, nthr = blockDim.x;
+  const int slot = tid / P, d = tid % P, slots = nthr / P;
+  const int K = a.g.K, L = a.g.L, Lp = a.g.Lp, LpE = a.g.LpE, SS = a.g.SS;
+  const int nck = (L + S_CH - 1) / S_CH, nw = (L + 31) / 32, kw = (K + 31) / 32;
+  const unsigned lane_mask = (P == 32) ? 0xFFFFFFFFu : (((1u << P) - 1u) << ((tid & 31) & ~(P - 1)));
+
+  size_t off = 0;
+  int16_t *E = (int16_t *)smem + (size_t)slot * P * LpE;
+  off += (((size_t)slots * P * LpE * 2) + 15) & ~(size_t)15;
+  uint4 *ckpt = (uint4 *)(smem + off);  off += (size_t)nck * nthr * 16;
+  uint4 *chunk = (uint4 *)(smem + off); off += (size_t)(S_CH - 1) * nthr * 16;
+  uint32_t *bitsw = (uint32_t *)(smem + off); off += (size_t)nw * nthr * 4;
+  uint32_t *outw = (uint32_t *)(smem + off) + (size_t)slot * kw;
+
+  if (d == 0) { s_cb[slot] = -1; s_fresh[slot] = 0; }
+  if (tid == 0) s_empty = 0;
+  __syncthreads();
+
+  for (;;) {
+    /* ---- refill idle slots from the work queue ---- */
+    if (d == 0 && s_cb[slot] < 0 && !s_empty) {
+      const unsigned q = atomicAdd(a.queue, 1u);
+      if (q < a.ncb) { s_cb[slot] = (int)q; s_n[slot] = 0; s_fresh[slot] = 1; }
+      else s_empty = 1;
+    }
+    __syncthreads();
+    const int cb = s_cb[slot];
+    if (!__syncthreads_or(cb >= 0)) break;
+    if (cb >= 0 && s_fresh[slot]) {               /* apriori = 0 before the first half-iteration */
+      uint32_t *e32 = (uint32_t *)E;
+      for (int i = d; i < P * LpE / 2; i += P) e32[i] = 0;
+    }
+    __syncthreads();
+    if (d == 0) s_fresh[slot] = 0;
+
+    int done = 0;
+    if (cb >= 0) {
+      const FecCbDesc desc = a.cbs[cb];
+      const int n = s_n[slot], par = n & 1;
+      WinLane w;
+      w.S = desc.soft + d * Lp;
+      w.Y = desc.soft + (1 + par) * SS + d * Lp;
+      w.T = a.step_tab + par * SS + d * Lp;
+      w.E = E;
+      w.smask = par ? 0 : -1;
+      const int16_t *tail = desc.soft + 3 * SS + (par ? 6 : 0);   /* x at [0,2,4], parity at [1,3,5] */
+      const uint32_t *R = a.crcpow[desc.crc_sel];
+
+      int o[8], x, y;
+      /* ---- beta warm-up over the first 40 symbols of this sub-block (turbodecoder_win.h:321-384) ---- */
+#pragma unroll
+      for (int i = 0; i < 8; i++) o[i] = NEGINF;
+      for (int k = 39; k >= 0; k--) { win_load_xy(w, k, x, y); win_beta_step(o, x, y); win_norm(k, o); }
+      /* lane shift: sub-block d starts from the estimate of sub-block d+1 (:347-355) */
+#pragma unroll
+      for (int i = 0; i < 8; i++) o[i] = __shfl_down_sync(lane_mask, o[i], 1, P);
+      if (d == P - 1) {   /* known end state through the 3 tail steps, WRAPPING adds (:263-307) */
+        int t[8];
+        t[0] = 0;
+#pragma unroll
+        for (int i = 1; i < 8; i++) t[i] = -10000;
+        for (int k = 2; k >= 0; k--) {
+          const int tx = tail[2 * k], ty = tail[2 * k + 1];
+          const int txy = (short)(tx + ty);
+          int nn[8];
+          nn[0] = max((int)(short)(t[4] + txy), t[0]);
+          nn[1] = max(t[4], (int)(short)(t[0] + txy));
+          nn[2] = max((int)(short)(t[5] + ty), (int)(short)(t[1] + tx));
+          nn[3] = max((int)(short)(t[5] + tx), (int)(short)(t[1] + ty));
+          nn[4] = max((int)(short)(t[6] + tx), (int)(short)(t[2] + ty));
+          nn[5] = max((int)(short)(t[6] + ty), (int)(short)(t[2] + tx));
+          nn[6] = max(t[7], (int)(short)(t[3] + txy));
+          nn[7] = max((int)(short)(t[7] + txy), t[3]);
+#pragma unroll
+          for (int i = 0; i < 8; i++) t[i] = nn[i];
+        }
+#pragma unroll
+        for (int i = 0; i < 8; i++) o[i] = t[i] + BIAS;
+      }
+      /* ---- beta main pass, checkpoint every S_CH steps (store is pre-normalisation, :419-432) ---- */
+      ckpt[tid] = pack8(o);
+      {
+        int c = 1, knext = L - S_CH;
+        for (int k = L - 1; k >= 0; k--) {
+          win_load_xy(w, k, x, y);
+          win_beta_step(o, x, y);
+          if (k == knext && c < nck) { ckpt[c * nthr + tid] = pack8(o); c++; knext -= S_CH; }
+          win_norm(k, o);
+        }
+      }
+      /* ---- alpha warm-up over the last 40 symbols (:459-506) ---- */
+      int m[8], nb[8];
+#pragma unroll
+      for (int i = 0; i < 8; i++) o[i] = NEGINF;
+      for (int k = 0; k < 40; k++) {
+        win_load_xy(w, L - 40 + k, x, y);
+        win_alpha_branches(o, x, y, m, nb);
+#pragma unroll
+        for (int i = 0; i < 8; i++) o[i] = max(m[i], nb[i]);
+        win_norm(k, o);
+      }
+#pragma unroll
+      for (int i = 0; i < 8; i++) o[i] = __shfl_up_sync(lane_mask, o[i], 1, P);
+      if (d == 0) {
+        o[0] = BIAS;
+#pragma unroll
+        for (int i = 1; i < 8; i++) o[i] = NEGINF;
+      }
+      /* ---- alpha main pass: per chunk, recompute beta from its checkpoint, then alpha + LLR ---- */
+      uint32_t crc = 0, wbits = 0;
+      for (int c = nck - 1; c >= 0; c--) {
+        const int khi = L - c * S_CH, klo = max(0, khi - S_CH);
+        const uint4 ck = ckpt[c * nthr + tid];
+        {
+          int b[8];
+          unpack8_true(ck, b);
+#pragma unroll
+          for (int i = 0; i < 8; i++) b[i] += BIAS;
+          if (c > 0) win_norm(khi, b);
+          for (int k = khi - 1; k > klo; k--) {
+            win_load_xy(w, k, x, y);
+            win_beta_step(b, x, y);
+            chunk[(k - klo - 1) * nthr + tid] = pack8(b);
+            win_norm(k, b);
+          }
+        }
+        for (int k = klo; k < khi; k++) {
+          const uint32_t t = __ldg(w.T + k);
+          const int ea = t & 0xFFFFu, nat = t >> 16;
+          const int e = w.E[ea];
+          x = sat16(((int)__ldg(w.S + k) & w.smask) + e);
+          y = (int)__ldg(w.Y + k);
+          win_alpha_branches(o, x, y, m, nb);
+          int b[8], v0[8], v1[8];
+          unpack8_true((k == khi - 1) ? ck : chunk[(k - klo) * nthr + tid], b);
+#pragma unroll
+          for (int i = 0; i < 8; i++) { v0[i] = sadd(m[i], b[i]); v1[i] = sadd(nb[i], b[i]); }
+          int r = sat16(max8(v1) - max8(v0));
+          if (P == 8) r >>= 1;                       /* divide_output: sse16 only (turbodecoder_win.h:61,565) */
+          w.E[ea] = (int16_t)(r - e);                /* next apriori = LLR - (what this decoder was given), wrapping */
+          if (a.dbg_llr) a.dbg_llr[(size_t)desc.status * FEC_MAX_K + nat] = (int16_t)r;
+          if (r > 0) { crc ^= __ldg(R + (K - 1 - nat)); wbits |= 1u << (k & 31); }
+          if ((k & 31) == 31 || k == L - 1) { bitsw[(k >> 5) * nthr + tid] = wbits; wbits = 0; }
+#pragma unroll
+          for (int i = 0; i < 8; i++) o[i] = max(m[i], nb[i]);
+          win_norm(k, o);
+        }
+      }
+      /* ---- CRC over the K hard decisions of this half-iteration: XOR-reduce over the P lanes ---- */
+#pragma unroll
+      for (int s = P / 2; s > 0; s >>= 1) crc ^= __shfl_xor_sync(lane_mask, crc, s, P);
+      const int n1 = n + 1;
+      const int crc_ok = (crc == 0);
+      done = (crc_ok && !(desc.flags & FEC_F_NO_EARLY)) || (n1 >= (int)desc.max_its);
+      if (done) {
+        /* hard bits -> bytes, natural order, MSB first (turbodecoder_win.h:676-716) */
+        for (int i = d; i < kw; i += P) outw[i] = 0;
+        __syncwarp(lane_mask);
+        for (int k = 0; k < L; k++) {
+          if ((bitsw[(k >> 5) * nthr + tid] >> (k & 31)) & 1u) {
+            const int nat = __ldg(w.T + k) >> 16;
+            atomicOr(&outw[nat >> 5], 1u << (8 * ((nat >> 3) & 3) + 7 - (nat & 7)));
+          }
+        }
+        __syncwarp(lane_mask);
+        const uint8_t *ob = (const uint8_t *)outw;
+        for (int i = d; i < K / 8; i += P) desc.out[i] = ob[i];
+        if (d == 0) { a.status[desc.status].its = (uint32_t)n1; a.status[desc.status].crc_ok = (uint32_t)crc_ok; }
+      }
+      if (d == 0) s_n[slot] = n1;
+    }
+    __syncthreads();
+    if (d == 0 && done) s_cb[slot] = -1;
+  }
+}
+
+/* =====================================================================================================
+ * Non-windowed decoder for K <= 400 (AUTO class 0): one thread per code block, wrapping int16
+ * arithmetic (turbodecoder_sse.c). alpha is stored for every step, beta runs backward with the LLR.
+ * ===================================================================================================== */
+#define W16(v) ((int)(short)(v))
+
+__global__ void fec_tdec_small_kernel(const FecDecodeArgs a)
+{
+  extern __shared__ __align__(16) unsigned char smem[];
+  __shared__ int s_empty;
+  const int tid = threadIdx.x, nthr = blockDim.x;
+  const int K = a.g.K;
+  uint4 *A = (uint4 *)smem;                                        /* [(K+1)][nthr] alpha store */
+  int16_t *E = (int16_t *)(smem + (size_t)(K + 1) * nthr * 16);    /* [K][nthr] */
+  uint8_t *ob = (uint8_t *)(E + (size_t)K * nthr);                 /* [K/8][nthr] */
+  const uint32_t *T0 = a.step_tab;
+  int cb = -1, n = 0;
+  if (tid == 0) s_empty = 0;
+  __syncthreads();
+
+  for (;;) {
+    if (cb < 0 && !s_empty) {
+      const unsigned q = atomicAdd(a.queue, 1u);
+      if (q < a.ncb) { cb = (int)q; n = 0; for (int i = 0; i < K; i++) E[i * nthr + tid] = 0; }
+      else s_empty = 1;
+    }
+    if (!__syncthreads_or(cb >= 0)) break;
+    if (cb >= 0) {
+      const FecCbDesc desc = a.cbs[cb];
+      const int par = n & 1, smask = par ? 0 : -1;
+      const int16_t *S = desc.soft, *Y = desc.soft + (1 + par) * a.g.SS;
+      const uint32_t *T = T0 + par * a.g.SS;
+      const int16_t *tail = desc.soft + 3 * a.g.SS + (par ? 6 : 0);
+      const uint32_t *R = a.crcpow[desc.crc_sel];
+      for (int i = 0; i < K / 8; i++) ob[i * nthr + tid] = 0;
+
+      /* forward recursion (turbodecoder_sse.c:211-297) */
+      int al[8];
+      al[0] = 0;
+#pragma unroll
+      for (int i = 1; i < 8; i++) al[i] = -10000;
+      {
+        int tmp[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) tmp[i] = al[i] + BIAS;
+        A[tid] = pack8(tmp);
+      }
+      for (int k = 0; k < K; k++) {
+        const uint32_t t = __ldg(T + k);
+        const int x = W16(((int)__ldg(S + k) & smask) + E[(t & 0xFFFFu) * nthr + tid]);
+        const int p = (int)__ldg(Y + k);
+        const int g1 = W16(x + p) >> 1, g0 = W16(x - p) >> 1;
+        int nx[8];
+        /* alpha'[j] = max(alpha[SP[j]] + g, alpha[SN[j]] - g), g = g1 for states {0,1,6,7}, g0 for {2,3,4,5} */
+        nx[0] = max(W16(al[1] + g1), W16(al[0] - g1));
+        nx[1] = max(W16(al[2] + g0), W16(al[3] - g0));
+        nx[2] = max(W16(al[5] + g0), W16(al[4] - g0));
+        nx[3] = max(W16(al[6] + g1), W16(al[7] - g1));
+        nx[4] = max(W16(al[0] + g1), W16(al[1] - g1));
+        nx[5] = max(W16(al[3] + g0), W16(al[2] - g0));
+        nx[6] = max(W16(al[4] + g0), W16(al[5] - g0));
+        nx[7] = max(W16(al[7] + g1), W16(al[6] - g1));
+        int tmp[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) { al[i] = nx[i]; tmp[i] = nx[i] + BIAS; }
+        A[(k + 1) * nthr + tid] = pack8(tmp);                       /* stored before normalisation */
+        if ((k & 3) == 3) {
+          const int z = al[0];
+#pragma unroll
+          for (int i = 0; i < 8; i++) al[i] = W16(al[i] - z);
+        }
+      }
+      /* backward recursion + LLR (turbodecoder_sse.c:105-206) */
+      int be[8];
+      be[0] = 0;
+#pragma unroll
+      for (int i = 1; i < 8; i++) be[i] = -10000;
+      uint32_t crc = 0;
+      int cnt = 0;
+      for (int k = K + 2; k >= 0; k--) {
+        int g0, g1, ea = 0, nat = 0, e = 0;
+        if (k >= K) {
+          const int tx = tail[2 * (k - K)], tp = tail[2 * (k - K) + 1];
+          g0 = W16((tx - tp) / 2); g1 = W16((tx + tp) / 2);
+        } else {
+          const uint32_t t = __ldg(T + k);
+          ea = t & 0xFFFFu; nat = t >> 16;
+          e = E[ea * nthr + tid];
+          const int x = W16(((int)__ldg(S + k) & smask) + e);
+          const int p = (int)__ldg(Y + k);
+          g1 = W16(x + p) >> 1; g0 = W16(x - p) >> 1;
+        }
+        /* sp[j] = (beta+g)[BP[j]], sn[j] = (beta-g)[BN[j]], g = g1 for states {0,3,4,7}, g0 for {1,2,5,6} */
+        int sp[8], sn[8];
+        sp[0] = W16(be[4] + g1); sn[0] = W16(be[0] - g1);
+        sp[1] = W16(be[0] + g1); sn[1] = W16(be[4] - g1);
+        sp[2] = W16(be[1] + g0); sn[2] = W16(be[5] - g0);
+        sp[3] = W16(be[5] + g0); sn[3] = W16(be[1] - g0);
+        sp[4] = W16(be[6] + g0); sn[4] = W16(be[2] - g0);
+        sp[5] = W16(be[2] + g0); sn[5] = W16(be[6] - g0);
+        sp[6] = W16(be[3] + g1); sn[6] = W16(be[7] - g1);
+        sp[7] = W16(be[7] + g1); sn[7] = W16(be[3] - g1);
+#pragma unroll
+        for (int i = 0; i < 8; i++) be[i] = max(sp[i], sn[i]);
+        if (k < K) {
+          int av[8];
+          unpack8_true(A[k * nthr + tid], av);
+          int mp = W16(sp[0] + av[0]), mn = W16(sn[0] + av[0]);
+#pragma unroll
+          for (int i = 1; i < 8; i++) { mp = max(mp, W16(sp[i] + av[i])); mn = max(mn, W16(sn[i] + av[i])); }
+          const int r = W16(mp - mn);                              /* hMax() returns 0x7FFF-max: :97-102,178 */
+          E[ea * nthr + tid] = (int16_t)(r - e);
+          if (a.dbg_llr) a.dbg_llr[(size_t)desc.status * FEC_MAX_K + nat] = (int16_t)r;
+          if (r > 0) { crc ^= __ldg(R + (K - 1 - nat)); ob[(nat >> 3) * nthr + tid] |= (uint8_t)(0x80u >> (nat & 7)); }
+          if (++cnt == 4) {
+            cnt = 0;
+            const int z = be[0];
+#pragma unroll
+            for (int i = 0; i < 8; i++) be[i] = W16(be[i] - z);
+          }
+        }
+      }
+      n++;
+      const int crc_ok = (crc == 0);
+      if ((crc_ok && !(desc.flags & FEC_F_NO_EARLY)) || n >= (int)desc.max_its) {
+        for (int i = 0; i < K / 8; i++) desc.out[i] = ob[i * nthr + tid];
+        a.status[desc.status].its = (uint32_t)n;
+        a.status[desc.status].crc_ok = (uint32_t)crc_ok;
+        cb = -1;
+      }
+    }
+  }
+}
+
+static size_t fec_small_smem_per_cb(const fec_geom_t *g) { return (size_t)(g->K + 1) * 16 + (size_t)g->K * 2 + g->K / 8; }
+
+cudaError_t fec_launch_decode(const FecDecodeArgs &a, int sm_count, cudaStream_t st)
+{
+  if (a.ncb == 0) return cudaSuccess;
+  if (a.g.P == 0) {
+    int nthr = (int)((200 * 1024) / fec_small_smem_per_cb(&a.g));
+    if (nthr > 32) nthr = 32;
+    size_t smem = fec_small_smem_per_cb(&a.g) * nthr + 16;
+    int grid = (int)((a.ncb + nthr - 1) / nthr);
+    if (grid > sm_count * 4) grid = sm_count * 4;
+    fec_tdec_small_kernel<<<grid, nthr, smem, st>>>(a);
+    return cudaGetLastError();
+  }
+  const uint32_t slots = a.slots;
+  const size_t smem = fec_win_smem_bytes(&a.g, slots);
+  int grid = (int)((a.ncb + slots - 1) / slots);
+  const int per_sm = (int)((220 * 1024) / (smem + 1024));
+  const int cap = sm_count * (per_sm < 1 ? 1 : per_sm);
+  if (grid > cap) grid = cap;
+  if (a.g.P == 16) fec_tdec_win_kernel<16><<<grid, slots * 16, smem, st>>>(a);
+  else             fec_tdec_win_kernel<8><<<grid, slots * 8, smem, st>>>(a);
+  return cudaGetLastError();
+}
+
+/* =====================================================================================================
+ * Rate de-matching + HARQ combining as a GATHER over soft-buffer positions (rm_turbo.c:378-430 computes
+ * the same sums as a scatter: soft[deinter[i % N]] += e[i]). Thread = 8 consecutive int16 of the slot:
+ * one 16-byte load of the rank table, one 16-byte read-modify-write of the slot, coalesced.
+ * ===================================================================================================== */
+__global__ void __launch_bounds__(256) fec_rm_rx_kernel(const FecRmDesc *descs)
+{
+  const FecRmDesc d = descs[blockIdx.y];
+  const uint32_t o = (blockIdx.x * blockDim.x + threadIdx.x) * 8;
+  if (o >= d.n_out) return;
+  const uint4 rk = *reinterpret_cast<const uint4 *>(d.rank + o);
+  uint4 old = make_uint4(0, 0, 0, 0);
+  if (!d.new_data) old = *reinterpret_cast<const uint4 *>(d.soft + o);
+  const uint32_t rw[4] = {rk.x, rk.y, rk.z, rk.w};
+  uint32_t ow[4] = {old.x, old.y, old.z, old.w};
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    uint32_t res = 0;
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      const uint32_t r = (rw[i] >> (16 * h)) & 0xFFFFu;
+      int acc = (int)((ow[i] >> (16 * h)) & 0xFFFFu);
+      if (r != 0xFFFFu) {
+        uint32_t j = r + d.N - d.off;
+        if (j >= d.N) j -= d.N;
+        for (; j < d.E; j += d.N) acc += (int)__ldg(d.e + j);      /* repeats accumulate when E > 3K+12 */
+      }
+      res |= ((uint32_t)acc & 0xFFFFu) << (16 * h);               /* wrapping int16 */
+    }
+    ow[i] = res;
+  }
+  *reinterpret_cast<uint4 *>(d.soft + o) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+}
+
+cudaError_t fec_launch_rm(const FecRmDesc *descs, uint32_t n, uint32_t max_n_out, cudaStream_t st)
+{
+  if (n == 0) return cudaSuccess;
+  dim3 grid((max_n_out / 8 + 255) / 256, n);
+  fec_rm_rx_kernel<<<grid, 256, 0, st>>>(descs);
+  return cudaGetLastError();
+}
+
+/* natural [s p p'] x K + 12 tail  ->  device layout (srslte_tdec_* level input, force_not_sb path) */
+__global__ void __launch_bounds__(256) fec_extract_kernel(const FecExtractDesc *descs)
+{
+  const FecExtractDesc d = descs[blockIdx.y];
+  const int n_out = 3 * d.g.SS + 16;
+  for (int o = blockIdx.x * blockDim.x + threadIdx.x; o < n_out; o += gridDim.x * blockDim.x) {
+    int16_t v = 0;
+    if (o >= 3 * d.g.SS) { if (o < 3 * d.g.SS + 12) v = d.in[3 * d.g.K + (o - 3 * d.g.SS)]; }
+    else {
+      const int s = o / d.g.SS, r = o % d.g.SS, lane = r / d.g.Lp, k = r % d.g.Lp;
+      if (k < d.g.L) v = d.in[3 * (lane * d.g.L + k) + s];
+    }
+    d.soft[o] = v;
+  }
+}
+
+cudaError_t fec_launch_extract(const FecExtractDesc *descs, uint32_t n, cudaStream_t st)
+{
+  if (n == 0) return cudaSuccess;
+  fec_extract_kernel<<<dim3(8, n), 256, 0, st>>>(descs);
+  return cudaGetLastError();
+}
+
+/* device layout -> reference soft-buffer layout (18600 int16), for parity checks and srslte_rm_turbo_rx_lut */
+__global__ void fec_soft_to_ref_kernel(const int16_t *dev, int16_t *ref, fec_geom_t g, int sb)
+{
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 18600; i += gridDim.x * blockDim.x) ref[i] = 0;
+  __syncthreads();
+  if (gridDim.x != 1) return;   /* single-CTA kernel: the zero fill above must complete first */
+  for (int t = threadIdx.x; t < 3 * g.K + 12; t += blockDim.x) {
+    int od, orf;
+    if (t >= 3 * g.K) { od = 3 * g.SS + (t - 3 * g.K); orf = (sb && g.P) ? 3 * (g.K + 32) + (t - 3 * g.K) : t; }
+    else {
+      const int s = t % 3, x = t / 3;
+      od = s * g.SS + (x / g.L) * g.Lp + x % g.L;
+      orf = (sb && g.P) ? s * (g.K + 32) + (x % g.L) * g.P + x / g.L : t;
+    }
+    ref[orf] = dev[od];
+  }
+}
+
+cudaError_t fec_launch_soft_to_ref(const int16_t *soft_dev, int16_t *ref_dev, fec_geom_t g, int sb_layout, cudaStream_t st)
+{
+  fec_soft_to_ref_kernel<<<1, 1024, 0, st>>>(soft_dev, ref_dev, g, sb_layout);
+  return cudaGetLastError();
+}
+
+/* =====================================================================================================
+ * Transport-block assembly: concatenate code-block payloads exactly as decode_tb_cb's sequential writes
+ * do (sch.c:365,396-401: CB i writes K/8 bytes at i*rlen/8, later CBs overwrite its CRC bytes), refresh
+ * the decoded-CB cache (sch.c:410-417) and check CRC24A (sch.c:478-485). One CTA per transport block.
+ * ===================================================================================================== */
+__global__ void __launch_bounds__(256) fec_tb_assemble_kernel(const FecTbDesc *descs, const FecCbStatus *status,
+                                                              const uint32_t *r24a)
+{
+  const FecTbDesc &d = descs[blockIdx.x];
+  __shared__ uint32_t s_red[8];
+  __shared__ int s_ok;
+  const int tid = threadIdx.x;
+  if (tid == 0) {
+    int ok = 1;
+    for (uint32_t c = 0; c < d.C; c++) if (d.st_idx[c] >= 0 && !status[d.st_idx[c]].crc_ok) ok = 0;
+    s_ok = ok && d.all_ok;
+  }
+  if (tid < 3) d.data[d.tbs / 8 + tid] = 0;
+  __syncthreads();
+  for (uint32_t c = 0; c < d.C; c++) {
+    const int fresh = d.st_idx[c] >= 0;
+    const uint32_t nby = fresh ? d.K[c] / 8 : d.rlen[c] / 8, base = c * d.rlen[c] / 8;
+    for (uint32_t i = tid; i < nby; i += blockDim.x) d.data[base + i] = d.cb_bytes[c][i];
+    if (fresh && status[d.st_idx[c]].crc_ok)
+      for (uint32_t i = tid; i < d.rlen[c] / 8; i += blockDim.x) d.cache[c][i] = d.cb_bytes[c][i];
+    __syncthreads();
+  }
+  int ret = -1;
+  if (s_ok) {
+    uint32_t acc = 0;
+    const uint32_t nbytes = d.tbs / 8;
+    for (uint32_t b = tid; b < nbytes; b += blockDim.x) {
+      uint32_t v = d.data[b];
+      while (v) {
+        const int hb = 31 - __clz(v);            /* bit value 1<<hb is stream bit 8b + (7-hb) */
+        acc ^= r24a[d.tbs - 1 - (8 * b + (7 - hb))];
+        v &= ~(1u << hb);
+      }
+    }
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) acc ^= __shfl_xor_sync(0xFFFFFFFFu, acc, s);
+    if ((tid & 31) == 0) s_red[tid >> 5] = acc;
+    __syncthreads();
+    if (tid == 0) {
+      uint32_t par_rx = 0;
+      for (int i = 0; i < 8; i++) par_rx ^= s_red[i];
+      const uint32_t par_tx = ((uint32_t)d.data[nbytes] << 16) | ((uint32_t)d.data[nbytes + 1] << 8) | d.data[nbytes + 2];
+      ret = (par_rx == par_tx && par_rx) ? 0 : -1;
+    }
+  }
+  if (tid == 0) *d.ret = ret;
+}
+
+cudaError_t fec_launch_tb_assemble(const FecTbDesc *descs, const FecCbStatus *status, const uint32_t *r24a,
+                                   uint32_t n, cudaStream_t st)
+{
+  if (n == 0) return cudaSuccess;
+  fec_tb_assemble_kernel<<<n, 256, 0, st>>>(descs, status, r24a);
+  return cudaGetLastError();
+}
+
+cudaError_t fec_kernels_init(void)
+{
+  cudaError_t e;
+  e = cudaFuncSetAttribute(fec_tdec_win_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(fec_tdec_win_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(fec_tdec_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+}

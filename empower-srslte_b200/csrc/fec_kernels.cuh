@@ -1,0 +1,78 @@
+/*
+ * fec_kernels.cuh — device-side structures and kernel launch prototypes of libsrslte_fec_cuda.
+ * sm_100a only. See DESIGN.md for the data layout and the roofline of each kernel.
+ */
+#ifndef FEC_KERNELS_CUH
+#define FEC_KERNELS_CUH
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "fec_tables.h"
+
+#define FEC_WIN_THREADS   128     /* MAP lanes per CTA in the windowed kernel = slots x P */
+#define FEC_WIN_CHUNK     16      /* beta checkpoint spacing S (trellis steps) */
+#define FEC_F_NO_EARLY    1u
+
+/* one code block of a decode launch */
+struct FecCbDesc {
+  const int16_t *soft;     /* device-layout soft buffer slot (3 streams + 12 tail) */
+  uint8_t       *out;      /* K/8 decoded bytes */
+  uint32_t       crc_sel;  /* 0: CRC24A powers, 1: CRC24B powers */
+  uint32_t       max_its;  /* half-iteration cap */
+  uint32_t       flags;    /* FEC_F_NO_EARLY */
+  uint32_t       status;   /* index into the status array */
+};
+
+struct FecCbStatus { uint32_t its; uint32_t crc_ok; };
+
+/* everything a decode launch needs for one code-block size K */
+struct FecDecodeArgs {
+  fec_geom_t        g;
+  const uint32_t   *step_tab;   /* [2][NL*Lp] (nat<<16 | eaddr) */
+  const uint32_t   *crcpow[2];  /* R24A, R24B */
+  const FecCbDesc  *cbs;
+  FecCbStatus      *status;
+  unsigned int     *queue;      /* work-queue counter, zeroed before launch */
+  uint32_t          ncb;
+  uint32_t          slots;      /* code blocks in flight per CTA */
+  int16_t          *dbg_llr;    /* optional [ncb][6144]: LLRs of the last half-iteration, natural order (tests only) */
+};
+
+/* one code block of a rate-dematching launch */
+struct FecRmDesc {
+  const int16_t  *e;        /* E transmitted LLRs of this CB */
+  int16_t        *soft;     /* device-layout slot, read-modify-write */
+  const uint16_t *rank;     /* per-K rank table in device layout */
+  uint32_t        E;
+  uint32_t        N;        /* 3K+12 */
+  uint32_t        off;      /* start rank for this rv */
+  uint32_t        n_out;    /* 3*SS+16 (multiple of 8) */
+  uint32_t        new_data; /* 1: overwrite (fresh HARQ process), 0: accumulate */
+  uint32_t        pad;
+};
+
+/* natural-layout [s p p']xK+12 input -> device-layout slot (srslte_tdec_* level entry) */
+struct FecExtractDesc { const int16_t *in; int16_t *soft; fec_geom_t g; };
+
+/* one transport block of the assembly/CRC24A launch */
+struct FecTbDesc {
+  uint8_t        *data;        /* out: device TB buffer */
+  const uint8_t  *cb_bytes[13];/* decoded bytes per CB (fresh decode or cache) */
+  uint32_t        C, rlen[13], K[13];
+  uint32_t        tbs;
+  uint32_t        all_ok;      /* host-known part of AND(cb_crc): CBs skipped because already OK */
+  uint32_t        status0;     /* index of CB0's status entry, or per-CB status index array below */
+  int32_t         st_idx[13];  /* status index per CB, -1 if CB not decoded in this call (was OK already) */
+  uint8_t        *cache[13];   /* softbuffer->data[cb]: decoded-CB cache, updated when a CB newly passes */
+  int32_t        *ret;         /* out: 0 / -1 */
+};
+
+size_t fec_win_smem_bytes(const fec_geom_t *g, uint32_t slots);
+uint32_t fec_win_pick_slots(const fec_geom_t *g);
+cudaError_t fec_launch_decode(const FecDecodeArgs &a, int sm_count, cudaStream_t st);
+cudaError_t fec_launch_rm(const FecRmDesc *descs, uint32_t n, uint32_t max_n_out, cudaStream_t st);
+cudaError_t fec_launch_extract(const FecExtractDesc *descs, uint32_t n, cudaStream_t st);
+cudaError_t fec_launch_tb_assemble(const FecTbDesc *descs, const FecCbStatus *status, const uint32_t *r24a,
+                                   uint32_t n, cudaStream_t st);
+cudaError_t fec_launch_soft_to_ref(const int16_t *soft_dev, int16_t *ref_dev, fec_geom_t g, int sb_layout, cudaStream_t st);
+cudaError_t fec_kernels_init(void);
+#endif

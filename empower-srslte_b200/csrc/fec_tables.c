@@ -1,0 +1,122 @@
+/*
+ * fec_tables.c — host-side table generation for libsrslte_fec_cuda (see fec_tables.h).
+ * Replaces, for the decode path, the static tables the reference builds in
+ * srslte_rm_turbo_gentables (rm_turbo.c:267-305), srslte_tc_interl_LTE_gen_interl (tc_interl_lte.c:78-120)
+ * and gen_crc_table (crc.c:38-47) — but in the device layout, and only for the K actually used.
+ */
+#include "fec_tables.h"
+#include "lte_qpp_table.h"
+#include <math.h>
+#include <string.h>
+
+int fec_k_index(uint32_t K)
+{
+  for (int i = 0; i < FEC_NOF_K; i++) if (lte_qpp_table[i][0] >= K) return i;
+  return -1;
+}
+
+int fec_k_size(uint32_t idx) { return idx < FEC_NOF_K ? (int)lte_qpp_table[idx][0] : -1; }
+
+int fec_k_subblocks(uint32_t K)
+{
+  if ((K % 16) == 0 && K > 800) return 16;
+  if ((K % 8) == 0 && K > 400) return 8;
+  return 0;
+}
+
+int fec_segm(uint32_t tbs, uint32_t *o)
+{
+  memset(o, 0, 9 * sizeof(uint32_t));
+  if (tbs == 0) return 0;
+  uint32_t B = tbs + 24, C, Bp;
+  if (B <= FEC_MAX_K) { C = 1; Bp = B; }
+  else { C = (uint32_t)ceilf((float)B / (float)(FEC_MAX_K - 24)); Bp = B + 24 * C; }
+  int i1 = fec_k_index((Bp - 1) / C + 1);
+  if (i1 < 0) return -1;
+  uint32_t K1 = lte_qpp_table[i1][0], K2 = 0, K2i = 0, C1 = 1, C2 = 0;
+  if (C > 1) {
+    K2i = (uint32_t)i1 - 1; K2 = lte_qpp_table[K2i][0];
+    C2 = (C * K1 - Bp) / (K1 - K2); C1 = C - C2;
+  }
+  o[0] = C1 * K1 + C2 * K2 - Bp; o[1] = C; o[2] = K1; o[3] = K2; o[4] = (uint32_t)i1; o[5] = K2i;
+  o[6] = C1; o[7] = C2; o[8] = tbs;
+  return 0;
+}
+
+int fec_geom(uint32_t K, fec_geom_t *g)
+{
+  int idx = fec_k_index(K);
+  if (idx < 0 || lte_qpp_table[idx][0] != K) return -1;
+  g->K = (int)K; g->idx = idx; g->P = fec_k_subblocks(K);
+  g->NL = g->P ? g->P : 1;
+  g->L = g->K / g->NL;
+  g->Lp = (g->L + 7) & ~7;
+  if (g->P) { g->LpE = g->L; while ((g->LpE & 3) != 2) g->LpE++; }
+  else g->LpE = g->K;
+  g->SS = g->NL * g->Lp;
+  g->f1 = lte_qpp_table[idx][1]; g->f2 = lte_qpp_table[idx][2];
+  return 0;
+}
+
+void fec_gen_step_table(const fec_geom_t *g, uint32_t *tab)
+{
+  const int K = g->K, L = g->L;
+  memset(tab, 0, sizeof(uint32_t) * 2 * (size_t)g->SS);
+  for (int par = 0; par < 2; par++)
+    for (int j = 0; j < K; j++) {
+      uint64_t jj = (uint64_t)j;
+      int nat = par ? (int)(((uint64_t)g->f1 * jj + (uint64_t)g->f2 * jj * jj) % (uint64_t)K) : j;
+      int ea = (nat / L) * g->LpE + nat % L;
+      tab[(size_t)par * g->SS + (j / L) * g->Lp + j % L] = ((uint32_t)nat << 16) | (uint32_t)ea;
+    }
+}
+
+static const uint8_t rm_colperm[32] = {0, 16, 8, 24, 4, 20, 12, 28, 2, 18, 10, 26, 6, 22, 14, 30,
+                                       1, 17, 9, 25, 5, 21, 13, 29, 3, 19, 11, 27, 7, 23, 15, 31};
+
+int fec_soft_offset_dev(const fec_geom_t *g, int t)
+{
+  if (t >= 3 * g->K) return 3 * g->SS + (t - 3 * g->K);
+  int s = t % 3, x = t / 3;
+  return s * g->SS + (x / g->L) * g->Lp + x % g->L;
+}
+
+int fec_soft_offset_ref(const fec_geom_t *g, int t, int sb_layout)
+{
+  if (!sb_layout || g->P == 0) return t;
+  if (t >= 3 * g->K) return 3 * (g->K + 32) + (t - 3 * g->K);
+  int s = t % 3, x = t / 3;
+  return s * (g->K + 32) + (x % g->L) * g->P + x / g->L;
+}
+
+/* 36.212 5.1.4.1: three sub-block interleavers (32 columns, R rows, ND leading <NULL>s), bit collection
+ * w = [v0 | v1,v2 interlaced], circular read from k0(rv) skipping <NULL>s. The rank of a coded bit is its
+ * position among the non-NULL entries of w counted from w[0]. */
+void fec_gen_rm_rank(const fec_geom_t *g, uint16_t *rank, uint32_t off[4])
+{
+  const int D = g->K + 4, R = (D - 1) / 32 + 1, KP = 32 * R, ND = KP - D, NCB = 3 * KP;
+  int k0[4];
+  for (int rv = 0; rv < 4; rv++) k0[rv] = R * (2 * (int)ceilf((float)NCB / (float)(8 * R)) * rv + 2);
+  memset(rank, 0xFF, sizeof(uint16_t) * (size_t)(3 * g->SS + 16));
+  int cnt = 0;
+  for (int w = 0; w < NCB; w++) {
+    for (int rv = 0; rv < 4; rv++) if (w == k0[rv]) off[rv] = (uint32_t)cnt;
+    int y, stream, m;
+    if (w < KP) { stream = 0; y = (w % R) * 32 + rm_colperm[w / R]; }
+    else if (((w - KP) & 1) == 0) { m = (w - KP) / 2; stream = 1; y = (m % R) * 32 + rm_colperm[m / R]; }
+    else { m = (w - KP) / 2; stream = 2; y = (rm_colperm[m / R] + 32 * (m % R) + 1) % KP; }
+    if (y < ND) continue;
+    rank[fec_soft_offset_dev(g, 3 * (y - ND) + stream)] = (uint16_t)cnt++;
+  }
+}
+
+void fec_gen_crc_powers(uint32_t poly, uint32_t *Rt, int n)
+{
+  uint32_t r = poly & 0xFFFFFFu;         /* x^24 mod g */
+  for (int m = 0; m < n; m++) {
+    Rt[m] = r;
+    r <<= 1;
+    if (r & 0x1000000u) r ^= poly;
+    r &= 0xFFFFFFu;
+  }
+}

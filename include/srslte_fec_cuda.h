@@ -1,0 +1,118 @@
+/*
+ * srslte_fec_cuda.h — C ABI of libsrslte_fec_cuda.so: the B200 (sm_100a) transport-block decode path
+ * behind srsLTE's FEC / SCH decode API. Plain C, plain pointers and sizes; no torch / C++ types.
+ *
+ * Two layers:
+ *  (1) the batched API (fec_cuda_*): the ADDITION a GPU needs — many transport blocks (subframes x HARQ
+ *      processes x cells) per call. It replaces the per-TB loop the reference runs in
+ *      decode_tb()/decode_tb_cb() (lib/src/phy/phch/sch.c:307-498).
+ *  (2) the reference's own symbols (srslte_*): declared in srslte_fec_compat.h, batch-of-one wrappers over (1).
+ *
+ * Error codes follow lib/include/srslte/config.h:64-66: 0 success, -1 error (CRC fail), -2 invalid inputs.
+ * There is NO CPU fallback: every entry point that computes returns FEC_CUDA_ENODEV (-100) when no
+ * CUDA device / kernel image is usable.
+ */
+#ifndef SRSLTE_FEC_CUDA_H
+#define SRSLTE_FEC_CUDA_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FEC_CUDA_SUCCESS          0
+#define FEC_CUDA_ERROR           -1
+#define FEC_CUDA_EINVAL          -2
+#define FEC_CUDA_ENODEV          -100
+
+#define FEC_CUDA_MAX_CB           13       /* SRSLTE_MAX_CODEBLOCKS as reachable from tbs_tables */
+#define FEC_CUDA_MAX_K            6144
+#define FEC_CUDA_SOFT_SLOT        18464    /* int16 per code-block soft-buffer slot on the device (>= reference 18600 role) */
+
+/* flags for fec_cuda_decode_tbs */
+#define FEC_CUDA_F_DEVICE_IO      1u       /* e_bits / data are DEVICE pointers; nothing bulk crosses PCIe */
+#define FEC_CUDA_F_NO_EARLY_STOP  2u       /* run exactly max_its half-iterations (srslte_tdec_run_all semantics) */
+
+typedef struct fec_cuda_ctx fec_cuda_ctx_t;
+
+/* One transport block of a batch. Mirrors the arguments of decode_tb() (sch.c:437-441) plus the HARQ
+ * soft-buffer identity (srslte_softbuffer_rx_t, softbuffer.h:42-48) which lives on the device. */
+typedef struct {
+  /* in */
+  uint32_t       tbs;          /* transport block size in bits (cb_segm->tbs) */
+  uint32_t       Qm;           /* modulation order x layers, as decode_tb receives it */
+  uint32_t       rv;           /* redundancy version 0..3 */
+  uint32_t       nof_e_bits;   /* number of LLRs in e_bits (cfg->nbits[].nof_bits) */
+  uint32_t       max_its;      /* max HALF-iterations per code block (srslte_sch_set_max_noi) */
+  uint32_t       softbuffer;   /* device soft-buffer id from fec_cuda_softbuffer_alloc */
+  uint32_t       new_data;     /* 1: srslte_softbuffer_rx_reset_tbs() semantics before combining */
+  uint32_t       reserved;
+  const int16_t *e_bits;       /* LLRs, host (default) or device (FEC_CUDA_F_DEVICE_IO) */
+  uint8_t       *data;         /* out: tbs/8 + 3 bytes are written (TB + CRC24A); needs tbs/8+3+768 bytes of room */
+  /* out */
+  int32_t        ret;          /* 0 TB OK, -1 CRC fail, -2 invalid (decode_tb return value) */
+  uint32_t       avg_its;      /* sum of half-iterations / C, integer division (sch.c:420, srslte_sch_last_noi) */
+  uint8_t        cb_crc[FEC_CUDA_MAX_CB];   /* per-CB CRC state after this call (softbuffer->cb_crc) */
+  uint8_t        cb_its[FEC_CUDA_MAX_CB];   /* half-iterations run per CB in this call (0 = skipped, already OK) */
+  uint8_t        pad[6];
+} fec_cuda_tb_t;
+
+/* One bare code block for the srslte_tdec_* level (turbodecoder.h:102-140): natural-layout input
+ * [s p p'] x K + 12 tail, as srslte_tdec_run_all / turbodecoder_test feed it. */
+typedef struct {
+  uint32_t       K;            /* code block size, must be one of the 188 LTE sizes */
+  uint32_t       max_its;      /* half-iterations (cap, or exact count with FEC_CUDA_F_NO_EARLY_STOP) */
+  uint32_t       crc_type;     /* 0 CRC24A, 1 CRC24B — only used for early stop */
+  uint32_t       reserved;
+  const int16_t *llr;          /* 3K+12 int16 */
+  uint8_t       *out;          /* K/8 bytes */
+  uint32_t       its;          /* out: half-iterations run */
+  uint32_t       crc_ok;       /* out: 1 if the CRC over the K decoded bits is zero */
+} fec_cuda_cb_t;
+
+/* ---- lifecycle ------------------------------------------------------------------------------------ */
+/* device: CUDA ordinal. max_tbs_per_call bounds the staging buffers (pinned host + device). */
+int  fec_cuda_create(fec_cuda_ctx_t **ctx, int device, uint32_t max_tbs_per_call);
+void fec_cuda_destroy(fec_cuda_ctx_t *ctx);
+const char *fec_cuda_last_error(fec_cuda_ctx_t *ctx);
+/* the CUDA stream (cudaStream_t) all kernels of this context are launched on — for event timing */
+void *fec_cuda_stream(fec_cuda_ctx_t *ctx);
+/* number of kernels launched by this context so far */
+uint64_t fec_cuda_launch_count(fec_cuda_ctx_t *ctx);
+
+/* ---- HARQ soft buffers (replace srslte_softbuffer_rx_init/free/reset, softbuffer.c:46-151) ---------- */
+/* allocates n TB soft buffers (13 code-block slots each) in HBM; ids are first_id .. first_id+n-1 */
+int  fec_cuda_softbuffer_alloc(fec_cuda_ctx_t *ctx, uint32_t n, uint32_t *first_id);
+int  fec_cuda_softbuffer_reset(fec_cuda_ctx_t *ctx, uint32_t id);           /* srslte_softbuffer_rx_reset */
+/* debugging / parity: copy one CB slot out in the REFERENCE soft-buffer layout (18600 int16, rm_turbo.c:250-264) */
+int  fec_cuda_softbuffer_read_ref_layout(fec_cuda_ctx_t *ctx, uint32_t id, uint32_t cb, uint32_t K, int16_t *out18600);
+
+/* ---- the hot path ------------------------------------------------------------------------------------ */
+/* rate de-matching + HARQ combine -> turbo decode with CRC early stop -> TB assembly + CRC24A, for n TBs.
+ * Synchronous: returns when all outputs are in place. Per-TB results in tbs[i].ret; the call itself
+ * returns 0 unless the batch could not be run at all. */
+int  fec_cuda_decode_tbs(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, uint32_t n, uint32_t flags);
+
+/* bare turbo decoding of n code blocks from natural-layout LLRs (host pointers) */
+int  fec_cuda_decode_cbs(fec_cuda_ctx_t *ctx, fec_cuda_cb_t *cbs, uint32_t n, uint32_t flags);
+
+/* standalone rate de-matching into a HOST soft buffer in the reference layout — drop-in body of
+ * srslte_rm_turbo_rx_lut_ (rm_turbo.c:378-430); computed on the device. */
+int  fec_cuda_rm_rx(fec_cuda_ctx_t *ctx, const int16_t *in, uint32_t E, uint32_t cb_idx, uint32_t rv,
+                    int sb_layout, int16_t *soft18600);
+
+/* ---- test hooks (LLR dump of the last half-iteration of fec_cuda_decode_cbs; not a product feature) ---- */
+int  fec_cuda_debug_llr_enable(fec_cuda_ctx_t *ctx, uint32_t n_code_blocks);
+int  fec_cuda_debug_llr_read(fec_cuda_ctx_t *ctx, int16_t *out /* n x 6144 */, uint32_t n);
+
+/* ---- host-side helpers (pure integer bookkeeping, no device) ---------------------------------------- */
+int  fec_cuda_cb_index(uint32_t K);               /* srslte_cbsegm_cbindex   cbsegm.c:116-127 */
+int  fec_cuda_cb_size(uint32_t idx);              /* srslte_cbsegm_cbsize    cbsegm.c:134-141 */
+int  fec_cuda_subblocks(uint32_t K);              /* srslte_tdec_autoimp_get_subblocks turbodecoder.c:364-376 */
+int  fec_cuda_cbsegm(uint32_t tbs, uint32_t out9[9]);   /* srslte_cbsegm: {F,C,K1,K2,K1_idx,K2_idx,C1,C2,tbs} */
+
+#ifdef __cplusplus
+}
+#endif
+#endif
