@@ -1,0 +1,354 @@
+#!/usr/bin/env python
+"""bench.py — throughput of the DL-SCH transport-block decode path on B200 (contract: see the task brief).
+
+One "step" = one pass of the hot path (rate de-matching + HARQ combine -> turbo decode with CRC24B early
+stop -> TB assembly + CRC24A) over one batch of synthetic transport blocks of BASELINE.json configs[1]:
+20 MHz SISO MCS28, TBS 75376, 13 code blocks of K=5824, 90000 int16 LLRs per TB, rv 0, max 8 half-iterations.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--batch TBs/GPU] [--sigma S]
+
+`value`   : decoded information Gbit/s (TBS bits of CRC-passing TBs / device time), inputs resident in HBM.
+`e2e`     : same metric through the C ABI with HOST (pinned) buffers, H2D/D2H inside the timed region.
+`roofline`: MAP-decoder kernel, algorithmic int16 ops / its CUDA-event duration vs ALU peak,
+            plus the HBM figure for the same launch.
+`cpu_baseline`: the reference's own AVX2 path (oracle/_ref) on the box's host cores, bounded sample.
+"""
+import argparse
+import ctypes as C
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+TBS, QM, NBITS, RV, MAX_ITS = 75376, 6, 90000, 0, 8
+K_CB, C_CB, P_CB = 5824, 13, 16
+DATA_STRIDE = 10240            # >= TBS/8 + 3 + 768 bytes of room per TB output
+METRIC = "decoded DL-SCH Gbps & code blocks/s per B200 (20MHz MCS28, 8 it)"
+UNIT = "Gbit/s"
+
+
+def ops_per_halfit(K, P):
+    """algorithmic int16 lane-ops of one half-iteration"""
+    return 84 * K + 2040 * P + 63 if P else 90 * K
+
+
+def algorithmic_bytes_per_cb(K, E):
+    """HBM bytes the unfused pipeline must move per code block with new data: LLRs in, soft-buffer write,
+    decoder read of the soft buffer, decoded bytes out"""
+    return 2 * E + 2 * (3 * K + 12) + 2 * (3 * K + 12) + K // 8
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        j = json.load(open(p))
+        return dict(hbm_gbs=float(j["hbm_gbs"]), sm_max_mhz=float(j.get("sm_max_mhz", 1965.0)), src="measured")
+    return dict(hbm_gbs=6650.0, sm_max_mhz=1965.0, src="fallback")
+
+
+def alu_peak_tops(n_sm, sm_mhz):
+    """int16 ALU peak in Tops/s: SMs x int16 lane-ops/clk/SM x clock. The per-SM rate is the measured
+    register-only packed s16x2 rate from tools/alu_peak.cu when profiles/alu_peak.json holds it,
+    else the nominal 128 lanes x 2."""
+    per_clk, src = 256.0, "nominal 128 lanes x s16x2"
+    p = os.path.join(ROOT, "profiles", "alu_peak.json")
+    if os.path.exists(p):
+        j = json.load(open(p))
+        per_clk, src = float(j["int16_ops_per_clk_per_sm"]), j.get("how", "measured microbenchmark")
+    return n_sm * per_clk * sm_mhz * 1e6 / 1e12, src
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks + throttle reasons DURING the timed region (B200_PROFILING.md clocks line)"""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.proc = index, [], None
+
+    def run(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                self.rows.append([c.strip() for c in line.split(",")])
+        except Exception:
+            pass
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        self.join(timeout=2)
+        sm = sorted(float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit())
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 3 + i and r[3 + i] == "Active" for r in self.rows)]
+        pw = [float(r[2]) for r in self.rows if len(r) > 2 and r[2].replace(".", "").isdigit()]
+        return dict(sm_mhz=sm[len(sm) // 2] if sm else None, sm_max_mhz=max(mx) if mx else None,
+                    power_w_max=max(pw) if pw else None, samples=len(self.rows), reasons=reasons)
+
+
+def make_llrs(batch, sigma, seed, out):
+    """batch AWGN-corrupted MCS28 transport blocks -> out[batch, NBITS] int16; returns payload[ncw, TBS/8].
+    16 distinct codewords (numpy encoder, empower-srslte_b200/synth.py), independent noise per TB."""
+    synth = importlib.import_module("empower-srslte_b200.synth")
+    ncw = min(16, batch)
+    rng = np.random.default_rng(seed)
+    payload = rng.integers(0, 256, size=(ncw, TBS // 8), dtype=np.uint8)
+    e = synth.encode_tbs(payload, TBS, QM, RV, NBITS)
+    for i0 in range(0, batch, 64):
+        i1 = min(batch, i0 + 64)
+        synth.awgn_llr(e[np.arange(i0, i1) % ncw], sigma, rng, out=out[i0:i1])
+    return payload
+
+
+def cpu_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def cpu_arm(llr, ntb, budget_s):
+    """the reference's CPU implementation of the same step on this box's host cores (bounded sample).
+    oracle/_ref (unmodified reference objects, AVX2 AUTO decoders) when present, else the scalar oracle port."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from _libs import P, oracle, ref
+    cores = cpu_cores()
+    lib = ref()
+    kind = "reference" if lib is not None else "port"
+    if lib is None:
+        lib = oracle()
+    ntb = min(ntb, llr.shape[0])
+    sample = np.ascontiguousarray(llr[:ntb])
+    out = np.zeros(3, np.uint64)
+
+    def run(reps):
+        if kind == "reference":
+            return lib.ref_bench_tb_mt(cores, ntb, TBS, QM, RV, NBITS, P(sample), MAX_ITS, reps, 100, P(out))
+        return lib.orc_bench_tb_mt(cores, ntb, TBS, QM, RV, NBITS, P(sample), MAX_ITS, reps, P(out))
+
+    t1 = run(1)
+    reps = max(1, min(2000, int(budget_s / max(t1, 1e-3))))
+    t = run(reps)
+    n_tb, n_ok, sum_its = int(out[0]), int(out[1]), int(out[2])
+    return dict(value=n_ok * TBS / t / 1e9, unit=UNIT, cores=cores, kind=kind, seconds=t,
+                tbs_per_s=n_tb / t, cbs_per_s=n_tb * C_CB / t, tb_ok=n_ok, tb_total=n_tb,
+                mean_halfits=sum_its / max(n_tb, 1),
+                sample=f"{ntb} of the step's TBs x {reps} passes, {cores} threads (one srslte_sch_t + soft buffers each), "
+                       f"srslte_dlsch_decode AUTO AVX2" if kind == "reference" else
+                       f"{ntb} of the step's TBs x {reps} passes, {cores} threads, scalar C port of the reference path")
+
+
+def reference_main(args, rank, world):
+    """--impl reference: the reference's own CPU path, rank 0 only"""
+    if rank != 0:
+        return
+    ntb = max(cpu_cores() * 4, 32)
+    llr = np.empty((ntb, NBITS), np.int16)
+    make_llrs(ntb, args.sigma, 1234, llr)
+    per_step_budget = min(20.0, 150.0 / max(args.steps + args.warmup, 1))
+    vals = []
+    last = None
+    for s in range(args.warmup + args.steps):
+        last = cpu_arm(llr, ntb, per_step_budget)
+        if s >= args.warmup:
+            vals.append(last)
+    tot_bits = sum(v["tb_ok"] for v in vals) * TBS
+    tot_s = sum(v["seconds"] for v in vals)
+    val = tot_bits / tot_s / 1e9
+    line = dict(impl="reference", metric=METRIC, value=val, unit=UNIT, n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
+                ms_per_step=1e3 * tot_s / max(len(vals), 1), higher_is_better=True, scaling="weak", vs_baseline=None,
+                dtype="int16", data="synthetic",
+                config=dict(workload="pdsch_mcs28_100prb_tbs75376_13xK5824", sigma=args.sigma, max_half_iterations=MAX_ITS,
+                            tbs_per_step=last["tb_total"], early_stop=True, host_only=True),
+                cbs_per_s=sum(v["tb_total"] for v in vals) * C_CB / tot_s,
+                mean_halfits=last["mean_halfits"],
+                cpu_baseline=dict(value=val, unit=UNIT, cores=last["cores"], kind=last["kind"], sample=last["sample"]),
+                e2e=dict(value=val, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)
+    print(json.dumps(line), flush=True)
+
+
+def fill_descs(pkg, d, n, e_ptr0, data_ptr0, sb0, new_data=1):
+    for i in range(n):
+        d[i].tbs, d[i].Qm, d[i].rv, d[i].nof_e_bits, d[i].max_its = TBS, QM, RV, NBITS, MAX_ITS
+        d[i].softbuffer, d[i].new_data = sb0 + i, new_data
+        d[i].e_bits, d[i].data = e_ptr0 + i * NBITS * 2, data_ptr0 + i * DATA_STRIDE
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=1184, help="transport blocks per GPU per step (default 8 per SM)")
+    ap.add_argument("--sigma", type=float, default=0.45, help="AWGN std of the synthetic LLRs (0.45 = operating point)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-worst-case", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        return reference_main(args, rank, world)
+
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — this path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    pkg = importlib.import_module("empower-srslte_b200")
+    fec = pkg.FecCuda(local_rank, max_tbs=args.batch)
+    B = args.batch
+
+    # ---- synthetic workload: host pinned LLRs (e2e arm) and a device-resident copy (kernel arm) ----
+    h_llr = pkg.PinnedArray((B, NBITS), np.int16)
+    h_out = pkg.PinnedArray((B, DATA_STRIDE), np.uint8)
+    payload = make_llrs(B, args.sigma, 1000 + rank, h_llr.a)
+    d_llr = torch.from_numpy(h_llr.a).to(f"cuda:{local_rank}")
+    d_out = torch.zeros((B, DATA_STRIDE), dtype=torch.uint8, device=f"cuda:{local_rank}")
+    sb0 = fec.softbuffer_alloc(B)
+    dd = (pkg.TbDesc * B)()
+    fill_descs(pkg, dd, B, d_llr.data_ptr(), d_out.data_ptr(), sb0)
+    hd = (pkg.TbDesc * B)()
+    fill_descs(pkg, hd, B, h_llr.a.ctypes.data, h_out.a.ctypes.data, sb0)
+    stream = torch.cuda.ExternalStream(fec.stream, device=f"cuda:{local_rank}")
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(descs, flags, steps, phases=None):
+        """time exactly `steps` passes with CUDA events on the library's stream; max over ranks"""
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            fec.decode_tbs(descs, flags)
+            if phases is not None:
+                phases.append(fec.last_phase_ms())
+        e1.record(stream)
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=f"cuda:{local_rank}")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    def tally(descs):
+        ok = sum(1 for i in range(B) if descs[i].ret == 0)
+        its = sum(sum(descs[i].cb_its[:C_CB]) for i in range(B))
+        return ok, its
+
+    def allsum(v):
+        if world > 1:
+            t = torch.tensor([float(v)], device=f"cuda:{local_rank}", dtype=torch.float64)
+            dist.all_reduce(t)
+            return float(t.item())
+        return float(v)
+
+    # ---- device-resident arm (value) ----
+    for _ in range(args.warmup):
+        fec.decode_tbs(dd, pkg.F_DEVICE_IO)
+    l0 = fec.launches
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    time.sleep(0.3)
+    phases = []
+    ms = timed(dd, pkg.F_DEVICE_IO, args.steps, phases)
+    launches = fec.launches - l0
+    ok, its = tally(dd)
+    # parity spot check of what was decoded: payload bytes of every CRC-passing TB
+    out_host = d_out.cpu().numpy()
+    bad = sum(1 for i in range(B) if dd[i].ret == 0 and not (out_host[i, :TBS // 8] == payload[i % payload.shape[0]]).all())
+    if bad:
+        raise SystemExit(f"bench.py: {bad} CRC-passing transport blocks differ from the transmitted payload")
+    ok_all, its_all = allsum(ok), allsum(its)
+    sec = ms / 1e3
+    value = ok_all * TBS * args.steps / sec / 1e9
+    cbs_per_s = world * B * C_CB * args.steps / sec
+
+    # ---- end-to-end arm: host pinned buffers through the C ABI, H2D + D2H inside the timed region ----
+    for _ in range(2):
+        fec.decode_tbs(hd, 0)
+    ms_e = timed(hd, 0, args.steps)
+    clocks = sampler.stop()
+    ok_e, _ = tally(hd)
+    e2e_val = allsum(ok_e) * TBS * args.steps / (ms_e / 1e3) / 1e9
+    h2d = B * NBITS * 2 + B * C_CB * (32 + 48) + B * 520
+    d2h = B * (((TBS // 8 + 3 + 768 + 15) // 16) * 16) + B * C_CB * 8 + B * 4
+
+    # ---- worst case: all 8 half-iterations for every code block (no early stop), same inputs ----
+    worst = None
+    if not args.no_worst_case:
+        fec.decode_tbs(dd, pkg.F_DEVICE_IO | pkg.F_NO_EARLY_STOP)
+        ms_w = timed(dd, pkg.F_DEVICE_IO | pkg.F_NO_EARLY_STOP, max(2, args.steps // 3))
+        ok_w, its_w = tally(dd)
+        nst = max(2, args.steps // 3)
+        worst = dict(gbps=allsum(ok_w) * TBS * nst / (ms_w / 1e3) / 1e9, cbs_per_s=world * B * C_CB * nst / (ms_w / 1e3),
+                     halfits_per_cb=allsum(its_w) / (world * B * C_CB), ms_per_step=ms_w / nst)
+
+    # ---- roofline of the dominant kernel (turbo MAP decoder), per launch ----
+    pk = peaks()
+    n_sm = torch.cuda.get_device_properties(local_rank).multi_processor_count
+    dec_ms = sum(p[1] for p in phases) / len(phases)
+    rm_ms = sum(p[0] for p in phases) / len(phases)
+    asm_ms = sum(p[2] for p in phases) / len(phases)
+    ops = its * ops_per_halfit(K_CB, P_CB)                     # this rank, one launch
+    achieved = ops / (dec_ms / 1e3) / 1e12
+    sm_mhz = clocks["sm_mhz"] or pk["sm_max_mhz"]
+    peak_nom, peak_src = alu_peak_tops(n_sm, pk["sm_max_mhz"])
+    peak_run, _ = alu_peak_tops(n_sm, sm_mhz)
+    hbm_bytes = B * C_CB * algorithmic_bytes_per_cb(K_CB, NBITS // C_CB)
+    roof = dict(bound="alu_int16", kernel="fec_tdec_win_kernel<16>", achieved=achieved, peak=peak_nom, unit="Tops/s",
+                frac=achieved / peak_nom, frac_at_sustained_clock=achieved / peak_run, peak_source=peak_src + f" @ {pk['sm_max_mhz']:.0f} MHz",
+                traffic=None, ops_per_launch=ops, ms_per_launch=dec_ms,
+                share_of_step=dec_ms / (ms / args.steps),
+                phases_ms=dict(rate_dematch=rm_ms, turbo_decode=dec_ms, tb_assemble_crc24a=asm_ms),
+                hbm=dict(bound="hbm", algorithmic_bytes_per_step=hbm_bytes, achieved=hbm_bytes / (ms / args.steps / 1e3) / 1e9,
+                         peak=pk["hbm_gbs"], unit="GB/s", frac=hbm_bytes / (ms / args.steps / 1e3) / 1e9 / pk["hbm_gbs"],
+                         peak_source=pk["src"],
+                         rate_dematch_kernel_gbs=B * C_CB * (2 * (NBITS // C_CB) + 2 * (3 * K_CB + 12) + 2 * (3 * K_CB + 12)) / (rm_ms / 1e3) / 1e9))
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        c = cpu_arm(h_llr.a, max(cpu_cores() * 4, 32), 15.0)
+        cpu = dict(value=c["value"], unit=UNIT, cores=c["cores"], kind=c["kind"], sample=c["sample"],
+                   cbs_per_s=c["cbs_per_s"], mean_halfits=c["mean_halfits"], tb_ok=c["tb_ok"], tb_total=c["tb_total"])
+
+    if rank == 0:
+        line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=args.warmup,
+                    ms_per_step=ms / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None, dtype="int16",
+                    data="synthetic",
+                    config=dict(workload="pdsch_mcs28_100prb_tbs75376_13xK5824", tbs_per_gpu_per_step=B, sigma=args.sigma,
+                                llr="rint(100*(+-1+sigma*n)) int16", max_half_iterations=MAX_ITS, early_stop=True, rv=RV, new_data=True,
+                                sharding="independent TB batches per GPU, no collective",
+                                l2="inputs larger than L2: %.0f MB LLRs + %.0f MB soft buffers per step" % (B * NBITS * 2 / 1e6, B * C_CB * 18464 * 2 / 1e6)),
+                    cbs_per_s=cbs_per_s, tb_ok_frac=ok_all / (world * B), halfits_per_cb=its_all / (world * B * C_CB),
+                    e2e=dict(value=e2e_val, unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h, ms_per_step=ms_e / args.steps),
+                    gpu_launches=launches, clocks=clocks, roofline=roof, worst_case_8_halfits=worst, cpu_baseline=cpu)
+        print(json.dumps(line), flush=True)
+    fec.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

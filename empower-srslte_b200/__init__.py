@@ -75,6 +75,10 @@ def load():
         lib.fec_cuda_decode_cbs.argtypes = [C.c_void_p, C.POINTER(CbDesc), C.c_uint32, C.c_uint32]
         lib.fec_cuda_rm_rx.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p]
         lib.fec_cuda_cbsegm.argtypes = [C.c_uint32, C.POINTER(C.c_uint32)]
+        lib.fec_cuda_last_phase_ms.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
+        lib.fec_cuda_host_alloc.argtypes = [C.c_size_t]
+        lib.fec_cuda_host_alloc.restype = C.c_void_p
+        lib.fec_cuda_host_free.argtypes = [C.c_void_p]
         _lib = lib
     return _lib
 
@@ -85,6 +89,25 @@ def cbsegm(tbs):
     if load().fec_cuda_cbsegm(tbs, o):
         return None
     return dict(zip(("F", "C", "K1", "K2", "K1_idx", "K2_idx", "C1", "C2", "tbs"), [int(v) for v in o]))
+
+
+class PinnedArray:
+    """numpy view over page-locked host memory from fec_cuda_host_alloc (DMA'd without a staging copy)"""
+
+    def __init__(self, shape, dtype):
+        self.lib = load()
+        nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        self.ptr = self.lib.fec_cuda_host_alloc(nbytes)
+        if not self.ptr:
+            raise RuntimeError("fec_cuda_host_alloc failed (no CUDA device?)")
+        buf = (C.c_uint8 * nbytes).from_address(self.ptr)
+        self.a = np.frombuffer(buf, dtype=dtype).reshape(shape)
+
+    def free(self):
+        if self.ptr:
+            self.a = None
+            self.lib.fec_cuda_host_free(self.ptr)
+            self.ptr = None
 
 
 class FecCuda:
@@ -115,6 +138,14 @@ class FecCuda:
     @property
     def launches(self):
         return int(self.lib.fec_cuda_launch_count(self.h))
+
+    def last_phase_ms(self):
+        """device ms of (rate de-matching, turbo decode, TB assembly+CRC24A) in the last decode_tbs call"""
+        o = (C.c_float * 3)()
+        rc = self.lib.fec_cuda_last_phase_ms(self.h, o)
+        if rc:
+            raise RuntimeError(f"fec_cuda_last_phase_ms: {rc}")
+        return [float(v) for v in o]
 
     def error(self):
         return self.lib.fec_cuda_last_error(self.h).decode()

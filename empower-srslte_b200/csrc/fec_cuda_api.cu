@@ -48,6 +48,8 @@ struct fec_cuda_ctx {
   int16_t      *d_tmpsoft; size_t tmpsoft_cap;
   unsigned int *d_queue;   /* FEC_NOF_K counters */
   int16_t      *d_dbg; size_t dbg_cap; uint32_t *dbg_slot; uint32_t dbg_n;   /* test hook: LLR dump */
+  cudaEvent_t   ev[4];     /* phase boundaries of the last decode_tbs call: rm | decode | assemble */
+  int           ev_valid;
 };
 
 static int fail(fec_cuda_ctx_t *c, int code, const char *fmt, ...)
@@ -119,6 +121,7 @@ extern "C" int fec_cuda_create(fec_cuda_ctx_t **out, int device, uint32_t max_tb
   cudaMemcpy(ctx->d_r24b, R, sizeof(uint32_t) * FEC_MAX_K, cudaMemcpyHostToDevice);
   free(R);
   cudaMalloc(&ctx->d_queue, sizeof(unsigned int) * FEC_NOF_K);
+  for (int i = 0; i < 4; i++) cudaEventCreate(&ctx->ev[i]);
   if (cudaGetLastError() != cudaSuccess) { free(ctx); return FEC_CUDA_ENODEV; }
   *out = ctx;
   return FEC_CUDA_SUCCESS;
@@ -135,6 +138,7 @@ extern "C" void fec_cuda_destroy(fec_cuda_ctx_t *ctx)
   stage_free(&ctx->st_e); stage_free(&ctx->st_data); stage_free(&ctx->st_cbd); stage_free(&ctx->st_rmd);
   stage_free(&ctx->st_tbd); stage_free(&ctx->st_status); stage_free(&ctx->st_ret); stage_free(&ctx->st_exd);
   cudaFree(ctx->d_cbbytes); cudaFree(ctx->d_tmpsoft); cudaFree(ctx->d_r24a); cudaFree(ctx->d_r24b); cudaFree(ctx->d_queue);
+  for (int i = 0; i < 4; i++) cudaEventDestroy(ctx->ev[i]);
   cudaStreamDestroy(ctx->stream);
   free(ctx);
 }
@@ -142,6 +146,23 @@ extern "C" void fec_cuda_destroy(fec_cuda_ctx_t *ctx)
 extern "C" const char *fec_cuda_last_error(fec_cuda_ctx_t *ctx) { return ctx ? ctx->err : "null context"; }
 extern "C" void *fec_cuda_stream(fec_cuda_ctx_t *ctx) { return ctx ? (void *)ctx->stream : NULL; }
 extern "C" uint64_t fec_cuda_launch_count(fec_cuda_ctx_t *ctx) { return ctx ? ctx->launches : 0; }
+
+/* pinned host memory for LLR / output buffers (what srslte_vec_malloc hands out in the drop-in build) */
+extern "C" void *fec_cuda_host_alloc(size_t bytes)
+{
+  void *p = NULL;
+  if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return NULL; }
+  return p;
+}
+extern "C" void fec_cuda_host_free(void *p) { if (p) cudaFreeHost(p); }
+
+extern "C" int fec_cuda_last_phase_ms(fec_cuda_ctx_t *ctx, float out3[3])
+{
+  if (!ctx || !out3 || !ctx->ev_valid) return FEC_CUDA_EINVAL;
+  for (int i = 0; i < 3; i++)
+    if (cudaEventElapsedTime(&out3[i], ctx->ev[i], ctx->ev[i + 1]) != cudaSuccess) return FEC_CUDA_ERROR;
+  return 0;
+}
 
 static int ktab_get(fec_cuda_ctx_t *ctx, uint32_t K, ktab_t **out)
 {
@@ -226,7 +247,7 @@ extern "C" int fec_cuda_softbuffer_read_ref_layout(fec_cuda_ctx_t *ctx, uint32_t
 }
 
 /* ---------------------------------------------------------------- batched transport-block decode ---- */
-typedef struct { uint32_t seg[9]; sbchunk_t *chunk; uint32_t local; int valid; uint32_t first_cb; uint32_t ndec; size_t data_off, e_off; } tbplan_t;
+typedef struct { uint32_t seg[9]; sbchunk_t *chunk; uint32_t local; int valid, pinned; uint32_t first_cb; uint32_t ndec; size_t data_off, e_off; } tbplan_t;
 
 #define CUF(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { free(plan); \
   return fail(ctx, FEC_CUDA_ENODEV, "%s: %s", #call, cudaGetErrorString(e_)); } } while (0)
@@ -314,22 +335,49 @@ extern "C" int fec_cuda_decode_tbs(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, uint
       d->max_its = t->max_its ? t->max_its : 1; d->flags = (flags & FEC_CUDA_F_NO_EARLY_STOP) ? FEC_F_NO_EARLY : 0; d->status = slot;
       td->st_idx[cb] = (int32_t)slot; td->cb_bytes[cb] = d->out;
     }
-    if (!dev_io) memcpy((int16_t *)ctx->st_e.h + p->e_off, t->e_bits, (size_t)t->nof_e_bits * 2);
+    if (!dev_io) {
+      /* pinned caller memory (fec_cuda_host_alloc / cudaHostRegister) is DMA'd straight from where it lies */
+      cudaPointerAttributes pa;
+      p->pinned = (cudaPointerGetAttributes(&pa, t->e_bits) == cudaSuccess && pa.type == cudaMemoryTypeHost);
+      cudaGetLastError();
+      if (!p->pinned) memcpy((int16_t *)ctx->st_e.h + p->e_off, t->e_bits, (size_t)t->nof_e_bits * 2);
+    }
     itb++;
   }
   if (rc) { free(plan); return rc; }
 
   cudaStream_t st = ctx->stream;
-  if (!dev_io) CUF(cudaMemcpyAsync(ctx->st_e.d, ctx->st_e.h, e_total * 2, cudaMemcpyHostToDevice, st));
+  if (!dev_io) {
+    /* one H2D copy per run of transport blocks that is contiguous on both sides */
+    uint32_t i = 0;
+    while (i < n) {
+      if (!plan[i].valid) { i++; continue; }
+      const int pinned = plan[i].pinned;
+      const char *src0 = pinned ? (const char *)tbs[i].e_bits : (const char *)((int16_t *)ctx->st_e.h + plan[i].e_off);
+      const size_t dst0 = plan[i].e_off * 2;
+      size_t len = (size_t)tbs[i].nof_e_bits * 2;
+      uint32_t j = i + 1;
+      for (; j < n; j++) {
+        if (!plan[j].valid || plan[j].pinned != pinned || plan[j].e_off * 2 != dst0 + len) break;
+        if (pinned && (const char *)tbs[j].e_bits != src0 + len) break;
+        if (!pinned && (((size_t)tbs[j - 1].nof_e_bits) & 7)) break;
+        len += (size_t)tbs[j].nof_e_bits * 2;
+      }
+      CUF(cudaMemcpyAsync((char *)ctx->st_e.d + dst0, src0, len, cudaMemcpyHostToDevice, st));
+      i = j;
+    }
+  }
   CUF(cudaMemcpyAsync(ctx->st_cbd.d, cbd, sizeof(FecCbDesc) * ncb, cudaMemcpyHostToDevice, st));
   CUF(cudaMemcpyAsync(ctx->st_rmd.d, rmd, sizeof(FecRmDesc) * ncb, cudaMemcpyHostToDevice, st));
   CUF(cudaMemcpyAsync(ctx->st_tbd.d, tbd, sizeof(FecTbDesc) * ntb, cudaMemcpyHostToDevice, st));
   CUF(cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned int) * FEC_NOF_K, st));
+  CUF(cudaEventRecord(ctx->ev[0], st));
   for (uint32_t o = 0; o < ncb; o += 32768) {                       /* grid.y limit */
     const uint32_t m = ncb - o < 32768 ? ncb - o : 32768;
     CUF(fec_launch_rm((const FecRmDesc *)ctx->st_rmd.d + o, m, max_n_out, st));
     ctx->launches++;
   }
+  CUF(cudaEventRecord(ctx->ev[1], st));
   for (int k = 0; k < FEC_NOF_K; k++) {
     if (!grp_cnt[k]) continue;
     FecDecodeArgs a;
@@ -339,8 +387,11 @@ extern "C" int fec_cuda_decode_tbs(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, uint
     CUF(fec_launch_decode(a, ctx->sm_count, st));
     ctx->launches++;
   }
+  CUF(cudaEventRecord(ctx->ev[2], st));
   CUF(fec_launch_tb_assemble((const FecTbDesc *)ctx->st_tbd.d, (const FecCbStatus *)ctx->st_status.d, ctx->d_r24a, ntb, st));
   ctx->launches++;
+  CUF(cudaEventRecord(ctx->ev[3], st));
+  ctx->ev_valid = 1;
   if (ncb) CUF(cudaMemcpyAsync(ctx->st_status.h, ctx->st_status.d, sizeof(FecCbStatus) * ncb, cudaMemcpyDeviceToHost, st));
   CUF(cudaMemcpyAsync(ctx->st_ret.h, ctx->st_ret.d, sizeof(int32_t) * ntb, cudaMemcpyDeviceToHost, st));
   if (!dev_io) CUF(cudaMemcpyAsync(ctx->st_data.h, ctx->st_data.d, data_total, cudaMemcpyDeviceToHost, st));

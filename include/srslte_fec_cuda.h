@@ -15,6 +15,7 @@
 #ifndef SRSLTE_FEC_CUDA_H
 #define SRSLTE_FEC_CUDA_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -80,6 +81,15 @@ const char *fec_cuda_last_error(fec_cuda_ctx_t *ctx);
 void *fec_cuda_stream(fec_cuda_ctx_t *ctx);
 /* number of kernels launched by this context so far */
 uint64_t fec_cuda_launch_count(fec_cuda_ctx_t *ctx);
+/* device time (CUDA events on the context's stream) of the three phases of the LAST fec_cuda_decode_tbs call:
+ * out3 = { rate de-matching, turbo decode (all K groups), TB assembly + CRC24A } in milliseconds */
+int  fec_cuda_last_phase_ms(fec_cuda_ctx_t *ctx, float out3[3]);
+
+/* Pinned (page-locked) host memory for e_bits / data buffers: replaces srslte_vec_malloc
+ * (lib/src/phy/utils/vector.c:125-132) for the buffers handed to the decode calls. Buffers obtained here (or
+ * registered with cudaHostRegister) are DMA'd directly; any other host pointer is staged through a copy. */
+void *fec_cuda_host_alloc(size_t bytes);
+void  fec_cuda_host_free(void *p);
 
 /* ---- HARQ soft buffers (replace srslte_softbuffer_rx_init/free/reset, softbuffer.c:46-151) ---------- */
 /* allocates n TB soft buffers (13 code-block slots each) in HBM; ids are first_id .. first_id+n-1 */
