@@ -22,6 +22,8 @@ typedef struct {
   uint16_t  *d_rank;
   uint32_t   off[4];
   uint32_t   slots;
+  uint32_t  *d_pair_addr;     /* packed kernel: decoder-2 address words */
+  uint2     *d_pair_crc[2];   /* packed kernel: CRC syndrome words, CRC24A / CRC24B */
 } ktab_t;
 
 typedef struct {
@@ -46,7 +48,10 @@ struct fec_cuda_ctx {
   stage_t       st_e, st_data, st_cbd, st_rmd, st_tbd, st_status, st_ret, st_exd;
   uint8_t      *d_cbbytes; size_t cbbytes_cap;
   int16_t      *d_tmpsoft; size_t tmpsoft_cap;
-  unsigned int *d_queue;   /* FEC_NOF_K counters */
+  unsigned int *d_queue;   /* per K: work-queue counters of the packed and the exact kernel (2 x FEC_NOF_K), then FEC_NOF_K hand-over counts */
+  uint32_t     *d_softmax; size_t softmax_cap;   /* per code block of the call: max |soft-buffer entry| */
+  uint32_t     *d_exact;   size_t exact_cap;     /* per code block of the call: hand-over list of the packed kernel */
+  int           force_exact;
   int16_t      *d_dbg; size_t dbg_cap; uint32_t *dbg_slot; uint32_t dbg_n;   /* test hook: LLR dump */
   cudaEvent_t   ev[4];     /* phase boundaries of the last decode_tbs call: rm | decode | assemble */
   int           ev_valid;
@@ -120,7 +125,8 @@ extern "C" int fec_cuda_create(fec_cuda_ctx_t **out, int device, uint32_t max_tb
   fec_gen_crc_powers(0x1800063u, R, FEC_MAX_K);
   cudaMemcpy(ctx->d_r24b, R, sizeof(uint32_t) * FEC_MAX_K, cudaMemcpyHostToDevice);
   free(R);
-  cudaMalloc(&ctx->d_queue, sizeof(unsigned int) * FEC_NOF_K);
+  cudaMalloc(&ctx->d_queue, sizeof(unsigned int) * 3 * FEC_NOF_K);
+  { const char *fe = getenv("FEC_CUDA_FORCE_EXACT"); ctx->force_exact = fe && fe[0] == '1'; }
   for (int i = 0; i < 4; i++) cudaEventCreate(&ctx->ev[i]);
   if (cudaGetLastError() != cudaSuccess) { free(ctx); return FEC_CUDA_ENODEV; }
   *out = ctx;
@@ -132,7 +138,11 @@ extern "C" void fec_cuda_destroy(fec_cuda_ctx_t *ctx)
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
-  for (int i = 0; i < FEC_NOF_K; i++) if (ctx->ktab[i].ready) { cudaFree(ctx->ktab[i].d_step); cudaFree(ctx->ktab[i].d_rank); }
+  for (int i = 0; i < FEC_NOF_K; i++) if (ctx->ktab[i].ready) {
+    cudaFree(ctx->ktab[i].d_step); cudaFree(ctx->ktab[i].d_rank); cudaFree(ctx->ktab[i].d_pair_addr);
+    cudaFree(ctx->ktab[i].d_pair_crc[0]); cudaFree(ctx->ktab[i].d_pair_crc[1]);
+  }
+  cudaFree(ctx->d_softmax); cudaFree(ctx->d_exact);
   for (uint32_t i = 0; i < ctx->nchunks; i++) { cudaFree(ctx->chunks[i].d_soft); cudaFree(ctx->chunks[i].d_cache); free(ctx->chunks[i].cb_crc); }
   free(ctx->chunks);
   stage_free(&ctx->st_e); stage_free(&ctx->st_data); stage_free(&ctx->st_cbd); stage_free(&ctx->st_rmd);
@@ -181,6 +191,19 @@ static int ktab_get(fec_cuda_ctx_t *ctx, uint32_t K, ktab_t **out)
     CU(cudaMemcpy(t->d_step, step, nstep * 4, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(t->d_rank, rank, nrank * 2, cudaMemcpyHostToDevice));
     free(step); free(rank);
+    if (t->g.P) {
+      const size_t rows = (size_t)(t->g.P / 2) * t->g.Lp;
+      uint32_t *pa = (uint32_t *)malloc(rows * 4), *pc = (uint32_t *)malloc(rows * 16);
+      fec_gen_pair_addr_table(&t->g, pa);
+      CU(cudaMalloc(&t->d_pair_addr, rows * 4));
+      CU(cudaMemcpy(t->d_pair_addr, pa, rows * 4, cudaMemcpyHostToDevice));
+      for (int c = 0; c < 2; c++) {
+        fec_gen_pair_crc_table(&t->g, c ? 0x1800063u : 0x1864CFBu, pc);
+        CU(cudaMalloc(&t->d_pair_crc[c], rows * 16));
+        CU(cudaMemcpy(t->d_pair_crc[c], pc, rows * 16, cudaMemcpyHostToDevice));
+      }
+      free(pa); free(pc);
+    }
     t->slots = t->g.P ? fec_win_pick_slots(&t->g) : 0;
     t->ready = 1;
   }
@@ -246,6 +269,18 @@ extern "C" int fec_cuda_softbuffer_read_ref_layout(fec_cuda_ctx_t *ctx, uint32_t
   return 0;
 }
 
+static void fill_decode_args(fec_cuda_ctx_t *ctx, int k, FecDecodeArgs *a, uint32_t off, uint32_t cnt, int16_t *dbg)
+{
+  const ktab_t *t = &ctx->ktab[k];
+  memset(a, 0, sizeof(*a));
+  a->g = t->g; a->step_tab = t->d_step; a->crcpow[0] = ctx->d_r24a; a->crcpow[1] = ctx->d_r24b;
+  a->cbs = (const FecCbDesc *)ctx->st_cbd.d + off; a->status = (FecCbStatus *)ctx->st_status.d;
+  a->queue = ctx->d_queue + 2 * k; a->ncb = cnt; a->slots = t->slots; a->dbg_llr = dbg;
+  a->pair_addr = t->d_pair_addr; a->pair_crc[0] = t->d_pair_crc[0]; a->pair_crc[1] = t->d_pair_crc[1];
+  a->soft_max = ctx->d_softmax;
+  if (t->g.P && !ctx->force_exact && !dbg) { a->exact_list = ctx->d_exact + off; a->exact_count = ctx->d_queue + 2 * FEC_NOF_K + k; }
+}
+
 /* ---------------------------------------------------------------- batched transport-block decode ---- */
 typedef struct { uint32_t seg[9]; sbchunk_t *chunk; uint32_t local; int valid, pinned; uint32_t first_cb; uint32_t ndec; size_t data_off, e_off; } tbplan_t;
 
@@ -295,6 +330,8 @@ extern "C" int fec_cuda_decode_tbs(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, uint
       stage_reserve(ctx, &ctx->st_tbd, sizeof(FecTbDesc) * ntb) || stage_reserve(ctx, &ctx->st_status, sizeof(FecCbStatus) * (ncb + 1)) ||
       stage_reserve(ctx, &ctx->st_ret, sizeof(int32_t) * ntb) ||
       dev_reserve(ctx, (void **)&ctx->d_cbbytes, &ctx->cbbytes_cap, (size_t)(ncb + 1) * CB_BYTES) ||
+      dev_reserve(ctx, (void **)&ctx->d_softmax, &ctx->softmax_cap, (size_t)(ncb + 1) * 4) ||
+      dev_reserve(ctx, (void **)&ctx->d_exact, &ctx->exact_cap, (size_t)(ncb + 1) * 4) ||
       (!dev_io && (stage_reserve(ctx, &ctx->st_e, e_total * 2) || stage_reserve(ctx, &ctx->st_data, data_total)))) { free(plan); return FEC_CUDA_ENODEV; }
 
   FecCbDesc *cbd = (FecCbDesc *)ctx->st_cbd.h;
@@ -328,7 +365,7 @@ extern "C" int fec_cuda_decode_tbs(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, uint
       const uint32_t slot = grp_off[kt->g.idx] + grp_fill[kt->g.idx]++;
       FecRmDesc *r = &rmd[slot];
       r->e = e_dev + rp; r->soft = soft0 + (size_t)cb * FEC_CUDA_SOFT_SLOT; r->rank = kt->d_rank;
-      r->E = E; r->N = 3 * K + 12; r->off = kt->off[t->rv]; r->n_out = 3 * kt->g.SS + 16; r->new_data = t->new_data ? 1 : 0; r->pad = 0;
+      r->E = E; r->N = 3 * K + 12; r->off = kt->off[t->rv]; r->n_out = 3 * kt->g.SS + 16; r->new_data = t->new_data ? 1 : 0; r->slot = slot;
       if (r->n_out > max_n_out) max_n_out = r->n_out;
       FecCbDesc *d = &cbd[slot];
       d->soft = r->soft; d->out = ctx->d_cbbytes + (size_t)slot * CB_BYTES; d->crc_sel = C > 1 ? 1 : 0;
@@ -370,22 +407,21 @@ extern "C" int fec_cuda_decode_tbs(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, uint
   CUF(cudaMemcpyAsync(ctx->st_cbd.d, cbd, sizeof(FecCbDesc) * ncb, cudaMemcpyHostToDevice, st));
   CUF(cudaMemcpyAsync(ctx->st_rmd.d, rmd, sizeof(FecRmDesc) * ncb, cudaMemcpyHostToDevice, st));
   CUF(cudaMemcpyAsync(ctx->st_tbd.d, tbd, sizeof(FecTbDesc) * ntb, cudaMemcpyHostToDevice, st));
-  CUF(cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned int) * FEC_NOF_K, st));
+  CUF(cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned int) * 3 * FEC_NOF_K, st));
+  CUF(cudaMemsetAsync(ctx->d_softmax, 0, (size_t)ncb * 4, st));
   CUF(cudaEventRecord(ctx->ev[0], st));
   for (uint32_t o = 0; o < ncb; o += 32768) {                       /* grid.y limit */
     const uint32_t m = ncb - o < 32768 ? ncb - o : 32768;
-    CUF(fec_launch_rm((const FecRmDesc *)ctx->st_rmd.d + o, m, max_n_out, st));
+    CUF(fec_launch_rm((const FecRmDesc *)ctx->st_rmd.d + o, ctx->d_softmax, m, max_n_out, st));
     ctx->launches++;
   }
   CUF(cudaEventRecord(ctx->ev[1], st));
   for (int k = 0; k < FEC_NOF_K; k++) {
     if (!grp_cnt[k]) continue;
     FecDecodeArgs a;
-    a.g = ctx->ktab[k].g; a.step_tab = ctx->ktab[k].d_step; a.crcpow[0] = ctx->d_r24a; a.crcpow[1] = ctx->d_r24b;
-    a.cbs = (const FecCbDesc *)ctx->st_cbd.d + grp_off[k]; a.status = (FecCbStatus *)ctx->st_status.d;
-    a.queue = ctx->d_queue + k; a.ncb = grp_cnt[k]; a.slots = ctx->ktab[k].slots; a.dbg_llr = DBG_LLR;
+    fill_decode_args(ctx, k, &a, grp_off[k], grp_cnt[k], DBG_LLR);
     CUF(fec_launch_decode(a, ctx->sm_count, st));
-    ctx->launches++;
+    ctx->launches += a.exact_list ? 2 : 1;
   }
   CUF(cudaEventRecord(ctx->ev[2], st));
   CUF(fec_launch_tb_assemble((const FecTbDesc *)ctx->st_tbd.d, (const FecCbStatus *)ctx->st_status.d, ctx->d_r24a, ntb, st));
@@ -447,6 +483,8 @@ extern "C" int fec_cuda_decode_cbs(fec_cuda_ctx_t *ctx, fec_cuda_cb_t *cbs, uint
   if (stage_reserve(ctx, &ctx->st_e, llr_total * 2) || stage_reserve(ctx, &ctx->st_cbd, sizeof(FecCbDesc) * n) ||
       stage_reserve(ctx, &ctx->st_exd, sizeof(FecExtractDesc) * n) || stage_reserve(ctx, &ctx->st_status, sizeof(FecCbStatus) * n) ||
       stage_reserve(ctx, &ctx->st_data, (size_t)n * CB_BYTES) ||
+      dev_reserve(ctx, (void **)&ctx->d_softmax, &ctx->softmax_cap, (size_t)(n + 1) * 4) ||
+      dev_reserve(ctx, (void **)&ctx->d_exact, &ctx->exact_cap, (size_t)(n + 1) * 4) ||
       dev_reserve(ctx, (void **)&ctx->d_tmpsoft, &ctx->tmpsoft_cap, (size_t)n * FEC_CUDA_SOFT_SLOT * sizeof(int16_t))) return FEC_CUDA_ENODEV;
   if (ctx->dbg_cap && ctx->dbg_cap < (size_t)n * FEC_MAX_K * 2) { cudaFree(ctx->d_dbg); ctx->d_dbg = NULL; ctx->dbg_cap = 0; }
   FecCbDesc *cbd = (FecCbDesc *)ctx->st_cbd.h;
@@ -460,7 +498,7 @@ extern "C" int fec_cuda_decode_cbs(fec_cuda_ctx_t *ctx, fec_cuda_cb_t *cbs, uint
     slot_of[i] = slot;
     const size_t len = (size_t)3 * cbs[i].K + 12;
     memcpy((int16_t *)ctx->st_e.h + eo, cbs[i].llr, len * 2);
-    exd[slot].in = (const int16_t *)ctx->st_e.d + eo; exd[slot].soft = ctx->d_tmpsoft + (size_t)slot * FEC_CUDA_SOFT_SLOT; exd[slot].g = kt->g;
+    exd[slot].in = (const int16_t *)ctx->st_e.d + eo; exd[slot].soft = ctx->d_tmpsoft + (size_t)slot * FEC_CUDA_SOFT_SLOT; exd[slot].g = kt->g; exd[slot].slot = slot;
     eo += (len + 7) & ~(size_t)7;
     cbd[slot].soft = exd[slot].soft; cbd[slot].out = (uint8_t *)ctx->st_data.d + (size_t)slot * CB_BYTES;
     cbd[slot].crc_sel = cbs[i].crc_type ? 1 : 0; cbd[slot].max_its = cbs[i].max_its ? cbs[i].max_its : 1;
@@ -471,19 +509,18 @@ extern "C" int fec_cuda_decode_cbs(fec_cuda_ctx_t *ctx, fec_cuda_cb_t *cbs, uint
   CUF(cudaMemcpyAsync(ctx->st_e.d, ctx->st_e.h, llr_total * 2, cudaMemcpyHostToDevice, st));
   CUF(cudaMemcpyAsync(ctx->st_cbd.d, cbd, sizeof(FecCbDesc) * n, cudaMemcpyHostToDevice, st));
   CUF(cudaMemcpyAsync(ctx->st_exd.d, exd, sizeof(FecExtractDesc) * n, cudaMemcpyHostToDevice, st));
-  CUF(cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned int) * FEC_NOF_K, st));
+  CUF(cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned int) * 3 * FEC_NOF_K, st));
+  CUF(cudaMemsetAsync(ctx->d_softmax, 0, (size_t)n * 4, st));
   for (uint32_t o = 0; o < n; o += 32768) {
-    CUF(fec_launch_extract((const FecExtractDesc *)ctx->st_exd.d + o, n - o < 32768 ? n - o : 32768, st));
+    CUF(fec_launch_extract((const FecExtractDesc *)ctx->st_exd.d + o, ctx->d_softmax, n - o < 32768 ? n - o : 32768, st));
     ctx->launches++;
   }
   for (int k = 0; k < FEC_NOF_K; k++) {
     if (!grp_cnt[k]) continue;
     FecDecodeArgs a;
-    a.g = ctx->ktab[k].g; a.step_tab = ctx->ktab[k].d_step; a.crcpow[0] = ctx->d_r24a; a.crcpow[1] = ctx->d_r24b;
-    a.cbs = (const FecCbDesc *)ctx->st_cbd.d + grp_off[k]; a.status = (FecCbStatus *)ctx->st_status.d;
-    a.queue = ctx->d_queue + k; a.ncb = grp_cnt[k]; a.slots = ctx->ktab[k].slots; a.dbg_llr = DBG_LLR;
+    fill_decode_args(ctx, k, &a, grp_off[k], grp_cnt[k], DBG_LLR);
     CUF(fec_launch_decode(a, ctx->sm_count, st));
-    ctx->launches++;
+    ctx->launches += a.exact_list ? 2 : 1;
   }
   CUF(cudaMemcpyAsync(ctx->st_status.h, ctx->st_status.d, sizeof(FecCbStatus) * n, cudaMemcpyDeviceToHost, st));
   CUF(cudaMemcpyAsync(ctx->st_data.h, ctx->st_data.d, (size_t)n * CB_BYTES, cudaMemcpyDeviceToHost, st));
@@ -508,15 +545,16 @@ extern "C" int fec_cuda_rm_rx(fec_cuda_ctx_t *ctx, const int16_t *in, uint32_t E
   void *plan = NULL;
   if (stage_reserve(ctx, &ctx->st_e, ((size_t)E + 8) * 2) || stage_reserve(ctx, &ctx->st_rmd, sizeof(FecRmDesc)) ||
       stage_reserve(ctx, &ctx->st_data, 18600 * 2) ||
+      dev_reserve(ctx, (void **)&ctx->d_softmax, &ctx->softmax_cap, 8) ||
       dev_reserve(ctx, (void **)&ctx->d_tmpsoft, &ctx->tmpsoft_cap, 2 * FEC_CUDA_SOFT_SLOT * sizeof(int16_t))) return FEC_CUDA_ENODEV;
   memcpy(ctx->st_e.h, in, (size_t)E * 2);
   FecRmDesc *r = (FecRmDesc *)ctx->st_rmd.h;
   r->e = (const int16_t *)ctx->st_e.d; r->soft = ctx->d_tmpsoft; r->rank = kt->d_rank; r->E = E; r->N = 3 * kt->g.K + 12;
-  r->off = kt->off[rv]; r->n_out = 3 * kt->g.SS + 16; r->new_data = 1; r->pad = 0;
+  r->off = kt->off[rv]; r->n_out = 3 * kt->g.SS + 16; r->new_data = 1; r->slot = 0;
   cudaStream_t st = ctx->stream;
   CUF(cudaMemcpyAsync(ctx->st_e.d, ctx->st_e.h, (size_t)E * 2, cudaMemcpyHostToDevice, st));
   CUF(cudaMemcpyAsync(ctx->st_rmd.d, r, sizeof(FecRmDesc), cudaMemcpyHostToDevice, st));
-  CUF(fec_launch_rm((const FecRmDesc *)ctx->st_rmd.d, 1, r->n_out, st));
+  CUF(fec_launch_rm((const FecRmDesc *)ctx->st_rmd.d, ctx->d_softmax, 1, r->n_out, st));
   CUF(fec_launch_soft_to_ref(ctx->d_tmpsoft, (int16_t *)ctx->st_data.d, kt->g, sb_layout, st));
   ctx->launches += 2;
   CUF(cudaMemcpyAsync(ctx->st_data.h, ctx->st_data.d, 18600 * 2, cudaMemcpyDeviceToHost, st));

@@ -104,9 +104,9 @@ __device__ __forceinline__ void win_load_xy(const WinLane &w, int k, int &x, int
 {
   const uint32_t t = __ldg(w.T + k);
   const int e = w.E[t & 0xFFFFu];
-  const int s = (int)__ldg(w.S + k) & w.smask;
+  const int s = (int)__ldg(w.S + 2 * k) & w.smask;
   x = sat16(s + e);
-  y = (int)__ldg(w.Y + k);
+  y = (int)__ldg(w.Y + 2 * k);
 }
 
 size_t fec_win_smem_bytes(const fec_geom_t *g, uint32_t slots)
@@ -158,7 +158,8 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 1) fec_tdec_win_kernel(const 
     /* ---- refill idle slots from the work queue ---- */
     if (d == 0 && s_cb[slot] < 0 && !s_empty) {
       const unsigned q = atomicAdd(a.queue, 1u);
-      if (q < a.ncb) { s_cb[slot] = (int)q; s_n[slot] = 0; s_fresh[slot] = 1; }
+      const unsigned total = a.list ? *a.list_count : a.ncb;
+      if (q < total) { s_cb[slot] = a.list ? (int)a.list[q] : (int)q; s_n[slot] = 0; s_fresh[slot] = 1; }
       else s_empty = 1;
     }
     __syncthreads();
@@ -176,8 +177,8 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 1) fec_tdec_win_kernel(const 
       const FecCbDesc desc = a.cbs[cb];
       const int n = s_n[slot], par = n & 1;
       WinLane w;
-      w.S = desc.soft + d * Lp;
-      w.Y = desc.soft + (1 + par) * SS + d * Lp;
+      w.S = desc.soft + (d >> 1) * 2 * Lp + (d & 1);              /* pair-row layout: lane d, step k at row[2k + (d&1)] */
+      w.Y = desc.soft + (1 + par) * SS + (d >> 1) * 2 * Lp + (d & 1);
       w.T = a.step_tab + par * SS + d * Lp;
       w.E = E;
       w.smask = par ? 0 : -1;
@@ -266,8 +267,8 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 1) fec_tdec_win_kernel(const 
           const uint32_t t = __ldg(w.T + k);
           const int ea = t & 0xFFFFu, nat = t >> 16;
           const int e = w.E[ea];
-          x = sat16(((int)__ldg(w.S + k) & w.smask) + e);
-          y = (int)__ldg(w.Y + k);
+          x = sat16(((int)__ldg(w.S + 2 * k) & w.smask) + e);
+          y = (int)__ldg(w.Y + 2 * k);
           win_alpha_branches(o, x, y, m, nb);
           int b[8], v0[8], v1[8];
           unpack8_true((k == khi - 1) ? ck : chunk[(k - klo) * nthr + tid], b);
@@ -335,7 +336,8 @@ __global__ void fec_tdec_small_kernel(const FecDecodeArgs a)
   for (;;) {
     if (cb < 0 && !s_empty) {
       const unsigned q = atomicAdd(a.queue, 1u);
-      if (q < a.ncb) { cb = (int)q; n = 0; for (int i = 0; i < K; i++) E[i * nthr + tid] = 0; }
+      const unsigned total = a.list ? *a.list_count : a.ncb;
+      if (q < total) { cb = a.list ? (int)a.list[q] : (int)q; n = 0; for (int i = 0; i < K; i++) E[i * nthr + tid] = 0; }
       else s_empty = 1;
     }
     if (!__syncthreads_or(cb >= 0)) break;
@@ -460,6 +462,19 @@ cudaError_t fec_launch_decode(const FecDecodeArgs &a, int sm_count, cudaStream_t
     fec_tdec_small_kernel<<<grid, nthr, smem, st>>>(a);
     return cudaGetLastError();
   }
+  if (a.exact_list && !a.dbg_llr) {
+    /* fast path first; whatever it hands over (range condition) is decoded by the exact kernel */
+    cudaError_t e = fec_launch_decode_packed(a, sm_count, st);
+    if (e != cudaSuccess) return e;
+    FecDecodeArgs b = a;
+    b.list = a.exact_list; b.list_count = a.exact_count; b.queue = a.queue + 1;
+    const uint32_t slots = b.slots;
+    const size_t smem = fec_win_smem_bytes(&b.g, slots);
+    const int grid = sm_count;                     /* persistent; CTAs find the list empty and exit in the common case */
+    if (b.g.P == 16) fec_tdec_win_kernel<16><<<grid, slots * 16, smem, st>>>(b);
+    else             fec_tdec_win_kernel<8><<<grid, slots * 8, smem, st>>>(b);
+    return cudaGetLastError();
+  }
   const uint32_t slots = a.slots;
   const size_t smem = fec_win_smem_bytes(&a.g, slots);
   int grid = (int)((a.ncb + slots - 1) / slots);
@@ -476,11 +491,19 @@ cudaError_t fec_launch_decode(const FecDecodeArgs &a, int sm_count, cudaStream_t
  * the same sums as a scatter: soft[deinter[i % N]] += e[i]). Thread = 8 consecutive int16 of the slot:
  * one 16-byte load of the rank table, one 16-byte read-modify-write of the slot, coalesced.
  * ===================================================================================================== */
-__global__ void __launch_bounds__(256) fec_rm_rx_kernel(const FecRmDesc *descs)
+__device__ __forceinline__ void fec_softmax_commit(uint32_t *dst, int amax)
+{
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) amax = max(amax, __shfl_xor_sync(0xFFFFFFFFu, amax, s));
+  if ((threadIdx.x & 31) == 0 && amax > 0) atomicMax(dst, (uint32_t)amax);
+}
+
+__global__ void __launch_bounds__(256) fec_rm_rx_kernel(const FecRmDesc *descs, uint32_t *soft_max)
 {
   const FecRmDesc d = descs[blockIdx.y];
   const uint32_t o = (blockIdx.x * blockDim.x + threadIdx.x) * 8;
-  if (o >= d.n_out) return;
+  int amax = 0;
+  if (o < d.n_out) {
   const uint4 rk = *reinterpret_cast<const uint4 *>(d.rank + o);
   uint4 old = make_uint4(0, 0, 0, 0);
   if (!d.new_data) old = *reinterpret_cast<const uint4 *>(d.soft + o);
@@ -499,40 +522,50 @@ __global__ void __launch_bounds__(256) fec_rm_rx_kernel(const FecRmDesc *descs)
         for (; j < d.E; j += d.N) acc += (int)__ldg(d.e + j);      /* repeats accumulate when E > 3K+12 */
       }
       res |= ((uint32_t)acc & 0xFFFFu) << (16 * h);               /* wrapping int16 */
+      const int sv = (int)(short)acc;
+      amax = max(amax, sv < 0 ? -sv : sv);
     }
     ow[i] = res;
   }
   *reinterpret_cast<uint4 *>(d.soft + o) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+  }
+  fec_softmax_commit(soft_max + d.slot, amax);
 }
 
-cudaError_t fec_launch_rm(const FecRmDesc *descs, uint32_t n, uint32_t max_n_out, cudaStream_t st)
+cudaError_t fec_launch_rm(const FecRmDesc *descs, uint32_t *soft_max, uint32_t n, uint32_t max_n_out, cudaStream_t st)
 {
   if (n == 0) return cudaSuccess;
   dim3 grid((max_n_out / 8 + 255) / 256, n);
-  fec_rm_rx_kernel<<<grid, 256, 0, st>>>(descs);
+  fec_rm_rx_kernel<<<grid, 256, 0, st>>>(descs, soft_max);
   return cudaGetLastError();
 }
 
 /* natural [s p p'] x K + 12 tail  ->  device layout (srslte_tdec_* level input, force_not_sb path) */
-__global__ void __launch_bounds__(256) fec_extract_kernel(const FecExtractDesc *descs)
+__global__ void __launch_bounds__(256) fec_extract_kernel(const FecExtractDesc *descs, uint32_t *soft_max)
 {
   const FecExtractDesc d = descs[blockIdx.y];
   const int n_out = 3 * d.g.SS + 16;
+  int amax = 0;
   for (int o = blockIdx.x * blockDim.x + threadIdx.x; o < n_out; o += gridDim.x * blockDim.x) {
     int16_t v = 0;
     if (o >= 3 * d.g.SS) { if (o < 3 * d.g.SS + 12) v = d.in[3 * d.g.K + (o - 3 * d.g.SS)]; }
     else {
-      const int s = o / d.g.SS, r = o % d.g.SS, lane = r / d.g.Lp, k = r % d.g.Lp;
+      const int s = o / d.g.SS, r = o % d.g.SS;
+      int lane, k;
+      if (d.g.P) { lane = 2 * (r / (2 * d.g.Lp)) + (r & 1); k = (r % (2 * d.g.Lp)) >> 1; }
+      else { lane = 0; k = r; }
       if (k < d.g.L) v = d.in[3 * (lane * d.g.L + k) + s];
     }
     d.soft[o] = v;
+    amax = max(amax, v < 0 ? -(int)v : (int)v);
   }
+  fec_softmax_commit(soft_max + d.slot, amax);
 }
 
-cudaError_t fec_launch_extract(const FecExtractDesc *descs, uint32_t n, cudaStream_t st)
+cudaError_t fec_launch_extract(const FecExtractDesc *descs, uint32_t *soft_max, uint32_t n, cudaStream_t st)
 {
   if (n == 0) return cudaSuccess;
-  fec_extract_kernel<<<dim3(8, n), 256, 0, st>>>(descs);
+  fec_extract_kernel<<<dim3(8, n), 256, 0, st>>>(descs, soft_max);
   return cudaGetLastError();
 }
 
@@ -546,8 +579,8 @@ __global__ void fec_soft_to_ref_kernel(const int16_t *dev, int16_t *ref, fec_geo
     int od, orf;
     if (t >= 3 * g.K) { od = 3 * g.SS + (t - 3 * g.K); orf = (sb && g.P) ? 3 * (g.K + 32) + (t - 3 * g.K) : t; }
     else {
-      const int s = t % 3, x = t / 3;
-      od = s * g.SS + (x / g.L) * g.Lp + x % g.L;
+      const int s = t % 3, x = t / 3, dl = x / g.L, kk = x % g.L;
+      od = g.P ? s * g.SS + (dl >> 1) * 2 * g.Lp + 2 * kk + (dl & 1) : s * g.SS + kk;
       orf = (sb && g.P) ? s * (g.K + 32) + (x % g.L) * g.P + x / g.L : t;
     }
     ref[orf] = dev[od];
@@ -624,6 +657,8 @@ cudaError_t fec_launch_tb_assemble(const FecTbDesc *descs, const FecCbStatus *st
 cudaError_t fec_kernels_init(void)
 {
   cudaError_t e;
+  e = fec_pk_init();
+  if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(fec_tdec_win_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(fec_tdec_win_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);

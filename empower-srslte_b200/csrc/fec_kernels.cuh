@@ -11,6 +11,8 @@
 #define FEC_WIN_THREADS   128     /* MAP lanes per CTA in the windowed kernel = slots x P */
 #define FEC_WIN_CHUNK     16      /* beta checkpoint spacing S (trellis steps) */
 #define FEC_F_NO_EARLY    1u
+#define FEC_PK_WARPS      4       /* packed kernel: warps per CTA (= tensor-memory lane quarters) */
+#define FEC_PK_GMAX       2000u   /* packed kernel: largest max|x| + max|y| for which int16 saturation is excluded */
 
 /* one code block of a decode launch */
 struct FecCbDesc {
@@ -35,6 +37,15 @@ struct FecDecodeArgs {
   uint32_t          ncb;
   uint32_t          slots;      /* code blocks in flight per CTA */
   int16_t          *dbg_llr;    /* optional [ncb][6144]: LLRs of the last half-iteration, natural order (tests only) */
+  /* packed fast path (fec_tdec_packed.cu) */
+  const uint32_t   *pair_addr;  /* decoder-2 address words, (P/2) x Lp */
+  const uint2      *pair_crc[2];/* CRC syndrome words per polynomial, [2 parities][(P/2) x Lp] */
+  const uint32_t   *soft_max;   /* per status slot: max |soft-buffer entry| of the code block (rate de-matching / extract kernel) */
+  uint32_t         *exact_list; /* out: code blocks (indices into cbs) outside the proven range -> exact kernel */
+  unsigned int     *exact_count;
+  /* exact kernels: optional indirect work list (NULL = all ncb code blocks) */
+  const uint32_t   *list;
+  const unsigned int *list_count;
 };
 
 /* one code block of a rate-dematching launch */
@@ -47,11 +58,11 @@ struct FecRmDesc {
   uint32_t        off;      /* start rank for this rv */
   uint32_t        n_out;    /* 3*SS+16 (multiple of 8) */
   uint32_t        new_data; /* 1: overwrite (fresh HARQ process), 0: accumulate */
-  uint32_t        pad;
+  uint32_t        slot;     /* status slot: soft_max[slot] receives max |soft-buffer entry| */
 };
 
 /* natural-layout [s p p']xK+12 input -> device-layout slot (srslte_tdec_* level entry) */
-struct FecExtractDesc { const int16_t *in; int16_t *soft; fec_geom_t g; };
+struct FecExtractDesc { const int16_t *in; int16_t *soft; fec_geom_t g; uint32_t slot; };
 
 /* one transport block of the assembly/CRC24A launch */
 struct FecTbDesc {
@@ -69,8 +80,11 @@ struct FecTbDesc {
 size_t fec_win_smem_bytes(const fec_geom_t *g, uint32_t slots);
 uint32_t fec_win_pick_slots(const fec_geom_t *g);
 cudaError_t fec_launch_decode(const FecDecodeArgs &a, int sm_count, cudaStream_t st);
-cudaError_t fec_launch_rm(const FecRmDesc *descs, uint32_t n, uint32_t max_n_out, cudaStream_t st);
-cudaError_t fec_launch_extract(const FecExtractDesc *descs, uint32_t n, cudaStream_t st);
+cudaError_t fec_launch_decode_packed(const FecDecodeArgs &a, int sm_count, cudaStream_t st);
+size_t fec_pk_smem_bytes(const fec_geom_t *g);
+cudaError_t fec_pk_init(void);
+cudaError_t fec_launch_rm(const FecRmDesc *descs, uint32_t *soft_max, uint32_t n, uint32_t max_n_out, cudaStream_t st);
+cudaError_t fec_launch_extract(const FecExtractDesc *descs, uint32_t *soft_max, uint32_t n, cudaStream_t st);
 cudaError_t fec_launch_tb_assemble(const FecTbDesc *descs, const FecCbStatus *status, const uint32_t *r24a,
                                    uint32_t n, cudaStream_t st);
 cudaError_t fec_launch_soft_to_ref(const int16_t *soft_dev, int16_t *ref_dev, fec_geom_t g, int sb_layout, cudaStream_t st);

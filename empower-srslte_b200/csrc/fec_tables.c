@@ -7,6 +7,7 @@
 #include "fec_tables.h"
 #include "lte_qpp_table.h"
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 int fec_k_index(uint32_t K)
@@ -54,6 +55,7 @@ int fec_geom(uint32_t K, fec_geom_t *g)
   if (g->P) { g->LpE = g->L; while ((g->LpE & 3) != 2) g->LpE++; }
   else g->LpE = g->K;
   g->SS = g->NL * g->Lp;
+  g->Lw = g->L; while ((g->Lw & 7) != 4) g->Lw++;
   g->f1 = lte_qpp_table[idx][1]; g->f2 = lte_qpp_table[idx][2];
   return 0;
 }
@@ -71,14 +73,51 @@ void fec_gen_step_table(const fec_geom_t *g, uint32_t *tab)
     }
 }
 
+static int qpp_nat(const fec_geom_t *g, int par, int j)
+{
+  uint64_t jj = (uint64_t)j;
+  return par ? (int)(((uint64_t)g->f1 * jj + (uint64_t)g->f2 * jj * jj) % (uint64_t)g->K) : j;
+}
+
+void fec_gen_pair_addr_table(const fec_geom_t *g, uint32_t *tab)
+{
+  const int L = g->L;
+  memset(tab, 0, sizeof(uint32_t) * (size_t)(g->P / 2) * g->Lp);
+  for (int j = 0; j < g->P / 2; j++)
+    for (int k = 0; k < L; k++) {
+      uint32_t ea[2];
+      for (int h = 0; h < 2; h++) {
+        const int nat = qpp_nat(g, 1, (2 * j + h) * L + k), d = nat / L, kk = nat % L;
+        ea[h] = (uint32_t)(2 * ((d >> 1) * g->Lw + kk) + (d & 1));
+      }
+      tab[(size_t)j * g->Lp + k] = (ea[1] << 16) | ea[0];
+    }
+}
+
+void fec_gen_pair_crc_table(const fec_geom_t *g, uint32_t poly, uint32_t *tab)
+{
+  const int L = g->L, K = g->K;
+  const size_t rows = (size_t)(g->P / 2) * g->Lp;
+  uint32_t *R = (uint32_t *)malloc(sizeof(uint32_t) * (size_t)K);
+  fec_gen_crc_powers(poly, R, K);
+  memset(tab, 0, sizeof(uint32_t) * 2 * 2 * rows);
+  for (int par = 0; par < 2; par++)
+    for (int j = 0; j < g->P / 2; j++)
+      for (int k = 0; k < L; k++)
+        for (int h = 0; h < 2; h++)
+          tab[2 * ((size_t)par * rows + (size_t)j * g->Lp + k) + h] = R[K - 1 - qpp_nat(g, par, (2 * j + h) * L + k)];
+  free(R);
+}
+
 static const uint8_t rm_colperm[32] = {0, 16, 8, 24, 4, 20, 12, 28, 2, 18, 10, 26, 6, 22, 14, 30,
                                        1, 17, 9, 25, 5, 21, 13, 29, 3, 19, 11, 27, 7, 23, 15, 31};
 
 int fec_soft_offset_dev(const fec_geom_t *g, int t)
 {
   if (t >= 3 * g->K) return 3 * g->SS + (t - 3 * g->K);
-  int s = t % 3, x = t / 3;
-  return s * g->SS + (x / g->L) * g->Lp + x % g->L;
+  int s = t % 3, x = t / 3, d = x / g->L, k = x % g->L;
+  if (g->P == 0) return s * g->SS + k;
+  return s * g->SS + (d >> 1) * 2 * g->Lp + 2 * k + (d & 1);
 }
 
 int fec_soft_offset_ref(const fec_geom_t *g, int t, int sb_layout)

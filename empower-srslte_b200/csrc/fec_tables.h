@@ -16,10 +16,13 @@ extern "C" {
 #define FEC_R24A_LEN     (13 * 6144 + 64)   /* CRC power table long enough for the largest transport block */
 
 /* Device layout of one code block ("geometry"). The reference's sub-block-interleaved soft buffer
- * (rm_turbo.c:250-264: element k of sub-block d at k*P+d) becomes, on the device, NL contiguous lanes of
- * Lp int16 per stream so that one thread walks one sub-block with unit stride:
- *   stream s (0 syst, 1 parity, 2 parity'), lane d, step k  ->  s*SS + d*Lp + k ;  12 tail LLRs at 3*SS.
- * The extrinsic array E lives in shared memory with lane stride LpE (LpE/2 odd: conflict-free gathers). */
+ * (rm_turbo.c:250-264: element k of sub-block d at k*P+d) becomes, on the device, PAIR rows: sub-blocks
+ * (lanes) 2j and 2j+1 share one row of Lp 32-bit words, word k = (lane 2j | lane 2j+1 << 16) at step k, so
+ * that one thread walks two sub-blocks with packed s16x2 arithmetic and 16-byte loads:
+ *   stream s (0 syst, 1 parity, 2 parity'), lane d, step k  ->  int16 index s*SS + (d>>1)*2*Lp + 2*k + (d&1)
+ *   (non-windowed class P=0: one lane, index s*SS + k);  12 tail LLRs at 3*SS.
+ * Exact (32-bit) kernels keep the extrinsic array E in shared memory with lane stride LpE (LpE/2 odd:
+ * conflict-free gathers); the packed kernel keeps E in pair rows of Lw words (Lw mod 8 == 4). */
 typedef struct {
   int K;      /* code block size */
   int idx;    /* index in the 188-entry table */
@@ -27,7 +30,8 @@ typedef struct {
   int NL;     /* lanes = P, or 1 for the non-windowed class */
   int L;      /* K / NL */
   int Lp;     /* lane stride in HBM, multiple of 8 */
-  int LpE;    /* lane stride of E in shared memory */
+  int LpE;    /* lane stride of E in shared memory (exact kernels) */
+  int Lw;     /* pair-row stride of E in words (packed kernel), Lw >= L, Lw mod 8 == 4 */
   int SS;     /* stream stride NL*Lp */
   int f1, f2; /* QPP parameters */
 } fec_geom_t;
@@ -40,6 +44,12 @@ int  fec_geom(uint32_t K, fec_geom_t *g);        /* -1 if K is not an LTE size *
 
 /* step table, 2 parities x NL x Lp entries of (natural_position << 16 | E_address); pads = 0 */
 void fec_gen_step_table(const fec_geom_t *g, uint32_t *tab);
+/* packed kernel: address table of the INTERLEAVED decoder, (P/2) x Lp words: (E halfword index of lane 2j+1) << 16
+ * | (E halfword index of lane 2j) at step k, E halfword index of natural bit (d',k') = 2*((d'>>1)*Lw + k') + (d'&1) */
+void fec_gen_pair_addr_table(const fec_geom_t *g, uint32_t *tab);
+/* packed kernel: CRC syndrome words per pair-step, [2 parities][(P/2) x Lp] uint2 = {R of lane 2j's bit, R of lane 2j+1's bit}
+ * with R = x^(K-1-nat+24) mod g(x) of the natural position decided at that step; crc_sel picks the polynomial */
+void fec_gen_pair_crc_table(const fec_geom_t *g, uint32_t poly, uint32_t *tab);
 /* rate-matching rank table in device soft-buffer layout (3*SS+16 entries, pad = 0xFFFF) and the 4 rv
  * start ranks: transmitted index of soft position o for rv is (rank[o] - off[rv]) mod (3K+12). */
 void fec_gen_rm_rank(const fec_geom_t *g, uint16_t *rank, uint32_t off[4]);

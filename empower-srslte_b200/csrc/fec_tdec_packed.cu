@@ -1,0 +1,488 @@
+/*
+ * fec_tdec_packed.cu — the fast path of the windowed max-log-MAP turbo decoder (classes P=16 and P=8).
+ *
+ * Replaces tdec_win{avx16,sse16}_dec + run_tdec_iteration_16bit + the CRC early-stop loop of decode_tb_cb
+ * (turbodecoder_win.h:310-586, turbodecoder_iter.h:73-147, sch.c:361-391) for every half-iteration whose
+ * inputs satisfy the range condition below; code blocks that do not are handed, untouched, to the exact
+ * 32-bit kernel in fec_kernels.cu (same results by construction, it saturates like the reference).
+ *
+ * Arithmetic: two sub-blocks (lanes 2j, 2j+1) of one code block per thread, all 8 trellis states in 8
+ * registers of packed int16x2; adds are VIADD.16x2 / VIADDMNMX.S16x2 (max(a+b,c), one instruction), which
+ * WRAP where the reference SATURATES. They are identical as long as no intermediate leaves int16.
+ * Range condition (proof in DESIGN.md section 3.3): with G = max|x| + max|y| over the half-iteration
+ * (x = systematic + apriori, y = parity, tails included), every intermediate of the reference is bounded
+ * by 10000 + 10 G, so G <= FEC_PK_GMAX = 2000 excludes saturation. G of the NEXT half-iteration is known
+ * when the current one ends (max|new extrinsic| is tracked), so the decision is taken before any work is lost.
+ *
+ * Memory: the extrinsic/apriori array E of every resident code block lives in shared memory (pair rows of
+ * Lw words), the interleaver address table of decoder 2 once per CTA; beta checkpoints every 8 steps live in
+ * TENSOR MEMORY (tcgen05.st/ld, 32 lanes x 8 columns per checkpoint, lane-private), the 7 recomputed betas
+ * of a chunk in registers. Systematic/parity streams are read from HBM/L2 as 16-byte words (4 steps).
+ * One warp = 32/(P/2) code blocks in lockstep; warps are independent (no CTA barrier in the loop).
+ */
+#include "fec_kernels.cuh"
+
+#define PK_CH      8                 /* checkpoint spacing = chunk length (trellis steps) */
+#define PK_NEG     0xD8F0D8F0u       /* (-10000, -10000) */
+#define PK_WARPS   FEC_PK_WARPS
+
+#ifndef FEC_PK_TMEM
+#define FEC_PK_TMEM 1
+#endif
+
+/* ---------------------------------------------------------------- packed helpers ---- */
+__device__ __forceinline__ uint32_t pk_add(uint32_t a, uint32_t b) { return __vadd2(a, b); }
+__device__ __forceinline__ uint32_t pk_sub(uint32_t a, uint32_t b) { return __vsub2(a, b); }
+__device__ __forceinline__ uint32_t pk_max(uint32_t a, uint32_t b) { return __vmaxs2(a, b); }
+__device__ __forceinline__ uint32_t pk_min(uint32_t a, uint32_t b) { return __vmins2(a, b); }
+__device__ __forceinline__ uint32_t pk_addmax(uint32_t a, uint32_t b, uint32_t c) { return __viaddmax_s16x2(a, b, c); }
+__device__ __forceinline__ uint32_t pk_prmt(uint32_t a, uint32_t b, uint32_t sel)
+{
+  uint32_t r;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
+  return r;
+}
+
+/* turbodecoder_win.h:244-261: subtract state 0 from states 1..7, state 0 := 0 (every even k != 0) */
+__device__ __forceinline__ void pk_norm(uint32_t *o)
+{
+#pragma unroll
+  for (int i = 1; i < 8; i++) o[i] = pk_sub(o[i], o[0]);
+  o[0] = 0;
+}
+
+/* backward step (turbodecoder_win.h:397-418), 4 adds + 8 add-max */
+__device__ __forceinline__ void pk_beta(uint32_t *o, uint32_t x, uint32_t y)
+{
+  const uint32_t xy = pk_add(x, y);
+  uint32_t n[8];
+  n[0] = pk_addmax(o[4], xy, o[0]);
+  n[1] = pk_addmax(o[0], xy, o[4]);
+  n[2] = pk_addmax(o[1], x, pk_add(o[5], y));
+  n[3] = pk_addmax(o[1], y, pk_add(o[5], x));
+  n[4] = pk_addmax(o[2], y, pk_add(o[6], x));
+  n[5] = pk_addmax(o[2], x, pk_add(o[6], y));
+  n[6] = pk_addmax(o[3], xy, o[7]);
+  n[7] = pk_addmax(o[7], xy, o[3]);
+#pragma unroll
+  for (int i = 0; i < 8; i++) o[i] = n[i];
+}
+
+/* forward branches (turbodecoder_win.h:521-539): m = bit-0 hypothesis, n = bit-1 hypothesis */
+__device__ __forceinline__ void pk_alpha_branches(const uint32_t *o, uint32_t x, uint32_t y, uint32_t *m, uint32_t *n)
+{
+  const uint32_t xy = pk_add(x, y);
+  m[0] = o[0];             m[1] = pk_add(o[3], y); m[2] = pk_add(o[4], y); m[3] = o[7];
+  m[4] = o[1];             m[5] = pk_add(o[2], y); m[6] = pk_add(o[5], y); m[7] = o[6];
+  n[0] = pk_add(o[1], xy); n[1] = pk_add(o[2], x); n[2] = pk_add(o[5], x); n[3] = pk_add(o[6], xy);
+  n[4] = pk_add(o[0], xy); n[5] = pk_add(o[3], x); n[6] = pk_add(o[4], x); n[7] = pk_add(o[7], xy);
+}
+
+/* ---------------------------------------------------------------- tensor-memory checkpoint store ---- */
+#if FEC_PK_TMEM
+__device__ __forceinline__ void pk_ck_store(uint32_t taddr, const uint32_t *o)
+{
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+               :: "r"(taddr), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]), "r"(o[4]), "r"(o[5]), "r"(o[6]), "r"(o[7]) : "memory");
+}
+__device__ __forceinline__ void pk_ck_store_fence() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void pk_ck_load(uint32_t taddr, uint32_t *o)
+{
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(o[0]), "=r"(o[1]), "=r"(o[2]), "=r"(o[3]), "=r"(o[4]), "=r"(o[5]), "=r"(o[6]), "=r"(o[7]) : "r"(taddr) : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+#endif
+
+/* ---------------------------------------------------------------- per-thread view of one half-iteration ---- */
+struct PkView {
+  const uint32_t *Srow;    /* systematic pair row (HBM), read only when par == 0 */
+  const uint32_t *Yrow;    /* parity pair row of this decoder */
+  const uint2    *Rrow;    /* CRC syndrome pair row of this decoder and polynomial */
+  const uint32_t *Trow;    /* smem: decoder-2 address words of this pair row */
+  const uint16_t *Eh;      /* smem: extrinsic array of this code block, halfword view */
+  uint32_t        ident;   /* decoder-1 address word of step 0: (2*j*Lw) * 0x10001 + 0x10000 */
+  int             par;     /* 0: decoder 1 (natural order), 1: decoder 2 (interleaved order) */
+};
+
+/* raw global loads of one 8-step chunk [k0, k0+8), steps i >= i0 only (i0 > 0 only for the bottom chunk) */
+struct PkRaw { uint32_t s[8], y[8]; };
+
+__device__ __forceinline__ void pk_load_raw(const PkView &v, int k0, int i0, bool vec, PkRaw &r)
+{
+  if (vec && i0 == 0) {
+    const uint4 y0 = __ldg(reinterpret_cast<const uint4 *>(v.Yrow + k0)), y1 = __ldg(reinterpret_cast<const uint4 *>(v.Yrow + k0 + 4));
+    r.y[0] = y0.x; r.y[1] = y0.y; r.y[2] = y0.z; r.y[3] = y0.w; r.y[4] = y1.x; r.y[5] = y1.y; r.y[6] = y1.z; r.y[7] = y1.w;
+    uint4 s0 = make_uint4(0, 0, 0, 0), s1 = s0;
+    if (!v.par) { s0 = __ldg(reinterpret_cast<const uint4 *>(v.Srow + k0)); s1 = __ldg(reinterpret_cast<const uint4 *>(v.Srow + k0 + 4)); }
+    r.s[0] = s0.x; r.s[1] = s0.y; r.s[2] = s0.z; r.s[3] = s0.w; r.s[4] = s1.x; r.s[5] = s1.y; r.s[6] = s1.z; r.s[7] = s1.w;
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      r.s[i] = 0; r.y[i] = 0;
+      if (i >= i0) { r.y[i] = __ldg(v.Yrow + k0 + i); if (!v.par) r.s[i] = __ldg(v.Srow + k0 + i); }
+    }
+  }
+}
+
+/* address words + apriori gather + x = systematic + apriori for the chunk */
+__device__ __forceinline__ void pk_finish_chunk(const PkView &v, int k0, int i0, const PkRaw &r, uint32_t *xs, uint32_t *tw, uint32_t *es)
+{
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    xs[i] = 0; tw[i] = 0; es[i] = 0;
+    if (i >= i0) {
+      const int k = k0 + i;
+      const uint32_t t = v.par ? v.Trow[k] : v.ident + (uint32_t)k * 0x20002u;
+      const uint32_t e = pk_prmt(v.Eh[t & 0xFFFFu], v.Eh[t >> 16], 0x5410u);
+      tw[i] = t; es[i] = e;
+      xs[i] = pk_add(r.s[i], e);
+    }
+  }
+}
+
+/* One half-iteration of one constituent decoder for the two lanes of this thread.
+ * TPC = threads per code block (P/2), LODD = L is odd (fixes which steps are normalised in the main passes).
+ * Returns through refs: crc (XOR of the syndrome words of all bits decided 1 by this thread), emx/emn (running
+ * packed max/min of the new extrinsics), and leaves the decisions in bits[] (lane-major, step order, MSB first). */
+template <int TPC, bool LODD>
+__device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, bool vec, uint32_t tbase, unsigned gmask, int j,
+                                                   const int16_t *tail, uint16_t *Ew, uint32_t *bits_lo, uint32_t *bits_hi,
+                                                   bool shift_out, uint32_t &crc, uint32_t &emx, uint32_t &emn)
+{
+  const int nck = (L + PK_CH - 1) / PK_CH;
+  uint32_t o[8], xs[8], tw[8], es[8];
+  PkRaw raw, nraw;
+
+  /* ---- beta warm-up over the first 40 symbols of both sub-blocks (turbodecoder_win.h:321-384) ---- */
+#pragma unroll
+  for (int i = 0; i < 8; i++) o[i] = PK_NEG;
+  pk_load_raw(v, 32, 0, true, raw);
+  for (int c = 4; c >= 0; c--) {
+    if (c > 0) pk_load_raw(v, 8 * (c - 1), 0, true, nraw);
+    pk_finish_chunk(v, 8 * c, 0, raw, xs, tw, es);
+#pragma unroll
+    for (int i = 7; i >= 0; i--) {
+      pk_beta(o, xs[i], raw.y[i]);
+      if ((i & 1) == 0 && !(i == 0 && c == 0)) pk_norm(o);
+    }
+    raw = nraw;
+  }
+  /* lane shift: sub-block d starts from the estimate of sub-block d+1 (:347-355); the last sub-block of the
+   * code block starts from the known end state through the 3 tail steps with WRAPPING adds (:263-307) */
+  {
+    int t[8];
+    t[0] = 0;
+#pragma unroll
+    for (int i = 1; i < 8; i++) t[i] = -10000;
+    for (int k = 2; k >= 0; k--) {
+      const int tx = tail[2 * k], ty = tail[2 * k + 1];
+      const int txy = (short)(tx + ty);
+      int nn[8];
+      nn[0] = max((int)(short)(t[4] + txy), t[0]);
+      nn[1] = max(t[4], (int)(short)(t[0] + txy));
+      nn[2] = max((int)(short)(t[5] + ty), (int)(short)(t[1] + tx));
+      nn[3] = max((int)(short)(t[5] + tx), (int)(short)(t[1] + ty));
+      nn[4] = max((int)(short)(t[6] + tx), (int)(short)(t[2] + ty));
+      nn[5] = max((int)(short)(t[6] + ty), (int)(short)(t[2] + tx));
+      nn[6] = max(t[7], (int)(short)(t[3] + txy));
+      nn[7] = max((int)(short)(t[7] + txy), t[3]);
+#pragma unroll
+      for (int i = 0; i < 8; i++) t[i] = nn[i];
+    }
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      const uint32_t w = __shfl_down_sync(gmask, o[i], 1, TPC);
+      o[i] = (j == TPC - 1) ? ((o[i] >> 16) | ((uint32_t)t[i] << 16)) : pk_prmt(o[i], w, 0x5432u);
+    }
+  }
+  /* ---- beta main pass, chunks aligned from the top; checkpoint B[L-8c] (value BEFORE normalisation, :419-432) ---- */
+  pk_ck_store(tbase, o);
+  {
+    int k0 = L - PK_CH;
+    pk_load_raw(v, k0, k0 < 0 ? -k0 : 0, vec, raw);
+    for (int c = 0; c < nck; c++, k0 -= PK_CH) {
+      const int i0 = k0 < 0 ? -k0 : 0;
+      if (c + 1 < nck) { const int n0 = k0 - PK_CH; pk_load_raw(v, n0, n0 < 0 ? -n0 : 0, vec, nraw); }
+      pk_finish_chunk(v, k0, i0, raw, xs, tw, es);
+#pragma unroll
+      for (int i = 7; i >= 0; i--) {
+        if (i >= i0) {
+          pk_beta(o, xs[i], raw.y[i]);
+          if (i == 0 && c + 1 < nck) pk_ck_store(tbase + 8 * (c + 1), o);
+          if ((((i & 1) != 0) == LODD) && (k0 + i) != 0) pk_norm(o);
+        }
+      }
+      raw = nraw;
+    }
+  }
+  pk_ck_store_fence();
+  /* ---- alpha warm-up over the last 40 symbols (:459-506), normalisation by the warm-up counter ---- */
+  uint32_t m[8], n[8];
+#pragma unroll
+  for (int i = 0; i < 8; i++) o[i] = PK_NEG;
+  pk_load_raw(v, L - 40, 0, vec, raw);
+  for (int c = 0; c < 5; c++) {
+    if (c < 4) pk_load_raw(v, L - 40 + 8 * (c + 1), 0, vec, nraw);
+    pk_finish_chunk(v, L - 40 + 8 * c, 0, raw, xs, tw, es);
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      pk_alpha_branches(o, xs[i], raw.y[i], m, n);
+#pragma unroll
+      for (int s = 0; s < 8; s++) o[s] = pk_max(m[s], n[s]);
+      if ((i & 1) == 0 && !(i == 0 && c == 0)) pk_norm(o);
+    }
+    raw = nraw;
+  }
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    const uint32_t w = __shfl_up_sync(gmask, o[i], 1, TPC);
+    const uint32_t first = (i == 0) ? 0u : 0xD8F0u;
+    o[i] = (j == 0) ? (first | (o[i] << 16)) : pk_prmt(w, o[i], 0x5432u);
+  }
+  /* ---- alpha main pass: per chunk (ascending k) recompute the 7 inner betas from the checkpoint, then alpha + LLR ---- */
+  uint32_t wlo = 0, whi = 0;
+  int nbits = 0, wi = 0;
+  {
+    int k0 = L - PK_CH * nck;                     /* bottom chunk first (may start below 0) */
+    pk_load_raw(v, k0, k0 < 0 ? -k0 : 0, vec, raw);
+    uint2 rr[8], nrr[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) { rr[i] = make_uint2(0, 0); if (k0 + i >= 0) rr[i] = __ldg(v.Rrow + k0 + i); }
+    for (int c = nck - 1; c >= 0; c--, k0 += PK_CH) {
+      const int i0 = k0 < 0 ? -k0 : 0;
+      if (c > 0) {
+        pk_load_raw(v, k0 + PK_CH, 0, vec, nraw);
+#pragma unroll
+        for (int i = 0; i < 8; i++) nrr[i] = __ldg(v.Rrow + k0 + PK_CH + i);
+      }
+      uint32_t ck[8], b[8], bb[8][8];
+      pk_ck_load(tbase + 8 * c, ck);
+      pk_finish_chunk(v, k0, i0, raw, xs, tw, es);
+#pragma unroll
+      for (int s = 0; s < 8; s++) b[s] = ck[s];
+      if (c > 0 && !LODD) pk_norm(b);              /* the normalisation that followed the store at step k0+8 */
+#pragma unroll
+      for (int i = 7; i >= 1; i--) {
+        if (i >= i0 + 1 || (i >= 1 && i0 == 0)) {
+          pk_beta(b, xs[i], raw.y[i]);
+#pragma unroll
+          for (int s = 0; s < 8; s++) bb[i][s] = b[s];
+          if ((((i & 1) != 0) == LODD)) pk_norm(b);
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 8; i++) {
+        if (i >= i0) {
+          pk_alpha_branches(o, xs[i], raw.y[i], m, n);
+          const uint32_t *bn = (i == 7) ? ck : bb[(i + 1) & 7];
+          uint32_t m0 = pk_add(bn[0], m[0]), m1 = pk_add(bn[0], n[0]);
+#pragma unroll
+          for (int s = 1; s < 8; s++) { m0 = pk_addmax(bn[s], m[s], m0); m1 = pk_addmax(bn[s], n[s], m1); }
+          uint32_t r = pk_sub(m1, m0);
+          if (shift_out) r = ((r >> 1) & 0x7FFF7FFFu) | (r & 0x80008000u);   /* divide_output, sse16 only (:61,565) */
+          const uint32_t en = pk_sub(r, es[i]);                               /* next apriori = LLR - what this decoder was given */
+          Ew[tw[i] & 0xFFFFu] = (uint16_t)en;
+          Ew[tw[i] >> 16] = (uint16_t)(en >> 16);
+          emx = pk_max(emx, en); emn = pk_min(emn, en);
+          const uint32_t nr = pk_sub(0u, r);                                  /* sign set <=> LLR > 0 <=> bit 1 */
+          const uint32_t mlo = pk_prmt(nr, 0u, 0x9999u), mhi = pk_prmt(nr, 0u, 0xBBBBu);
+          crc ^= (mlo & rr[i].x) ^ (mhi & rr[i].y);
+          wlo = __funnelshift_l(mlo, wlo, 1); whi = __funnelshift_l(mhi, whi, 1);
+          if (++nbits == 32) { bits_lo[wi] = wlo; bits_hi[wi] = whi; wi++; nbits = 0; }
+#pragma unroll
+          for (int s = 0; s < 8; s++) o[s] = pk_max(m[s], n[s]);
+          if ((((i & 1) != 0) == LODD) && (k0 + i) != 0) pk_norm(o);
+        }
+      }
+      raw = nraw;
+#pragma unroll
+      for (int i = 0; i < 8; i++) rr[i] = nrr[i];
+    }
+  }
+  if (nbits) { bits_lo[wi] = wlo << (32 - nbits); bits_hi[wi] = whi << (32 - nbits); }
+}
+
+/* ---------------------------------------------------------------- output of a finished code block ---- */
+/* n bits (1..32) of bit row `row` (MSB-first words) starting at bit k, left-aligned in the result */
+__device__ __forceinline__ uint32_t pk_row_bits(const uint32_t *row, int k)
+{
+  const int wi = k >> 5, off = k & 31;
+  return __funnelshift_l(row[wi + 1], row[wi], off);
+}
+
+/* natural-order hard decisions -> K/8 bytes MSB first (turbodecoder_win.h:676-716). rows: [P][nw+1] words,
+ * row d holds bits d*L .. d*L+L-1. Called by the TPC threads of one code block. */
+template <int TPC>
+__device__ __forceinline__ void pk_write_output(const uint32_t *rows, int nw1, int K, int L, int j, uint8_t *out)
+{
+  const int nwords = K >> 5;
+  uint32_t *out32 = reinterpret_cast<uint32_t *>(out);
+  for (int ow = j; ow < nwords; ow += TPC) {
+    const int p = ow << 5, d = p / L, k = p - d * L, avail = L - k;
+    uint32_t w = pk_row_bits(rows + d * nw1, k);
+    if (avail < 32) w = (w & ~(0xFFFFFFFFu >> avail)) | (pk_row_bits(rows + (d + 1) * nw1, 0) >> avail);
+    out32[ow] = __byte_perm(w, 0, 0x0123);
+  }
+  for (int ob = (nwords << 2) + j; ob < (K >> 3); ob += TPC) {      /* K/8 not a multiple of 4: last 1..3 bytes */
+    const int p = ob << 3, d = p / L, k = p - d * L, avail = L - k;
+    uint32_t w = pk_row_bits(rows + d * nw1, k);
+    if (avail < 8) w = (w & ~(0xFFFFFFFFu >> avail)) | (pk_row_bits(rows + (d + 1) * nw1, 0) >> avail);
+    out[ob] = (uint8_t)(w >> 24);
+  }
+}
+
+/* ---------------------------------------------------------------- the kernel ---- */
+/* shared memory: [T2: TPC*Lp words][E: nslots x (TPC*Lw+1) words][bit rows: nslots x P x (nw+1) words] */
+size_t fec_pk_smem_bytes(const fec_geom_t *g)
+{
+  const size_t tpc = g->P / 2, nslots = (size_t)FEC_PK_WARPS * (32 / tpc), nw1 = (g->L + 31) / 32 + 1;
+  return 4 * (tpc * g->Lp + nslots * (tpc * g->Lw + 1) + nslots * g->P * nw1);
+}
+
+template <int P, bool LODD>
+__global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const FecDecodeArgs a)
+{
+  constexpr int TPC = P / 2, CPW = 32 / TPC;
+  extern __shared__ __align__(16) unsigned char smem[];
+  __shared__ uint32_t s_tmem;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane / TPC, j = lane % TPC;
+  const int K = a.g.K, L = a.g.L, Lp = a.g.Lp, Lw = a.g.Lw, SS = a.g.SS;
+  const int nw1 = (L + 31) / 32 + 1, Es = TPC * Lw + 1, nslots = FEC_PK_WARPS * CPW, slot = warp * CPW + g;
+  uint32_t *T2 = reinterpret_cast<uint32_t *>(smem);
+  uint32_t *Eslot = T2 + TPC * Lp + slot * Es;
+  uint32_t *rows = T2 + TPC * Lp + nslots * Es + slot * (P * nw1);
+  const bool vec = (L & 3) == 0;
+  const unsigned gmask = (TPC == 32) ? 0xFFFFFFFFu : (((1u << TPC) - 1u) << (g * TPC));
+
+  for (int i = tid; i < TPC * Lp; i += blockDim.x) T2[i] = a.pair_addr[i];
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" :: "r"((uint32_t)__cvta_generic_to_shared(&s_tmem)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tbase = s_tmem + ((uint32_t)(warp * 32) << 16);
+
+  int cb = -1, n = 0;
+  uint32_t M = 0;
+  bool exhausted = false;
+  for (;;) {
+    /* ---- refill this group's slot from the work queue (group-uniform control flow) ---- */
+    while (cb < 0 && !exhausted) {
+      unsigned q = 0;
+      if (j == 0) q = atomicAdd(a.queue, 1u);
+      q = __shfl_sync(gmask, q, g * TPC);
+      if (q >= a.ncb) { exhausted = true; break; }
+      M = a.soft_max[a.cbs[q].status];
+      if (2 * M > FEC_PK_GMAX) {                    /* first half-iteration already outside the proven range */
+        if (j == 0) a.exact_list[atomicAdd(a.exact_count, 1u)] = q;
+        continue;
+      }
+      cb = (int)q; n = 0;
+      for (int i = j; i < Es; i += TPC) Eslot[i] = 0;   /* apriori = 0 before the first half-iteration */
+    }
+    __syncwarp();
+    if (!__any_sync(0xFFFFFFFFu, cb >= 0)) break;
+
+    /* ---- one half-iteration for every slot of the warp; idle slots run on code block 0's inputs and their
+     *      own scratch E (keeps the warp convergent for the .aligned tensor-memory accesses), results dropped ---- */
+    const bool active = cb >= 0;
+    const FecCbDesc desc = a.cbs[active ? cb : 0];
+    const int par = n & 1;
+    PkView v;
+    v.par = par;
+    v.Srow = reinterpret_cast<const uint32_t *>(desc.soft) + j * Lp;
+    v.Yrow = reinterpret_cast<const uint32_t *>(desc.soft + (1 + par) * SS) + j * Lp;
+    v.Rrow = a.pair_crc[desc.crc_sel] + (size_t)par * TPC * Lp + j * Lp;
+    v.Trow = T2 + j * Lp;
+    v.Eh = reinterpret_cast<const uint16_t *>(Eslot);
+    v.ident = (uint32_t)(2 * j * Lw) * 0x10001u + 0x10000u;
+    uint32_t crc = 0, emx = 0x80008000u, emn = 0x7FFF7FFFu;
+    pk_half_iteration<TPC, LODD>(v, L, vec, tbase, gmask, j, desc.soft + 3 * SS + (par ? 6 : 0),
+                                 reinterpret_cast<uint16_t *>(Eslot), rows + (2 * j) * nw1, rows + (2 * j + 1) * nw1,
+                                 P == 8, crc, emx, emn);
+#pragma unroll
+    for (int s = TPC / 2; s > 0; s >>= 1) {
+      crc ^= __shfl_xor_sync(0xFFFFFFFFu, crc, s, TPC);
+      emx = pk_max(emx, __shfl_xor_sync(0xFFFFFFFFu, emx, s, TPC));
+      emn = pk_min(emn, __shfl_xor_sync(0xFFFFFFFFu, emn, s, TPC));
+    }
+    __syncwarp();
+    if (active) {
+      const int n1 = n + 1, crc_ok = (crc == 0);
+      const bool done = (crc_ok && !(desc.flags & FEC_F_NO_EARLY)) || (n1 >= (int)desc.max_its);
+      if (done) {
+        if (par) {
+          /* decisions are in interleaved order: spread them to natural positions through the (now dead) E array,
+           * then rebuild the natural bit rows */
+          const uint32_t *blo = rows + (2 * j) * nw1, *bhi = rows + (2 * j + 1) * nw1;
+          uint16_t *Eh = reinterpret_cast<uint16_t *>(Eslot);
+          for (int k = 0; k < L; k++) {
+            const uint32_t t = v.Trow[k];
+            Eh[t & 0xFFFFu] = (uint16_t)(0u - ((blo[k >> 5] >> (31 - (k & 31))) & 1u));
+            Eh[t >> 16] = (uint16_t)(0u - ((bhi[k >> 5] >> (31 - (k & 31))) & 1u));
+          }
+          __syncwarp(gmask);
+          uint32_t wlo = 0, whi = 0;
+          uint32_t *olo = rows + (2 * j) * nw1, *ohi = rows + (2 * j + 1) * nw1;
+          for (int k = 0; k < L; k++) {
+            const uint32_t w = Eslot[j * Lw + k];
+            wlo = __funnelshift_l(w << 16, wlo, 1); whi = __funnelshift_l(w, whi, 1);
+            if ((k & 31) == 31) { olo[k >> 5] = wlo; ohi[k >> 5] = whi; }
+          }
+          if (L & 31) { olo[L >> 5] = wlo << (32 - (L & 31)); ohi[L >> 5] = whi << (32 - (L & 31)); }
+        }
+        __syncwarp(gmask);
+        pk_write_output<TPC>(rows, nw1, K, L, j, desc.out);
+        if (j == 0) { a.status[desc.status].its = (uint32_t)n1; a.status[desc.status].crc_ok = (uint32_t)crc_ok; }
+        __syncwarp(gmask);
+        cb = -1;
+      } else {
+        /* range condition of the NEXT half-iteration: |x| <= max|new extrinsic| (+ max|systematic| for decoder 1) */
+        const int e0 = (short)(emx & 0xFFFFu), e1 = (short)(emx >> 16), e2 = -(int)(short)(emn & 0xFFFFu), e3 = -(int)(short)(emn >> 16);
+        const uint32_t emax = (uint32_t)max(max(e0, e1), max(max(e2, e3), 0));
+        const uint32_t bx = (n1 & 1) ? emax : emax + M;
+        if (bx + M > FEC_PK_GMAX) {
+          if (j == 0) a.exact_list[atomicAdd(a.exact_count, 1u)] = (uint32_t)cb;   /* re-decoded from scratch by the exact kernel */
+          cb = -1;
+        } else n = n1;
+      }
+    }
+    __syncwarp();
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" :: "r"(s_tmem) : "memory");
+}
+
+cudaError_t fec_launch_decode_packed(const FecDecodeArgs &a, int sm_count, cudaStream_t st)
+{
+  if (a.ncb == 0) return cudaSuccess;
+  const size_t smem = fec_pk_smem_bytes(&a.g);
+  const int tpc = a.g.P / 2, per_cta = FEC_PK_WARPS * (32 / tpc);
+  int grid = (int)((a.ncb + per_cta - 1) / per_cta);
+  if (grid > sm_count) grid = sm_count;
+  const bool lodd = (a.g.L & 1) != 0;
+  if (a.g.P == 16) {
+    if (lodd) fec_tdec_pk_kernel<16, true><<<grid, FEC_PK_WARPS * 32, smem, st>>>(a);
+    else      fec_tdec_pk_kernel<16, false><<<grid, FEC_PK_WARPS * 32, smem, st>>>(a);
+  } else {
+    if (lodd) fec_tdec_pk_kernel<8, true><<<grid, FEC_PK_WARPS * 32, smem, st>>>(a);
+    else      fec_tdec_pk_kernel<8, false><<<grid, FEC_PK_WARPS * 32, smem, st>>>(a);
+  }
+  return cudaGetLastError();
+}
+
+cudaError_t fec_pk_init(void)
+{
+  cudaError_t e;
+  e = cudaFuncSetAttribute(fec_tdec_pk_kernel<16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(fec_tdec_pk_kernel<16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(fec_tdec_pk_kernel<8, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(fec_tdec_pk_kernel<8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+}

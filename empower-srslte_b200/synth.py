@@ -206,7 +206,7 @@ def encode_tbs(payload, tbs, Qm, rv, nof_e_bits):
 
 def awgn_llr(e_bits, sigma, rng, amp=100.0, out=None):
     """LLR = rint(amp*(+-1 + sigma*n)) as int16, bit 1 -> +amp"""
-    x = e_bits.astype(np.float32)
+    x = np.ascontiguousarray(e_bits, dtype=np.float32) if e_bits.dtype == np.float32 else np.array(e_bits, dtype=np.float32, order="C")
     x *= 2.0
     x -= 1.0
     x += np.float32(sigma) * rng.standard_normal(e_bits.shape, dtype=np.float32)
@@ -214,6 +214,6 @@ def awgn_llr(e_bits, sigma, rng, amp=100.0, out=None):
     np.rint(x, out=x)
     np.clip(x, -32768, 32767, out=x)
     if out is None:
-        return x.astype(np.int16)
+        return np.ascontiguousarray(x.astype(np.int16))
     out[...] = x
     return out

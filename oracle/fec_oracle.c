@@ -150,7 +150,22 @@ int orc_rm_rx(const int16_t *in, int E, int K, int rv, int sb_layout, int16_t *s
 
 /* ------------------------------------------------------------------ constituent MAP decoders ---- */
 #define NEG_INF (-10000)
-static inline int16_t sat16(int v) { return (int16_t)(v > 32767 ? 32767 : (v < -32768 ? -32768 : v)); }
+/* test instrumentation: how often a saturating op clipped / peak intermediate magnitude / peak MAP input magnitude
+ * since the last orc_dbg_reset() (thread-local). Used to validate the range proof behind the packed CUDA fast path. */
+static __thread long orc_sat_count = 0;
+static __thread int  orc_peak_val = 0, orc_peak_in = 0;
+void orc_dbg_reset(void) { orc_sat_count = 0; orc_peak_val = 0; orc_peak_in = 0; }
+long orc_dbg_sat_count(void) { return orc_sat_count; }
+int  orc_dbg_peak_val(void) { return orc_peak_val; }
+int  orc_dbg_peak_in(void) { return orc_peak_in; }
+static inline int16_t sat16(int v)
+{
+  int a = v < 0 ? -v : v;
+  if (a > orc_peak_val) orc_peak_val = a;
+  if (v > 32767) { orc_sat_count++; return 32767; }
+  if (v < -32768) { orc_sat_count++; return -32768; }
+  return (int16_t)v;
+}
 static inline int16_t adds(int16_t a, int16_t b) { return sat16((int)a + (int)b); }
 static inline int16_t subs(int16_t a, int16_t b) { return sat16((int)a - (int)b); }
 static inline int16_t wrap16(int v) { return (int16_t)(uint16_t)v; }
@@ -202,7 +217,12 @@ static void map_windowed(int K, int P, const int16_t *in, const int16_t *app, co
   static __thread int16_t X[ORC_MAX_K];
   static __thread int16_t B[16][ORC_MAX_K / 8 + 1][8];   /* beta store, (L+1) x 8 per lane; L <= 768 (K=6144,P=8 manual) */
   int16_t warm[16][8], o[8];
-  for (int i = 0; i < K; i++) X[i] = app ? adds(app[i], in[i]) : in[i];
+  for (int i = 0; i < K; i++) {
+    X[i] = app ? adds(app[i], in[i]) : in[i];
+    int ax = X[i] < 0 ? -X[i] : X[i], ay = par[i] < 0 ? -par[i] : par[i];
+    if (ax > orc_peak_in) orc_peak_in = ax;
+    if (ay > orc_peak_in) orc_peak_in = ay;
+  }
 
   /* beta warm-up over the FIRST 40 symbols of every sub-block */
   for (int d = 0; d < P; d++) {

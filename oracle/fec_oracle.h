@@ -33,6 +33,12 @@ int      orc_rm_table(int K, int rv, uint16_t *tab);                /* rm_turbo.
 int      orc_rm_soft_index(int t, int K, int P);                    /* rm_turbo.c:250-264 */
 int      orc_rm_rx(const int16_t *in, int E, int K, int rv, int sb_layout, int16_t *soft); /* rm_turbo.c:378-430 */
 
+/* instrumentation (thread-local): saturation clips, peak |intermediate|, peak |MAP input| since orc_dbg_reset() */
+void orc_dbg_reset(void);
+long orc_dbg_sat_count(void);
+int  orc_dbg_peak_val(void);
+int  orc_dbg_peak_in(void);
+
 /* one constituent MAP decoder run, natural order. tail_x/tail_p: the 3 tail LLRs of this decoder. */
 void orc_map(int K, int P, const int16_t *x, const int16_t *app, const int16_t *par,
              const int16_t *tail_x, const int16_t *tail_p, int16_t *out);
