@@ -43,6 +43,17 @@ __device__ __forceinline__ uint32_t pk_prmt(uint32_t a, uint32_t b, uint32_t sel
   return r;
 }
 
+__device__ __forceinline__ uint32_t pk_lds_u16(uint32_t addr)
+{
+  uint32_t r;
+  asm volatile("ld.shared.u16 %0, [%1];" : "=r"(r) : "r"(addr));
+  return r;
+}
+__device__ __forceinline__ void pk_sts_u16(uint32_t addr, uint32_t val)
+{
+  asm volatile("st.shared.u16 [%0], %1;" :: "r"(addr), "r"(val) : "memory");
+}
+
 /* turbodecoder_win.h:244-261: subtract state 0 from states 1..7, state 0 := 0 (every even k != 0) */
 __device__ __forceinline__ void pk_norm(uint32_t *o)
 {
@@ -99,18 +110,19 @@ struct PkView {
   const uint32_t *Srow;    /* systematic pair row (HBM), read only when par == 0 */
   const uint32_t *Yrow;    /* parity pair row of this decoder */
   const uint2    *Rrow;    /* CRC syndrome pair row of this decoder and polynomial */
-  const uint32_t *Trow;    /* smem: decoder-2 address words of this pair row */
-  const uint16_t *Eh;      /* smem: extrinsic array of this code block, halfword view */
-  uint32_t        ident;   /* decoder-1 address word of step 0: (2*j*Lw) * 0x10001 + 0x10000 */
+  const uint16_t *Tlo, *Thi; /* smem: decoder-2 byte offsets into E of lanes 2j / 2j+1 at step k */
+  uint32_t        Eb;      /* shared-memory byte address of this code block's extrinsic array E */
+  uint32_t        ident;   /* decoder-1 byte offset of lane 2j at step 0: 4*j*Lw (lane 2j+1: +2; step k: +4k) */
   int             par;     /* 0: decoder 1 (natural order), 1: decoder 2 (interleaved order) */
 };
 
-/* raw global loads of one 8-step chunk [k0, k0+8), steps i >= i0 only (i0 > 0 only for the bottom chunk) */
+/* raw global loads of one 8-step chunk [k0, k0+8). FULL: all 8 steps exist; else only steps i >= i0 (bottom chunk) */
 struct PkRaw { uint32_t s[8], y[8]; };
 
-__device__ __forceinline__ void pk_load_raw(const PkView &v, int k0, int i0, bool vec, PkRaw &r)
+template <bool FULL, bool VEC>
+__device__ __forceinline__ void pk_load_raw(const PkView &v, int k0, int i0, PkRaw &r)
 {
-  if (vec && i0 == 0) {
+  if (FULL && VEC) {
     const uint4 y0 = __ldg(reinterpret_cast<const uint4 *>(v.Yrow + k0)), y1 = __ldg(reinterpret_cast<const uint4 *>(v.Yrow + k0 + 4));
     r.y[0] = y0.x; r.y[1] = y0.y; r.y[2] = y0.z; r.y[3] = y0.w; r.y[4] = y1.x; r.y[5] = y1.y; r.y[6] = y1.z; r.y[7] = y1.w;
     uint4 s0 = make_uint4(0, 0, 0, 0), s1 = s0;
@@ -120,51 +132,115 @@ __device__ __forceinline__ void pk_load_raw(const PkView &v, int k0, int i0, boo
 #pragma unroll
     for (int i = 0; i < 8; i++) {
       r.s[i] = 0; r.y[i] = 0;
-      if (i >= i0) { r.y[i] = __ldg(v.Yrow + k0 + i); if (!v.par) r.s[i] = __ldg(v.Srow + k0 + i); }
+      if (FULL || i >= i0) { r.y[i] = __ldg(v.Yrow + k0 + i); if (!v.par) r.s[i] = __ldg(v.Srow + k0 + i); }
     }
   }
 }
 
-/* address words + apriori gather + x = systematic + apriori for the chunk */
-__device__ __forceinline__ void pk_finish_chunk(const PkView &v, int k0, int i0, const PkRaw &r, uint32_t *xs, uint32_t *tw, uint32_t *es)
+/* E byte addresses of the two lanes at each step + apriori gather + x = systematic + apriori */
+template <bool FULL>
+__device__ __forceinline__ void pk_finish_chunk(const PkView &v, int k0, int i0, const PkRaw &r, uint32_t *xs, uint32_t *alo, uint32_t *ahi, uint32_t *es)
 {
 #pragma unroll
   for (int i = 0; i < 8; i++) {
-    xs[i] = 0; tw[i] = 0; es[i] = 0;
-    if (i >= i0) {
+    xs[i] = 0; alo[i] = v.Eb; ahi[i] = v.Eb; es[i] = 0;
+    if (FULL || i >= i0) {
       const int k = k0 + i;
-      const uint32_t t = v.par ? v.Trow[k] : v.ident + (uint32_t)k * 0x20002u;
-      const uint32_t e = pk_prmt(v.Eh[t & 0xFFFFu], v.Eh[t >> 16], 0x5410u);
-      tw[i] = t; es[i] = e;
+      uint32_t ol, oh;
+      if (v.par) { ol = v.Tlo[k]; oh = v.Thi[k]; } else { ol = v.ident + 4u * (uint32_t)k; oh = ol + 2u; }
+      alo[i] = v.Eb + ol; ahi[i] = v.Eb + oh;
+      const uint32_t e = pk_prmt(pk_lds_u16(alo[i]), pk_lds_u16(ahi[i]), 0x5410u);
+      es[i] = e;
       xs[i] = pk_add(r.s[i], e);
     }
   }
 }
 
-/* One half-iteration of one constituent decoder for the two lanes of this thread.
- * TPC = threads per code block (P/2), LODD = L is odd (fixes which steps are normalised in the main passes).
- * Returns through refs: crc (XOR of the syndrome words of all bits decided 1 by this thread), emx/emn (running
- * packed max/min of the new extrinsics), and leaves the decisions in bits[] (lane-major, step order, MSB first). */
-template <int TPC, bool LODD>
-__device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, bool vec, uint32_t tbase, unsigned gmask, int j,
-                                                   const int16_t *tail, uint16_t *Ew, uint32_t *bits_lo, uint32_t *bits_hi,
-                                                   bool shift_out, uint32_t &crc, uint32_t &emx, uint32_t &emn)
+/* 8 backward steps of the main pass (i = 7..0), checkpoint after step i = 0, normalisation on even k */
+template <bool FULL, bool LODD>
+__device__ __forceinline__ void pk_beta_chunk(uint32_t *o, const uint32_t *xs, const uint32_t *ys, int i0, uint32_t ck_addr)
 {
-  const int nck = (L + PK_CH - 1) / PK_CH;
-  uint32_t o[8], xs[8], tw[8], es[8];
+#pragma unroll
+  for (int i = 7; i >= 0; i--) {
+    if (FULL || i >= i0) {
+      pk_beta(o, xs[i], ys[i]);
+      if (FULL && i == 0) pk_ck_store(ck_addr, o);
+      if (((i & 1) != 0) == LODD) pk_norm(o);        /* the step k = 0 is never followed by a use of o */
+    }
+  }
+}
+
+struct PkAcc { uint32_t crc, emx, emn, wlo, whi; };
+
+/* one chunk of the forward pass: recompute the inner betas from the checkpoint `ck` (= B[k0+8], stored value),
+ * then alpha recursion + LLR + extrinsic write-back + CRC syndrome + decision bits for steps i = i0..7 */
+template <bool FULL, bool LODD, bool SHIFT>
+__device__ __forceinline__ void pk_alpha_chunk(uint32_t *o, const uint32_t *ck, bool norm_ck, bool k0_nonzero, int i0,
+                                               const uint32_t *xs, const uint32_t *ys, const uint32_t *es,
+                                               const uint32_t *alo, const uint32_t *ahi, const uint2 *rr, PkAcc &acc)
+{
+  uint32_t b[8], bb[8][8], m[8], n[8];
+#pragma unroll
+  for (int s = 0; s < 8; s++) b[s] = ck[s];
+  if (norm_ck) pk_norm(b);                           /* the normalisation that followed the store at step k0+8 */
+#pragma unroll
+  for (int i = 7; i >= 1; i--) {
+    if (FULL || i >= i0 + 1) {
+      pk_beta(b, xs[i], ys[i]);
+#pragma unroll
+      for (int s = 0; s < 8; s++) bb[i][s] = b[s];
+      if (((i & 1) != 0) == LODD) pk_norm(b);
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    if (FULL || i >= i0) {
+      pk_alpha_branches(o, xs[i], ys[i], m, n);
+      const uint32_t *bn = (i == 7) ? ck : bb[(i + 1) & 7];
+      uint32_t m0 = pk_add(bn[0], m[0]), m1 = pk_add(bn[0], n[0]);
+#pragma unroll
+      for (int s = 1; s < 8; s++) { m0 = pk_addmax(bn[s], m[s], m0); m1 = pk_addmax(bn[s], n[s], m1); }
+      uint32_t r = pk_sub(m1, m0);
+      if (SHIFT) r = ((r >> 1) & 0x7FFF7FFFu) | (r & 0x80008000u);        /* divide_output, sse16 only (:61,565) */
+      const uint32_t en = pk_sub(r, es[i]);                                /* next apriori = LLR - what this decoder was given */
+      pk_sts_u16(alo[i], en);
+      pk_sts_u16(ahi[i], en >> 16);
+      acc.emx = pk_max(acc.emx, en); acc.emn = pk_min(acc.emn, en);
+      const uint32_t nr = pk_sub(0u, r);                                   /* sign set <=> LLR > 0 <=> bit 1 */
+      const uint32_t mlo = pk_prmt(nr, 0u, 0x9999u), mhi = pk_prmt(nr, 0u, 0xBBBBu);
+      acc.crc ^= (mlo & rr[i].x) ^ (mhi & rr[i].y);
+      acc.wlo = __funnelshift_l(mlo, acc.wlo, 1); acc.whi = __funnelshift_l(mhi, acc.whi, 1);
+#pragma unroll
+      for (int s = 0; s < 8; s++) o[s] = pk_max(m[s], n[s]);
+      if (((i & 1) != 0) == LODD) { if (FULL ? (i != 0 || k0_nonzero) : (i != i0)) pk_norm(o); }   /* no normalisation at k = 0 */
+    } else { acc.wlo <<= 1; acc.whi <<= 1; }
+  }
+}
+
+/* One half-iteration of one constituent decoder for the two lanes of this thread.
+ * TPC = threads per code block (P/2); MODE 0: L % 4 == 0 (16-byte loads), 1: L even, 2: L odd (the parity of L
+ * fixes which steps of the main passes are normalised). Decisions go to bits_lo/bits_hi as MSB-first words; bit
+ * k of a lane sits at bit index k + (8*nck - L) of its row. */
+template <int TPC, int MODE, bool SHIFT>
+__device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32_t tbase, unsigned gmask, int j,
+                                                   const int16_t *tail, uint32_t *bits_lo, uint32_t *bits_hi, PkAcc &acc)
+{
+  constexpr bool LODD = MODE == 2, VEC = MODE == 0;
+  const int nfull = L >> 3, rem = L & 7, nck = nfull + (rem ? 1 : 0);
+  uint32_t o[8], xs[8], alo[8], ahi[8], es[8];
   PkRaw raw, nraw;
 
   /* ---- beta warm-up over the first 40 symbols of both sub-blocks (turbodecoder_win.h:321-384) ---- */
 #pragma unroll
   for (int i = 0; i < 8; i++) o[i] = PK_NEG;
-  pk_load_raw(v, 32, 0, true, raw);
+  pk_load_raw<true, true>(v, 32, 0, raw);
   for (int c = 4; c >= 0; c--) {
-    if (c > 0) pk_load_raw(v, 8 * (c - 1), 0, true, nraw);
-    pk_finish_chunk(v, 8 * c, 0, raw, xs, tw, es);
+    if (c > 0) pk_load_raw<true, true>(v, 8 * (c - 1), 0, nraw);
+    pk_finish_chunk<true>(v, 8 * c, 0, raw, xs, alo, ahi, es);
 #pragma unroll
     for (int i = 7; i >= 0; i--) {
       pk_beta(o, xs[i], raw.y[i]);
-      if ((i & 1) == 0 && !(i == 0 && c == 0)) pk_norm(o);
+      if ((i & 1) == 0 && (i != 0 || c != 0)) pk_norm(o);
     }
     raw = nraw;
   }
@@ -196,43 +272,38 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, bool v
       o[i] = (j == TPC - 1) ? ((o[i] >> 16) | ((uint32_t)t[i] << 16)) : pk_prmt(o[i], w, 0x5432u);
     }
   }
-  /* ---- beta main pass, chunks aligned from the top; checkpoint B[L-8c] (value BEFORE normalisation, :419-432) ---- */
+  /* ---- beta main pass, chunks aligned from the top; checkpoint c = B[L-8c] (value BEFORE normalisation, :419-432) ---- */
   pk_ck_store(tbase, o);
   {
     int k0 = L - PK_CH;
-    pk_load_raw(v, k0, k0 < 0 ? -k0 : 0, vec, raw);
-    for (int c = 0; c < nck; c++, k0 -= PK_CH) {
-      const int i0 = k0 < 0 ? -k0 : 0;
-      if (c + 1 < nck) { const int n0 = k0 - PK_CH; pk_load_raw(v, n0, n0 < 0 ? -n0 : 0, vec, nraw); }
-      pk_finish_chunk(v, k0, i0, raw, xs, tw, es);
-#pragma unroll
-      for (int i = 7; i >= 0; i--) {
-        if (i >= i0) {
-          pk_beta(o, xs[i], raw.y[i]);
-          if (i == 0 && c + 1 < nck) pk_ck_store(tbase + 8 * (c + 1), o);
-          if ((((i & 1) != 0) == LODD) && (k0 + i) != 0) pk_norm(o);
-        }
-      }
+    pk_load_raw<true, VEC>(v, k0, 0, raw);
+    for (int c = 0; c < nfull; c++, k0 -= PK_CH) {
+      if (c + 1 < nfull) pk_load_raw<true, VEC>(v, k0 - PK_CH, 0, nraw);
+      pk_finish_chunk<true>(v, k0, 0, raw, xs, alo, ahi, es);
+      pk_beta_chunk<true, LODD>(o, xs, raw.y, 0, tbase + 8 * (c + 1));
       raw = nraw;
     }
+    /* the bottom partial chunk only serves the (unused) end of the recursion: nothing to do */
   }
   pk_ck_store_fence();
   /* ---- alpha warm-up over the last 40 symbols (:459-506), normalisation by the warm-up counter ---- */
-  uint32_t m[8], n[8];
+  {
+    uint32_t m[8], n[8];
 #pragma unroll
-  for (int i = 0; i < 8; i++) o[i] = PK_NEG;
-  pk_load_raw(v, L - 40, 0, vec, raw);
-  for (int c = 0; c < 5; c++) {
-    if (c < 4) pk_load_raw(v, L - 40 + 8 * (c + 1), 0, vec, nraw);
-    pk_finish_chunk(v, L - 40 + 8 * c, 0, raw, xs, tw, es);
+    for (int i = 0; i < 8; i++) o[i] = PK_NEG;
+    pk_load_raw<true, VEC>(v, L - 40, 0, raw);
+    for (int c = 0; c < 5; c++) {
+      if (c < 4) pk_load_raw<true, VEC>(v, L - 40 + 8 * (c + 1), 0, nraw);
+      pk_finish_chunk<true>(v, L - 40 + 8 * c, 0, raw, xs, alo, ahi, es);
 #pragma unroll
-    for (int i = 0; i < 8; i++) {
-      pk_alpha_branches(o, xs[i], raw.y[i], m, n);
+      for (int i = 0; i < 8; i++) {
+        pk_alpha_branches(o, xs[i], raw.y[i], m, n);
 #pragma unroll
-      for (int s = 0; s < 8; s++) o[s] = pk_max(m[s], n[s]);
-      if ((i & 1) == 0 && !(i == 0 && c == 0)) pk_norm(o);
+        for (int s = 0; s < 8; s++) o[s] = pk_max(m[s], n[s]);
+        if ((i & 1) == 0 && (i != 0 || c != 0)) pk_norm(o);
+      }
+      raw = nraw;
     }
-    raw = nraw;
   }
 #pragma unroll
   for (int i = 0; i < 8; i++) {
@@ -240,67 +311,42 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, bool v
     const uint32_t first = (i == 0) ? 0u : 0xD8F0u;
     o[i] = (j == 0) ? (first | (o[i] << 16)) : pk_prmt(w, o[i], 0x5432u);
   }
-  /* ---- alpha main pass: per chunk (ascending k) recompute the 7 inner betas from the checkpoint, then alpha + LLR ---- */
-  uint32_t wlo = 0, whi = 0;
-  int nbits = 0, wi = 0;
-  {
-    int k0 = L - PK_CH * nck;                     /* bottom chunk first (may start below 0) */
-    pk_load_raw(v, k0, k0 < 0 ? -k0 : 0, vec, raw);
-    uint2 rr[8], nrr[8];
+  /* ---- alpha main pass, ascending k: bottom partial chunk (if any), then the full chunks ---- */
+  acc.wlo = 0; acc.whi = 0;
+  int wi = 0, cc = 0;
+  uint2 rr[8], nrr[8];
+  uint32_t ck[8];
+  if (rem) {
+    const int k0 = rem - PK_CH, i0 = PK_CH - rem;
+    pk_load_raw<false, VEC>(v, k0, i0, raw);
 #pragma unroll
-    for (int i = 0; i < 8; i++) { rr[i] = make_uint2(0, 0); if (k0 + i >= 0) rr[i] = __ldg(v.Rrow + k0 + i); }
-    for (int c = nck - 1; c >= 0; c--, k0 += PK_CH) {
-      const int i0 = k0 < 0 ? -k0 : 0;
+    for (int i = 0; i < 8; i++) { rr[i] = make_uint2(0, 0); if (i >= i0) rr[i] = __ldg(v.Rrow + k0 + i); }
+    pk_ck_load(tbase + 8 * nfull, ck);
+    pk_finish_chunk<false>(v, k0, i0, raw, xs, alo, ahi, es);
+    pk_alpha_chunk<false, LODD, SHIFT>(o, ck, !LODD, true, i0, xs, raw.y, es, alo, ahi, rr, acc);
+    cc = 1;
+  }
+  {
+    int k0 = rem;
+    pk_load_raw<true, VEC>(v, k0, 0, raw);
+#pragma unroll
+    for (int i = 0; i < 8; i++) rr[i] = __ldg(v.Rrow + k0 + i);
+    for (int c = nfull - 1; c >= 0; c--, k0 += PK_CH, cc++) {
       if (c > 0) {
-        pk_load_raw(v, k0 + PK_CH, 0, vec, nraw);
+        pk_load_raw<true, VEC>(v, k0 + PK_CH, 0, nraw);
 #pragma unroll
         for (int i = 0; i < 8; i++) nrr[i] = __ldg(v.Rrow + k0 + PK_CH + i);
       }
-      uint32_t ck[8], b[8], bb[8][8];
       pk_ck_load(tbase + 8 * c, ck);
-      pk_finish_chunk(v, k0, i0, raw, xs, tw, es);
-#pragma unroll
-      for (int s = 0; s < 8; s++) b[s] = ck[s];
-      if (c > 0 && !LODD) pk_norm(b);              /* the normalisation that followed the store at step k0+8 */
-#pragma unroll
-      for (int i = 7; i >= 1; i--) {
-        if (i >= i0 + 1 || (i >= 1 && i0 == 0)) {
-          pk_beta(b, xs[i], raw.y[i]);
-#pragma unroll
-          for (int s = 0; s < 8; s++) bb[i][s] = b[s];
-          if ((((i & 1) != 0) == LODD)) pk_norm(b);
-        }
-      }
-#pragma unroll
-      for (int i = 0; i < 8; i++) {
-        if (i >= i0) {
-          pk_alpha_branches(o, xs[i], raw.y[i], m, n);
-          const uint32_t *bn = (i == 7) ? ck : bb[(i + 1) & 7];
-          uint32_t m0 = pk_add(bn[0], m[0]), m1 = pk_add(bn[0], n[0]);
-#pragma unroll
-          for (int s = 1; s < 8; s++) { m0 = pk_addmax(bn[s], m[s], m0); m1 = pk_addmax(bn[s], n[s], m1); }
-          uint32_t r = pk_sub(m1, m0);
-          if (shift_out) r = ((r >> 1) & 0x7FFF7FFFu) | (r & 0x80008000u);   /* divide_output, sse16 only (:61,565) */
-          const uint32_t en = pk_sub(r, es[i]);                               /* next apriori = LLR - what this decoder was given */
-          Ew[tw[i] & 0xFFFFu] = (uint16_t)en;
-          Ew[tw[i] >> 16] = (uint16_t)(en >> 16);
-          emx = pk_max(emx, en); emn = pk_min(emn, en);
-          const uint32_t nr = pk_sub(0u, r);                                  /* sign set <=> LLR > 0 <=> bit 1 */
-          const uint32_t mlo = pk_prmt(nr, 0u, 0x9999u), mhi = pk_prmt(nr, 0u, 0xBBBBu);
-          crc ^= (mlo & rr[i].x) ^ (mhi & rr[i].y);
-          wlo = __funnelshift_l(mlo, wlo, 1); whi = __funnelshift_l(mhi, whi, 1);
-          if (++nbits == 32) { bits_lo[wi] = wlo; bits_hi[wi] = whi; wi++; nbits = 0; }
-#pragma unroll
-          for (int s = 0; s < 8; s++) o[s] = pk_max(m[s], n[s]);
-          if ((((i & 1) != 0) == LODD) && (k0 + i) != 0) pk_norm(o);
-        }
-      }
+      pk_finish_chunk<true>(v, k0, 0, raw, xs, alo, ahi, es);
+      pk_alpha_chunk<true, LODD, SHIFT>(o, ck, c > 0 && !LODD, k0 != 0, 0, xs, raw.y, es, alo, ahi, rr, acc);
+      if ((cc & 3) == 3) { bits_lo[wi] = acc.wlo; bits_hi[wi] = acc.whi; wi++; }
       raw = nraw;
 #pragma unroll
       for (int i = 0; i < 8; i++) rr[i] = nrr[i];
     }
   }
-  if (nbits) { bits_lo[wi] = wlo << (32 - nbits); bits_hi[wi] = whi << (32 - nbits); }
+  if (cc & 3) { const int sh = 32 - 8 * (cc & 3); bits_lo[wi] = acc.wlo << sh; bits_hi[wi] = acc.whi << sh; }
 }
 
 /* ---------------------------------------------------------------- output of a finished code block ---- */
@@ -312,35 +358,35 @@ __device__ __forceinline__ uint32_t pk_row_bits(const uint32_t *row, int k)
 }
 
 /* natural-order hard decisions -> K/8 bytes MSB first (turbodecoder_win.h:676-716). rows: [P][nw+1] words,
- * row d holds bits d*L .. d*L+L-1. Called by the TPC threads of one code block. */
+ * row d holds bits d*L .. d*L+L-1 starting at bit index `pad`. Called by the TPC threads of one code block. */
 template <int TPC>
-__device__ __forceinline__ void pk_write_output(const uint32_t *rows, int nw1, int K, int L, int j, uint8_t *out)
+__device__ __forceinline__ void pk_write_output(const uint32_t *rows, int nw1, int pad, int K, int L, int j, uint8_t *out)
 {
   const int nwords = K >> 5;
   uint32_t *out32 = reinterpret_cast<uint32_t *>(out);
   for (int ow = j; ow < nwords; ow += TPC) {
     const int p = ow << 5, d = p / L, k = p - d * L, avail = L - k;
-    uint32_t w = pk_row_bits(rows + d * nw1, k);
-    if (avail < 32) w = (w & ~(0xFFFFFFFFu >> avail)) | (pk_row_bits(rows + (d + 1) * nw1, 0) >> avail);
+    uint32_t w = pk_row_bits(rows + d * nw1, k + pad);
+    if (avail < 32) w = (w & ~(0xFFFFFFFFu >> avail)) | (pk_row_bits(rows + (d + 1) * nw1, pad) >> avail);
     out32[ow] = __byte_perm(w, 0, 0x0123);
   }
   for (int ob = (nwords << 2) + j; ob < (K >> 3); ob += TPC) {      /* K/8 not a multiple of 4: last 1..3 bytes */
     const int p = ob << 3, d = p / L, k = p - d * L, avail = L - k;
-    uint32_t w = pk_row_bits(rows + d * nw1, k);
-    if (avail < 8) w = (w & ~(0xFFFFFFFFu >> avail)) | (pk_row_bits(rows + (d + 1) * nw1, 0) >> avail);
+    uint32_t w = pk_row_bits(rows + d * nw1, k + pad);
+    if (avail < 8) w = (w & ~(0xFFFFFFFFu >> avail)) | (pk_row_bits(rows + (d + 1) * nw1, pad) >> avail);
     out[ob] = (uint8_t)(w >> 24);
   }
 }
 
 /* ---------------------------------------------------------------- the kernel ---- */
-/* shared memory: [T2: TPC*Lp words][E: nslots x (TPC*Lw+1) words][bit rows: nslots x P x (nw+1) words] */
+/* shared memory: [Tlo, Thi: TPC*Lw halfwords each][E: nslots x (TPC*Lw+1) words][bit rows: nslots x P x nw1 words] */
 size_t fec_pk_smem_bytes(const fec_geom_t *g)
 {
   const size_t tpc = g->P / 2, nslots = (size_t)FEC_PK_WARPS * (32 / tpc), nw1 = (g->L + 31) / 32 + 1;
-  return 4 * (tpc * g->Lp + nslots * (tpc * g->Lw + 1) + nslots * g->P * nw1);
+  return 4 * (tpc * g->Lw + nslots * (tpc * g->Lw + 1) + nslots * g->P * nw1);
 }
 
-template <int P, bool LODD>
+template <int P, int MODE>
 __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const FecDecodeArgs a)
 {
   constexpr int TPC = P / 2, CPW = 32 / TPC;
@@ -349,13 +395,18 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane / TPC, j = lane % TPC;
   const int K = a.g.K, L = a.g.L, Lp = a.g.Lp, Lw = a.g.Lw, SS = a.g.SS;
   const int nw1 = (L + 31) / 32 + 1, Es = TPC * Lw + 1, nslots = FEC_PK_WARPS * CPW, slot = warp * CPW + g;
-  uint32_t *T2 = reinterpret_cast<uint32_t *>(smem);
-  uint32_t *Eslot = T2 + TPC * Lp + slot * Es;
-  uint32_t *rows = T2 + TPC * Lp + nslots * Es + slot * (P * nw1);
-  const bool vec = (L & 3) == 0;
+  const int pad = (8 - (L & 7)) & 7;
+  uint16_t *Tlo = reinterpret_cast<uint16_t *>(smem), *Thi = Tlo + TPC * Lw;
+  uint32_t *Eslot = reinterpret_cast<uint32_t *>(smem) + TPC * Lw + slot * Es;
+  uint32_t *rows = reinterpret_cast<uint32_t *>(smem) + TPC * Lw + nslots * Es + slot * (P * nw1);
   const unsigned gmask = (TPC == 32) ? 0xFFFFFFFFu : (((1u << TPC) - 1u) << (g * TPC));
 
-  for (int i = tid; i < TPC * Lp; i += blockDim.x) T2[i] = a.pair_addr[i];
+  for (int i = tid; i < TPC * L; i += blockDim.x) {
+    const int r = i / L, k = i - r * L;
+    const uint32_t w = a.pair_addr[r * Lp + k];
+    Tlo[r * Lw + k] = (uint16_t)((w & 0xFFFFu) * 2u);
+    Thi[r * Lw + k] = (uint16_t)((w >> 16) * 2u);
+  }
   if (warp == 0) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" :: "r"((uint32_t)__cvta_generic_to_shared(&s_tmem)) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -396,13 +447,14 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
     v.Srow = reinterpret_cast<const uint32_t *>(desc.soft) + j * Lp;
     v.Yrow = reinterpret_cast<const uint32_t *>(desc.soft + (1 + par) * SS) + j * Lp;
     v.Rrow = a.pair_crc[desc.crc_sel] + (size_t)par * TPC * Lp + j * Lp;
-    v.Trow = T2 + j * Lp;
-    v.Eh = reinterpret_cast<const uint16_t *>(Eslot);
-    v.ident = (uint32_t)(2 * j * Lw) * 0x10001u + 0x10000u;
-    uint32_t crc = 0, emx = 0x80008000u, emn = 0x7FFF7FFFu;
-    pk_half_iteration<TPC, LODD>(v, L, vec, tbase, gmask, j, desc.soft + 3 * SS + (par ? 6 : 0),
-                                 reinterpret_cast<uint16_t *>(Eslot), rows + (2 * j) * nw1, rows + (2 * j + 1) * nw1,
-                                 P == 8, crc, emx, emn);
+    v.Tlo = Tlo + j * Lw; v.Thi = Thi + j * Lw;
+    v.Eb = (uint32_t)__cvta_generic_to_shared(Eslot);
+    v.ident = (uint32_t)(4 * j * Lw);
+    PkAcc acc;
+    acc.crc = 0; acc.emx = 0x80008000u; acc.emn = 0x7FFF7FFFu;
+    uint32_t *blo = rows + (2 * j) * nw1, *bhi = rows + (2 * j + 1) * nw1;
+    pk_half_iteration<TPC, MODE, P == 8>(v, L, tbase, gmask, j, desc.soft + 3 * SS + (par ? 6 : 0), blo, bhi, acc);
+    uint32_t crc = acc.crc, emx = acc.emx, emn = acc.emn;
 #pragma unroll
     for (int s = TPC / 2; s > 0; s >>= 1) {
       crc ^= __shfl_xor_sync(0xFFFFFFFFu, crc, s, TPC);
@@ -417,25 +469,23 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
         if (par) {
           /* decisions are in interleaved order: spread them to natural positions through the (now dead) E array,
            * then rebuild the natural bit rows */
-          const uint32_t *blo = rows + (2 * j) * nw1, *bhi = rows + (2 * j + 1) * nw1;
-          uint16_t *Eh = reinterpret_cast<uint16_t *>(Eslot);
           for (int k = 0; k < L; k++) {
-            const uint32_t t = v.Trow[k];
-            Eh[t & 0xFFFFu] = (uint16_t)(0u - ((blo[k >> 5] >> (31 - (k & 31))) & 1u));
-            Eh[t >> 16] = (uint16_t)(0u - ((bhi[k >> 5] >> (31 - (k & 31))) & 1u));
+            const int kb = k + pad;
+            pk_sts_u16(v.Eb + v.Tlo[k], 0u - ((blo[kb >> 5] >> (31 - (kb & 31))) & 1u));
+            pk_sts_u16(v.Eb + v.Thi[k], 0u - ((bhi[kb >> 5] >> (31 - (kb & 31))) & 1u));
           }
           __syncwarp(gmask);
           uint32_t wlo = 0, whi = 0;
-          uint32_t *olo = rows + (2 * j) * nw1, *ohi = rows + (2 * j + 1) * nw1;
           for (int k = 0; k < L; k++) {
+            const int kb = k + pad;
             const uint32_t w = Eslot[j * Lw + k];
             wlo = __funnelshift_l(w << 16, wlo, 1); whi = __funnelshift_l(w, whi, 1);
-            if ((k & 31) == 31) { olo[k >> 5] = wlo; ohi[k >> 5] = whi; }
+            if ((kb & 31) == 31) { blo[kb >> 5] = wlo; bhi[kb >> 5] = whi; }
           }
-          if (L & 31) { olo[L >> 5] = wlo << (32 - (L & 31)); ohi[L >> 5] = whi << (32 - (L & 31)); }
+          if ((L + pad) & 31) { const int sh = 32 - ((L + pad) & 31); blo[(L + pad) >> 5] = wlo << sh; bhi[(L + pad) >> 5] = whi << sh; }
         }
         __syncwarp(gmask);
-        pk_write_output<TPC>(rows, nw1, K, L, j, desc.out);
+        pk_write_output<TPC>(rows, nw1, pad, K, L, j, desc.out);
         if (j == 0) { a.status[desc.status].its = (uint32_t)n1; a.status[desc.status].crc_ok = (uint32_t)crc_ok; }
         __syncwarp(gmask);
         cb = -1;
@@ -457,6 +507,16 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
   if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" :: "r"(s_tmem) : "memory");
 }
 
+template <int P>
+static cudaError_t pk_launch(const FecDecodeArgs &a, int grid, size_t smem, cudaStream_t st)
+{
+  const int L = a.g.L;
+  if ((L & 3) == 0)      fec_tdec_pk_kernel<P, 0><<<grid, FEC_PK_WARPS * 32, smem, st>>>(a);
+  else if ((L & 1) == 0) fec_tdec_pk_kernel<P, 1><<<grid, FEC_PK_WARPS * 32, smem, st>>>(a);
+  else                   fec_tdec_pk_kernel<P, 2><<<grid, FEC_PK_WARPS * 32, smem, st>>>(a);
+  return cudaGetLastError();
+}
+
 cudaError_t fec_launch_decode_packed(const FecDecodeArgs &a, int sm_count, cudaStream_t st)
 {
   if (a.ncb == 0) return cudaSuccess;
@@ -464,25 +524,21 @@ cudaError_t fec_launch_decode_packed(const FecDecodeArgs &a, int sm_count, cudaS
   const int tpc = a.g.P / 2, per_cta = FEC_PK_WARPS * (32 / tpc);
   int grid = (int)((a.ncb + per_cta - 1) / per_cta);
   if (grid > sm_count) grid = sm_count;
-  const bool lodd = (a.g.L & 1) != 0;
-  if (a.g.P == 16) {
-    if (lodd) fec_tdec_pk_kernel<16, true><<<grid, FEC_PK_WARPS * 32, smem, st>>>(a);
-    else      fec_tdec_pk_kernel<16, false><<<grid, FEC_PK_WARPS * 32, smem, st>>>(a);
-  } else {
-    if (lodd) fec_tdec_pk_kernel<8, true><<<grid, FEC_PK_WARPS * 32, smem, st>>>(a);
-    else      fec_tdec_pk_kernel<8, false><<<grid, FEC_PK_WARPS * 32, smem, st>>>(a);
-  }
-  return cudaGetLastError();
+  return a.g.P == 16 ? pk_launch<16>(a, grid, smem, st) : pk_launch<8>(a, grid, smem, st);
+}
+
+template <int P, int MODE> static cudaError_t pk_attr()
+{
+  return cudaFuncSetAttribute(fec_tdec_pk_kernel<P, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
 }
 
 cudaError_t fec_pk_init(void)
 {
   cudaError_t e;
-  e = cudaFuncSetAttribute(fec_tdec_pk_kernel<16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-  if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(fec_tdec_pk_kernel<16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-  if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(fec_tdec_pk_kernel<8, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-  if (e != cudaSuccess) return e;
-  return cudaFuncSetAttribute(fec_tdec_pk_kernel<8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  if ((e = pk_attr<16, 0>()) != cudaSuccess) return e;
+  if ((e = pk_attr<16, 1>()) != cudaSuccess) return e;
+  if ((e = pk_attr<16, 2>()) != cudaSuccess) return e;
+  if ((e = pk_attr<8, 0>()) != cudaSuccess) return e;
+  if ((e = pk_attr<8, 1>()) != cudaSuccess) return e;
+  return pk_attr<8, 2>();
 }
