@@ -34,6 +34,8 @@ typedef struct {
 } sbchunk_t;
 
 typedef struct { void *h, *d; size_t cap; } stage_t;   /* pinned host + device mirror, grown on demand */
+#define FEC_NPIPE 4
+typedef struct fec_pipe fec_pipe_t;
 
 struct fec_cuda_ctx {
   int           device, sm_count;
@@ -53,9 +55,15 @@ struct fec_cuda_ctx {
   uint32_t     *d_exact;   size_t exact_cap;     /* per code block of the call: hand-over list of the packed kernel */
   int           force_exact;
   int16_t      *d_dbg; size_t dbg_cap; uint32_t *dbg_slot; uint32_t dbg_n;   /* test hook: LLR dump */
-  cudaEvent_t   ev[4];     /* phase boundaries of the last decode_tbs call: rm | decode | assemble */
+  float         phase_ms[3];   /* device time of rm | decode | assemble summed over the sub-batches of the last decode_tbs call */
   int           ev_valid;
+  cudaStream_t  s_copy, s_out, s_comp[2];
+  fec_pipe_t   *pipes;
+  uint32_t      sub_tbs;
 };
+
+static int pipes_create(fec_cuda_ctx_t *ctx);
+static void pipes_destroy(fec_cuda_ctx_t *ctx);
 
 static int fail(fec_cuda_ctx_t *c, int code, const char *fmt, ...)
 {
@@ -127,7 +135,7 @@ extern "C" int fec_cuda_create(fec_cuda_ctx_t **out, int device, uint32_t max_tb
   free(R);
   cudaMalloc(&ctx->d_queue, sizeof(unsigned int) * 3 * FEC_NOF_K);
   { const char *fe = getenv("FEC_CUDA_FORCE_EXACT"); ctx->force_exact = fe && fe[0] == '1'; }
-  for (int i = 0; i < 4; i++) cudaEventCreate(&ctx->ev[i]);
+  if (pipes_create(ctx)) { free(ctx); return FEC_CUDA_ENODEV; }
   if (cudaGetLastError() != cudaSuccess) { free(ctx); return FEC_CUDA_ENODEV; }
   *out = ctx;
   return FEC_CUDA_SUCCESS;
@@ -148,7 +156,7 @@ extern "C" void fec_cuda_destroy(fec_cuda_ctx_t *ctx)
   stage_free(&ctx->st_e); stage_free(&ctx->st_data); stage_free(&ctx->st_cbd); stage_free(&ctx->st_rmd);
   stage_free(&ctx->st_tbd); stage_free(&ctx->st_status); stage_free(&ctx->st_ret); stage_free(&ctx->st_exd);
   cudaFree(ctx->d_cbbytes); cudaFree(ctx->d_tmpsoft); cudaFree(ctx->d_r24a); cudaFree(ctx->d_r24b); cudaFree(ctx->d_queue);
-  for (int i = 0; i < 4; i++) cudaEventDestroy(ctx->ev[i]);
+  pipes_destroy(ctx);
   cudaStreamDestroy(ctx->stream);
   free(ctx);
 }
@@ -169,8 +177,7 @@ extern "C" void fec_cuda_host_free(void *p) { if (p) cudaFreeHost(p); }
 extern "C" int fec_cuda_last_phase_ms(fec_cuda_ctx_t *ctx, float out3[3])
 {
   if (!ctx || !out3 || !ctx->ev_valid) return FEC_CUDA_EINVAL;
-  for (int i = 0; i < 3; i++)
-    if (cudaEventElapsedTime(&out3[i], ctx->ev[i], ctx->ev[i + 1]) != cudaSuccess) return FEC_CUDA_ERROR;
+  for (int i = 0; i < 3; i++) out3[i] = ctx->phase_ms[i];
   return 0;
 }
 
@@ -223,6 +230,7 @@ extern "C" int fec_cuda_softbuffer_alloc(fec_cuda_ctx_t *ctx, uint32_t n, uint32
   CU(cudaMalloc(&c.d_cache, (size_t)n * FEC_CUDA_MAX_CB * CB_BYTES));
   CU(cudaMemsetAsync(c.d_soft, 0, (size_t)n * FEC_CUDA_MAX_CB * FEC_CUDA_SOFT_SLOT * sizeof(int16_t), ctx->stream));
   CU(cudaMemsetAsync(c.d_cache, 0, (size_t)n * FEC_CUDA_MAX_CB * CB_BYTES, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));      /* decode calls run on several streams */
   c.cb_crc = (uint8_t *)calloc((size_t)n * FEC_CUDA_MAX_CB, 1);
   ctx->chunks = (sbchunk_t *)realloc(ctx->chunks, sizeof(sbchunk_t) * (ctx->nchunks + 1));
   ctx->chunks[ctx->nchunks++] = c;
@@ -250,6 +258,7 @@ extern "C" int fec_cuda_softbuffer_reset(fec_cuda_ctx_t *ctx, uint32_t id)
   memset(c->cb_crc + (size_t)l * FEC_CUDA_MAX_CB, 0, FEC_CUDA_MAX_CB);
   CU(cudaMemsetAsync(c->d_soft + (size_t)l * FEC_CUDA_MAX_CB * FEC_CUDA_SOFT_SLOT, 0,
                      (size_t)FEC_CUDA_MAX_CB * FEC_CUDA_SOFT_SLOT * sizeof(int16_t), ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
   return 0;
 }
 
@@ -269,36 +278,71 @@ extern "C" int fec_cuda_softbuffer_read_ref_layout(fec_cuda_ctx_t *ctx, uint32_t
   return 0;
 }
 
-static void fill_decode_args(fec_cuda_ctx_t *ctx, int k, FecDecodeArgs *a, uint32_t off, uint32_t cnt, int16_t *dbg)
+static void fill_decode_args(fec_cuda_ctx_t *ctx, int k, FecDecodeArgs *a, const FecCbDesc *cbd_dev, FecCbStatus *status_dev,
+                             unsigned int *queue3, const uint32_t *softmax, uint32_t *exact, uint32_t off, uint32_t cnt, int16_t *dbg)
 {
   const ktab_t *t = &ctx->ktab[k];
   memset(a, 0, sizeof(*a));
   a->g = t->g; a->step_tab = t->d_step; a->crcpow[0] = ctx->d_r24a; a->crcpow[1] = ctx->d_r24b;
-  a->cbs = (const FecCbDesc *)ctx->st_cbd.d + off; a->status = (FecCbStatus *)ctx->st_status.d;
-  a->queue = ctx->d_queue + 2 * k; a->ncb = cnt; a->slots = t->slots; a->dbg_llr = dbg;
+  a->cbs = cbd_dev + off; a->status = status_dev;
+  a->queue = queue3 + 2 * k; a->ncb = cnt; a->slots = t->slots; a->dbg_llr = dbg;
   a->pair_addr = t->d_pair_addr; a->pair_crc[0] = t->d_pair_crc[0]; a->pair_crc[1] = t->d_pair_crc[1];
-  a->soft_max = ctx->d_softmax;
-  if (t->g.P && !ctx->force_exact && !dbg) { a->exact_list = ctx->d_exact + off; a->exact_count = ctx->d_queue + 2 * FEC_NOF_K + k; }
+  a->soft_max = softmax;
+  if (t->g.P && !ctx->force_exact && !dbg) { a->exact_list = exact + off; a->exact_count = queue3 + 2 * FEC_NOF_K + k; }
 }
 
 /* ---------------------------------------------------------------- batched transport-block decode ---- */
-typedef struct { uint32_t seg[9]; sbchunk_t *chunk; uint32_t local; int valid, pinned; uint32_t first_cb; uint32_t ndec; size_t data_off, e_off; } tbplan_t;
+/* A call is cut into sub-batches that flow through a ring of FEC_NPIPE "pipes" (own pinned staging, device
+ * scratch and events each): while the GPU works on sub-batch i (H2D of its LLRs on the copy stream, kernels on
+ * one of two compute streams, D2H on the output stream) the host builds the descriptors of sub-batch i+1 and
+ * unpacks the results of sub-batch i-1. The call returns when every sub-batch is done. */
+typedef struct { uint32_t seg[9]; sbchunk_t *chunk; uint32_t local; int valid, pinned; uint32_t ndec; size_t data_off, e_off; int kidx[2]; } tbplan_t;
 
-#define CUF(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { free(plan); \
-  return fail(ctx, FEC_CUDA_ENODEV, "%s: %s", #call, cudaGetErrorString(e_)); } } while (0)
+struct fec_pipe {
+  stage_t       st_e, st_data, st_cbd, st_rmd, st_tbd, st_status, st_ret;
+  uint8_t      *d_cbbytes; size_t cbbytes_cap;
+  uint32_t     *d_softmax; size_t softmax_cap;
+  uint32_t     *d_exact;   size_t exact_cap;
+  unsigned int *d_queue;
+  cudaEvent_t   ev_in, ev_k, ev_done, ev[4];
+  tbplan_t     *plan; size_t plan_cap;
+  fec_cuda_tb_t *tbs; uint32_t n, ncb, ntb; int dev_io, busy;
+  size_t        data_total;
+};
 
-#define DBG_LLR NULL
-extern "C" int fec_cuda_decode_tbs(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, uint32_t n, uint32_t flags)
+static int pipe_init(fec_cuda_ctx_t *ctx, fec_pipe_t *p)
 {
-  if (!ctx || (!tbs && n)) return FEC_CUDA_EINVAL;
-  if (n == 0) return 0;
-  cudaSetDevice(ctx->device);
+  memset(p, 0, sizeof(*p));
+  CU(cudaMalloc(&p->d_queue, sizeof(unsigned int) * 3 * FEC_NOF_K));
+  CU(cudaEventCreateWithFlags(&p->ev_in, cudaEventDisableTiming));
+  CU(cudaEventCreateWithFlags(&p->ev_k, cudaEventDisableTiming));
+  CU(cudaEventCreateWithFlags(&p->ev_done, cudaEventDisableTiming));
+  for (int i = 0; i < 4; i++) CU(cudaEventCreate(&p->ev[i]));
+  return 0;
+}
+
+static void pipe_free(fec_pipe_t *p)
+{
+  stage_free(&p->st_e); stage_free(&p->st_data); stage_free(&p->st_cbd); stage_free(&p->st_rmd);
+  stage_free(&p->st_tbd); stage_free(&p->st_status); stage_free(&p->st_ret);
+  cudaFree(p->d_cbbytes); cudaFree(p->d_softmax); cudaFree(p->d_exact); cudaFree(p->d_queue);
+  if (p->ev_in) { cudaEventDestroy(p->ev_in); cudaEventDestroy(p->ev_k); cudaEventDestroy(p->ev_done); for (int i = 0; i < 4; i++) cudaEventDestroy(p->ev[i]); }
+  free(p->plan);
+  memset(p, 0, sizeof(*p));
+}
+
+/* build descriptors for tbs[0..n), enqueue copies + kernels; returns without waiting */
+static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, uint32_t n, uint32_t flags, cudaStream_t sc)
+{
   const int dev_io = (flags & FEC_CUDA_F_DEVICE_IO) != 0;
-  tbplan_t *plan = (tbplan_t *)calloc(n, sizeof(tbplan_t));
+  if (pp->plan_cap < n) { free(pp->plan); pp->plan = (tbplan_t *)malloc(sizeof(tbplan_t) * n); pp->plan_cap = n; }
+  tbplan_t *plan = pp->plan;
+  memset(plan, 0, sizeof(tbplan_t) * n);
   uint32_t grp_cnt[FEC_NOF_K], grp_off[FEC_NOF_K], grp_fill[FEC_NOF_K];
   memset(grp_cnt, 0, sizeof(grp_cnt));
   uint32_t ncb = 0, ntb = 0;
   size_t e_total = 0, data_total = 0;
+  pp->tbs = tbs; pp->n = n; pp->dev_io = dev_io; pp->ncb = pp->ntb = 0; pp->busy = 0;
 
   /* pass 1: argument checks of decode_tb (sch.c:444-457) + segmentation + HARQ state */
   for (uint32_t i = 0; i < n; i++) {
@@ -314,33 +358,33 @@ extern "C" int fec_cuda_decode_tbs(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, uint
     if (!p->chunk) continue;
     uint8_t *crc = p->chunk->cb_crc + (size_t)p->local * FEC_CUDA_MAX_CB;
     if (t->new_data) memset(crc, 0, FEC_CUDA_MAX_CB);
-    p->valid = 1; p->first_cb = ncb; p->ndec = 0;
+    p->kidx[0] = (int)p->seg[4]; p->kidx[1] = (int)p->seg[5];
+    p->valid = 1; p->ndec = 0;
     for (uint32_t cb = 0; cb < p->seg[1]; cb++)
-      if (!crc[cb]) { uint32_t K = cb < p->seg[6] ? p->seg[2] : p->seg[3]; grp_cnt[fec_k_index(K)]++; p->ndec++; }
+      if (!crc[cb]) { grp_cnt[p->kidx[cb < p->seg[6] ? 0 : 1]]++; p->ndec++; }
     ncb += p->ndec; ntb++;
     p->e_off = e_total; e_total += ((size_t)t->nof_e_bits + 7) & ~(size_t)7;
     p->data_off = data_total; data_total += ((size_t)t->tbs / 8 + 3 + CB_BYTES + 15) & ~(size_t)15;
   }
-  if (ntb == 0) { free(plan); return 0; }
+  if (ntb == 0) return 0;
   uint32_t acc = 0;
   for (int k = 0; k < FEC_NOF_K; k++) { grp_off[k] = acc; grp_fill[k] = 0; acc += grp_cnt[k]; }
 
-  int rc = 0;
-  if (stage_reserve(ctx, &ctx->st_cbd, sizeof(FecCbDesc) * (ncb + 1)) || stage_reserve(ctx, &ctx->st_rmd, sizeof(FecRmDesc) * (ncb + 1)) ||
-      stage_reserve(ctx, &ctx->st_tbd, sizeof(FecTbDesc) * ntb) || stage_reserve(ctx, &ctx->st_status, sizeof(FecCbStatus) * (ncb + 1)) ||
-      stage_reserve(ctx, &ctx->st_ret, sizeof(int32_t) * ntb) ||
-      dev_reserve(ctx, (void **)&ctx->d_cbbytes, &ctx->cbbytes_cap, (size_t)(ncb + 1) * CB_BYTES) ||
-      dev_reserve(ctx, (void **)&ctx->d_softmax, &ctx->softmax_cap, (size_t)(ncb + 1) * 4) ||
-      dev_reserve(ctx, (void **)&ctx->d_exact, &ctx->exact_cap, (size_t)(ncb + 1) * 4) ||
-      (!dev_io && (stage_reserve(ctx, &ctx->st_e, e_total * 2) || stage_reserve(ctx, &ctx->st_data, data_total)))) { free(plan); return FEC_CUDA_ENODEV; }
+  if (stage_reserve(ctx, &pp->st_cbd, sizeof(FecCbDesc) * (ncb + 1)) || stage_reserve(ctx, &pp->st_rmd, sizeof(FecRmDesc) * (ncb + 1)) ||
+      stage_reserve(ctx, &pp->st_tbd, sizeof(FecTbDesc) * ntb) || stage_reserve(ctx, &pp->st_status, sizeof(FecCbStatus) * (ncb + 1)) ||
+      stage_reserve(ctx, &pp->st_ret, sizeof(int32_t) * ntb) ||
+      dev_reserve(ctx, (void **)&pp->d_cbbytes, &pp->cbbytes_cap, (size_t)(ncb + 1) * CB_BYTES) ||
+      dev_reserve(ctx, (void **)&pp->d_softmax, &pp->softmax_cap, (size_t)(ncb + 1) * 4) ||
+      dev_reserve(ctx, (void **)&pp->d_exact, &pp->exact_cap, (size_t)(ncb + 1) * 4) ||
+      (!dev_io && (stage_reserve(ctx, &pp->st_e, e_total * 2) || stage_reserve(ctx, &pp->st_data, data_total)))) return FEC_CUDA_ENODEV;
 
-  FecCbDesc *cbd = (FecCbDesc *)ctx->st_cbd.h;
-  FecRmDesc *rmd = (FecRmDesc *)ctx->st_rmd.h;
-  FecTbDesc *tbd = (FecTbDesc *)ctx->st_tbd.h;
+  FecCbDesc *cbd = (FecCbDesc *)pp->st_cbd.h;
+  FecRmDesc *rmd = (FecRmDesc *)pp->st_rmd.h;
+  FecTbDesc *tbd = (FecTbDesc *)pp->st_tbd.h;
   uint32_t max_n_out = 0, itb = 0;
 
   /* pass 2: descriptors. E / rp per code block exactly as decode_tb_cb derives them (sch.c:328-342) */
-  for (uint32_t i = 0; i < n && !rc; i++) {
+  for (uint32_t i = 0; i < n; i++) {
     fec_cuda_tb_t *t = &tbs[i];
     tbplan_t *p = &plan[i];
     if (!p->valid) continue;
@@ -348,18 +392,20 @@ extern "C" int fec_cuda_decode_tbs(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, uint
     uint8_t *crc = p->chunk->cb_crc + (size_t)p->local * FEC_CUDA_MAX_CB;
     int16_t *soft0 = p->chunk->d_soft + (size_t)p->local * FEC_CUDA_MAX_CB * FEC_CUDA_SOFT_SLOT;
     uint8_t *cache0 = p->chunk->d_cache + (size_t)p->local * FEC_CUDA_MAX_CB * CB_BYTES;
-    const int16_t *e_dev = dev_io ? t->e_bits : (const int16_t *)ctx->st_e.d + p->e_off;
+    const int16_t *e_dev = dev_io ? t->e_bits : (const int16_t *)pp->st_e.d + p->e_off;
     FecTbDesc *td = &tbd[itb];
     memset(td, 0, sizeof(*td));
-    td->data = dev_io ? t->data : (uint8_t *)ctx->st_data.d + p->data_off;
-    td->C = C; td->tbs = t->tbs; td->all_ok = 1; td->ret = (int32_t *)ctx->st_ret.d + itb;
+    td->data = dev_io ? t->data : (uint8_t *)pp->st_data.d + p->data_off;
+    td->C = C; td->tbs = t->tbs; td->all_ok = 1; td->ret = (int32_t *)pp->st_ret.d + itb;
     const uint32_t Gp = t->nof_e_bits / t->Qm, gamma = Gp % C, n_e = t->Qm * (Gp / C);
+    ktab_t *kts[2] = {NULL, NULL};
     for (uint32_t cb = 0; cb < C; cb++) {
-      const uint32_t K = cb < C1 ? p->seg[2] : p->seg[3];
+      const int which = cb < C1 ? 0 : 1;
+      const uint32_t K = which ? p->seg[3] : p->seg[2];
       td->K[cb] = K; td->rlen[cb] = C == 1 ? K : K - 24; td->cache[cb] = cache0 + (size_t)cb * CB_BYTES;
       if (crc[cb]) { td->st_idx[cb] = -1; td->cb_bytes[cb] = td->cache[cb]; continue; }
-      ktab_t *kt;
-      if (ktab_get(ctx, K, &kt)) { rc = FEC_CUDA_EINVAL; break; }
+      if (!kts[which] && ktab_get(ctx, K, &kts[which])) return FEC_CUDA_EINVAL;
+      ktab_t *kt = kts[which];
       uint32_t rp = cb * n_e, E = n_e;
       if (cb > C - gamma) { E = n_e + t->Qm; rp = (C - gamma) * n_e + (cb - (C - gamma)) * E; }   /* sch.c:339 off-by-one kept */
       const uint32_t slot = grp_off[kt->g.idx] + grp_fill[kt->g.idx]++;
@@ -368,7 +414,7 @@ extern "C" int fec_cuda_decode_tbs(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, uint
       r->E = E; r->N = 3 * K + 12; r->off = kt->off[t->rv]; r->n_out = 3 * kt->g.SS + 16; r->new_data = t->new_data ? 1 : 0; r->slot = slot;
       if (r->n_out > max_n_out) max_n_out = r->n_out;
       FecCbDesc *d = &cbd[slot];
-      d->soft = r->soft; d->out = ctx->d_cbbytes + (size_t)slot * CB_BYTES; d->crc_sel = C > 1 ? 1 : 0;
+      d->soft = r->soft; d->out = pp->d_cbbytes + (size_t)slot * CB_BYTES; d->crc_sel = C > 1 ? 1 : 0;
       d->max_its = t->max_its ? t->max_its : 1; d->flags = (flags & FEC_CUDA_F_NO_EARLY_STOP) ? FEC_F_NO_EARLY : 0; d->status = slot;
       td->st_idx[cb] = (int32_t)slot; td->cb_bytes[cb] = d->out;
     }
@@ -377,68 +423,85 @@ extern "C" int fec_cuda_decode_tbs(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, uint
       cudaPointerAttributes pa;
       p->pinned = (cudaPointerGetAttributes(&pa, t->e_bits) == cudaSuccess && pa.type == cudaMemoryTypeHost);
       cudaGetLastError();
-      if (!p->pinned) memcpy((int16_t *)ctx->st_e.h + p->e_off, t->e_bits, (size_t)t->nof_e_bits * 2);
+      if (!p->pinned) memcpy((int16_t *)pp->st_e.h + p->e_off, t->e_bits, (size_t)t->nof_e_bits * 2);
     }
     itb++;
   }
-  if (rc) { free(plan); return rc; }
 
-  cudaStream_t st = ctx->stream;
+  /* ---- copy stream: LLRs (one copy per run of TBs contiguous on both sides) + descriptors ---- */
+  cudaStream_t sin = ctx->s_copy, sout = ctx->s_out;
   if (!dev_io) {
-    /* one H2D copy per run of transport blocks that is contiguous on both sides */
     uint32_t i = 0;
     while (i < n) {
       if (!plan[i].valid) { i++; continue; }
       const int pinned = plan[i].pinned;
-      const char *src0 = pinned ? (const char *)tbs[i].e_bits : (const char *)((int16_t *)ctx->st_e.h + plan[i].e_off);
+      const char *src0 = pinned ? (const char *)tbs[i].e_bits : (const char *)((int16_t *)pp->st_e.h + plan[i].e_off);
       const size_t dst0 = plan[i].e_off * 2;
       size_t len = (size_t)tbs[i].nof_e_bits * 2;
       uint32_t j = i + 1;
       for (; j < n; j++) {
         if (!plan[j].valid || plan[j].pinned != pinned || plan[j].e_off * 2 != dst0 + len) break;
         if (pinned && (const char *)tbs[j].e_bits != src0 + len) break;
-        if (!pinned && (((size_t)tbs[j - 1].nof_e_bits) & 7)) break;
         len += (size_t)tbs[j].nof_e_bits * 2;
       }
-      CUF(cudaMemcpyAsync((char *)ctx->st_e.d + dst0, src0, len, cudaMemcpyHostToDevice, st));
+      CU(cudaMemcpyAsync((char *)pp->st_e.d + dst0, src0, len, cudaMemcpyHostToDevice, sin));
       i = j;
     }
   }
-  CUF(cudaMemcpyAsync(ctx->st_cbd.d, cbd, sizeof(FecCbDesc) * ncb, cudaMemcpyHostToDevice, st));
-  CUF(cudaMemcpyAsync(ctx->st_rmd.d, rmd, sizeof(FecRmDesc) * ncb, cudaMemcpyHostToDevice, st));
-  CUF(cudaMemcpyAsync(ctx->st_tbd.d, tbd, sizeof(FecTbDesc) * ntb, cudaMemcpyHostToDevice, st));
-  CUF(cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned int) * 3 * FEC_NOF_K, st));
-  CUF(cudaMemsetAsync(ctx->d_softmax, 0, (size_t)ncb * 4, st));
-  CUF(cudaEventRecord(ctx->ev[0], st));
+  CU(cudaMemcpyAsync(pp->st_cbd.d, cbd, sizeof(FecCbDesc) * ncb, cudaMemcpyHostToDevice, sin));
+  CU(cudaMemcpyAsync(pp->st_rmd.d, rmd, sizeof(FecRmDesc) * ncb, cudaMemcpyHostToDevice, sin));
+  CU(cudaMemcpyAsync(pp->st_tbd.d, tbd, sizeof(FecTbDesc) * ntb, cudaMemcpyHostToDevice, sin));
+  CU(cudaEventRecord(pp->ev_in, sin));
+
+  /* ---- compute stream: rate de-matching, turbo decode per K group, TB assembly + CRC24A ---- */
+  CU(cudaMemsetAsync(pp->d_queue, 0, sizeof(unsigned int) * 3 * FEC_NOF_K, sc));
+  CU(cudaMemsetAsync(pp->d_softmax, 0, (size_t)ncb * 4, sc));
+  CU(cudaStreamWaitEvent(sc, pp->ev_in, 0));
+  CU(cudaEventRecord(pp->ev[0], sc));
   for (uint32_t o = 0; o < ncb; o += 32768) {                       /* grid.y limit */
     const uint32_t m = ncb - o < 32768 ? ncb - o : 32768;
-    CUF(fec_launch_rm((const FecRmDesc *)ctx->st_rmd.d + o, ctx->d_softmax, m, max_n_out, st));
+    CU(fec_launch_rm((const FecRmDesc *)pp->st_rmd.d + o, pp->d_softmax, m, max_n_out, sc));
     ctx->launches++;
   }
-  CUF(cudaEventRecord(ctx->ev[1], st));
+  CU(cudaEventRecord(pp->ev[1], sc));
   for (int k = 0; k < FEC_NOF_K; k++) {
     if (!grp_cnt[k]) continue;
     FecDecodeArgs a;
-    fill_decode_args(ctx, k, &a, grp_off[k], grp_cnt[k], DBG_LLR);
-    CUF(fec_launch_decode(a, ctx->sm_count, st));
+    fill_decode_args(ctx, k, &a, (const FecCbDesc *)pp->st_cbd.d, (FecCbStatus *)pp->st_status.d, pp->d_queue, pp->d_softmax, pp->d_exact,
+                     grp_off[k], grp_cnt[k], NULL);
+    CU(fec_launch_decode(a, ctx->sm_count, sc));
     ctx->launches += a.exact_list ? 2 : 1;
   }
-  CUF(cudaEventRecord(ctx->ev[2], st));
-  CUF(fec_launch_tb_assemble((const FecTbDesc *)ctx->st_tbd.d, (const FecCbStatus *)ctx->st_status.d, ctx->d_r24a, ntb, st));
+  CU(cudaEventRecord(pp->ev[2], sc));
+  CU(fec_launch_tb_assemble((const FecTbDesc *)pp->st_tbd.d, (const FecCbStatus *)pp->st_status.d, ctx->d_r24a, ntb, sc));
   ctx->launches++;
-  CUF(cudaEventRecord(ctx->ev[3], st));
-  ctx->ev_valid = 1;
-  if (ncb) CUF(cudaMemcpyAsync(ctx->st_status.h, ctx->st_status.d, sizeof(FecCbStatus) * ncb, cudaMemcpyDeviceToHost, st));
-  CUF(cudaMemcpyAsync(ctx->st_ret.h, ctx->st_ret.d, sizeof(int32_t) * ntb, cudaMemcpyDeviceToHost, st));
-  if (!dev_io) CUF(cudaMemcpyAsync(ctx->st_data.h, ctx->st_data.d, data_total, cudaMemcpyDeviceToHost, st));
-  CUF(cudaStreamSynchronize(st));
+  CU(cudaEventRecord(pp->ev[3], sc));
+  CU(cudaEventRecord(pp->ev_k, sc));
 
-  /* pass 3: results + HARQ state (softbuffer->cb_crc, sch.c:384,404-408; nof_iterations sch.c:420) */
-  const FecCbStatus *stt = (const FecCbStatus *)ctx->st_status.h;
-  itb = 0;
-  for (uint32_t i = 0; i < n; i++) {
-    fec_cuda_tb_t *t = &tbs[i];
-    tbplan_t *p = &plan[i];
+  /* ---- output stream: results back ---- */
+  CU(cudaStreamWaitEvent(sout, pp->ev_k, 0));
+  if (ncb) CU(cudaMemcpyAsync(pp->st_status.h, pp->st_status.d, sizeof(FecCbStatus) * ncb, cudaMemcpyDeviceToHost, sout));
+  CU(cudaMemcpyAsync(pp->st_ret.h, pp->st_ret.d, sizeof(int32_t) * ntb, cudaMemcpyDeviceToHost, sout));
+  if (!dev_io) CU(cudaMemcpyAsync(pp->st_data.h, pp->st_data.d, data_total, cudaMemcpyDeviceToHost, sout));
+  CU(cudaEventRecord(pp->ev_done, sout));
+  pp->ncb = ncb; pp->ntb = ntb; pp->data_total = data_total; pp->busy = 1;
+  return 0;
+}
+
+/* wait for a submitted sub-batch and unpack its results + HARQ state (softbuffer->cb_crc, sch.c:384,404-408;
+ * nof_iterations sch.c:420) */
+static int pipe_finish(fec_cuda_ctx_t *ctx, fec_pipe_t *pp)
+{
+  if (!pp->busy) return 0;
+  pp->busy = 0;
+  CU(cudaEventSynchronize(pp->ev_done));
+  for (int i = 0; i < 3; i++) { float ms = 0; if (cudaEventElapsedTime(&ms, pp->ev[i], pp->ev[i + 1]) == cudaSuccess) ctx->phase_ms[i] += ms; }
+  const FecCbStatus *stt = (const FecCbStatus *)pp->st_status.h;
+  const FecTbDesc *tbd = (const FecTbDesc *)pp->st_tbd.h;
+  uint32_t itb = 0;
+  for (uint32_t i = 0; i < pp->n; i++) {
+    fec_cuda_tb_t *t = &pp->tbs[i];
+    tbplan_t *p = &pp->plan[i];
     if (!p->valid) continue;
     const FecTbDesc *td = &tbd[itb];
     uint8_t *crc = p->chunk->cb_crc + (size_t)p->local * FEC_CUDA_MAX_CB;
@@ -452,16 +515,60 @@ extern "C" int fec_cuda_decode_tbs(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, uint
       t->cb_crc[cb] = crc[cb];
     }
     t->avg_its = sum / p->seg[1];
-    t->ret = ((const int32_t *)ctx->st_ret.h)[itb];
-    if (!dev_io) memcpy(t->data, (uint8_t *)ctx->st_data.h + p->data_off, (size_t)t->tbs / 8 + 3);
+    t->ret = ((const int32_t *)pp->st_ret.h)[itb];
+    if (!pp->dev_io) memcpy(t->data, (uint8_t *)pp->st_data.h + p->data_off, (size_t)t->tbs / 8 + 3);
     itb++;
   }
-  free(plan);
   return 0;
 }
 
+static int pipes_create(fec_cuda_ctx_t *ctx)
+{
+  ctx->pipes = (fec_pipe_t *)calloc(FEC_NPIPE, sizeof(fec_pipe_t));
+  if (!ctx->pipes) return -1;
+  for (int i = 0; i < FEC_NPIPE; i++) if (pipe_init(ctx, &ctx->pipes[i])) return -1;
+  if (cudaStreamCreateWithFlags(&ctx->s_copy, cudaStreamNonBlocking) != cudaSuccess || cudaStreamCreateWithFlags(&ctx->s_out, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&ctx->s_comp[1], cudaStreamNonBlocking) != cudaSuccess) return -1;
+  ctx->s_comp[0] = ctx->stream;
+  const char *sb = getenv("FEC_CUDA_SUB_TBS");
+  ctx->sub_tbs = sb ? (uint32_t)atoi(sb) : 296;
+  if (ctx->sub_tbs == 0) ctx->sub_tbs = 296;
+  return 0;
+}
+
+static void pipes_destroy(fec_cuda_ctx_t *ctx)
+{
+  if (!ctx->pipes) return;
+  for (int i = 0; i < FEC_NPIPE; i++) pipe_free(&ctx->pipes[i]);
+  free(ctx->pipes); ctx->pipes = NULL;
+  if (ctx->s_copy) cudaStreamDestroy(ctx->s_copy);
+  if (ctx->s_out) cudaStreamDestroy(ctx->s_out);
+  if (ctx->s_comp[1]) cudaStreamDestroy(ctx->s_comp[1]);
+}
+
+extern "C" int fec_cuda_decode_tbs(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, uint32_t n, uint32_t flags)
+{
+  if (!ctx || (!tbs && n)) return FEC_CUDA_EINVAL;
+  if (n == 0) return 0;
+  cudaSetDevice(ctx->device);
+  ctx->phase_ms[0] = ctx->phase_ms[1] = ctx->phase_ms[2] = 0; ctx->ev_valid = 1;
+  /* sub-batch size: big enough to fill the GPU for several waves, small enough to pipeline */
+  uint32_t nsub = (n + ctx->sub_tbs - 1) / ctx->sub_tbs;
+  const uint32_t per = (n + nsub - 1) / nsub;
+  int rc = 0;
+  uint32_t s = 0;
+  for (uint32_t off = 0; off < n && !rc; off += per, s++) {
+    fec_pipe_t *pp = &ctx->pipes[s % FEC_NPIPE];
+    rc = pipe_finish(ctx, pp);
+    if (!rc) rc = pipe_submit(ctx, pp, tbs + off, n - off < per ? n - off : per, flags, ctx->s_comp[s & 1]);
+  }
+  for (uint32_t i = 0; i < FEC_NPIPE; i++) { const int r2 = pipe_finish(ctx, &ctx->pipes[(s + i) % FEC_NPIPE]); if (!rc) rc = r2; }
+  return rc;
+}
+
 /* ---------------------------------------------------------------- bare code blocks (srslte_tdec_* level) ---- */
-#undef DBG_LLR
+#define CUF(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { free(plan); \
+  return fail(ctx, FEC_CUDA_ENODEV, "%s: %s", #call, cudaGetErrorString(e_)); } } while (0)
 #define DBG_LLR ctx->d_dbg
 extern "C" int fec_cuda_decode_cbs(fec_cuda_ctx_t *ctx, fec_cuda_cb_t *cbs, uint32_t n, uint32_t flags)
 {
@@ -518,7 +625,8 @@ extern "C" int fec_cuda_decode_cbs(fec_cuda_ctx_t *ctx, fec_cuda_cb_t *cbs, uint
   for (int k = 0; k < FEC_NOF_K; k++) {
     if (!grp_cnt[k]) continue;
     FecDecodeArgs a;
-    fill_decode_args(ctx, k, &a, grp_off[k], grp_cnt[k], DBG_LLR);
+    fill_decode_args(ctx, k, &a, (const FecCbDesc *)ctx->st_cbd.d, (FecCbStatus *)ctx->st_status.d, ctx->d_queue, ctx->d_softmax, ctx->d_exact,
+                     grp_off[k], grp_cnt[k], DBG_LLR);
     CUF(fec_launch_decode(a, ctx->sm_count, st));
     ctx->launches += a.exact_list ? 2 : 1;
   }

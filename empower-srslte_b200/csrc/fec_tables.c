@@ -12,8 +12,13 @@
 
 int fec_k_index(uint32_t K)
 {
-  for (int i = 0; i < FEC_NOF_K; i++) if (lte_qpp_table[i][0] >= K) return i;
-  return -1;
+  /* the 188 sizes are 40..512 step 8, 528..1024 step 16, 1056..2048 step 32, 2112..6144 step 64 (cbsegm.c:35-52) */
+  if (K > FEC_MAX_K) return -1;
+  if (K <= 40) return 0;
+  if (K <= 512) return (int)((K - 40 + 7) / 8);
+  if (K <= 1024) return 59 + (int)((K - 512 + 15) / 16);
+  if (K <= 2048) return 91 + (int)((K - 1024 + 31) / 32);
+  return 123 + (int)((K - 2048 + 63) / 64);
 }
 
 int fec_k_size(uint32_t idx) { return idx < FEC_NOF_K ? (int)lte_qpp_table[idx][0] : -1; }

@@ -109,6 +109,7 @@ __device__ __forceinline__ void pk_ck_load(uint32_t taddr, uint32_t *o)
 struct PkView {
   const uint32_t *Srow;    /* systematic pair row (HBM), read only when par == 0 */
   const uint32_t *Yrow;    /* parity pair row of this decoder */
+  const uint32_t *Ynext;   /* parity pair row of the other decoder (prefetch only) */
   const uint2    *Rrow;    /* CRC syndrome pair row of this decoder and polynomial */
   const uint16_t *Tlo, *Thi; /* smem: decoder-2 byte offsets into E of lanes 2j / 2j+1 at step k */
   uint32_t        Eb;      /* shared-memory byte address of this code block's extrinsic array E */
@@ -226,9 +227,16 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
                                                    const int16_t *tail, uint32_t *bits_lo, uint32_t *bits_hi, PkAcc &acc)
 {
   constexpr bool LODD = MODE == 2, VEC = MODE == 0;
-  const int nfull = L >> 3, rem = L & 7, nck = nfull + (rem ? 1 : 0);
+  const int nfull = L >> 3, rem = L & 7;
   uint32_t o[8], xs[8], alo[8], ahi[8], es[8];
   PkRaw raw, nraw;
+
+  /* pull this half-iteration's rows (first touch comes from HBM) and the next one's towards L2 */
+  for (int off = 0; off < L; off += 32) {
+    asm volatile("prefetch.global.L2 [%0];" :: "l"(v.Yrow + off));
+    asm volatile("prefetch.global.L2 [%0];" :: "l"(v.Ynext + off));
+    if (!v.par) asm volatile("prefetch.global.L2 [%0];" :: "l"(v.Srow + off));
+  }
 
   /* ---- beta warm-up over the first 40 symbols of both sub-blocks (turbodecoder_win.h:321-384) ---- */
 #pragma unroll
@@ -446,6 +454,7 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
     v.par = par;
     v.Srow = reinterpret_cast<const uint32_t *>(desc.soft) + j * Lp;
     v.Yrow = reinterpret_cast<const uint32_t *>(desc.soft + (1 + par) * SS) + j * Lp;
+    v.Ynext = reinterpret_cast<const uint32_t *>(desc.soft + (2 - par) * SS) + j * Lp;
     v.Rrow = a.pair_crc[desc.crc_sel] + (size_t)par * TPC * Lp + j * Lp;
     v.Tlo = Tlo + j * Lw; v.Thi = Thi + j * Lw;
     v.Eb = (uint32_t)__cvta_generic_to_shared(Eslot);
