@@ -21,6 +21,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", 
 MAX_CB = 13
 F_DEVICE_IO = 1
 F_NO_EARLY_STOP = 2
+F_SERIAL = 4
 
 
 class TbDesc(C.Structure):

@@ -59,7 +59,7 @@ struct fec_cuda_ctx {
   int           ev_valid;
   cudaStream_t  s_copy, s_out, s_comp[2];
   fec_pipe_t   *pipes;
-  uint32_t      sub_tbs;
+  uint32_t      sub_tbs, sub_tbs_dev;
 };
 
 static int pipes_create(fec_cuda_ctx_t *ctx);
@@ -533,6 +533,9 @@ static int pipes_create(fec_cuda_ctx_t *ctx)
   const char *sb = getenv("FEC_CUDA_SUB_TBS");
   ctx->sub_tbs = sb ? (uint32_t)atoi(sb) : 296;
   if (ctx->sub_tbs == 0) ctx->sub_tbs = 296;
+  sb = getenv("FEC_CUDA_SUB_TBS_DEV");
+  ctx->sub_tbs_dev = sb ? (uint32_t)atoi(sb) : 592;
+  if (ctx->sub_tbs_dev == 0) ctx->sub_tbs_dev = 592;
   return 0;
 }
 
@@ -553,7 +556,11 @@ extern "C" int fec_cuda_decode_tbs(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, uint
   cudaSetDevice(ctx->device);
   ctx->phase_ms[0] = ctx->phase_ms[1] = ctx->phase_ms[2] = 0; ctx->ev_valid = 1;
   /* sub-batch size: big enough to fill the GPU for several waves, small enough to pipeline */
-  uint32_t nsub = (n + ctx->sub_tbs - 1) / ctx->sub_tbs;
+  /* host buffers: small sub-batches so that the PCIe copy of one overlaps the kernels of the previous (the copy is
+   * the longer of the two); device buffers: nothing to overlap but host-side descriptor work, and every launch pays
+   * one ragged tail (the slowest code blocks run 8 half-iterations), so use few, large sub-batches */
+  const uint32_t sub = (flags & FEC_CUDA_F_DEVICE_IO) ? ctx->sub_tbs_dev : ctx->sub_tbs;
+  uint32_t nsub = (flags & FEC_CUDA_F_SERIAL) ? 1 : (n + sub - 1) / sub;
   const uint32_t per = (n + nsub - 1) / nsub;
   int rc = 0;
   uint32_t s = 0;

@@ -54,6 +54,27 @@ __device__ __forceinline__ void pk_sts_u16(uint32_t addr, uint32_t val)
   asm volatile("st.shared.u16 [%0], %1;" :: "r"(addr), "r"(val) : "memory");
 }
 
+/* global loads as volatile asm: ptxas otherwise sinks the prefetch loads down to their first use (register
+ * pressure heuristic), which collapses the software-pipelining distance to zero */
+__device__ __forceinline__ uint4 pk_ldg128(const void *p)
+{
+  uint4 r;
+  asm volatile("ld.global.nc.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ uint2 pk_ldg64(const void *p)
+{
+  uint2 r;
+  asm volatile("ld.global.nc.v2.u32 {%0, %1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ uint32_t pk_ldg32(const void *p)
+{
+  uint32_t r;
+  asm volatile("ld.global.nc.u32 %0, [%1];" : "=r"(r) : "l"(p));
+  return r;
+}
+
 /* turbodecoder_win.h:244-261: subtract state 0 from states 1..7, state 0 := 0 (every even k != 0) */
 __device__ __forceinline__ void pk_norm(uint32_t *o)
 {
@@ -97,11 +118,15 @@ __device__ __forceinline__ void pk_ck_store(uint32_t taddr, const uint32_t *o)
                :: "r"(taddr), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]), "r"(o[4]), "r"(o[5]), "r"(o[6]), "r"(o[7]) : "memory");
 }
 __device__ __forceinline__ void pk_ck_store_fence() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
-__device__ __forceinline__ void pk_ck_load(uint32_t taddr, uint32_t *o)
+__device__ __forceinline__ void pk_ck_load_issue(uint32_t taddr, uint32_t *o)
 {
   asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
                : "=r"(o[0]), "=r"(o[1]), "=r"(o[2]), "=r"(o[3]), "=r"(o[4]), "=r"(o[5]), "=r"(o[6]), "=r"(o[7]) : "r"(taddr) : "memory");
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void pk_ck_load_wait(uint32_t *o)
+{
+  /* the registers are tied to the wait so that no use can be scheduled above it */
+  asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(o[0]), "+r"(o[1]), "+r"(o[2]), "+r"(o[3]), "+r"(o[4]), "+r"(o[5]), "+r"(o[6]), "+r"(o[7]) :: "memory");
 }
 #endif
 
@@ -124,17 +149,33 @@ template <bool FULL, bool VEC>
 __device__ __forceinline__ void pk_load_raw(const PkView &v, int k0, int i0, PkRaw &r)
 {
   if (FULL && VEC) {
-    const uint4 y0 = __ldg(reinterpret_cast<const uint4 *>(v.Yrow + k0)), y1 = __ldg(reinterpret_cast<const uint4 *>(v.Yrow + k0 + 4));
+    const uint4 y0 = pk_ldg128(v.Yrow + k0), y1 = pk_ldg128(v.Yrow + k0 + 4);
     r.y[0] = y0.x; r.y[1] = y0.y; r.y[2] = y0.z; r.y[3] = y0.w; r.y[4] = y1.x; r.y[5] = y1.y; r.y[6] = y1.z; r.y[7] = y1.w;
     uint4 s0 = make_uint4(0, 0, 0, 0), s1 = s0;
-    if (!v.par) { s0 = __ldg(reinterpret_cast<const uint4 *>(v.Srow + k0)); s1 = __ldg(reinterpret_cast<const uint4 *>(v.Srow + k0 + 4)); }
+    if (!v.par) { s0 = pk_ldg128(v.Srow + k0); s1 = pk_ldg128(v.Srow + k0 + 4); }
     r.s[0] = s0.x; r.s[1] = s0.y; r.s[2] = s0.z; r.s[3] = s0.w; r.s[4] = s1.x; r.s[5] = s1.y; r.s[6] = s1.z; r.s[7] = s1.w;
   } else {
 #pragma unroll
     for (int i = 0; i < 8; i++) {
       r.s[i] = 0; r.y[i] = 0;
-      if (FULL || i >= i0) { r.y[i] = __ldg(v.Yrow + k0 + i); if (!v.par) r.s[i] = __ldg(v.Srow + k0 + i); }
+      if (FULL || i >= i0) { r.y[i] = pk_ldg32(v.Yrow + k0 + i); if (!v.par) r.s[i] = pk_ldg32(v.Srow + k0 + i); }
     }
+  }
+}
+
+/* CRC syndrome words of the chunk */
+template <bool FULL, bool VEC>
+__device__ __forceinline__ void pk_load_crc(const PkView &v, int k0, int i0, uint2 *rr)
+{
+  if (FULL && VEC) {
+#pragma unroll
+    for (int i = 0; i < 8; i += 2) {
+      const uint4 t = pk_ldg128(v.Rrow + k0 + i);
+      rr[i] = make_uint2(t.x, t.y); rr[i + 1] = make_uint2(t.z, t.w);
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; i++) { rr[i] = make_uint2(0, 0); if (FULL || i >= i0) rr[i] = pk_ldg64(v.Rrow + k0 + i); }
   }
 }
 
@@ -157,40 +198,44 @@ __device__ __forceinline__ void pk_finish_chunk(const PkView &v, int k0, int i0,
   }
 }
 
-/* 8 backward steps of the main pass (i = 7..0), checkpoint after step i = 0, normalisation on even k */
-template <bool FULL, bool LODD>
+/* Normalisation schedule of THIS kernel: every 4th step (after steps i = 4 and i = 0 going backward, i = 3 and
+ * i = 7 going forward) instead of the reference's every 2nd. Outputs (LLR = difference of two maxima over the
+ * same alpha/beta offsets) do not depend on when the common offset is removed as long as nothing overflows;
+ * with this schedule every sum stays within max(13 G, 10000 + 10 G). */
+
+/* 8 backward steps of the main pass (i = 7..0); the checkpoint is the NORMALISED state after step i = 0 */
+template <bool FULL>
 __device__ __forceinline__ void pk_beta_chunk(uint32_t *o, const uint32_t *xs, const uint32_t *ys, int i0, uint32_t ck_addr)
 {
 #pragma unroll
   for (int i = 7; i >= 0; i--) {
     if (FULL || i >= i0) {
       pk_beta(o, xs[i], ys[i]);
+      if ((i & 3) == 0) pk_norm(o);
       if (FULL && i == 0) pk_ck_store(ck_addr, o);
-      if (((i & 1) != 0) == LODD) pk_norm(o);        /* the step k = 0 is never followed by a use of o */
     }
   }
 }
 
 struct PkAcc { uint32_t crc, emx, emn, wlo, whi; };
 
-/* one chunk of the forward pass: recompute the inner betas from the checkpoint `ck` (= B[k0+8], stored value),
+/* one chunk of the forward pass: recompute the inner betas from the checkpoint `ck` (= normalised beta at k0+8),
  * then alpha recursion + LLR + extrinsic write-back + CRC syndrome + decision bits for steps i = i0..7 */
-template <bool FULL, bool LODD, bool SHIFT>
-__device__ __forceinline__ void pk_alpha_chunk(uint32_t *o, const uint32_t *ck, bool norm_ck, bool k0_nonzero, int i0,
+template <bool FULL, bool SHIFT>
+__device__ __forceinline__ void pk_alpha_chunk(uint32_t *o, const uint32_t *ck, int i0,
                                                const uint32_t *xs, const uint32_t *ys, const uint32_t *es,
                                                const uint32_t *alo, const uint32_t *ahi, const uint2 *rr, PkAcc &acc)
 {
   uint32_t b[8], bb[8][8], m[8], n[8];
 #pragma unroll
   for (int s = 0; s < 8; s++) b[s] = ck[s];
-  if (norm_ck) pk_norm(b);                           /* the normalisation that followed the store at step k0+8 */
 #pragma unroll
   for (int i = 7; i >= 1; i--) {
     if (FULL || i >= i0 + 1) {
       pk_beta(b, xs[i], ys[i]);
+      if (i == 4) pk_norm(b);
 #pragma unroll
       for (int s = 0; s < 8; s++) bb[i][s] = b[s];
-      if (((i & 1) != 0) == LODD) pk_norm(b);
     }
   }
 #pragma unroll
@@ -213,20 +258,18 @@ __device__ __forceinline__ void pk_alpha_chunk(uint32_t *o, const uint32_t *ck, 
       acc.wlo = __funnelshift_l(mlo, acc.wlo, 1); acc.whi = __funnelshift_l(mhi, acc.whi, 1);
 #pragma unroll
       for (int s = 0; s < 8; s++) o[s] = pk_max(m[s], n[s]);
-      if (((i & 1) != 0) == LODD) { if (FULL ? (i != 0 || k0_nonzero) : (i != i0)) pk_norm(o); }   /* no normalisation at k = 0 */
+      if ((i & 3) == 3) pk_norm(o);
     } else { acc.wlo <<= 1; acc.whi <<= 1; }
   }
 }
 
 /* One half-iteration of one constituent decoder for the two lanes of this thread.
- * TPC = threads per code block (P/2); MODE 0: L % 4 == 0 (16-byte loads), 1: L even, 2: L odd (the parity of L
- * fixes which steps of the main passes are normalised). Decisions go to bits_lo/bits_hi as MSB-first words; bit
- * k of a lane sits at bit index k + (8*nck - L) of its row. */
-template <int TPC, int MODE, bool SHIFT>
+ * TPC = threads per code block (P/2); VEC: L % 4 == 0 (16-byte loads). Decisions go to bits_lo/bits_hi as
+ * MSB-first words; bit k of a lane sits at bit index k + (8*nck - L) of its row. */
+template <int TPC, bool VEC, bool SHIFT>
 __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32_t tbase, unsigned gmask, int j,
                                                    const int16_t *tail, uint32_t *bits_lo, uint32_t *bits_hi, PkAcc &acc)
 {
-  constexpr bool LODD = MODE == 2, VEC = MODE == 0;
   const int nfull = L >> 3, rem = L & 7;
   uint32_t o[8], xs[8], alo[8], ahi[8], es[8];
   PkRaw raw, nraw;
@@ -240,7 +283,7 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
 
   /* ---- beta warm-up over the first 40 symbols of both sub-blocks (turbodecoder_win.h:321-384) ---- */
 #pragma unroll
-  for (int i = 0; i < 8; i++) o[i] = PK_NEG;
+  for (int i = 0; i < 8; i++) o[i] = 0;            /* the reference starts from 8 equal metrics (-10000): only differences matter */
   pk_load_raw<true, true>(v, 32, 0, raw);
   for (int c = 4; c >= 0; c--) {
     if (c > 0) pk_load_raw<true, true>(v, 8 * (c - 1), 0, nraw);
@@ -248,7 +291,7 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
 #pragma unroll
     for (int i = 7; i >= 0; i--) {
       pk_beta(o, xs[i], raw.y[i]);
-      if ((i & 1) == 0 && (i != 0 || c != 0)) pk_norm(o);
+      if ((i & 3) == 0) pk_norm(o);
     }
     raw = nraw;
   }
@@ -279,17 +322,21 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
       const uint32_t w = __shfl_down_sync(gmask, o[i], 1, TPC);
       o[i] = (j == TPC - 1) ? ((o[i] >> 16) | ((uint32_t)t[i] << 16)) : pk_prmt(o[i], w, 0x5432u);
     }
+    pk_norm(o);
   }
-  /* ---- beta main pass, chunks aligned from the top; checkpoint c = B[L-8c] (value BEFORE normalisation, :419-432) ---- */
+  /* ---- beta main pass, chunks aligned from the top; checkpoint c = normalised beta at k = L-8c ---- */
   pk_ck_store(tbase, o);
   {
     int k0 = L - PK_CH;
+    PkRaw n2raw;
     pk_load_raw<true, VEC>(v, k0, 0, raw);
+    if (nfull > 1) pk_load_raw<true, VEC>(v, k0 - PK_CH, 0, nraw);
+#pragma unroll 1
     for (int c = 0; c < nfull; c++, k0 -= PK_CH) {
-      if (c + 1 < nfull) pk_load_raw<true, VEC>(v, k0 - PK_CH, 0, nraw);
+      if (c + 2 < nfull) pk_load_raw<true, VEC>(v, k0 - 2 * PK_CH, 0, n2raw);      /* two chunks ahead: a beta chunk is shorter than an L2 hit */
       pk_finish_chunk<true>(v, k0, 0, raw, xs, alo, ahi, es);
-      pk_beta_chunk<true, LODD>(o, xs, raw.y, 0, tbase + 8 * (c + 1));
-      raw = nraw;
+      pk_beta_chunk<true>(o, xs, raw.y, 0, tbase + 8 * (c + 1));
+      raw = nraw; nraw = n2raw;
     }
     /* the bottom partial chunk only serves the (unused) end of the recursion: nothing to do */
   }
@@ -298,7 +345,7 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
   {
     uint32_t m[8], n[8];
 #pragma unroll
-    for (int i = 0; i < 8; i++) o[i] = PK_NEG;
+    for (int i = 0; i < 8; i++) o[i] = 0;
     pk_load_raw<true, VEC>(v, L - 40, 0, raw);
     for (int c = 0; c < 5; c++) {
       if (c < 4) pk_load_raw<true, VEC>(v, L - 40 + 8 * (c + 1), 0, nraw);
@@ -308,7 +355,7 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
         pk_alpha_branches(o, xs[i], raw.y[i], m, n);
 #pragma unroll
         for (int s = 0; s < 8; s++) o[s] = pk_max(m[s], n[s]);
-        if ((i & 1) == 0 && (i != 0 || c != 0)) pk_norm(o);
+        if ((i & 3) == 3) pk_norm(o);
       }
       raw = nraw;
     }
@@ -319,39 +366,35 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
     const uint32_t first = (i == 0) ? 0u : 0xD8F0u;
     o[i] = (j == 0) ? (first | (o[i] << 16)) : pk_prmt(w, o[i], 0x5432u);
   }
+  pk_norm(o);
   /* ---- alpha main pass, ascending k: bottom partial chunk (if any), then the full chunks ---- */
   acc.wlo = 0; acc.whi = 0;
   int wi = 0, cc = 0;
-  uint2 rr[8], nrr[8];
+  uint2 rr[8];
   uint32_t ck[8];
   if (rem) {
     const int k0 = rem - PK_CH, i0 = PK_CH - rem;
+    pk_ck_load_issue(tbase + 8 * nfull, ck);
     pk_load_raw<false, VEC>(v, k0, i0, raw);
-#pragma unroll
-    for (int i = 0; i < 8; i++) { rr[i] = make_uint2(0, 0); if (i >= i0) rr[i] = __ldg(v.Rrow + k0 + i); }
-    pk_ck_load(tbase + 8 * nfull, ck);
+    pk_load_crc<false, VEC>(v, k0, i0, rr);
     pk_finish_chunk<false>(v, k0, i0, raw, xs, alo, ahi, es);
-    pk_alpha_chunk<false, LODD, SHIFT>(o, ck, !LODD, true, i0, xs, raw.y, es, alo, ahi, rr, acc);
+    pk_ck_load_wait(ck);
+    pk_alpha_chunk<false, SHIFT>(o, ck, i0, xs, raw.y, es, alo, ahi, rr, acc);
     cc = 1;
   }
   {
     int k0 = rem;
     pk_load_raw<true, VEC>(v, k0, 0, raw);
-#pragma unroll
-    for (int i = 0; i < 8; i++) rr[i] = __ldg(v.Rrow + k0 + i);
+#pragma unroll 1
     for (int c = nfull - 1; c >= 0; c--, k0 += PK_CH, cc++) {
-      if (c > 0) {
-        pk_load_raw<true, VEC>(v, k0 + PK_CH, 0, nraw);
-#pragma unroll
-        for (int i = 0; i < 8; i++) nrr[i] = __ldg(v.Rrow + k0 + PK_CH + i);
-      }
-      pk_ck_load(tbase + 8 * c, ck);
+      pk_ck_load_issue(tbase + 8 * c, ck);
+      if (c > 0) pk_load_raw<true, VEC>(v, k0 + PK_CH, 0, nraw);
+      pk_load_crc<true, VEC>(v, k0, 0, rr);
       pk_finish_chunk<true>(v, k0, 0, raw, xs, alo, ahi, es);
-      pk_alpha_chunk<true, LODD, SHIFT>(o, ck, c > 0 && !LODD, k0 != 0, 0, xs, raw.y, es, alo, ahi, rr, acc);
+      pk_ck_load_wait(ck);
+      pk_alpha_chunk<true, SHIFT>(o, ck, 0, xs, raw.y, es, alo, ahi, rr, acc);
       if ((cc & 3) == 3) { bits_lo[wi] = acc.wlo; bits_hi[wi] = acc.whi; wi++; }
       raw = nraw;
-#pragma unroll
-      for (int i = 0; i < 8; i++) rr[i] = nrr[i];
     }
   }
   if (cc & 3) { const int sh = 32 - 8 * (cc & 3); bits_lo[wi] = acc.wlo << sh; bits_hi[wi] = acc.whi << sh; }
@@ -394,7 +437,7 @@ size_t fec_pk_smem_bytes(const fec_geom_t *g)
   return 4 * (tpc * g->Lw + nslots * (tpc * g->Lw + 1) + nslots * g->P * nw1);
 }
 
-template <int P, int MODE>
+template <int P, bool VEC>
 __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const FecDecodeArgs a)
 {
   constexpr int TPC = P / 2, CPW = 32 / TPC;
@@ -462,7 +505,7 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
     PkAcc acc;
     acc.crc = 0; acc.emx = 0x80008000u; acc.emn = 0x7FFF7FFFu;
     uint32_t *blo = rows + (2 * j) * nw1, *bhi = rows + (2 * j + 1) * nw1;
-    pk_half_iteration<TPC, MODE, P == 8>(v, L, tbase, gmask, j, desc.soft + 3 * SS + (par ? 6 : 0), blo, bhi, acc);
+    pk_half_iteration<TPC, VEC, P == 8>(v, L, tbase, gmask, j, desc.soft + 3 * SS + (par ? 6 : 0), blo, bhi, acc);
     uint32_t crc = acc.crc, emx = acc.emx, emn = acc.emn;
 #pragma unroll
     for (int s = TPC / 2; s > 0; s >>= 1) {
@@ -503,7 +546,7 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
         const int e0 = (short)(emx & 0xFFFFu), e1 = (short)(emx >> 16), e2 = -(int)(short)(emn & 0xFFFFu), e3 = -(int)(short)(emn >> 16);
         const uint32_t emax = (uint32_t)max(max(e0, e1), max(max(e2, e3), 0));
         const uint32_t bx = (n1 & 1) ? emax : emax + M;
-        if (bx + M > FEC_PK_GMAX) {
+        if (max(bx, M) + M > FEC_PK_GMAX) {
           if (j == 0) a.exact_list[atomicAdd(a.exact_count, 1u)] = (uint32_t)cb;   /* re-decoded from scratch by the exact kernel */
           cb = -1;
         } else n = n1;
@@ -519,10 +562,8 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
 template <int P>
 static cudaError_t pk_launch(const FecDecodeArgs &a, int grid, size_t smem, cudaStream_t st)
 {
-  const int L = a.g.L;
-  if ((L & 3) == 0)      fec_tdec_pk_kernel<P, 0><<<grid, FEC_PK_WARPS * 32, smem, st>>>(a);
-  else if ((L & 1) == 0) fec_tdec_pk_kernel<P, 1><<<grid, FEC_PK_WARPS * 32, smem, st>>>(a);
-  else                   fec_tdec_pk_kernel<P, 2><<<grid, FEC_PK_WARPS * 32, smem, st>>>(a);
+  if ((a.g.L & 3) == 0) fec_tdec_pk_kernel<P, true><<<grid, FEC_PK_WARPS * 32, smem, st>>>(a);
+  else                  fec_tdec_pk_kernel<P, false><<<grid, FEC_PK_WARPS * 32, smem, st>>>(a);
   return cudaGetLastError();
 }
 
@@ -536,18 +577,16 @@ cudaError_t fec_launch_decode_packed(const FecDecodeArgs &a, int sm_count, cudaS
   return a.g.P == 16 ? pk_launch<16>(a, grid, smem, st) : pk_launch<8>(a, grid, smem, st);
 }
 
-template <int P, int MODE> static cudaError_t pk_attr()
+template <int P, bool VEC> static cudaError_t pk_attr()
 {
-  return cudaFuncSetAttribute(fec_tdec_pk_kernel<P, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+  return cudaFuncSetAttribute(fec_tdec_pk_kernel<P, VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
 }
 
 cudaError_t fec_pk_init(void)
 {
   cudaError_t e;
-  if ((e = pk_attr<16, 0>()) != cudaSuccess) return e;
-  if ((e = pk_attr<16, 1>()) != cudaSuccess) return e;
-  if ((e = pk_attr<16, 2>()) != cudaSuccess) return e;
-  if ((e = pk_attr<8, 0>()) != cudaSuccess) return e;
-  if ((e = pk_attr<8, 1>()) != cudaSuccess) return e;
-  return pk_attr<8, 2>();
+  if ((e = pk_attr<16, true>()) != cudaSuccess) return e;
+  if ((e = pk_attr<16, false>()) != cudaSuccess) return e;
+  if ((e = pk_attr<8, true>()) != cudaSuccess) return e;
+  return pk_attr<8, false>();
 }

@@ -34,6 +34,8 @@ extern "C" {
 /* flags for fec_cuda_decode_tbs */
 #define FEC_CUDA_F_DEVICE_IO      1u       /* e_bits / data are DEVICE pointers; nothing bulk crosses PCIe */
 #define FEC_CUDA_F_NO_EARLY_STOP  2u       /* run exactly max_its half-iterations (srslte_tdec_run_all semantics) */
+#define FEC_CUDA_F_SERIAL         4u       /* do not cut the call into pipelined sub-batches: one launch per kernel, so that
+                                              fec_cuda_last_phase_ms reports un-overlapped kernel durations (profiling) */
 
 typedef struct fec_cuda_ctx fec_cuda_ctx_t;
 
@@ -81,8 +83,9 @@ const char *fec_cuda_last_error(fec_cuda_ctx_t *ctx);
 void *fec_cuda_stream(fec_cuda_ctx_t *ctx);
 /* number of kernels launched by this context so far */
 uint64_t fec_cuda_launch_count(fec_cuda_ctx_t *ctx);
-/* device time (CUDA events on the context's stream) of the three phases of the LAST fec_cuda_decode_tbs call:
- * out3 = { rate de-matching, turbo decode (all K groups), TB assembly + CRC24A } in milliseconds */
+/* device time (CUDA events on the compute streams) of the three phases of the LAST fec_cuda_decode_tbs call, summed over
+ * its sub-batches: out3 = { rate de-matching, turbo decode (all K groups), TB assembly + CRC24A } in milliseconds.
+ * Sub-batches overlap on two streams; use FEC_CUDA_F_SERIAL for un-overlapped kernel durations. */
 int  fec_cuda_last_phase_ms(fec_cuda_ctx_t *ctx, float out3[3]);
 
 /* Pinned (page-locked) host memory for e_bits / data buffers: replaces srslte_vec_malloc

@@ -56,6 +56,29 @@ def test_tdec_saturation_vs_oracle(fec, orc):
                 assert (r["out"] == ob[nof - 1]).all(), (K, amp, nof)
 
 
+def test_tdec_at_range_bound_vs_oracle(fec, orc):
+    """inputs sitting exactly on the packed kernel's range condition (max|soft| = GMAX/2 = 1000, adversarial
+    sign patterns): the fast path must still be bit-exact; later half-iterations exercise the hand-over"""
+    Ks, llrs, want = [], [], []
+    for K in (408, 800, 816, 1008, 5824, 6144):
+        n = 3 * K + 12
+        r = np.random.default_rng(K)
+        pats = [np.full(n, 1000), np.full(n, -1000), np.where(np.arange(n) % 2 == 0, 1000, -1000),
+                np.where((np.arange(n) // 3) % 2 == 0, 1000, -1000), 1000 * (r.integers(0, 2, n) * 2 - 1),
+                np.where(np.arange(n) % 3 == 0, 1000, -1000), r.integers(-1000, 1001, n), 500 * (r.integers(0, 2, n) * 2 - 1)]
+        for pt in pats:
+            inp = np.ascontiguousarray(pt, dtype=np.int16)
+            ob = np.zeros((3, K // 8), np.uint8)
+            assert orc.orc_tdec_halfits(K, P(inp), 3, P(ob), None) == 0
+            for nof in (1, 2, 3):
+                Ks.append(K); llrs.append(inp); want.append((nof, ob[nof - 1].copy()))
+    for nof in (1, 2, 3):
+        sel = [i for i, w in enumerate(want) if w[0] == nof]
+        res = fec.decode_cbs([Ks[i] for i in sel], [llrs[i] for i in sel], nof, early_stop=False)
+        bad = [(Ks[i], nof) for i, r in zip(sel, res) if not (r["out"] == want[i][1]).all()]
+        assert not bad, bad
+
+
 def test_rm_rx_golden_subset(fec):
     z = G.tables()
     rows = [r for r in z["rm"] if int(r[0]) in (40, 104, 400, 408, 800, 816, 1024, 3136, 5824, 6144)]
