@@ -13,7 +13,7 @@ import subprocess
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libsrslte_fec_cuda.so")
+LIB_PATH = os.environ.get("FEC_CUDA_LIB") or os.path.join(HERE, "libsrslte_fec_cuda.so")   # FEC_CUDA_LIB: tuning builds (tools/variants.sh)
 CSRC = os.path.join(HERE, "csrc")
 SOURCES = ["fec_kernels.cu", "fec_tdec_packed.cu", "fec_cuda_api.cu", "fec_compat.cu", "fec_tables.c"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-Xcompiler", "-fPIC", "-shared"]

@@ -98,15 +98,20 @@ struct WinLane {           /* per-lane view of one half-iteration */
   const uint32_t *T;       /* step table of this lane and parity */
   int16_t        *E;       /* extrinsic array of this code block (shared memory) */
   int             smask;   /* -1: x = sat(S + E) (decoder 1);  0: x = E (decoder 2) */
+  int             tpc, dj, dh; /* pairs per code block, pair index and half of this lane */
 };
+
+/* int16 offset of (lane d, step k) inside one stream of the device layout (fec_tables.h) */
+__device__ __forceinline__ int win_widx(const WinLane &w, int k) { return 2 * ((((k >> 2) * w.tpc + w.dj) << 2) + (k & 3)) + w.dh; }
 
 __device__ __forceinline__ void win_load_xy(const WinLane &w, int k, int &x, int &y)
 {
   const uint32_t t = __ldg(w.T + k);
   const int e = w.E[t & 0xFFFFu];
-  const int s = (int)__ldg(w.S + 2 * k) & w.smask;
+  const int wi = win_widx(w, k);
+  const int s = (int)__ldg(w.S + wi) & w.smask;
   x = sat16(s + e);
-  y = (int)__ldg(w.Y + 2 * k);
+  y = (int)__ldg(w.Y + wi);
 }
 
 size_t fec_win_smem_bytes(const fec_geom_t *g, uint32_t slots)
@@ -177,8 +182,9 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 1) fec_tdec_win_kernel(const 
       const FecCbDesc desc = a.cbs[cb];
       const int n = s_n[slot], par = n & 1;
       WinLane w;
-      w.S = desc.soft + (d >> 1) * 2 * Lp + (d & 1);              /* pair-row layout: lane d, step k at row[2k + (d&1)] */
-      w.Y = desc.soft + (1 + par) * SS + (d >> 1) * 2 * Lp + (d & 1);
+      w.S = desc.soft;
+      w.Y = desc.soft + (1 + par) * SS;
+      w.tpc = P / 2; w.dj = d >> 1; w.dh = d & 1;
       w.T = a.step_tab + par * SS + d * Lp;
       w.E = E;
       w.smask = par ? 0 : -1;
@@ -267,8 +273,8 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 1) fec_tdec_win_kernel(const 
           const uint32_t t = __ldg(w.T + k);
           const int ea = t & 0xFFFFu, nat = t >> 16;
           const int e = w.E[ea];
-          x = sat16(((int)__ldg(w.S + 2 * k) & w.smask) + e);
-          y = (int)__ldg(w.Y + 2 * k);
+          x = sat16(((int)__ldg(w.S + win_widx(w, k)) & w.smask) + e);
+          y = (int)__ldg(w.Y + win_widx(w, k));
           win_alpha_branches(o, x, y, m, nb);
           int b[8], v0[8], v1[8];
           unpack8_true((k == khi - 1) ? ck : chunk[(k - klo) * nthr + tid], b);
@@ -552,7 +558,7 @@ __global__ void __launch_bounds__(256) fec_extract_kernel(const FecExtractDesc *
     else {
       const int s = o / d.g.SS, r = o % d.g.SS;
       int lane, k;
-      if (d.g.P) { lane = 2 * (r / (2 * d.g.Lp)) + (r & 1); k = (r % (2 * d.g.Lp)) >> 1; }
+      if (d.g.P) { const int wd = r >> 1, tpc = d.g.P / 2; lane = 2 * ((wd >> 2) % tpc) + (r & 1); k = ((wd >> 2) / tpc) * 4 + (wd & 3); }
       else { lane = 0; k = r; }
       if (k < d.g.L) v = d.in[3 * (lane * d.g.L + k) + s];
     }
@@ -580,7 +586,7 @@ __global__ void fec_soft_to_ref_kernel(const int16_t *dev, int16_t *ref, fec_geo
     if (t >= 3 * g.K) { od = 3 * g.SS + (t - 3 * g.K); orf = (sb && g.P) ? 3 * (g.K + 32) + (t - 3 * g.K) : t; }
     else {
       const int s = t % 3, x = t / 3, dl = x / g.L, kk = x % g.L;
-      od = g.P ? s * g.SS + (dl >> 1) * 2 * g.Lp + 2 * kk + (dl & 1) : s * g.SS + kk;
+      od = g.P ? s * g.SS + 2 * ((((kk >> 2) * (g.P / 2) + (dl >> 1)) << 2) + (kk & 3)) + (dl & 1) : s * g.SS + kk;
       orf = (sb && g.P) ? s * (g.K + 32) + (x % g.L) * g.P + x / g.L : t;
     }
     ref[orf] = dev[od];

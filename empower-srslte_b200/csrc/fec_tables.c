@@ -110,7 +110,7 @@ void fec_gen_pair_crc_table(const fec_geom_t *g, uint32_t poly, uint32_t *tab)
     for (int j = 0; j < g->P / 2; j++)
       for (int k = 0; k < L; k++)
         for (int h = 0; h < 2; h++)
-          tab[2 * ((size_t)par * rows + (size_t)j * g->Lp + k) + h] = R[K - 1 - qpp_nat(g, par, (2 * j + h) * L + k)];
+          tab[2 * ((size_t)par * rows + (size_t)(((k >> 1) * (g->P / 2) + j) * 2 + (k & 1))) + h] = R[K - 1 - qpp_nat(g, par, (2 * j + h) * L + k)];
   free(R);
 }
 
@@ -122,7 +122,7 @@ int fec_soft_offset_dev(const fec_geom_t *g, int t)
   if (t >= 3 * g->K) return 3 * g->SS + (t - 3 * g->K);
   int s = t % 3, x = t / 3, d = x / g->L, k = x % g->L;
   if (g->P == 0) return s * g->SS + k;
-  return s * g->SS + (d >> 1) * 2 * g->Lp + 2 * k + (d & 1);
+  return s * g->SS + 2 * ((((k >> 2) * (g->P / 2) + (d >> 1)) << 2) + (k & 3)) + (d & 1);
 }
 
 int fec_soft_offset_ref(const fec_geom_t *g, int t, int sb_layout)

@@ -17,9 +17,11 @@ extern "C" {
 
 /* Device layout of one code block ("geometry"). The reference's sub-block-interleaved soft buffer
  * (rm_turbo.c:250-264: element k of sub-block d at k*P+d) becomes, on the device, PAIR rows: sub-blocks
- * (lanes) 2j and 2j+1 share one row of Lp 32-bit words, word k = (lane 2j | lane 2j+1 << 16) at step k, so
- * that one thread walks two sub-blocks with packed s16x2 arithmetic and 16-byte loads:
- *   stream s (0 syst, 1 parity, 2 parity'), lane d, step k  ->  int16 index s*SS + (d>>1)*2*Lp + 2*k + (d&1)
+ * (lanes) 2j and 2j+1 share 32-bit words (lane 2j | lane 2j+1 << 16), so that one thread walks two sub-blocks
+ * with packed s16x2 arithmetic; the words of the P/2 pairs are interleaved in groups of 4 steps, so that the
+ * 16-byte loads of the P/2 threads of a code block fall into ONE 128-byte line (coalesced):
+ *   stream s (0 syst, 1 parity, 2 parity'), lane d, step k  ->  word W = ((k>>2)*(P/2) + (d>>1))*4 + (k&3),
+ *   int16 index s*SS + 2*W + (d&1)
  *   (non-windowed class P=0: one lane, index s*SS + k);  12 tail LLRs at 3*SS.
  * Exact (32-bit) kernels keep the extrinsic array E in shared memory with lane stride LpE (LpE/2 odd:
  * conflict-free gathers); the packed kernel keeps E in pair rows of Lw words (Lw mod 8 == 4). */
@@ -47,7 +49,8 @@ void fec_gen_step_table(const fec_geom_t *g, uint32_t *tab);
 /* packed kernel: address table of the INTERLEAVED decoder, (P/2) x Lp words: (E halfword index of lane 2j+1) << 16
  * | (E halfword index of lane 2j) at step k, E halfword index of natural bit (d',k') = 2*((d'>>1)*Lw + k') + (d'&1) */
 void fec_gen_pair_addr_table(const fec_geom_t *g, uint32_t *tab);
-/* packed kernel: CRC syndrome words per pair-step, [2 parities][(P/2) x Lp] uint2 = {R of lane 2j's bit, R of lane 2j+1's bit}
+/* packed kernel: CRC syndrome words per pair-step, [2 parities][(P/2) x Lp] uint2 = {R of lane 2j's bit, R of lane 2j+1's bit},
+ * pair j, step k at uint2 index ((k>>1)*(P/2) + j)*2 + (k&1) (two steps = one 16-byte load, P/2 threads = one line),
  * with R = x^(K-1-nat+24) mod g(x) of the natural position decided at that step; crc_sel picks the polynomial */
 void fec_gen_pair_crc_table(const fec_geom_t *g, uint32_t poly, uint32_t *tab);
 /* rate-matching rank table in device soft-buffer layout (3*SS+16 entries, pad = 0xFFFF) and the 4 rv

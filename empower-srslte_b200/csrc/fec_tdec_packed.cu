@@ -29,6 +29,16 @@
 #ifndef FEC_PK_TMEM
 #define FEC_PK_TMEM 1
 #endif
+/* tuning switches (A/B-measured on B200, see profiles/): */
+#ifndef PK_BETA16
+#define PK_BETA16 1      /* beta main pass: 16 steps per loop iteration */
+#endif
+#ifndef PK_NRR
+#define PK_NRR 0         /* alpha pass: CRC syndrome words loaded one chunk ahead */
+#endif
+#ifndef PK_KEEP_ADDR
+#define PK_KEEP_ADDR 0   /* keep the 16 E addresses of a chunk in registers instead of recomputing them at write-back */
+#endif
 
 /* ---------------------------------------------------------------- packed helpers ---- */
 __device__ __forceinline__ uint32_t pk_add(uint32_t a, uint32_t b) { return __vadd2(a, b); }
@@ -132,10 +142,12 @@ __device__ __forceinline__ void pk_ck_load_wait(uint32_t *o)
 
 /* ---------------------------------------------------------------- per-thread view of one half-iteration ---- */
 struct PkView {
-  const uint32_t *Srow;    /* systematic pair row (HBM), read only when par == 0 */
-  const uint32_t *Yrow;    /* parity pair row of this decoder */
-  const uint32_t *Ynext;   /* parity pair row of the other decoder (prefetch only) */
-  const uint2    *Rrow;    /* CRC syndrome pair row of this decoder and polynomial */
+  const uint32_t *Srow;    /* systematic stream of the code block + 4*j words (HBM), read only when par == 0; step k of this
+                              thread's pair sits at word (k>>2)*4*TPC + (k&3) from here (fec_tables.h) */
+  const uint32_t *Yrow;    /* parity stream of this decoder, same addressing */
+  const uint32_t *Ynext;   /* parity stream of the other decoder (prefetch only) */
+  const uint2    *Rrow;    /* CRC syndrome words of this decoder and polynomial + 2*j; step k at (k>>1)*2*TPC + (k&1) */
+  int             tpc4;    /* 4*TPC */
   const uint16_t *Tlo, *Thi; /* smem: decoder-2 byte offsets into E of lanes 2j / 2j+1 at step k */
   uint32_t        Eb;      /* shared-memory byte address of this code block's extrinsic array E */
   uint32_t        ident;   /* decoder-1 byte offset of lane 2j at step 0: 4*j*Lw (lane 2j+1: +2; step k: +4k) */
@@ -149,16 +161,20 @@ template <bool FULL, bool VEC>
 __device__ __forceinline__ void pk_load_raw(const PkView &v, int k0, int i0, PkRaw &r)
 {
   if (FULL && VEC) {
-    const uint4 y0 = pk_ldg128(v.Yrow + k0), y1 = pk_ldg128(v.Yrow + k0 + 4);
+    const int w0 = (k0 >> 2) * v.tpc4;
+    const uint4 y0 = pk_ldg128(v.Yrow + w0), y1 = pk_ldg128(v.Yrow + w0 + v.tpc4);
     r.y[0] = y0.x; r.y[1] = y0.y; r.y[2] = y0.z; r.y[3] = y0.w; r.y[4] = y1.x; r.y[5] = y1.y; r.y[6] = y1.z; r.y[7] = y1.w;
     uint4 s0 = make_uint4(0, 0, 0, 0), s1 = s0;
-    if (!v.par) { s0 = pk_ldg128(v.Srow + k0); s1 = pk_ldg128(v.Srow + k0 + 4); }
+    if (!v.par) { s0 = pk_ldg128(v.Srow + w0); s1 = pk_ldg128(v.Srow + w0 + v.tpc4); }
     r.s[0] = s0.x; r.s[1] = s0.y; r.s[2] = s0.z; r.s[3] = s0.w; r.s[4] = s1.x; r.s[5] = s1.y; r.s[6] = s1.z; r.s[7] = s1.w;
   } else {
 #pragma unroll
     for (int i = 0; i < 8; i++) {
       r.s[i] = 0; r.y[i] = 0;
-      if (FULL || i >= i0) { r.y[i] = pk_ldg32(v.Yrow + k0 + i); if (!v.par) r.s[i] = pk_ldg32(v.Srow + k0 + i); }
+      if (FULL || i >= i0) {
+        const int k = k0 + i, w = (k >> 2) * v.tpc4 + (k & 3);
+        r.y[i] = pk_ldg32(v.Yrow + w); if (!v.par) r.s[i] = pk_ldg32(v.Srow + w);
+      }
     }
   }
 }
@@ -170,28 +186,39 @@ __device__ __forceinline__ void pk_load_crc(const PkView &v, int k0, int i0, uin
   if (FULL && VEC) {
 #pragma unroll
     for (int i = 0; i < 8; i += 2) {
-      const uint4 t = pk_ldg128(v.Rrow + k0 + i);
+      const uint4 t = pk_ldg128(v.Rrow + ((k0 + i) >> 1) * (v.tpc4 >> 1));
       rr[i] = make_uint2(t.x, t.y); rr[i + 1] = make_uint2(t.z, t.w);
     }
   } else {
 #pragma unroll
-    for (int i = 0; i < 8; i++) { rr[i] = make_uint2(0, 0); if (FULL || i >= i0) rr[i] = pk_ldg64(v.Rrow + k0 + i); }
+    for (int i = 0; i < 8; i++) {
+      rr[i] = make_uint2(0, 0);
+      if (FULL || i >= i0) { const int k = k0 + i; rr[i] = pk_ldg64(v.Rrow + (k >> 1) * (v.tpc4 >> 1) + (k & 1)); }
+    }
   }
 }
 
-/* E byte addresses of the two lanes at each step + apriori gather + x = systematic + apriori */
+/* E byte addresses of the two lanes at step k (decoder 2: table in shared memory; decoder 1: own pair row) */
+__device__ __forceinline__ void pk_eaddr(const PkView &v, int k, uint32_t &alo, uint32_t &ahi)
+{
+  uint32_t ol, oh;
+  if (v.par) { ol = v.Tlo[k]; oh = v.Thi[k]; } else { ol = v.ident + 4u * (uint32_t)k; oh = ol + 2u; }
+  alo = v.Eb + ol; ahi = v.Eb + oh;
+}
+
+/* apriori gather + x = systematic + apriori for the chunk (addresses are recomputed at write-back time:
+ * two more LSU/FMA-pipe instructions per step instead of 16 live registers) */
 template <bool FULL>
-__device__ __forceinline__ void pk_finish_chunk(const PkView &v, int k0, int i0, const PkRaw &r, uint32_t *xs, uint32_t *alo, uint32_t *ahi, uint32_t *es)
+__device__ __forceinline__ void pk_finish_chunk(const PkView &v, int k0, int i0, const PkRaw &r, uint32_t *xs, uint32_t *es, uint32_t *ka = nullptr)
 {
 #pragma unroll
   for (int i = 0; i < 8; i++) {
-    xs[i] = 0; alo[i] = v.Eb; ahi[i] = v.Eb; es[i] = 0;
+    xs[i] = 0; es[i] = 0;
     if (FULL || i >= i0) {
-      const int k = k0 + i;
-      uint32_t ol, oh;
-      if (v.par) { ol = v.Tlo[k]; oh = v.Thi[k]; } else { ol = v.ident + 4u * (uint32_t)k; oh = ol + 2u; }
-      alo[i] = v.Eb + ol; ahi[i] = v.Eb + oh;
-      const uint32_t e = pk_prmt(pk_lds_u16(alo[i]), pk_lds_u16(ahi[i]), 0x5410u);
+      uint32_t alo, ahi;
+      pk_eaddr(v, k0 + i, alo, ahi);
+      if (PK_KEEP_ADDR && ka) { ka[2 * i] = alo; ka[2 * i + 1] = ahi; }
+      const uint32_t e = pk_prmt(pk_lds_u16(alo), pk_lds_u16(ahi), 0x5410u);
       es[i] = e;
       xs[i] = pk_add(r.s[i], e);
     }
@@ -222,9 +249,9 @@ struct PkAcc { uint32_t crc, emx, emn, wlo, whi; };
 /* one chunk of the forward pass: recompute the inner betas from the checkpoint `ck` (= normalised beta at k0+8),
  * then alpha recursion + LLR + extrinsic write-back + CRC syndrome + decision bits for steps i = i0..7 */
 template <bool FULL, bool SHIFT>
-__device__ __forceinline__ void pk_alpha_chunk(uint32_t *o, const uint32_t *ck, int i0,
+__device__ __forceinline__ void pk_alpha_chunk(const PkView &v, int k0, uint32_t *o, const uint32_t *ck, int i0,
                                                const uint32_t *xs, const uint32_t *ys, const uint32_t *es,
-                                               const uint32_t *alo, const uint32_t *ahi, const uint2 *rr, PkAcc &acc)
+                                               const uint2 *rr, PkAcc &acc, const uint32_t *ka)
 {
   uint32_t b[8], bb[8][8], m[8], n[8];
 #pragma unroll
@@ -249,8 +276,10 @@ __device__ __forceinline__ void pk_alpha_chunk(uint32_t *o, const uint32_t *ck, 
       uint32_t r = pk_sub(m1, m0);
       if (SHIFT) r = ((r >> 1) & 0x7FFF7FFFu) | (r & 0x80008000u);        /* divide_output, sse16 only (:61,565) */
       const uint32_t en = pk_sub(r, es[i]);                                /* next apriori = LLR - what this decoder was given */
-      pk_sts_u16(alo[i], en);
-      pk_sts_u16(ahi[i], en >> 16);
+      uint32_t alo, ahi;
+      if (PK_KEEP_ADDR) { alo = ka[2 * i]; ahi = ka[2 * i + 1]; } else pk_eaddr(v, k0 + i, alo, ahi);
+      pk_sts_u16(alo, en);
+      pk_sts_u16(ahi, en >> 16);
       acc.emx = pk_max(acc.emx, en); acc.emn = pk_min(acc.emn, en);
       const uint32_t nr = pk_sub(0u, r);                                   /* sign set <=> LLR > 0 <=> bit 1 */
       const uint32_t mlo = pk_prmt(nr, 0u, 0x9999u), mhi = pk_prmt(nr, 0u, 0xBBBBu);
@@ -271,11 +300,11 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
                                                    const int16_t *tail, uint32_t *bits_lo, uint32_t *bits_hi, PkAcc &acc)
 {
   const int nfull = L >> 3, rem = L & 7;
-  uint32_t o[8], xs[8], alo[8], ahi[8], es[8];
+  uint32_t o[8], xs[8], es[8], ka[16];
   PkRaw raw, nraw;
 
   /* pull this half-iteration's rows (first touch comes from HBM) and the next one's towards L2 */
-  for (int off = 0; off < L; off += 32) {
+  for (int off = j * 28; off < L * TPC; off += TPC * 32) {      /* each of the TPC threads takes every TPC-th 128-byte line */
     asm volatile("prefetch.global.L2 [%0];" :: "l"(v.Yrow + off));
     asm volatile("prefetch.global.L2 [%0];" :: "l"(v.Ynext + off));
     if (!v.par) asm volatile("prefetch.global.L2 [%0];" :: "l"(v.Srow + off));
@@ -287,7 +316,7 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
   pk_load_raw<true, true>(v, 32, 0, raw);
   for (int c = 4; c >= 0; c--) {
     if (c > 0) pk_load_raw<true, true>(v, 8 * (c - 1), 0, nraw);
-    pk_finish_chunk<true>(v, 8 * c, 0, raw, xs, alo, ahi, es);
+    pk_finish_chunk<true>(v, 8 * c, 0, raw, xs, es);
 #pragma unroll
     for (int i = 7; i >= 0; i--) {
       pk_beta(o, xs[i], raw.y[i]);
@@ -327,16 +356,37 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
   /* ---- beta main pass, chunks aligned from the top; checkpoint c = normalised beta at k = L-8c ---- */
   pk_ck_store(tbase, o);
   {
-    int k0 = L - PK_CH;
+    /* two chunks (16 steps) per iteration, the loads of the next 16 steps issued first: a single beta chunk is
+     * shorter than an L2 hit, and the register rotation at the end of the body has to wait for those loads */
+    int k0 = L - PK_CH, c = 0;
+    PkRaw rawB, nrawB;
+#if !PK_BETA16
     PkRaw n2raw;
     pk_load_raw<true, VEC>(v, k0, 0, raw);
     if (nfull > 1) pk_load_raw<true, VEC>(v, k0 - PK_CH, 0, nraw);
 #pragma unroll 1
-    for (int c = 0; c < nfull; c++, k0 -= PK_CH) {
-      if (c + 2 < nfull) pk_load_raw<true, VEC>(v, k0 - 2 * PK_CH, 0, n2raw);      /* two chunks ahead: a beta chunk is shorter than an L2 hit */
-      pk_finish_chunk<true>(v, k0, 0, raw, xs, alo, ahi, es);
+    for (; c < nfull; c++, k0 -= PK_CH) {
+      if (c + 2 < nfull) pk_load_raw<true, VEC>(v, k0 - 2 * PK_CH, 0, n2raw);
+      pk_finish_chunk<true>(v, k0, 0, raw, xs, es);
       pk_beta_chunk<true>(o, xs, raw.y, 0, tbase + 8 * (c + 1));
       raw = nraw; nraw = n2raw;
+    }
+#endif
+    if (PK_BETA16 && (nfull & 1)) {
+      pk_load_raw<true, VEC>(v, k0, 0, raw);
+      pk_finish_chunk<true>(v, k0, 0, raw, xs, es);
+      pk_beta_chunk<true>(o, xs, raw.y, 0, tbase + 8);
+      k0 -= PK_CH; c = 1;
+    }
+    if (PK_BETA16 && c < nfull) { pk_load_raw<true, VEC>(v, k0, 0, raw); pk_load_raw<true, VEC>(v, k0 - PK_CH, 0, rawB); }
+#pragma unroll 1
+    for (; c < nfull; c += 2, k0 -= 2 * PK_CH) {
+      if (c + 2 < nfull) { pk_load_raw<true, VEC>(v, k0 - 2 * PK_CH, 0, nraw); pk_load_raw<true, VEC>(v, k0 - 3 * PK_CH, 0, nrawB); }
+      pk_finish_chunk<true>(v, k0, 0, raw, xs, es);
+      pk_beta_chunk<true>(o, xs, raw.y, 0, tbase + 8 * (c + 1));
+      pk_finish_chunk<true>(v, k0 - PK_CH, 0, rawB, xs, es);
+      pk_beta_chunk<true>(o, xs, rawB.y, 0, tbase + 8 * (c + 2));
+      raw = nraw; rawB = nrawB;
     }
     /* the bottom partial chunk only serves the (unused) end of the recursion: nothing to do */
   }
@@ -349,7 +399,7 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
     pk_load_raw<true, VEC>(v, L - 40, 0, raw);
     for (int c = 0; c < 5; c++) {
       if (c < 4) pk_load_raw<true, VEC>(v, L - 40 + 8 * (c + 1), 0, nraw);
-      pk_finish_chunk<true>(v, L - 40 + 8 * c, 0, raw, xs, alo, ahi, es);
+      pk_finish_chunk<true>(v, L - 40 + 8 * c, 0, raw, xs, es);
 #pragma unroll
       for (int i = 0; i < 8; i++) {
         pk_alpha_branches(o, xs[i], raw.y[i], m, n);
@@ -377,24 +427,30 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
     pk_ck_load_issue(tbase + 8 * nfull, ck);
     pk_load_raw<false, VEC>(v, k0, i0, raw);
     pk_load_crc<false, VEC>(v, k0, i0, rr);
-    pk_finish_chunk<false>(v, k0, i0, raw, xs, alo, ahi, es);
+    pk_finish_chunk<false>(v, k0, i0, raw, xs, es, ka);
     pk_ck_load_wait(ck);
-    pk_alpha_chunk<false, SHIFT>(o, ck, i0, xs, raw.y, es, alo, ahi, rr, acc);
+    pk_alpha_chunk<false, SHIFT>(v, k0, o, ck, i0, xs, raw.y, es, rr, acc, ka);
     cc = 1;
   }
   {
     int k0 = rem;
+    uint2 nrr[8];
     pk_load_raw<true, VEC>(v, k0, 0, raw);
+    pk_load_crc<true, VEC>(v, k0, 0, rr);
 #pragma unroll 1
     for (int c = nfull - 1; c >= 0; c--, k0 += PK_CH, cc++) {
       pk_ck_load_issue(tbase + 8 * c, ck);
-      if (c > 0) pk_load_raw<true, VEC>(v, k0 + PK_CH, 0, nraw);
-      pk_load_crc<true, VEC>(v, k0, 0, rr);
-      pk_finish_chunk<true>(v, k0, 0, raw, xs, alo, ahi, es);
+      if (c > 0) { pk_load_raw<true, VEC>(v, k0 + PK_CH, 0, nraw); if (PK_NRR) pk_load_crc<true, VEC>(v, k0 + PK_CH, 0, nrr); }
+      if (!PK_NRR && c < nfull - 1) pk_load_crc<true, VEC>(v, k0, 0, rr);
+      pk_finish_chunk<true>(v, k0, 0, raw, xs, es, ka);
       pk_ck_load_wait(ck);
-      pk_alpha_chunk<true, SHIFT>(o, ck, 0, xs, raw.y, es, alo, ahi, rr, acc);
+      pk_alpha_chunk<true, SHIFT>(v, k0, o, ck, 0, xs, raw.y, es, rr, acc, ka);
       if ((cc & 3) == 3) { bits_lo[wi] = acc.wlo; bits_hi[wi] = acc.whi; wi++; }
       raw = nraw;
+      if (PK_NRR) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) rr[i] = nrr[i];
+      }
     }
   }
   if (cc & 3) { const int sh = 32 - 8 * (cc & 3); bits_lo[wi] = acc.wlo << sh; bits_hi[wi] = acc.whi << sh; }
@@ -495,10 +551,11 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
     const int par = n & 1;
     PkView v;
     v.par = par;
-    v.Srow = reinterpret_cast<const uint32_t *>(desc.soft) + j * Lp;
-    v.Yrow = reinterpret_cast<const uint32_t *>(desc.soft + (1 + par) * SS) + j * Lp;
-    v.Ynext = reinterpret_cast<const uint32_t *>(desc.soft + (2 - par) * SS) + j * Lp;
-    v.Rrow = a.pair_crc[desc.crc_sel] + (size_t)par * TPC * Lp + j * Lp;
+    v.tpc4 = 4 * TPC;
+    v.Srow = reinterpret_cast<const uint32_t *>(desc.soft) + 4 * j;
+    v.Yrow = reinterpret_cast<const uint32_t *>(desc.soft + (1 + par) * SS) + 4 * j;
+    v.Ynext = reinterpret_cast<const uint32_t *>(desc.soft + (2 - par) * SS) + 4 * j;
+    v.Rrow = a.pair_crc[desc.crc_sel] + (size_t)par * TPC * Lp + 2 * j;
     v.Tlo = Tlo + j * Lw; v.Thi = Thi + j * Lw;
     v.Eb = (uint32_t)__cvta_generic_to_shared(Eslot);
     v.ident = (uint32_t)(4 * j * Lw);
