@@ -30,12 +30,6 @@
 #define FEC_PK_TMEM 1
 #endif
 /* tuning switches (A/B-measured on B200, see profiles/): */
-#ifndef PK_BETA16
-#define PK_BETA16 1      /* beta main pass: 16 steps per loop iteration */
-#endif
-#ifndef PK_NRR
-#define PK_NRR 0         /* alpha pass: CRC syndrome words loaded one chunk ahead */
-#endif
 #ifndef PK_KEEP_ADDR
 #define PK_KEEP_ADDR 0   /* keep the 16 E addresses of a chunk in registers instead of recomputing them at write-back */
 #endif
@@ -63,6 +57,17 @@ __device__ __forceinline__ void pk_sts_u16(uint32_t addr, uint32_t val)
 {
   asm volatile("st.shared.u16 [%0], %1;" :: "r"(addr), "r"(val) : "memory");
 }
+
+/* scheduling fence: ptxas does not move memory instructions across a warp barrier, which keeps the prefetch
+ * loads where they are issued in the source (it otherwise sinks them to the register rotation at the loop end) */
+#ifndef PK_PINMODE
+#define PK_PINMODE 1
+#endif
+#if PK_PINMODE == 1
+#define PK_PIN() asm volatile("bar.warp.sync 0xffffffff;" ::: "memory")
+#else
+#define PK_PIN() do { } while (0)
+#endif
 
 /* global loads as volatile asm: ptxas otherwise sinks the prefetch loads down to their first use (register
  * pressure heuristic), which collapses the software-pipelining distance to zero */
@@ -313,14 +318,20 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
   /* ---- beta warm-up over the first 40 symbols of both sub-blocks (turbodecoder_win.h:321-384) ---- */
 #pragma unroll
   for (int i = 0; i < 8; i++) o[i] = 0;            /* the reference starts from 8 equal metrics (-10000): only differences matter */
-  pk_load_raw<true, true>(v, 32, 0, raw);
-  for (int c = 4; c >= 0; c--) {
+  /* every loop below has the shape  { issue the loads of the NEXT chunk; PK_PIN; work on this chunk; rotate }  and
+   * starts with a load-only iteration: no load is in flight when a loop is entered, so the only scoreboard
+   * wait on global loads sits at the rotation, a whole chunk after their issue */
+#pragma unroll 1
+  for (int c = 5; c >= 0; c--) {
     if (c > 0) pk_load_raw<true, true>(v, 8 * (c - 1), 0, nraw);
-    pk_finish_chunk<true>(v, 8 * c, 0, raw, xs, es);
+    PK_PIN();
+    if (c < 5) {
+      pk_finish_chunk<true>(v, 8 * c, 0, raw, xs, es);
 #pragma unroll
-    for (int i = 7; i >= 0; i--) {
-      pk_beta(o, xs[i], raw.y[i]);
-      if ((i & 3) == 0) pk_norm(o);
+      for (int i = 7; i >= 0; i--) {
+        pk_beta(o, xs[i], raw.y[i]);
+        if ((i & 3) == 0) pk_norm(o);
+      }
     }
     raw = nraw;
   }
@@ -358,34 +369,25 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
   {
     /* two chunks (16 steps) per iteration, the loads of the next 16 steps issued first: a single beta chunk is
      * shorter than an L2 hit, and the register rotation at the end of the body has to wait for those loads */
-    int k0 = L - PK_CH, c = 0;
+    const int c0 = nfull & 1;                        /* chunk c covers steps [L - 8(c+1), L - 8c) */
     PkRaw rawB, nrawB;
-#if !PK_BETA16
-    PkRaw n2raw;
-    pk_load_raw<true, VEC>(v, k0, 0, raw);
-    if (nfull > 1) pk_load_raw<true, VEC>(v, k0 - PK_CH, 0, nraw);
-#pragma unroll 1
-    for (; c < nfull; c++, k0 -= PK_CH) {
-      if (c + 2 < nfull) pk_load_raw<true, VEC>(v, k0 - 2 * PK_CH, 0, n2raw);
-      pk_finish_chunk<true>(v, k0, 0, raw, xs, es);
-      pk_beta_chunk<true>(o, xs, raw.y, 0, tbase + 8 * (c + 1));
-      raw = nraw; nraw = n2raw;
-    }
-#endif
-    if (PK_BETA16 && (nfull & 1)) {
-      pk_load_raw<true, VEC>(v, k0, 0, raw);
-      pk_finish_chunk<true>(v, k0, 0, raw, xs, es);
+    if (c0) {
+      pk_load_raw<true, VEC>(v, L - PK_CH, 0, raw);
+      PK_PIN();
+      pk_finish_chunk<true>(v, L - PK_CH, 0, raw, xs, es);
       pk_beta_chunk<true>(o, xs, raw.y, 0, tbase + 8);
-      k0 -= PK_CH; c = 1;
     }
-    if (PK_BETA16 && c < nfull) { pk_load_raw<true, VEC>(v, k0, 0, raw); pk_load_raw<true, VEC>(v, k0 - PK_CH, 0, rawB); }
 #pragma unroll 1
-    for (; c < nfull; c += 2, k0 -= 2 * PK_CH) {
+    for (int c = c0 - 2; c < nfull; c += 2) {
+      const int k0 = L - PK_CH * (c + 1);
       if (c + 2 < nfull) { pk_load_raw<true, VEC>(v, k0 - 2 * PK_CH, 0, nraw); pk_load_raw<true, VEC>(v, k0 - 3 * PK_CH, 0, nrawB); }
-      pk_finish_chunk<true>(v, k0, 0, raw, xs, es);
-      pk_beta_chunk<true>(o, xs, raw.y, 0, tbase + 8 * (c + 1));
-      pk_finish_chunk<true>(v, k0 - PK_CH, 0, rawB, xs, es);
-      pk_beta_chunk<true>(o, xs, rawB.y, 0, tbase + 8 * (c + 2));
+      PK_PIN();
+      if (c >= c0) {
+        pk_finish_chunk<true>(v, k0, 0, raw, xs, es);
+        pk_beta_chunk<true>(o, xs, raw.y, 0, tbase + 8 * (c + 1));
+        pk_finish_chunk<true>(v, k0 - PK_CH, 0, rawB, xs, es);
+        pk_beta_chunk<true>(o, xs, rawB.y, 0, tbase + 8 * (c + 2));
+      }
       raw = nraw; rawB = nrawB;
     }
     /* the bottom partial chunk only serves the (unused) end of the recursion: nothing to do */
@@ -396,16 +398,19 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
     uint32_t m[8], n[8];
 #pragma unroll
     for (int i = 0; i < 8; i++) o[i] = 0;
-    pk_load_raw<true, VEC>(v, L - 40, 0, raw);
-    for (int c = 0; c < 5; c++) {
+#pragma unroll 1
+    for (int c = -1; c < 5; c++) {
       if (c < 4) pk_load_raw<true, VEC>(v, L - 40 + 8 * (c + 1), 0, nraw);
-      pk_finish_chunk<true>(v, L - 40 + 8 * c, 0, raw, xs, es);
+      PK_PIN();
+      if (c >= 0) {
+        pk_finish_chunk<true>(v, L - 40 + 8 * c, 0, raw, xs, es);
 #pragma unroll
-      for (int i = 0; i < 8; i++) {
-        pk_alpha_branches(o, xs[i], raw.y[i], m, n);
+        for (int i = 0; i < 8; i++) {
+          pk_alpha_branches(o, xs[i], raw.y[i], m, n);
 #pragma unroll
-        for (int s = 0; s < 8; s++) o[s] = pk_max(m[s], n[s]);
-        if ((i & 3) == 3) pk_norm(o);
+          for (int s = 0; s < 8; s++) o[s] = pk_max(m[s], n[s]);
+          if ((i & 3) == 3) pk_norm(o);
+        }
       }
       raw = nraw;
     }
@@ -427,31 +432,26 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
     pk_ck_load_issue(tbase + 8 * nfull, ck);
     pk_load_raw<false, VEC>(v, k0, i0, raw);
     pk_load_crc<false, VEC>(v, k0, i0, rr);
+    PK_PIN();
     pk_finish_chunk<false>(v, k0, i0, raw, xs, es, ka);
     pk_ck_load_wait(ck);
     pk_alpha_chunk<false, SHIFT>(v, k0, o, ck, i0, xs, raw.y, es, rr, acc, ka);
     cc = 1;
   }
-  {
-    int k0 = rem;
-    uint2 nrr[8];
-    pk_load_raw<true, VEC>(v, k0, 0, raw);
-    pk_load_crc<true, VEC>(v, k0, 0, rr);
 #pragma unroll 1
-    for (int c = nfull - 1; c >= 0; c--, k0 += PK_CH, cc++) {
-      pk_ck_load_issue(tbase + 8 * c, ck);
-      if (c > 0) { pk_load_raw<true, VEC>(v, k0 + PK_CH, 0, nraw); if (PK_NRR) pk_load_crc<true, VEC>(v, k0 + PK_CH, 0, nrr); }
-      if (!PK_NRR && c < nfull - 1) pk_load_crc<true, VEC>(v, k0, 0, rr);
+  for (int c = nfull; c >= 0; c--) {                 /* iteration c works on steps [k0, k0+8), k0 = rem + 8(nfull-1-c) */
+    const int k0 = rem + PK_CH * (nfull - 1 - c);
+    if (c > 0) pk_load_raw<true, VEC>(v, k0 + PK_CH, 0, nraw);
+    if (c < nfull) { pk_ck_load_issue(tbase + 8 * c, ck); pk_load_crc<true, VEC>(v, k0, 0, rr); }
+    PK_PIN();
+    if (c < nfull) {
       pk_finish_chunk<true>(v, k0, 0, raw, xs, es, ka);
       pk_ck_load_wait(ck);
       pk_alpha_chunk<true, SHIFT>(v, k0, o, ck, 0, xs, raw.y, es, rr, acc, ka);
       if ((cc & 3) == 3) { bits_lo[wi] = acc.wlo; bits_hi[wi] = acc.whi; wi++; }
-      raw = nraw;
-      if (PK_NRR) {
-#pragma unroll
-        for (int i = 0; i < 8; i++) rr[i] = nrr[i];
-      }
+      cc++;
     }
+    raw = nraw;
   }
   if (cc & 3) { const int sh = 32 - 8 * (cc & 3); bits_lo[wi] = acc.wlo << sh; bits_hi[wi] = acc.whi << sh; }
 }
