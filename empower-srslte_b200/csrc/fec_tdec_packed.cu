@@ -31,7 +31,7 @@
 #endif
 /* tuning switches (A/B-measured on B200, see profiles/): */
 #ifndef PK_KEEP_ADDR
-#define PK_KEEP_ADDR 0   /* keep the 16 E addresses of a chunk in registers instead of recomputing them at write-back */
+#define PK_KEEP_ADDR 1   /* keep the 16 E addresses of a chunk in registers instead of recomputing them at write-back */
 #endif
 
 /* ---------------------------------------------------------------- packed helpers ---- */
@@ -60,6 +60,9 @@ __device__ __forceinline__ void pk_sts_u16(uint32_t addr, uint32_t val)
 
 /* scheduling fence: ptxas does not move memory instructions across a warp barrier, which keeps the prefetch
  * loads where they are issued in the source (it otherwise sinks them to the register rotation at the loop end) */
+#ifndef PK_CRC64
+#define PK_CRC64 1       /* CRC syndrome words by 8-byte instead of 16-byte loads */
+#endif
 #ifndef PK_PINMODE
 #define PK_PINMODE 1
 #endif
@@ -188,7 +191,7 @@ __device__ __forceinline__ void pk_load_raw(const PkView &v, int k0, int i0, PkR
 template <bool FULL, bool VEC>
 __device__ __forceinline__ void pk_load_crc(const PkView &v, int k0, int i0, uint2 *rr)
 {
-  if (FULL && VEC) {
+  if (FULL && VEC && !PK_CRC64) {
 #pragma unroll
     for (int i = 0; i < 8; i += 2) {
       const uint4 t = pk_ldg128(v.Rrow + ((k0 + i) >> 1) * (v.tpc4 >> 1));

@@ -37,6 +37,18 @@ def main():
     ins = decode(cubin, "fec_tdec_pk_kernelILi16ELb1EE")
     ldg_sb = set(x["wb"] for x in ins if x["s"].find("LDG") >= 0 and x["wb"] != 7)
     print("instructions", len(ins), "LDG scoreboards", sorted(ldg_sb))
+    last = {}
+    print("-- waits that follow an LDG on the same scoreboard by < 150 instructions (exposed latency):")
+    for k, x in enumerate(ins):
+        for b in range(6):
+            if (x["wait"] >> b) & 1 and b in last and k - last[b] < 150:
+                print("   %5d %-60s waits SB%d set %d instructions earlier by %s" % (k, x["s"][:60], b, k - last[b], ins[last[b]]["s"][:50]))
+        if "LDG" in x["s"] and x["wb"] != 7:
+            last[x["wb"]] = k
+        elif x["wb"] != 7 and x["wb"] in last:
+            del last[x["wb"]]
+    if "-v" not in sys.argv:
+        return
     for k, x in enumerate(ins):
         s = x["s"]
         w = [b for b in range(6) if (x["wait"] >> b) & 1 and b in ldg_sb]
