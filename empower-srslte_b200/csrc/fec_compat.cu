@@ -1,0 +1,269 @@
+/*
+ * fec_compat.cu — the reference's own C symbols for the decode path as batch-of-one wrappers over the batched
+ * API (include/srslte_fec_compat.h).  Host code only; every computation goes through fec_cuda_* (device).
+ *
+ * One process-wide context (device FEC_CUDA_DEVICE, default 0) is created on first use and shared by all
+ * objects; calls are serialised by a mutex.  The reference has no locks on this path and expects one object
+ * per worker thread (SURVEY 8b "Threading"): serialising keeps that contract; throughput-minded callers use
+ * the batched API directly.
+ */
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+
+#include "../../include/srslte_fec_cuda.h"
+#include "../../include/srslte_fec_compat.h"
+#include "fec_tables.h"
+
+static_assert(sizeof(srslte_tdec_t) == 18264, "srslte_tdec_t view must keep the reference size (SURVEY Appendix B)");
+static_assert(offsetof(srslte_tdec_t, n_iter) == 18256, "n_iter offset");
+static_assert(sizeof(srslte_softbuffer_rx_t) == 40, "srslte_softbuffer_rx_t view must keep the reference size");
+static_assert(offsetof(srslte_softbuffer_rx_t, buffer_f) == 8 && offsetof(srslte_softbuffer_rx_t, cb_crc) == 24 &&
+              offsetof(srslte_softbuffer_rx_t, tb_crc) == 32, "soft buffer field offsets");
+
+#define COMPAT_MAGIC 0xFEC0B200u
+#define SRSLTE_SUCCESS 0
+#define SRSLTE_ERROR (-1)
+#define SRSLTE_ERROR_INVALID_INPUTS (-2)
+
+static std::mutex g_mu;
+static fec_cuda_ctx_t *g_ctx = NULL;
+
+static fec_cuda_ctx_t *compat_ctx(void)
+{
+  if (!g_ctx) {
+    const char *e = getenv("FEC_CUDA_DEVICE");
+    fec_cuda_ctx_t *c = NULL;
+    if (fec_cuda_create(&c, e ? atoi(e) : 0, 64) != 0) {
+      fprintf(stderr, "libsrslte_fec_cuda: no usable CUDA device (there is no CPU fallback)\n");
+      return NULL;
+    }
+    g_ctx = c;
+  }
+  return g_ctx;
+}
+
+/* ================================================================= turbo decoder (turbodecoder.c:133-533) ==== */
+extern "C" int srslte_tdec_init_manual(srslte_tdec_t *h, uint32_t max_long_cb, srslte_tdec_impl_type_t dec_type)
+{
+  if (!h) return SRSLTE_ERROR_INVALID_INPUTS;
+  std::lock_guard<std::mutex> lk(g_mu);
+  memset(h, 0, sizeof(*h));                                     /* turbodecoder.c:156 */
+  if (dec_type != SRSLTE_TDEC_AUTO) {
+    /* manual modes pick ONE arithmetic class for every K (turbodecoder.c:160-190); this library implements the AUTO
+     * mapping of an AVX2 build only */
+    fprintf(stderr, "srslte_tdec_init_manual: only SRSLTE_TDEC_AUTO is provided by libsrslte_fec_cuda\n");
+    return SRSLTE_ERROR;
+  }
+  if (max_long_cb > FEC_CUDA_MAX_K) return SRSLTE_ERROR;
+  h->fec_ctx = compat_ctx();
+  if (!h->fec_ctx) return SRSLTE_ERROR;
+  h->fec_input = (int16_t *)malloc(sizeof(int16_t) * (3 * FEC_CUDA_MAX_K + 12));
+  if (!h->fec_input) return SRSLTE_ERROR;
+  h->max_long_cb = max_long_cb;
+  h->fec_magic = COMPAT_MAGIC;
+  return SRSLTE_SUCCESS;
+}
+
+extern "C" int srslte_tdec_init(srslte_tdec_t *h, uint32_t max_long_cb) { return srslte_tdec_init_manual(h, max_long_cb, SRSLTE_TDEC_AUTO); }
+
+extern "C" void srslte_tdec_free(srslte_tdec_t *h)
+{
+  if (!h) return;
+  if (h->fec_magic == COMPAT_MAGIC && h->fec_input) free(h->fec_input);
+  memset(h, 0, sizeof(*h));                                     /* turbodecoder.c:350 */
+}
+
+extern "C" void srslte_tdec_force_not_sb(srslte_tdec_t *h) { if (h) h->fec_force_not_sb = 1; }            /* turbodecoder.c:353-355 */
+
+extern "C" int srslte_tdec_new_cb(srslte_tdec_t *h, uint32_t long_cb)
+{
+  if (!h || h->fec_magic != COMPAT_MAGIC) return SRSLTE_ERROR;
+  if (long_cb > h->max_long_cb) {                               /* turbodecoder.c:495-499 */
+    fprintf(stderr, "TDEC was initialized for max_long_cb=%u\n", h->max_long_cb);
+    return SRSLTE_ERROR;
+  }
+  const int idx = fec_k_index(long_cb);
+  if (idx < 0 || (uint32_t)fec_k_size((uint32_t)idx) != long_cb) {   /* turbodecoder.c:501-505: not an LTE block size */
+    fprintf(stderr, "Invalid CB length %u\n", long_cb);
+    return SRSLTE_ERROR;
+  }
+  h->n_iter = 0;
+  h->fec_K = long_cb;
+  return SRSLTE_SUCCESS;
+}
+
+extern "C" int srslte_tdec_get_nof_iterations(srslte_tdec_t *h) { return h ? (int)h->n_iter : 0; }
+
+extern "C" uint32_t srslte_tdec_autoimp_get_subblocks(uint32_t nof_bits) { return (uint32_t)fec_k_subblocks(nof_bits); }
+
+/* sub-block count of the 8-bit decoders, AVX2 build (turbodecoder.c:392-406); only the mapping is provided, not the decoders */
+extern "C" uint32_t srslte_tdec_autoimp_get_subblocks_8bit(uint32_t nof_bits)
+{
+  if ((nof_bits % 32) == 0 && nof_bits > 2048) return 32;
+  if ((nof_bits % 16) == 0 && nof_bits > 800) return 16;
+  if ((nof_bits % 8) == 0 && nof_bits > 400) return 8;
+  return 0;
+}
+
+/* the caller's input is in the sub-block layout of srslte_rm_turbo_rx_lut_(…, true) unless force_not_sb was set
+ * or the block size has no windowed decoder (turbodecoder_iter.h:48,61-70,91-103): bring it to the natural layout */
+static void compat_take_input(srslte_tdec_t *h, const int16_t *in)
+{
+  const uint32_t K = h->fec_K;
+  fec_geom_t g;
+  fec_geom(K, &g);
+  if (g.P == 0 || h->fec_force_not_sb) { memcpy(h->fec_input, in, sizeof(int16_t) * (3 * K + 12)); return; }
+  for (uint32_t t = 0; t < 3 * K + 12; t++) h->fec_input[t] = in[fec_soft_offset_ref(&g, (int)t, 1)];
+}
+
+/* Runs the code block from its LLRs for (n_iter + 1) half-iterations: the device decoder is deterministic, so this
+ * IS the state the reference reaches by its (n_iter+1)-th incremental call (turbodecoder_iter.h:73-147). */
+static int compat_run(srslte_tdec_t *h, uint8_t *output, uint32_t halfits)
+{
+  fec_cuda_cb_t cb;
+  memset(&cb, 0, sizeof(cb));
+  cb.K = h->fec_K; cb.max_its = halfits; cb.crc_type = 1; cb.llr = h->fec_input; cb.out = output;
+  const int r = fec_cuda_decode_cbs((fec_cuda_ctx_t *)h->fec_ctx, &cb, 1, FEC_CUDA_F_NO_EARLY_STOP);
+  if (r) fprintf(stderr, "libsrslte_fec_cuda: %s\n", fec_cuda_last_error((fec_cuda_ctx_t *)h->fec_ctx));
+  return r;
+}
+
+extern "C" void srslte_tdec_iteration(srslte_tdec_t *h, int16_t *input, uint8_t *output)
+{
+  if (!h || h->fec_magic != COMPAT_MAGIC || !h->fec_K || !input || !output) return;
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (h->n_iter == 0) compat_take_input(h, input);
+  if (compat_run(h, output, h->n_iter + 1) == 0) h->n_iter++;
+}
+
+extern "C" int srslte_tdec_run_all(srslte_tdec_t *h, int16_t *input, uint8_t *output, uint32_t nof_iterations, uint32_t long_cb)
+{
+  if (srslte_tdec_new_cb(h, long_cb)) return SRSLTE_ERROR;       /* turbodecoder.c:510-533 */
+  if (!input || !output) return SRSLTE_ERROR;
+  std::lock_guard<std::mutex> lk(g_mu);
+  compat_take_input(h, input);
+  if (nof_iterations == 0) return SRSLTE_SUCCESS;
+  if (compat_run(h, output, nof_iterations)) return SRSLTE_ERROR;
+  h->n_iter = nof_iterations;
+  return SRSLTE_SUCCESS;
+}
+
+extern "C" void srslte_tdec_iteration_8bit(srslte_tdec_t *, int8_t *, uint8_t *)
+{
+  fprintf(stderr, "srslte_tdec_iteration_8bit: the 8-bit LLR path is not provided by libsrslte_fec_cuda\n");
+}
+extern "C" int srslte_tdec_run_all_8bit(srslte_tdec_t *, int8_t *, uint8_t *, uint32_t, uint32_t)
+{
+  fprintf(stderr, "srslte_tdec_run_all_8bit: the 8-bit LLR path is not provided by libsrslte_fec_cuda\n");
+  return SRSLTE_ERROR;
+}
+
+/* ================================================================= rate de-matching (rm_turbo.c:267-430) ==== */
+extern "C" void srslte_rm_turbo_gentables(void) { }
+extern "C" void srslte_rm_turbo_free_tables(void) { }
+
+extern "C" int srslte_rm_turbo_rx_lut_(int16_t *input, int16_t *output, uint32_t in_len, uint32_t cb_idx, uint32_t rv_idx, bool enable_input_tdec)
+{
+  if (!input || !output || rv_idx >= 4 || cb_idx >= FEC_NOF_K) {  /* rm_turbo.c:395,426-429 */
+    fprintf(stderr, "Invalid inputs rv_idx=%d, cb_idx=%d\n", rv_idx, cb_idx);
+    return SRSLTE_ERROR_INVALID_INPUTS;
+  }
+  std::lock_guard<std::mutex> lk(g_mu);
+  fec_cuda_ctx_t *ctx = compat_ctx();
+  if (!ctx) return SRSLTE_ERROR;
+  const int r = fec_cuda_rm_rx(ctx, input, in_len, cb_idx, rv_idx, enable_input_tdec ? 1 : 0, output);
+  return r == 0 ? SRSLTE_SUCCESS : (r == FEC_CUDA_EINVAL ? SRSLTE_ERROR_INVALID_INPUTS : SRSLTE_ERROR);
+}
+
+extern "C" int srslte_rm_turbo_rx_lut(int16_t *input, int16_t *output, uint32_t in_len, uint32_t cb_idx, uint32_t rv_idx)
+{
+  return srslte_rm_turbo_rx_lut_(input, output, in_len, cb_idx, rv_idx, false);          /* rm_turbo.c:378-381 */
+}
+
+/* ================================================================= soft buffers (softbuffer.c:46-151) ==== */
+typedef struct { uint32_t magic, id, pending_new; } compat_sb_t;
+
+/* TBS of I_TBS = 26 for 1..110 PRB (36.213 table 7.1.7.2.1-1), divided as softbuffer.c:52-54: max_cb = TBS/6120 + 1 */
+static const uint32_t tbs_itbs26[110] = {
+  712, 1480, 2216, 2984, 3752, 4392, 5160, 5992, 6712, 7480, 8248, 8760, 9528, 10296, 11064, 11832, 12576, 13536, 14112, 14688, 15264,
+  16416, 16992, 17568, 18336, 19080, 19848, 20616, 21384, 22152, 22920, 23688, 24496, 25456, 25456, 26416, 27376, 28336, 29296, 29296,
+  30576, 30576, 31704, 32856, 32856, 34008, 35160, 35160, 36696, 36696, 37888, 37888, 39232, 40576, 40576, 40576, 42368, 42368, 43816,
+  43816, 45352, 45352, 46888, 46888, 48936, 48936, 48936, 51024, 51024, 52752, 52752, 52752, 55056, 55056, 55056, 55056, 57336, 57336,
+  57336, 59256, 59256, 59256, 61664, 61664, 61664, 63776, 63776, 63776, 66592, 66592, 66592, 68808, 68808, 68808, 71112, 71112, 71112,
+  73712, 73712, 75376, 75376, 75376, 75376, 75376, 75376, 75376, 75376, 75376, 75376, 75376 };
+
+static compat_sb_t *compat_sb(srslte_softbuffer_rx_t *q)
+{
+  compat_sb_t *s = q ? (compat_sb_t *)q->buffer_f : NULL;
+  return (s && s->magic == COMPAT_MAGIC) ? s : NULL;
+}
+
+extern "C" int srslte_softbuffer_rx_init(srslte_softbuffer_rx_t *q, uint32_t nof_prb)
+{
+  if (!q) return SRSLTE_ERROR_INVALID_INPUTS;
+  memset(q, 0, sizeof(*q));                                      /* softbuffer.c:50 */
+  if (nof_prb < 1 || nof_prb > 110) return SRSLTE_ERROR;         /* srslte_ra_tbs_from_idx fails (softbuffer.c:52-53) */
+  std::lock_guard<std::mutex> lk(g_mu);
+  fec_cuda_ctx_t *ctx = compat_ctx();
+  if (!ctx) return SRSLTE_ERROR;
+  compat_sb_t *s = (compat_sb_t *)calloc(1, sizeof(*s));
+  q->max_cb = tbs_itbs26[nof_prb - 1] / (6144 - 24) + 1;
+  q->cb_crc = (bool *)calloc(q->max_cb, sizeof(bool));
+  if (!s || !q->cb_crc || fec_cuda_softbuffer_alloc(ctx, 1, &s->id)) { free(s); free(q->cb_crc); memset(q, 0, sizeof(*q)); return SRSLTE_ERROR; }
+  s->magic = COMPAT_MAGIC; s->pending_new = 1;
+  q->buffer_f = (int16_t **)s;
+  return SRSLTE_SUCCESS;
+}
+
+extern "C" void srslte_softbuffer_rx_free(srslte_softbuffer_rx_t *q)
+{
+  if (!q) return;
+  /* device slots are pooled for the lifetime of the context (softbuffer ids are not recycled) */
+  if (compat_sb(q)) free(q->buffer_f);
+  if (q->cb_crc) free(q->cb_crc);
+  memset(q, 0, sizeof(*q));
+}
+
+/* the reference zeroes the first nof_cb CB buffers and ALL cb_crc flags (softbuffer.c:138-151).  Zeroing is deferred:
+ * the next decode combines with new_data = 1, i.e. the rate de-matcher writes instead of accumulating. */
+extern "C" void srslte_softbuffer_rx_reset_cb(srslte_softbuffer_rx_t *q, uint32_t)
+{
+  compat_sb_t *s = compat_sb(q);
+  if (s) s->pending_new = 1;
+  if (q && q->cb_crc) memset(q->cb_crc, 0, sizeof(bool) * q->max_cb);
+}
+extern "C" void srslte_softbuffer_rx_reset_tbs(srslte_softbuffer_rx_t *q, uint32_t tbs) { srslte_softbuffer_rx_reset_cb(q, (tbs + 24) / (6144 - 24) + 1); }
+extern "C" void srslte_softbuffer_rx_reset(srslte_softbuffer_rx_t *q) { if (q) srslte_softbuffer_rx_reset_cb(q, q->max_cb); }
+
+/* ================================================================= decode_tb (sch.c:437-486) ==== */
+extern "C" int srslte_sch_decode_tb_cuda(srslte_softbuffer_rx_t *softbuffer, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits,
+                                         int16_t *e_bits, uint8_t *data, uint32_t max_iterations, uint32_t *nof_iterations)
+{
+  compat_sb_t *s = compat_sb(softbuffer);
+  if (!s || !data || !e_bits) return SRSLTE_ERROR_INVALID_INPUTS;          /* sch.c:444-448 */
+  uint32_t seg[9];
+  if (fec_segm(tbs, seg)) return SRSLTE_ERROR_INVALID_INPUTS;
+  if (tbs == 0 || seg[1] == 0) return SRSLTE_SUCCESS;                          /* sch.c:450-452 */
+  if (seg[0]) { fprintf(stderr, "Error filler bits are not supported. Use standard TBS\n"); return SRSLTE_ERROR_INVALID_INPUTS; }
+  if (seg[1] > softbuffer->max_cb) {
+    fprintf(stderr, "Error number of CB (%d) exceeds soft buffer size (%d CBs)\n", seg[1], softbuffer->max_cb);
+    return SRSLTE_ERROR_INVALID_INPUTS;
+  }
+  std::lock_guard<std::mutex> lk(g_mu);
+  fec_cuda_ctx_t *ctx = compat_ctx();
+  if (!ctx) return SRSLTE_ERROR;
+  fec_cuda_tb_t t;
+  memset(&t, 0, sizeof(t));
+  t.tbs = tbs; t.Qm = Qm; t.rv = rv; t.nof_e_bits = nof_e_bits; t.max_its = max_iterations; t.softbuffer = s->id;
+  t.new_data = s->pending_new; t.e_bits = e_bits; t.data = data;
+  if (fec_cuda_decode_tbs(ctx, &t, 1, 0)) { fprintf(stderr, "libsrslte_fec_cuda: %s\n", fec_cuda_last_error(ctx)); return SRSLTE_ERROR; }
+  s->pending_new = 0;
+  for (uint32_t c = 0; c < seg[1] && c < softbuffer->max_cb; c++) softbuffer->cb_crc[c] = t.cb_crc[c] != 0;
+  bool all = true;
+  for (uint32_t c = 0; c < seg[1]; c++) all = all && t.cb_crc[c];
+  softbuffer->tb_crc = all;                                                    /* sch.c:404-408 */
+  if (nof_iterations) *nof_iterations = t.avg_its;                             /* sch.c:420 */
+  return t.ret;
+}

@@ -575,27 +575,54 @@ cudaError_t fec_launch_extract(const FecExtractDesc *descs, uint32_t *soft_max, 
   return cudaGetLastError();
 }
 
-/* device layout -> reference soft-buffer layout (18600 int16), for parity checks and srslte_rm_turbo_rx_lut */
-__global__ void fec_soft_to_ref_kernel(const int16_t *dev, int16_t *ref, fec_geom_t g, int sb)
+/* (stream s, natural position x) or tail entry t >= 3K  ->  offsets in the device and the reference soft-buffer layouts */
+__device__ __forceinline__ void fec_soft_pair(const fec_geom_t &g, int t, int sb, int &od, int &orf)
 {
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 18600; i += gridDim.x * blockDim.x) ref[i] = 0;
-  __syncthreads();
-  if (gridDim.x != 1) return;   /* single-CTA kernel: the zero fill above must complete first */
+  if (t >= 3 * g.K) { od = 3 * g.SS + (t - 3 * g.K); orf = (sb && g.P) ? 3 * (g.K + 32) + (t - 3 * g.K) : t; }
+  else {
+    const int s = t % 3, x = t / 3, dl = x / g.L, kk = x % g.L;
+    od = g.P ? s * g.SS + 2 * ((((kk >> 2) * (g.P / 2) + (dl >> 1)) << 2) + (kk & 3)) + (dl & 1) : s * g.SS + kk;
+    orf = (sb && g.P) ? s * (g.K + 32) + (x % g.L) * g.P + x / g.L : t;
+  }
+}
+
+/* device layout -> reference soft-buffer layout (18600 int16), for parity checks and srslte_rm_turbo_rx_lut.
+ * keep != 0: entries of `ref` that no code-block position maps to are left as they are (the reference never
+ * touches them either), else they are zeroed. Single CTA. */
+__global__ void fec_soft_to_ref_kernel(const int16_t *dev, int16_t *ref, fec_geom_t g, int sb, int keep)
+{
+  if (!keep) {
+    for (int i = threadIdx.x; i < 18600; i += blockDim.x) ref[i] = 0;
+    __syncthreads();
+  }
   for (int t = threadIdx.x; t < 3 * g.K + 12; t += blockDim.x) {
     int od, orf;
-    if (t >= 3 * g.K) { od = 3 * g.SS + (t - 3 * g.K); orf = (sb && g.P) ? 3 * (g.K + 32) + (t - 3 * g.K) : t; }
-    else {
-      const int s = t % 3, x = t / 3, dl = x / g.L, kk = x % g.L;
-      od = g.P ? s * g.SS + 2 * ((((kk >> 2) * (g.P / 2) + (dl >> 1)) << 2) + (kk & 3)) + (dl & 1) : s * g.SS + kk;
-      orf = (sb && g.P) ? s * (g.K + 32) + (x % g.L) * g.P + x / g.L : t;
-    }
+    fec_soft_pair(g, t, sb, od, orf);
     ref[orf] = dev[od];
   }
 }
 
-cudaError_t fec_launch_soft_to_ref(const int16_t *soft_dev, int16_t *ref_dev, fec_geom_t g, int sb_layout, cudaStream_t st)
+/* reference soft-buffer layout -> device layout (a caller-owned host soft buffer entering srslte_rm_turbo_rx_lut) */
+__global__ void fec_ref_to_soft_kernel(const int16_t *ref, int16_t *dev, fec_geom_t g, int sb)
 {
-  fec_soft_to_ref_kernel<<<1, 1024, 0, st>>>(soft_dev, ref_dev, g, sb_layout);
+  for (int i = threadIdx.x; i < 3 * g.SS + 16; i += blockDim.x) dev[i] = 0;
+  __syncthreads();
+  for (int t = threadIdx.x; t < 3 * g.K + 12; t += blockDim.x) {
+    int od, orf;
+    fec_soft_pair(g, t, sb, od, orf);
+    dev[od] = ref[orf];
+  }
+}
+
+cudaError_t fec_launch_soft_to_ref(const int16_t *soft_dev, int16_t *ref_dev, fec_geom_t g, int sb_layout, int keep, cudaStream_t st)
+{
+  fec_soft_to_ref_kernel<<<1, 1024, 0, st>>>(soft_dev, ref_dev, g, sb_layout, keep);
+  return cudaGetLastError();
+}
+
+cudaError_t fec_launch_ref_to_soft(const int16_t *ref_dev, int16_t *soft_dev, fec_geom_t g, int sb_layout, cudaStream_t st)
+{
+  fec_ref_to_soft_kernel<<<1, 1024, 0, st>>>(ref_dev, soft_dev, g, sb_layout);
   return cudaGetLastError();
 }
 

@@ -87,6 +87,7 @@ cudaError_t fec_launch_rm(const FecRmDesc *descs, uint32_t *soft_max, uint32_t n
 cudaError_t fec_launch_extract(const FecExtractDesc *descs, uint32_t *soft_max, uint32_t n, cudaStream_t st);
 cudaError_t fec_launch_tb_assemble(const FecTbDesc *descs, const FecCbStatus *status, const uint32_t *r24a,
                                    uint32_t n, cudaStream_t st);
-cudaError_t fec_launch_soft_to_ref(const int16_t *soft_dev, int16_t *ref_dev, fec_geom_t g, int sb_layout, cudaStream_t st);
+cudaError_t fec_launch_soft_to_ref(const int16_t *soft_dev, int16_t *ref_dev, fec_geom_t g, int sb_layout, int keep, cudaStream_t st);
+cudaError_t fec_launch_ref_to_soft(const int16_t *ref_dev, int16_t *soft_dev, fec_geom_t g, int sb_layout, cudaStream_t st);
 cudaError_t fec_kernels_init(void);
 #endif

@@ -69,3 +69,28 @@ def test_product_never_touches_oracle():
             if f.endswith((".cu", ".cuh", ".c", ".h", ".py")):
                 s = open(os.path.join(dp, f)).read()
                 assert "fec_oracle" not in s and "libsrslte_ref" not in s and "oracle/" not in s, f
+
+
+def test_compat_entry_points_without_device():
+    """the reference's own symbols (include/srslte_fec_compat.h): pure bookkeeping works anywhere, everything that
+    computes refuses to run without a device (no CPU fallback), with the reference's error codes"""
+    import torch
+    pkg = _pkg()
+    lib = pkg.load()
+    for K in ALL_K:
+        assert lib.srslte_tdec_autoimp_get_subblocks(K) == (16 if K > 800 and K % 16 == 0 else 8 if K > 400 else 0)
+        assert lib.srslte_tdec_autoimp_get_subblocks_8bit(K) == (32 if K > 2048 and K % 32 == 0 else 16 if K > 800 and K % 16 == 0
+                                                                 else 8 if K > 400 else 0)
+    e, s = np.zeros(16, np.int16), np.zeros(18600, np.int16)
+    lib.srslte_rm_turbo_rx_lut.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32]
+    assert lib.srslte_rm_turbo_rx_lut(e.ctypes.data, s.ctypes.data, 16, 188, 0) == -2     # rm_turbo.c:426-429
+    assert lib.srslte_rm_turbo_rx_lut(e.ctypes.data, s.ctypes.data, 16, 0, 4) == -2
+    if torch.cuda.is_available():
+        return
+    h = C.create_string_buffer(18264)
+    lib.srslte_tdec_init.argtypes = [C.c_void_p, C.c_uint32]
+    assert lib.srslte_tdec_init(h, 6144) == -1
+    q = C.create_string_buffer(40)
+    lib.srslte_softbuffer_rx_init.argtypes = [C.c_void_p, C.c_uint32]
+    assert lib.srslte_softbuffer_rx_init(q, 100) == -1
+    assert lib.srslte_rm_turbo_rx_lut(e.ctypes.data, s.ctypes.data, 16, 0, 0) == -1

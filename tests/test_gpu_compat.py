@@ -1,0 +1,130 @@
+"""The reference's own entry points (include/srslte_fec_compat.h) on the GPU: srslte_tdec_*, srslte_rm_turbo_rx_lut[_],
+srslte_softbuffer_rx_* and the decode_tb body, called the way the reference's tests call them
+(turbodecoder_test.c:181-330, rm_turbo_test.c, pdsch_test.c) and compared bit for bit with the golden vectors
+generated from the unmodified reference and with the CPU oracle."""
+import ctypes as C
+import importlib
+
+import numpy as np
+import pytest
+
+import _golden as G
+from _libs import ALL_K, P, int_gauss
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def lib():
+    pkg = importlib.import_module("empower-srslte_b200")
+    l = pkg.load()
+    l.srslte_tdec_init.argtypes = [C.c_void_p, C.c_uint32]
+    l.srslte_tdec_free.argtypes = [C.c_void_p]
+    l.srslte_tdec_force_not_sb.argtypes = [C.c_void_p]
+    l.srslte_tdec_new_cb.argtypes = [C.c_void_p, C.c_uint32]
+    l.srslte_tdec_get_nof_iterations.argtypes = [C.c_void_p]
+    l.srslte_tdec_iteration.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    l.srslte_tdec_iteration.restype = None
+    l.srslte_tdec_run_all.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]
+    l.srslte_rm_turbo_rx_lut_.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_bool]
+    l.srslte_rm_turbo_rx_lut.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32]
+    l.srslte_softbuffer_rx_init.argtypes = [C.c_void_p, C.c_uint32]
+    l.srslte_softbuffer_rx_free.argtypes = [C.c_void_p]
+    l.srslte_softbuffer_rx_reset_tbs.argtypes = [C.c_void_p, C.c_uint32]
+    l.srslte_sch_decode_tb_cuda.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p,
+                                            C.c_uint32, C.c_void_p]
+    return l
+
+
+def _tdec(lib, max_k=6144):
+    h = C.create_string_buffer(18264)          # sizeof(srslte_tdec_t), caller-allocated as in the reference
+    assert lib.srslte_tdec_init(h, max_k) == 0
+    return h
+
+
+@pytest.mark.parametrize("case", list(G.tdec_cases()), ids=lambda c: c["id"])
+def test_tdec_run_all_and_iteration_golden(lib, case):
+    """turbodecoder_test.c drives srslte_tdec_run_all on natural-layout input with force_not_sb; the golden bytes after
+    every half-iteration come from the reference's srslte_tdec_iteration"""
+    K = case["K"]
+    h = _tdec(lib)
+    lib.srslte_tdec_force_not_sb(h)
+    inp = np.ascontiguousarray(case["inp"])
+    out = np.zeros(K // 8, np.uint8)
+    assert lib.srslte_tdec_run_all(h, P(inp), P(out), case["nof"], K) == 0
+    assert lib.srslte_tdec_get_nof_iterations(h) == case["nof"]
+    assert (out == case["bytes"][case["nof"] - 1]).all()
+    assert lib.srslte_tdec_new_cb(h, K) == 0
+    for n in range(case["nof"]):
+        lib.srslte_tdec_iteration(h, P(inp), P(out))
+        assert lib.srslte_tdec_get_nof_iterations(h) == n + 1
+        assert (out == case["bytes"][n]).all(), (K, n)
+    lib.srslte_tdec_free(h)
+
+
+def test_tdec_sb_layout_input_vs_oracle(lib, orc):
+    """without force_not_sb the decoder expects the sub-block layout srslte_rm_turbo_rx_lut_(.., true) produces
+    (turbodecoder_iter.h:61-70): rate de-match into a soft buffer, decode from it"""
+    for K in (408, 1024, 5824, 6144):
+        E = 3 * K + 12 + 600
+        e = (int_gauss(E, 31 * K) % 1201 - 600).astype(np.int16)
+        soft = np.zeros(18600, np.int16)
+        assert lib.srslte_rm_turbo_rx_lut_(P(e), P(soft), E, ALL_K.index(K), 0, True) == 0
+        want_soft = np.zeros(18600, np.int16)
+        assert orc.orc_rm_rx(P(e), E, K, 0, 1, P(want_soft)) == 0
+        assert (soft == want_soft).all()
+        want = np.zeros(K // 8, np.uint8)
+        nits = C.c_int(0)
+        orc.orc_decode_cb(P(want_soft), K, 4, 1, P(want), C.byref(nits))
+        h = _tdec(lib)
+        out = np.zeros(K // 8, np.uint8)
+        assert lib.srslte_tdec_new_cb(h, K) == 0
+        for _ in range(nits.value):
+            lib.srslte_tdec_iteration(h, P(soft), P(out))
+        assert (out == want).all(), K
+        lib.srslte_tdec_free(h)
+
+
+def test_tdec_argument_checks(lib):
+    h = _tdec(lib, 1024)
+    assert lib.srslte_tdec_new_cb(h, 2048) == -1        # larger than max_long_cb (turbodecoder.c:495-499)
+    assert lib.srslte_tdec_new_cb(h, 1000) == -1        # not an LTE size
+    assert lib.srslte_tdec_new_cb(h, 1024) == 0
+    lib.srslte_tdec_free(h)
+
+
+def test_rm_rx_lut_accumulates_like_reference(lib, orc):
+    """two transmissions (rv 0 then rv 2) into one caller-owned soft buffer, natural and sub-block layouts"""
+    for K, sb in ((40, False), (512, False), (512, True), (6144, True)):
+        soft = np.zeros(18600, np.int16)
+        want = np.zeros(18600, np.int16)
+        for rv in (0, 2):
+            E = 2 * K + 7
+            e = (int_gauss(E, K + rv) % 30001 - 15000).astype(np.int16)        # large: wrapping adds are exercised
+            assert lib.srslte_rm_turbo_rx_lut_(P(e), P(soft), E, ALL_K.index(K), rv, sb) == 0
+            assert orc.orc_rm_rx(P(e), E, K, rv, int(sb), P(want)) == 0
+        assert (soft == want).all(), (K, sb)
+    assert lib.srslte_rm_turbo_rx_lut(P(e), P(soft), 10, 188, 0) == -2
+    assert lib.srslte_rm_turbo_rx_lut(P(e), P(soft), 10, 0, 4) == -2
+
+
+@pytest.mark.parametrize("case", list(G.tb_cases()), ids=lambda c: c["id"])
+def test_decode_tb_with_reference_softbuffer_calls(lib, case):
+    """pdsch_test.c shape: srslte_softbuffer_rx_init / reset_tbs, then one decode_tb per (re)transmission"""
+    tbs = case["tbs"]
+    nC = importlib.import_module("empower-srslte_b200").cbsegm(tbs)["C"]
+    q = C.create_string_buffer(40)             # sizeof(srslte_softbuffer_rx_t)
+    assert lib.srslte_softbuffer_rx_init(q, 100) == 0
+    assert C.c_uint32.from_buffer(q, 0).value == 13
+    lib.srslte_softbuffer_rx_reset_tbs(q, tbs)
+    for tx in case["tx"]:
+        data = np.zeros(tbs // 8 + 3 + 768, np.uint8)
+        noi = C.c_uint32(0)
+        llr = np.ascontiguousarray(tx["llr"])
+        ret = lib.srslte_sch_decode_tb_cuda(q, tbs, case["Qm"], tx["rv"], case["nbits"], P(llr), P(data), case["max_its"], C.byref(noi))
+        assert ret == tx["ret"]
+        assert (data[: tbs // 8 + 3] == tx["data"][: tbs // 8 + 3]).all()
+        crc = (C.c_bool * 13).from_address(C.c_void_p.from_buffer(q, 24).value)
+        assert [bool(crc[i]) for i in range(nC)] == [bool(v) for v in tx["crc"][:nC]]
+    lib.srslte_softbuffer_rx_free(q)
+    assert bytes(q.raw) == bytes(40)
