@@ -213,6 +213,7 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     pkg = importlib.import_module("empower-srslte_b200")
+    shard = importlib.import_module("empower-srslte_b200.shard")
     fec = pkg.FecCuda(local_rank, max_tbs=args.batch)
     B = args.batch
 
@@ -245,11 +246,7 @@ def main():
                 phases.append(fec.last_phase_ms())
         e1.record(stream)
         barrier()
-        ms = e0.elapsed_time(e1)
-        if world > 1:
-            t = torch.tensor([ms], device=f"cuda:{local_rank}")
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
+        ms, _ = shard.reduce_job(dist if world > 1 else None, f"cuda:{local_rank}", e0.elapsed_time(e1))
         return ms
 
     def tally(descs):
@@ -258,11 +255,7 @@ def main():
         return ok, its
 
     def allsum(v):
-        if world > 1:
-            t = torch.tensor([float(v)], device=f"cuda:{local_rank}", dtype=torch.float64)
-            dist.all_reduce(t)
-            return float(t.item())
-        return float(v)
+        return shard.reduce_job(dist if world > 1 else None, f"cuda:{local_rank}", 0.0, v=v)[1]["v"]
 
     # ---- device-resident arm (value) ----
     for _ in range(args.warmup):
@@ -324,7 +317,7 @@ def main():
     peak_nom, peak_src = alu_peak_tops(n_sm, pk["sm_max_mhz"])
     peak_run, _ = alu_peak_tops(n_sm, sm_mhz)
     hbm_bytes = B * C_CB * algorithmic_bytes_per_cb(K_CB, NBITS // C_CB)
-    roof = dict(bound="alu_int16", kernel="fec_tdec_pk_kernel<16,0>", achieved=achieved, peak=peak_nom, unit="Tops/s",
+    roof = dict(bound="alu_int16", kernel="fec_tdec_pk_kernel<16,true>", achieved=achieved, peak=peak_nom, unit="Tops/s",
                 frac=achieved / peak_nom, frac_at_sustained_clock=achieved / peak_run, peak_source=peak_src + f" @ {pk['sm_max_mhz']:.0f} MHz",
                 traffic=None, ops_per_launch=ops, ms_per_launch=dec_ms,
                 share_of_step=dec_ms / (rm_ms + dec_ms + asm_ms), serial_step_ms=rm_ms + dec_ms + asm_ms,
