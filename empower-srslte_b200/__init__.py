@@ -73,6 +73,8 @@ def load():
         lib.fec_cuda_softbuffer_reset.argtypes = [C.c_void_p, C.c_uint32]
         lib.fec_cuda_softbuffer_read_ref_layout.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]
         lib.fec_cuda_decode_tbs.argtypes = [C.c_void_p, C.POINTER(TbDesc), C.c_uint32, C.c_uint32]
+        lib.fec_cuda_submit_tbs.argtypes = [C.c_void_p, C.POINTER(TbDesc), C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64)]
+        lib.fec_cuda_wait.argtypes = [C.c_void_p, C.c_uint64]
         lib.fec_cuda_decode_cbs.argtypes = [C.c_void_p, C.POINTER(CbDesc), C.c_uint32, C.c_uint32]
         lib.fec_cuda_rm_rx.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p]
         lib.fec_cuda_cbsegm.argtypes = [C.c_uint32, C.POINTER(C.c_uint32)]
@@ -174,6 +176,19 @@ class FecCuda:
         if rc:
             raise RuntimeError(f"fec_cuda_decode_tbs: {rc} {self.error()}")
         return descs
+
+    def submit_tbs(self, descs, flags=0):
+        """asynchronous half of decode_tbs: enqueue the batch, return its ticket (results are valid after wait)"""
+        t = C.c_uint64(0)
+        rc = self.lib.fec_cuda_submit_tbs(self.h, descs, len(descs), flags, C.byref(t))
+        if rc:
+            raise RuntimeError(f"fec_cuda_submit_tbs: {rc} {self.error()}")
+        return t.value
+
+    def wait(self, ticket):
+        rc = self.lib.fec_cuda_wait(self.h, ticket)
+        if rc:
+            raise RuntimeError(f"fec_cuda_wait: {rc} {self.error()}")
 
     def decode_tb(self, tbs, Qm, rv, e_bits, softbuffer, new_data, max_its=8, flags=0):
         """single transport block convenience (the srslte_dlsch_decode call shape). e_bits: int16 numpy."""

@@ -12,6 +12,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <time.h>
 
 #define CB_BYTES 768     /* 6144/8: per-CB decoded byte slot */
 
@@ -34,7 +35,7 @@ typedef struct {
 } sbchunk_t;
 
 typedef struct { void *h, *d; size_t cap; } stage_t;   /* pinned host + device mirror, grown on demand */
-#define FEC_NPIPE 4
+#define FEC_NPIPE 8
 typedef struct fec_pipe fec_pipe_t;
 
 struct fec_cuda_ctx {
@@ -60,9 +61,16 @@ struct fec_cuda_ctx {
   cudaStream_t  s_copy, s_out, s_comp[2];
   fec_pipe_t   *pipes;
   uint32_t      sub_tbs, sub_tbs_dev;
+  size_t        hw[9];          /* high-water marks of the per-pipe staging buffers */
+  uint64_t      call_seq;       /* tickets of fec_cuda_submit_tbs */
+  uint32_t      pipe_next;      /* next slot of the pipe ring (runs on across calls) */
+  int           trace;          /* FEC_CUDA_TRACE=1: print the device timeline of every sub-batch to stderr */
+  cudaEvent_t   ev_call;        /* start of the current decode_tbs call (copy stream) */
+  double        t_call;         /* host clock at the start of the call */
 };
 
 static int pipes_create(fec_cuda_ctx_t *ctx);
+static double now_ms(void) { struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e3 + ts.tv_nsec / 1e6; }
 static void pipes_destroy(fec_cuda_ctx_t *ctx);
 
 static int fail(fec_cuda_ctx_t *c, int code, const char *fmt, ...)
@@ -287,7 +295,7 @@ static void fill_decode_args(fec_cuda_ctx_t *ctx, int k, FecDecodeArgs *a, const
   a->cbs = cbd_dev + off; a->status = status_dev;
   a->queue = queue3 + 2 * k; a->ncb = cnt; a->slots = t->slots; a->dbg_llr = dbg;
   a->pair_addr = t->d_pair_addr; a->pair_crc[0] = t->d_pair_crc[0]; a->pair_crc[1] = t->d_pair_crc[1];
-  a->soft_max = softmax;
+  a->soft_max = softmax; a->status_off = off;
   if (t->g.P && !ctx->force_exact && !dbg) { a->exact_list = exact + off; a->exact_count = queue3 + 2 * FEC_NOF_K + k; }
 }
 
@@ -308,15 +316,17 @@ struct fec_pipe {
   tbplan_t     *plan; size_t plan_cap;
   fec_cuda_tb_t *tbs; uint32_t n, ncb, ntb; int dev_io, busy;
   size_t        data_total;
+  uint64_t      call_id;        /* ticket of the call this sub-batch belongs to */
+  double        t_submit;       /* host time (ms since call start) when the sub-batch had been submitted */
 };
 
 static int pipe_init(fec_cuda_ctx_t *ctx, fec_pipe_t *p)
 {
   memset(p, 0, sizeof(*p));
   CU(cudaMalloc(&p->d_queue, sizeof(unsigned int) * 3 * FEC_NOF_K));
-  CU(cudaEventCreateWithFlags(&p->ev_in, cudaEventDisableTiming));
+  CU(cudaEventCreate(&p->ev_in));
   CU(cudaEventCreateWithFlags(&p->ev_k, cudaEventDisableTiming));
-  CU(cudaEventCreateWithFlags(&p->ev_done, cudaEventDisableTiming));
+  CU(cudaEventCreate(&p->ev_done));
   for (int i = 0; i < 4; i++) CU(cudaEventCreate(&p->ev[i]));
   return 0;
 }
@@ -370,13 +380,18 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
   uint32_t acc = 0;
   for (int k = 0; k < FEC_NOF_K; k++) { grp_off[k] = acc; grp_fill[k] = 0; acc += grp_cnt[k]; }
 
-  if (stage_reserve(ctx, &pp->st_cbd, sizeof(FecCbDesc) * (ncb + 1)) || stage_reserve(ctx, &pp->st_rmd, sizeof(FecRmDesc) * (ncb + 1)) ||
-      stage_reserve(ctx, &pp->st_tbd, sizeof(FecTbDesc) * ntb) || stage_reserve(ctx, &pp->st_status, sizeof(FecCbStatus) * (ncb + 1)) ||
-      stage_reserve(ctx, &pp->st_ret, sizeof(int32_t) * ntb) ||
-      dev_reserve(ctx, (void **)&pp->d_cbbytes, &pp->cbbytes_cap, (size_t)(ncb + 1) * CB_BYTES) ||
-      dev_reserve(ctx, (void **)&pp->d_softmax, &pp->softmax_cap, (size_t)(ncb + 1) * 4) ||
-      dev_reserve(ctx, (void **)&pp->d_exact, &pp->exact_cap, (size_t)(ncb + 1) * 4) ||
-      (!dev_io && (stage_reserve(ctx, &pp->st_e, e_total * 2) || stage_reserve(ctx, &pp->st_data, data_total)))) return FEC_CUDA_ENODEV;
+  /* every pipe of the ring is sized for the largest sub-batch seen so far: (re)allocation of pinned / device staging
+   * synchronises the device, so it must stop after the first calls */
+  size_t need[9] = { sizeof(FecCbDesc) * (ncb + 1), sizeof(FecRmDesc) * (ncb + 1), sizeof(FecTbDesc) * ntb, sizeof(FecCbStatus) * (ncb + 1),
+                     sizeof(int32_t) * ntb, (size_t)(ncb + 1) * CB_BYTES, (size_t)(ncb + 1) * 4, dev_io ? 0 : e_total * 2, dev_io ? 0 : data_total };
+  for (int i = 0; i < 9; i++) { if (need[i] > ctx->hw[i]) ctx->hw[i] = need[i]; need[i] = ctx->hw[i]; }
+  if (stage_reserve(ctx, &pp->st_cbd, need[0]) || stage_reserve(ctx, &pp->st_rmd, need[1]) ||
+      stage_reserve(ctx, &pp->st_tbd, need[2]) || stage_reserve(ctx, &pp->st_status, need[3]) ||
+      stage_reserve(ctx, &pp->st_ret, need[4]) ||
+      dev_reserve(ctx, (void **)&pp->d_cbbytes, &pp->cbbytes_cap, need[5]) ||
+      dev_reserve(ctx, (void **)&pp->d_softmax, &pp->softmax_cap, need[6]) ||
+      dev_reserve(ctx, (void **)&pp->d_exact, &pp->exact_cap, need[6]) ||
+      (!dev_io && (stage_reserve(ctx, &pp->st_e, need[7]) || stage_reserve(ctx, &pp->st_data, need[8])))) return FEC_CUDA_ENODEV;
 
   FecCbDesc *cbd = (FecCbDesc *)pp->st_cbd.h;
   FecRmDesc *rmd = (FecRmDesc *)pp->st_rmd.h;
@@ -458,11 +473,8 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
   CU(cudaMemsetAsync(pp->d_softmax, 0, (size_t)ncb * 4, sc));
   CU(cudaStreamWaitEvent(sc, pp->ev_in, 0));
   CU(cudaEventRecord(pp->ev[0], sc));
-  for (uint32_t o = 0; o < ncb; o += 32768) {                       /* grid.y limit */
-    const uint32_t m = ncb - o < 32768 ? ncb - o : 32768;
-    CU(fec_launch_rm((const FecRmDesc *)pp->st_rmd.d + o, pp->d_softmax, m, max_n_out, sc));
-    ctx->launches++;
-  }
+  CU(fec_launch_rm((const FecRmDesc *)pp->st_rmd.d, pp->d_softmax, ncb, max_n_out, sc));
+  ctx->launches++;
   CU(cudaEventRecord(pp->ev[1], sc));
   for (int k = 0; k < FEC_NOF_K; k++) {
     if (!grp_cnt[k]) continue;
@@ -485,6 +497,7 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
   if (!dev_io) CU(cudaMemcpyAsync(pp->st_data.h, pp->st_data.d, data_total, cudaMemcpyDeviceToHost, sout));
   CU(cudaEventRecord(pp->ev_done, sout));
   pp->ncb = ncb; pp->ntb = ntb; pp->data_total = data_total; pp->busy = 1;
+  pp->t_submit = now_ms() - ctx->t_call;
   return 0;
 }
 
@@ -496,6 +509,14 @@ static int pipe_finish(fec_cuda_ctx_t *ctx, fec_pipe_t *pp)
   pp->busy = 0;
   CU(cudaEventSynchronize(pp->ev_done));
   for (int i = 0; i < 3; i++) { float ms = 0; if (cudaEventElapsedTime(&ms, pp->ev[i], pp->ev[i + 1]) == cudaSuccess) ctx->phase_ms[i] += ms; }
+  if (ctx->trace) {
+    float t[6] = {0, 0, 0, 0, 0, 0};
+    cudaEventElapsedTime(&t[0], ctx->ev_call, pp->ev_in);
+    for (int i = 0; i < 4; i++) cudaEventElapsedTime(&t[1 + i], ctx->ev_call, pp->ev[i]);
+    cudaEventElapsedTime(&t[5], ctx->ev_call, pp->ev_done);
+    fprintf(stderr, "[fec trace] sub-batch %u TBs %u CBs: submitted@%.3f h2d_done %.3f | rm %.3f-%.3f | dec -%.3f | asm -%.3f | d2h_done %.3f | host now %.3f ms\n",
+            pp->n, pp->ncb, pp->t_submit, t[0], t[1], t[2], t[3], t[4], t[5], now_ms() - ctx->t_call);
+  }
   const FecCbStatus *stt = (const FecCbStatus *)pp->st_status.h;
   const FecTbDesc *tbd = (const FecTbDesc *)pp->st_tbd.h;
   uint32_t itb = 0;
@@ -536,6 +557,9 @@ static int pipes_create(fec_cuda_ctx_t *ctx)
   sb = getenv("FEC_CUDA_SUB_TBS_DEV");
   ctx->sub_tbs_dev = sb ? (uint32_t)atoi(sb) : 592;
   if (ctx->sub_tbs_dev == 0) ctx->sub_tbs_dev = 592;
+  sb = getenv("FEC_CUDA_TRACE");
+  ctx->trace = sb ? atoi(sb) : 0;
+  CU(cudaEventCreate(&ctx->ev_call));
   return 0;
 }
 
@@ -549,28 +573,54 @@ static void pipes_destroy(fec_cuda_ctx_t *ctx)
   if (ctx->s_comp[1]) cudaStreamDestroy(ctx->s_comp[1]);
 }
 
-extern "C" int fec_cuda_decode_tbs(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, uint32_t n, uint32_t flags)
+extern "C" int fec_cuda_submit_tbs(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, uint32_t n, uint32_t flags, uint64_t *ticket)
 {
   if (!ctx || (!tbs && n)) return FEC_CUDA_EINVAL;
+  const uint64_t id = ++ctx->call_seq;
+  if (ticket) *ticket = id;
   if (n == 0) return 0;
   cudaSetDevice(ctx->device);
   ctx->phase_ms[0] = ctx->phase_ms[1] = ctx->phase_ms[2] = 0; ctx->ev_valid = 1;
-  /* sub-batch size: big enough to fill the GPU for several waves, small enough to pipeline */
+  ctx->t_call = now_ms();
+  if (ctx->trace) CU(cudaEventRecord(ctx->ev_call, ctx->s_copy));
   /* host buffers: small sub-batches so that the PCIe copy of one overlaps the kernels of the previous (the copy is
-   * the longer of the two); device buffers: nothing to overlap but host-side descriptor work, and every launch pays
-   * one ragged tail (the slowest code blocks run 8 half-iterations), so use few, large sub-batches */
+   * the longer of the two); device buffers: nothing to overlap but host-side descriptor work, so few, large ones */
   const uint32_t sub = (flags & FEC_CUDA_F_DEVICE_IO) ? ctx->sub_tbs_dev : ctx->sub_tbs;
-  uint32_t nsub = (flags & FEC_CUDA_F_SERIAL) ? 1 : (n + sub - 1) / sub;
-  const uint32_t per = (n + nsub - 1) / nsub;
   int rc = 0;
-  uint32_t s = 0;
-  for (uint32_t off = 0; off < n && !rc; off += per, s++) {
-    fec_pipe_t *pp = &ctx->pipes[s % FEC_NPIPE];
-    rc = pipe_finish(ctx, pp);
-    if (!rc) rc = pipe_submit(ctx, pp, tbs + off, n - off < per ? n - off : per, flags, ctx->s_comp[s & 1]);
+  uint32_t s = 0, off = 0;
+  while (off < n && !rc) {
+    /* ramp: the first sub-batches are small so that the GPU starts after a short descriptor build and a short rate
+     * de-matching launch; everything after that is hidden behind the kernels of the previous sub-batch */
+    uint32_t cnt = (flags & FEC_CUDA_F_SERIAL) ? n : (s == 0 ? sub / 4 : s == 1 ? sub / 2 : sub);
+    if (cnt == 0) cnt = 1;
+    if (n - off < cnt + cnt / 2) cnt = n - off;          /* no tiny last sub-batch */
+    const uint32_t slot = ctx->pipe_next++;
+    fec_pipe_t *pp = &ctx->pipes[slot % FEC_NPIPE];
+    rc = pipe_finish(ctx, pp);                           /* ring full: the oldest sub-batch (maybe of an earlier call) completes first */
+    if (!rc) { pp->call_id = id; rc = pipe_submit(ctx, pp, tbs + off, cnt, flags, ctx->s_comp[slot & 1]); }
+    off += cnt; s++;
   }
-  for (uint32_t i = 0; i < FEC_NPIPE; i++) { const int r2 = pipe_finish(ctx, &ctx->pipes[(s + i) % FEC_NPIPE]); if (!rc) rc = r2; }
   return rc;
+}
+
+extern "C" int fec_cuda_wait(fec_cuda_ctx_t *ctx, uint64_t ticket)
+{
+  if (!ctx) return FEC_CUDA_EINVAL;
+  cudaSetDevice(ctx->device);
+  int rc = 0;
+  for (uint32_t i = 0; i < FEC_NPIPE; i++) {             /* oldest first */
+    fec_pipe_t *pp = &ctx->pipes[(ctx->pipe_next + i) % FEC_NPIPE];
+    if (pp->busy && pp->call_id <= ticket) { const int r2 = pipe_finish(ctx, pp); if (!rc) rc = r2; }
+  }
+  return rc;
+}
+
+extern "C" int fec_cuda_decode_tbs(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, uint32_t n, uint32_t flags)
+{
+  uint64_t ticket = 0;
+  const int rc = fec_cuda_submit_tbs(ctx, tbs, n, flags, &ticket);
+  const int r2 = fec_cuda_wait(ctx, ticket);
+  return rc ? rc : r2;
 }
 
 /* ---------------------------------------------------------------- bare code blocks (srslte_tdec_* level) ---- */

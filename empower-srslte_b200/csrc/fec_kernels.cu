@@ -494,8 +494,7 @@ cudaError_t fec_launch_decode(const FecDecodeArgs &a, int sm_count, cudaStream_t
 
 /* =====================================================================================================
  * Rate de-matching + HARQ combining as a GATHER over soft-buffer positions (rm_turbo.c:378-430 computes
- * the same sums as a scatter: soft[deinter[i % N]] += e[i]). Thread = 8 consecutive int16 of the slot:
- * one 16-byte load of the rank table, one 16-byte read-modify-write of the slot, coalesced.
+ * the same sums as a scatter: soft[deinter[i % N]] += e[i]).
  * ===================================================================================================== */
 __device__ __forceinline__ void fec_softmax_commit(uint32_t *dst, int amax)
 {
@@ -504,36 +503,58 @@ __device__ __forceinline__ void fec_softmax_commit(uint32_t *dst, int amax)
   if ((threadIdx.x & 31) == 0 && amax > 0) atomicMax(dst, (uint32_t)amax);
 }
 
-__global__ void __launch_bounds__(256) fec_rm_rx_kernel(const FecRmDesc *descs, uint32_t *soft_max)
+/* One CTA per code block. The received LLRs are staged in shared memory in CIRCULAR-BUFFER order (entry p of the
+ * NULL-free buffer <- e[i], p = (i + k0 offset of the rv) mod N; i, i+N, i+2N... are the repeats of one entry and are
+ * summed in the reference's order; entries never transmitted are 0): a coalesced read and a conflict-free write.
+ * The slot is then produced 16 bytes per thread: the per-K rank table (device offset -> p) turns the sub-block
+ * de-interleaving into a gather from shared memory, added to the old content for a retransmission, and written
+ * coalesced together with max |entry|. HBM traffic = the algorithmic minimum (2E bytes in, the slot out / in+out). */
+__global__ void __launch_bounds__(FEC_RM_THREADS) fec_rm_rx_kernel(const FecRmDesc *descs, uint32_t *soft_max)
 {
-  const FecRmDesc d = descs[blockIdx.y];
-  const uint32_t o = (blockIdx.x * blockDim.x + threadIdx.x) * 8;
-  int amax = 0;
-  if (o < d.n_out) {
-  const uint4 rk = *reinterpret_cast<const uint4 *>(d.rank + o);
-  uint4 old = make_uint4(0, 0, 0, 0);
-  if (!d.new_data) old = *reinterpret_cast<const uint4 *>(d.soft + o);
-  const uint32_t rw[4] = {rk.x, rk.y, rk.z, rk.w};
-  uint32_t ow[4] = {old.x, old.y, old.z, old.w};
+  extern __shared__ __align__(16) int16_t rm_tile[];
+  const FecRmDesc d = descs[blockIdx.x];
+  const int tid = threadIdx.x;
+  if (d.E <= d.N) {
+    /* the common case (no repetition): a plain rotated copy, 8 independent loads in flight per thread */
+    const uint32_t wrap = d.N - d.off;                 /* entries i >= wrap land at p = i - wrap */
+    for (uint32_t i0 = tid; i0 < d.E; i0 += 8 * FEC_RM_THREADS) {
+      int16_t v[8];
 #pragma unroll
-  for (int i = 0; i < 4; i++) {
-    uint32_t res = 0;
+      for (int u = 0; u < 8; u++) { const uint32_t i = i0 + u * FEC_RM_THREADS; v[u] = i < d.E ? __ldg(d.e + i) : (int16_t)0; }
 #pragma unroll
-    for (int h = 0; h < 2; h++) {
-      const uint32_t r = (rw[i] >> (16 * h)) & 0xFFFFu;
-      int acc = (int)((ow[i] >> (16 * h)) & 0xFFFFu);
-      if (r != 0xFFFFu) {
-        uint32_t j = r + d.N - d.off;
-        if (j >= d.N) j -= d.N;
-        for (; j < d.E; j += d.N) acc += (int)__ldg(d.e + j);      /* repeats accumulate when E > 3K+12 */
-      }
-      res |= ((uint32_t)acc & 0xFFFFu) << (16 * h);               /* wrapping int16 */
-      const int sv = (int)(short)acc;
-      amax = max(amax, sv < 0 ? -sv : sv);
+      for (int u = 0; u < 8; u++) { const uint32_t i = i0 + u * FEC_RM_THREADS; if (i < d.E) rm_tile[i < wrap ? i + d.off : i - wrap] = v[u]; }
     }
-    ow[i] = res;
+    for (uint32_t i = d.E + tid; i < d.N; i += FEC_RM_THREADS) rm_tile[i < wrap ? i + d.off : i - wrap] = 0;   /* never transmitted */
+  } else {
+    for (uint32_t i = tid; i < d.N; i += FEC_RM_THREADS) {
+      int acc = 0;
+      for (uint32_t j = i; j < d.E; j += d.N) acc += (int)__ldg(d.e + j);    /* repeats accumulate when E > 3K+12 */
+      uint32_t p = i + d.off;
+      if (p >= d.N) p -= d.N;
+      rm_tile[p] = (int16_t)acc;
+    }
   }
-  *reinterpret_cast<uint4 *>(d.soft + o) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+  __syncthreads();
+  const uint4 *rank4 = reinterpret_cast<const uint4 *>(d.rank);
+  uint4 *soft4 = reinterpret_cast<uint4 *>(d.soft);
+  int amax = 0;
+#pragma unroll 2
+  for (int v = tid; v < (int)d.n_out / 8; v += FEC_RM_THREADS) {
+    const uint4 rk = __ldg(rank4 + v);
+    uint4 old = make_uint4(0, 0, 0, 0);
+    if (!d.new_data) old = soft4[v];
+    const uint32_t rw[4] = {rk.x, rk.y, rk.z, rk.w};
+    uint32_t ow[4] = {old.x, old.y, old.z, old.w};
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const uint32_t r0 = rw[k] & 0xFFFFu, r1 = rw[k] >> 16;
+      const int a0 = (int)(short)(ow[k] & 0xFFFFu) + (r0 != 0xFFFFu ? (int)rm_tile[r0] : 0);
+      const int a1 = ((int)ow[k] >> 16) + (r1 != 0xFFFFu ? (int)rm_tile[r1] : 0);
+      const int s0 = (int)(short)a0, s1 = (int)(short)a1;                    /* wrapping int16 (rm_turbo.c:411-420) */
+      ow[k] = ((uint32_t)s0 & 0xFFFFu) | ((uint32_t)s1 << 16);
+      amax = max(amax, max(s0 < 0 ? -s0 : s0, s1 < 0 ? -s1 : s1));
+    }
+    soft4[v] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
   }
   fec_softmax_commit(soft_max + d.slot, amax);
 }
@@ -541,8 +562,7 @@ __global__ void __launch_bounds__(256) fec_rm_rx_kernel(const FecRmDesc *descs, 
 cudaError_t fec_launch_rm(const FecRmDesc *descs, uint32_t *soft_max, uint32_t n, uint32_t max_n_out, cudaStream_t st)
 {
   if (n == 0) return cudaSuccess;
-  dim3 grid((max_n_out / 8 + 255) / 256, n);
-  fec_rm_rx_kernel<<<grid, 256, 0, st>>>(descs, soft_max);
+  fec_rm_rx_kernel<<<n, FEC_RM_THREADS, (size_t)max_n_out * 2, st>>>(descs, soft_max);   /* N = 3K+12 <= n_out */
   return cudaGetLastError();
 }
 

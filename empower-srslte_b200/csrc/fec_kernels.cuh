@@ -40,6 +40,7 @@ struct FecDecodeArgs {
   /* packed fast path (fec_tdec_packed.cu) */
   const uint32_t   *pair_addr;  /* decoder-2 address words, (P/2) x Lp */
   const uint2      *pair_crc[2];/* CRC syndrome words per polynomial, [2 parities][(P/2) x Lp] */
+  uint32_t          status_off; /* status / soft_max index of cbs[0] (cbs[q].status == status_off + q) */
   const uint32_t   *soft_max;   /* per status slot: max |soft-buffer entry| of the code block (rate de-matching / extract kernel) */
   uint32_t         *exact_list; /* out: code blocks (indices into cbs) outside the proven range -> exact kernel */
   unsigned int     *exact_count;
@@ -49,10 +50,11 @@ struct FecDecodeArgs {
 };
 
 /* one code block of a rate-dematching launch */
+#define FEC_RM_THREADS 256
 struct FecRmDesc {
   const int16_t  *e;        /* E transmitted LLRs of this CB */
   int16_t        *soft;     /* device-layout slot, read-modify-write */
-  const uint16_t *rank;     /* per-K rank table in device layout */
+  const uint16_t *rank;     /* per-K table in device layout: soft offset -> entry of the NULL-free circular buffer (0xFFFF: none) */
   uint32_t        E;
   uint32_t        N;        /* 3K+12 */
   uint32_t        off;      /* start rank for this rv */

@@ -60,6 +60,20 @@ __device__ __forceinline__ void pk_sts_u16(uint32_t addr, uint32_t val)
 
 /* scheduling fence: ptxas does not move memory instructions across a warp barrier, which keeps the prefetch
  * loads where they are issued in the source (it otherwise sinks them to the register rotation at the loop end) */
+#ifndef PK_OPT_DESC
+#define PK_OPT_DESC 1
+#endif
+#ifndef PK_OPT_EPI
+#define PK_OPT_EPI 0
+#endif
+#ifndef PK_EPI_NOINLINE
+#define PK_EPI_NOINLINE 1
+#endif
+#if PK_EPI_NOINLINE
+#define PK_EPI_INLINE __noinline__
+#else
+#define PK_EPI_INLINE __forceinline__
+#endif
 #ifndef PK_CRC64
 #define PK_CRC64 1       /* CRC syndrome words by 8-byte instead of 16-byte loads */
 #endif
@@ -474,11 +488,14 @@ __device__ __forceinline__ void pk_write_output(const uint32_t *rows, int nw1, i
 {
   const int nwords = K >> 5;
   uint32_t *out32 = reinterpret_cast<uint32_t *>(out);
+  int d = (j << 5) / L, k = (j << 5) - d * L;
   for (int ow = j; ow < nwords; ow += TPC) {
-    const int p = ow << 5, d = p / L, k = p - d * L, avail = L - k;
+    const int avail = L - k;
     uint32_t w = pk_row_bits(rows + d * nw1, k + pad);
     if (avail < 32) w = (w & ~(0xFFFFFFFFu >> avail)) | (pk_row_bits(rows + (d + 1) * nw1, pad) >> avail);
     out32[ow] = __byte_perm(w, 0, 0x0123);
+    k += 32 * TPC;
+    while (k >= L) { k -= L; d++; }
   }
   for (int ob = (nwords << 2) + j; ob < (K >> 3); ob += TPC) {      /* K/8 not a multiple of 4: last 1..3 bytes */
     const int p = ob << 3, d = p / L, k = p - d * L, avail = L - k;
@@ -486,6 +503,52 @@ __device__ __forceinline__ void pk_write_output(const uint32_t *rows, int nw1, i
     if (avail < 8) w = (w & ~(0xFFFFFFFFu >> avail)) | (pk_row_bits(rows + (d + 1) * nw1, pad) >> avail);
     out[ob] = (uint8_t)(w >> 24);
   }
+}
+
+/* A finished code block: natural-order bit rows (decoder 2 leaves them in interleaved order) and the output bytes.
+ * Kept out of line so that this cold code does not take part in the register allocation of the trellis loops. */
+template <int TPC>
+__device__ PK_EPI_INLINE void pk_finish_block(int par, uint32_t Eb, const uint16_t *Tlo, const uint16_t *Thi, const uint32_t *erow,
+                                              uint32_t *blo, uint32_t *bhi, const uint32_t *rows, int nw1, int pad, int K, int L, int j,
+                                              unsigned gmask, uint8_t *out)
+{
+    if (par) {
+      /* decisions are in interleaved order: spread them to natural positions through the (now dead) E array,
+       * then rebuild the natural bit rows */
+#if PK_OPT_EPI
+      /* loop 1: a halfword whose bit 15 is the decision goes to the natural position (one rotate per lane and step);
+       * loop 2: the natural rows are rebuilt from bits 15 / 31 of the pair words */
+      for (int w0 = 0; w0 < L + pad; w0 += 32) {
+        const uint32_t wl = blo[w0 >> 5], wh = bhi[w0 >> 5];
+#pragma unroll 8
+        for (int b = 0; b < 32; b++) {
+          const int k = w0 + b - pad;
+          if (k >= 0 && k < L) {
+            pk_sts_u16(Eb + Tlo[k], __funnelshift_r(wl, wl, (16 - b) & 31));
+            pk_sts_u16(Eb + Thi[k], __funnelshift_r(wh, wh, (16 - b) & 31));
+          }
+        }
+      }
+#else
+      for (int k = 0; k < L; k++) {
+        const int kb = k + pad;
+        pk_sts_u16(Eb + Tlo[k], 0u - ((blo[kb >> 5] >> (31 - (kb & 31))) & 1u));
+        pk_sts_u16(Eb + Thi[k], 0u - ((bhi[kb >> 5] >> (31 - (kb & 31))) & 1u));
+      }
+#endif
+      __syncwarp(gmask);
+      uint32_t wlo = 0, whi = 0;
+      #pragma unroll 4
+      for (int k = 0; k < L; k++) {
+        const int kb = k + pad;
+        const uint32_t w = erow[k];
+        wlo = __funnelshift_l(w << 16, wlo, 1); whi = __funnelshift_l(w, whi, 1);
+        if ((kb & 31) == 31) { blo[kb >> 5] = wlo; bhi[kb >> 5] = whi; }
+      }
+      if ((L + pad) & 31) { const int sh = 32 - ((L + pad) & 31); blo[(L + pad) >> 5] = wlo << sh; bhi[(L + pad) >> 5] = whi << sh; }
+    }
+    __syncwarp(gmask);
+    pk_write_output<TPC>(rows, nw1, pad, K, L, j, out);
 }
 
 /* ---------------------------------------------------------------- the kernel ---- */
@@ -502,6 +565,7 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
   constexpr int TPC = P / 2, CPW = 32 / TPC;
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ uint32_t s_tmem;
+  __shared__ __align__(16) FecCbDesc s_desc[FEC_PK_WARPS * (32 / (P / 2))];   /* descriptor of the code block in each slot */
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane / TPC, j = lane % TPC;
   const int K = a.g.K, L = a.g.L, Lp = a.g.Lp, Lw = a.g.Lw, SS = a.g.SS;
   const int nw1 = (L + 31) / 32 + 1, Es = TPC * Lw + 1, nslots = FEC_PK_WARPS * CPW, slot = warp * CPW + g;
@@ -526,6 +590,8 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tbase = s_tmem + ((uint32_t)(warp * 32) << 16);
 
+  if (j == 0) s_desc[slot] = a.cbs[0];
+  __syncwarp();
   int cb = -1, n = 0;
   uint32_t M = 0;
   bool exhausted = false;
@@ -536,7 +602,18 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
       if (j == 0) q = atomicAdd(a.queue, 1u);
       q = __shfl_sync(gmask, q, g * TPC);
       if (q >= a.ncb) { exhausted = true; break; }
+#if PK_OPT_DESC
+      {
+        /* descriptor (32 bytes, lanes 0/1 of the group) and max|soft| are fetched side by side */
+        const uint4 *src = reinterpret_cast<const uint4 *>(a.cbs + q);
+        uint4 dq = make_uint4(0, 0, 0, 0);
+        if (j < 2) dq = pk_ldg128(src + j);
+        M = a.soft_max[a.status_off + q];
+        if (j < 2) reinterpret_cast<uint4 *>(&s_desc[slot])[j] = dq;
+      }
+#else
       M = a.soft_max[a.cbs[q].status];
+#endif
       if (2 * M > FEC_PK_GMAX) {                    /* first half-iteration already outside the proven range */
         if (j == 0) a.exact_list[atomicAdd(a.exact_count, 1u)] = q;
         continue;
@@ -550,7 +627,12 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
     /* ---- one half-iteration for every slot of the warp; idle slots run on code block 0's inputs and their
      *      own scratch E (keeps the warp convergent for the .aligned tensor-memory accesses), results dropped ---- */
     const bool active = cb >= 0;
+#if PK_OPT_DESC
+    __syncwarp();
+    const FecCbDesc desc = s_desc[slot];             /* idle slots keep their last (or code block 0's) descriptor */
+#else
     const FecCbDesc desc = a.cbs[active ? cb : 0];
+#endif
     const int par = n & 1;
     PkView v;
     v.par = par;
@@ -578,26 +660,7 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
       const int n1 = n + 1, crc_ok = (crc == 0);
       const bool done = (crc_ok && !(desc.flags & FEC_F_NO_EARLY)) || (n1 >= (int)desc.max_its);
       if (done) {
-        if (par) {
-          /* decisions are in interleaved order: spread them to natural positions through the (now dead) E array,
-           * then rebuild the natural bit rows */
-          for (int k = 0; k < L; k++) {
-            const int kb = k + pad;
-            pk_sts_u16(v.Eb + v.Tlo[k], 0u - ((blo[kb >> 5] >> (31 - (kb & 31))) & 1u));
-            pk_sts_u16(v.Eb + v.Thi[k], 0u - ((bhi[kb >> 5] >> (31 - (kb & 31))) & 1u));
-          }
-          __syncwarp(gmask);
-          uint32_t wlo = 0, whi = 0;
-          for (int k = 0; k < L; k++) {
-            const int kb = k + pad;
-            const uint32_t w = Eslot[j * Lw + k];
-            wlo = __funnelshift_l(w << 16, wlo, 1); whi = __funnelshift_l(w, whi, 1);
-            if ((kb & 31) == 31) { blo[kb >> 5] = wlo; bhi[kb >> 5] = whi; }
-          }
-          if ((L + pad) & 31) { const int sh = 32 - ((L + pad) & 31); blo[(L + pad) >> 5] = wlo << sh; bhi[(L + pad) >> 5] = whi << sh; }
-        }
-        __syncwarp(gmask);
-        pk_write_output<TPC>(rows, nw1, pad, K, L, j, desc.out);
+        pk_finish_block<TPC>(par, v.Eb, v.Tlo, v.Thi, Eslot + j * Lw, blo, bhi, rows, nw1, pad, K, L, j, gmask, desc.out);
         if (j == 0) { a.status[desc.status].its = (uint32_t)n1; a.status[desc.status].crc_ok = (uint32_t)crc_ok; }
         __syncwarp(gmask);
         cb = -1;
@@ -639,7 +702,14 @@ cudaError_t fec_launch_decode_packed(const FecDecodeArgs &a, int sm_count, cudaS
 
 template <int P, bool VEC> static cudaError_t pk_attr()
 {
-  return cudaFuncSetAttribute(fec_tdec_pk_kernel<P, VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+  /* opt in to everything the SM has: 227 KB per block minus this kernel's static (and system-reserved) shared memory */
+  cudaFuncAttributes fa;
+  cudaError_t e = cudaFuncGetAttributes(&fa, fec_tdec_pk_kernel<P, VEC>);
+  if (e != cudaSuccess) return e;
+  int dev = 0, optin = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  return cudaFuncSetAttribute(fec_tdec_pk_kernel<P, VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin - (int)fa.sharedSizeBytes);
 }
 
 cudaError_t fec_pk_init(void)

@@ -107,6 +107,15 @@ int  fec_cuda_softbuffer_read_ref_layout(fec_cuda_ctx_t *ctx, uint32_t id, uint3
  * returns 0 unless the batch could not be run at all. */
 int  fec_cuda_decode_tbs(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, uint32_t n, uint32_t flags);
 
+/* The same call split in two, for a caller that has the next batch ready before the previous one is done (a PHY worker
+ * per subframe, as srsENB's phch_worker pool): submit enqueues the batch and returns; wait(ticket) blocks until that batch
+ * and every earlier one is complete and their outputs are in place. fec_cuda_decode_tbs == submit + wait. Up to two
+ * batches in flight overlap one batch's ragged tail (the few code blocks that run all their half-iterations) with the
+ * next batch's bulk. tbs[] and every buffer it points to must stay valid until the wait; two batches in flight must
+ * not share soft buffers. One submitting thread per context. */
+int  fec_cuda_submit_tbs(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, uint32_t n, uint32_t flags, uint64_t *ticket);
+int  fec_cuda_wait(fec_cuda_ctx_t *ctx, uint64_t ticket);
+
 /* bare turbo decoding of n code blocks from natural-layout LLRs (host pointers) */
 int  fec_cuda_decode_cbs(fec_cuda_ctx_t *ctx, fec_cuda_cb_t *cbs, uint32_t n, uint32_t flags);
 

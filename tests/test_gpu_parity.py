@@ -163,3 +163,35 @@ def test_invalid_inputs(fec):
     r = fec.decode_tb(6120 + 8, 2, 0, np.zeros(20000, np.int16), sb, True)   # B'=6176 -> F != 0 not supported
     seg = pkg.cbsegm(6128)
     assert (seg["F"] != 0) == (r["ret"] == -2)
+
+
+def test_submit_wait_two_batches_in_flight(fec):
+    """fec_cuda_submit_tbs / fec_cuda_wait: two batches in flight (own soft buffers) give the golden results"""
+    pkg = importlib.import_module("empower-srslte_b200")
+    cases = list(G.tb_cases())
+    reps = 40                                   # enough transport blocks per batch to span several sub-batches
+    batches = []
+    for half in range(2):
+        mine = [c for i, c in enumerate(cases) if i % 2 == half] * reps
+        sb0 = fec.softbuffer_alloc(len(mine))
+        d = (pkg.TbDesc * len(mine))()
+        outs = []
+        for slot, c in enumerate(mine):
+            tx = c["tx"][0]
+            out = np.zeros(c["tbs"] // 8 + 3 + 768, np.uint8)
+            outs.append(out)
+            d[slot].tbs, d[slot].Qm, d[slot].rv, d[slot].nof_e_bits, d[slot].max_its = c["tbs"], c["Qm"], tx["rv"], c["nbits"], c["max_its"]
+            d[slot].softbuffer, d[slot].new_data = sb0 + slot, 1
+            d[slot].e_bits, d[slot].data = tx["llr"].ctypes.data, out.ctypes.data
+        batches.append((mine, d, outs))
+    t0 = fec.submit_tbs(batches[0][1])
+    t1 = fec.submit_tbs(batches[1][1])
+    assert t1 == t0 + 1
+    fec.wait(t0)
+    fec.wait(t1)
+    for mine, d, outs in batches:
+        for slot, c in enumerate(mine):
+            tx = c["tx"][0]
+            assert d[slot].ret == tx["ret"]
+            assert (outs[slot][: c["tbs"] // 8 + 3] == tx["data"][: c["tbs"] // 8 + 3]).all()
+            assert list(d[slot].cb_its)[: len(tx["its"])] == [int(v) for v in tx["its"]][:13]
