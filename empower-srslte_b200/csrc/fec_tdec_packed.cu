@@ -63,9 +63,6 @@ __device__ __forceinline__ void pk_sts_u16(uint32_t addr, uint32_t val)
 #ifndef PK_OPT_DESC
 #define PK_OPT_DESC 1
 #endif
-#ifndef PK_OPT_EPI
-#define PK_OPT_EPI 0
-#endif
 #ifndef PK_EPI_NOINLINE
 #define PK_EPI_NOINLINE 1
 #endif
@@ -513,37 +510,49 @@ __device__ PK_EPI_INLINE void pk_finish_block(int par, uint32_t Eb, const uint16
                                               unsigned gmask, uint8_t *out)
 {
     if (par) {
-      /* decisions are in interleaved order: spread them to natural positions through the (now dead) E array,
-       * then rebuild the natural bit rows */
-#if PK_OPT_EPI
-      /* loop 1: a halfword whose bit 15 is the decision goes to the natural position (one rotate per lane and step);
-       * loop 2: the natural rows are rebuilt from bits 15 / 31 of the pair words */
-      for (int w0 = 0; w0 < L + pad; w0 += 32) {
-        const uint32_t wl = blo[w0 >> 5], wh = bhi[w0 >> 5];
-#pragma unroll 8
-        for (int b = 0; b < 32; b++) {
-          const int k = w0 + b - pad;
-          if (k >= 0 && k < L) {
-            pk_sts_u16(Eb + Tlo[k], __funnelshift_r(wl, wl, (16 - b) & 31));
-            pk_sts_u16(Eb + Thi[k], __funnelshift_r(wh, wh, (16 - b) & 31));
+      /* decisions are in interleaved order: spread them to natural positions through the (now dead) E array
+       * (a halfword whose bit 15 is the decision), then rebuild the natural bit rows from bits 15 / 31 of the pair
+       * words. Both loops work on 8 steps at a time, all loads first: with one warp per scheduler a load-use
+       * pair per step costs a full shared-memory latency. */
+      if ((L & 3) == 0) {
+        for (int k0 = 0; k0 < L; k0 += 8) {
+          const int kb = k0 + pad, wi = kb >> 5, sh = kb & 31;
+          const bool two = k0 + 4 < L;
+          const uint2 tl0 = *reinterpret_cast<const uint2 *>(Tlo + k0), th0 = *reinterpret_cast<const uint2 *>(Thi + k0);
+          uint2 tl1 = tl0, th1 = th0;
+          if (two) { tl1 = *reinterpret_cast<const uint2 *>(Tlo + k0 + 4); th1 = *reinterpret_cast<const uint2 *>(Thi + k0 + 4); }
+          const uint32_t fl = __funnelshift_l(blo[wi + 1], blo[wi], sh), fh = __funnelshift_l(bhi[wi + 1], bhi[wi], sh);   /* steps k0.. at bits 31.. */
+          const uint32_t ol[8] = {tl0.x & 0xFFFFu, tl0.x >> 16, tl0.y & 0xFFFFu, tl0.y >> 16, tl1.x & 0xFFFFu, tl1.x >> 16, tl1.y & 0xFFFFu, tl1.y >> 16};
+          const uint32_t oh[8] = {th0.x & 0xFFFFu, th0.x >> 16, th0.y & 0xFFFFu, th0.y >> 16, th1.x & 0xFFFFu, th1.x >> 16, th1.y & 0xFFFFu, th1.y >> 16};
+#pragma unroll
+          for (int i = 0; i < 8; i++) {
+            if (i < 4 || two) {
+              pk_sts_u16(Eb + ol[i], fl >> (16 - i));
+              pk_sts_u16(Eb + oh[i], fh >> (16 - i));
+            }
           }
         }
+      } else {
+        for (int k = 0; k < L; k++) {
+          const int kb = k + pad;
+          pk_sts_u16(Eb + Tlo[k], 0u - ((blo[kb >> 5] >> (31 - (kb & 31))) & 1u));
+          pk_sts_u16(Eb + Thi[k], 0u - ((bhi[kb >> 5] >> (31 - (kb & 31))) & 1u));
+        }
       }
-#else
-      for (int k = 0; k < L; k++) {
-        const int kb = k + pad;
-        pk_sts_u16(Eb + Tlo[k], 0u - ((blo[kb >> 5] >> (31 - (kb & 31))) & 1u));
-        pk_sts_u16(Eb + Thi[k], 0u - ((bhi[kb >> 5] >> (31 - (kb & 31))) & 1u));
-      }
-#endif
       __syncwarp(gmask);
       uint32_t wlo = 0, whi = 0;
-      #pragma unroll 4
-      for (int k = 0; k < L; k++) {
-        const int kb = k + pad;
-        const uint32_t w = erow[k];
-        wlo = __funnelshift_l(w << 16, wlo, 1); whi = __funnelshift_l(w, whi, 1);
-        if ((kb & 31) == 31) { blo[kb >> 5] = wlo; bhi[kb >> 5] = whi; }
+      for (int k0 = 0; k0 < L; k0 += 8) {
+        uint32_t w[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) w[i] = (k0 + i < L) ? erow[k0 + i] : 0u;
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+          if (k0 + i < L) {
+            const int kb = k0 + i + pad;
+            wlo = __funnelshift_l(w[i] << 16, wlo, 1); whi = __funnelshift_l(w[i], whi, 1);
+            if ((kb & 31) == 31) { blo[kb >> 5] = wlo; bhi[kb >> 5] = whi; }
+          }
+        }
       }
       if ((L + pad) & 31) { const int sh = 32 - ((L + pad) & 31); blo[(L + pad) >> 5] = wlo << sh; bhi[(L + pad) >> 5] = whi << sh; }
     }
