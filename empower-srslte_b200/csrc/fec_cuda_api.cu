@@ -58,7 +58,8 @@ struct fec_cuda_ctx {
   int16_t      *d_dbg; size_t dbg_cap; uint32_t *dbg_slot; uint32_t dbg_n;   /* test hook: LLR dump */
   float         phase_ms[3];   /* device time of rm | decode | assemble summed over the sub-batches of the last decode_tbs call */
   int           ev_valid;
-  cudaStream_t  s_copy, s_out, s_comp[2];
+  cudaStream_t  s_copy, s_out, s_rm, s_comp[2];
+  int           ramp;           /* FEC_CUDA_RAMP=1: small first sub-batches (measured slower on B200, off by default) */
   fec_pipe_t   *pipes;
   uint32_t      sub_tbs, sub_tbs_dev;
   size_t        hw[9];          /* high-water marks of the per-pipe staging buffers */
@@ -469,13 +470,17 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
   CU(cudaEventRecord(pp->ev_in, sin));
 
   /* ---- compute stream: rate de-matching, turbo decode per K group, TB assembly + CRC24A ---- */
-  CU(cudaMemsetAsync(pp->d_queue, 0, sizeof(unsigned int) * 3 * FEC_NOF_K, sc));
-  CU(cudaMemsetAsync(pp->d_softmax, 0, (size_t)ncb * 4, sc));
-  CU(cudaStreamWaitEvent(sc, pp->ev_in, 0));
-  CU(cudaEventRecord(pp->ev[0], sc));
-  CU(fec_launch_rm((const FecRmDesc *)pp->st_rmd.d, pp->d_softmax, ncb, max_n_out, sc));
+  /* rate de-matching has its own stream: it depends on nothing but its inputs, so it must not queue up behind the
+   * decode kernel of an earlier sub-batch (which can hold a compute stream for the length of its slowest code block) */
+  cudaStream_t srm = (flags & FEC_CUDA_F_SERIAL) ? sc : ctx->s_rm;
+  CU(cudaMemsetAsync(pp->d_queue, 0, sizeof(unsigned int) * 3 * FEC_NOF_K, srm));
+  CU(cudaMemsetAsync(pp->d_softmax, 0, (size_t)ncb * 4, srm));
+  CU(cudaStreamWaitEvent(srm, pp->ev_in, 0));
+  CU(cudaEventRecord(pp->ev[0], srm));
+  CU(fec_launch_rm((const FecRmDesc *)pp->st_rmd.d, pp->d_softmax, ncb, max_n_out, srm));
   ctx->launches++;
-  CU(cudaEventRecord(pp->ev[1], sc));
+  CU(cudaEventRecord(pp->ev[1], srm));
+  if (srm != sc) CU(cudaStreamWaitEvent(sc, pp->ev[1], 0));
   for (int k = 0; k < FEC_NOF_K; k++) {
     if (!grp_cnt[k]) continue;
     FecDecodeArgs a;
@@ -549,7 +554,8 @@ static int pipes_create(fec_cuda_ctx_t *ctx)
   if (!ctx->pipes) return -1;
   for (int i = 0; i < FEC_NPIPE; i++) if (pipe_init(ctx, &ctx->pipes[i])) return -1;
   if (cudaStreamCreateWithFlags(&ctx->s_copy, cudaStreamNonBlocking) != cudaSuccess || cudaStreamCreateWithFlags(&ctx->s_out, cudaStreamNonBlocking) != cudaSuccess ||
-      cudaStreamCreateWithFlags(&ctx->s_comp[1], cudaStreamNonBlocking) != cudaSuccess) return -1;
+      cudaStreamCreateWithFlags(&ctx->s_comp[1], cudaStreamNonBlocking) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&ctx->s_rm, cudaStreamNonBlocking) != cudaSuccess) return -1;
   ctx->s_comp[0] = ctx->stream;
   const char *sb = getenv("FEC_CUDA_SUB_TBS");
   ctx->sub_tbs = sb ? (uint32_t)atoi(sb) : 296;
@@ -557,6 +563,8 @@ static int pipes_create(fec_cuda_ctx_t *ctx)
   sb = getenv("FEC_CUDA_SUB_TBS_DEV");
   ctx->sub_tbs_dev = sb ? (uint32_t)atoi(sb) : 592;
   if (ctx->sub_tbs_dev == 0) ctx->sub_tbs_dev = 592;
+  sb = getenv("FEC_CUDA_RAMP");
+  ctx->ramp = sb ? atoi(sb) : 0;
   sb = getenv("FEC_CUDA_TRACE");
   ctx->trace = sb ? atoi(sb) : 0;
   CU(cudaEventCreate(&ctx->ev_call));
@@ -571,6 +579,7 @@ static void pipes_destroy(fec_cuda_ctx_t *ctx)
   if (ctx->s_copy) cudaStreamDestroy(ctx->s_copy);
   if (ctx->s_out) cudaStreamDestroy(ctx->s_out);
   if (ctx->s_comp[1]) cudaStreamDestroy(ctx->s_comp[1]);
+  if (ctx->s_rm) cudaStreamDestroy(ctx->s_rm);
 }
 
 extern "C" int fec_cuda_submit_tbs(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, uint32_t n, uint32_t flags, uint64_t *ticket)
@@ -591,7 +600,7 @@ extern "C" int fec_cuda_submit_tbs(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, uint
   while (off < n && !rc) {
     /* ramp: the first sub-batches are small so that the GPU starts after a short descriptor build and a short rate
      * de-matching launch; everything after that is hidden behind the kernels of the previous sub-batch */
-    uint32_t cnt = (flags & FEC_CUDA_F_SERIAL) ? n : (s == 0 ? sub / 4 : s == 1 ? sub / 2 : sub);
+    uint32_t cnt = (flags & FEC_CUDA_F_SERIAL) ? n : !ctx->ramp ? sub : (s == 0 ? sub / 4 : s == 1 ? sub / 2 : sub);
     if (cnt == 0) cnt = 1;
     if (n - off < cnt + cnt / 2) cnt = n - off;          /* no tiny last sub-batch */
     const uint32_t slot = ctx->pipe_next++;

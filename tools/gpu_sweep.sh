@@ -1,10 +1,6 @@
 #!/bin/bash
-mkdir -p gpurun_out
-for v in 296 592 1184; do
-FEC_CUDA_SUB_TBS_DEV=$v timeout 600 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-worst-case 2>/dev/null | python -c "
-import sys,json; j=json.loads(sys.stdin.read()); print('dev',$v, j['value'], j['ms_per_step'], j['e2e']['value'], j['e2e']['ms_per_step'])"
-done
-for v in 148 296 592; do
-FEC_CUDA_SUB_TBS=$v timeout 600 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-worst-case 2>/dev/null | python -c "
-import sys,json; j=json.loads(sys.stdin.read()); print('host',$v, j['value'], j['ms_per_step'], j['e2e']['value'], j['e2e']['ms_per_step'])"
+# sweep of the sub-batch size (device-resident arm)
+for sub in ${SWEEP:-400 500 592 700 800}; do
+  FEC_CUDA_SUB_TBS_DEV=$sub timeout 300 python bench.py --steps 6 --warmup 3 --no-cpu-baseline --no-worst-case 2>/dev/null | python -c "
+import sys,json; j=json.loads(sys.stdin.read()); print('sub $sub: pipelined %.3f sync %.3f e2e %.3f / %.3f' % (j['ms_per_step'], j['sync_ms_per_step'], j['e2e']['ms_per_step'], j['e2e']['sync_ms_per_step']))"
 done
