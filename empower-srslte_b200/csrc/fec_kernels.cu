@@ -515,16 +515,54 @@ __global__ void __launch_bounds__(FEC_RM_THREADS) fec_rm_rx_kernel(const FecRmDe
   const FecRmDesc d = descs[blockIdx.x];
   const int tid = threadIdx.x;
   if (d.E <= d.N) {
-    /* the common case (no repetition): a plain rotated copy, 8 independent loads in flight per thread */
+    /* the common case (no repetition): a rotated copy. Entry i lands at p = i + off (mod N). LLR pairs are read as
+     * 32-bit words when the slice is 4-byte aligned (it is for every even Qm), 8 independent loads in flight per thread */
     const uint32_t wrap = d.N - d.off;                 /* entries i >= wrap land at p = i - wrap */
-    for (uint32_t i0 = tid; i0 < d.E; i0 += 8 * FEC_RM_THREADS) {
-      int16_t v[8];
+    const bool al = ((reinterpret_cast<size_t>(d.e) & 3) == 0);
+    if (al) {
+      const uint32_t *e32 = reinterpret_cast<const uint32_t *>(d.e);
+      const uint32_t npair = d.E >> 1;
+      for (uint32_t q0 = tid; q0 < npair; q0 += 8 * FEC_RM_THREADS) {
+        uint32_t v[8];
 #pragma unroll
-      for (int u = 0; u < 8; u++) { const uint32_t i = i0 + u * FEC_RM_THREADS; v[u] = i < d.E ? __ldg(d.e + i) : (int16_t)0; }
+        for (int u = 0; u < 8; u++) { const uint32_t q = q0 + u * FEC_RM_THREADS; v[u] = q < npair ? __ldg(e32 + q) : 0u; }
 #pragma unroll
-      for (int u = 0; u < 8; u++) { const uint32_t i = i0 + u * FEC_RM_THREADS; if (i < d.E) rm_tile[i < wrap ? i + d.off : i - wrap] = v[u]; }
+        for (int u = 0; u < 8; u++) {
+          const uint32_t q = q0 + u * FEC_RM_THREADS, i = 2 * q;
+          if (q < npair) {
+            const uint32_t p0 = i < wrap ? i + d.off : i - wrap, p1 = i + 1 < wrap ? i + 1 + d.off : i + 1 - wrap;
+            if (p1 == p0 + 1 && !(p0 & 1)) *reinterpret_cast<uint32_t *>(rm_tile + p0) = v[u];
+            else { rm_tile[p0] = (int16_t)(v[u] & 0xFFFFu); rm_tile[p1] = (int16_t)(v[u] >> 16); }
+          }
+        }
+      }
+      if ((d.E & 1) && tid == 0) { const uint32_t i = d.E - 1; rm_tile[i < wrap ? i + d.off : i - wrap] = __ldg(d.e + i); }
+    } else {
+      for (uint32_t i0 = tid; i0 < d.E; i0 += 8 * FEC_RM_THREADS) {
+        int16_t v[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++) { const uint32_t i = i0 + u * FEC_RM_THREADS; v[u] = i < d.E ? __ldg(d.e + i) : (int16_t)0; }
+#pragma unroll
+        for (int u = 0; u < 8; u++) { const uint32_t i = i0 + u * FEC_RM_THREADS; if (i < d.E) rm_tile[i < wrap ? i + d.off : i - wrap] = v[u]; }
+      }
     }
-    for (uint32_t i = d.E + tid; i < d.N; i += FEC_RM_THREADS) rm_tile[i < wrap ? i + d.off : i - wrap] = 0;   /* never transmitted */
+    /* entries never transmitted: p in [E + off, N + off) mod N, one or two contiguous runs, zeroed 16 bytes at a time */
+    {
+      const uint32_t a0 = d.E + d.off;                 /* first untransmitted p, before the wrap */
+      uint32_t lo[2], hi[2];
+      if (a0 >= d.N) { lo[0] = a0 - d.N; hi[0] = d.off; lo[1] = hi[1] = 0; }
+      else           { lo[0] = a0; hi[0] = d.N; lo[1] = 0; hi[1] = d.off; }
+#pragma unroll
+      for (int r = 0; r < 2; r++) {
+        const uint32_t l8 = (lo[r] + 7) & ~7u, h8 = hi[r] & ~7u;
+        if (l8 >= h8) { for (uint32_t p = lo[r] + tid; p < hi[r]; p += FEC_RM_THREADS) rm_tile[p] = 0; }
+        else {
+          for (uint32_t p = lo[r] + tid; p < l8; p += FEC_RM_THREADS) rm_tile[p] = 0;
+          for (uint32_t p = l8 + 8 * tid; p < h8; p += 8 * FEC_RM_THREADS) *reinterpret_cast<uint4 *>(rm_tile + p) = make_uint4(0, 0, 0, 0);
+          for (uint32_t p = h8 + tid; p < hi[r]; p += FEC_RM_THREADS) rm_tile[p] = 0;
+        }
+      }
+    }
   } else {
     for (uint32_t i = tid; i < d.N; i += FEC_RM_THREADS) {
       int acc = 0;
