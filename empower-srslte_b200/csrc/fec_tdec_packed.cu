@@ -481,11 +481,12 @@ __device__ __forceinline__ uint32_t pk_row_bits(const uint32_t *row, int k)
 /* natural-order hard decisions -> K/8 bytes MSB first (turbodecoder_win.h:676-716). rows: [P][nw+1] words,
  * row d holds bits d*L .. d*L+L-1 starting at bit index `pad`. Called by the TPC threads of one code block. */
 template <int TPC>
-__device__ __forceinline__ void pk_write_output(const uint32_t *rows, int nw1, int pad, int K, int L, int j, uint8_t *out)
+__device__ __forceinline__ void pk_write_output(const uint32_t *__restrict__ rows, int nw1, int pad, int K, int L, int j, uint8_t *__restrict__ out)
 {
   const int nwords = K >> 5;
   uint32_t *out32 = reinterpret_cast<uint32_t *>(out);
   int d = (j << 5) / L, k = (j << 5) - d * L;
+#pragma unroll 4
   for (int ow = j; ow < nwords; ow += TPC) {
     const int avail = L - k;
     uint32_t w = pk_row_bits(rows + d * nw1, k + pad);
@@ -540,21 +541,32 @@ __device__ PK_EPI_INLINE void pk_finish_block(int par, uint32_t Eb, const uint16
         }
       }
       __syncwarp(gmask);
+      /* 16 steps at a time: bits 15 / 31 of word i go to bits 15-i / 31-i of u (both lanes with one shift + one
+       * LOP3), then the two 16-bit fields are appended to the row words */
       uint32_t wlo = 0, whi = 0;
-      for (int k0 = 0; k0 < L; k0 += 8) {
-        uint32_t w[8];
+      int fill = pad;                                   /* bits already in the current row word */
+      int wi = 0;
+      for (int k0 = 0; k0 < L; k0 += 16) {
+        uint32_t w[16];
 #pragma unroll
-        for (int i = 0; i < 8; i++) w[i] = (k0 + i < L) ? erow[k0 + i] : 0u;
+        for (int i = 0; i < 16; i++) w[i] = (k0 + i < L) ? erow[k0 + i] : 0u;
+        uint32_t u = 0;
 #pragma unroll
-        for (int i = 0; i < 8; i++) {
-          if (k0 + i < L) {
-            const int kb = k0 + i + pad;
-            wlo = __funnelshift_l(w[i] << 16, wlo, 1); whi = __funnelshift_l(w[i], whi, 1);
-            if ((kb & 31) == 31) { blo[kb >> 5] = wlo; bhi[kb >> 5] = whi; }
-          }
+        for (int i = 0; i < 16; i++) u |= (w[i] >> i) & (0x80008000u >> i);
+        const int n = min(16, L - k0);                  /* valid steps in u: the top n bits of each half */
+        const uint32_t flo = u << 16, fhi = u & 0xFFFF0000u;        /* left-aligned 16-bit fields */
+        /* append n bits (left-aligned in f) to the MSB-first accumulators */
+        if (fill + n < 32) {
+          wlo |= flo >> fill; whi |= fhi >> fill; fill += n;
+        } else {
+          wlo |= flo >> fill; whi |= fhi >> fill;
+          blo[wi] = wlo; bhi[wi] = whi; wi++;
+          const int used = 32 - fill;                   /* bits of the field that went into the finished word */
+          wlo = used < 16 ? flo << used : 0u; whi = used < 16 ? fhi << used : 0u;
+          fill = n - used;
         }
       }
-      if ((L + pad) & 31) { const int sh = 32 - ((L + pad) & 31); blo[(L + pad) >> 5] = wlo << sh; bhi[(L + pad) >> 5] = whi << sh; }
+      if (fill) { blo[wi] = wlo; bhi[wi] = whi; }
     }
     __syncwarp(gmask);
     pk_write_output<TPC>(rows, nw1, pad, K, L, j, out);
