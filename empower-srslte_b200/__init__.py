@@ -15,7 +15,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("FEC_CUDA_LIB") or os.path.join(HERE, "libsrslte_fec_cuda.so")   # FEC_CUDA_LIB: tuning builds (tools/variants.sh)
 CSRC = os.path.join(HERE, "csrc")
-SOURCES = ["fec_kernels.cu", "fec_tdec_packed.cu", "fec_cuda_api.cu", "fec_compat.cu", "fec_tables.c"]
+SOURCES = ["fec_kernels.cu", "fec_tdec_packed.cu", "fec_frontend.cu", "fec_cuda_api.cu", "fec_compat.cu", "fec_tables.c"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-Xcompiler", "-fPIC", "-shared"]
 
 MAX_CB = 13
@@ -31,6 +31,14 @@ class TbDesc(C.Structure):
                 ("e_bits", C.c_void_p), ("data", C.c_void_p),
                 ("ret", C.c_int32), ("avg_its", C.c_uint32),
                 ("cb_crc", C.c_uint8 * MAX_CB), ("cb_its", C.c_uint8 * MAX_CB), ("pad", C.c_uint8 * 6)]
+
+
+class SymDesc(C.Structure):
+    """fec_cuda_sym_t: one transport block given as equalised symbols (front end, include/srslte_fec_cuda.h)"""
+    _fields_ = [("symbols", C.c_void_p), ("csi", C.c_void_p), ("nof_re", C.c_uint32), ("mod_bits", C.c_uint32),
+                ("c_init", C.c_uint32), ("nof_symb", C.c_uint32), ("ack_pos", C.c_void_p), ("ri_pos", C.c_void_p),
+                ("nof_ack_pos", C.c_uint32), ("nof_ri_pos", C.c_uint32), ("nof_cqi_bits", C.c_uint32), ("reserved", C.c_uint32),
+                ("uci_out", C.c_void_p)]
 
 
 class CbDesc(C.Structure):
@@ -79,6 +87,14 @@ def load():
         lib.fec_cuda_rm_rx.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p]
         lib.fec_cuda_cbsegm.argtypes = [C.c_uint32, C.POINTER(C.c_uint32)]
         lib.fec_cuda_last_phase_ms.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
+        lib.fec_cuda_decode_syms.argtypes = [C.c_void_p, C.POINTER(TbDesc), C.POINTER(SymDesc), C.c_uint32, C.c_uint32]
+        lib.fec_cuda_submit_syms.argtypes = [C.c_void_p, C.POINTER(TbDesc), C.POINTER(SymDesc), C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64)]
+        lib.fec_cuda_last_frontend_ms.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
+        lib.fec_cuda_frontend.argtypes = [C.c_void_p, C.POINTER(SymDesc), C.c_void_p]
+        lib.fec_cuda_cinit_pdsch.restype = C.c_uint32
+        lib.fec_cuda_cinit_pdsch.argtypes = [C.c_uint32] * 4
+        lib.fec_cuda_cinit_pusch.restype = C.c_uint32
+        lib.fec_cuda_cinit_pusch.argtypes = [C.c_uint32] * 3
         lib.fec_cuda_host_alloc.argtypes = [C.c_size_t]
         lib.fec_cuda_host_alloc.restype = C.c_void_p
         lib.fec_cuda_host_free.argtypes = [C.c_void_p]
@@ -189,6 +205,53 @@ class FecCuda:
         rc = self.lib.fec_cuda_wait(self.h, ticket)
         if rc:
             raise RuntimeError(f"fec_cuda_wait: {rc} {self.error()}")
+
+    def decode_syms(self, descs, syms, flags=0):
+        """transport blocks given as equalised symbols (TbDesc array + SymDesc array, filled in place)"""
+        rc = self.lib.fec_cuda_decode_syms(self.h, descs, syms, len(descs), flags)
+        if rc:
+            raise RuntimeError(f"fec_cuda_decode_syms: {rc} {self.error()}")
+        return descs
+
+    def submit_syms(self, descs, syms, flags=0):
+        t = C.c_uint64(0)
+        rc = self.lib.fec_cuda_submit_syms(self.h, descs, syms, len(descs), flags, C.byref(t))
+        if rc:
+            raise RuntimeError(f"fec_cuda_submit_syms: {rc} {self.error()}")
+        return t.value
+
+    def last_frontend_ms(self):
+        o = C.c_float(0)
+        rc = self.lib.fec_cuda_last_frontend_ms(self.h, C.byref(o))
+        if rc:
+            raise RuntimeError(f"fec_cuda_last_frontend_ms: {rc}")
+        return float(o.value)
+
+    def frontend(self, symbols, mod_bits, c_init, csi=None, nof_symb=0, ack_pos=(), ri_pos=(), nof_cqi_bits=0):
+        """symbols -> LLRs as decode_tb receives them (demodulation, descrambling, CSI weights / UL de-interleaver).
+        symbols: float32 pairs (re, im). Returns (llr int16[nof_re*mod_bits], uci int16[nack+nri+ncqi])"""
+        sym = np.ascontiguousarray(symbols, dtype=np.float32).reshape(-1)
+        n = sym.size // 2
+        buf = np.zeros(2 * n + 8, np.float32)
+        off = ((-buf.ctypes.data) % 16) // 4
+        buf[off:off + 2 * n] = sym                               # 16-byte aligned like srslte_vec_malloc memory
+        d = SymDesc()
+        d.symbols, d.nof_re, d.mod_bits, d.c_init, d.nof_symb = buf.ctypes.data + 4 * off, n, mod_bits, c_init, nof_symb
+        keep = [buf]
+        if csi is not None:
+            c = np.ascontiguousarray(csi, dtype=np.float32)
+            keep.append(c)
+            d.csi = c.ctypes.data
+        ack = np.ascontiguousarray(ack_pos, dtype=np.uint32)
+        ri = np.ascontiguousarray(ri_pos, dtype=np.uint32)
+        uci = np.zeros(ack.size + ri.size + nof_cqi_bits + 1, np.int16)
+        d.ack_pos, d.ri_pos, d.nof_ack_pos, d.nof_ri_pos, d.nof_cqi_bits = ack.ctypes.data, ri.ctypes.data, ack.size, ri.size, nof_cqi_bits
+        d.uci_out = uci.ctypes.data
+        out = np.zeros(n * mod_bits, np.int16)
+        rc = self.lib.fec_cuda_frontend(self.h, C.byref(d), out.ctypes.data_as(C.c_void_p))
+        if rc:
+            raise RuntimeError(f"fec_cuda_frontend: {rc} {self.error()}")
+        return out, uci[:-1]
 
     def decode_tb(self, tbs, Qm, rv, e_bits, softbuffer, new_data, max_its=8, flags=0):
         """single transport block convenience (the srslte_dlsch_decode call shape). e_bits: int16 numpy."""

@@ -62,10 +62,12 @@ struct fec_cuda_ctx {
   int           ramp;           /* FEC_CUDA_RAMP=1: small first sub-batches (measured slower on B200, off by default) */
   fec_pipe_t   *pipes;
   uint32_t      sub_tbs, sub_tbs_dev;
-  size_t        hw[9];          /* high-water marks of the per-pipe staging buffers */
+  size_t        hw[16];         /* high-water marks of the per-pipe staging buffers */
   uint64_t      call_seq;       /* tickets of fec_cuda_submit_tbs */
   uint32_t      pipe_next;      /* next slot of the pipe ring (runs on across calls) */
   int           trace;          /* FEC_CUDA_TRACE=1: print the device timeline of every sub-batch to stderr */
+  uint32_t     *d_x2masks, *d_x1states;   /* front end: scrambling-sequence jump tables (fec_frontend.cu) */
+  float         fe_ms;          /* device time of the front-end kernels of the last call */
   cudaEvent_t   ev_call;        /* start of the current decode_tbs call (copy stream) */
   double        t_call;         /* host clock at the start of the call */
 };
@@ -143,6 +145,15 @@ extern "C" int fec_cuda_create(fec_cuda_ctx_t **out, int device, uint32_t max_tb
   cudaMemcpy(ctx->d_r24b, R, sizeof(uint32_t) * FEC_MAX_K, cudaMemcpyHostToDevice);
   free(R);
   cudaMalloc(&ctx->d_queue, sizeof(unsigned int) * 3 * FEC_NOF_K);
+  {
+    uint32_t *m = (uint32_t *)malloc(sizeof(uint32_t) * FEC_FE_NBLK * 33);
+    fec_gen_gold_tables(m, m + FEC_FE_NBLK * 32);
+    cudaMalloc(&ctx->d_x2masks, sizeof(uint32_t) * FEC_FE_NBLK * 32);
+    cudaMalloc(&ctx->d_x1states, sizeof(uint32_t) * FEC_FE_NBLK);
+    cudaMemcpy(ctx->d_x2masks, m, sizeof(uint32_t) * FEC_FE_NBLK * 32, cudaMemcpyHostToDevice);
+    cudaMemcpy(ctx->d_x1states, m + FEC_FE_NBLK * 32, sizeof(uint32_t) * FEC_FE_NBLK, cudaMemcpyHostToDevice);
+    free(m);
+  }
   { const char *fe = getenv("FEC_CUDA_FORCE_EXACT"); ctx->force_exact = fe && fe[0] == '1'; }
   if (pipes_create(ctx)) { free(ctx); return FEC_CUDA_ENODEV; }
   if (cudaGetLastError() != cudaSuccess) { free(ctx); return FEC_CUDA_ENODEV; }
@@ -165,6 +176,7 @@ extern "C" void fec_cuda_destroy(fec_cuda_ctx_t *ctx)
   stage_free(&ctx->st_e); stage_free(&ctx->st_data); stage_free(&ctx->st_cbd); stage_free(&ctx->st_rmd);
   stage_free(&ctx->st_tbd); stage_free(&ctx->st_status); stage_free(&ctx->st_ret); stage_free(&ctx->st_exd);
   cudaFree(ctx->d_cbbytes); cudaFree(ctx->d_tmpsoft); cudaFree(ctx->d_r24a); cudaFree(ctx->d_r24b); cudaFree(ctx->d_queue);
+  cudaFree(ctx->d_x2masks); cudaFree(ctx->d_x1states);
   pipes_destroy(ctx);
   cudaStreamDestroy(ctx->stream);
   free(ctx);
@@ -305,10 +317,19 @@ static void fill_decode_args(fec_cuda_ctx_t *ctx, int k, FecDecodeArgs *a, const
  * scratch and events each): while the GPU works on sub-batch i (H2D of its LLRs on the copy stream, kernels on
  * one of two compute streams, D2H on the output stream) the host builds the descriptors of sub-batch i+1 and
  * unpacks the results of sub-batch i-1. The call returns when every sub-batch is done. */
-typedef struct { uint32_t seg[9]; sbchunk_t *chunk; uint32_t local; int valid, pinned; uint32_t ndec; size_t data_off, e_off; int kidx[2]; } tbplan_t;
+typedef struct {
+  uint32_t seg[9]; sbchunk_t *chunk; uint32_t local; int valid, pinned; uint32_t ndec; size_t data_off, e_off; int kidx[2];
+  /* front end (symbols in): offsets into the pipe's symbol / list / control-information staging */
+  int fe_valid, sym_pinned; size_t sym_off, csi_off, lst_off, uci_off; uint32_t nack_u, nri_u, nuci, last_ri_pos;
+} tbplan_t;
 
 struct fec_pipe {
   stage_t       st_e, st_data, st_cbd, st_rmd, st_tbd, st_status, st_ret;
+  stage_t       st_fed, st_lst, st_uci;            /* front end: descriptors, position lists, control-information LLRs */
+  int16_t      *d_llr; size_t llr_cap;             /* front end: LLRs produced on the device (decode_tb's e_bits / g_bits) */
+  float        *d_csimax; size_t csimax_cap;
+  const fec_cuda_sym_t *syms;
+  cudaEvent_t   ev_fe;
   uint8_t      *d_cbbytes; size_t cbbytes_cap;
   uint32_t     *d_softmax; size_t softmax_cap;
   uint32_t     *d_exact;   size_t exact_cap;
@@ -328,6 +349,7 @@ static int pipe_init(fec_cuda_ctx_t *ctx, fec_pipe_t *p)
   CU(cudaEventCreate(&p->ev_in));
   CU(cudaEventCreateWithFlags(&p->ev_k, cudaEventDisableTiming));
   CU(cudaEventCreate(&p->ev_done));
+  CU(cudaEventCreate(&p->ev_fe));
   for (int i = 0; i < 4; i++) CU(cudaEventCreate(&p->ev[i]));
   return 0;
 }
@@ -336,6 +358,9 @@ static void pipe_free(fec_pipe_t *p)
 {
   stage_free(&p->st_e); stage_free(&p->st_data); stage_free(&p->st_cbd); stage_free(&p->st_rmd);
   stage_free(&p->st_tbd); stage_free(&p->st_status); stage_free(&p->st_ret);
+  stage_free(&p->st_fed); stage_free(&p->st_lst); stage_free(&p->st_uci);
+  cudaFree(p->d_llr); cudaFree(p->d_csimax);
+  if (p->ev_fe) cudaEventDestroy(p->ev_fe);
   cudaFree(p->d_cbbytes); cudaFree(p->d_softmax); cudaFree(p->d_exact); cudaFree(p->d_queue);
   if (p->ev_in) { cudaEventDestroy(p->ev_in); cudaEventDestroy(p->ev_k); cudaEventDestroy(p->ev_done); for (int i = 0; i < 4; i++) cudaEventDestroy(p->ev[i]); }
   free(p->plan);
@@ -343,7 +368,62 @@ static void pipe_free(fec_pipe_t *p)
 }
 
 /* build descriptors for tbs[0..n), enqueue copies + kernels; returns without waiting */
-static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, uint32_t n, uint32_t flags, cudaStream_t sc)
+/* ascending, duplicates removed; returns the new length */
+static int cmp_u32(const void *a, const void *b) { const uint32_t x = *(const uint32_t *)a, y = *(const uint32_t *)b; return x < y ? -1 : x > y; }
+static uint32_t sort_unique(uint32_t *a, uint32_t n)
+{
+  if (!n) return 0;
+  qsort(a, n, sizeof(uint32_t), cmp_u32);
+  uint32_t m = 1;
+  for (uint32_t i = 1; i < n; i++) if (a[i] != a[m - 1]) a[m++] = a[i];
+  return m;
+}
+
+/* front-end argument checks for one transport block given as equalised symbols */
+static int fe_check(const fec_cuda_tb_t *t, const fec_cuda_sym_t *sy)
+{
+  const uint32_t mod = sy->mod_bits;
+  if (!sy->symbols || !sy->nof_re || !(mod == 1 || mod == 2 || mod == 4 || mod == 6)) return 0;
+  if (((uintptr_t)sy->symbols & 15) || (sy->csi && ((uintptr_t)sy->csi & 3))) return 0;
+  const uint64_t nb = (uint64_t)sy->nof_re * mod;
+  if (nb > (uint64_t)FEC_FE_NBLK * 256) return 0;                       /* MAX_SEQ_LEN, sequence.c:38 */
+  if (sy->nof_symb == 0) {                                              /* DL: pdsch.c:778-834 */
+    if (sy->nof_ack_pos || sy->nof_ri_pos || sy->nof_cqi_bits) return 0;
+    if (sy->csi && mod == 1) return 0;
+    return t->tbs == 0 || t->nof_e_bits == nb;
+  }
+  /* UL: pusch.c:617-657 */
+  if (sy->csi || mod == 1 || sy->nof_re % sy->nof_symb) return 0;
+  if ((sy->nof_ack_pos && !sy->ack_pos) || (sy->nof_ri_pos && !sy->ri_pos)) return 0;
+  if ((sy->nof_ack_pos || sy->nof_ri_pos || sy->nof_cqi_bits) && !sy->uci_out) return 0;
+  for (uint32_t i = 0; i < sy->nof_ack_pos; i++) if (sy->ack_pos[i] >= nb) return 0;
+  for (uint32_t i = 0; i < sy->nof_ri_pos; i++) if (sy->ri_pos[i] >= nb) return 0;
+  if (sy->nof_cqi_bits > nb) return 0;
+  return t->tbs == 0 || (uint64_t)t->nof_e_bits + sy->nof_cqi_bits <= nb;
+}
+
+/* UL position lists of one transport block: 2*(nack+nri) words at lst (host) / dl (its device mirror):
+ * [ACK, de-interleaved order, ascending | RI, same | the caller's q positions, ACK then RI] */
+static void fe_build_lists(const fec_cuda_sym_t *sy, FecFeDesc *f, uint32_t *lst, const uint32_t *dl)
+{
+  const uint32_t mod = sy->mod_bits, nuci = sy->nof_ack_pos + sy->nof_ri_pos;
+  uint32_t *raw = lst + nuci, last = 0;
+  for (uint32_t k = 0; k < nuci; k++) {
+    /* q position -> index after the channel de-interleaver without RI removal (ulsch_interleave_gen, sch.c:550-568) */
+    const uint32_t q = k < sy->nof_ack_pos ? sy->ack_pos[k] : sy->ri_pos[k - sy->nof_ack_pos];
+    const uint32_t sidx = q / mod, col = sidx / f->rows, row = sidx - col * f->rows;
+    lst[k] = (row * f->cols + col) * mod + (q - sidx * mod);
+    raw[k] = q;
+    if (k >= sy->nof_ack_pos && q > last) last = q;
+  }
+  f->nack = sort_unique(lst, sy->nof_ack_pos);
+  f->nri = sort_unique(lst + sy->nof_ack_pos, sy->nof_ri_pos);
+  f->last_ri_pos = last;
+  f->ack_ord = dl; f->ri_ord = dl + sy->nof_ack_pos; f->uci_pos = dl + nuci;
+}
+
+static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, const fec_cuda_sym_t *syms, uint32_t n, uint32_t flags,
+                       cudaStream_t sc)
 {
   const int dev_io = (flags & FEC_CUDA_F_DEVICE_IO) != 0;
   if (pp->plan_cap < n) { free(pp->plan); pp->plan = (tbplan_t *)malloc(sizeof(tbplan_t) * n); pp->plan_cap = n; }
@@ -351,9 +431,10 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
   memset(plan, 0, sizeof(tbplan_t) * n);
   uint32_t grp_cnt[FEC_NOF_K], grp_off[FEC_NOF_K], grp_fill[FEC_NOF_K];
   memset(grp_cnt, 0, sizeof(grp_cnt));
-  uint32_t ncb = 0, ntb = 0;
-  size_t e_total = 0, data_total = 0;
-  pp->tbs = tbs; pp->n = n; pp->dev_io = dev_io; pp->ncb = pp->ntb = 0; pp->busy = 0;
+  uint32_t ncb = 0, ntb = 0, nfe = 0, max_re = 0;
+  int any_csi = 0, any_uci = 0;
+  size_t e_total = 0, data_total = 0, sym_total = 0, lst_total = 0, uci_total = 0;
+  pp->tbs = tbs; pp->syms = syms; pp->n = n; pp->dev_io = dev_io; pp->ncb = pp->ntb = 0; pp->busy = 0;
 
   /* pass 1: argument checks of decode_tb (sch.c:444-457) + segmentation + HARQ state */
   for (uint32_t i = 0; i < n; i++) {
@@ -361,12 +442,29 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
     tbplan_t *p = &plan[i];
     t->ret = FEC_CUDA_EINVAL; t->avg_its = 0;
     memset(t->cb_crc, 0, sizeof(t->cb_crc)); memset(t->cb_its, 0, sizeof(t->cb_its));
-    if (!t->e_bits || !t->data || t->rv > 3 || t->Qm == 0) continue;
+    const fec_cuda_sym_t *sy = syms ? &syms[i] : NULL;
+    if ((!sy && !t->e_bits) || (!t->data && t->tbs) || t->rv > 3 || t->Qm == 0) continue;
+    if (sy && !fe_check(t, sy)) continue;
     if (fec_segm(t->tbs, p->seg)) continue;
-    if (t->tbs == 0 || p->seg[1] == 0) { t->ret = 0; continue; }
-    if (p->seg[0] || p->seg[1] > FEC_CUDA_MAX_CB) continue;            /* filler bits / too many CBs */
-    p->chunk = sb_find(ctx, t->softbuffer, &p->local);
-    if (!p->chunk) continue;
+    const int decode = !(t->tbs == 0 || p->seg[1] == 0);
+    if (decode) {
+      if (p->seg[0] || p->seg[1] > FEC_CUDA_MAX_CB) continue;            /* filler bits / too many CBs */
+      p->chunk = sb_find(ctx, t->softbuffer, &p->local);
+      if (!p->chunk) continue;
+    }
+    if (sy) {
+      /* the front end runs for every transport block whose symbols are usable, also for control-only PUSCH (tbs == 0) */
+      p->fe_valid = 1; nfe++;
+      if (sy->nof_re > max_re) max_re = sy->nof_re;
+      p->sym_off = sym_total; sym_total += ((size_t)sy->nof_re * 8 + 15) & ~(size_t)15;
+      if (sy->csi) { any_csi = 1; p->csi_off = sym_total; sym_total += ((size_t)sy->nof_re * 4 + 15) & ~(size_t)15; }
+      p->lst_off = lst_total; lst_total += 2 * ((size_t)sy->nof_ack_pos + sy->nof_ri_pos);
+      p->nuci = sy->nof_ack_pos + sy->nof_ri_pos;
+      p->uci_off = uci_total; uci_total += ((size_t)p->nuci + sy->nof_cqi_bits + 7) & ~(size_t)7;
+      if (p->nuci + sy->nof_cqi_bits) any_uci = 1;
+      p->e_off = e_total; e_total += ((size_t)sy->nof_re * sy->mod_bits + 7) & ~(size_t)7;
+    }
+    if (!decode) { t->ret = 0; continue; }
     uint8_t *crc = p->chunk->cb_crc + (size_t)p->local * FEC_CUDA_MAX_CB;
     if (t->new_data) memset(crc, 0, FEC_CUDA_MAX_CB);
     p->kidx[0] = (int)p->seg[4]; p->kidx[1] = (int)p->seg[5];
@@ -374,18 +472,20 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
     for (uint32_t cb = 0; cb < p->seg[1]; cb++)
       if (!crc[cb]) { grp_cnt[p->kidx[cb < p->seg[6] ? 0 : 1]]++; p->ndec++; }
     ncb += p->ndec; ntb++;
-    p->e_off = e_total; e_total += ((size_t)t->nof_e_bits + 7) & ~(size_t)7;
+    if (!sy) { p->e_off = e_total; e_total += ((size_t)t->nof_e_bits + 7) & ~(size_t)7; }
     p->data_off = data_total; data_total += ((size_t)t->tbs / 8 + 3 + CB_BYTES + 15) & ~(size_t)15;
   }
-  if (ntb == 0) return 0;
+  if (ntb == 0 && nfe == 0) return 0;
   uint32_t acc = 0;
   for (int k = 0; k < FEC_NOF_K; k++) { grp_off[k] = acc; grp_fill[k] = 0; acc += grp_cnt[k]; }
 
   /* every pipe of the ring is sized for the largest sub-batch seen so far: (re)allocation of pinned / device staging
    * synchronises the device, so it must stop after the first calls */
-  size_t need[9] = { sizeof(FecCbDesc) * (ncb + 1), sizeof(FecRmDesc) * (ncb + 1), sizeof(FecTbDesc) * ntb, sizeof(FecCbStatus) * (ncb + 1),
-                     sizeof(int32_t) * ntb, (size_t)(ncb + 1) * CB_BYTES, (size_t)(ncb + 1) * 4, dev_io ? 0 : e_total * 2, dev_io ? 0 : data_total };
-  for (int i = 0; i < 9; i++) { if (need[i] > ctx->hw[i]) ctx->hw[i] = need[i]; need[i] = ctx->hw[i]; }
+  size_t need[16] = { sizeof(FecCbDesc) * (ncb + 1), sizeof(FecRmDesc) * (ncb + 1), sizeof(FecTbDesc) * (ntb + 1), sizeof(FecCbStatus) * (ncb + 1),
+                      sizeof(int32_t) * (ntb + 1), (size_t)(ncb + 1) * CB_BYTES, (size_t)(ncb + 1) * 4,
+                      dev_io ? 0 : (syms ? sym_total : e_total * 2), dev_io ? 0 : data_total,
+                      /* front end */ sizeof(FecFeDesc) * nfe, syms ? e_total * 2 : 0, lst_total * 4, (dev_io || !syms) ? 0 : uci_total * 2, sizeof(float) * nfe, 0, 0 };
+  for (int i = 0; i < 16; i++) { if (need[i] > ctx->hw[i]) ctx->hw[i] = need[i]; need[i] = ctx->hw[i]; }
   if (stage_reserve(ctx, &pp->st_cbd, need[0]) || stage_reserve(ctx, &pp->st_rmd, need[1]) ||
       stage_reserve(ctx, &pp->st_tbd, need[2]) || stage_reserve(ctx, &pp->st_status, need[3]) ||
       stage_reserve(ctx, &pp->st_ret, need[4]) ||
@@ -393,11 +493,41 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
       dev_reserve(ctx, (void **)&pp->d_softmax, &pp->softmax_cap, need[6]) ||
       dev_reserve(ctx, (void **)&pp->d_exact, &pp->exact_cap, need[6]) ||
       (!dev_io && (stage_reserve(ctx, &pp->st_e, need[7]) || stage_reserve(ctx, &pp->st_data, need[8])))) return FEC_CUDA_ENODEV;
+  if (syms && (stage_reserve(ctx, &pp->st_fed, need[9]) || dev_reserve(ctx, (void **)&pp->d_llr, &pp->llr_cap, need[10]) ||
+               stage_reserve(ctx, &pp->st_lst, need[11]) || stage_reserve(ctx, &pp->st_uci, need[12]) ||
+               dev_reserve(ctx, (void **)&pp->d_csimax, &pp->csimax_cap, need[13]))) return FEC_CUDA_ENODEV;
 
   FecCbDesc *cbd = (FecCbDesc *)pp->st_cbd.h;
   FecRmDesc *rmd = (FecRmDesc *)pp->st_rmd.h;
   FecTbDesc *tbd = (FecTbDesc *)pp->st_tbd.h;
   uint32_t max_n_out = 0, itb = 0;
+
+  /* pass 1b: front-end descriptors (symbols in): staging of symbols / CSI, position lists in de-interleaved order */
+  FecFeDesc *fed = (FecFeDesc *)pp->st_fed.h;
+  for (uint32_t i = 0, ife = 0; syms && i < n; i++) {
+    tbplan_t *p = &plan[i];
+    if (!p->fe_valid) continue;
+    const fec_cuda_sym_t *sy = &syms[i];
+    FecFeDesc *f = &fed[ife++];
+    memset(f, 0, sizeof(*f));
+    const uint32_t mod = sy->mod_bits;
+    if (dev_io) { f->sym = (const float2 *)sy->symbols; f->csi = sy->csi; f->uci_out = sy->uci_out; }
+    else {
+      f->sym = (const float2 *)((char *)pp->st_e.d + p->sym_off);
+      f->csi = sy->csi ? (const float *)((char *)pp->st_e.d + p->csi_off) : NULL;
+      f->uci_out = (p->nuci + sy->nof_cqi_bits) ? (int16_t *)pp->st_uci.d + p->uci_off : NULL;
+      cudaPointerAttributes pa;
+      p->sym_pinned = (cudaPointerGetAttributes(&pa, sy->symbols) == cudaSuccess && pa.type == cudaMemoryTypeHost);
+      cudaGetLastError();
+      if (!p->sym_pinned) memcpy((char *)pp->st_e.h + p->sym_off, sy->symbols, (size_t)sy->nof_re * 8);
+      if (sy->csi) memcpy((char *)pp->st_e.h + p->csi_off, sy->csi, (size_t)sy->nof_re * 4);
+    }
+    f->e = pp->d_llr + p->e_off;
+    f->nof_re = sy->nof_re; f->mod = mod; f->c_init = sy->c_init & 0x7FFFFFFFu;
+    f->cols = sy->nof_symb; f->rows = sy->nof_symb ? sy->nof_re / sy->nof_symb : 0;
+    f->n_cqi = sy->nof_cqi_bits; f->nuci = p->nuci;
+    if (p->nuci) fe_build_lists(sy, f, (uint32_t *)pp->st_lst.h + p->lst_off, (const uint32_t *)pp->st_lst.d + p->lst_off);
+  }
 
   /* pass 2: descriptors. E / rp per code block exactly as decode_tb_cb derives them (sch.c:328-342) */
   for (uint32_t i = 0; i < n; i++) {
@@ -408,7 +538,8 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
     uint8_t *crc = p->chunk->cb_crc + (size_t)p->local * FEC_CUDA_MAX_CB;
     int16_t *soft0 = p->chunk->d_soft + (size_t)p->local * FEC_CUDA_MAX_CB * FEC_CUDA_SOFT_SLOT;
     uint8_t *cache0 = p->chunk->d_cache + (size_t)p->local * FEC_CUDA_MAX_CB * CB_BYTES;
-    const int16_t *e_dev = dev_io ? t->e_bits : (const int16_t *)pp->st_e.d + p->e_off;
+    const int16_t *e_dev = syms ? pp->d_llr + p->e_off + syms[i].nof_cqi_bits        /* g_bits + Q'_cqi*Qm, sch.c:963-973 */
+                                : dev_io ? t->e_bits : (const int16_t *)pp->st_e.d + p->e_off;
     FecTbDesc *td = &tbd[itb];
     memset(td, 0, sizeof(*td));
     td->data = dev_io ? t->data : (uint8_t *)pp->st_data.d + p->data_off;
@@ -434,7 +565,7 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
       d->max_its = t->max_its ? t->max_its : 1; d->flags = (flags & FEC_CUDA_F_NO_EARLY_STOP) ? FEC_F_NO_EARLY : 0; d->status = slot;
       td->st_idx[cb] = (int32_t)slot; td->cb_bytes[cb] = d->out;
     }
-    if (!dev_io) {
+    if (!dev_io && !syms) {
       /* pinned caller memory (fec_cuda_host_alloc / cudaHostRegister) is DMA'd straight from where it lies */
       cudaPointerAttributes pa;
       p->pinned = (cudaPointerGetAttributes(&pa, t->e_bits) == cudaSuccess && pa.type == cudaMemoryTypeHost);
@@ -446,7 +577,41 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
 
   /* ---- copy stream: LLRs (one copy per run of TBs contiguous on both sides) + descriptors ---- */
   cudaStream_t sin = ctx->s_copy, sout = ctx->s_out;
-  if (!dev_io) {
+  if (syms) {
+    if (!dev_io) {
+      /* symbols (+ CSI): pinned caller memory goes by DMA from where it lies, the rest through the pinned staging; runs of
+       * transport blocks that are contiguous on both sides travel as one copy */
+      uint32_t i = 0;
+      while (i < n) {
+        if (!plan[i].fe_valid) { i++; continue; }
+        if (!plan[i].sym_pinned) {
+          uint32_t j = i;
+          size_t lo = plan[i].sym_off, hi = lo;
+          for (; j < n && (!plan[j].fe_valid || !plan[j].sym_pinned); j++)
+            if (plan[j].fe_valid) hi = (syms[j].csi ? plan[j].csi_off + (size_t)syms[j].nof_re * 4 : plan[j].sym_off + (size_t)syms[j].nof_re * 8);
+          CU(cudaMemcpyAsync((char *)pp->st_e.d + lo, (char *)pp->st_e.h + lo, hi - lo, cudaMemcpyHostToDevice, sin));
+          i = j;
+        } else {
+          const char *src0 = (const char *)syms[i].symbols;
+          const size_t dst0 = plan[i].sym_off;
+          size_t len = (size_t)syms[i].nof_re * 8;
+          uint32_t j = i + 1;
+          if (!syms[i].csi)
+            for (; j < n; j++) {
+              if (!plan[j].fe_valid || !plan[j].sym_pinned || syms[j].csi || plan[j].sym_off != dst0 + len ||
+                  (const char *)syms[j].symbols != src0 + len || (len & 15)) break;
+              len += (size_t)syms[j].nof_re * 8;
+            }
+          CU(cudaMemcpyAsync((char *)pp->st_e.d + dst0, src0, len, cudaMemcpyHostToDevice, sin));
+          if (syms[i].csi) CU(cudaMemcpyAsync((char *)pp->st_e.d + plan[i].csi_off, (char *)pp->st_e.h + plan[i].csi_off,
+                                              (size_t)syms[i].nof_re * 4, cudaMemcpyHostToDevice, sin));
+          i = j;
+        }
+      }
+    }
+    if (lst_total) CU(cudaMemcpyAsync(pp->st_lst.d, pp->st_lst.h, lst_total * 4, cudaMemcpyHostToDevice, sin));
+    CU(cudaMemcpyAsync(pp->st_fed.d, fed, sizeof(FecFeDesc) * nfe, cudaMemcpyHostToDevice, sin));
+  } else if (!dev_io) {
     uint32_t i = 0;
     while (i < n) {
       if (!plan[i].valid) { i++; continue; }
@@ -464,9 +629,9 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
       i = j;
     }
   }
-  CU(cudaMemcpyAsync(pp->st_cbd.d, cbd, sizeof(FecCbDesc) * ncb, cudaMemcpyHostToDevice, sin));
-  CU(cudaMemcpyAsync(pp->st_rmd.d, rmd, sizeof(FecRmDesc) * ncb, cudaMemcpyHostToDevice, sin));
-  CU(cudaMemcpyAsync(pp->st_tbd.d, tbd, sizeof(FecTbDesc) * ntb, cudaMemcpyHostToDevice, sin));
+  if (ncb) CU(cudaMemcpyAsync(pp->st_cbd.d, cbd, sizeof(FecCbDesc) * ncb, cudaMemcpyHostToDevice, sin));
+  if (ncb) CU(cudaMemcpyAsync(pp->st_rmd.d, rmd, sizeof(FecRmDesc) * ncb, cudaMemcpyHostToDevice, sin));
+  if (ntb) CU(cudaMemcpyAsync(pp->st_tbd.d, tbd, sizeof(FecTbDesc) * ntb, cudaMemcpyHostToDevice, sin));
   CU(cudaEventRecord(pp->ev_in, sin));
 
   /* ---- compute stream: rate de-matching, turbo decode per K group, TB assembly + CRC24A ---- */
@@ -474,11 +639,16 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
    * decode kernel of an earlier sub-batch (which can hold a compute stream for the length of its slowest code block) */
   cudaStream_t srm = (flags & FEC_CUDA_F_SERIAL) ? sc : ctx->s_rm;
   CU(cudaMemsetAsync(pp->d_queue, 0, sizeof(unsigned int) * 3 * FEC_NOF_K, srm));
-  CU(cudaMemsetAsync(pp->d_softmax, 0, (size_t)ncb * 4, srm));
+  if (ncb) CU(cudaMemsetAsync(pp->d_softmax, 0, (size_t)ncb * 4, srm));
   CU(cudaStreamWaitEvent(srm, pp->ev_in, 0));
+  CU(cudaEventRecord(pp->ev_fe, srm));
+  if (nfe) {
+    /* symbols -> LLRs in decode_tb order: soft demodulation, descrambling, CSI weights / UL channel de-interleaver */
+    CU(fec_launch_frontend((const FecFeDesc *)pp->st_fed.d, pp->d_csimax, ctx->d_x2masks, ctx->d_x1states, nfe, max_re, any_csi, any_uci, srm));
+    ctx->launches += 1 + (any_csi ? 1 : 0) + (any_uci ? 1 : 0);
+  }
   CU(cudaEventRecord(pp->ev[0], srm));
-  CU(fec_launch_rm((const FecRmDesc *)pp->st_rmd.d, pp->d_softmax, ncb, max_n_out, srm));
-  ctx->launches++;
+  if (ncb) { CU(fec_launch_rm((const FecRmDesc *)pp->st_rmd.d, pp->d_softmax, ncb, max_n_out, srm)); ctx->launches++; }
   CU(cudaEventRecord(pp->ev[1], srm));
   if (srm != sc) CU(cudaStreamWaitEvent(sc, pp->ev[1], 0));
   for (int k = 0; k < FEC_NOF_K; k++) {
@@ -490,16 +660,16 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
     ctx->launches += a.exact_list ? 2 : 1;
   }
   CU(cudaEventRecord(pp->ev[2], sc));
-  CU(fec_launch_tb_assemble((const FecTbDesc *)pp->st_tbd.d, (const FecCbStatus *)pp->st_status.d, ctx->d_r24a, ntb, sc));
-  ctx->launches++;
+  if (ntb) { CU(fec_launch_tb_assemble((const FecTbDesc *)pp->st_tbd.d, (const FecCbStatus *)pp->st_status.d, ctx->d_r24a, ntb, sc)); ctx->launches++; }
   CU(cudaEventRecord(pp->ev[3], sc));
   CU(cudaEventRecord(pp->ev_k, sc));
 
   /* ---- output stream: results back ---- */
   CU(cudaStreamWaitEvent(sout, pp->ev_k, 0));
   if (ncb) CU(cudaMemcpyAsync(pp->st_status.h, pp->st_status.d, sizeof(FecCbStatus) * ncb, cudaMemcpyDeviceToHost, sout));
-  CU(cudaMemcpyAsync(pp->st_ret.h, pp->st_ret.d, sizeof(int32_t) * ntb, cudaMemcpyDeviceToHost, sout));
-  if (!dev_io) CU(cudaMemcpyAsync(pp->st_data.h, pp->st_data.d, data_total, cudaMemcpyDeviceToHost, sout));
+  if (ntb) CU(cudaMemcpyAsync(pp->st_ret.h, pp->st_ret.d, sizeof(int32_t) * ntb, cudaMemcpyDeviceToHost, sout));
+  if (!dev_io && data_total) CU(cudaMemcpyAsync(pp->st_data.h, pp->st_data.d, data_total, cudaMemcpyDeviceToHost, sout));
+  if (!dev_io && syms && uci_total) CU(cudaMemcpyAsync(pp->st_uci.h, pp->st_uci.d, uci_total * 2, cudaMemcpyDeviceToHost, sout));
   CU(cudaEventRecord(pp->ev_done, sout));
   pp->ncb = ncb; pp->ntb = ntb; pp->data_total = data_total; pp->busy = 1;
   pp->t_submit = now_ms() - ctx->t_call;
@@ -514,6 +684,13 @@ static int pipe_finish(fec_cuda_ctx_t *ctx, fec_pipe_t *pp)
   pp->busy = 0;
   CU(cudaEventSynchronize(pp->ev_done));
   for (int i = 0; i < 3; i++) { float ms = 0; if (cudaEventElapsedTime(&ms, pp->ev[i], pp->ev[i + 1]) == cudaSuccess) ctx->phase_ms[i] += ms; }
+  { float ms = 0; if (cudaEventElapsedTime(&ms, pp->ev_fe, pp->ev[0]) == cudaSuccess) ctx->fe_ms += ms; }
+  if (pp->syms && !pp->dev_io)
+    for (uint32_t i = 0; i < pp->n; i++) {
+      const tbplan_t *p = &pp->plan[i];
+      const uint32_t nout = p->fe_valid ? p->nuci + pp->syms[i].nof_cqi_bits : 0;
+      if (nout) memcpy(pp->syms[i].uci_out, (int16_t *)pp->st_uci.h + p->uci_off, (size_t)nout * 2);
+    }
   if (ctx->trace) {
     float t[6] = {0, 0, 0, 0, 0, 0};
     cudaEventElapsedTime(&t[0], ctx->ev_call, pp->ev_in);
@@ -582,14 +759,14 @@ static void pipes_destroy(fec_cuda_ctx_t *ctx)
   if (ctx->s_rm) cudaStreamDestroy(ctx->s_rm);
 }
 
-extern "C" int fec_cuda_submit_tbs(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, uint32_t n, uint32_t flags, uint64_t *ticket)
+static int submit_common(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, const fec_cuda_sym_t *syms, uint32_t n, uint32_t flags, uint64_t *ticket)
 {
   if (!ctx || (!tbs && n)) return FEC_CUDA_EINVAL;
   const uint64_t id = ++ctx->call_seq;
   if (ticket) *ticket = id;
   if (n == 0) return 0;
   cudaSetDevice(ctx->device);
-  ctx->phase_ms[0] = ctx->phase_ms[1] = ctx->phase_ms[2] = 0; ctx->ev_valid = 1;
+  ctx->phase_ms[0] = ctx->phase_ms[1] = ctx->phase_ms[2] = 0; ctx->fe_ms = 0; ctx->ev_valid = 1;
   ctx->t_call = now_ms();
   if (ctx->trace) CU(cudaEventRecord(ctx->ev_call, ctx->s_copy));
   /* host buffers: small sub-batches so that the PCIe copy of one overlaps the kernels of the previous (the copy is
@@ -606,10 +783,37 @@ extern "C" int fec_cuda_submit_tbs(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, uint
     const uint32_t slot = ctx->pipe_next++;
     fec_pipe_t *pp = &ctx->pipes[slot % FEC_NPIPE];
     rc = pipe_finish(ctx, pp);                           /* ring full: the oldest sub-batch (maybe of an earlier call) completes first */
-    if (!rc) { pp->call_id = id; rc = pipe_submit(ctx, pp, tbs + off, cnt, flags, ctx->s_comp[slot & 1]); }
+    if (!rc) { pp->call_id = id; rc = pipe_submit(ctx, pp, tbs + off, syms ? syms + off : NULL, cnt, flags, ctx->s_comp[slot & 1]); }
     off += cnt; s++;
   }
   return rc;
+}
+
+extern "C" int fec_cuda_submit_tbs(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, uint32_t n, uint32_t flags, uint64_t *ticket)
+{
+  return submit_common(ctx, tbs, NULL, n, flags, ticket);
+}
+
+/* same pipeline fed with equalised symbols: the front-end kernel produces decode_tb's LLRs on the device */
+extern "C" int fec_cuda_submit_syms(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, const fec_cuda_sym_t *syms, uint32_t n, uint32_t flags, uint64_t *ticket)
+{
+  if (!syms && n) return FEC_CUDA_EINVAL;
+  return submit_common(ctx, tbs, syms, n, flags, ticket);
+}
+
+extern "C" int fec_cuda_decode_syms(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, const fec_cuda_sym_t *syms, uint32_t n, uint32_t flags)
+{
+  uint64_t ticket = 0;
+  const int rc = fec_cuda_submit_syms(ctx, tbs, syms, n, flags, &ticket);
+  const int r2 = fec_cuda_wait(ctx, ticket);
+  return rc ? rc : r2;
+}
+
+extern "C" int fec_cuda_last_frontend_ms(fec_cuda_ctx_t *ctx, float *ms)
+{
+  if (!ctx || !ms || !ctx->ev_valid) return FEC_CUDA_EINVAL;
+  *ms = ctx->fe_ms;
+  return 0;
 }
 
 extern "C" int fec_cuda_wait(fec_cuda_ctx_t *ctx, uint64_t ticket)
@@ -740,6 +944,54 @@ extern "C" int fec_cuda_rm_rx(fec_cuda_ctx_t *ctx, const int16_t *in, uint32_t E
   CUF(cudaMemcpyAsync(ctx->st_data.h, ctx->st_data.d, 18600 * 2, cudaMemcpyDeviceToHost, st));
   CUF(cudaStreamSynchronize(st));
   memcpy(soft, ctx->st_data.h, 18600 * 2);
+  return 0;
+}
+
+/* ---------------------------------------------------------------- standalone front end ---- */
+extern "C" uint32_t fec_cuda_cinit_pdsch(uint32_t rnti, uint32_t codeword, uint32_t nslot, uint32_t cell_id)
+{
+  return (rnti << 14) + (codeword << 13) + ((nslot / 2) << 9) + cell_id;
+}
+extern "C" uint32_t fec_cuda_cinit_pusch(uint32_t rnti, uint32_t nslot, uint32_t cell_id)
+{
+  return (rnti << 14) + ((nslot / 2) << 9) + cell_id;
+}
+
+extern "C" int fec_cuda_frontend(fec_cuda_ctx_t *ctx, const fec_cuda_sym_t *sy, int16_t *llr_out)
+{
+  if (!ctx || !sy || !llr_out) return FEC_CUDA_EINVAL;
+  fec_cuda_tb_t none;
+  memset(&none, 0, sizeof(none));
+  if (!fe_check(&none, sy)) return FEC_CUDA_EINVAL;
+  cudaSetDevice(ctx->device);
+  const uint32_t mod = sy->mod_bits, nb = sy->nof_re * mod, nuci = sy->nof_ack_pos + sy->nof_ri_pos;
+  const size_t symb = ((size_t)sy->nof_re * 8 + 15) & ~(size_t)15, csib = sy->csi ? (((size_t)sy->nof_re * 4 + 15) & ~(size_t)15) : 0;
+  const size_t lstb = ((size_t)2 * nuci * 4 + 15) & ~(size_t)15, ucib = (((size_t)nuci + sy->nof_cqi_bits) * 2 + 15) & ~(size_t)15;
+  const size_t outb = ((size_t)nb * 2 + 15) & ~(size_t)15;
+  void *plan = NULL;
+  /* one staging block: [symbols | csi | lists | descriptor] in, [LLRs | control-information LLRs | csi max] out */
+  if (stage_reserve(ctx, &ctx->st_e, symb + csib + lstb + sizeof(FecFeDesc)) || stage_reserve(ctx, &ctx->st_data, outb + ucib + 16)) return FEC_CUDA_ENODEV;
+  char *h = (char *)ctx->st_e.h, *d = (char *)ctx->st_e.d, *od = (char *)ctx->st_data.d;
+  memcpy(h, sy->symbols, (size_t)sy->nof_re * 8);
+  if (sy->csi) memcpy(h + symb, sy->csi, (size_t)sy->nof_re * 4);
+  FecFeDesc *f = (FecFeDesc *)(h + symb + csib + lstb);
+  memset(f, 0, sizeof(*f));
+  f->sym = (const float2 *)d; f->csi = sy->csi ? (const float *)(d + symb) : NULL;
+  f->e = (int16_t *)od; f->uci_out = (nuci + sy->nof_cqi_bits) ? (int16_t *)(od + outb) : NULL;
+  f->nof_re = sy->nof_re; f->mod = mod; f->c_init = sy->c_init & 0x7FFFFFFFu;
+  f->cols = sy->nof_symb; f->rows = sy->nof_symb ? sy->nof_re / sy->nof_symb : 0;
+  f->n_cqi = sy->nof_cqi_bits; f->nuci = nuci;
+  if (nuci) fe_build_lists(sy, f, (uint32_t *)(h + symb + csib), (const uint32_t *)(d + symb + csib));
+  cudaStream_t st = ctx->stream;
+  CUF(cudaMemcpyAsync(d, h, symb + csib + lstb + sizeof(FecFeDesc), cudaMemcpyHostToDevice, st));
+  CUF(cudaMemsetAsync(od, 0, outb, st));       /* UL: the positions behind the last de-interleaved LLR are not written */
+  CUF(fec_launch_frontend((const FecFeDesc *)(d + symb + csib + lstb), (float *)(od + outb + ucib), ctx->d_x2masks, ctx->d_x1states,
+                          1, sy->nof_re, sy->csi != NULL, f->uci_out != NULL, st));
+  ctx->launches += 1 + (sy->csi ? 1 : 0) + (f->uci_out ? 1 : 0);
+  CUF(cudaMemcpyAsync(ctx->st_data.h, od, outb + ucib, cudaMemcpyDeviceToHost, st));
+  CUF(cudaStreamSynchronize(st));
+  memcpy(llr_out, ctx->st_data.h, (size_t)nb * 2);
+  if (f->uci_out) memcpy(sy->uci_out, (char *)ctx->st_data.h + outb, ((size_t)nuci + sy->nof_cqi_bits) * 2);
   return 0;
 }
 

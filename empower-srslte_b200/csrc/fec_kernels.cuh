@@ -79,6 +79,26 @@ struct FecTbDesc {
   int32_t        *ret;         /* out: 0 / -1 */
 };
 
+/* one transport block of the front-end launch (fec_frontend.cu): equalised symbols -> int16 LLRs in decode_tb order */
+#define FEC_FE_NBLK 512          /* jump-table entries: 512 x 256 = 131072 scrambling bits (MAX_SEQ_LEN, sequence.c:38) */
+struct FecFeDesc {
+  const float2   *sym;       /* nof_re equalised symbols, 16-byte aligned */
+  const float    *csi;       /* DL: NULL or nof_re weights */
+  int16_t        *e;         /* out: nof_re*mod LLRs (DL: e_bits; UL: g_bits) */
+  const uint32_t *ack_ord;   /* UL: de-interleaved bit indices of the HARQ-ACK positions, ascending */
+  const uint32_t *ri_ord;    /* UL: de-interleaved bit indices of the RI positions, ascending */
+  const uint32_t *uci_pos;   /* UL: q positions to hand back raw (ACK then RI, caller's order) */
+  int16_t        *uci_out;   /* UL: out, nuci raw LLRs then the first n_cqi LLRs of g */
+  uint32_t        nof_re, mod, c_init;
+  uint32_t        cols, rows;          /* UL: channel interleaver matrix (cols = N_pusch_symbs); DL: cols = 0 */
+  uint32_t        nack, nri, nuci, n_cqi;
+  uint32_t        last_ri_pos;         /* UL: largest RI q position (value that ends up in g[0]) */
+  uint32_t        pad;
+};
+cudaError_t fec_launch_frontend(const FecFeDesc *descs, float *csi_max, const uint32_t *x2_masks, const uint32_t *x1_states,
+                                uint32_t ntb, uint32_t max_re, int any_csi, int any_uci, cudaStream_t st);
+extern "C" void fec_gen_gold_tables(uint32_t *x2_masks, uint32_t *x1_states);
+
 size_t fec_win_smem_bytes(const fec_geom_t *g, uint32_t slots);
 uint32_t fec_win_pick_slots(const fec_geom_t *g);
 cudaError_t fec_launch_decode(const FecDecodeArgs &a, int sm_count, cudaStream_t st);

@@ -71,6 +71,12 @@ __device__ __forceinline__ void pk_sts_u16(uint32_t addr, uint32_t val)
 #else
 #define PK_EPI_INLINE __forceinline__
 #endif
+#ifndef PK_LATE_ZERO
+#define PK_LATE_ZERO 1
+#endif
+#ifndef PK_PF_L1
+#define PK_PF_L1 1
+#endif
 #ifndef PK_CRC64
 #define PK_CRC64 1       /* CRC syndrome words by 8-byte instead of 16-byte loads */
 #endif
@@ -311,12 +317,28 @@ __device__ __forceinline__ void pk_alpha_chunk(const PkView &v, int k0, uint32_t
   }
 }
 
+/* first 40 steps of a stream (pair-interleaved layout: 40 * TPC words, contiguous) into L1, one or two lines per thread */
+template <int TPC>
+__device__ __forceinline__ void pk_prefetch_warm(const uint32_t *y, const uint32_t *s, int j)
+{
+  constexpr int NL = (40 * TPC * 4 + 127) / 128;
+#pragma unroll
+  for (int l = 0; l < (NL + TPC - 1) / TPC; l++) {
+    const int line = j + l * TPC;
+    if (line < NL) {
+      asm volatile("prefetch.global.L1 [%0];" :: "l"(y + line * 32));
+      if (s) asm volatile("prefetch.global.L1 [%0];" :: "l"(s + line * 32));
+    }
+  }
+}
+
 /* One half-iteration of one constituent decoder for the two lanes of this thread.
  * TPC = threads per code block (P/2); VEC: L % 4 == 0 (16-byte loads). Decisions go to bits_lo/bits_hi as
  * MSB-first words; bit k of a lane sits at bit index k + (8*nck - L) of its row. */
 template <int TPC, bool VEC, bool SHIFT>
 __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32_t tbase, unsigned gmask, int j,
-                                                   const int16_t *tail, uint32_t *bits_lo, uint32_t *bits_hi, PkAcc &acc)
+                                                   const int16_t *tail, uint32_t *bits_lo, uint32_t *bits_hi, PkAcc &acc,
+                                                   uint32_t *Ezero, int nEz)
 {
   const int nfull = L >> 3, rem = L & 7;
   uint32_t o[8], xs[8], es[8], ka[16];
@@ -327,6 +349,11 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
     asm volatile("prefetch.global.L2 [%0];" :: "l"(v.Yrow + off));
     asm volatile("prefetch.global.L2 [%0];" :: "l"(v.Ynext + off));
     if (!v.par) asm volatile("prefetch.global.L2 [%0];" :: "l"(v.Srow + off));
+  }
+  /* a fresh code block starts from apriori = 0; zeroed here so that the HBM fetches above are already under way */
+  if (nEz) {
+    for (int i = j; i < nEz; i += TPC) Ezero[i] = 0;
+    __syncwarp(gmask);
   }
 
   /* ---- beta warm-up over the first 40 symbols of both sub-blocks (turbodecoder_win.h:321-384) ---- */
@@ -468,6 +495,11 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
     raw = nraw;
   }
   if (cc & 3) { const int sh = 32 - 8 * (cc & 3); bits_lo[wi] = acc.wlo << sh; bits_hi[wi] = acc.whi << sh; }
+#if PK_PF_L1
+  /* the next half-iteration starts with the first 40 steps of the other decoder's rows (10 lines per stream):
+   * pull them into L1 while the CRC is reduced and the slot decides how to go on */
+  pk_prefetch_warm<TPC>(v.Ynext - 4 * j, v.par ? v.Srow - 4 * j : nullptr, j);
+#endif
 }
 
 /* ---------------------------------------------------------------- output of a finished code block ---- */
@@ -615,7 +647,7 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
   __syncwarp();
   int cb = -1, n = 0;
   uint32_t M = 0;
-  bool exhausted = false;
+  bool exhausted = false, fresh = false;
   for (;;) {
     /* ---- refill this group's slot from the work queue (group-uniform control flow) ---- */
     while (cb < 0 && !exhausted) {
@@ -640,7 +672,11 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
         continue;
       }
       cb = (int)q; n = 0;
+#if PK_LATE_ZERO
+      fresh = true;
+#else
       for (int i = j; i < Es; i += TPC) Eslot[i] = 0;   /* apriori = 0 before the first half-iteration */
+#endif
     }
     __syncwarp();
     if (!__any_sync(0xFFFFFFFFu, cb >= 0)) break;
@@ -668,7 +704,9 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
     PkAcc acc;
     acc.crc = 0; acc.emx = 0x80008000u; acc.emn = 0x7FFF7FFFu;
     uint32_t *blo = rows + (2 * j) * nw1, *bhi = rows + (2 * j + 1) * nw1;
-    pk_half_iteration<TPC, VEC, P == 8>(v, L, tbase, gmask, j, desc.soft + 3 * SS + (par ? 6 : 0), blo, bhi, acc);
+    pk_half_iteration<TPC, VEC, P == 8>(v, L, tbase, gmask, j, desc.soft + 3 * SS + (par ? 6 : 0), blo, bhi, acc,
+                                              Eslot, fresh ? Es : 0);
+    fresh = false;
     uint32_t crc = acc.crc, emx = acc.emx, emn = acc.emn;
 #pragma unroll
     for (int s = TPC / 2; s > 0; s >>= 1) {

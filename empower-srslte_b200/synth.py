@@ -217,3 +217,71 @@ def awgn_llr(e_bits, sigma, rng, amp=100.0, out=None):
         return np.ascontiguousarray(x.astype(np.int16))
     out[...] = x
     return out
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Symbols for the front end: scrambling + modulation (+ UL channel interleaver), 36.211 7.1/7.2,
+# 36.212 5.2.2.8.  Host-side synthesis only; pinned against the reference's modulator and sequence generator in
+# tests/test_synth.py.
+
+def gold_sequence(c_init, n):
+    """c(0..n-1) of 36.211 7.2 as a uint8 array; generated 28 bits per step on Python integers"""
+    def run(state, taps, total):
+        x, have = state, 31
+        while have < total:
+            new = 0
+            for t in taps:
+                new ^= x >> (have - 31 + t)
+            x |= (new & 0x0FFFFFFF) << have
+            have += 28
+        return x
+    total = 1600 + n + 31
+    x1 = run(1, (0, 3), total)
+    x2 = run(c_init & 0x7FFFFFFF, (0, 1, 2, 3), total)
+    c = ((x1 ^ x2) >> 1600) & ((1 << n) - 1)
+    return np.unpackbits(np.frombuffer(c.to_bytes((n + 7) // 8, "little"), np.uint8), bitorder="little")[:n].copy()
+
+
+def cinit_pdsch(rnti, q, nslot, cell_id):
+    return ((rnti << 14) + (q << 13) + ((nslot // 2) << 9) + cell_id) & 0xFFFFFFFF
+
+
+def cinit_pusch(rnti, nslot, cell_id):
+    return ((rnti << 14) + ((nslot // 2) << 9) + cell_id) & 0xFFFFFFFF
+
+
+def modulate(bits, mod_bits):
+    """36.211 7.1 mapping; bits: (..., n*mod_bits) of 0/1 -> complex64 (..., n)"""
+    b = 1.0 - 2.0 * bits.reshape(bits.shape[:-1] + (-1, mod_bits)).astype(np.float64)
+    if mod_bits == 1:
+        i = q = b[..., 0] / math.sqrt(2)
+    elif mod_bits == 2:
+        i, q = b[..., 0] / math.sqrt(2), b[..., 1] / math.sqrt(2)
+    elif mod_bits == 4:
+        i, q = b[..., 0] * (2 - b[..., 2]) / math.sqrt(10), b[..., 1] * (2 - b[..., 3]) / math.sqrt(10)
+    else:
+        i = b[..., 0] * (4 - b[..., 2] * (2 - b[..., 4])) / math.sqrt(42)
+        q = b[..., 1] * (4 - b[..., 3] * (2 - b[..., 5])) / math.sqrt(42)
+    return (i + 1j * q).astype(np.complex64)
+
+
+def ulsch_interleave(g_bits, mod_bits, cols, ri_pos=()):
+    """UL-SCH channel interleaver without control multiplexing payloads (36.212 5.2.2.8): g -> q; RI positions are left 0"""
+    n = g_bits.shape[-1] + len(ri_pos)
+    rows = n // mod_bits // cols
+    taken = np.zeros(n, bool)
+    taken[list(ri_pos)] = True
+    order = (np.arange(cols)[None, :, None] * rows + np.arange(rows)[:, None, None]) * mod_bits + np.arange(mod_bits)[None, None, :]
+    order = order.reshape(-1)                        # q positions in the order g is consumed (row by row)
+    order = order[~taken[order]]
+    q = np.zeros(g_bits.shape[:-1] + (n,), g_bits.dtype)
+    q[..., order] = g_bits
+    return q
+
+
+def awgn_symbols(sym, sigma, rng):
+    """complex AWGN with standard deviation sigma per real dimension, float32 (re, im) pairs out"""
+    out = np.empty(sym.shape + (2,), np.float32)
+    out[..., 0] = sym.real + sigma * rng.standard_normal(sym.shape)
+    out[..., 1] = sym.imag + sigma * rng.standard_normal(sym.shape)
+    return out

@@ -116,6 +116,49 @@ int  fec_cuda_decode_tbs(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, uint32_t n, ui
 int  fec_cuda_submit_tbs(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, uint32_t n, uint32_t flags, uint64_t *ticket);
 int  fec_cuda_wait(fec_cuda_ctx_t *ctx, uint64_t ticket);
 
+/* ---- front end: transport blocks given as equalised symbols (SURVEY 8f rows f1 + f2) ------------------------------
+ * Replaces, per codeword, the calls between the equaliser and decode_tb:
+ *   DL  srslte_pdsch_codeword_decode (pdsch.c:778-834): srslte_demod_soft_demodulate_s (demod_soft.c:437-456),
+ *       srslte_scrambling_s_offset (scrambling.c:49-52) with the sequence of srslte_sequence_pdsch (sequences.c:64-66,
+ *       sequence.c:54-86), csi_correction (pdsch.c:675-776), srslte_dlsch_decode2;
+ *   UL  srslte_pusch_decode from the demodulator on (pusch.c:617-657): demodulation, HARQ-ACK positions zeroed
+ *       (sch.c:913-916), descrambling, ulsch_deinterleave (sch.c:860-881), decode_tb on g_bits + Q'_cqi*Qm.
+ * One fused kernel writes the int16 LLRs to HBM; the host ships 8 bytes per resource element instead of 2*Qm. The
+ * LLRs are bit-identical with the reference's AVX2 build (rounding of its SIMD bodies and scalar tails, the CSI weights
+ * of its SSE loop, g[0] overwritten by the last RI position). 16-bit LLRs only (llr_is_8bit = false). */
+typedef struct {
+  const void     *symbols;      /* nof_re complex floats (cf_t), 16-byte aligned: q->d[cw] (pdsch.c:797) / q->d (pusch.c:620);
+                                   host, or device with FEC_CUDA_F_DEVICE_IO */
+  const float    *csi;          /* DL: NULL (csi_enabled = false) or nof_re weights q->csi[cw]; same memory space as symbols */
+  uint32_t        nof_re;       /* cfg->nbits.nof_re */
+  uint32_t        mod_bits;     /* bits per symbol of grant.mcs.mod: 1, 2, 4 or 6 (tb.Qm stays "Qm x Nl" as decode_tb gets it) */
+  uint32_t        c_init;       /* scrambling seed: fec_cuda_cinit_pdsch / fec_cuda_cinit_pusch */
+  uint32_t        nof_symb;     /* 0: downlink. Uplink: cfg->nbits.nof_symb = columns of the channel interleaver */
+  /* uplink control information multiplexed with the data (HOST arrays in either mode): q-bit positions as
+   * srslte_uci_decode_ack_ri leaves them in ack_ri_bits[].position (uci.c:499-546) */
+  const uint32_t *ack_pos;      /* zeroed before descrambling */
+  const uint32_t *ri_pos;       /* taken out of the de-interleaved stream */
+  uint32_t        nof_ack_pos, nof_ri_pos;
+  uint32_t        nof_cqi_bits; /* Q'_cqi * Qm: LLRs at the head of g that belong to the CQI (sch.c:951-962); decode_tb starts after them */
+  uint32_t        reserved;
+  int16_t        *uci_out;      /* out (needed if any of the three counts is non-zero): raw q LLRs (before descrambling) at
+                                   ack_pos[..] then ri_pos[..] — the input of srslte_uci_decode_ack_ri — then the first
+                                   nof_cqi_bits LLRs of g — the input of srslte_uci_decode_cqi_pusch */
+} fec_cuda_sym_t;
+
+/* tbs[i] as for fec_cuda_decode_tbs except that e_bits is ignored: DL needs nof_e_bits == nof_re * mod_bits, UL
+ * nof_e_bits = G * Qm (sch.c:965-969). tbs[i].tbs == 0 runs the front end only (control-only PUSCH). */
+int  fec_cuda_decode_syms(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, const fec_cuda_sym_t *syms, uint32_t n, uint32_t flags);
+int  fec_cuda_submit_syms(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, const fec_cuda_sym_t *syms, uint32_t n, uint32_t flags,
+                          uint64_t *ticket);
+/* device time of the front-end kernels of the last call (ms) */
+int  fec_cuda_last_frontend_ms(fec_cuda_ctx_t *ctx, float *ms);
+/* front end alone: LLRs as decode_tb would receive them (e_bits for DL, g_bits for UL), nof_re*mod_bits int16, host
+ * pointers; drop-in body of srslte_demod_soft_demodulate_s + srslte_scrambling_s_offset (+ csi / de-interleaver) */
+int  fec_cuda_frontend(fec_cuda_ctx_t *ctx, const fec_cuda_sym_t *sym, int16_t *llr_out);
+uint32_t fec_cuda_cinit_pdsch(uint32_t rnti, uint32_t codeword, uint32_t nslot, uint32_t cell_id);   /* sequences.c:64-66 */
+uint32_t fec_cuda_cinit_pusch(uint32_t rnti, uint32_t nslot, uint32_t cell_id);                       /* sequences.c:71-73 */
+
 /* bare turbo decoding of n code blocks from natural-layout LLRs (host pointers) */
 int  fec_cuda_decode_cbs(fec_cuda_ctx_t *ctx, fec_cuda_cb_t *cbs, uint32_t n, uint32_t flags);
 

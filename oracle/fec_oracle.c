@@ -529,3 +529,173 @@ double orc_bench_tb_mt(int nthreads, int ntb, uint32_t tbs, uint32_t Qm, uint32_
   pthread_barrier_destroy(&bar);
   return t1 - t0;
 }
+
+/* ================================================================== front end ====
+ * Soft demodulation, scrambling sequence, descrambling, CSI weighting and the UL-SCH channel de-interleaver: the
+ * stages between the equaliser and decode_tb. Scalar restatement of what the reference's AVX2 build computes,
+ * INCLUDING its quirks (SIMD body vs scalar tail rounding, swapped CSI weights inside a symbol pair, g[0]
+ * overwritten by RI positions); checked bit for bit against oracle/_ref in tests/test_oracle_frontend.py. */
+
+/* cvtps2dq / cvttps2dq followed by packssdw: out-of-range and NaN give the "integer indefinite" 0x80000000 -> -32768 */
+static int16_t fe_cvt_sat16(float v, int truncate)
+{
+  if (!(v >= -2147483648.0f && v < 2147483648.0f)) return -32768;
+  long r = truncate ? (long)truncf(v) : lrintf(v);          /* default rounding mode: nearest even */
+  return (int16_t)(r > 32767 ? 32767 : r < -32768 ? -32768 : r);
+}
+/* C conversion float/double -> short as gcc emits it on x86-64: cvttss2si to 32 bits, low half kept */
+static int16_t fe_cvt_c16(double v)
+{
+  if (!(v > -2147483649.0 && v < 2147483648.0)) return 0;
+  return (int16_t)(int32_t)v;
+}
+static int16_t fe_abs16(int16_t v) { return (int16_t)(v < 0 ? -v : v); }   /* pabsw: |-32768| = -32768 */
+
+/* srslte_demod_soft_demodulate_s (demod_soft.c:437-456) -> demod_{bpsk,qpsk,16qam,64qam}_lte_s (:56-60,72-74,98-138,206-219,
+ * 238-301,372-390) */
+int orc_demod_s(int mod_bits, const float *sym, int16_t *llr, int nsym)
+{
+  switch (mod_bits) {
+  case 1:
+    for (int i = 0; i < nsym; i++) {
+      const float s = -100.0f * (sym[2 * i] + sym[2 * i + 1]);
+      llr[i] = fe_cvt_c16((double)s / sqrt(2));
+    }
+    return 0;
+  case 2: {
+    /* srslte_vec_convert_fi_simd (vector_simd.c:394-429): 16 values per AVX2 step with truncation + saturation, scalar tail */
+    const float scale = (float)(-100 * sqrt(2));
+    const int len = 2 * nsym;
+    int i = 0;
+    for (; i < len - 16 + 1; i += 16)
+      for (int k = 0; k < 16; k++) llr[i + k] = fe_cvt_sat16(sym[i + k] * scale, 1);
+    for (; i < len; i++) llr[i] = fe_cvt_c16(sym[i] * scale);
+    return 0;
+  }
+  case 4: {
+    const int16_t off = (int16_t)(2 * 400 / sqrt(10));
+    int i = 0;
+    for (; i < 4 * (nsym / 4); i++) {
+      const int16_t re = fe_cvt_sat16(sym[2 * i] * -400.0f, 0), im = fe_cvt_sat16(sym[2 * i + 1] * -400.0f, 0);
+      llr[4 * i + 0] = re; llr[4 * i + 1] = im;
+      llr[4 * i + 2] = (int16_t)(fe_abs16(re) - off); llr[4 * i + 3] = (int16_t)(fe_abs16(im) - off);
+    }
+    for (; i < nsym; i++) {
+      const short yre = fe_cvt_c16(400 * sym[2 * i]), yim = fe_cvt_c16(400 * sym[2 * i + 1]);
+      llr[4 * i + 0] = (int16_t)-yre; llr[4 * i + 1] = (int16_t)-yim;
+      llr[4 * i + 2] = fe_cvt_c16(abs(yre) - 2 * 400 / sqrt(10));
+      llr[4 * i + 3] = fe_cvt_c16(abs(yim) - 2 * 400 / sqrt(10));
+    }
+    return 0;
+  }
+  case 6: {
+    const int16_t off1 = (int16_t)(4 * 700 / sqrt(42)), off2 = (int16_t)(2 * 700 / sqrt(42));
+    int i = 0;
+    for (; i < 4 * (nsym / 4); i++) {
+      for (int c = 0; c < 2; c++) {
+        const int16_t y = fe_cvt_sat16(sym[2 * i + c] * -700.0f, 0);
+        const int16_t a1 = (int16_t)(fe_abs16(y) - off1);
+        const int16_t a2 = (int16_t)(fe_abs16(a1) - off2);
+        llr[6 * i + c] = y; llr[6 * i + 2 + c] = a1; llr[6 * i + 4 + c] = a2;
+      }
+    }
+    for (; i < nsym; i++) {
+      for (int c = 0; c < 2; c++) {
+        const float y = fe_cvt_c16(700 * sym[2 * i + c]);
+        llr[6 * i + c] = fe_cvt_c16(-y);
+        llr[6 * i + 2 + c] = fe_cvt_c16(abs((int)y) - 4 * 700 / sqrt(42));
+        llr[6 * i + 4 + c] = fe_cvt_c16(abs(llr[6 * i + 2 + c]) - 2 * 700 / sqrt(42));
+      }
+    }
+    return 0;
+  }
+  default:
+    return -1;
+  }
+}
+
+/* srslte_sequence_set_LTE_pr (sequence.c:54-86), 36.211 7.2: c(n) = x1(n+1600) ^ x2(n+1600), x1(0)=1, x2 from c_init;
+ * written with two 31-bit shift registers */
+void orc_sequence(uint32_t c_init, uint32_t len, uint8_t *c)
+{
+  uint32_t x1 = 1, x2 = c_init & 0x7FFFFFFFu;
+  for (uint32_t n = 0; n < 1600 + len; n++) {
+    if (n >= 1600) c[n - 1600] = (uint8_t)((x1 ^ x2) & 1);
+    const uint32_t f1 = ((x1 >> 3) ^ x1) & 1, f2 = ((x2 >> 3) ^ (x2 >> 2) ^ (x2 >> 1) ^ x2) & 1;
+    x1 = (x1 >> 1) | (f1 << 30);
+    x2 = (x2 >> 1) | (f2 << 30);
+  }
+}
+
+/* sequences.c:64-73 */
+uint32_t orc_cinit_pdsch(uint32_t rnti, uint32_t q, uint32_t nslot, uint32_t cell_id) { return (rnti << 14) + (q << 13) + ((nslot / 2) << 9) + cell_id; }
+uint32_t orc_cinit_pusch(uint32_t rnti, uint32_t nslot, uint32_t cell_id) { return (rnti << 14) + ((nslot / 2) << 9) + cell_id; }
+
+/* srslte_scrambling_s_offset (scrambling.c:49-52) -> srslte_vec_neg_sss (vector_simd.c:223-250): psignw with +-1, wrapping */
+void orc_descramble_s(const uint8_t *c, int16_t *llr, uint32_t len)
+{
+  for (uint32_t i = 0; i < len; i++) if (c[i]) llr[i] = (int16_t)-llr[i];
+}
+
+/* csi_correction, 16-bit branch of the SSE build (pdsch.c:675-776) */
+void orc_csi_s(int mod_bits, int16_t *e, const float *csi, uint32_t nof_bits)
+{
+  const uint32_t qm = (uint32_t)mod_bits, nsym = nof_bits / qm;
+  float csi_max = 1.0f;
+  if (nsym) { csi_max = -INFINITY; for (uint32_t i = 0; i < nsym; i++) if (csi[i] > csi_max) csi_max = csi[i]; }  /* srslte_vec_max_fi */
+  const float scale = 32767 / csi_max;
+  uint32_t i = 0;        /* bit index */
+#define CSI_W(s) fe_cvt_sat16(csi[s] * scale, 0)
+#define CSI_MULHI(x, w) ((int16_t)(((int32_t)(x) * (int32_t)(w)) >> 16))
+  if (qm == 2) {
+    for (; nof_bits >= 4 && i < nof_bits - 3; i += 4) {   /* (the reference's unsigned bound underflows below 4 bits) */
+      /* two symbols per step; the blend hands each symbol the OTHER one's weight */
+      const uint32_t s = i / 2;
+      const int16_t w1 = CSI_W(s), w2 = CSI_W(s + 1);
+      e[i] = CSI_MULHI(e[i], w2); e[i + 1] = CSI_MULHI(e[i + 1], w2);
+      e[i + 2] = CSI_MULHI(e[i + 2], w1); e[i + 3] = CSI_MULHI(e[i + 3], w1);
+    }
+  } else if (qm == 4) {
+    for (; nof_bits >= 4 && i < nof_bits - 3; i += 4) {
+      const int16_t w = CSI_W(i / 4);
+      for (int k = 0; k < 4; k++) e[i + k] = CSI_MULHI(e[i + k], w);
+    }
+  } else if (qm == 6) {
+    for (; nof_bits >= 12 && i < nof_bits - 11; i += 12) {  /* two symbols per step; the middle quad takes [w3 w3 w1 w1] */
+      const uint32_t s = i / 6;
+      const int16_t w1 = CSI_W(s), w3 = CSI_W(s + 1);
+      for (int k = 0; k < 4; k++) e[i + k] = CSI_MULHI(e[i + k], w1);
+      e[i + 4] = CSI_MULHI(e[i + 4], w3); e[i + 5] = CSI_MULHI(e[i + 5], w3);
+      e[i + 6] = CSI_MULHI(e[i + 6], w1); e[i + 7] = CSI_MULHI(e[i + 7], w1);
+      for (int k = 8; k < 12; k++) e[i + k] = CSI_MULHI(e[i + k], w3);
+    }
+  }
+  i /= qm;
+  for (; i < nsym; i++) {
+    const float w = csi[i] / csi_max;
+    for (uint32_t k = 0; k < qm; k++) e[qm * i + k] = fe_cvt_c16((float)e[qm * i + k] * w);
+  }
+#undef CSI_W
+#undef CSI_MULHI
+}
+
+/* ulsch_deinterleave (sch.c:860-881) = ulsch_interleave_gen (:550-568) + srslte_vec_lut_sis (vector.c:119-123): q is
+ * column-major (cols SC-FDMA symbols x rows), g row-major without the RI positions; RI positions get lut 0, so g[0]
+ * ends up holding the LAST RI position's value (scatter in ascending q order). g must be pre-filled by the caller if the
+ * untouched tail matters (the reference leaves it as it was). */
+void orc_ulsch_deinterleave(const int16_t *q, uint32_t Qm, uint32_t Hp, uint32_t cols, int16_t *g, const uint32_t *ri_pos, uint32_t nri)
+{
+  const uint32_t rows = Hp / cols, n = Hp * Qm;
+  uint8_t *present = calloc(n + 1, 1);
+  uint32_t *lut = calloc(n + 1, sizeof(uint32_t));
+  for (uint32_t i = 0; i < nri; i++) present[ri_pos[i]] = 1;
+  uint32_t idx = 0;
+  for (uint32_t j = 0; j < rows; j++)
+    for (uint32_t i = 0; i < cols; i++)
+      for (uint32_t k = 0; k < Qm; k++) {
+        const uint32_t p = (i * rows + j) * Qm + k;
+        lut[p] = present[p] ? 0 : idx++;
+      }
+  for (uint32_t p = 0; p < n; p++) g[lut[p]] = q[p];
+  free(present); free(lut);
+}

@@ -72,6 +72,16 @@ int   orc_tb_decode(void *p, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t no
                     uint32_t max_its, uint8_t *data, uint8_t *cb_crc_out, uint32_t *cb_its); /* sch.c:307-498 */
 void  orc_tb_get_soft(void *p, int cb, int16_t *out);
 
+/* front end in front of decode_tb: see the section header in fec_oracle.c */
+int      orc_demod_s(int mod_bits, const float *sym, int16_t *llr, int nsym);                 /* demod_soft.c:437-456 */
+void     orc_sequence(uint32_t c_init, uint32_t len, uint8_t *c);                              /* sequence.c:54-86 */
+uint32_t orc_cinit_pdsch(uint32_t rnti, uint32_t q, uint32_t nslot, uint32_t cell_id);         /* sequences.c:64-66 */
+uint32_t orc_cinit_pusch(uint32_t rnti, uint32_t nslot, uint32_t cell_id);                     /* sequences.c:71-73 */
+void     orc_descramble_s(const uint8_t *c, int16_t *llr, uint32_t len);                       /* scrambling.c:49-52 */
+void     orc_csi_s(int mod_bits, int16_t *e, const float *csi, uint32_t nof_bits);             /* pdsch.c:675-776 */
+void     orc_ulsch_deinterleave(const int16_t *q, uint32_t Qm, uint32_t Hp, uint32_t cols, int16_t *g,
+                                const uint32_t *ri_pos, uint32_t nri);                         /* sch.c:860-881 */
+
 /* multithreaded timing harness for bench.py's cpu_baseline leg ("port") */
 double orc_bench_tb_mt(int nthreads, int ntb, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits,
                        const int16_t *e_bits_all, uint32_t max_its, int reps, uint64_t *out3);

@@ -142,7 +142,64 @@ def gen_tb():
     np.savez_compressed(os.path.join(OUT, "tb.npz"), **out)
 
 
+def fe_symbols(n, seed):
+    """deterministic equalised symbols: integer pseudo-Gaussians scaled in float64, rounded once to float32"""
+    from _libs import aligned
+    a = aligned(2 * n, np.float32)
+    a[:] = (int_gauss(2 * n, seed).astype(np.float64) * (0.75 / 65536.0)).astype(np.float32)
+    return a
+
+
+def fe_csi(n, seed):
+    from _libs import aligned
+    a = aligned(n, np.float32)
+    a[:] = (0.2 + (np.abs(int_gauss(n, seed)) % 60000).astype(np.float64) / 40000.0).astype(np.float32)
+    return a
+
+
+def gen_frontend():
+    """LLRs the reference hands to decode_tb from equalised symbols: DL = demodulate + descramble (+ csi_correction),
+    UL = pusch.c:617-657 with HARQ-ACK / RI positions (q after descrambling and g after ulsch_deinterleave)."""
+    out = {}
+    dl, ul = [], []
+    for mod, n, use_csi, c_init in [(1, 37, 0, 11), (2, 1201, 0, 0x1234567), (2, 1201, 1, 0x1234567), (4, 2401, 1, 99), (4, 403, 0, 7),
+                                    (6, 15000, 0, 0x2C0A21), (6, 15000, 1, 0x2C0A21), (6, 1001, 1, 5), (6, 7, 0, 1)]:
+        i = len(dl)
+        sym = fe_symbols(n, 700 + i)
+        e = np.zeros(n * mod + 32, np.int16)
+        assert R.ref_demod_s(mod, P(sym), P(e), n) == 0
+        assert R.ref_descramble_s(c_init, P(e), n * mod) == 0
+        if use_csi:
+            assert R.ref_csi_s(mod, P(e), P(fe_csi(n, 900 + i)), n * mod) == 0
+        e = e[: n * mod]
+        out[f"dl_crc_{i}"] = np.array([crc32(e)], np.uint32)
+        if n <= 1300:
+            out[f"dl_e_{i}"] = e.copy()
+        dl.append((mod, n, use_csi, c_init, 700 + i, 900 + i))
+    for mod, prb, cols, nack, nri, c_init in [(2, 6, 12, 0, 0, 3), (4, 10, 12, 1, 1, 0x55AA55), (4, 25, 12, 2, 0, 77), (6, 12, 11, 0, 1, 1234567)]:
+        i = len(ul)
+        n = 12 * prb * cols
+        sym = fe_symbols(n, 800 + i)
+        t = C.c_void_p(R.ref_ul_new(100))
+        uci_len = np.array([nack, nri, 0], np.uint32)
+        ioff = np.array([9, 6, 7], np.uint32)
+        data, o1, o2 = np.zeros(4096, np.uint8), np.zeros(4, np.uint8), np.zeros(64, np.uint8)
+        q, g = np.zeros(n * mod, np.int16), np.zeros(n * mod, np.int16)
+        ap, rp, cnt = np.zeros(12 * 288, np.uint32), np.zeros(12 * 288, np.uint32), np.zeros(2, np.uint32)
+        R.ref_ul_decode(t, 0, mod, 0, prb, cols, c_init, P(sym), P(uci_len), P(ioff), 8, P(data), P(o1), P(o2), P(q), P(g), None,
+                        P(ap), P(rp), P(cnt))
+        R.ref_ul_free(t)
+        ng = n * mod - int(cnt[1])
+        out[f"ul_ack_{i}"], out[f"ul_ri_{i}"] = ap[: cnt[0]].copy(), rp[: cnt[1]].copy()
+        out[f"ul_crc_{i}"] = np.array([crc32(q), crc32(g[:ng])], np.uint32)
+        out[f"ul_g0_{i}"] = g[:64].copy()
+        ul.append((mod, prb, cols, nack, nri, c_init, 800 + i))
+    out["dl"], out["ul"] = np.array(dl, np.int64), np.array(ul, np.int64)
+    np.savez_compressed(os.path.join(OUT, "frontend.npz"), **out)
+
+
 if __name__ == "__main__":
+    gen_frontend()
     gen_tdec()
     gen_tables()
     gen_tb()

@@ -52,3 +52,39 @@ def soft_crc_ref_layout(s, K, P):
     if P == 0:
         return crc32(s[: 3 * K + 12])
     return crc32(np.concatenate([s[0:K], s[K + 32:2 * K + 32], s[2 * K + 64:3 * K + 64], s[3 * K + 96:3 * K + 108]]))
+
+
+def fe_symbols(n, seed):
+    """same generator as oracle/gen_golden.py: 16-byte aligned float32 (re, im) pairs"""
+    from _libs import aligned
+    a = aligned(2 * n, np.float32)
+    a[:] = (int_gauss(2 * n, seed).astype(np.float64) * (0.75 / 65536.0)).astype(np.float32)
+    return a
+
+
+def fe_csi(n, seed):
+    from _libs import aligned
+    a = aligned(n, np.float32)
+    a[:] = (0.2 + (np.abs(int_gauss(n, seed)) % 60000).astype(np.float64) / 40000.0).astype(np.float32)
+    return a
+
+
+def fe_dl_cases():
+    """yield dict(mod, n, sym, csi or None, c_init, crc, e or None): LLRs the reference hands to srslte_dlsch_decode2"""
+    z = np.load(os.path.join(GOLD, "frontend.npz"))
+    for i, (mod, n, use_csi, c_init, s1, s2) in enumerate(z["dl"]):
+        mod, n, c_init = int(mod), int(n), int(c_init)
+        yield dict(mod=mod, n=n, sym=fe_symbols(n, int(s1)), csi=fe_csi(n, int(s2)) if use_csi else None, c_init=c_init,
+                   crc=int(z[f"dl_crc_{i}"][0]), e=z[f"dl_e_{i}"] if f"dl_e_{i}" in z.files else None,
+                   id=f"dl-qm{mod}-n{n}-{'csi' if use_csi else 'nocsi'}")
+
+
+def fe_ul_cases():
+    """yield dict(mod, prb, cols, sym, c_init, ack_pos, ri_pos, crc_q, crc_g, g0): pusch.c:617-657 outputs"""
+    z = np.load(os.path.join(GOLD, "frontend.npz"))
+    for i, (mod, prb, cols, nack, nri, c_init, s1) in enumerate(z["ul"]):
+        mod, prb, cols = int(mod), int(prb), int(cols)
+        yield dict(mod=mod, prb=prb, cols=cols, sym=fe_symbols(12 * prb * cols, int(s1)), c_init=int(c_init),
+                   ack_pos=[int(v) for v in z[f"ul_ack_{i}"]], ri_pos=[int(v) for v in z[f"ul_ri_{i}"]],
+                   crc_q=int(z[f"ul_crc_{i}"][0]), crc_g=int(z[f"ul_crc_{i}"][1]), g0=z[f"ul_g0_{i}"],
+                   id=f"ul-qm{mod}-prb{prb}-ack{int(nack)}-ri{int(nri)}")

@@ -39,6 +39,17 @@ def oracle():
         lib.orc_bench_tb_mt.argtypes = [C.c_int, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p,
                                         C.c_uint32, C.c_int, C.c_void_p]
         lib.orc_map.argtypes = [C.c_int, C.c_int] + [C.c_void_p] * 6
+        lib.orc_demod_s.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+        lib.orc_sequence.argtypes = [C.c_uint32, C.c_uint32, C.c_void_p]
+        lib.orc_sequence.restype = None
+        lib.orc_descramble_s.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
+        lib.orc_descramble_s.restype = None
+        lib.orc_csi_s.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32]
+        lib.orc_csi_s.restype = None
+        lib.orc_cinit_pdsch.restype = C.c_uint32
+        lib.orc_cinit_pusch.restype = C.c_uint32
+        lib.orc_ulsch_deinterleave.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32]
+        lib.orc_ulsch_deinterleave.restype = None
         _cache["orc"] = lib
     return _cache["orc"]
 
@@ -47,8 +58,8 @@ def ref():
     if "ref" not in _cache:
         so = os.path.join(ORACLE_DIR, "_ref", "libsrslte_ref.so")
         if os.path.isdir("/root/reference/lib/src/phy/fec"):
-            shim = os.path.join(ORACLE_DIR, "ref_shim.c")
-            if not os.path.exists(so) or os.path.getmtime(shim) > os.path.getmtime(so):
+            shims = [os.path.join(ORACLE_DIR, f) for f in ("ref_shim.c", "ref_shim_fe.c", "Makefile")]
+            if not os.path.exists(so) or any(os.path.getmtime(f) > os.path.getmtime(so) for f in shims):
                 subprocess.check_call(["make", "-s", "-j8", "-C", ORACLE_DIR, "ref"])
         if not os.path.exists(so):
             _cache["ref"] = None
@@ -69,9 +80,38 @@ def ref():
         lib.ref_bench_tb_mt.restype = C.c_double
         lib.ref_bench_tb_mt.argtypes = [C.c_int, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p,
                                         C.c_uint32, C.c_int, C.c_int, C.c_void_p]
+        if hasattr(lib, "ref_cw_new"):           # front-end shim (ref_shim_fe.c)
+            lib.ref_cw_new.restype = C.c_void_p
+            lib.ref_cw_new.argtypes = [C.c_int, C.c_uint32]
+            lib.ref_cw_free.argtypes = [C.c_void_p]
+            lib.ref_cw_reset.argtypes = [C.c_void_p, C.c_uint32]
+            lib.ref_cw_decode.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
+                                          C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+            lib.ref_ul_new.restype = C.c_void_p
+            lib.ref_ul_new.argtypes = [C.c_int]
+            lib.ref_ul_free.argtypes = [C.c_void_p]
+            lib.ref_ul_reset.argtypes = [C.c_void_p, C.c_uint32]
+            lib.ref_ul_decode.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32] + [C.c_void_p] * 3 + \
+                                         [C.c_uint32] + [C.c_void_p] * 9
+            lib.ref_modulate.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+            lib.ref_demod_s.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+            lib.ref_sequence.argtypes = [C.c_uint32, C.c_uint32, C.c_void_p]
+            lib.ref_descramble_s.argtypes = [C.c_uint32, C.c_void_p, C.c_uint32]
+            lib.ref_csi_s.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32]
+            lib.ref_cinit_pdsch.restype = C.c_uint32
+            lib.ref_cinit_pusch.restype = C.c_uint32
+            lib.ref_ulsch_deinterleave.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32]
         assert lib.ref_init() == 0
         _cache["ref"] = lib
     return _cache["ref"]
+
+
+def aligned(n, dtype, align=64):
+    """zeroed 1-D array whose data pointer is `align`-byte aligned (what srslte_vec_malloc hands the reference's SIMD loops)"""
+    item = np.dtype(dtype).itemsize
+    raw = np.zeros(n * item + align, np.uint8)
+    off = (-raw.ctypes.data) % align
+    return raw[off:off + n * item].view(dtype)
 
 
 ALL_K = (list(range(40, 513, 8)) + list(range(528, 1025, 16)) + list(range(1056, 2049, 32))

@@ -93,3 +93,23 @@ def test_golden_tb(orc, case):
         if ret == 0:
             assert (d[: tbs // 8] == case["tbdata"]).all()
     orc.orc_tb_free(t)
+
+
+@pytest.mark.parametrize("case", list(G.fe_dl_cases()), ids=lambda c: c["id"])
+def test_golden_frontend_dl(orc, case):
+    """demodulate + descramble (+ CSI weights): LLRs of the reference's pdsch.c:795-813"""
+    import _fe
+    e, _ = _fe.oracle_frontend(orc, case["sym"], case["mod"], case["c_init"], case["csi"])
+    assert G.crc32(e) == case["crc"]
+    if case["e"] is not None:
+        assert (e == case["e"]).all()
+
+
+@pytest.mark.parametrize("case", list(G.fe_ul_cases()), ids=lambda c: c["id"])
+def test_golden_frontend_ul(orc, case):
+    """pusch.c:617-657: HARQ-ACK positions zeroed, descrambling, channel de-interleaver around the RI positions"""
+    import _fe
+    g, _ = _fe.oracle_frontend(orc, case["sym"], case["mod"], case["c_init"], None, case["cols"], case["ack_pos"], case["ri_pos"])
+    ng = g.size - len(case["ri_pos"])
+    assert (g[:64] == case["g0"]).all()
+    assert G.crc32(g[:ng]) == case["crc_g"]

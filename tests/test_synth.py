@@ -5,6 +5,7 @@ import importlib
 import numpy as np
 
 import _golden as G
+from _libs import P
 
 synth = importlib.import_module("empower-srslte_b200.synth")
 
@@ -44,3 +45,32 @@ def test_llr_convention_and_contiguity():
     e = np.array([[0, 1, 1, 0]], np.uint8)
     llr = synth.awgn_llr(e, 0.0, np.random.default_rng(0))
     assert llr.flags["C_CONTIGUOUS"] and llr.dtype == np.int16 and llr.tolist() == [[-100, 100, 100, -100]]
+
+
+def test_symbol_synthesis_matches_reference(reflib):
+    """scrambling sequence, modulation mapping and the UL channel interleaver of the symbol synthesiser against the
+    reference's srslte_sequence_LTE_pr / srslte_mod_modulate / ulsch_deinterleave"""
+    from _libs import aligned
+    rng = np.random.default_rng(8)
+    for c_init, n in ((1, 40), (0x2345678, 90000), (synth.cinit_pdsch(0x1234, 1, 7, 301), 777)):
+        want = np.zeros(n, np.uint8)
+        assert reflib.ref_sequence(c_init, n, P(want)) == 0
+        assert (synth.gold_sequence(c_init, n) == want).all()
+    assert synth.cinit_pdsch(1234, 1, 13, 77) == reflib.ref_cinit_pdsch(1234, 1, 13, 77)
+    assert synth.cinit_pusch(1234, 13, 77) == reflib.ref_cinit_pusch(1234, 13, 77)
+    for mod in (1, 2, 4, 6):
+        bits = rng.integers(0, 2, 64 * 6 * mod).astype(np.uint8)
+        want = aligned(2 * bits.size // mod, np.float32)
+        assert reflib.ref_modulate(mod, P(bits), P(want), bits.size) == bits.size // mod
+        got = synth.modulate(bits, mod)
+        assert np.allclose(got.view(np.float32), want, atol=1e-6), mod
+    # interleave here, de-interleave there
+    for mod, prb, cols, nri in ((2, 3, 12, 0), (4, 5, 12, 6), (6, 4, 11, 3)):
+        rows = 12 * prb
+        ri_pos = [((rows - 1 - i // 4) + rows * (1, 10, 7, 4)[i % 4]) * mod + k for i in range(nri) for k in range(mod)]
+        g = rng.integers(1, 1000, rows * cols * mod - len(ri_pos)).astype(np.int16)
+        q = synth.ulsch_interleave(g, mod, cols, ri_pos)
+        back = np.zeros(q.size, np.int16)
+        pos = np.array(ri_pos + [0], np.uint32)
+        assert reflib.ref_ulsch_deinterleave(P(q), mod, rows * cols, cols, P(back), P(pos), len(ri_pos)) == 0
+        assert (back[1: g.size] == g[1:]).all() and (nri or back[0] == g[0])
