@@ -199,6 +199,8 @@ def main():
     ap.add_argument("--sigma", type=float, default=0.45, help="AWGN std of the synthetic LLRs (0.45 = operating point)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-worst-case", action="store_true")
+    ap.add_argument("--no-symbols", action="store_true", help="skip the leg that starts from equalised symbols (front end)")
+    ap.add_argument("--sigma-sym", type=float, default=0.062, help="AWGN std per real dimension of the synthetic 64QAM symbols")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
@@ -318,6 +320,75 @@ def main():
     h2d = B * NBITS * 2 + B * C_CB * (32 + 48) + B * 520
     d2h = B * (((TBS // 8 + 3 + 768 + 15) // 16) * 16) + B * C_CB * 8 + B * 4
 
+    # ---- front-end leg: the same transport blocks given as equalised 64QAM symbols (8 B per resource element
+    #      instead of 12 B of LLRs); soft demodulation + descrambling run in the fused front-end kernel on the device ----
+    front = None
+    if not args.no_symbols:
+        synth = importlib.import_module("empower-srslte_b200.synth")
+        nre = NBITS // QM
+        h_sym = pkg.PinnedArray((B, nre, 2), np.float32)
+        rng = np.random.default_rng(5000 + rank)
+        ncw = payload.shape[0]
+        c_inits = [synth.cinit_pdsch(0x1000 + k, 0, 2 * (k % 10), 1) for k in range(ncw)]
+        e = synth.encode_tbs(payload, TBS, QM, RV, NBITS)
+        cw_sym = np.stack([synth.modulate(e[k] ^ synth.gold_sequence(c_inits[k], NBITS), QM) for k in range(ncw)])
+        for i0 in range(0, B, 64):
+            i1 = min(B, i0 + 64)
+            h_sym.a[i0:i1] = synth.awgn_symbols(cw_sym[np.arange(i0, i1) % ncw], args.sigma_sym, rng)
+        d_sym = torch.from_numpy(h_sym.a).to(f"cuda:{local_rank}")
+        sy_ab = []
+        for dev in (True, False):
+            sets = []
+            for s_ in range(2):
+                sd = (pkg.SymDesc * B)()
+                base = d_sym.data_ptr() if dev else h_sym.a.ctypes.data
+                for i in range(B):
+                    sd[i].symbols, sd[i].nof_re, sd[i].mod_bits, sd[i].c_init = base + i * nre * 8, nre, QM, c_inits[i % ncw]
+                sets.append(sd)
+            sy_ab.append(sets)
+
+        def timed_syms(tb_sets, sym_sets, flags, steps):
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            prev = None
+            for i in range(steps):
+                t = fec.submit_syms(tb_sets[i & 1], sym_sets[i & 1], flags)
+                if prev is not None:
+                    fec.wait(prev)
+                prev = t
+            fec.wait(prev)
+            e1.record(stream)
+            barrier()
+            return shard.reduce_job(dist if world > 1 else None, f"cuda:{local_rank}", e0.elapsed_time(e1))[0]
+
+        for i in range(6):
+            fec.decode_syms(dd_ab[i & 1], sy_ab[0][i & 1], pkg.F_DEVICE_IO)
+        ms_sd = timed_syms(dd_ab, sy_ab[0], pkg.F_DEVICE_IO, args.steps)
+        ok_s, its_s = tally(dd)
+        fec.decode_syms(dd, sy_ab[0][0], pkg.F_DEVICE_IO | pkg.F_SERIAL)
+        fe_ms = fec.last_frontend_ms()
+        ph_s = fec.last_phase_ms()
+        out_host = d_out[0].cpu().numpy()
+        bad = sum(1 for i in range(B) if dd[i].ret == 0 and not (out_host[i, :TBS // 8] == payload[i % ncw]).all())
+        if bad:
+            raise SystemExit(f"bench.py: {bad} CRC-passing transport blocks of the symbol leg differ from the transmitted payload")
+        for i in range(6):
+            fec.decode_syms(hd_ab[i & 1], sy_ab[1][i & 1], 0)
+        ms_sh = timed_syms(hd_ab, sy_ab[1], 0, args.steps)
+        ok_sh, _ = tally(hd)
+        fe_bytes = B * (nre * 8 + NBITS * 2)
+        front = dict(workload="same TBs as 64QAM symbols (15000 RE), soft demodulation + descrambling on the device",
+                     sigma_sym=args.sigma_sym, value=allsum(ok_s) * TBS * args.steps / (ms_sd / 1e3) / 1e9, unit=UNIT,
+                     ms_per_step=ms_sd / args.steps, tb_ok_frac=allsum(ok_s) / (world * B), halfits_per_cb=allsum(its_s) / (world * B * C_CB),
+                     e2e=dict(value=allsum(ok_sh) * TBS * args.steps / (ms_sh / 1e3) / 1e9, unit=UNIT, ms_per_step=ms_sh / args.steps,
+                              h2d_bytes_per_step=B * nre * 8 + B * C_CB * (32 + 48) + B * (520 + 80), d2h_bytes_per_step=d2h),
+                     serial_phases_ms=dict(frontend=fe_ms, rate_dematch=ph_s[0], turbo_decode=ph_s[1], tb_assemble_crc24a=ph_s[2]),
+                     frontend_kernel=dict(ms_per_launch=fe_ms, algorithmic_bytes=fe_bytes, achieved=fe_bytes / (fe_ms / 1e3) / 1e9,
+                                          peak=peaks()["hbm_gbs"], unit="GB/s", frac=fe_bytes / (fe_ms / 1e3) / 1e9 / peaks()["hbm_gbs"], bound="hbm"))
+        # the LLR legs below reuse dd / hd: put the soft buffers back into the state of the LLR workload
+        fec.decode_tbs(dd, pkg.F_DEVICE_IO)
+
     # ---- worst case: all 8 half-iterations for every code block (no early stop), same inputs ----
     worst = None
     if not args.no_worst_case:
@@ -378,7 +449,7 @@ def main():
                     e2e=dict(value=e2e_val, unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h, ms_per_step=ms_e / args.steps,
                              sync_ms_per_step=ms_e_sync / args.steps),
                     sync_ms_per_step=ms_sync / args.steps,
-                    gpu_launches=launches, clocks=clocks, roofline=roof, worst_case_8_halfits=worst, cpu_baseline=cpu)
+                    gpu_launches=launches, clocks=clocks, roofline=roof, worst_case_8_halfits=worst, frontend_symbols=front, cpu_baseline=cpu)
         print(json.dumps(line), flush=True)
     fec.close()
     if world > 1:

@@ -432,7 +432,7 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
   uint32_t grp_cnt[FEC_NOF_K], grp_off[FEC_NOF_K], grp_fill[FEC_NOF_K];
   memset(grp_cnt, 0, sizeof(grp_cnt));
   uint32_t ncb = 0, ntb = 0, nfe = 0, max_re = 0;
-  int any_csi = 0, any_uci = 0;
+  int any_csi = 0, any_uci = 0, fe_kinds = 0;
   size_t e_total = 0, data_total = 0, sym_total = 0, lst_total = 0, uci_total = 0;
   pp->tbs = tbs; pp->syms = syms; pp->n = n; pp->dev_io = dev_io; pp->ncb = pp->ntb = 0; pp->busy = 0;
 
@@ -455,6 +455,7 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
     if (sy) {
       /* the front end runs for every transport block whose symbols are usable, also for control-only PUSCH (tbs == 0) */
       p->fe_valid = 1; nfe++;
+      fe_kinds |= sy->nof_symb ? 2 : 1;
       if (sy->nof_re > max_re) max_re = sy->nof_re;
       p->sym_off = sym_total; sym_total += ((size_t)sy->nof_re * 8 + 15) & ~(size_t)15;
       if (sy->csi) { any_csi = 1; p->csi_off = sym_total; sym_total += ((size_t)sy->nof_re * 4 + 15) & ~(size_t)15; }
@@ -644,8 +645,8 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
   CU(cudaEventRecord(pp->ev_fe, srm));
   if (nfe) {
     /* symbols -> LLRs in decode_tb order: soft demodulation, descrambling, CSI weights / UL channel de-interleaver */
-    CU(fec_launch_frontend((const FecFeDesc *)pp->st_fed.d, pp->d_csimax, ctx->d_x2masks, ctx->d_x1states, nfe, max_re, any_csi, any_uci, srm));
-    ctx->launches += 1 + (any_csi ? 1 : 0) + (any_uci ? 1 : 0);
+    CU(fec_launch_frontend((const FecFeDesc *)pp->st_fed.d, pp->d_csimax, ctx->d_x2masks, ctx->d_x1states, nfe, max_re, any_csi, any_uci, fe_kinds, srm));
+    ctx->launches += (fe_kinds == 3 ? 2 : 1) + (any_csi ? 1 : 0) + (any_uci ? 1 : 0);
   }
   CU(cudaEventRecord(pp->ev[0], srm));
   if (ncb) { CU(fec_launch_rm((const FecRmDesc *)pp->st_rmd.d, pp->d_softmax, ncb, max_n_out, srm)); ctx->launches++; }
@@ -986,7 +987,7 @@ extern "C" int fec_cuda_frontend(fec_cuda_ctx_t *ctx, const fec_cuda_sym_t *sy, 
   CUF(cudaMemcpyAsync(d, h, symb + csib + lstb + sizeof(FecFeDesc), cudaMemcpyHostToDevice, st));
   CUF(cudaMemsetAsync(od, 0, outb, st));       /* UL: the positions behind the last de-interleaved LLR are not written */
   CUF(fec_launch_frontend((const FecFeDesc *)(d + symb + csib + lstb), (float *)(od + outb + ucib), ctx->d_x2masks, ctx->d_x1states,
-                          1, sy->nof_re, sy->csi != NULL, f->uci_out != NULL, st));
+                          1, sy->nof_re, sy->csi != NULL, f->uci_out != NULL, sy->nof_symb ? 2 : 1, st));
   ctx->launches += 1 + (sy->csi ? 1 : 0) + (f->uci_out ? 1 : 0);
   CUF(cudaMemcpyAsync(ctx->st_data.h, od, outb + ucib, cudaMemcpyDeviceToHost, st));
   CUF(cudaStreamSynchronize(st));

@@ -182,9 +182,10 @@ __global__ void __launch_bounds__(FE_THREADS) fec_fe_csimax_kernel(const FecFeDe
   }
 }
 
+/* ---- UL tile: per-bit handling of the control positions, LLRs scattered straight to their de-interleaved places ---- */
 template <int MOD>
-__device__ __forceinline__ void fe_tile(const FecFeDesc &d, uint32_t s0, const float *csi_max, const uint32_t *x2_masks,
-                                        const uint32_t *x1_states, const FeConst &kc, uint32_t *cw, int16_t *tile)
+__device__ __forceinline__ void fe_tile_ul(const FecFeDesc &d, uint32_t s0, const uint32_t *x2_masks,
+                                           const uint32_t *x1_states, const FeConst &kc, uint32_t *cw)
 {
   constexpr uint32_t mod = MOD;
   const uint32_t nsym = min((uint32_t)FE_SEG, d.nof_re - s0);
@@ -202,10 +203,8 @@ __device__ __forceinline__ void fe_tile(const FecFeDesc &d, uint32_t s0, const f
   }
   __syncthreads();
 
-  const bool ul = d.cols != 0;
+  constexpr bool ul = true;
   const uint32_t body_end = (mod == 2) ? 16 * ((2 * d.nof_re) / 16) : 4 * (d.nof_re / 4);    /* values (QPSK) / symbols */
-  const float cmax = d.csi ? csi_max[blockIdx.y] : 1.0f;
-  const float cscale = __fdiv_rn(32767.0f, cmax);
 
   for (uint32_t pr = threadIdx.x; 2 * pr < nsym; pr += FE_THREADS) {
     const uint32_t ls = 2 * pr, s = s0 + ls;                 /* first symbol of the pair (s0 is even) */
@@ -248,39 +247,7 @@ __device__ __forceinline__ void fe_tile(const FecFeDesc &d, uint32_t s0, const f
         const uint32_t b = (ls + h) * mod + k;
         if ((cw[b >> 5] >> (b & 31)) & 1) v[6 * h + k] = fe_wrap16(-v[6 * h + k]);
       }
-    if (!ul) {
-      if (d.csi) {
-        /* csi_correction: SSE body over whole groups (QPSK / 64QAM: symbol pairs, 16QAM: symbols), scalar tail */
-        const uint32_t nb = d.nof_re * mod;
-        if (mod == 6 || mod == 2) {
-          if (two && (s + 2) * mod <= nb) {
-            const int w1 = fe_sat16_rn(__fmul_rn(d.csi[s], cscale)), w3 = fe_sat16_rn(__fmul_rn(d.csi[s + 1], cscale));
-            if (mod == 6) {
-              for (int k = 0; k < 4; k++) v[k] = fe_mulhi16(v[k], w1);
-              v[4] = fe_mulhi16(v[4], w3); v[5] = fe_mulhi16(v[5], w3);
-              v[6] = fe_mulhi16(v[6], w1); v[7] = fe_mulhi16(v[7], w1);
-              for (int k = 2; k < 6; k++) v[6 + k] = fe_mulhi16(v[6 + k], w3);
-            } else {
-              v[0] = fe_mulhi16(v[0], w3); v[1] = fe_mulhi16(v[1], w3);
-              v[6] = fe_mulhi16(v[6], w1); v[7] = fe_mulhi16(v[7], w1);
-            }
-          } else {
-            const float w = __fdiv_rn(d.csi[s], cmax);
-            _Pragma("unroll") for (uint32_t k = 0; k < mod; k++) v[k] = fe_c16((double)__fmul_rn((float)v[k], w));
-          }
-        } else if (mod == 4) {
-#pragma unroll
-          for (int h = 0; h < 2; h++) {
-            if (h && !two) break;
-            const int w = fe_sat16_rn(__fmul_rn(d.csi[s + h], cscale));
-            for (int k = 0; k < 4; k++) v[6 * h + k] = fe_mulhi16(v[6 * h + k], w);
-          }
-        }
-      }
-#pragma unroll
-      for (int h = 0; h < 2; h++)
-        if (!(h && !two)) _Pragma("unroll") for (uint32_t k = 0; k < mod; k++) tile[(ls + h) * mod + k] = (int16_t)v[6 * h + k];
-    } else {
+    {
 #pragma unroll
       for (int h = 0; h < 2; h++) {
         if (h && !two) break;
@@ -303,29 +270,161 @@ __device__ __forceinline__ void fe_tile(const FecFeDesc &d, uint32_t s0, const f
       }
     }
   }
-  if (!ul) {
-    __syncthreads();
-    /* tile -> HBM: p0*2 bytes is a multiple of 16 (p0 = 2048*mod*blockIdx.x) */
-    int16_t *dst = d.e + p0;
-    const uint32_t n16 = nbits / 8;
-    for (uint32_t i = threadIdx.x; i < n16; i += FE_THREADS) reinterpret_cast<uint4 *>(dst)[i] = reinterpret_cast<const uint4 *>(tile)[i];
-    for (uint32_t i = n16 * 8 + threadIdx.x; i < nbits; i += FE_THREADS) dst[i] = tile[i];
+}
+
+/* ---- DL tile: registers -> packed words -> shared-memory tile -> 16-byte stores ---- */
+template <int MOD, bool CSI>
+__device__ __forceinline__ void fe_tile_dl(const FecFeDesc &d, uint32_t s0, float cmax, const uint32_t *x2_masks,
+                                           const uint32_t *x1_states, const FeConst &kc, uint32_t *cw, uint32_t *tile)
+{
+  constexpr uint32_t mod = MOD;
+  constexpr int NP = FE_SEG / 2 / FE_THREADS;                /* symbol pairs per thread */
+  const uint32_t nsym = min((uint32_t)FE_SEG, d.nof_re - s0);
+  const uint32_t nbits = nsym * mod, p0 = s0 * mod;
+  const uint32_t body_end = (mod == 2) ? 16 * ((2 * d.nof_re) / 16) : 4 * (d.nof_re / 4);
+
+  /* symbols (and weights) of all pairs of this thread first: their HBM latency hides behind the sequence generation */
+  float4 q[NP];
+  float cs[NP][2];
+#pragma unroll
+  for (int r = 0; r < NP; r++) {
+    const uint32_t ls = 2 * (threadIdx.x + r * FE_THREADS);
+    q[r] = make_float4(0.f, 0.f, 0.f, 0.f);
+    cs[r][0] = cs[r][1] = 0.f;
+    if (ls + 1 < nsym) q[r] = *reinterpret_cast<const float4 *>(d.sym + s0 + ls);
+    else if (ls < nsym) { const float2 t = d.sym[s0 + ls]; q[r].x = t.x; q[r].y = t.y; }
+    if (CSI) {
+      if (ls < nsym) cs[r][0] = d.csi[s0 + ls];
+      if (ls + 1 < nsym) cs[r][1] = d.csi[s0 + ls + 1];
+    }
+  }
+  {
+    const uint32_t nblk = (nbits + FE_BLK_BITS - 1) / FE_BLK_BITS;
+    if (threadIdx.x < nblk) {
+      uint32_t s1, s2;
+      fe_block_states(x2_masks, x1_states, p0 / FE_BLK_BITS + threadIdx.x, d.c_init, s1, s2);
+#pragma unroll
+      for (int w = 0; w < FE_BLK_BITS / 32; w++) cw[threadIdx.x * (FE_BLK_BITS / 32) + w] = fe_x1_next32(s1) ^ fe_x2_next32(s2);
+    }
+    if (threadIdx.x == 0) cw[nblk * (FE_BLK_BITS / 32)] = 0;
+  }
+  __syncthreads();
+  const float cscale = CSI ? __fdiv_rn(32767.0f, cmax) : 0.f;
+
+#pragma unroll
+  for (int r = 0; r < NP; r++) {
+    const uint32_t pr = threadIdx.x + r * FE_THREADS, ls = 2 * pr, s = s0 + ls;
+    if (ls >= nsym) break;
+    const bool two = ls + 1 < nsym;
+    int v[12];
+#pragma unroll
+    for (int k = 0; k < 12; k++) v[k] = 0;
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      const uint32_t sh = s + h;
+      const bool body = mod == 2 ? 2 * sh < body_end : sh < body_end;
+      const bool body_im = mod == 2 ? 2 * sh + 1 < body_end : body;
+      fe_demod<MOD>(h ? q[r].z : q[r].x, h ? q[r].w : q[r].y, body, body_im, kc, v + 6 * h);
+    }
+    /* descrambling: the 2*mod sequence bits of the pair sit at bit ls*mod of the tile's sequence words */
+    const uint32_t b0 = ls * mod;
+    const uint32_t bits = __funnelshift_r(cw[b0 >> 5], cw[(b0 >> 5) + 1], b0 & 31);
+#pragma unroll
+    for (int h = 0; h < 2; h++)
+#pragma unroll
+      for (uint32_t k = 0; k < mod; k++)
+        if ((bits >> (h * mod + k)) & 1) v[6 * h + k] = CSI ? fe_wrap16(-v[6 * h + k]) : -v[6 * h + k];
+    if (CSI) {
+      /* csi_correction: SSE body over whole groups (QPSK / 64QAM: symbol pairs, 16QAM: symbols), scalar tail */
+      if (mod == 6 || mod == 2) {
+        if (two) {
+          const int w1 = fe_sat16_rn(__fmul_rn(cs[r][0], cscale)), w3 = fe_sat16_rn(__fmul_rn(cs[r][1], cscale));
+          if (mod == 6) {
+#pragma unroll
+            for (int k = 0; k < 4; k++) v[k] = fe_mulhi16(v[k], w1);
+            v[4] = fe_mulhi16(v[4], w3); v[5] = fe_mulhi16(v[5], w3);
+            v[6] = fe_mulhi16(v[6], w1); v[7] = fe_mulhi16(v[7], w1);
+#pragma unroll
+            for (int k = 2; k < 6; k++) v[6 + k] = fe_mulhi16(v[6 + k], w3);
+          } else {
+            v[0] = fe_mulhi16(v[0], w3); v[1] = fe_mulhi16(v[1], w3);
+            v[6] = fe_mulhi16(v[6], w1); v[7] = fe_mulhi16(v[7], w1);
+          }
+        } else {
+          const float w = __fdiv_rn(cs[r][0], cmax);
+#pragma unroll
+          for (uint32_t k = 0; k < mod; k++) v[k] = fe_c16((double)__fmul_rn((float)v[k], w));
+        }
+      } else if (mod == 4) {
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          const int w = fe_sat16_rn(__fmul_rn(cs[r][h], cscale));
+#pragma unroll
+          for (int k = 0; k < 4; k++) v[6 * h + k] = fe_mulhi16(v[6 * h + k], w);
+        }
+      }
+    }
+    /* 2*mod int16 = mod words (mod 1: one word, upper half unused by a lone symbol) */
+    if (mod == 1) {
+      tile[pr] = __byte_perm(v[0], v[6], 0x5410);
+    } else {
+      uint32_t w[MOD];
+#pragma unroll
+      for (uint32_t k = 0; k < mod / 2; k++) {
+        w[k] = __byte_perm(v[2 * k], v[2 * k + 1], 0x5410);
+        w[mod / 2 + k] = __byte_perm(v[6 + 2 * k], v[6 + 2 * k + 1], 0x5410);
+      }
+      if (mod == 2) { *reinterpret_cast<uint2 *>(tile + 2 * pr) = make_uint2(w[0], w[1]); }
+      else {
+#pragma unroll
+        for (uint32_t k = 0; k < mod / 2; k++) *reinterpret_cast<uint2 *>(tile + mod * pr + 2 * k) = make_uint2(w[2 * k], w[2 * k + 1]);
+      }
+    }
+  }
+  __syncthreads();
+  /* tile -> HBM: p0*2 bytes is a multiple of 16 (p0 = 2048*mod*blockIdx.x) */
+  int16_t *dst = d.e + p0;
+  const uint32_t n16 = nbits / 8;
+  for (uint32_t i = threadIdx.x; i < n16; i += FE_THREADS) reinterpret_cast<uint4 *>(dst)[i] = reinterpret_cast<const uint4 *>(tile)[i];
+  for (uint32_t i = n16 * 8 + threadIdx.x; i < nbits; i += FE_THREADS) dst[i] = reinterpret_cast<const int16_t *>(tile)[i];
+}
+
+__global__ void __launch_bounds__(FE_THREADS, 4)
+fec_fe_dl_kernel(const FecFeDesc *descs, const float *csi_max, const uint32_t *x2_masks, const uint32_t *x1_states, FeConst kc)
+{
+  const FecFeDesc d = descs[blockIdx.y];
+  const uint32_t s0 = blockIdx.x * FE_SEG;
+  if (d.cols || s0 >= d.nof_re) return;
+  __shared__ uint32_t cw[FE_SEG * 6 / 32 + 1];
+  __shared__ __align__(16) uint32_t tile[FE_SEG * 6 / 2];
+  if (d.csi) {
+    const float cmax = csi_max[blockIdx.y];
+    switch (d.mod) {
+    case 6: fe_tile_dl<6, true>(d, s0, cmax, x2_masks, x1_states, kc, cw, tile); break;
+    case 4: fe_tile_dl<4, true>(d, s0, cmax, x2_masks, x1_states, kc, cw, tile); break;
+    default: fe_tile_dl<2, true>(d, s0, cmax, x2_masks, x1_states, kc, cw, tile); break;
+    }
+  } else {
+    switch (d.mod) {
+    case 6: fe_tile_dl<6, false>(d, s0, 1.f, x2_masks, x1_states, kc, cw, tile); break;
+    case 4: fe_tile_dl<4, false>(d, s0, 1.f, x2_masks, x1_states, kc, cw, tile); break;
+    case 2: fe_tile_dl<2, false>(d, s0, 1.f, x2_masks, x1_states, kc, cw, tile); break;
+    default: fe_tile_dl<1, false>(d, s0, 1.f, x2_masks, x1_states, kc, cw, tile); break;
+    }
   }
 }
 
 __global__ void __launch_bounds__(FE_THREADS)
-fec_fe_kernel(const FecFeDesc *descs, const float *csi_max, const uint32_t *x2_masks, const uint32_t *x1_states, FeConst kc)
+fec_fe_ul_kernel(const FecFeDesc *descs, const uint32_t *x2_masks, const uint32_t *x1_states, FeConst kc)
 {
   const FecFeDesc d = descs[blockIdx.y];
   const uint32_t s0 = blockIdx.x * FE_SEG;
-  if (s0 >= d.nof_re) return;
+  if (!d.cols || s0 >= d.nof_re) return;
   __shared__ uint32_t cw[FE_SEG * 6 / 32];
-  __shared__ __align__(16) int16_t tile[FE_SEG * 6];
   switch (d.mod) {
-  case 6: fe_tile<6>(d, s0, csi_max, x2_masks, x1_states, kc, cw, tile); break;
-  case 4: fe_tile<4>(d, s0, csi_max, x2_masks, x1_states, kc, cw, tile); break;
-  case 2: fe_tile<2>(d, s0, csi_max, x2_masks, x1_states, kc, cw, tile); break;
-  default: fe_tile<1>(d, s0, csi_max, x2_masks, x1_states, kc, cw, tile); break;
+  case 6: fe_tile_ul<6>(d, s0, x2_masks, x1_states, kc, cw); break;
+  case 4: fe_tile_ul<4>(d, s0, x2_masks, x1_states, kc, cw); break;
+  default: fe_tile_ul<2>(d, s0, x2_masks, x1_states, kc, cw); break;
   }
 }
 
@@ -356,7 +455,7 @@ __global__ void __launch_bounds__(FE_THREADS) fec_fe_uci_kernel(const FecFeDesc 
 }
 
 cudaError_t fec_launch_frontend(const FecFeDesc *descs, float *csi_max, const uint32_t *x2_masks, const uint32_t *x1_states,
-                                uint32_t ntb, uint32_t max_re, int any_csi, int any_uci, cudaStream_t st)
+                                uint32_t ntb, uint32_t max_re, int any_csi, int any_uci, int kinds, cudaStream_t st)
 {
   if (!ntb || !max_re) return cudaSuccess;
   FeConst kc;
@@ -366,7 +465,8 @@ cudaError_t fec_launch_frontend(const FecFeDesc *descs, float *csi_max, const ui
   kc.ioff16 = (short)kc.off16; kc.ioff64a = (short)kc.off64a; kc.ioff64b = (short)kc.off64b;
   if (any_csi) fec_fe_csimax_kernel<<<ntb, FE_THREADS, 0, st>>>(descs, csi_max);
   dim3 grid((max_re + FE_SEG - 1) / FE_SEG, ntb);
-  fec_fe_kernel<<<grid, FE_THREADS, 0, st>>>(descs, csi_max, x2_masks, x1_states, kc);
+  if (kinds & 1) fec_fe_dl_kernel<<<grid, FE_THREADS, 0, st>>>(descs, csi_max, x2_masks, x1_states, kc);
+  if (kinds & 2) fec_fe_ul_kernel<<<grid, FE_THREADS, 0, st>>>(descs, x2_masks, x1_states, kc);
   if (any_uci) fec_fe_uci_kernel<<<ntb, FE_THREADS, 0, st>>>(descs, kc);
   return cudaGetLastError();
 }

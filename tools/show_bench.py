@@ -5,3 +5,11 @@ print("value %.2f Gbps  step %.3f ms | serial phases rm %.3f dec %.3f asm %.3f |
     j["value"], j["ms_per_step"], r["phases_ms"]["rate_dematch"], r["phases_ms"]["turbo_decode"], r["phases_ms"]["tb_assemble_crc24a"],
     r["frac"], j["e2e"]["value"], j["e2e"]["ms_per_step"],
     ("%.2f Gbps %.2f ms" % (j["worst_case_8_halfits"]["gbps"], j["worst_case_8_halfits"]["ms_per_step"])) if j.get("worst_case_8_halfits") else "-"))
+f = j.get("frontend_symbols")
+if f:
+    k = f["frontend_kernel"]
+    print("symbols: value %.2f Gbps step %.3f ms ok %.2f its %.2f | e2e %.2f Gbps (%.2f ms) | fe kernel %.3f ms %.0f GB/s (%.2f of HBM)" % (
+        f["value"], f["ms_per_step"], f["tb_ok_frac"], f["halfits_per_cb"], f["e2e"]["value"], f["e2e"]["ms_per_step"],
+        k["ms_per_launch"], k["achieved"], k["frac"]))
+    if "serial_phases_ms" in f:
+        print("symbols serial phases:", {k: round(v, 3) for k, v in f["serial_phases_ms"].items()})
