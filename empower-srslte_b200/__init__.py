@@ -87,6 +87,7 @@ def load():
         lib.fec_cuda_rm_rx.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p]
         lib.fec_cuda_cbsegm.argtypes = [C.c_uint32, C.POINTER(C.c_uint32)]
         lib.fec_cuda_last_phase_ms.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
+        lib.fec_cuda_last_path_counts.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
         lib.fec_cuda_decode_syms.argtypes = [C.c_void_p, C.POINTER(TbDesc), C.POINTER(SymDesc), C.c_uint32, C.c_uint32]
         lib.fec_cuda_submit_syms.argtypes = [C.c_void_p, C.POINTER(TbDesc), C.POINTER(SymDesc), C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64)]
         lib.fec_cuda_last_frontend_ms.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
@@ -165,6 +166,14 @@ class FecCuda:
         if rc:
             raise RuntimeError(f"fec_cuda_last_phase_ms: {rc}")
         return [float(v) for v in o]
+
+    def last_path_counts(self):
+        """code blocks of the last decode call handed (to the certificate variant of the packed kernel, on to the exact kernel)"""
+        o = (C.c_uint64 * 2)()
+        rc = self.lib.fec_cuda_last_path_counts(self.h, o)
+        if rc:
+            raise RuntimeError(f"fec_cuda_last_path_counts: {rc}")
+        return int(o[0]), int(o[1])
 
     def error(self):
         return self.lib.fec_cuda_last_error(self.h).decode()

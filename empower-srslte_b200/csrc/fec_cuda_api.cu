@@ -51,7 +51,8 @@ struct fec_cuda_ctx {
   stage_t       st_e, st_data, st_cbd, st_rmd, st_tbd, st_status, st_ret, st_exd;
   uint8_t      *d_cbbytes; size_t cbbytes_cap;
   int16_t      *d_tmpsoft; size_t tmpsoft_cap;
-  unsigned int *d_queue;   /* per K: work-queue counters of the packed and the exact kernel (2 x FEC_NOF_K), then FEC_NOF_K hand-over counts */
+  unsigned int *d_queue;   /* per K: work-queue counters of the packed and the exact kernel (2 x FEC_NOF_K), FEC_NOF_K hand-over counts to the
+                              exact kernel, then work-queue counters and hand-over counts of the certificate kernel (FEC_NQUEUE x FEC_NOF_K) */
   uint32_t     *d_softmax; size_t softmax_cap;   /* per code block of the call: max |soft-buffer entry| */
   uint32_t     *d_exact;   size_t exact_cap;     /* per code block of the call: hand-over list of the packed kernel */
   int           force_exact;
@@ -68,6 +69,8 @@ struct fec_cuda_ctx {
   int           trace;          /* FEC_CUDA_TRACE=1: print the device timeline of every sub-batch to stderr */
   uint32_t     *d_x2masks, *d_x1states;   /* front end: scrambling-sequence jump tables (fec_frontend.cu) */
   float         fe_ms;          /* device time of the front-end kernels of the last call */
+  uint64_t      path_cnt[2];    /* last call: code blocks handed to the certificate kernel / to the exact kernel */
+  unsigned int *h_queue;        /* pinned mirror of d_queue (fec_cuda_decode_cbs) */
   cudaEvent_t   ev_call;        /* start of the current decode_tbs call (copy stream) */
   double        t_call;         /* host clock at the start of the call */
 };
@@ -144,7 +147,8 @@ extern "C" int fec_cuda_create(fec_cuda_ctx_t **out, int device, uint32_t max_tb
   fec_gen_crc_powers(0x1800063u, R, FEC_MAX_K);
   cudaMemcpy(ctx->d_r24b, R, sizeof(uint32_t) * FEC_MAX_K, cudaMemcpyHostToDevice);
   free(R);
-  cudaMalloc(&ctx->d_queue, sizeof(unsigned int) * 3 * FEC_NOF_K);
+  cudaMalloc(&ctx->d_queue, sizeof(unsigned int) * FEC_NQUEUE * FEC_NOF_K);
+  cudaMallocHost(&ctx->h_queue, sizeof(unsigned int) * FEC_NQUEUE * FEC_NOF_K);
   {
     uint32_t *m = (uint32_t *)malloc(sizeof(uint32_t) * FEC_FE_NBLK * 33);
     fec_gen_gold_tables(m, m + FEC_FE_NBLK * 32);
@@ -170,7 +174,7 @@ extern "C" void fec_cuda_destroy(fec_cuda_ctx_t *ctx)
     cudaFree(ctx->ktab[i].d_step); cudaFree(ctx->ktab[i].d_rank); cudaFree(ctx->ktab[i].d_pair_addr);
     cudaFree(ctx->ktab[i].d_pair_crc[0]); cudaFree(ctx->ktab[i].d_pair_crc[1]);
   }
-  cudaFree(ctx->d_softmax); cudaFree(ctx->d_exact);
+  cudaFree(ctx->d_softmax); cudaFree(ctx->d_exact); cudaFreeHost(ctx->h_queue);
   for (uint32_t i = 0; i < ctx->nchunks; i++) { cudaFree(ctx->chunks[i].d_soft); cudaFree(ctx->chunks[i].d_cache); free(ctx->chunks[i].cb_crc); }
   free(ctx->chunks);
   stage_free(&ctx->st_e); stage_free(&ctx->st_data); stage_free(&ctx->st_cbd); stage_free(&ctx->st_rmd);
@@ -194,6 +198,18 @@ extern "C" void *fec_cuda_host_alloc(size_t bytes)
   return p;
 }
 extern "C" void fec_cuda_host_free(void *p) { if (p) cudaFreeHost(p); }
+
+static void path_count_add(fec_cuda_ctx_t *ctx, const unsigned int *q)
+{
+  for (int k = 0; k < FEC_NOF_K; k++) { ctx->path_cnt[0] += q[4 * FEC_NOF_K + k]; ctx->path_cnt[1] += q[2 * FEC_NOF_K + k]; }
+}
+
+extern "C" int fec_cuda_last_path_counts(fec_cuda_ctx_t *ctx, uint64_t out2[2])
+{
+  if (!ctx || !out2) return FEC_CUDA_EINVAL;
+  out2[0] = ctx->path_cnt[0]; out2[1] = ctx->path_cnt[1];
+  return 0;
+}
 
 extern "C" int fec_cuda_last_phase_ms(fec_cuda_ctx_t *ctx, float out3[3])
 {
@@ -300,7 +316,7 @@ extern "C" int fec_cuda_softbuffer_read_ref_layout(fec_cuda_ctx_t *ctx, uint32_t
 }
 
 static void fill_decode_args(fec_cuda_ctx_t *ctx, int k, FecDecodeArgs *a, const FecCbDesc *cbd_dev, FecCbStatus *status_dev,
-                             unsigned int *queue3, const uint32_t *softmax, uint32_t *exact, uint32_t off, uint32_t cnt, int16_t *dbg)
+                             unsigned int *queue3, const uint32_t *softmax, uint32_t *exact, uint32_t *trk, uint32_t off, uint32_t cnt, int16_t *dbg)
 {
   const ktab_t *t = &ctx->ktab[k];
   memset(a, 0, sizeof(*a));
@@ -309,7 +325,10 @@ static void fill_decode_args(fec_cuda_ctx_t *ctx, int k, FecDecodeArgs *a, const
   a->queue = queue3 + 2 * k; a->ncb = cnt; a->slots = t->slots; a->dbg_llr = dbg;
   a->pair_addr = t->d_pair_addr; a->pair_crc[0] = t->d_pair_crc[0]; a->pair_crc[1] = t->d_pair_crc[1];
   a->soft_max = softmax; a->status_off = off;
-  if (t->g.P && !ctx->force_exact && !dbg) { a->exact_list = exact + off; a->exact_count = queue3 + 2 * FEC_NOF_K + k; }
+  if (t->g.P && !ctx->force_exact && !dbg) {
+    a->exact_list = exact + off; a->exact_count = queue3 + 2 * FEC_NOF_K + k;
+    a->trk_list = trk + off; a->trk_queue = queue3 + 3 * FEC_NOF_K + k; a->trk_count = queue3 + 4 * FEC_NOF_K + k;
+  }
 }
 
 /* ---------------------------------------------------------------- batched transport-block decode ---- */
@@ -333,7 +352,7 @@ struct fec_pipe {
   uint8_t      *d_cbbytes; size_t cbbytes_cap;
   uint32_t     *d_softmax; size_t softmax_cap;
   uint32_t     *d_exact;   size_t exact_cap;
-  unsigned int *d_queue;
+  unsigned int *d_queue, *h_queue;
   cudaEvent_t   ev_in, ev_k, ev_done, ev[4];
   tbplan_t     *plan; size_t plan_cap;
   fec_cuda_tb_t *tbs; uint32_t n, ncb, ntb; int dev_io, busy;
@@ -345,7 +364,8 @@ struct fec_pipe {
 static int pipe_init(fec_cuda_ctx_t *ctx, fec_pipe_t *p)
 {
   memset(p, 0, sizeof(*p));
-  CU(cudaMalloc(&p->d_queue, sizeof(unsigned int) * 3 * FEC_NOF_K));
+  CU(cudaMalloc(&p->d_queue, sizeof(unsigned int) * FEC_NQUEUE * FEC_NOF_K));
+  CU(cudaMallocHost(&p->h_queue, sizeof(unsigned int) * FEC_NQUEUE * FEC_NOF_K));
   CU(cudaEventCreate(&p->ev_in));
   CU(cudaEventCreateWithFlags(&p->ev_k, cudaEventDisableTiming));
   CU(cudaEventCreate(&p->ev_done));
@@ -361,7 +381,7 @@ static void pipe_free(fec_pipe_t *p)
   stage_free(&p->st_fed); stage_free(&p->st_lst); stage_free(&p->st_uci);
   cudaFree(p->d_llr); cudaFree(p->d_csimax);
   if (p->ev_fe) cudaEventDestroy(p->ev_fe);
-  cudaFree(p->d_cbbytes); cudaFree(p->d_softmax); cudaFree(p->d_exact); cudaFree(p->d_queue);
+  cudaFree(p->d_cbbytes); cudaFree(p->d_softmax); cudaFree(p->d_exact); cudaFree(p->d_queue); cudaFreeHost(p->h_queue);
   if (p->ev_in) { cudaEventDestroy(p->ev_in); cudaEventDestroy(p->ev_k); cudaEventDestroy(p->ev_done); for (int i = 0; i < 4; i++) cudaEventDestroy(p->ev[i]); }
   free(p->plan);
   memset(p, 0, sizeof(*p));
@@ -492,7 +512,7 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
       stage_reserve(ctx, &pp->st_ret, need[4]) ||
       dev_reserve(ctx, (void **)&pp->d_cbbytes, &pp->cbbytes_cap, need[5]) ||
       dev_reserve(ctx, (void **)&pp->d_softmax, &pp->softmax_cap, need[6]) ||
-      dev_reserve(ctx, (void **)&pp->d_exact, &pp->exact_cap, need[6]) ||
+      dev_reserve(ctx, (void **)&pp->d_exact, &pp->exact_cap, 2 * need[6]) ||
       (!dev_io && (stage_reserve(ctx, &pp->st_e, need[7]) || stage_reserve(ctx, &pp->st_data, need[8])))) return FEC_CUDA_ENODEV;
   if (syms && (stage_reserve(ctx, &pp->st_fed, need[9]) || dev_reserve(ctx, (void **)&pp->d_llr, &pp->llr_cap, need[10]) ||
                stage_reserve(ctx, &pp->st_lst, need[11]) || stage_reserve(ctx, &pp->st_uci, need[12]) ||
@@ -639,7 +659,7 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
   /* rate de-matching has its own stream: it depends on nothing but its inputs, so it must not queue up behind the
    * decode kernel of an earlier sub-batch (which can hold a compute stream for the length of its slowest code block) */
   cudaStream_t srm = (flags & FEC_CUDA_F_SERIAL) ? sc : ctx->s_rm;
-  CU(cudaMemsetAsync(pp->d_queue, 0, sizeof(unsigned int) * 3 * FEC_NOF_K, srm));
+  CU(cudaMemsetAsync(pp->d_queue, 0, sizeof(unsigned int) * FEC_NQUEUE * FEC_NOF_K, srm));
   if (ncb) CU(cudaMemsetAsync(pp->d_softmax, 0, (size_t)ncb * 4, srm));
   CU(cudaStreamWaitEvent(srm, pp->ev_in, 0));
   CU(cudaEventRecord(pp->ev_fe, srm));
@@ -655,10 +675,10 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
   for (int k = 0; k < FEC_NOF_K; k++) {
     if (!grp_cnt[k]) continue;
     FecDecodeArgs a;
-    fill_decode_args(ctx, k, &a, (const FecCbDesc *)pp->st_cbd.d, (FecCbStatus *)pp->st_status.d, pp->d_queue, pp->d_softmax, pp->d_exact,
+    fill_decode_args(ctx, k, &a, (const FecCbDesc *)pp->st_cbd.d, (FecCbStatus *)pp->st_status.d, pp->d_queue, pp->d_softmax, pp->d_exact, pp->d_exact + pp->exact_cap / 8,
                      grp_off[k], grp_cnt[k], NULL);
     CU(fec_launch_decode(a, ctx->sm_count, sc));
-    ctx->launches += a.exact_list ? 2 : 1;
+    ctx->launches += a.exact_list ? 3 : 1;
   }
   CU(cudaEventRecord(pp->ev[2], sc));
   if (ntb) { CU(fec_launch_tb_assemble((const FecTbDesc *)pp->st_tbd.d, (const FecCbStatus *)pp->st_status.d, ctx->d_r24a, ntb, sc)); ctx->launches++; }
@@ -669,6 +689,7 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
   CU(cudaStreamWaitEvent(sout, pp->ev_k, 0));
   if (ncb) CU(cudaMemcpyAsync(pp->st_status.h, pp->st_status.d, sizeof(FecCbStatus) * ncb, cudaMemcpyDeviceToHost, sout));
   if (ntb) CU(cudaMemcpyAsync(pp->st_ret.h, pp->st_ret.d, sizeof(int32_t) * ntb, cudaMemcpyDeviceToHost, sout));
+  if (ncb) CU(cudaMemcpyAsync(pp->h_queue, pp->d_queue, sizeof(unsigned int) * FEC_NQUEUE * FEC_NOF_K, cudaMemcpyDeviceToHost, sout));
   if (!dev_io && data_total) CU(cudaMemcpyAsync(pp->st_data.h, pp->st_data.d, data_total, cudaMemcpyDeviceToHost, sout));
   if (!dev_io && syms && uci_total) CU(cudaMemcpyAsync(pp->st_uci.h, pp->st_uci.d, uci_total * 2, cudaMemcpyDeviceToHost, sout));
   CU(cudaEventRecord(pp->ev_done, sout));
@@ -686,6 +707,7 @@ static int pipe_finish(fec_cuda_ctx_t *ctx, fec_pipe_t *pp)
   CU(cudaEventSynchronize(pp->ev_done));
   for (int i = 0; i < 3; i++) { float ms = 0; if (cudaEventElapsedTime(&ms, pp->ev[i], pp->ev[i + 1]) == cudaSuccess) ctx->phase_ms[i] += ms; }
   { float ms = 0; if (cudaEventElapsedTime(&ms, pp->ev_fe, pp->ev[0]) == cudaSuccess) ctx->fe_ms += ms; }
+  if (pp->ncb) path_count_add(ctx, pp->h_queue);
   if (pp->syms && !pp->dev_io)
     for (uint32_t i = 0; i < pp->n; i++) {
       const tbplan_t *p = &pp->plan[i];
@@ -768,6 +790,7 @@ static int submit_common(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, const fec_cuda
   if (n == 0) return 0;
   cudaSetDevice(ctx->device);
   ctx->phase_ms[0] = ctx->phase_ms[1] = ctx->phase_ms[2] = 0; ctx->fe_ms = 0; ctx->ev_valid = 1;
+  ctx->path_cnt[0] = ctx->path_cnt[1] = 0;
   ctx->t_call = now_ms();
   if (ctx->trace) CU(cudaEventRecord(ctx->ev_call, ctx->s_copy));
   /* host buffers: small sub-batches so that the PCIe copy of one overlaps the kernels of the previous (the copy is
@@ -862,7 +885,7 @@ extern "C" int fec_cuda_decode_cbs(fec_cuda_ctx_t *ctx, fec_cuda_cb_t *cbs, uint
       stage_reserve(ctx, &ctx->st_exd, sizeof(FecExtractDesc) * n) || stage_reserve(ctx, &ctx->st_status, sizeof(FecCbStatus) * n) ||
       stage_reserve(ctx, &ctx->st_data, (size_t)n * CB_BYTES) ||
       dev_reserve(ctx, (void **)&ctx->d_softmax, &ctx->softmax_cap, (size_t)(n + 1) * 4) ||
-      dev_reserve(ctx, (void **)&ctx->d_exact, &ctx->exact_cap, (size_t)(n + 1) * 4) ||
+      dev_reserve(ctx, (void **)&ctx->d_exact, &ctx->exact_cap, (size_t)(n + 1) * 8) ||
       dev_reserve(ctx, (void **)&ctx->d_tmpsoft, &ctx->tmpsoft_cap, (size_t)n * FEC_CUDA_SOFT_SLOT * sizeof(int16_t))) return FEC_CUDA_ENODEV;
   if (ctx->dbg_cap && ctx->dbg_cap < (size_t)n * FEC_MAX_K * 2) { cudaFree(ctx->d_dbg); ctx->d_dbg = NULL; ctx->dbg_cap = 0; }
   FecCbDesc *cbd = (FecCbDesc *)ctx->st_cbd.h;
@@ -887,7 +910,7 @@ extern "C" int fec_cuda_decode_cbs(fec_cuda_ctx_t *ctx, fec_cuda_cb_t *cbs, uint
   CUF(cudaMemcpyAsync(ctx->st_e.d, ctx->st_e.h, llr_total * 2, cudaMemcpyHostToDevice, st));
   CUF(cudaMemcpyAsync(ctx->st_cbd.d, cbd, sizeof(FecCbDesc) * n, cudaMemcpyHostToDevice, st));
   CUF(cudaMemcpyAsync(ctx->st_exd.d, exd, sizeof(FecExtractDesc) * n, cudaMemcpyHostToDevice, st));
-  CUF(cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned int) * 3 * FEC_NOF_K, st));
+  CUF(cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned int) * FEC_NQUEUE * FEC_NOF_K, st));
   CUF(cudaMemsetAsync(ctx->d_softmax, 0, (size_t)n * 4, st));
   for (uint32_t o = 0; o < n; o += 32768) {
     CUF(fec_launch_extract((const FecExtractDesc *)ctx->st_exd.d + o, ctx->d_softmax, n - o < 32768 ? n - o : 32768, st));
@@ -896,14 +919,17 @@ extern "C" int fec_cuda_decode_cbs(fec_cuda_ctx_t *ctx, fec_cuda_cb_t *cbs, uint
   for (int k = 0; k < FEC_NOF_K; k++) {
     if (!grp_cnt[k]) continue;
     FecDecodeArgs a;
-    fill_decode_args(ctx, k, &a, (const FecCbDesc *)ctx->st_cbd.d, (FecCbStatus *)ctx->st_status.d, ctx->d_queue, ctx->d_softmax, ctx->d_exact,
+    fill_decode_args(ctx, k, &a, (const FecCbDesc *)ctx->st_cbd.d, (FecCbStatus *)ctx->st_status.d, ctx->d_queue, ctx->d_softmax, ctx->d_exact, ctx->d_exact + ctx->exact_cap / 8,
                      grp_off[k], grp_cnt[k], DBG_LLR);
     CUF(fec_launch_decode(a, ctx->sm_count, st));
-    ctx->launches += a.exact_list ? 2 : 1;
+    ctx->launches += a.exact_list ? 3 : 1;
   }
   CUF(cudaMemcpyAsync(ctx->st_status.h, ctx->st_status.d, sizeof(FecCbStatus) * n, cudaMemcpyDeviceToHost, st));
   CUF(cudaMemcpyAsync(ctx->st_data.h, ctx->st_data.d, (size_t)n * CB_BYTES, cudaMemcpyDeviceToHost, st));
+  CUF(cudaMemcpyAsync(ctx->h_queue, ctx->d_queue, sizeof(unsigned int) * FEC_NQUEUE * FEC_NOF_K, cudaMemcpyDeviceToHost, st));
   CUF(cudaStreamSynchronize(st));
+  ctx->path_cnt[0] = ctx->path_cnt[1] = 0;
+  path_count_add(ctx, ctx->h_queue);
   for (uint32_t i = 0; i < n; i++) {
     const FecCbStatus *s = (const FecCbStatus *)ctx->st_status.h + slot_of[i];
     cbs[i].its = s->its; cbs[i].crc_ok = s->crc_ok;

@@ -12,7 +12,9 @@
 #define FEC_WIN_CHUNK     16      /* beta checkpoint spacing S (trellis steps) */
 #define FEC_F_NO_EARLY    1u
 #define FEC_PK_WARPS      4       /* packed kernel: warps per CTA (= tensor-memory lane quarters) */
-#define FEC_PK_GMAX       2000u   /* packed kernel: largest max|x| + max|y| for which int16 saturation is excluded */
+#define FEC_PK_GMAX       2000u   /* packed kernel: largest max|x| + max|y| for which int16 saturation is excluded a priori */
+#define FEC_NQUEUE        5       /* device counters per K: packed queue, exact queue, exact count, certificate queue, certificate count */
+#define FEC_PK_GMAX_TRK   4500u   /* ... and the largest for which the run-time range certificate can still hold (10000 + 5G <= 32767) */
 
 /* one code block of a decode launch */
 struct FecCbDesc {
@@ -44,6 +46,9 @@ struct FecDecodeArgs {
   const uint32_t   *soft_max;   /* per status slot: max |soft-buffer entry| of the code block (rate de-matching / extract kernel) */
   uint32_t         *exact_list; /* out: code blocks (indices into cbs) outside the proven range -> exact kernel */
   unsigned int     *exact_count;
+  uint32_t         *trk_list;   /* out: code blocks beyond the a-priori range -> certificate variant of the packed kernel */
+  unsigned int     *trk_count;
+  unsigned int     *trk_queue;  /* work-queue counter of the certificate kernel */
   /* exact kernels: optional indirect work list (NULL = all ncb code blocks) */
   const uint32_t   *list;
   const unsigned int *list_count;

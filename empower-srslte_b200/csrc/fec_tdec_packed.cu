@@ -118,6 +118,32 @@ __device__ __forceinline__ void pk_norm(uint32_t *o)
   o[0] = 0;
 }
 
+/* ---- run-time range certificate (TRK variants) ------------------------------------------------
+ * Beyond G = FEC_PK_GMAX the a-priori proof no longer excludes saturation, but real traffic stays far from it
+ * (the reference's own demodulator at 64QAM: peak |intermediate| ~12000). The TRK variant of a half-iteration
+ * therefore (1) normalises exactly where the reference does (after every even step k != 0, no normalisation at
+ * the lane shifts), so that every state metric, branch sum and LLR sum of the main passes equals the reference's
+ * value as long as nothing overflowed, and (2) records the extremes of the state metrics after every
+ * normalisation and at the start of the two main passes, plus the extremes of the two LLR maxima. The
+ * certificate evaluated from them at the end of the half-iteration (pk_certificate) proves by induction over
+ * the normalisation windows that no add of the reference saturated and none of ours wrapped. */
+struct PkTrk { uint32_t hi, lo; };
+/* extremes of a NORMALISED state (o[0] == 0 is covered by the accumulators' initial value 0) */
+__device__ __forceinline__ void pk_trk7(PkTrk &t, const uint32_t *o)
+{
+  t.hi = __vimax3_s16x2(t.hi, o[1], o[2]); t.hi = __vimax3_s16x2(t.hi, o[3], o[4]);
+  t.hi = __vimax3_s16x2(t.hi, o[5], o[6]); t.hi = __vmaxs2(t.hi, o[7]);
+  t.lo = __vimin3_s16x2(t.lo, o[1], o[2]); t.lo = __vimin3_s16x2(t.lo, o[3], o[4]);
+  t.lo = __vimin3_s16x2(t.lo, o[5], o[6]); t.lo = __vmins2(t.lo, o[7]);
+}
+__device__ __forceinline__ void pk_trk8(PkTrk &t, const uint32_t *o)
+{
+  pk_trk7(t, o);
+  t.hi = __vmaxs2(t.hi, o[0]); t.lo = __vmins2(t.lo, o[0]);
+}
+/* normalise + record, at the reference's normalisation points */
+__device__ __forceinline__ void pk_norm_trk(uint32_t *o, PkTrk &t) { pk_norm(o); pk_trk7(t, o); }
+
 /* backward step (turbodecoder_win.h:397-418), 4 adds + 8 add-max */
 __device__ __forceinline__ void pk_beta(uint32_t *o, uint32_t x, uint32_t y)
 {
@@ -268,26 +294,49 @@ __device__ __forceinline__ void pk_beta_chunk(uint32_t *o, const uint32_t *xs, c
     }
   }
 }
+/* TRK variant: the reference's schedule. Step i of the chunk is trellis step k = k0 + i, kpar = k0 & 1, knz = (k0 != 0);
+ * the checkpoint is the state BEFORE normalisation, as the reference stores beta (turbodecoder_win.h:419-432) */
+__device__ __forceinline__ void pk_beta_chunk_trk(uint32_t *o, const uint32_t *xs, const uint32_t *ys, uint32_t ck_addr,
+                                                  int kpar, bool knz, PkTrk &t)
+{
+#pragma unroll
+  for (int i = 7; i >= 0; i--) {
+    pk_beta(o, xs[i], ys[i]);
+    if (i == 0) pk_ck_store(ck_addr, o);
+    if ((((i + kpar) & 1) == 0) && (i != 0 || knz)) pk_norm_trk(o, t);
+  }
+}
 
-struct PkAcc { uint32_t crc, emx, emn, wlo, whi; };
+struct PkAcc { uint32_t crc, emx, emn, wlo, whi; uint32_t vmx, vmn, rb; PkTrk ta; };   /* vmx.. only used by the TRK variant */
 
 /* one chunk of the forward pass: recompute the inner betas from the checkpoint `ck` (= normalised beta at k0+8),
  * then alpha recursion + LLR + extrinsic write-back + CRC syndrome + decision bits for steps i = i0..7 */
-template <bool FULL, bool SHIFT>
+template <bool FULL, bool SHIFT, bool TRK>
 __device__ __forceinline__ void pk_alpha_chunk(const PkView &v, int k0, uint32_t *o, const uint32_t *ck, int i0,
                                                const uint32_t *xs, const uint32_t *ys, const uint32_t *es,
-                                               const uint2 *rr, PkAcc &acc, const uint32_t *ka)
+                                               const uint2 *rr, PkAcc &acc, const uint32_t *ka, int kpar = 0, bool top = false)
 {
   uint32_t b[8], bb[8][8], m[8], n[8];
 #pragma unroll
   for (int s = 0; s < 8; s++) b[s] = ck[s];
+  if (TRK) {
+    /* ck = beta at k0+8 before normalisation; the reference normalises it if k0+8 is even, except at the top of the
+     * sub-block (k0+8 == L), where the recursion starts from the shifted warm-up state as it is */
+    if (!top && !(kpar & 1)) pk_norm(b);
+  }
 #pragma unroll
   for (int i = 7; i >= 1; i--) {
     if (FULL || i >= i0 + 1) {
       pk_beta(b, xs[i], ys[i]);
-      if (i == 4) pk_norm(b);
+      if (TRK) {
 #pragma unroll
-      for (int s = 0; s < 8; s++) bb[i][s] = b[s];
+        for (int s = 0; s < 8; s++) bb[i][s] = b[s];                      /* beta[k0+i] as the reference stores it */
+        if (((i + kpar) & 1) == 0) pk_norm(b);
+      } else {
+        if (i == 4) pk_norm(b);
+#pragma unroll
+        for (int s = 0; s < 8; s++) bb[i][s] = b[s];
+      }
     }
   }
 #pragma unroll
@@ -298,6 +347,7 @@ __device__ __forceinline__ void pk_alpha_chunk(const PkView &v, int k0, uint32_t
       uint32_t m0 = pk_add(bn[0], m[0]), m1 = pk_add(bn[0], n[0]);
 #pragma unroll
       for (int s = 1; s < 8; s++) { m0 = pk_addmax(bn[s], m[s], m0); m1 = pk_addmax(bn[s], n[s], m1); }
+      if (TRK) { acc.vmx = __vimax3_s16x2(acc.vmx, m0, m1); acc.vmn = __vimin3_s16x2(acc.vmn, m0, m1); }
       uint32_t r = pk_sub(m1, m0);
       if (SHIFT) r = ((r >> 1) & 0x7FFF7FFFu) | (r & 0x80008000u);        /* divide_output, sse16 only (:61,565) */
       const uint32_t en = pk_sub(r, es[i]);                                /* next apriori = LLR - what this decoder was given */
@@ -312,7 +362,8 @@ __device__ __forceinline__ void pk_alpha_chunk(const PkView &v, int k0, uint32_t
       acc.wlo = __funnelshift_l(mlo, acc.wlo, 1); acc.whi = __funnelshift_l(mhi, acc.whi, 1);
 #pragma unroll
       for (int s = 0; s < 8; s++) o[s] = pk_max(m[s], n[s]);
-      if ((i & 3) == 3) pk_norm(o);
+      if (TRK) { if ((((i + kpar) & 1) == 0) && (k0 + i != 0)) pk_norm_trk(o, acc.ta); }
+      else if ((i & 3) == 3) pk_norm(o);
     } else { acc.wlo <<= 1; acc.whi <<= 1; }
   }
 }
@@ -335,14 +386,18 @@ __device__ __forceinline__ void pk_prefetch_warm(const uint32_t *y, const uint32
 /* One half-iteration of one constituent decoder for the two lanes of this thread.
  * TPC = threads per code block (P/2); VEC: L % 4 == 0 (16-byte loads). Decisions go to bits_lo/bits_hi as
  * MSB-first words; bit k of a lane sits at bit index k + (8*nck - L) of its row. */
-template <int TPC, bool VEC, bool SHIFT>
+template <int TPC, bool VEC, bool SHIFT, bool TRK>
 __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32_t tbase, unsigned gmask, int j,
                                                    const int16_t *tail, uint32_t *bits_lo, uint32_t *bits_hi, PkAcc &acc,
                                                    uint32_t *Ezero, int nEz)
 {
   const int nfull = L >> 3, rem = L & 7;
+  const int kpar = VEC ? 0 : (L & 1);               /* parity of every chunk base k0 (chunks are 8 steps, aligned to L) */
   uint32_t o[8], xs[8], es[8], ka[16];
   PkRaw raw, nraw;
+  PkTrk tb;                                         /* TRK: extremes of the beta recursion (warm-up + main pass) */
+  tb.hi = 0; tb.lo = 0;
+  if (TRK) { acc.ta.hi = 0; acc.ta.lo = 0; acc.vmx = 0x80008000u; acc.vmn = 0x7FFF7FFFu; }
 
   /* pull this half-iteration's rows (first touch comes from HBM) and the next one's towards L2 */
   for (int off = j * 28; off < L * TPC; off += TPC * 32) {      /* each of the TPC threads takes every TPC-th 128-byte line */
@@ -371,7 +426,8 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
 #pragma unroll
       for (int i = 7; i >= 0; i--) {
         pk_beta(o, xs[i], raw.y[i]);
-        if ((i & 3) == 0) pk_norm(o);
+        if (TRK) { if (!(i & 1) && (i != 0 || c != 0)) pk_norm_trk(o, tb); }     /* even k != 0 (:244-261) */
+        else if ((i & 3) == 0) pk_norm(o);
       }
     }
     raw = nraw;
@@ -403,7 +459,8 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
       const uint32_t w = __shfl_down_sync(gmask, o[i], 1, TPC);
       o[i] = (j == TPC - 1) ? ((o[i] >> 16) | ((uint32_t)t[i] << 16)) : pk_prmt(o[i], w, 0x5432u);
     }
-    pk_norm(o);
+    if (TRK) pk_trk8(tb, o);                          /* the reference starts the main pass from this state as it is */
+    else pk_norm(o);
   }
   /* ---- beta main pass, chunks aligned from the top; checkpoint c = normalised beta at k = L-8c ---- */
   pk_ck_store(tbase, o);
@@ -416,7 +473,8 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
       pk_load_raw<true, VEC>(v, L - PK_CH, 0, raw);
       PK_PIN();
       pk_finish_chunk<true>(v, L - PK_CH, 0, raw, xs, es);
-      pk_beta_chunk<true>(o, xs, raw.y, 0, tbase + 8);
+      if (TRK) pk_beta_chunk_trk(o, xs, raw.y, tbase + 8, kpar, L != PK_CH, tb);
+      else pk_beta_chunk<true>(o, xs, raw.y, 0, tbase + 8);
     }
 #pragma unroll 1
     for (int c = c0 - 2; c < nfull; c += 2) {
@@ -425,15 +483,18 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
       PK_PIN();
       if (c >= c0) {
         pk_finish_chunk<true>(v, k0, 0, raw, xs, es);
-        pk_beta_chunk<true>(o, xs, raw.y, 0, tbase + 8 * (c + 1));
+        if (TRK) pk_beta_chunk_trk(o, xs, raw.y, tbase + 8 * (c + 1), kpar, true, tb);
+        else pk_beta_chunk<true>(o, xs, raw.y, 0, tbase + 8 * (c + 1));
         pk_finish_chunk<true>(v, k0 - PK_CH, 0, rawB, xs, es);
-        pk_beta_chunk<true>(o, xs, rawB.y, 0, tbase + 8 * (c + 2));
+        if (TRK) pk_beta_chunk_trk(o, xs, rawB.y, tbase + 8 * (c + 2), kpar, k0 != PK_CH, tb);
+        else pk_beta_chunk<true>(o, xs, rawB.y, 0, tbase + 8 * (c + 2));
       }
       raw = nraw; rawB = nrawB;
     }
     /* the bottom partial chunk only serves the (unused) end of the recursion: nothing to do */
   }
   pk_ck_store_fence();
+  if (TRK) acc.rb = __vmaxs2(tb.hi, ~tb.lo);        /* max(hi, -lo - 1) per lane; the certificate adds the 1 back */
   /* ---- alpha warm-up over the last 40 symbols (:459-506), normalisation by the warm-up counter ---- */
   {
     uint32_t m[8], n[8];
@@ -450,7 +511,8 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
           pk_alpha_branches(o, xs[i], raw.y[i], m, n);
 #pragma unroll
           for (int s = 0; s < 8; s++) o[s] = pk_max(m[s], n[s]);
-          if ((i & 3) == 3) pk_norm(o);
+          if (TRK) { if (!(i & 1) && (i != 0 || c != 0)) pk_norm_trk(o, acc.ta); }   /* warm-up counter even, != 0 (:459-506) */
+          else if ((i & 3) == 3) pk_norm(o);
         }
       }
       raw = nraw;
@@ -462,7 +524,14 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
     const uint32_t first = (i == 0) ? 0u : 0xD8F0u;
     o[i] = (j == 0) ? (first | (o[i] << 16)) : pk_prmt(w, o[i], 0x5432u);
   }
-  pk_norm(o);
+  if (TRK) {
+    /* start state of the main pass as it is; the known start state (0, -10000 x 7) of sub-block 0 is covered by the
+     * certificate's constant term, not by the measurement */
+    uint32_t tv[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) tv[i] = (j == 0) ? (o[i] & 0xFFFF0000u) : o[i];
+    pk_trk8(acc.ta, tv);
+  } else pk_norm(o);
   /* ---- alpha main pass, ascending k: bottom partial chunk (if any), then the full chunks ---- */
   acc.wlo = 0; acc.whi = 0;
   int wi = 0, cc = 0;
@@ -476,7 +545,7 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
     PK_PIN();
     pk_finish_chunk<false>(v, k0, i0, raw, xs, es, ka);
     pk_ck_load_wait(ck);
-    pk_alpha_chunk<false, SHIFT>(v, k0, o, ck, i0, xs, raw.y, es, rr, acc, ka);
+    pk_alpha_chunk<false, SHIFT, TRK>(v, k0, o, ck, i0, xs, raw.y, es, rr, acc, ka, kpar, false);
     cc = 1;
   }
 #pragma unroll 1
@@ -488,7 +557,7 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
     if (c < nfull) {
       pk_finish_chunk<true>(v, k0, 0, raw, xs, es, ka);
       pk_ck_load_wait(ck);
-      pk_alpha_chunk<true, SHIFT>(v, k0, o, ck, 0, xs, raw.y, es, rr, acc, ka);
+      pk_alpha_chunk<true, SHIFT, TRK>(v, k0, o, ck, 0, xs, raw.y, es, rr, acc, ka, kpar, c == 0);
       if ((cc & 3) == 3) { bits_lo[wi] = acc.wlo; bits_hi[wi] = acc.whi; wi++; }
       cc++;
     }
@@ -604,6 +673,31 @@ __device__ PK_EPI_INLINE void pk_finish_block(int par, uint32_t Eb, const uint16
     pk_write_output<TPC>(rows, nw1, pad, K, L, j, out);
 }
 
+/* ---------------------------------------------------------------- run-time range certificate ---- */
+/* Inputs: packed per-lane extremes of one code block's half-iteration in the reference's frame (TRK schedule):
+ * [alo, ahi] alpha states after every normalisation and at the start of the main pass, rb = max(bhi, -blo - 1) for
+ * beta, [vmn, vmx] the two LLR maxima m0/m1 of every step; G = max|x| + max|y| (a priori, as for FEC_PK_GMAX).
+ * With Ra, Rb the state magnitudes: a state entering a normalisation window is within R, a window is at most 3 steps,
+ * every step adds at most G in magnitude, so
+ *   states and branch sums stay within R + 3G, the differences o[i] - o[0] of the normalisation within 2R + 6G   (C1)
+ *   LLR sums alpha-branch + beta stay within (Ra + 3G) + (Rb + 2G)                                               (C2)
+ *   sub-block 0 starts from (0, -10000 x 7): within 10000 + 3G for its first three steps, LLR sums there within
+ *   10000 + 3G + Rb + 2G; the reference's warm-ups start from -10000: 10000 + 3G                                 (C3)
+ *   the LLR m1 - m0 stays within vmx - vmn                                                                      (C4)
+ * If all four are <= 32767, induction over the windows (the first state is exact, so its measured extremes are exact,
+ * so its window cannot overflow, so the next state is exact ...) shows that no saturating add of the reference clipped
+ * and no wrapping add of this kernel wrapped: both computed the same integers. */
+__device__ __forceinline__ bool pk_certificate(uint32_t ahi, uint32_t alo, uint32_t rb, uint32_t vmx, uint32_t vmn, int G)
+{
+  const int a_hi = max((int)(short)(ahi & 0xFFFFu), (int)(short)(ahi >> 16));
+  const int a_lo = min((int)(short)(alo & 0xFFFFu), (int)(short)(alo >> 16));
+  const int Ra = max(a_hi, -a_lo);
+  const int Rb = max((int)(short)(rb & 0xFFFFu), (int)(short)(rb >> 16)) + 1;
+  const int v0 = (int)(short)(vmx & 0xFFFFu) - (int)(short)(vmn & 0xFFFFu), v1 = (int)(short)(vmx >> 16) - (int)(short)(vmn >> 16);
+  const int R = max(Ra, Rb);
+  return 2 * R + 6 * G <= 32767 && Ra + Rb + 5 * G <= 32767 && 10000 + Rb + 5 * G <= 32767 && max(v0, v1) <= 32767;
+}
+
 /* ---------------------------------------------------------------- the kernel ---- */
 /* shared memory: [Tlo, Thi: TPC*Lw halfwords each][E: nslots x (TPC*Lw+1) words][bit rows: nslots x P x nw1 words] */
 size_t fec_pk_smem_bytes(const fec_geom_t *g)
@@ -612,9 +706,13 @@ size_t fec_pk_smem_bytes(const fec_geom_t *g)
   return 4 * (tpc * g->Lw + nslots * (tpc * g->Lw + 1) + nslots * g->P * nw1);
 }
 
-template <int P, bool VEC>
+/* TRK = false: the common kernel, code blocks within the a-priori range FEC_PK_GMAX; what leaves it goes to trk_list.
+ * TRK = true: works through that list with the run-time range certificate; what the certificate cannot cover goes to
+ * exact_list (the 32-bit kernel). Both restart a handed-over code block from its soft buffer. */
+template <int P, bool VEC, bool TRK>
 __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const FecDecodeArgs a)
 {
+  if (TRK) { if (*a.list_count == 0) return; }
   constexpr int TPC = P / 2, CPW = 32 / TPC;
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ uint32_t s_tmem;
@@ -646,7 +744,7 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
   if (j == 0) s_desc[slot] = a.cbs[0];
   __syncwarp();
   int cb = -1, n = 0;
-  uint32_t M = 0;
+  uint32_t M = 0, G = 0;                         /* G: range figure max|x| + max|y| of the NEXT half-iteration of this slot */
   bool exhausted = false, fresh = false;
   for (;;) {
     /* ---- refill this group's slot from the work queue (group-uniform control flow) ---- */
@@ -654,7 +752,8 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
       unsigned q = 0;
       if (j == 0) q = atomicAdd(a.queue, 1u);
       q = __shfl_sync(gmask, q, g * TPC);
-      if (q >= a.ncb) { exhausted = true; break; }
+      if (q >= (TRK ? *a.list_count : a.ncb)) { exhausted = true; break; }
+      if (TRK) q = a.list[q];
 #if PK_OPT_DESC
       {
         /* descriptor (32 bytes, lanes 0/1 of the group) and max|soft| are fetched side by side */
@@ -667,11 +766,16 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
 #else
       M = a.soft_max[a.cbs[q].status];
 #endif
-      if (2 * M > FEC_PK_GMAX) {                    /* first half-iteration already outside the proven range */
+      if (2 * M > FEC_PK_GMAX_TRK) {                /* first half-iteration already outside what the certificate can cover */
         if (j == 0) a.exact_list[atomicAdd(a.exact_count, 1u)] = q;
         continue;
       }
-      cb = (int)q; n = 0;
+      if (!TRK && 2 * M + M / 2 > FEC_PK_GMAX) {    /* outside the a-priori range now or (decoder 1: G = 2M + max|extrinsic|) certain to
+                                                       leave it with the second iteration: certificate kernel from the start */
+        if (j == 0) a.trk_list[atomicAdd(a.trk_count, 1u)] = q;
+        continue;
+      }
+      cb = (int)q; n = 0; G = 2 * M;
 #if PK_LATE_ZERO
       fresh = true;
 #else
@@ -704,9 +808,20 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
     PkAcc acc;
     acc.crc = 0; acc.emx = 0x80008000u; acc.emn = 0x7FFF7FFFu;
     uint32_t *blo = rows + (2 * j) * nw1, *bhi = rows + (2 * j + 1) * nw1;
-    pk_half_iteration<TPC, VEC, P == 8>(v, L, tbase, gmask, j, desc.soft + 3 * SS + (par ? 6 : 0), blo, bhi, acc,
+    pk_half_iteration<TPC, VEC, P == 8, TRK>(v, L, tbase, gmask, j, desc.soft + 3 * SS + (par ? 6 : 0), blo, bhi, acc,
                                               Eslot, fresh ? Es : 0);
     fresh = false;
+    bool cert = true;
+    if (TRK) {
+      uint32_t ahi = acc.ta.hi, alo = acc.ta.lo, rb = acc.rb, vmx = acc.vmx, vmn = acc.vmn;
+#pragma unroll
+      for (int s = TPC / 2; s > 0; s >>= 1) {
+        ahi = pk_max(ahi, __shfl_xor_sync(0xFFFFFFFFu, ahi, s, TPC)); alo = pk_min(alo, __shfl_xor_sync(0xFFFFFFFFu, alo, s, TPC));
+        rb = pk_max(rb, __shfl_xor_sync(0xFFFFFFFFu, rb, s, TPC));
+        vmx = pk_max(vmx, __shfl_xor_sync(0xFFFFFFFFu, vmx, s, TPC)); vmn = pk_min(vmn, __shfl_xor_sync(0xFFFFFFFFu, vmn, s, TPC));
+      }
+      if (G > FEC_PK_GMAX) cert = pk_certificate(ahi, alo, rb, vmx, vmn, (int)G);
+    }
     uint32_t crc = acc.crc, emx = acc.emx, emn = acc.emn;
 #pragma unroll
     for (int s = TPC / 2; s > 0; s >>= 1) {
@@ -715,7 +830,11 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
       emn = pk_min(emn, __shfl_xor_sync(0xFFFFFFFFu, emn, s, TPC));
     }
     __syncwarp();
-    if (active) {
+    if (active && !cert) {
+      /* the certificate does not cover this half-iteration: its results are not used, the exact kernel re-decodes the block */
+      if (j == 0) a.exact_list[atomicAdd(a.exact_count, 1u)] = (uint32_t)cb;
+      cb = -1;
+    } else if (active) {
       const int n1 = n + 1, crc_ok = (crc == 0);
       const bool done = (crc_ok && !(desc.flags & FEC_F_NO_EARLY)) || (n1 >= (int)desc.max_its);
       if (done) {
@@ -728,8 +847,12 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
         const int e0 = (short)(emx & 0xFFFFu), e1 = (short)(emx >> 16), e2 = -(int)(short)(emn & 0xFFFFu), e3 = -(int)(short)(emn >> 16);
         const uint32_t emax = (uint32_t)max(max(e0, e1), max(max(e2, e3), 0));
         const uint32_t bx = (n1 & 1) ? emax : emax + M;
-        if (max(bx, M) + M > FEC_PK_GMAX) {
+        G = max(bx, M) + M;
+        if (G > FEC_PK_GMAX_TRK) {
           if (j == 0) a.exact_list[atomicAdd(a.exact_count, 1u)] = (uint32_t)cb;   /* re-decoded from scratch by the exact kernel */
+          cb = -1;
+        } else if (!TRK && G > FEC_PK_GMAX) {
+          if (j == 0) a.trk_list[atomicAdd(a.trk_count, 1u)] = (uint32_t)cb;       /* ... by the certificate kernel */
           cb = -1;
         } else n = n1;
       }
@@ -741,11 +864,11 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
   if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" :: "r"(s_tmem) : "memory");
 }
 
-template <int P>
+template <int P, bool TRK>
 static cudaError_t pk_launch(const FecDecodeArgs &a, int grid, size_t smem, cudaStream_t st)
 {
-  if ((a.g.L & 3) == 0) fec_tdec_pk_kernel<P, true><<<grid, FEC_PK_WARPS * 32, smem, st>>>(a);
-  else                  fec_tdec_pk_kernel<P, false><<<grid, FEC_PK_WARPS * 32, smem, st>>>(a);
+  if ((a.g.L & 3) == 0) fec_tdec_pk_kernel<P, true, TRK><<<grid, FEC_PK_WARPS * 32, smem, st>>>(a);
+  else                  fec_tdec_pk_kernel<P, false, TRK><<<grid, FEC_PK_WARPS * 32, smem, st>>>(a);
   return cudaGetLastError();
 }
 
@@ -756,26 +879,35 @@ cudaError_t fec_launch_decode_packed(const FecDecodeArgs &a, int sm_count, cudaS
   const int tpc = a.g.P / 2, per_cta = FEC_PK_WARPS * (32 / tpc);
   int grid = (int)((a.ncb + per_cta - 1) / per_cta);
   if (grid > sm_count) grid = sm_count;
-  return a.g.P == 16 ? pk_launch<16>(a, grid, smem, st) : pk_launch<8>(a, grid, smem, st);
+  cudaError_t e = a.g.P == 16 ? pk_launch<16, false>(a, grid, smem, st) : pk_launch<8, false>(a, grid, smem, st);
+  if (e != cudaSuccess) return e;
+  /* the certificate kernel works through what the first one handed over; its CTAs leave at once when the list is empty */
+  FecDecodeArgs b = a;
+  b.list = a.trk_list; b.list_count = a.trk_count; b.queue = a.trk_queue;
+  return a.g.P == 16 ? pk_launch<16, true>(b, grid, smem, st) : pk_launch<8, true>(b, grid, smem, st);
 }
 
-template <int P, bool VEC> static cudaError_t pk_attr()
+template <int P, bool VEC, bool TRK> static cudaError_t pk_attr()
 {
   /* opt in to everything the SM has: 227 KB per block minus this kernel's static (and system-reserved) shared memory */
   cudaFuncAttributes fa;
-  cudaError_t e = cudaFuncGetAttributes(&fa, fec_tdec_pk_kernel<P, VEC>);
+  cudaError_t e = cudaFuncGetAttributes(&fa, fec_tdec_pk_kernel<P, VEC, TRK>);
   if (e != cudaSuccess) return e;
   int dev = 0, optin = 0;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
-  return cudaFuncSetAttribute(fec_tdec_pk_kernel<P, VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin - (int)fa.sharedSizeBytes);
+  return cudaFuncSetAttribute(fec_tdec_pk_kernel<P, VEC, TRK>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin - (int)fa.sharedSizeBytes);
 }
 
 cudaError_t fec_pk_init(void)
 {
   cudaError_t e;
-  if ((e = pk_attr<16, true>()) != cudaSuccess) return e;
-  if ((e = pk_attr<16, false>()) != cudaSuccess) return e;
-  if ((e = pk_attr<8, true>()) != cudaSuccess) return e;
-  return pk_attr<8, false>();
+  if ((e = pk_attr<16, true, false>()) != cudaSuccess) return e;
+  if ((e = pk_attr<16, false, false>()) != cudaSuccess) return e;
+  if ((e = pk_attr<8, true, false>()) != cudaSuccess) return e;
+  if ((e = pk_attr<8, false, false>()) != cudaSuccess) return e;
+  if ((e = pk_attr<16, true, true>()) != cudaSuccess) return e;
+  if ((e = pk_attr<16, false, true>()) != cudaSuccess) return e;
+  if ((e = pk_attr<8, true, true>()) != cudaSuccess) return e;
+  return pk_attr<8, false, true>();
 }

@@ -88,6 +88,10 @@ uint64_t fec_cuda_launch_count(fec_cuda_ctx_t *ctx);
  * Sub-batches overlap on two streams; use FEC_CUDA_F_SERIAL for un-overlapped kernel durations. */
 int  fec_cuda_last_phase_ms(fec_cuda_ctx_t *ctx, float out3[3]);
 
+/* which kernels the code blocks of the LAST decode call took: out2 = { handed from the a-priori-range packed kernel to its
+ * run-time-certificate variant, handed on to the exact 32-bit kernel }; everything else stayed in the first kernel */
+int  fec_cuda_last_path_counts(fec_cuda_ctx_t *ctx, uint64_t out2[2]);
+
 /* Pinned (page-locked) host memory for e_bits / data buffers: replaces srslte_vec_malloc
  * (lib/src/phy/utils/vector.c:125-132) for the buffers handed to the decode calls. Buffers obtained here (or
  * registered with cudaHostRegister) are DMA'd directly; any other host pointer is staged through a copy. */

@@ -154,7 +154,21 @@ int orc_rm_rx(const int16_t *in, int E, int K, int rv, int sb_layout, int16_t *s
  * since the last orc_dbg_reset() (thread-local). Used to validate the range proof behind the packed CUDA fast path. */
 static __thread long orc_sat_count = 0;
 static __thread int  orc_peak_val = 0, orc_peak_in = 0;
-void orc_dbg_reset(void) { orc_sat_count = 0; orc_peak_val = 0; orc_peak_in = 0; }
+/* largest spread max_i o[i] - min_i o[i] of the 8 state metrics seen at a normalisation point, per recursion
+ * (0 beta warm-up, 1 beta, 2 alpha warm-up, 3 alpha): the quantity the packed kernel's run-time range certificate bounds */
+static __thread int  orc_phase = 0, orc_spread[4] = {0, 0, 0, 0};
+/* the quantities the packed CUDA kernel's run-time range certificate is computed from (fec_tdec_packed.cu, pk_certificate):
+ * orc_mag[phase]: largest |state metric| right after a normalisation and at the start of a main pass (sub-block 0's known
+ * alpha start state excluded); orc_llr_range: largest (max - min) over one sub-block of the two LLR maxima m0 / m1 */
+static __thread int  orc_mag[4] = {0, 0, 0, 0}, orc_llr_range = 0;
+void orc_dbg_reset(void) { orc_sat_count = 0; orc_peak_val = 0; orc_peak_in = 0; orc_llr_range = 0; for (int i = 0; i < 4; i++) orc_spread[i] = orc_mag[i] = 0; }
+int  orc_dbg_spread(int phase) { return orc_spread[phase & 3]; }
+int  orc_dbg_mag(int phase) { return orc_mag[phase & 3]; }
+int  orc_dbg_llr_range(void) { return orc_llr_range; }
+static void orc_track_mag(const int16_t o[8])
+{
+  for (int i = 0; i < 8; i++) { int a = o[i] < 0 ? -(int)o[i] : o[i]; if (a > orc_mag[orc_phase]) orc_mag[orc_phase] = a; }
+}
 long orc_dbg_sat_count(void) { return orc_sat_count; }
 int  orc_dbg_peak_val(void) { return orc_peak_val; }
 int  orc_dbg_peak_in(void) { return orc_peak_in; }
@@ -203,8 +217,12 @@ static void win_alpha_branches(const int16_t o[8], int16_t x, int16_t y, int16_t
 static inline void win_normalize(int k, int16_t o[8])
 {   /* turbodecoder_win.h:244-261 with normalize_period 2 */
   if ((k % 2) == 0 && k != 0) {
+    int hi = o[0], lo = o[0];
+    for (int i = 1; i < 8; i++) { if (o[i] > hi) hi = o[i]; if (o[i] < lo) lo = o[i]; }
+    if (hi - lo > orc_spread[orc_phase]) orc_spread[orc_phase] = hi - lo;
     for (int i = 1; i < 8; i++) o[i] = subs(o[i], o[0]);
     o[0] = 0;
+    orc_track_mag(o);
   }
 }
 
@@ -225,17 +243,20 @@ static void map_windowed(int K, int P, const int16_t *in, const int16_t *app, co
   }
 
   /* beta warm-up over the FIRST 40 symbols of every sub-block */
+  orc_phase = 0;
   for (int d = 0; d < P; d++) {
     for (int i = 0; i < 8; i++) o[i] = NEG_INF;
     for (int k = W - 1; k >= 0; k--) { win_beta_step(o, X[d * L + k], par[d * L + k], 1); win_normalize(k, o); }
     memcpy(warm[d], o, sizeof(o));
   }
+  orc_phase = 1;
   for (int d = 0; d < P; d++) {
     if (d < P - 1) memcpy(o, warm[d + 1], sizeof(o));
     else {   /* last lane: known end state through the 3 tail steps, no apriori, wrapping adds */
       o[0] = 0; for (int i = 1; i < 8; i++) o[i] = NEG_INF;
       for (int k = 2; k >= 0; k--) win_beta_step(o, tail_x[k], tail_p[k], 0);
     }
+    orc_track_mag(o);
     memcpy(B[d][L], o, sizeof(o));
     for (int k = L - 1; k >= 0; k--) {
       win_beta_step(o, X[d * L + k], par[d * L + k], 1);
@@ -244,6 +265,7 @@ static void map_windowed(int K, int P, const int16_t *in, const int16_t *app, co
     }
   }
   /* alpha warm-up over the LAST 40 symbols of every sub-block */
+  orc_phase = 2;
   for (int d = 0; d < P; d++) {
     int16_t m[8], n[8];
     for (int i = 0; i < 8; i++) o[i] = NEG_INF;
@@ -255,16 +277,23 @@ static void map_windowed(int K, int P, const int16_t *in, const int16_t *app, co
     }
     memcpy(warm[d], o, sizeof(o));
   }
+  orc_phase = 3;
   for (int d = 0; d < P; d++) {
     int16_t m[8], n[8];
-    if (d > 0) memcpy(o, warm[d - 1], sizeof(o));
+    if (d > 0) { memcpy(o, warm[d - 1], sizeof(o)); orc_track_mag(o); }
     else { o[0] = 0; for (int i = 1; i < 8; i++) o[i] = NEG_INF; }
+    int vhi = -40000, vlo = 40000;
     for (int k = 0; k < L; k++) {
       int idx = d * L + k;
       win_alpha_branches(o, X[idx], par[idx], m, n);
       const int16_t *b = B[d][k + 1];
       int16_t m0 = adds(b[0], m[0]), m1 = adds(b[0], n[0]);
       for (int i = 1; i < 8; i++) { m0 = maxs(m0, adds(b[i], m[i])); m1 = maxs(m1, adds(b[i], n[i])); }
+      if (m0 > vhi) vhi = m0;
+      if (m1 > vhi) vhi = m1;
+      if (m0 < vlo) vlo = m0;
+      if (m1 < vlo) vlo = m1;
+      if (vhi - vlo > orc_llr_range) orc_llr_range = vhi - vlo;
       int16_t r = subs(m1, m0);
       if (P == 8) r = (int16_t)(r >> 1);   /* divide_output exists for sse16 only (turbodecoder_win.h:61,565-567) */
       out[idx] = r;

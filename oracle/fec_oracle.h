@@ -38,6 +38,9 @@ void orc_dbg_reset(void);
 long orc_dbg_sat_count(void);
 int  orc_dbg_peak_val(void);
 int  orc_dbg_peak_in(void);
+int  orc_dbg_mag(int phase);      /* largest |state metric| after a normalisation / at the start of a main pass (certificate input) */
+int  orc_dbg_llr_range(void);     /* largest max-min of the LLR maxima m0/m1 over one sub-block (certificate input) */
+int  orc_dbg_spread(int phase);   /* largest state-metric spread at a normalisation point: 0 beta warm-up, 1 beta, 2 alpha warm-up, 3 alpha */
 
 /* one constituent MAP decoder run, natural order. tail_x/tail_p: the 3 tail LLRs of this decoder. */
 void orc_map(int K, int P, const int16_t *x, const int16_t *app, const int16_t *par,

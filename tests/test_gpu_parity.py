@@ -79,6 +79,64 @@ def test_tdec_at_range_bound_vs_oracle(fec, orc):
         assert not bad, bad
 
 
+def _noisy_codeword(K, amp, sigma, seed):
+    """natural-layout int16 LLRs [s p p'] x K + 12 tail of a random turbo codeword (CRC24B attached), bit 1 -> +amp"""
+    synth = importlib.import_module("empower-srslte_b200.synth")
+    rng = np.random.default_rng(seed)
+    body = rng.integers(0, 256, (1, K // 8 - 3), dtype=np.uint8)
+    blk = np.concatenate([body, synth._crc_bytes(synth.crc24(synth.CRC24B, body))], axis=1)
+    coded = synth.turbo_encode(np.unpackbits(blk, axis=1))[0]
+    x = amp * ((2.0 * coded - 1.0) + sigma * rng.standard_normal(coded.shape))
+    return np.ascontiguousarray(np.clip(np.rint(x), -32768, 32767).astype(np.int16))
+
+
+def test_tdec_beyond_apriori_range_vs_oracle(fec, orc):
+    """LLR scales of the reference's own demodulator and above (max|soft| 600 .. 2250, i.e. G up to 4500 and beyond): the
+    code blocks leave the a-priori range of the packed kernel and run in its certificate variant (reference normalisation
+    schedule + run-time range certificate) or, when the certificate cannot cover them, in the exact kernel. Decisions
+    of every half-iteration must be bit-exact either way; the certificate variant must actually carry the realistic
+    cases (few hand-overs to the exact kernel)."""
+    synth = importlib.import_module("empower-srslte_b200.synth")
+    cases = []
+    for K in (408, 800, 816, 1008, 1056, 2048, 5824, 6144):       # P=8 (L=51, 100), P=16 with L odd / = 2 mod 4 / = 0 mod 4
+        n = 3 * K + 12
+        r = np.random.default_rng(K + 7)
+        for amp in (1100, 1500, 2250):                              # adversarial constant-magnitude patterns
+            cases.append((K, np.where(np.arange(n) % 2 == 0, amp, -amp).astype(np.int16), "alt%d" % amp))
+            cases.append((K, (amp * (r.integers(0, 2, n) * 2 - 1)).astype(np.int16), "rnd%d" % amp))
+            cases.append((K, r.integers(-amp, amp + 1, n).astype(np.int16), "uni%d" % amp))
+        # noisy codewords at the scale of the reference's 64QAM demodulator (max|LLR| ~ 700..1300), several half-iterations needed
+        for amp, sigma in ((150, 0.9), (200, 0.8), (250, 0.75), (250, 1.0)):
+            cases.append((K, _noisy_codeword(K, amp, sigma, K + amp), "cw%d_%g" % (amp, sigma)))
+    NH = 8
+    want = []
+    for K, inp, _ in cases:
+        ob = np.zeros((NH, K // 8), np.uint8)
+        assert orc.orc_tdec_halfits(K, P(inp), NH, P(ob), None) == 0
+        want.append(ob)
+    tot_trk = tot_exact = 0
+    for nof in (1, 2, 3, 4, 6, 8):
+        res = fec.decode_cbs([c[0] for c in cases], [c[1] for c in cases], nof, early_stop=False)
+        bad = [(c[0], c[2], nof) for c, r, w in zip(cases, res, want) if not (r["out"] == w[nof - 1]).all()]
+        assert not bad, bad
+        t, e = fec.last_path_counts()
+        tot_trk += t; tot_exact += e
+    assert tot_trk > 0, "the certificate kernel never ran"
+    # realistic scales with CRC early stop (as decode_tb_cb runs them): the certificate variant must carry (nearly) all of them
+    idx = [i for i, c in enumerate(cases) if c[2].startswith("cw")]
+    exp_its = []
+    for i in idx:
+        K = cases[i][0]
+        ok = [n + 1 for n in range(NH) if orc.orc_crc(1, P(np.ascontiguousarray(want[i][n])), K) == 0]
+        exp_its.append(ok[0] if ok else NH)
+    res = fec.decode_cbs([cases[i][0] for i in idx], [cases[i][1] for i in idx], NH, crc_type=1, early_stop=True)
+    for i, r, n in zip(idx, res, exp_its):
+        assert r["its"] == n and (r["out"] == want[i][n - 1]).all(), (cases[i][0], cases[i][2], r["its"], n)
+    t, e = fec.last_path_counts()
+    print("certificate kernel: %d of %d realistic code blocks (half-iterations %s), exact kernel: %d" % (t, len(idx), exp_its, e))
+    assert t >= len(idx) // 2 and e <= len(idx) // 4, (t, e, len(idx))
+
+
 def test_rm_rx_golden_subset(fec):
     z = G.tables()
     rows = [r for r in z["rm"] if int(r[0]) in (40, 104, 400, 408, 800, 816, 1024, 3136, 5824, 6144)]

@@ -56,7 +56,7 @@ def run(sigma_sym, ntb=2, mode="sym", amp=100.0, sigma=0.45, max_its=8, seed=1):
             h = Tdec()
             orc.orc_tdec_new_cb_soft(C.byref(h), K, P(soft))
             out = np.zeros(K // 8, np.uint8)
-            its, sat_first, Gs, peaks = 0, None, [], []
+            its, sat_first, Gs, peaks, spr = 0, None, [], [], []
             emax = 0
             for n in range(max_its):
                 bx = emax + M if n % 2 == 0 else emax
@@ -67,6 +67,7 @@ def run(sigma_sym, ntb=2, mode="sym", amp=100.0, sigma=0.45, max_its=8, seed=1):
                 its += 1
                 sc = orc.orc_dbg_sat_count()
                 peaks.append(orc.orc_dbg_peak_val())
+                spr.append([orc.orc_dbg_spread(i) for i in range(4)])
                 if sc and sat_first is None: sat_first = n
                 # next apriori = LLR - given: decoder 1 leaves ext1 (= LLR), app of decoder 2 = ext1 - app1
                 if n % 2 == 0:
@@ -76,7 +77,7 @@ def run(sigma_sym, ntb=2, mode="sym", amp=100.0, sigma=0.45, max_its=8, seed=1):
                 emax = int(np.abs(a).max())
                 if orc.orc_crc(1, P(out), K) == 0:
                     break
-            rows.append(dict(M=M, its=its, sat_first=sat_first, G=Gs, peak=peaks))
+            rows.append(dict(M=M, its=its, sat_first=sat_first, G=Gs, peak=peaks, spr=spr))
     return rows
 
 
@@ -90,6 +91,13 @@ def summarise(tag, rows):
     print(f"{tag}: {n} CBs, mean half-its {its.mean():.2f}, M median {int(np.median([r['M'] for r in rows]))}, "
           f"inside G<=2000 for all half-its: {fast / n:.2f}, reference never saturates: {nosat / n:.2f}, "
           f"max G median {int(np.median(gm))} p90 {int(np.percentile(gm, 90))}, peak|intermediate| median {int(np.median(pk))} max {int(pk.max())}")
+    # run-time certificate candidates: Sa + Sb + c*G <= 32767 with the spreads measured at the reference's normalisation points
+    for c in (4, 7):
+        okc = sum(1 for r in rows if all(max(s[1], s[3]) + max(s[0], s[1]) + 0 * g + max(s[2], s[3]) * 0 + c * g <= 32767 and s[3] + s[1] + c * g <= 32767
+                                         for s, g in zip(r["spr"], r["G"])))
+        print(f"    certificate Sa+Sb+{c}G<=32767 holds for all half-its: {okc / n:.2f}")
+    allsp = np.array([[s + [g] for s, g in zip(r["spr"], r["G"])][-1] for r in rows])
+    print(f"    last half-it: spreads (bw, b, aw, a) median {np.median(allsp[:, :4], axis=0).astype(int)} max {allsp[:, :4].max(axis=0)}; G median {int(np.median(allsp[:, 4]))} max {allsp[:, 4].max()}")
     for k in (2, 3, 4, 6, 8):
         sel = [r for r in rows if r["its"] >= k]
         if sel:
