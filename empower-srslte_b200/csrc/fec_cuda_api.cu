@@ -70,6 +70,8 @@ struct fec_cuda_ctx {
   uint32_t     *d_x2masks, *d_x1states;   /* front end: scrambling-sequence jump tables (fec_frontend.cu) */
   float         fe_ms;          /* device time of the front-end kernels of the last call */
   uint64_t      path_cnt[2];    /* last call: code blocks handed to the certificate kernel / to the exact kernel */
+  int           eager_ttl;      /* > 0: recent sub-batches handed blocks to the certificate kernel: launch it right behind the first
+                                   kernel instead of after the host has seen the hand-over counts (pipe_finish) */
   unsigned int *h_queue;        /* pinned mirror of d_queue (fec_cuda_decode_cbs) */
   cudaEvent_t   ev_call;        /* start of the current decode_tbs call (copy stream) */
   double        t_call;         /* host clock at the start of the call */
@@ -353,6 +355,7 @@ struct fec_pipe {
   uint32_t     *d_softmax; size_t softmax_cap;
   uint32_t     *d_exact;   size_t exact_cap;
   unsigned int *d_queue, *h_queue;
+  struct { int k; uint32_t off, cnt; } *grp; int ngrp, stages;   /* decode launches of this sub-batch and the stages already enqueued */
   cudaEvent_t   ev_in, ev_k, ev_done, ev[4];
   tbplan_t     *plan; size_t plan_cap;
   fec_cuda_tb_t *tbs; uint32_t n, ncb, ntb; int dev_io, busy;
@@ -366,6 +369,8 @@ static int pipe_init(fec_cuda_ctx_t *ctx, fec_pipe_t *p)
   memset(p, 0, sizeof(*p));
   CU(cudaMalloc(&p->d_queue, sizeof(unsigned int) * FEC_NQUEUE * FEC_NOF_K));
   CU(cudaMallocHost(&p->h_queue, sizeof(unsigned int) * FEC_NQUEUE * FEC_NOF_K));
+  p->grp = (decltype(p->grp))malloc(sizeof(*p->grp) * FEC_NOF_K);
+  if (!p->grp) return -1;
   CU(cudaEventCreate(&p->ev_in));
   CU(cudaEventCreateWithFlags(&p->ev_k, cudaEventDisableTiming));
   CU(cudaEventCreate(&p->ev_done));
@@ -383,7 +388,7 @@ static void pipe_free(fec_pipe_t *p)
   if (p->ev_fe) cudaEventDestroy(p->ev_fe);
   cudaFree(p->d_cbbytes); cudaFree(p->d_softmax); cudaFree(p->d_exact); cudaFree(p->d_queue); cudaFreeHost(p->h_queue);
   if (p->ev_in) { cudaEventDestroy(p->ev_in); cudaEventDestroy(p->ev_k); cudaEventDestroy(p->ev_done); for (int i = 0; i < 4; i++) cudaEventDestroy(p->ev[i]); }
-  free(p->plan);
+  free(p->plan); free(p->grp);
   memset(p, 0, sizeof(*p));
 }
 
@@ -672,13 +677,21 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
   if (ncb) { CU(fec_launch_rm((const FecRmDesc *)pp->st_rmd.d, pp->d_softmax, ncb, max_n_out, srm)); ctx->launches++; }
   CU(cudaEventRecord(pp->ev[1], srm));
   if (srm != sc) CU(cudaStreamWaitEvent(sc, pp->ev[1], 0));
+  /* the certificate kernel follows the first kernel at once only while recent sub-batches needed it; otherwise pipe_finish
+   * launches it when it sees hand-over counts. Measured on the bench workload (nothing handed over, tools/variants.sh A/B
+   * on one box): first + exact kernel 1.69 ms per step, first + certificate + exact 1.78 ms, first alone 1.72-1.78 ms — a
+   * third persistent full-shared-memory grid between the sub-batches of the two compute streams costs 4 % even when it
+   * finds nothing to do, while the (empty) exact-kernel launch happens to pace the two streams well and stays */
+  pp->stages = FEC_ST_A | FEC_ST_C | (ctx->eager_ttl > 0 ? FEC_ST_B : 0);
+  pp->ngrp = 0;
   for (int k = 0; k < FEC_NOF_K; k++) {
     if (!grp_cnt[k]) continue;
     FecDecodeArgs a;
     fill_decode_args(ctx, k, &a, (const FecCbDesc *)pp->st_cbd.d, (FecCbStatus *)pp->st_status.d, pp->d_queue, pp->d_softmax, pp->d_exact, pp->d_exact + pp->exact_cap / 8,
                      grp_off[k], grp_cnt[k], NULL);
-    CU(fec_launch_decode(a, ctx->sm_count, sc));
-    ctx->launches += a.exact_list ? 3 : 1;
+    CU(fec_launch_decode(a, ctx->sm_count, sc, pp->stages));
+    ctx->launches += a.exact_list ? 1 + ((pp->stages & FEC_ST_B) != 0) + ((pp->stages & FEC_ST_C) != 0) : 1;
+    if (a.exact_list) { pp->grp[pp->ngrp].k = k; pp->grp[pp->ngrp].off = grp_off[k]; pp->grp[pp->ngrp].cnt = grp_cnt[k]; pp->ngrp++; }
   }
   CU(cudaEventRecord(pp->ev[2], sc));
   if (ntb) { CU(fec_launch_tb_assemble((const FecTbDesc *)pp->st_tbd.d, (const FecCbStatus *)pp->st_status.d, ctx->d_r24a, ntb, sc)); ctx->launches++; }
@@ -707,6 +720,35 @@ static int pipe_finish(fec_cuda_ctx_t *ctx, fec_pipe_t *pp)
   CU(cudaEventSynchronize(pp->ev_done));
   for (int i = 0; i < 3; i++) { float ms = 0; if (cudaEventElapsedTime(&ms, pp->ev[i], pp->ev[i + 1]) == cudaSuccess) ctx->phase_ms[i] += ms; }
   { float ms = 0; if (cudaEventElapsedTime(&ms, pp->ev_fe, pp->ev[0]) == cudaSuccess) ctx->fe_ms += ms; }
+  if (pp->ncb && pp->ngrp) {
+    /* hand-over counts of the kernels launched so far: run the stages that were left out and turn out to be needed */
+    uint64_t ntrk = 0, nexact = 0;
+    for (int g = 0; g < pp->ngrp; g++) { ntrk += pp->h_queue[4 * FEC_NOF_K + pp->grp[g].k]; nexact += pp->h_queue[2 * FEC_NOF_K + pp->grp[g].k]; }
+    if (ntrk && !(pp->stages & FEC_ST_B)) {
+      /* certificate kernel now, then the exact kernel once more for what the certificate cannot cover: its first run is
+       * complete, so its work-queue counter and its list start again from zero */
+      cudaStream_t sc = ctx->s_comp[0];
+      ctx->path_cnt[1] += nexact;
+      for (int g = 0; g < pp->ngrp; g++) {
+        const int k = pp->grp[g].k;
+        CU(cudaMemsetAsync(pp->d_queue + 2 * k + 1, 0, sizeof(unsigned int), sc));
+        CU(cudaMemsetAsync(pp->d_queue + 2 * FEC_NOF_K + k, 0, sizeof(unsigned int), sc));
+        FecDecodeArgs a;
+        fill_decode_args(ctx, k, &a, (const FecCbDesc *)pp->st_cbd.d, (FecCbStatus *)pp->st_status.d, pp->d_queue, pp->d_softmax, pp->d_exact,
+                         pp->d_exact + pp->exact_cap / 8, pp->grp[g].off, pp->grp[g].cnt, NULL);
+        CU(fec_launch_decode(a, ctx->sm_count, sc, FEC_ST_B | FEC_ST_C));
+        ctx->launches += 2;
+      }
+      if (pp->ntb) { CU(fec_launch_tb_assemble((const FecTbDesc *)pp->st_tbd.d, (const FecCbStatus *)pp->st_status.d, ctx->d_r24a, pp->ntb, sc)); ctx->launches++; }
+      CU(cudaMemcpyAsync(pp->st_status.h, pp->st_status.d, sizeof(FecCbStatus) * pp->ncb, cudaMemcpyDeviceToHost, sc));
+      if (pp->ntb) CU(cudaMemcpyAsync(pp->st_ret.h, pp->st_ret.d, sizeof(int32_t) * pp->ntb, cudaMemcpyDeviceToHost, sc));
+      CU(cudaMemcpyAsync(pp->h_queue, pp->d_queue, sizeof(unsigned int) * FEC_NQUEUE * FEC_NOF_K, cudaMemcpyDeviceToHost, sc));
+      if (!pp->dev_io && pp->data_total) CU(cudaMemcpyAsync(pp->st_data.h, pp->st_data.d, pp->data_total, cudaMemcpyDeviceToHost, sc));
+      CU(cudaStreamSynchronize(sc));
+    }
+    /* launch policy of the next sub-batches */
+    if (ntrk) ctx->eager_ttl = 16; else if (ctx->eager_ttl > 0) ctx->eager_ttl--;
+  }
   if (pp->ncb) path_count_add(ctx, pp->h_queue);
   if (pp->syms && !pp->dev_io)
     for (uint32_t i = 0; i < pp->n; i++) {
@@ -921,7 +963,7 @@ extern "C" int fec_cuda_decode_cbs(fec_cuda_ctx_t *ctx, fec_cuda_cb_t *cbs, uint
     FecDecodeArgs a;
     fill_decode_args(ctx, k, &a, (const FecCbDesc *)ctx->st_cbd.d, (FecCbStatus *)ctx->st_status.d, ctx->d_queue, ctx->d_softmax, ctx->d_exact, ctx->d_exact + ctx->exact_cap / 8,
                      grp_off[k], grp_cnt[k], DBG_LLR);
-    CUF(fec_launch_decode(a, ctx->sm_count, st));
+    CUF(fec_launch_decode(a, ctx->sm_count, st, FEC_ST_ALL));
     ctx->launches += a.exact_list ? 3 : 1;
   }
   CUF(cudaMemcpyAsync(ctx->st_status.h, ctx->st_status.d, sizeof(FecCbStatus) * n, cudaMemcpyDeviceToHost, st));

@@ -456,7 +456,7 @@ __global__ void fec_tdec_small_kernel(const FecDecodeArgs a)
 
 static size_t fec_small_smem_per_cb(const fec_geom_t *g) { return (size_t)(g->K + 1) * 16 + (size_t)g->K * 2 + g->K / 8; }
 
-cudaError_t fec_launch_decode(const FecDecodeArgs &a, int sm_count, cudaStream_t st)
+cudaError_t fec_launch_decode(const FecDecodeArgs &a, int sm_count, cudaStream_t st, int stages)
 {
   if (a.ncb == 0) return cudaSuccess;
   if (a.g.P == 0) {
@@ -470,8 +470,8 @@ cudaError_t fec_launch_decode(const FecDecodeArgs &a, int sm_count, cudaStream_t
   }
   if (a.exact_list && !a.dbg_llr) {
     /* fast path first; whatever it hands over (range condition) is decoded by the exact kernel */
-    cudaError_t e = fec_launch_decode_packed(a, sm_count, st);
-    if (e != cudaSuccess) return e;
+    cudaError_t e = fec_launch_decode_packed(a, sm_count, st, stages);
+    if (e != cudaSuccess || !(stages & FEC_ST_C)) return e;
     FecDecodeArgs b = a;
     b.list = a.exact_list; b.list_count = a.exact_count; b.queue = a.queue + 1;
     const uint32_t slots = b.slots;

@@ -106,8 +106,16 @@ extern "C" void fec_gen_gold_tables(uint32_t *x2_masks, uint32_t *x1_states);
 
 size_t fec_win_smem_bytes(const fec_geom_t *g, uint32_t slots);
 uint32_t fec_win_pick_slots(const fec_geom_t *g);
-cudaError_t fec_launch_decode(const FecDecodeArgs &a, int sm_count, cudaStream_t st);
-cudaError_t fec_launch_decode_packed(const FecDecodeArgs &a, int sm_count, cudaStream_t st);
+/* stages of a windowed decode launch (classes P = 8, 16 with hand-over lists): A the a-priori-range packed kernel, B its
+ * run-time-certificate variant on what A handed over, C the exact kernel on what A and B handed over. A caller may leave B
+ * and C out and launch them later, once it has seen non-zero hand-over counts (fec_cuda_api.cu does, so that the common
+ * case is one launch); C must come after B. Ignored by the single-launch paths (P = 0, forced exact, LLR dump). */
+#define FEC_ST_A 1
+#define FEC_ST_B 2
+#define FEC_ST_C 4
+#define FEC_ST_ALL 7
+cudaError_t fec_launch_decode(const FecDecodeArgs &a, int sm_count, cudaStream_t st, int stages);
+cudaError_t fec_launch_decode_packed(const FecDecodeArgs &a, int sm_count, cudaStream_t st, int stages);
 size_t fec_pk_smem_bytes(const fec_geom_t *g);
 cudaError_t fec_pk_init(void);
 cudaError_t fec_launch_rm(const FecRmDesc *descs, uint32_t *soft_max, uint32_t n, uint32_t max_n_out, cudaStream_t st);

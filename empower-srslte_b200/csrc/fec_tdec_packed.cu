@@ -872,15 +872,16 @@ static cudaError_t pk_launch(const FecDecodeArgs &a, int grid, size_t smem, cuda
   return cudaGetLastError();
 }
 
-cudaError_t fec_launch_decode_packed(const FecDecodeArgs &a, int sm_count, cudaStream_t st)
+cudaError_t fec_launch_decode_packed(const FecDecodeArgs &a, int sm_count, cudaStream_t st, int stages)
 {
   if (a.ncb == 0) return cudaSuccess;
   const size_t smem = fec_pk_smem_bytes(&a.g);
   const int tpc = a.g.P / 2, per_cta = FEC_PK_WARPS * (32 / tpc);
   int grid = (int)((a.ncb + per_cta - 1) / per_cta);
   if (grid > sm_count) grid = sm_count;
-  cudaError_t e = a.g.P == 16 ? pk_launch<16, false>(a, grid, smem, st) : pk_launch<8, false>(a, grid, smem, st);
-  if (e != cudaSuccess) return e;
+  cudaError_t e = cudaSuccess;
+  if (stages & FEC_ST_A) e = a.g.P == 16 ? pk_launch<16, false>(a, grid, smem, st) : pk_launch<8, false>(a, grid, smem, st);
+  if (e != cudaSuccess || !(stages & FEC_ST_B)) return e;
   /* the certificate kernel works through what the first one handed over; its CTAs leave at once when the list is empty */
   FecDecodeArgs b = a;
   b.list = a.trk_list; b.list_count = a.trk_count; b.queue = a.trk_queue;
