@@ -199,6 +199,7 @@ def main():
     ap.add_argument("--sigma", type=float, default=0.45, help="AWGN std of the synthetic LLRs (0.45 = operating point)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-worst-case", action="store_true")
+    ap.add_argument("--no-tx", action="store_true", help="skip the transmit-side leg (turbo encoder + rate matching on the device)")
     ap.add_argument("--no-symbols", action="store_true", help="skip the leg that starts from equalised symbols (front end)")
     ap.add_argument("--sigma-sym", type=float, default=0.062, help="AWGN std per real dimension of the synthetic 64QAM symbols")
     args = ap.parse_args()
@@ -369,6 +370,7 @@ def main():
         fec.decode_syms(dd, sy_ab[0][0], pkg.F_DEVICE_IO | pkg.F_SERIAL)
         fe_ms = fec.last_frontend_ms()
         ph_s = fec.last_phase_ms()
+        path_s = fec.last_path_counts()
         out_host = d_out[0].cpu().numpy()
         bad = sum(1 for i in range(B) if dd[i].ret == 0 and not (out_host[i, :TBS // 8] == payload[i % ncw]).all())
         if bad:
@@ -383,11 +385,44 @@ def main():
                      ms_per_step=ms_sd / args.steps, tb_ok_frac=allsum(ok_s) / (world * B), halfits_per_cb=allsum(its_s) / (world * B * C_CB),
                      e2e=dict(value=allsum(ok_sh) * TBS * args.steps / (ms_sh / 1e3) / 1e9, unit=UNIT, ms_per_step=ms_sh / args.steps,
                               h2d_bytes_per_step=B * nre * 8 + B * C_CB * (32 + 48) + B * (520 + 80), d2h_bytes_per_step=d2h),
+                     code_blocks_by_kernel=dict(total=B * C_CB, certificate_variant=path_s[0], exact=path_s[1]),
                      serial_phases_ms=dict(frontend=fe_ms, rate_dematch=ph_s[0], turbo_decode=ph_s[1], tb_assemble_crc24a=ph_s[2]),
                      frontend_kernel=dict(ms_per_launch=fe_ms, algorithmic_bytes=fe_bytes, achieved=fe_bytes / (fe_ms / 1e3) / 1e9,
                                           peak=peaks()["hbm_gbs"], unit="GB/s", frac=fe_bytes / (fe_ms / 1e3) / 1e9 / peaks()["hbm_gbs"], bound="hbm"))
         # the LLR legs below reuse dd / hd: put the soft buffers back into the state of the LLR workload
         fec.decode_tbs(dd, pkg.F_DEVICE_IO)
+
+    # ---- transmit side: the same transport blocks through CRC + segmentation + turbo encoding + rate matching
+    #      on the device (fec_cuda_encode_tbs, device-resident payloads and packed output), checked against the oracle ----
+    tx = None
+    if not args.no_tx:
+        ncw = payload.shape[0]
+        d_pay = torch.from_numpy(np.ascontiguousarray(payload[np.arange(B) % ncw])).to(f"cuda:{local_rank}")
+        EST = (NBITS // 8 + 15) & ~15
+        d_e = torch.zeros((B, EST), dtype=torch.uint8, device=f"cuda:{local_rank}")
+        td = (pkg.TxTbDesc * B)()
+        for i in range(B):
+            td[i].tbs, td[i].Qm, td[i].rv, td[i].nof_e_bits = TBS, QM, RV, NBITS
+            td[i].data, td[i].e_bits = d_pay.data_ptr() + i * (TBS // 8), d_e.data_ptr() + i * EST
+        for _ in range(3):
+            fec.encode_tbs(td, pkg.F_DEVICE_IO)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(args.steps):
+            fec.encode_tbs(td, pkg.F_DEVICE_IO)
+        e1.record(stream)
+        barrier()
+        ms_tx = shard.reduce_job(dist if world > 1 else None, f"cuda:{local_rank}", e0.elapsed_time(e1))[0]
+        if rank == 0:
+            synth_ = importlib.import_module("empower-srslte_b200.synth")
+            want = np.packbits(synth_.encode_tbs(payload[:2], TBS, QM, RV, NBITS), axis=1)
+            got = d_e[:2].cpu().numpy()
+            if not (got[:, : NBITS // 8] == want).all():
+                raise SystemExit("bench.py: the device encoder's bits differ from the host synthesiser's")
+        tx = dict(workload="the same transport blocks encoded: CRC-24A, segmentation, CRC-24B, turbo encoder, rate matching",
+                  value=world * B * TBS * args.steps / (ms_tx / 1e3) / 1e9, unit="Gbit/s of transport-block bits", ms_per_step=ms_tx / args.steps,
+                  cbs_per_s=world * B * C_CB * args.steps / (ms_tx / 1e3), checked="first 2 transport blocks bit-exact vs the numpy synthesiser (itself pinned to srslte_dlsch_encode)")
 
     # ---- worst case: all 8 half-iterations for every code block (no early stop), same inputs ----
     worst = None
@@ -449,7 +484,7 @@ def main():
                     e2e=dict(value=e2e_val, unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h, ms_per_step=ms_e / args.steps,
                              sync_ms_per_step=ms_e_sync / args.steps),
                     sync_ms_per_step=ms_sync / args.steps,
-                    gpu_launches=launches, clocks=clocks, roofline=roof, worst_case_8_halfits=worst, frontend_symbols=front, cpu_baseline=cpu)
+                    gpu_launches=launches, clocks=clocks, roofline=roof, worst_case_8_halfits=worst, frontend_symbols=front, transmit_side=tx, cpu_baseline=cpu)
         print(json.dumps(line), flush=True)
     fec.close()
     if world > 1:

@@ -15,13 +15,18 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("FEC_CUDA_LIB") or os.path.join(HERE, "libsrslte_fec_cuda.so")   # FEC_CUDA_LIB: tuning builds (tools/variants.sh)
 CSRC = os.path.join(HERE, "csrc")
-SOURCES = ["fec_kernels.cu", "fec_tdec_packed.cu", "fec_frontend.cu", "fec_cuda_api.cu", "fec_compat.cu", "fec_tables.c"]
+SOURCES = ["fec_kernels.cu", "fec_tdec_packed.cu", "fec_frontend.cu", "fec_tx.cu", "fec_cuda_api.cu", "fec_compat.cu", "fec_tables.c"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-Xcompiler", "-fPIC", "-shared"]
 
 MAX_CB = 13
 F_DEVICE_IO = 1
 F_NO_EARLY_STOP = 2
 F_SERIAL = 4
+
+
+class TxTbDesc(C.Structure):          # == fec_cuda_txtb_t
+    _fields_ = [("tbs", C.c_uint32), ("Qm", C.c_uint32), ("rv", C.c_uint32), ("nof_e_bits", C.c_uint32),
+                ("data", C.c_void_p), ("e_bits", C.c_void_p), ("ret", C.c_int32), ("reserved", C.c_uint32)]
 
 
 class TbDesc(C.Structure):
@@ -88,6 +93,7 @@ def load():
         lib.fec_cuda_cbsegm.argtypes = [C.c_uint32, C.POINTER(C.c_uint32)]
         lib.fec_cuda_last_phase_ms.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
         lib.fec_cuda_last_path_counts.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
+        lib.fec_cuda_encode_tbs.argtypes = [C.c_void_p, C.POINTER(TxTbDesc), C.c_uint32, C.c_uint32]
         lib.fec_cuda_decode_syms.argtypes = [C.c_void_p, C.POINTER(TbDesc), C.POINTER(SymDesc), C.c_uint32, C.c_uint32]
         lib.fec_cuda_submit_syms.argtypes = [C.c_void_p, C.POINTER(TbDesc), C.POINTER(SymDesc), C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64)]
         lib.fec_cuda_last_frontend_ms.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
@@ -166,6 +172,22 @@ class FecCuda:
         if rc:
             raise RuntimeError(f"fec_cuda_last_phase_ms: {rc}")
         return [float(v) for v in o]
+
+    def encode_tbs(self, descs, flags=0):
+        """fec_cuda_encode_tbs on a ctypes array of TxTbDesc"""
+        rc = self.lib.fec_cuda_encode_tbs(self.h, descs, len(descs), flags)
+        if rc:
+            raise RuntimeError(f"fec_cuda_encode_tbs: {rc} {self.error()}")
+
+    def encode_tb(self, tbs, Qm, rv, nof_e_bits, data):
+        """one transport block: data[tbs/8] uint8 -> (ret, packed e_bits[(nof_e_bits+7)/8]) as srslte_dlsch_encode emits them"""
+        d = (TxTbDesc * 1)()
+        a = np.ascontiguousarray(data, dtype=np.uint8)
+        o = np.zeros((nof_e_bits + 7) // 8, np.uint8)
+        d[0].tbs, d[0].Qm, d[0].rv, d[0].nof_e_bits = tbs, Qm, rv, nof_e_bits
+        d[0].data, d[0].e_bits = a.ctypes.data, o.ctypes.data
+        self.encode_tbs(d)
+        return int(d[0].ret), o
 
     def last_path_counts(self):
         """code blocks of the last decode call handed (to the certificate variant of the packed kernel, on to the exact kernel)"""

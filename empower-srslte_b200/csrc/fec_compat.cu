@@ -267,3 +267,18 @@ extern "C" int srslte_sch_decode_tb_cuda(srslte_softbuffer_rx_t *softbuffer, uin
   if (nof_iterations) *nof_iterations = t.avg_its;                             /* sch.c:420 */
   return t.ret;
 }
+
+/* ================================================================= encode_tb_off (sch.c:188-296) ==== */
+extern "C" int srslte_sch_encode_tb_cuda(uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits, uint8_t *data, uint8_t *e_bits)
+{
+  if (!e_bits || !data) return SRSLTE_ERROR_INVALID_INPUTS;                    /* sch.c:196-199 */
+  std::lock_guard<std::mutex> lk(g_mu);
+  fec_cuda_ctx_t *ctx = compat_ctx();
+  if (!ctx) return SRSLTE_ERROR;
+  fec_cuda_txtb_t t;
+  memset(&t, 0, sizeof(t));
+  t.tbs = tbs; t.Qm = Qm; t.rv = rv; t.nof_e_bits = nof_e_bits; t.data = data; t.e_bits = e_bits;
+  if (fec_cuda_encode_tbs(ctx, &t, 1, 0)) { fprintf(stderr, "libsrslte_fec_cuda: %s\n", fec_cuda_last_error(ctx)); return SRSLTE_ERROR; }
+  if (t.ret == SRSLTE_ERROR) fprintf(stderr, "Error filler bits are not supported. Use standard TBS\n");
+  return t.ret;
+}

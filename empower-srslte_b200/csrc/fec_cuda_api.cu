@@ -25,6 +25,7 @@ typedef struct {
   uint32_t   slots;
   uint32_t  *d_pair_addr;     /* packed kernel: decoder-2 address words */
   uint2     *d_pair_crc[2];   /* packed kernel: CRC syndrome words, CRC24A / CRC24B */
+  uint16_t  *d_txsrc;         /* transmit side: circular-buffer position -> d-stream bit (built on the first encode of this K) */
 } ktab_t;
 
 typedef struct {
@@ -49,6 +50,8 @@ struct fec_cuda_ctx {
   sbchunk_t    *chunks;
   uint32_t      nchunks, next_id;
   stage_t       st_e, st_data, st_cbd, st_rmd, st_tbd, st_status, st_ret, st_exd;
+  stage_t       st_txin, st_txout, st_txtb, st_txcb;   /* transmit side: payloads, packed output, descriptors */
+  uint8_t      *d_txcrc; size_t txcrc_cap;
   uint8_t      *d_cbbytes; size_t cbbytes_cap;
   int16_t      *d_tmpsoft; size_t tmpsoft_cap;
   unsigned int *d_queue;   /* per K: work-queue counters of the packed and the exact kernel (2 x FEC_NOF_K), FEC_NOF_K hand-over counts to the
@@ -173,7 +176,7 @@ extern "C" void fec_cuda_destroy(fec_cuda_ctx_t *ctx)
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
   for (int i = 0; i < FEC_NOF_K; i++) if (ctx->ktab[i].ready) {
-    cudaFree(ctx->ktab[i].d_step); cudaFree(ctx->ktab[i].d_rank); cudaFree(ctx->ktab[i].d_pair_addr);
+    cudaFree(ctx->ktab[i].d_step); cudaFree(ctx->ktab[i].d_rank); cudaFree(ctx->ktab[i].d_pair_addr); cudaFree(ctx->ktab[i].d_txsrc);
     cudaFree(ctx->ktab[i].d_pair_crc[0]); cudaFree(ctx->ktab[i].d_pair_crc[1]);
   }
   cudaFree(ctx->d_softmax); cudaFree(ctx->d_exact); cudaFreeHost(ctx->h_queue);
@@ -181,6 +184,7 @@ extern "C" void fec_cuda_destroy(fec_cuda_ctx_t *ctx)
   free(ctx->chunks);
   stage_free(&ctx->st_e); stage_free(&ctx->st_data); stage_free(&ctx->st_cbd); stage_free(&ctx->st_rmd);
   stage_free(&ctx->st_tbd); stage_free(&ctx->st_status); stage_free(&ctx->st_ret); stage_free(&ctx->st_exd);
+  stage_free(&ctx->st_txin); stage_free(&ctx->st_txout); stage_free(&ctx->st_txtb); stage_free(&ctx->st_txcb); cudaFree(ctx->d_txcrc);
   cudaFree(ctx->d_cbbytes); cudaFree(ctx->d_tmpsoft); cudaFree(ctx->d_r24a); cudaFree(ctx->d_r24b); cudaFree(ctx->d_queue);
   cudaFree(ctx->d_x2masks); cudaFree(ctx->d_x1states);
   pipes_destroy(ctx);
@@ -979,6 +983,104 @@ extern "C" int fec_cuda_decode_cbs(fec_cuda_ctx_t *ctx, fec_cuda_cb_t *cbs, uint
   }
   free(ctx->dbg_slot); ctx->dbg_slot = slot_of; ctx->dbg_n = n;
   return 0;
+}
+
+/* ---------------------------------------------------------------- transmit side ---- */
+/* encode_tb_off for n transport blocks (sch.c:188-296): CRC-24A, segmentation, CRC-24B, turbo encoding, rate matching.
+ * Synchronous. Stateless: a retransmission is encoded from the data again (the reference reads the circular buffer it
+ * kept in srslte_softbuffer_tx_t; the bits are the same). */
+extern "C" int fec_cuda_encode_tbs(fec_cuda_ctx_t *ctx, fec_cuda_txtb_t *tbs, uint32_t n, uint32_t flags)
+{
+  if (!ctx || (!tbs && n)) return FEC_CUDA_EINVAL;
+  if (n == 0) return 0;
+  cudaSetDevice(ctx->device);
+  const int dev_io = (flags & FEC_CUDA_F_DEVICE_IO) != 0;
+  uint32_t ntb = 0, ncb = 0;
+  size_t in_total = 0, out_total = 0;
+  uint32_t (*seg)[9] = (uint32_t (*)[9])malloc(sizeof(uint32_t) * 9 * n);
+  size_t *offs = (size_t *)malloc(sizeof(size_t) * 2 * n);
+  if (!seg || !offs) { free(seg); free(offs); return FEC_CUDA_ERROR; }
+  void *plan = seg;
+  for (uint32_t i = 0; i < n; i++) {
+    fec_cuda_txtb_t *t = &tbs[i];
+    t->ret = FEC_CUDA_EINVAL;
+    if (!t->data || !t->e_bits || t->rv > 3 || t->Qm == 0 || (t->tbs & 7) || fec_segm(t->tbs, seg[i])) continue;
+    if (dev_io && ((uintptr_t)t->e_bits & 3)) continue;
+    if (seg[i][0] || seg[i][1] > FEC_CUDA_MAX_CB) { t->ret = FEC_CUDA_ERROR; continue; }      /* filler bits / too many CBs: sch.c:202-210 */
+    t->ret = 1;                                                                                   /* marks "planned" until the end */
+    if (seg[i][1] == 0) continue;
+    offs[2 * i] = in_total; in_total += ((size_t)t->tbs / 8 + 15) & ~(size_t)15;
+    offs[2 * i + 1] = out_total; out_total += (((size_t)t->nof_e_bits + 7) / 8 + 15) & ~(size_t)15;
+    ntb++; ncb += seg[i][1];
+  }
+  int rc = 0;
+  if (ntb) {
+    if (stage_reserve(ctx, &ctx->st_txtb, sizeof(FecTxTbDesc) * ntb) || stage_reserve(ctx, &ctx->st_txcb, sizeof(FecTxCbDesc) * ncb) ||
+        dev_reserve(ctx, (void **)&ctx->d_txcrc, &ctx->txcrc_cap, (size_t)ntb * 4) ||
+        (!dev_io && (stage_reserve(ctx, &ctx->st_txin, in_total) || stage_reserve(ctx, &ctx->st_txout, out_total)))) { free(plan); free(offs); return FEC_CUDA_ENODEV; }
+    FecTxTbDesc *tbd = (FecTxTbDesc *)ctx->st_txtb.h;
+    FecTxCbDesc *cbd = (FecTxCbDesc *)ctx->st_txcb.h;
+    cudaStream_t st = ctx->stream;
+    uint32_t itb = 0, icb = 0;
+    for (uint32_t i = 0; i < n && !rc; i++) {
+      fec_cuda_txtb_t *t = &tbs[i];
+      if (t->ret != 1 || seg[i][1] == 0) continue;
+      const uint32_t C = seg[i][1], C2 = seg[i][7];
+      const uint8_t *data_dev = dev_io ? t->data : (const uint8_t *)ctx->st_txin.d + offs[2 * i];
+      uint8_t *e_dev = dev_io ? t->e_bits : (uint8_t *)ctx->st_txout.d + offs[2 * i + 1];
+      if (!dev_io) memcpy((uint8_t *)ctx->st_txin.h + offs[2 * i], t->data, t->tbs / 8);
+      tbd[itb].data = data_dev; tbd[itb].tbs = t->tbs; tbd[itb].crc3 = ctx->d_txcrc + 4 * (size_t)itb;
+      tbd[itb].e_out = (uint32_t *)e_dev; tbd[itb].e_words = (t->nof_e_bits + 31) / 32;
+      const uint32_t Gp = t->nof_e_bits / t->Qm, gamma = Gp % C;
+      uint32_t rp = 0, wp = 0;
+      for (uint32_t cb = 0; cb < C; cb++) {
+        const uint32_t K = cb < C2 ? seg[i][3] : seg[i][2], rlen = C > 1 ? K - 24 : K;
+        const uint32_t n_e = (cb + gamma + 1 <= C) ? t->Qm * (Gp / C) : t->Qm * ((Gp + C - 1) / C);         /* sch.c:241-245 */
+        ktab_t *kt;
+        if (ktab_get(ctx, K, &kt)) { rc = FEC_CUDA_EINVAL; break; }
+        if (!kt->d_txsrc) {
+          const size_t N = 3 * (size_t)K + 12;
+          uint16_t *src = (uint16_t *)malloc(N * 2);
+          fec_gen_rm_txsrc(&kt->g, 32 * FEC_TX_W, src);
+          if (cudaMalloc(&kt->d_txsrc, N * 2) != cudaSuccess || cudaMemcpy(kt->d_txsrc, src, N * 2, cudaMemcpyHostToDevice) != cudaSuccess) rc = FEC_CUDA_ENODEV;
+          free(src);
+          if (rc) break;
+        }
+        FecTxCbDesc *d = &cbd[icb++];
+        memset(d, 0, sizeof(*d));
+        const int last = cb == C - 1;
+        d->src = data_dev + rp / 8; d->tbcrc = tbd[itb].crc3; d->e_out = e_dev; d->txsrc = kt->d_txsrc;
+        d->nsrc = rlen / 8 - (last ? 3 : 0); d->ntb = last ? 3 : 0; d->cbcrc = C > 1;
+        d->K = K; d->f1 = (uint32_t)kt->g.f1; d->f2 = (uint32_t)kt->g.f2;
+        d->wp = wp; d->E = n_e; d->off = kt->off[t->rv]; d->N = 3 * K + 12;
+        rp += rlen; wp += n_e;
+      }
+      itb++;
+    }
+    if (!rc) {
+      cudaError_t e = cudaSuccess;
+      if (!dev_io) {
+        e = cudaMemcpyAsync(ctx->st_txin.d, ctx->st_txin.h, in_total, cudaMemcpyHostToDevice, st);
+      }
+      if (e == cudaSuccess) e = cudaMemcpyAsync(ctx->st_txtb.d, tbd, sizeof(FecTxTbDesc) * ntb, cudaMemcpyHostToDevice, st);
+      if (e == cudaSuccess) e = cudaMemcpyAsync(ctx->st_txcb.d, cbd, sizeof(FecTxCbDesc) * icb, cudaMemcpyHostToDevice, st);
+      if (e == cudaSuccess) e = fec_launch_tx((const FecTxTbDesc *)ctx->st_txtb.d, ntb, (const FecTxCbDesc *)ctx->st_txcb.d, icb, ctx->d_r24a, ctx->d_r24b, st);
+      ctx->launches += 2;
+      if (e == cudaSuccess && !dev_io) e = cudaMemcpyAsync(ctx->st_txout.h, ctx->st_txout.d, out_total, cudaMemcpyDeviceToHost, st);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+      if (e != cudaSuccess) rc = fail(ctx, FEC_CUDA_ERROR, "encode: %s", cudaGetErrorString(e));
+    }
+  }
+  for (uint32_t i = 0; i < n; i++) {
+    fec_cuda_txtb_t *t = &tbs[i];
+    if (t->ret != 1) continue;
+    if (rc) { t->ret = FEC_CUDA_ERROR; continue; }
+    if (seg[i][1] == 0) { if (!dev_io) memset(t->e_bits, 0, ((size_t)t->nof_e_bits + 7) / 8); t->ret = 0; continue; }
+    if (!dev_io) memcpy(t->e_bits, (uint8_t *)ctx->st_txout.h + offs[2 * i + 1], ((size_t)t->nof_e_bits + 7) / 8);
+    t->ret = 0;
+  }
+  free(plan); free(offs);
+  return rc;
 }
 
 /* ---------------------------------------------------------------- standalone rate de-matching ---- */

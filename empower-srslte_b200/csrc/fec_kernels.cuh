@@ -106,6 +106,23 @@ extern "C" void fec_gen_gold_tables(uint32_t *x2_masks, uint32_t *x1_states);
 
 size_t fec_win_smem_bytes(const fec_geom_t *g, uint32_t slots);
 uint32_t fec_win_pick_slots(const fec_geom_t *g);
+/* ---- transmit side (fec_tx.cu) ---- */
+#define FEC_TX_W 194              /* words per d-stream in shared memory: K + 4 <= 6148 bits */
+struct FecTxTbDesc { const uint8_t *data; uint32_t tbs; uint8_t *crc3; uint32_t *e_out; uint32_t e_words; };   /* e_out: zeroed by the CRC kernel */
+struct FecTxCbDesc {
+  const uint8_t  *src;      /* payload bytes of this code block inside the transport block (device) */
+  const uint8_t  *tbcrc;    /* the 3 CRC-24A bytes of the transport block (follow the payload of its last code block) */
+  uint8_t        *e_out;    /* packed output of the transport block, 4-byte aligned, zeroed */
+  const uint16_t *txsrc;    /* per K: NULL-free circular-buffer position -> bit index stream * 32 * FEC_TX_W + i */
+  uint32_t        nsrc, ntb;/* payload bytes from src, CRC-24A bytes behind them (0 or 3) */
+  uint32_t        cbcrc;    /* 1: CRC-24B over the first K - 24 bits goes into the last 24 */
+  uint32_t        K, f1, f2;
+  uint32_t        wp, E;    /* output bit offset inside e_out and number of bits (encode_tb_off: wp, n_e) */
+  uint32_t        off, N;   /* start position for this rv and length 3K + 12 of the NULL-free circular buffer */
+};
+cudaError_t fec_launch_tx(const FecTxTbDesc *tbd, uint32_t ntb, const FecTxCbDesc *cbd, uint32_t ncb,
+                          const uint32_t *r24a, const uint32_t *r24b, cudaStream_t st);
+
 /* stages of a windowed decode launch (classes P = 8, 16 with hand-over lists): A the a-priori-range packed kernel, B its
  * run-time-certificate variant on what A handed over, C the exact kernel on what A and B handed over. A caller may leave B
  * and C out and launch them later, once it has seen non-zero hand-over counts (fec_cuda_api.cu does, so that the common

@@ -154,6 +154,20 @@ void fec_gen_rm_rank(const fec_geom_t *g, uint16_t *rank, uint32_t off[4])
   }
 }
 
+void fec_gen_rm_txsrc(const fec_geom_t *g, uint32_t stream_bits, uint16_t *src)
+{
+  const int D = g->K + 4, R = (D - 1) / 32 + 1, KP = 32 * R, ND = KP - D, NCB = 3 * KP;
+  int cnt = 0;
+  for (int w = 0; w < NCB; w++) {
+    int y, stream, m;
+    if (w < KP) { stream = 0; y = (w % R) * 32 + rm_colperm[w / R]; }
+    else if (((w - KP) & 1) == 0) { m = (w - KP) / 2; stream = 1; y = (m % R) * 32 + rm_colperm[m / R]; }
+    else { m = (w - KP) / 2; stream = 2; y = (rm_colperm[m / R] + 32 * (m % R) + 1) % KP; }
+    if (y < ND) continue;
+    src[cnt++] = (uint16_t)((uint32_t)stream * stream_bits + (uint32_t)(y - ND));
+  }
+}
+
 void fec_gen_crc_powers(uint32_t poly, uint32_t *Rt, int n)
 {
   uint32_t r = poly & 0xFFFFFFu;         /* x^24 mod g */

@@ -57,6 +57,9 @@ void fec_gen_pair_crc_table(const fec_geom_t *g, uint32_t poly, uint32_t *tab);
  * start ranks: transmitted index of soft position o for rv is (rank[o] - off[rv]) mod (3K+12). */
 void fec_gen_rm_rank(const fec_geom_t *g, uint16_t *rank, uint32_t off[4]);
 /* natural coded position t (0..3K+11) -> device soft-buffer offset, and -> reference soft-buffer offset */
+/* transmit side: NULL-free circular-buffer position (counted from w[0], as rank) -> stream * stream_bits + index in d_stream,
+ * index < K + 4 (36.212 5.1.4.1.1-2); n = 3K + 12 entries */
+void fec_gen_rm_txsrc(const fec_geom_t *g, uint32_t stream_bits, uint16_t *src);
 int  fec_soft_offset_dev(const fec_geom_t *g, int t);
 int  fec_soft_offset_ref(const fec_geom_t *g, int t, int sb_layout);
 /* R[m] = x^(m+24) mod g(x): CRC of a message is the XOR of R[nbits-1-i] over its set bits i */

@@ -81,6 +81,10 @@ void srslte_softbuffer_rx_reset_cb(srslte_softbuffer_rx_t *q, uint32_t nof_cb);
 int  srslte_sch_decode_tb_cuda(srslte_softbuffer_rx_t *softbuffer, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits,
                                int16_t *e_bits, uint8_t *data, uint32_t max_iterations, uint32_t *nof_iterations);
 
+/* ---- encode_tb_off (sch.c:188-296): the body a patched sch.c calls on the transmit side. data = NULL (the reference
+ * re-reads its tx soft buffer for a retransmission) is not supported: pass the transport block again. w_offset = 0. */
+int  srslte_sch_encode_tb_cuda(uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits, uint8_t *data, uint8_t *e_bits);
+
 #ifdef __cplusplus
 }
 #endif

@@ -163,6 +163,24 @@ int  fec_cuda_frontend(fec_cuda_ctx_t *ctx, const fec_cuda_sym_t *sym, int16_t *
 uint32_t fec_cuda_cinit_pdsch(uint32_t rnti, uint32_t codeword, uint32_t nslot, uint32_t cell_id);   /* sequences.c:64-66 */
 uint32_t fec_cuda_cinit_pusch(uint32_t rnti, uint32_t nslot, uint32_t cell_id);                       /* sequences.c:71-73 */
 
+/* ---- transmit side -------------------------------------------------------------------------------
+ * The data part of srslte_dlsch_encode / srslte_ulsch_encode, i.e. encode_tb_off (sch.c:188-296): CRC-24A over the
+ * transport block, segmentation, CRC-24B per code block, turbo encoding (srslte_tcod_encode_lut, turbocoder.c:196-330)
+ * and rate matching (srslte_rm_turbo_tx_lut, rm_turbo.c:332-376) for a batch of transport blocks. Stateless: a
+ * retransmission (rv != 0) is encoded from the data again instead of from srslte_softbuffer_tx_t; the bits are the same. */
+typedef struct {
+  uint32_t       tbs;          /* transport block size in bits (multiple of 8) */
+  uint32_t       Qm;           /* modulation order x layers, as encode_tb_off receives it */
+  uint32_t       rv;           /* redundancy version 0..3 */
+  uint32_t       nof_e_bits;   /* cfg->nbits[].nof_bits */
+  const uint8_t *data;         /* tbs/8 bytes; host, or device with FEC_CUDA_F_DEVICE_IO */
+  uint8_t       *e_bits;       /* out: (nof_e_bits + 7) / 8 bytes, packed MSB first as srslte_dlsch_encode leaves them; a device
+                                  pointer must be 4-byte aligned and have room up to the next multiple of 4 bytes */
+  int32_t        ret;          /* 0, -1 (filler bits / too many code blocks, sch.c:202-210), -2 invalid */
+  uint32_t       reserved;
+} fec_cuda_txtb_t;
+int  fec_cuda_encode_tbs(fec_cuda_ctx_t *ctx, fec_cuda_txtb_t *tbs, uint32_t n, uint32_t flags);
+
 /* bare turbo decoding of n code blocks from natural-layout LLRs (host pointers) */
 int  fec_cuda_decode_cbs(fec_cuda_ctx_t *ctx, fec_cuda_cb_t *cbs, uint32_t n, uint32_t flags);
 

@@ -534,6 +534,85 @@ static void *orc_mt_worker(void *a_)
   return NULL;
 }
 
+/* ------------------------------------------------------------------ transmit side ---- */
+/* One constituent encoder of 36.212 5.1.3.2.1 (g0 = 1 + D^2 + D^3 feedback, g1 = 1 + D + D^3), restating the bitwise
+ * srslte_tcod_encode (turbocoder.c:82-165): u[K] -> z[K], then the 3 trellis-termination steps -> xt[3], zt[3]. */
+static void rsc_encode(const uint8_t *u, int K, uint8_t *z, uint8_t *xt, uint8_t *zt)
+{
+  int r1 = 0, r2 = 0, r3 = 0;
+  for (int k = 0; k < K; k++) {
+    int fb = u[k] ^ r2 ^ r3;
+    z[k] = (uint8_t)(fb ^ r1 ^ r3);
+    r3 = r2; r2 = r1; r1 = fb;
+  }
+  for (int k = 0; k < 3; k++) {            /* switch in the lower position: the input is the feedback itself */
+    xt[k] = (uint8_t)(r2 ^ r3);
+    zt[k] = (uint8_t)(r1 ^ r3);
+    r3 = r2; r2 = r1; r1 = 0;
+  }
+}
+
+/* bits[K] (one per byte) -> coded[3K+12] (one per byte) in the order srslte_tcod_encode emits:
+ * [x0 z0 z'0 x1 z1 z'1 ...] then xK zK xK+1 zK+1 xK+2 zK+2 x'K z'K x'K+1 z'K+1 x'K+2 z'K+2 (turbocoder.c:82-165) */
+int orc_encode_cb(int K, const uint8_t *bits, uint8_t *coded)
+{
+  static __thread uint8_t ui[ORC_MAX_K], z0[ORC_MAX_K], z1[ORC_MAX_K];
+  static __thread uint16_t fwd[ORC_MAX_K], rev[ORC_MAX_K];
+  uint8_t xt0[3], zt0[3], xt1[3], zt1[3];
+  if (orc_qpp(K, fwd, rev)) return -1;
+  for (int i = 0; i < K; i++) ui[i] = bits[fwd[i]];
+  rsc_encode(bits, K, z0, xt0, zt0);
+  rsc_encode(ui, K, z1, xt1, zt1);
+  for (int i = 0; i < K; i++) { coded[3 * i] = bits[i]; coded[3 * i + 1] = z0[i]; coded[3 * i + 2] = z1[i]; }
+  for (int k = 0; k < 3; k++) {
+    coded[3 * K + 2 * k] = xt0[k]; coded[3 * K + 2 * k + 1] = zt0[k];
+    coded[3 * K + 6 + 2 * k] = xt1[k]; coded[3 * K + 6 + 2 * k + 1] = zt1[k];
+  }
+  return 0;
+}
+
+/* encode_tb_off + srslte_tcod_encode_lut + srslte_rm_turbo_tx_lut (sch.c:188-296, turbocoder.c:196-330,
+ * rm_turbo.c:332-376): data[tbs/8] -> e_bits, packed MSB first, (nof_e_bits+7)/8 bytes. Stateless: a retransmission
+ * (rv != 0) re-derives the circular buffer the reference keeps in its tx soft buffer. 0 / -1 / -2 as the reference. */
+int orc_tb_encode(uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits, const uint8_t *data, uint8_t *e_bits)
+{
+  uint32_t s[9];
+  if (!data || !e_bits || rv > 3 || Qm == 0) return -2;
+  if (orc_cbsegm(tbs, s)) return -2;
+  const uint32_t F = s[0], C = s[1], K1 = s[2], K2 = s[3], C2 = s[7];
+  if (F) return -1;                                  /* "filler bits are not supported" sch.c:202-205 */
+  if (C > ORC_MAX_CB) return -1;
+  memset(e_bits, 0, (nof_e_bits + 7) / 8);
+  if (C == 0) return 0;
+  static __thread uint8_t tb[ORC_MAX_CB * ORC_MAX_K / 8 + 8], cbb[ORC_MAX_K / 8];
+  static __thread uint8_t bits[ORC_MAX_K], coded[3 * ORC_MAX_K + 12];
+  static __thread uint16_t tab[3 * ORC_MAX_K + 12];
+  const uint32_t par = orc_crc(0, data, (int)tbs);   /* TB CRC-24A, attached behind the data (36.212 5.3.2.1) */
+  memcpy(tb, data, tbs / 8);
+  tb[tbs / 8] = (uint8_t)(par >> 16); tb[tbs / 8 + 1] = (uint8_t)(par >> 8); tb[tbs / 8 + 2] = (uint8_t)par;
+  const uint32_t Gp = nof_e_bits / Qm, gamma = Gp % C;
+  uint32_t rp = 0, wp = 0;
+  for (uint32_t i = 0; i < C; i++) {
+    const uint32_t K = i < C2 ? K2 : K1, rlen = C > 1 ? K - 24 : K;
+    const uint32_t n_e = (i <= C - gamma - 1) ? Qm * (Gp / C) : Qm * ((Gp + C - 1) / C);      /* sch.c:241-245 */
+    memcpy(cbb, tb + rp / 8, rlen / 8);
+    if (C > 1) {
+      const uint32_t c = orc_crc(1, cbb, (int)rlen);                                          /* CB CRC-24B */
+      cbb[rlen / 8] = (uint8_t)(c >> 16); cbb[rlen / 8 + 1] = (uint8_t)(c >> 8); cbb[rlen / 8 + 2] = (uint8_t)c;
+    }
+    for (uint32_t k = 0; k < K; k++) bits[k] = (cbb[k >> 3] >> (7 - (k & 7))) & 1u;
+    if (orc_encode_cb((int)K, bits, coded)) return -1;
+    orc_rm_table((int)K, (int)rv, tab);
+    const uint32_t N = 3 * K + 12;
+    for (uint32_t m = 0; m < n_e; m++) {
+      const uint32_t o = wp + m;
+      if (coded[tab[m % N]]) e_bits[o >> 3] |= (uint8_t)(0x80u >> (o & 7));
+    }
+    rp += rlen; wp += n_e;
+  }
+  return 0;
+}
+
 /* out3 = {TBs decoded, TBs OK, total CB half-iterations}; returns wall seconds */
 double orc_bench_tb_mt(int nthreads, int ntb, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits,
                        const int16_t *e_bits_all, uint32_t max_its, int reps, uint64_t *out3)

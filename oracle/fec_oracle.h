@@ -85,6 +85,11 @@ void     orc_csi_s(int mod_bits, int16_t *e, const float *csi, uint32_t nof_bits
 void     orc_ulsch_deinterleave(const int16_t *q, uint32_t Qm, uint32_t Hp, uint32_t cols, int16_t *g,
                                 const uint32_t *ri_pos, uint32_t nri);                         /* sch.c:860-881 */
 
+/* transmit side: turbo encoder + rate matching of srslte_dlsch_encode / srslte_ulsch_encode's data part */
+int      orc_encode_cb(int K, const uint8_t *bits, uint8_t *coded);                              /* turbocoder.c:82-165 */
+int      orc_tb_encode(uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits, const uint8_t *data,
+                       uint8_t *e_bits);                                                        /* sch.c:188-296 */
+
 /* multithreaded timing harness for bench.py's cpu_baseline leg ("port") */
 double orc_bench_tb_mt(int nthreads, int ntb, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits,
                        const int16_t *e_bits_all, uint32_t max_its, int reps, uint64_t *out3);

@@ -128,3 +128,17 @@ def test_decode_tb_with_reference_softbuffer_calls(lib, case):
         assert [bool(crc[i]) for i in range(nC)] == [bool(v) for v in tx["crc"][:nC]]
     lib.srslte_softbuffer_rx_free(q)
     assert bytes(q.raw) == bytes(40)
+
+
+def test_encode_tb_wrapper_golden(lib):
+    """the transmit-side body a patched sch.c calls: the packed bits srslte_dlsch_encode emitted (golden fixtures)"""
+    import os
+    z = np.load(os.path.join(G.GOLD, "tb.npz"))
+    lib.srslte_sch_encode_tb_cuda.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]
+    for ci, c in enumerate(G.tb_cases()):
+        data = np.ascontiguousarray(c["tbdata"][: c["tbs"] // 8])
+        for tx, t in enumerate(c["tx"]):
+            e = np.zeros((c["nbits"] + 7) // 8, np.uint8)
+            assert lib.srslte_sch_encode_tb_cuda(c["tbs"], c["Qm"], t["rv"], c["nbits"], P(data), P(e)) == 0
+            assert (np.unpackbits(e)[: c["nbits"]] == np.unpackbits(z[f"e_{ci}_{tx}"])[: c["nbits"]]).all(), (c["id"], tx)
+    assert lib.srslte_sch_encode_tb_cuda(75376, 6, 0, 90000, None, P(np.zeros(8, np.uint8))) == -2

@@ -113,3 +113,21 @@ def test_golden_frontend_ul(orc, case):
     ng = g.size - len(case["ri_pos"])
     assert (g[:64] == case["g0"]).all()
     assert G.crc32(g[:ng]) == case["crc_g"]
+
+
+def test_tb_encode_golden(orc):
+    """transmit side: the oracle's encoder reproduces the bits srslte_dlsch_encode emitted for every
+    (re)transmission of the golden transport blocks (sch.c:188-296)"""
+    import os
+    import _golden as G
+    z = np.load(os.path.join(G.GOLD, "tb.npz"))
+    n = 0
+    for ci, c in enumerate(G.tb_cases()):
+        data = np.ascontiguousarray(c["tbdata"][: c["tbs"] // 8])
+        for tx, t in enumerate(c["tx"]):
+            want = z[f"e_{ci}_{tx}"]
+            got = np.zeros((c["nbits"] + 7) // 8, np.uint8)
+            assert orc.orc_tb_encode(c["tbs"], c["Qm"], t["rv"], c["nbits"], P(data), P(got)) == 0
+            assert (np.unpackbits(got)[: c["nbits"]] == np.unpackbits(want)[: c["nbits"]]).all(), (c["id"], tx)
+            n += 1
+    assert n >= 4

@@ -13,3 +13,6 @@ if f:
         k["ms_per_launch"], k["achieved"], k["frac"]))
     if "serial_phases_ms" in f:
         print("symbols serial phases:", {k: round(v, 3) for k, v in f["serial_phases_ms"].items()})
+t = j.get("transmit_side")
+if t:
+    print("transmit side: %.1f Gbit/s, %.3f ms per step, %.2f M code blocks/s" % (t["value"], t["ms_per_step"], t["cbs_per_s"] / 1e6))
