@@ -29,7 +29,7 @@ def _oracle_tb(orc, ot, tbs, Qm, rv, nbits, llr, max_its):
     return ret, dd, crc, its
 
 
-def _run_harq(fec, orc, tbs, Qm, nbits, sigma, ntb, seed, max_its=8):
+def _run_harq(fec, orc, tbs, Qm, nbits, sigma, ntb, seed, max_its=8, amp=100.0):
     """ntb HARQ processes, rv sequence 0,2,3,1 until ACK, all processes of a round in ONE batched call"""
     rng = np.random.default_rng(seed)
     payload = rng.integers(0, 256, (ntb, tbs // 8), dtype=np.uint8)
@@ -43,7 +43,7 @@ def _run_harq(fec, orc, tbs, Qm, nbits, sigma, ntb, seed, max_its=8):
         if not live:
             break
         e = synth.encode_tbs(payload[live], tbs, Qm, rv, nbits)
-        llr = synth.awgn_llr(e, sigma, rng)
+        llr = synth.awgn_llr(e, sigma, rng, amp)
         d = (pkg.TbDesc * len(live))()
         outs = []
         for s, i in enumerate(live):
@@ -53,6 +53,8 @@ def _run_harq(fec, orc, tbs, Qm, nbits, sigma, ntb, seed, max_its=8):
             d[s].softbuffer, d[s].new_data = sb0 + i, int(txi == 0)
             d[s].e_bits, d[s].data = llr[s].ctypes.data, out.ctypes.data
         fec.decode_tbs(d)
+        pc = fec.last_path_counts()
+        stats["trk"] = stats.get("trk", 0) + pc[0]; stats["exact"] = stats.get("exact", 0) + pc[1]
         nxt = []
         for s, i in enumerate(live):
             ret, dd, crc, its = _oracle_tb(orc, ots[i], tbs, Qm, rv, nbits, llr[s], max_its)
@@ -70,6 +72,18 @@ def _run_harq(fec, orc, tbs, Qm, nbits, sigma, ntb, seed, max_its=8):
     for ot in ots:
         orc.orc_tb_free(ot)
     return stats
+
+
+def test_harq_at_demodulator_llr_scale(fec, orc):
+    """the same HARQ flow with LLRs at the scale of the reference's 64QAM demodulator (max|LLR| ~ 800, doubled by soft
+    combining): code blocks leave the a-priori range of the packed kernel and run in its certificate variant — launched by
+    the host when the hand-over counts come back (first call) and right behind the first kernel afterwards — or in the exact
+    kernel; every transmission is still bit-exact against the oracle"""
+    st = _run_harq(fec, orc, 75376, 6, 86400, 0.48, ntb=8, seed=5, amp=250.0)
+    assert st["rounds"] >= 2 and st["acked"] >= 1, st
+    assert st["trk"] > 0, st
+    st2 = _run_harq(fec, orc, 6200, 6, 14400, 0.7, ntb=24, seed=6, amp=250.0)
+    assert st2["trk"] > 0, st2
 
 
 def test_config3_harq_retransmissions_tm4_shape(fec, orc):

@@ -1,5 +1,5 @@
 import json, sys
-j = json.load(open(sys.argv[1] if len(sys.argv) > 1 else "/root/repo/gpurun_out/bench.json"))
+j = json.loads([l for l in open(sys.argv[1] if len(sys.argv) > 1 else "/root/repo/gpurun_out/bench.json").read().splitlines() if l.startswith("{")][-1])
 r = j["roofline"]
 print("value %.2f Gbps  step %.3f ms | serial phases rm %.3f dec %.3f asm %.3f | frac %.3f | e2e %.2f Gbps (%.2f ms) | worst %s" % (
     j["value"], j["ms_per_step"], r["phases_ms"]["rate_dematch"], r["phases_ms"]["turbo_decode"], r["phases_ms"]["tb_assemble_crc24a"],
