@@ -35,7 +35,7 @@ METRIC = "decoded DL-SCH Gbps & code blocks/s per B200 (20MHz MCS28, 8 it)"
 UNIT = "Gbit/s"
 
 
-NCU_DRAM_BYTES_PER_CB = 41790          # measured, see roofline.traffic_source
+NCU_DRAM_BYTES_PER_CB = 42534          # measured, see roofline.traffic_source
 
 
 def ops_per_halfit(K, P):
@@ -455,9 +455,14 @@ def main():
     hbm_bytes = B * C_CB * algorithmic_bytes_per_cb(K_CB, NBITS // C_CB)
     roof = dict(bound="alu_int16", kernel="fec_tdec_pk_kernel<16,true>", achieved=achieved, peak=peak_nom, unit="Tops/s",
                 frac=achieved / peak_nom, frac_at_sustained_clock=achieved / peak_run, peak_source=peak_src + f" @ {pk['sm_max_mhz']:.0f} MHz",
-                traffic=NCU_DRAM_BYTES_PER_CB * B * C_CB, traffic_source="ncu --set full of one 7696-CB launch (profiles/r1e_map_kernel_ncu.txt): "
-                "dram__bytes_read.sum + dram__bytes_write.sum = 321.6 MB = 41.8 KB per code block, scaled to this launch",
+                traffic=NCU_DRAM_BYTES_PER_CB * B * C_CB, traffic_source="ncu --set full of one 7696-CB launch (profiles/r1f_map_kernel_ncu.txt): "
+                "dram__bytes_read.sum + dram__bytes_write.sum = 327.3 MB = 42.5 KB per code block, scaled to this launch",
                 ops_per_launch=ops, ms_per_launch=dec_ms,
+                # the packed add / add-max instructions only exist on the ALU pipe (half rate: 64 lanes/clk/SM); the peak above also
+                # counts the FMA pipe (IMAD), which this instruction mix cannot use. Against the ALU pipe alone:
+                alu_pipe_only=dict(peak=peak_nom * 64.0 / 124.3, frac=achieved / (peak_nom * 64.0 / 124.3),
+                                   ncu="profiles/r1f_map_kernel_ncu.txt: issue slots 46.6 % busy, 47 % of stall samples issuing + 24 % the second "
+                                       "cycle of a half-rate instruction = 70 % ALU-pipe occupancy; rest: 8 % global loads, 7 % final barrier (ragged tail)"),
                 share_of_step=dec_ms / (rm_ms + dec_ms + asm_ms), serial_step_ms=rm_ms + dec_ms + asm_ms,
                 phases_ms=dict(rate_dematch=rm_ms, turbo_decode=dec_ms, tb_assemble_crc24a=asm_ms),
                 hbm=dict(bound="hbm", algorithmic_bytes_per_step=hbm_bytes, achieved=hbm_bytes / (ms / args.steps / 1e3) / 1e9,
