@@ -509,6 +509,13 @@ __device__ __forceinline__ void fec_softmax_commit(uint32_t *dst, int amax)
  * The slot is then produced 16 bytes per thread: the per-K rank table (device offset -> p) turns the sub-block
  * de-interleaving into a gather from shared memory, added to the old content for a retransmission, and written
  * coalesced together with max |entry|. HBM traffic = the algorithmic minimum (2E bytes in, the slot out / in+out). */
+__device__ __forceinline__ uint32_t rm_lds_u16(uint32_t addr)
+{
+  uint32_t r;
+  asm volatile("ld.shared.u16 %0, [%1];" : "=r"(r) : "r"(addr));
+  return r;
+}
+
 __global__ void __launch_bounds__(FEC_RM_THREADS) fec_rm_rx_kernel(const FecRmDesc *descs, uint32_t *soft_max)
 {
   extern __shared__ __align__(16) int16_t rm_tile[];
@@ -572,29 +579,44 @@ __global__ void __launch_bounds__(FEC_RM_THREADS) fec_rm_rx_kernel(const FecRmDe
       rm_tile[p] = (int16_t)acc;
     }
   }
+  if (tid == 0) rm_tile[d.N] = 0;                      /* the entry the table's "no coded bit here" offsets point at */
   __syncthreads();
+  /* the rank table holds byte offsets into the tile: per soft value one 16-bit shared-memory load, per pair one PRMT, one
+   * packed wrapping add (rm_turbo.c:411-420 adds int16 with wrap-around) when combining, and a packed min / max for max|soft| */
   const uint4 *rank4 = reinterpret_cast<const uint4 *>(d.rank);
   uint4 *soft4 = reinterpret_cast<uint4 *>(d.soft);
-  int amax = 0;
+  const uint32_t tb = (uint32_t)__cvta_generic_to_shared(rm_tile);
+  uint32_t mx = 0, mn = 0;
+  if (d.new_data) {
 #pragma unroll 2
-  for (int v = tid; v < (int)d.n_out / 8; v += FEC_RM_THREADS) {
-    const uint4 rk = __ldg(rank4 + v);
-    uint4 old = make_uint4(0, 0, 0, 0);
-    if (!d.new_data) old = soft4[v];
-    const uint32_t rw[4] = {rk.x, rk.y, rk.z, rk.w};
-    uint32_t ow[4] = {old.x, old.y, old.z, old.w};
+    for (int v = tid; v < (int)d.n_out / 8; v += FEC_RM_THREADS) {
+      const uint4 rk = __ldg(rank4 + v);
+      const uint32_t rw[4] = {rk.x, rk.y, rk.z, rk.w};
+      uint32_t ow[4];
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
-      const uint32_t r0 = rw[k] & 0xFFFFu, r1 = rw[k] >> 16;
-      const int a0 = (int)(short)(ow[k] & 0xFFFFu) + (r0 != 0xFFFFu ? (int)rm_tile[r0] : 0);
-      const int a1 = ((int)ow[k] >> 16) + (r1 != 0xFFFFu ? (int)rm_tile[r1] : 0);
-      const int s0 = (int)(short)a0, s1 = (int)(short)a1;                    /* wrapping int16 (rm_turbo.c:411-420) */
-      ow[k] = ((uint32_t)s0 & 0xFFFFu) | ((uint32_t)s1 << 16);
-      amax = max(amax, max(s0 < 0 ? -s0 : s0, s1 < 0 ? -s1 : s1));
+      for (int k = 0; k < 4; k++) {
+        ow[k] = __byte_perm(rm_lds_u16(tb + (rw[k] & 0xFFFFu)), rm_lds_u16(tb + (rw[k] >> 16)), 0x5410);
+        mx = __vmaxs2(mx, ow[k]); mn = __vmins2(mn, ow[k]);
+      }
+      soft4[v] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
     }
-    soft4[v] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+  } else {
+#pragma unroll 2
+    for (int v = tid; v < (int)d.n_out / 8; v += FEC_RM_THREADS) {
+      const uint4 rk = __ldg(rank4 + v);
+      const uint4 old = soft4[v];
+      const uint32_t rw[4] = {rk.x, rk.y, rk.z, rk.w};
+      uint32_t ow[4] = {old.x, old.y, old.z, old.w};
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        ow[k] = __vadd2(ow[k], __byte_perm(rm_lds_u16(tb + (rw[k] & 0xFFFFu)), rm_lds_u16(tb + (rw[k] >> 16)), 0x5410));
+        mx = __vmaxs2(mx, ow[k]); mn = __vmins2(mn, ow[k]);
+      }
+      soft4[v] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+    }
   }
-  fec_softmax_commit(soft_max + d.slot, amax);
+  const int hi = max((int)(short)(mx & 0xFFFFu), (int)(short)(mx >> 16)), lo = min((int)(short)(mn & 0xFFFFu), (int)(short)(mn >> 16));
+  fec_softmax_commit(soft_max + d.slot, max(hi, -lo));
 }
 
 cudaError_t fec_launch_rm(const FecRmDesc *descs, uint32_t *soft_max, uint32_t n, uint32_t max_n_out, cudaStream_t st)

@@ -59,7 +59,7 @@ struct FecDecodeArgs {
 struct FecRmDesc {
   const int16_t  *e;        /* E transmitted LLRs of this CB */
   int16_t        *soft;     /* device-layout slot, read-modify-write */
-  const uint16_t *rank;     /* per-K table in device layout: soft offset -> entry of the NULL-free circular buffer (0xFFFF: none) */
+  const uint16_t *rank;     /* per-K table in device layout: soft offset -> 2 x entry of the NULL-free circular buffer (byte offset into the tile; 2N: none) */
   uint32_t        E;
   uint32_t        N;        /* 3K+12 */
   uint32_t        off;      /* start rank for this rv */

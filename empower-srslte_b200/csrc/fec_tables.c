@@ -141,7 +141,9 @@ void fec_gen_rm_rank(const fec_geom_t *g, uint16_t *rank, uint32_t off[4])
   const int D = g->K + 4, R = (D - 1) / 32 + 1, KP = 32 * R, ND = KP - D, NCB = 3 * KP;
   int k0[4];
   for (int rv = 0; rv < 4; rv++) k0[rv] = R * (2 * (int)ceilf((float)NCB / (float)(8 * R)) * rv + 2);
-  memset(rank, 0xFF, sizeof(uint16_t) * (size_t)(3 * g->SS + 16));
+  /* entries are BYTE offsets into the rate de-matcher's shared-memory tile (2 * position); device offsets no coded bit maps
+   * to (lane padding) point at tile entry N = 3K + 12, which the kernel keeps at zero */
+  for (int i = 0; i < 3 * g->SS + 16; i++) rank[i] = (uint16_t)(2 * (3 * g->K + 12));
   int cnt = 0;
   for (int w = 0; w < NCB; w++) {
     for (int rv = 0; rv < 4; rv++) if (w == k0[rv]) off[rv] = (uint32_t)cnt;
@@ -150,7 +152,7 @@ void fec_gen_rm_rank(const fec_geom_t *g, uint16_t *rank, uint32_t off[4])
     else if (((w - KP) & 1) == 0) { m = (w - KP) / 2; stream = 1; y = (m % R) * 32 + rm_colperm[m / R]; }
     else { m = (w - KP) / 2; stream = 2; y = (rm_colperm[m / R] + 32 * (m % R) + 1) % KP; }
     if (y < ND) continue;
-    rank[fec_soft_offset_dev(g, 3 * (y - ND) + stream)] = (uint16_t)cnt++;
+    rank[fec_soft_offset_dev(g, 3 * (y - ND) + stream)] = (uint16_t)(2 * cnt++);
   }
 }
 

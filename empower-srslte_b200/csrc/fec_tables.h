@@ -53,7 +53,7 @@ void fec_gen_pair_addr_table(const fec_geom_t *g, uint32_t *tab);
  * pair j, step k at uint2 index ((k>>1)*(P/2) + j)*2 + (k&1) (two steps = one 16-byte load, P/2 threads = one line),
  * with R = x^(K-1-nat+24) mod g(x) of the natural position decided at that step; crc_sel picks the polynomial */
 void fec_gen_pair_crc_table(const fec_geom_t *g, uint32_t poly, uint32_t *tab);
-/* rate-matching rank table in device soft-buffer layout (3*SS+16 entries, pad = 0xFFFF) and the 4 rv
+/* rate-matching rank table in device soft-buffer layout (3*SS+16 entries of 2 x rank, pad = 2 x (3K+12)) and the 4 rv
  * start ranks: transmitted index of soft position o for rv is (rank[o] - off[rv]) mod (3K+12). */
 void fec_gen_rm_rank(const fec_geom_t *g, uint16_t *rank, uint32_t off[4]);
 /* natural coded position t (0..3K+11) -> device soft-buffer offset, and -> reference soft-buffer offset */
