@@ -509,6 +509,10 @@ __device__ __forceinline__ void fec_softmax_commit(uint32_t *dst, int amax)
  * The slot is then produced 16 bytes per thread: the per-K rank table (device offset -> p) turns the sub-block
  * de-interleaving into a gather from shared memory, added to the old content for a retransmission, and written
  * coalesced together with max |entry|. HBM traffic = the algorithmic minimum (2E bytes in, the slot out / in+out). */
+#ifndef RM_UNROLL
+#define RM_UNROLL 2
+#endif
+constexpr int kRmUnroll = RM_UNROLL;
 __device__ __forceinline__ uint32_t rm_lds_u16(uint32_t addr)
 {
   uint32_t r;
@@ -588,7 +592,7 @@ __global__ void __launch_bounds__(FEC_RM_THREADS) fec_rm_rx_kernel(const FecRmDe
   const uint32_t tb = (uint32_t)__cvta_generic_to_shared(rm_tile);
   uint32_t mx = 0, mn = 0;
   if (d.new_data) {
-#pragma unroll 2
+#pragma unroll kRmUnroll
     for (int v = tid; v < (int)d.n_out / 8; v += FEC_RM_THREADS) {
       const uint4 rk = __ldg(rank4 + v);
       const uint32_t rw[4] = {rk.x, rk.y, rk.z, rk.w};
