@@ -199,6 +199,8 @@ def main():
     ap.add_argument("--sigma", type=float, default=0.45, help="AWGN std of the synthetic LLRs (0.45 = operating point)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-worst-case", action="store_true")
+    ap.add_argument("--no-uplink", action="store_true", help="skip the PUSCH leg of the symbol front end")
+    ap.add_argument("--sigma-ul", type=float, default=0.17, help="AWGN std per real dimension of the synthetic 16QAM PUSCH symbols")
     ap.add_argument("--no-tx", action="store_true", help="skip the transmit-side leg (turbo encoder + rate matching on the device)")
     ap.add_argument("--no-symbols", action="store_true", help="skip the leg that starts from equalised symbols (front end)")
     ap.add_argument("--sigma-sym", type=float, default=0.062, help="AWGN std per real dimension of the synthetic 64QAM symbols")
@@ -389,6 +391,61 @@ def main():
                      serial_phases_ms=dict(frontend=fe_ms, rate_dematch=ph_s[0], turbo_decode=ph_s[1], tb_assemble_crc24a=ph_s[2]),
                      frontend_kernel=dict(ms_per_launch=fe_ms, algorithmic_bytes=fe_bytes, achieved=fe_bytes / (fe_ms / 1e3) / 1e9,
                                           peak=peaks()["hbm_gbs"], unit="GB/s", frac=fe_bytes / (fe_ms / 1e3) / 1e9 / peaks()["hbm_gbs"], bound="hbm"))
+        # ---- uplink leg (BASELINE configs[4] shape per cell-subframe): PUSCH from the demodulator on — 16QAM (what
+        #      srsENB grants, phch_worker.cc:598-601), 96 PRB, TBS 36696 = 6 x K=6144, HARQ-ACK / RI / CQI multiplexed: soft
+        #      demodulation, ACK zeroing, descrambling, channel de-interleaver with RI removal, then decode_tb on g_bits ----
+        if not args.no_uplink:
+            ACK_COLS, RI_COLS, uci_positions = synth.ACK_COLS, synth.RI_COLS, synth.uci_positions
+            U_TBS, U_MOD, U_PRB, U_COLS, U_CQI = 36696, 4, 96, 12, 32
+            u_rows, u_nre = 12 * U_PRB, 12 * U_PRB * U_COLS
+            ack_pos = np.array(uci_positions(8, U_MOD, u_rows, ACK_COLS), np.uint32)
+            ri_pos = np.array(uci_positions(4, U_MOD, u_rows, RI_COLS), np.uint32)
+            U_G = u_nre * U_MOD - ri_pos.size - U_CQI
+            u_ncw = 16
+            u_pay = np.random.default_rng(7000 + rank).integers(0, 256, (u_ncw, U_TBS // 8), dtype=np.uint8)
+            u_e = synth.encode_tbs(u_pay, U_TBS, U_MOD, 0, U_G)
+            u_cq = rng.integers(0, 2, (u_ncw, U_CQI)).astype(u_e.dtype)
+            u_q = synth.ulsch_interleave(np.concatenate([u_cq, u_e], axis=1), U_MOD, U_COLS, list(ri_pos))
+            u_ci = [synth.cinit_pusch(0x46 + k, 2 * (k % 10), 1 + k % 64) for k in range(u_ncw)]
+            u_clean = np.stack([synth.modulate(u_q[k] ^ synth.gold_sequence(u_ci[k], u_nre * U_MOD), U_MOD) for k in range(u_ncw)])
+            hu_sym = pkg.PinnedArray((B, u_nre, 2), np.float32)
+            for i0 in range(0, B, 64):
+                i1 = min(B, i0 + 64)
+                hu_sym.a[i0:i1] = synth.awgn_symbols(u_clean[np.arange(i0, i1) % u_ncw], args.sigma_ul, rng)
+            du_sym = torch.from_numpy(hu_sym.a).to(f"cuda:{local_rank}")
+            n_uci = ack_pos.size + ri_pos.size + U_CQI
+            du_uci = torch.zeros((2, B, (n_uci + 7) & ~7), dtype=torch.int16, device=f"cuda:{local_rank}")
+            u_tb, u_sy = [], []
+            for s_ in range(2):
+                t_ = (pkg.TbDesc * B)()
+                y_ = (pkg.SymDesc * B)()
+                for i in range(B):
+                    t_[i].tbs, t_[i].Qm, t_[i].rv, t_[i].nof_e_bits, t_[i].max_its = U_TBS, U_MOD, 0, U_G, 8
+                    t_[i].softbuffer, t_[i].new_data = sb0 + s_ * B + i, 1
+                    t_[i].data = d_out[s_].data_ptr() + i * DATA_STRIDE
+                    y_[i].symbols, y_[i].nof_re, y_[i].mod_bits, y_[i].c_init = du_sym.data_ptr() + i * u_nre * 8, u_nre, U_MOD, u_ci[i % u_ncw]
+                    y_[i].nof_symb = U_COLS
+                    y_[i].ack_pos, y_[i].ri_pos, y_[i].nof_ack_pos, y_[i].nof_ri_pos = ack_pos.ctypes.data, ri_pos.ctypes.data, ack_pos.size, ri_pos.size
+                    y_[i].nof_cqi_bits = U_CQI
+                    y_[i].uci_out = du_uci[s_, i].data_ptr()
+                u_tb.append(t_); u_sy.append(y_)
+            for i in range(6):
+                fec.decode_syms(u_tb[i & 1], u_sy[i & 1], pkg.F_DEVICE_IO)
+            ms_ul = timed_syms(u_tb, u_sy, pkg.F_DEVICE_IO, args.steps)
+            ok_u, its_u = tally(u_tb[0])
+            out_host = d_out[0].cpu().numpy()
+            bad = sum(1 for i in range(B) if u_tb[0][i].ret == 0 and not (out_host[i, :U_TBS // 8] == u_pay[i % u_ncw]).all())
+            if bad:
+                raise SystemExit(f"bench.py: {bad} CRC-passing transport blocks of the uplink leg differ from the transmitted payload")
+            fec.decode_syms(u_tb[0], u_sy[0], pkg.F_DEVICE_IO | pkg.F_SERIAL)
+            U_C = 6
+            front["uplink"] = dict(workload="PUSCH 16QAM 96 PRB, TBS 36696 (6 x K=6144), 32 HARQ-ACK + 16 RI positions + 32 CQI bits multiplexed; "
+                                            "symbols in, device-resident", sigma_sym=args.sigma_ul,
+                                   value=allsum(ok_u) * U_TBS * args.steps / (ms_ul / 1e3) / 1e9, unit=UNIT, ms_per_step=ms_ul / args.steps,
+                                   tb_ok_frac=allsum(ok_u) / (world * B), halfits_per_cb=allsum(its_u) / (world * B * U_C),
+                                   cbs_per_s=world * B * U_C * args.steps / (ms_ul / 1e3),
+                                   serial_phases_ms=dict(zip(("rate_dematch", "turbo_decode", "tb_assemble_crc24a"), fec.last_phase_ms()),
+                                                         frontend=fec.last_frontend_ms()))
         # the LLR legs below reuse dd / hd: put the soft buffers back into the state of the LLR workload
         fec.decode_tbs(dd, pkg.F_DEVICE_IO)
 

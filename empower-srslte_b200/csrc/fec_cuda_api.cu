@@ -422,7 +422,7 @@ static int fe_check(const fec_cuda_tb_t *t, const fec_cuda_sym_t *sy)
     return t->tbs == 0 || t->nof_e_bits == nb;
   }
   /* UL: pusch.c:617-657 */
-  if (sy->csi || mod == 1 || sy->nof_re % sy->nof_symb) return 0;
+  if (sy->csi || mod == 1 || sy->nof_re % sy->nof_symb || sy->nof_symb > 14) return 0;      /* 12 / 10 columns (normal / extended CP), one less with SRS */
   if ((sy->nof_ack_pos && !sy->ack_pos) || (sy->nof_ri_pos && !sy->ri_pos)) return 0;
   if ((sy->nof_ack_pos || sy->nof_ri_pos || sy->nof_cqi_bits) && !sy->uci_out) return 0;
   for (uint32_t i = 0; i < sy->nof_ack_pos; i++) if (sy->ack_pos[i] >= nb) return 0;

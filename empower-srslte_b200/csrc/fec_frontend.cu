@@ -182,93 +182,105 @@ __global__ void __launch_bounds__(FE_THREADS) fec_fe_csimax_kernel(const FecFeDe
   }
 }
 
-/* ---- UL tile: per-bit handling of the control positions, LLRs scattered straight to their de-interleaved places ---- */
+/* ---- UL tile: the channel de-interleaver is a transpose (q is column-major: symbol c*rows + r; g is row-major:
+ * (r*cols + c)*Qm + k, sch.c:550-568), so a CTA takes FE_SEG/cols ROWS of all columns: per column a run of consecutive
+ * symbols is read (coalesced), the LLRs go through a shared-memory tile in g order and leave as 16-byte stores. The few
+ * bits at and behind the first HARQ-ACK / RI position (they sit in the bottom rows) take the per-bit path: ACK zeroing
+ * (sch.c:913-916), RI removal (binary search in the ascending position lists), scattered 2-byte stores. ---- */
+#define FE_UL_MAXCOLS 14   /* columns of the channel interleaver: 12 / 10 (normal / extended CP), one less with SRS; bound for the shared-memory run table */
+#define FE_UL_RT 170       /* rows per tile at most: 255 + 6 * 170 bits fit FE_UL_RUNW words */
+#define FE_UL_RUNW 40      /* scrambling words per column run: 255 + 6*FE_SEG/cols bits at most for cols >= 9 ... see fe_tile_ul */
 template <int MOD>
-__device__ __forceinline__ void fe_tile_ul(const FecFeDesc &d, uint32_t s0, const uint32_t *x2_masks,
-                                           const uint32_t *x1_states, const FeConst &kc, uint32_t *cw)
+__device__ __forceinline__ void fe_tile_ul(const FecFeDesc &d, uint32_t tile_idx, const uint32_t *x2_masks,
+                                           const uint32_t *x1_states, const FeConst &kc, uint32_t *cw, int16_t *tile)
 {
   constexpr uint32_t mod = MOD;
-  const uint32_t nsym = min((uint32_t)FE_SEG, d.nof_re - s0);
-  const uint32_t nbits = nsym * mod, p0 = s0 * mod;
+  const uint32_t cols = d.cols, rows = d.rows;
+  const uint32_t rt = min((uint32_t)FE_SEG / cols, (uint32_t)FE_UL_RT), r0 = tile_idx * rt;
+  const uint32_t nr = min(rt, rows - r0), nsym = nr * cols;
+  const uint32_t total_bits = d.nof_re * mod;
 
-  /* ---- scrambling bits of this tile: bit b of cw[w] = c(p0 + 32 w + b) ---- */
-  {
-    const uint32_t nblk = (nbits + FE_BLK_BITS - 1) / FE_BLK_BITS;
-    if (threadIdx.x < nblk) {
+  /* ---- scrambling bits of the cols runs of this tile: run c covers q bits [(c*rows + r0)*mod, +nr*mod); word w of the run
+   *      holds c(256*(first block) + 32 w + b) at bit b ---- */
+  const uint32_t run_blks = (255 + nr * mod + FE_BLK_BITS - 1) / FE_BLK_BITS;        /* <= FE_UL_RUNW / 8 */
+  for (uint32_t j = threadIdx.x; j < cols * run_blks; j += FE_THREADS) {
+    const uint32_t c = j / run_blks, i = j - c * run_blks;
+    const uint32_t blk = ((c * rows + r0) * mod) / FE_BLK_BITS + i;
+    if (blk * FE_BLK_BITS < total_bits) {
       uint32_t s1, s2;
-      fe_block_states(x2_masks, x1_states, p0 / FE_BLK_BITS + threadIdx.x, d.c_init, s1, s2);
+      fe_block_states(x2_masks, x1_states, blk, d.c_init, s1, s2);
 #pragma unroll
-      for (int w = 0; w < FE_BLK_BITS / 32; w++) cw[threadIdx.x * (FE_BLK_BITS / 32) + w] = fe_x1_next32(s1) ^ fe_x2_next32(s2);
+      for (int w = 0; w < FE_BLK_BITS / 32; w++) cw[c * FE_UL_RUNW + i * (FE_BLK_BITS / 32) + w] = fe_x1_next32(s1) ^ fe_x2_next32(s2);
+    }
+  }
+  /* first de-interleaved bit index that needs the per-bit path, rounded down to a symbol */
+  uint32_t first = 0xFFFFFFFFu;
+  if (d.nack) first = min(first, d.ack_ord[0]);
+  if (d.nri) first = min(first, d.ri_ord[0]);
+  if (first != 0xFFFFFFFFu) first = (first / mod) * mod;
+  __syncthreads();
+
+  const uint32_t body_end = (mod == 2) ? 16 * ((2 * d.nof_re) / 16) : 4 * (d.nof_re / 4);    /* values (QPSK) / symbols */
+  const uint32_t g0 = r0 * cols * mod;                    /* first g index of this tile */
+  const uint32_t shift = g0 & 7u;                         /* same 16-byte phase in shared memory as in global memory */
+
+  for (uint32_t t = threadIdx.x; t < nsym; t += FE_THREADS) {
+    const uint32_t c = t / nr, lr = t - c * nr, sh = c * rows + r0 + lr;
+    const float2 q = d.sym[sh];
+    int v[6];
+    const bool body = mod == 2 ? 2 * sh < body_end : sh < body_end;
+    const bool body_im = mod == 2 ? 2 * sh + 1 < body_end : body;
+    fe_demod<MOD>(q.x, q.y, body, body_im, kc, v);
+    const uint32_t o0 = ((r0 + lr) * cols + c) * mod;     /* de-interleaved index of bit 0 of this symbol */
+    const uint32_t boff = (((c * rows + r0) * mod) & (FE_BLK_BITS - 1)) + lr * mod;
+    if (o0 + mod <= first) {
+      /* bulk: descramble (psignw with +-1: wrapping negate), into the tile at its g position */
+#pragma unroll
+      for (uint32_t k = 0; k < mod; k++) {
+        const uint32_t b = boff + k;
+        int val = v[k];
+        if ((cw[c * FE_UL_RUNW + (b >> 5)] >> (b & 31)) & 1) val = fe_wrap16(-val);
+        tile[shift + o0 - g0 + k] = (int16_t)val;
+      }
+    } else {
+#pragma unroll
+      for (uint32_t k = 0; k < mod; k++) {
+        bool hit = false, skip = false;
+        int val = v[k];
+        if (d.nack) { fe_lower_bound(d.ack_ord, d.nack, o0 + k, hit); if (hit) val = 0; }
+        uint32_t before = 0;
+        if (d.nri) { before = fe_lower_bound(d.ri_ord, d.nri, o0 + k, hit); skip = hit; }
+        const uint32_t b = boff + k;
+        if ((cw[c * FE_UL_RUNW + (b >> 5)] >> (b & 31)) & 1) val = fe_wrap16(-val);
+        if (!skip) d.e[o0 + k - before] = (int16_t)val;
+      }
     }
   }
   __syncthreads();
-
-  constexpr bool ul = true;
-  const uint32_t body_end = (mod == 2) ? 16 * ((2 * d.nof_re) / 16) : 4 * (d.nof_re / 4);    /* values (QPSK) / symbols */
-
-  for (uint32_t pr = threadIdx.x; 2 * pr < nsym; pr += FE_THREADS) {
-    const uint32_t ls = 2 * pr, s = s0 + ls;                 /* first symbol of the pair (s0 is even) */
-    const bool two = ls + 1 < nsym;
-    float re[2], im[2];
-    if (two) { const float4 q = *reinterpret_cast<const float4 *>(d.sym + s); re[0] = q.x; im[0] = q.y; re[1] = q.z; im[1] = q.w; }
-    else { const float2 q = d.sym[s]; re[0] = q.x; im[0] = q.y; re[1] = im[1] = 0.f; }
-    int v[12];
-#pragma unroll
-    for (int h = 0; h < 2; h++) {
-      const uint32_t sh = s + h;
-      const bool body = mod == 2 ? 2 * sh < body_end : sh < body_end;
-      const bool body_im = mod == 2 ? 2 * sh + 1 < body_end : body;
-      fe_demod<MOD>( re[h], im[h], body, body_im, kc, v + 6 * h);
-    }
-    /* UL: HARQ-ACK positions are zeroed before descrambling (sch.c:913-916); RI positions do not reach g. Per bit, as
-     * ulsch_interleave_gen walks them (sch.c:550-568): o = (row*cols + col)*Qm + k */
-    bool skip[12];
-    uint32_t opos[12];
-#pragma unroll
-    for (int k = 0; k < 12; k++) { skip[k] = false; opos[k] = 0; }
-    if (ul) {
-#pragma unroll
-      for (int h = 0; h < 2; h++) {
-        if (h && !two) break;
-        const uint32_t sh = s + h, col = sh / d.rows, row = sh - col * d.rows, o0 = (row * d.cols + col) * mod;
-        _Pragma("unroll") for (uint32_t k = 0; k < mod; k++) {
-          bool hit = false;
-          if (d.nack) { fe_lower_bound(d.ack_ord, d.nack, o0 + k, hit); if (hit) v[6 * h + k] = 0; }
-          uint32_t before = 0;
-          if (d.nri) { before = fe_lower_bound(d.ri_ord, d.nri, o0 + k, hit); skip[6 * h + k] = hit; }
-          opos[6 * h + k] = o0 + k - before;
-        }
-      }
-    }
-    /* descrambling: psignw with +-1 (wrapping negate) */
-#pragma unroll
-    for (int h = 0; h < 2; h++)
-      _Pragma("unroll") for (uint32_t k = 0; k < mod; k++) {
-        const uint32_t b = (ls + h) * mod + k;
-        if ((cw[b >> 5] >> (b & 31)) & 1) v[6 * h + k] = fe_wrap16(-v[6 * h + k]);
-      }
-    {
-#pragma unroll
-      for (int h = 0; h < 2; h++) {
-        if (h && !two) break;
-        _Pragma("unroll") for (uint32_t k = 0; k < mod; k++) {
-          if (skip[6 * h + k]) continue;
-          int val = v[6 * h + k];
-          if (opos[6 * h + k] == 0 && d.nri) {
-            /* g[0] quirk: every RI position scatters to index 0 after the rightful owner did (sch.c:559, vector.c:119-123);
-             * the last one in q order stays */
-            const uint32_t p = d.last_ri_pos, ps = p / mod;
-            const float2 q = d.sym[ps];
-            int t[6];
-            const bool body = mod == 2 ? 2 * ps < body_end : ps < body_end;
-            const bool body_im = mod == 2 ? 2 * ps + 1 < body_end : body;
-            fe_demod<MOD>( q.x, q.y, body, body_im, kc, t);
-            val = fe_seq_bit(x2_masks, x1_states, d.c_init, p) ? fe_wrap16(-fe_pick<MOD>(t, p - ps * mod)) : fe_pick<MOD>(t, p - ps * mod);
-          }
-          d.e[opos[6 * h + k]] = (int16_t)val;
-        }
-      }
-    }
+  /* ---- the tile leaves in g order: elements [g0, hi) with hi = end of the tile or the first per-bit index ---- */
+  const uint32_t hi = min(g0 + nsym * mod, first);
+  if (hi > g0) {
+    const uint32_t n = hi - g0;
+    const uint32_t head = min(n, (8u - shift) & 7u);      /* int16 until the global address is 16-byte aligned */
+    for (uint32_t i = threadIdx.x; i < head; i += FE_THREADS) d.e[g0 + i] = tile[shift + i];
+    const uint32_t nvec = (n - head) / 8;
+    const uint4 *src = reinterpret_cast<const uint4 *>(tile + shift + head);
+    uint4 *dst = reinterpret_cast<uint4 *>(d.e + g0 + head);
+    for (uint32_t i = threadIdx.x; i < nvec; i += FE_THREADS) dst[i] = src[i];
+    for (uint32_t i = head + 8 * nvec + threadIdx.x; i < n; i += FE_THREADS) d.e[g0 + i] = tile[shift + i];
+  }
+  __syncthreads();
+  if (tile_idx == 0 && d.nri && threadIdx.x == 0) {
+    /* g[0] quirk: every RI position scatters to index 0 after the rightful owner did (sch.c:559, vector.c:119-123); the
+     * last one in q order stays */
+    const uint32_t p = d.last_ri_pos, ps = p / mod;
+    const float2 q = d.sym[ps];
+    int t[6];
+    const bool body = mod == 2 ? 2 * ps < body_end : ps < body_end;
+    const bool body_im = mod == 2 ? 2 * ps + 1 < body_end : body;
+    fe_demod<MOD>(q.x, q.y, body, body_im, kc, t);
+    const int val = fe_seq_bit(x2_masks, x1_states, d.c_init, p) ? fe_wrap16(-fe_pick<MOD>(t, p - ps * mod)) : fe_pick<MOD>(t, p - ps * mod);
+    d.e[0] = (int16_t)val;
   }
 }
 
@@ -418,13 +430,17 @@ __global__ void __launch_bounds__(FE_THREADS)
 fec_fe_ul_kernel(const FecFeDesc *descs, const uint32_t *x2_masks, const uint32_t *x1_states, FeConst kc)
 {
   const FecFeDesc d = descs[blockIdx.y];
-  const uint32_t s0 = blockIdx.x * FE_SEG;
-  if (!d.cols || s0 >= d.nof_re) return;
-  __shared__ uint32_t cw[FE_SEG * 6 / 32];
-  switch (d.mod) {
-  case 6: fe_tile_ul<6>(d, s0, x2_masks, x1_states, kc, cw); break;
-  case 4: fe_tile_ul<4>(d, s0, x2_masks, x1_states, kc, cw); break;
-  default: fe_tile_ul<2>(d, s0, x2_masks, x1_states, kc, cw); break;
+  if (!d.cols) return;
+  __shared__ uint32_t cw[FE_UL_MAXCOLS * FE_UL_RUNW];
+  __shared__ __align__(16) int16_t tile[FE_SEG * 6 + 8];
+  const uint32_t rt = min((uint32_t)FE_SEG / d.cols, (uint32_t)FE_UL_RT);
+  for (uint32_t t = blockIdx.x; t * rt < d.rows; t += gridDim.x) {        /* grid-stride: any cols / rows combination is covered */
+    switch (d.mod) {
+    case 6: fe_tile_ul<6>(d, t, x2_masks, x1_states, kc, cw, tile); break;
+    case 4: fe_tile_ul<4>(d, t, x2_masks, x1_states, kc, cw, tile); break;
+    default: fe_tile_ul<2>(d, t, x2_masks, x1_states, kc, cw, tile); break;
+    }
+    __syncthreads();
   }
 }
 
@@ -466,7 +482,9 @@ cudaError_t fec_launch_frontend(const FecFeDesc *descs, float *csi_max, const ui
   if (any_csi) fec_fe_csimax_kernel<<<ntb, FE_THREADS, 0, st>>>(descs, csi_max);
   dim3 grid((max_re + FE_SEG - 1) / FE_SEG, ntb);
   if (kinds & 1) fec_fe_dl_kernel<<<grid, FE_THREADS, 0, st>>>(descs, csi_max, x2_masks, x1_states, kc);
-  if (kinds & 2) fec_fe_ul_kernel<<<grid, FE_THREADS, 0, st>>>(descs, x2_masks, x1_states, kc);
+  /* UL tiles are FE_SEG / cols whole rows: up to one tile more than nof_re / FE_SEG (cols does not divide FE_SEG) */
+  dim3 grid_ul(grid.x + 1, ntb);
+  if (kinds & 2) fec_fe_ul_kernel<<<grid_ul, FE_THREADS, 0, st>>>(descs, x2_masks, x1_states, kc);
   if (any_uci) fec_fe_uci_kernel<<<ntb, FE_THREADS, 0, st>>>(descs, kc);
   return cudaGetLastError();
 }

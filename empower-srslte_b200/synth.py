@@ -285,3 +285,17 @@ def awgn_symbols(sym, sigma, rng):
     out[..., 0] = sym.real + sigma * rng.standard_normal(sym.shape)
     out[..., 1] = sym.imag + sigma * rng.standard_normal(sym.shape)
     return out
+
+
+ACK_COLS = (2, 3, 8, 9)          # HARQ-ACK / RI columns of the channel interleaver, normal CP (uci.c:499-546)
+RI_COLS = (1, 4, 7, 10)
+
+
+def uci_positions(n_sym_uci, mod, rows, cols_set):
+    """q-bit positions of n_sym_uci control symbols: rows from the bottom, columns in the (3*i)%4 visiting order
+    (uci.c:499-546: HARQ-ACK {2,3,8,9}, RI {1,4,7,10}, normal CP)"""
+    pos = []
+    for i in range(n_sym_uci):
+        row, col = rows - 1 - i // 4, cols_set[(3 * i) % 4]
+        pos += [row * mod + rows * col * mod + k for k in range(mod)]
+    return pos

@@ -9,18 +9,7 @@ from _libs import P, aligned
 synth = importlib.import_module("empower-srslte_b200.synth")
 
 
-def uci_positions(n_sym_uci, mod, rows, cols_set):
-    """q-bit positions of n_sym_uci control symbols: rows from the bottom, columns in the (3*i)%4 visiting order
-    (uci.c:499-546: HARQ-ACK {2,3,8,9}, RI {1,4,7,10}, normal CP)"""
-    pos = []
-    for i in range(n_sym_uci):
-        row, col = rows - 1 - i // 4, cols_set[(3 * i) % 4]
-        pos += [row * mod + rows * col * mod + k for k in range(mod)]
-    return pos
-
-
-ACK_COLS = (2, 3, 8, 9)
-RI_COLS = (1, 4, 7, 10)
+uci_positions, ACK_COLS, RI_COLS = synth.uci_positions, synth.ACK_COLS, synth.RI_COLS
 
 
 def oracle_frontend(orc, sym, mod, c_init, csi=None, nof_symb=0, ack_pos=(), ri_pos=()):
