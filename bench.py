@@ -438,12 +438,14 @@ def main():
             if bad:
                 raise SystemExit(f"bench.py: {bad} CRC-passing transport blocks of the uplink leg differ from the transmitted payload")
             fec.decode_syms(u_tb[0], u_sy[0], pkg.F_DEVICE_IO | pkg.F_SERIAL)
+            path_u = fec.last_path_counts()
             U_C = 6
             front["uplink"] = dict(workload="PUSCH 16QAM 96 PRB, TBS 36696 (6 x K=6144), 32 HARQ-ACK + 16 RI positions + 32 CQI bits multiplexed; "
                                             "symbols in, device-resident", sigma_sym=args.sigma_ul,
                                    value=allsum(ok_u) * U_TBS * args.steps / (ms_ul / 1e3) / 1e9, unit=UNIT, ms_per_step=ms_ul / args.steps,
                                    tb_ok_frac=allsum(ok_u) / (world * B), halfits_per_cb=allsum(its_u) / (world * B * U_C),
                                    cbs_per_s=world * B * U_C * args.steps / (ms_ul / 1e3),
+                                   code_blocks_by_kernel=dict(total=B * U_C, certificate_variant=path_u[0], exact=path_u[1]),
                                    serial_phases_ms=dict(zip(("rate_dematch", "turbo_decode", "tb_assemble_crc24a"), fec.last_phase_ms()),
                                                          frontend=fec.last_frontend_ms()))
         # the LLR legs below reuse dd / hd: put the soft buffers back into the state of the LLR workload

@@ -15,8 +15,8 @@ if f:
         print("symbols serial phases:", {k: round(v, 3) for k, v in f["serial_phases_ms"].items()})
 u = (f or {}).get("uplink")
 if u:
-    print("uplink: value %.2f Gbps step %.3f ms ok %.2f its %.2f | phases %s" % (u["value"], u["ms_per_step"], u["tb_ok_frac"], u["halfits_per_cb"],
-          {k: round(v, 3) for k, v in u["serial_phases_ms"].items()}))
+    print("uplink: value %.2f Gbps step %.3f ms ok %.2f its %.2f | phases %s | kernels %s" % (u["value"], u["ms_per_step"], u["tb_ok_frac"], u["halfits_per_cb"],
+          {k: round(v, 3) for k, v in u["serial_phases_ms"].items()}, u.get("code_blocks_by_kernel")))
 t = j.get("transmit_side")
 if t:
     print("transmit side: %.1f Gbit/s, %.3f ms per step, %.2f M code blocks/s" % (t["value"], t["ms_per_step"], t["cbs_per_s"] / 1e6))
