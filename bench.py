@@ -483,6 +483,21 @@ def main():
                   value=world * B * TBS * args.steps / (ms_tx / 1e3) / 1e9, unit="Gbit/s of transport-block bits", ms_per_step=ms_tx / args.steps,
                   cbs_per_s=world * B * C_CB * args.steps / (ms_tx / 1e3), checked="first 2 transport blocks bit-exact vs the numpy synthesiser (itself pinned to srslte_dlsch_encode)")
 
+    # ---- latency of the reference's call shape: ONE transport block per blocking call (srslte_dlsch_decode as pdsch.c:816
+    #      makes it, level 2 of INTEGRATION.md), host buffers, everything inside the timed call ----
+    lat = None
+    if rank == 0:
+        one = (pkg.TbDesc * 1)()
+        ts = []
+        for i in range(64):
+            fill_descs(pkg, one, 1, h_llr.a.ctypes.data + (i % B) * NBITS * 2, h_out.a.ctypes.data, sb0)
+            t0 = time.perf_counter()
+            fec.decode_tbs(one, 0)
+            ts.append((time.perf_counter() - t0) * 1e6)
+        ts = sorted(ts[8:])
+        lat = dict(call="fec_cuda_decode_tbs(n=1), 13 code blocks, host LLRs in, payload out", median_us=ts[len(ts) // 2], p90_us=ts[int(len(ts) * 0.9)],
+                   min_us=ts[0])
+
     # ---- worst case: all 8 half-iterations for every code block (no early stop), same inputs ----
     worst = None
     if not args.no_worst_case:
@@ -548,7 +563,7 @@ def main():
                     e2e=dict(value=e2e_val, unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h, ms_per_step=ms_e / args.steps,
                              sync_ms_per_step=ms_e_sync / args.steps),
                     sync_ms_per_step=ms_sync / args.steps,
-                    gpu_launches=launches, clocks=clocks, roofline=roof, worst_case_8_halfits=worst, frontend_symbols=front, transmit_side=tx, cpu_baseline=cpu)
+                    gpu_launches=launches, clocks=clocks, roofline=roof, worst_case_8_halfits=worst, frontend_symbols=front, transmit_side=tx, single_tb_latency=lat, cpu_baseline=cpu)
         print(json.dumps(line), flush=True)
     fec.close()
     if world > 1:

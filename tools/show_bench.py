@@ -20,3 +20,6 @@ if u:
 t = j.get("transmit_side")
 if t:
     print("transmit side: %.1f Gbit/s, %.3f ms per step, %.2f M code blocks/s" % (t["value"], t["ms_per_step"], t["cbs_per_s"] / 1e6))
+l = j.get("single_tb_latency")
+if l:
+    print("single-TB call latency: median %.0f us, p90 %.0f us, min %.0f us" % (l["median_us"], l["p90_us"], l["min_us"]))
