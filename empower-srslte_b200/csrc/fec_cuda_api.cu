@@ -57,7 +57,8 @@ struct fec_cuda_ctx {
   unsigned int *d_queue;   /* per K: work-queue counters of the packed and the exact kernel (2 x FEC_NOF_K), FEC_NOF_K hand-over counts to the
                               exact kernel, then work-queue counters and hand-over counts of the certificate kernel (FEC_NQUEUE x FEC_NOF_K) */
   uint32_t     *d_softmax; size_t softmax_cap;   /* per code block of the call: max |soft-buffer entry| */
-  uint32_t     *d_exact;   size_t exact_cap;     /* per code block of the call: hand-over list of the packed kernel */
+  uint32_t     *d_exact;   size_t exact_cap;     /* per code block of the call: hand-over lists of the packed kernels + continuation words */
+  uint32_t     *d_econt;   size_t econt_cap;     /* extrinsic arrays of code blocks handed over in mid-decode */
   int           force_exact;
   int16_t      *d_dbg; size_t dbg_cap; uint32_t *dbg_slot; uint32_t dbg_n;   /* test hook: LLR dump */
   float         phase_ms[3];   /* device time of rm | decode | assemble summed over the sub-batches of the last decode_tbs call */
@@ -179,7 +180,7 @@ extern "C" void fec_cuda_destroy(fec_cuda_ctx_t *ctx)
     cudaFree(ctx->ktab[i].d_step); cudaFree(ctx->ktab[i].d_rank); cudaFree(ctx->ktab[i].d_pair_addr); cudaFree(ctx->ktab[i].d_txsrc);
     cudaFree(ctx->ktab[i].d_pair_crc[0]); cudaFree(ctx->ktab[i].d_pair_crc[1]);
   }
-  cudaFree(ctx->d_softmax); cudaFree(ctx->d_exact); cudaFreeHost(ctx->h_queue);
+  cudaFree(ctx->d_softmax); cudaFree(ctx->d_exact); cudaFree(ctx->d_econt); cudaFreeHost(ctx->h_queue);
   for (uint32_t i = 0; i < ctx->nchunks; i++) { cudaFree(ctx->chunks[i].d_soft); cudaFree(ctx->chunks[i].d_cache); free(ctx->chunks[i].cb_crc); }
   free(ctx->chunks);
   stage_free(&ctx->st_e); stage_free(&ctx->st_data); stage_free(&ctx->st_cbd); stage_free(&ctx->st_rmd);
@@ -322,7 +323,7 @@ extern "C" int fec_cuda_softbuffer_read_ref_layout(fec_cuda_ctx_t *ctx, uint32_t
 }
 
 static void fill_decode_args(fec_cuda_ctx_t *ctx, int k, FecDecodeArgs *a, const FecCbDesc *cbd_dev, FecCbStatus *status_dev,
-                             unsigned int *queue3, const uint32_t *softmax, uint32_t *exact, uint32_t *trk, uint32_t off, uint32_t cnt, int16_t *dbg)
+                             unsigned int *queue3, const uint32_t *softmax, uint32_t *exact, uint32_t *trk, uint32_t *econt, uint32_t off, uint32_t cnt, int16_t *dbg)
 {
   const ktab_t *t = &ctx->ktab[k];
   memset(a, 0, sizeof(*a));
@@ -334,6 +335,11 @@ static void fill_decode_args(fec_cuda_ctx_t *ctx, int k, FecDecodeArgs *a, const
   if (t->g.P && !ctx->force_exact && !dbg) {
     a->exact_list = exact + off; a->exact_count = queue3 + 2 * FEC_NOF_K + k;
     a->trk_list = trk + off; a->trk_queue = queue3 + 3 * FEC_NOF_K + k; a->trk_count = queue3 + 4 * FEC_NOF_K + k;
+    /* hand-over in mid-decode: continuation words behind the two lists, extrinsic scratch slots shared by the K groups of the
+     * call in proportion to their size */
+    a->trk_cont = trk + (trk - exact) + off;
+    a->econt = econt ? econt + (size_t)off * FEC_ECONT_WORDS : NULL;
+    a->econt_cap = econt ? cnt : 0;
   }
 }
 
@@ -358,6 +364,7 @@ struct fec_pipe {
   uint8_t      *d_cbbytes; size_t cbbytes_cap;
   uint32_t     *d_softmax; size_t softmax_cap;
   uint32_t     *d_exact;   size_t exact_cap;
+  uint32_t     *d_econt;   size_t econt_cap;
   unsigned int *d_queue, *h_queue;
   struct { int k; uint32_t off, cnt; } *grp; int ngrp, stages;   /* decode launches of this sub-batch and the stages already enqueued */
   cudaEvent_t   ev_in, ev_k, ev_done, ev[4];
@@ -390,7 +397,7 @@ static void pipe_free(fec_pipe_t *p)
   stage_free(&p->st_fed); stage_free(&p->st_lst); stage_free(&p->st_uci);
   cudaFree(p->d_llr); cudaFree(p->d_csimax);
   if (p->ev_fe) cudaEventDestroy(p->ev_fe);
-  cudaFree(p->d_cbbytes); cudaFree(p->d_softmax); cudaFree(p->d_exact); cudaFree(p->d_queue); cudaFreeHost(p->h_queue);
+  cudaFree(p->d_cbbytes); cudaFree(p->d_softmax); cudaFree(p->d_exact); cudaFree(p->d_econt); cudaFree(p->d_queue); cudaFreeHost(p->h_queue);
   if (p->ev_in) { cudaEventDestroy(p->ev_in); cudaEventDestroy(p->ev_k); cudaEventDestroy(p->ev_done); for (int i = 0; i < 4; i++) cudaEventDestroy(p->ev[i]); }
   free(p->plan); free(p->grp);
   memset(p, 0, sizeof(*p));
@@ -521,7 +528,8 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
       stage_reserve(ctx, &pp->st_ret, need[4]) ||
       dev_reserve(ctx, (void **)&pp->d_cbbytes, &pp->cbbytes_cap, need[5]) ||
       dev_reserve(ctx, (void **)&pp->d_softmax, &pp->softmax_cap, need[6]) ||
-      dev_reserve(ctx, (void **)&pp->d_exact, &pp->exact_cap, 2 * need[6]) ||
+      dev_reserve(ctx, (void **)&pp->d_exact, &pp->exact_cap, 3 * need[6]) ||
+      dev_reserve(ctx, (void **)&pp->d_econt, &pp->econt_cap, (size_t)(ncb + 1) * FEC_ECONT_WORDS * 4) ||
       (!dev_io && (stage_reserve(ctx, &pp->st_e, need[7]) || stage_reserve(ctx, &pp->st_data, need[8])))) return FEC_CUDA_ENODEV;
   if (syms && (stage_reserve(ctx, &pp->st_fed, need[9]) || dev_reserve(ctx, (void **)&pp->d_llr, &pp->llr_cap, need[10]) ||
                stage_reserve(ctx, &pp->st_lst, need[11]) || stage_reserve(ctx, &pp->st_uci, need[12]) ||
@@ -691,7 +699,7 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
   for (int k = 0; k < FEC_NOF_K; k++) {
     if (!grp_cnt[k]) continue;
     FecDecodeArgs a;
-    fill_decode_args(ctx, k, &a, (const FecCbDesc *)pp->st_cbd.d, (FecCbStatus *)pp->st_status.d, pp->d_queue, pp->d_softmax, pp->d_exact, pp->d_exact + pp->exact_cap / 8,
+    fill_decode_args(ctx, k, &a, (const FecCbDesc *)pp->st_cbd.d, (FecCbStatus *)pp->st_status.d, pp->d_queue, pp->d_softmax, pp->d_exact, pp->d_exact + pp->exact_cap / 12, pp->d_econt,
                      grp_off[k], grp_cnt[k], NULL);
     CU(fec_launch_decode(a, ctx->sm_count, sc, pp->stages));
     ctx->launches += a.exact_list ? 1 + ((pp->stages & FEC_ST_B) != 0) + ((pp->stages & FEC_ST_C) != 0) : 1;
@@ -739,7 +747,7 @@ static int pipe_finish(fec_cuda_ctx_t *ctx, fec_pipe_t *pp)
         CU(cudaMemsetAsync(pp->d_queue + 2 * FEC_NOF_K + k, 0, sizeof(unsigned int), sc));
         FecDecodeArgs a;
         fill_decode_args(ctx, k, &a, (const FecCbDesc *)pp->st_cbd.d, (FecCbStatus *)pp->st_status.d, pp->d_queue, pp->d_softmax, pp->d_exact,
-                         pp->d_exact + pp->exact_cap / 8, pp->grp[g].off, pp->grp[g].cnt, NULL);
+                         pp->d_exact + pp->exact_cap / 12, pp->d_econt, pp->grp[g].off, pp->grp[g].cnt, NULL);
         CU(fec_launch_decode(a, ctx->sm_count, sc, FEC_ST_B | FEC_ST_C));
         ctx->launches += 2;
       }
@@ -931,7 +939,8 @@ extern "C" int fec_cuda_decode_cbs(fec_cuda_ctx_t *ctx, fec_cuda_cb_t *cbs, uint
       stage_reserve(ctx, &ctx->st_exd, sizeof(FecExtractDesc) * n) || stage_reserve(ctx, &ctx->st_status, sizeof(FecCbStatus) * n) ||
       stage_reserve(ctx, &ctx->st_data, (size_t)n * CB_BYTES) ||
       dev_reserve(ctx, (void **)&ctx->d_softmax, &ctx->softmax_cap, (size_t)(n + 1) * 4) ||
-      dev_reserve(ctx, (void **)&ctx->d_exact, &ctx->exact_cap, (size_t)(n + 1) * 8) ||
+      dev_reserve(ctx, (void **)&ctx->d_exact, &ctx->exact_cap, (size_t)(n + 1) * 12) ||
+      dev_reserve(ctx, (void **)&ctx->d_econt, &ctx->econt_cap, (size_t)(n + 1) * FEC_ECONT_WORDS * 4) ||
       dev_reserve(ctx, (void **)&ctx->d_tmpsoft, &ctx->tmpsoft_cap, (size_t)n * FEC_CUDA_SOFT_SLOT * sizeof(int16_t))) return FEC_CUDA_ENODEV;
   if (ctx->dbg_cap && ctx->dbg_cap < (size_t)n * FEC_MAX_K * 2) { cudaFree(ctx->d_dbg); ctx->d_dbg = NULL; ctx->dbg_cap = 0; }
   FecCbDesc *cbd = (FecCbDesc *)ctx->st_cbd.h;
@@ -965,7 +974,7 @@ extern "C" int fec_cuda_decode_cbs(fec_cuda_ctx_t *ctx, fec_cuda_cb_t *cbs, uint
   for (int k = 0; k < FEC_NOF_K; k++) {
     if (!grp_cnt[k]) continue;
     FecDecodeArgs a;
-    fill_decode_args(ctx, k, &a, (const FecCbDesc *)ctx->st_cbd.d, (FecCbStatus *)ctx->st_status.d, ctx->d_queue, ctx->d_softmax, ctx->d_exact, ctx->d_exact + ctx->exact_cap / 8,
+    fill_decode_args(ctx, k, &a, (const FecCbDesc *)ctx->st_cbd.d, (FecCbStatus *)ctx->st_status.d, ctx->d_queue, ctx->d_softmax, ctx->d_exact, ctx->d_exact + ctx->exact_cap / 12, ctx->d_econt,
                      grp_off[k], grp_cnt[k], DBG_LLR);
     CUF(fec_launch_decode(a, ctx->sm_count, st, FEC_ST_ALL));
     ctx->launches += a.exact_list ? 3 : 1;

@@ -14,6 +14,7 @@
 #define FEC_PK_WARPS      4       /* packed kernel: warps per CTA (= tensor-memory lane quarters) */
 #define FEC_PK_GMAX       2000u   /* packed kernel: largest max|x| + max|y| for which int16 saturation is excluded a priori */
 #define FEC_NQUEUE        5       /* device counters per K: packed queue, exact queue, exact count, certificate queue, certificate count */
+#define FEC_ECONT_WORDS   3200    /* scratch words per handed-over code block: >= (P/2) * Lw + 1 for every K (3105 at K = 6144) */
 #define FEC_PK_GMAX_TRK   4500u   /* ... and the largest for which the run-time range certificate can still hold (10000 + 5G <= 32767) */
 
 /* one code block of a decode launch */
@@ -49,6 +50,9 @@ struct FecDecodeArgs {
   uint32_t         *trk_list;   /* out: code blocks beyond the a-priori range -> certificate variant of the packed kernel */
   unsigned int     *trk_count;
   unsigned int     *trk_queue;  /* work-queue counter of the certificate kernel */
+  uint32_t         *trk_cont;   /* per trk_list entry: 0 = decode from the soft buffer, else half-iterations done | G << 8 and ... */
+  uint32_t         *econt;      /* ... the extrinsic array of the block in scratch slot [entry index] (Es words each) */
+  uint32_t          econt_cap;  /* scratch slots */
   /* exact kernels: optional indirect work list (NULL = all ncb code blocks) */
   const uint32_t   *list;
   const unsigned int *list_count;

@@ -673,6 +673,24 @@ __device__ PK_EPI_INLINE void pk_finish_block(int par, uint32_t Eb, const uint16
     pk_write_output<TPC>(rows, nw1, pad, K, L, j, out);
 }
 
+/* A code block that leaves the a-priori range in mid-decode continues in the certificate kernel where it stands: its state
+ * is the extrinsic array E (shared memory) and the half-iteration count. E goes to a scratch slot indexed like the hand-over
+ * list entry; blocks beyond the scratch capacity restart from their soft buffer (cont = 0). Cold path, kept out of line. */
+template <int TPC>
+__device__ __noinline__ void pk_hand_over(unsigned int *trk_count, uint32_t *trk_list, uint32_t *trk_cont, uint32_t *econt, uint32_t econt_cap,
+                                          uint32_t cb, const uint32_t *Eslot, int Es, uint32_t n1, uint32_t G, int j, int g, unsigned gmask)
+{
+  uint32_t idx = 0;
+  if (j == 0) idx = atomicAdd(trk_count, 1u);
+  idx = __shfl_sync(gmask, idx, g * TPC);
+  if (j == 0) trk_list[idx] = cb;
+  if (n1 && idx < econt_cap) {
+    uint32_t *dst = econt + (size_t)idx * Es;
+    for (int i = j; i < Es; i += TPC) dst[i] = Eslot[i];
+    if (j == 0) trk_cont[idx] = n1 | (G << 8);
+  } else if (j == 0) trk_cont[idx] = 0;
+}
+
 /* ---------------------------------------------------------------- run-time range certificate ---- */
 /* Inputs: packed per-lane extremes of one code block's half-iteration in the reference's frame (TRK schedule):
  * [alo, ahi] alpha states after every normalisation and at the start of the main pass, rb = max(bhi, -blo - 1) for
@@ -753,6 +771,7 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
       if (j == 0) q = atomicAdd(a.queue, 1u);
       q = __shfl_sync(gmask, q, g * TPC);
       if (q >= (TRK ? *a.list_count : a.ncb)) { exhausted = true; break; }
+      const unsigned qi = q;
       if (TRK) q = a.list[q];
 #if PK_OPT_DESC
       {
@@ -772,15 +791,20 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
       }
       if (!TRK && 2 * M + M / 2 > FEC_PK_GMAX) {    /* outside the a-priori range now or (decoder 1: G = 2M + max|extrinsic|) certain to
                                                        leave it with the second iteration: certificate kernel from the start */
-        if (j == 0) a.trk_list[atomicAdd(a.trk_count, 1u)] = q;
+        pk_hand_over<TPC>(a.trk_count, a.trk_list, a.trk_cont, a.econt, a.econt_cap, q, Eslot, Es, 0u, 0u, j, g, gmask);
         continue;
       }
       cb = (int)q; n = 0; G = 2 * M;
-#if PK_LATE_ZERO
       fresh = true;
-#else
-      for (int i = j; i < Es; i += TPC) Eslot[i] = 0;   /* apriori = 0 before the first half-iteration */
-#endif
+      if (TRK) {
+        const uint32_t cont = a.trk_cont[qi];
+        if (cont) {                                   /* handed over in mid-decode: go on from its extrinsics */
+          const uint32_t *src = a.econt + (size_t)qi * Es;
+          for (int i = j; i < Es; i += TPC) Eslot[i] = src[i];
+          n = (int)(cont & 0xFFu); G = cont >> 8;
+          fresh = false;
+        }
+      }
     }
     __syncwarp();
     if (!__any_sync(0xFFFFFFFFu, cb >= 0)) break;
@@ -852,7 +876,7 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
           if (j == 0) a.exact_list[atomicAdd(a.exact_count, 1u)] = (uint32_t)cb;   /* re-decoded from scratch by the exact kernel */
           cb = -1;
         } else if (!TRK && G > FEC_PK_GMAX) {
-          if (j == 0) a.trk_list[atomicAdd(a.trk_count, 1u)] = (uint32_t)cb;       /* ... by the certificate kernel */
+          pk_hand_over<TPC>(a.trk_count, a.trk_list, a.trk_cont, a.econt, a.econt_cap, (uint32_t)cb, Eslot, Es, (uint32_t)n1, G, j, g, gmask);   /* the certificate kernel goes on from here */
           cb = -1;
         } else n = n1;
       }

@@ -137,6 +137,41 @@ def test_tdec_beyond_apriori_range_vs_oracle(fec, orc):
     assert t >= len(idx) // 2 and e <= len(idx) // 4, (t, e, len(idx))
 
 
+def test_tdec_continues_in_certificate_kernel_vs_oracle(fec, orc):
+    """code blocks that START inside the a-priori range of the packed kernel (max|soft| <= 800) and leave it in mid-decode
+    because their extrinsics grow: the certificate kernel goes on from the dumped extrinsic array and half-iteration count
+    instead of restarting. The decisions of every half-iteration count must equal the oracle's, with and without CRC
+    early stop; every hand-over counted here is a mid-decode one (none of these blocks is routed there at refill)."""
+    cases = []
+    for K in (408, 800, 816, 1008, 1056, 2048, 5824, 6144):
+        for amp, sigma, clip in ((160, 1.0, 800), (220, 0.95, 800), (120, 1.05, 640), (250, 0.8, 750)):
+            x = _noisy_codeword(K, amp, sigma, 31 * K + amp)
+            cases.append((K, np.ascontiguousarray(np.clip(x, -clip, clip)), "cw%d_%g" % (amp, sigma)))
+    assert all(int(np.abs(c[1].astype(np.int32)).max()) <= 800 for c in cases)
+    NH = 10
+    want = []
+    for K, inp, _ in cases:
+        ob = np.zeros((NH, K // 8), np.uint8)
+        assert orc.orc_tdec_halfits(K, P(inp), NH, P(ob), None) == 0
+        want.append(ob)
+    tot_trk = 0
+    for nof in (2, 3, 4, 5, 7, 10):
+        res = fec.decode_cbs([c[0] for c in cases], [c[1] for c in cases], nof, early_stop=False)
+        bad = [(c[0], c[2], nof) for c, r, w in zip(cases, res, want) if not (r["out"] == w[nof - 1]).all()]
+        assert not bad, bad
+        t, e = fec.last_path_counts()
+        tot_trk += t
+    assert tot_trk >= len(cases), "no code block was handed over in mid-decode (%d)" % tot_trk
+    exp_its = []
+    for i, (K, _, _) in enumerate(cases):
+        ok = [n + 1 for n in range(NH) if orc.orc_crc(1, P(np.ascontiguousarray(want[i][n])), K) == 0]
+        exp_its.append(ok[0] if ok else NH)
+    res = fec.decode_cbs([c[0] for c in cases], [c[1] for c in cases], NH, crc_type=1, early_stop=True)
+    for c, r, w, n in zip(cases, res, want, exp_its):
+        assert r["its"] == n and (r["out"] == w[n - 1]).all(), (c[0], c[2], r["its"], n)
+    print("mid-decode hand-overs: %d over 6 runs of %d blocks; early-stop half-iterations %s" % (tot_trk, len(cases), exp_its))
+
+
 def test_rm_rx_golden_subset(fec):
     z = G.tables()
     rows = [r for r in z["rm"] if int(r[0]) in (40, 104, 400, 408, 800, 816, 1024, 3136, 5824, 6144)]
