@@ -32,6 +32,16 @@ int orc_subblocks(int K)
   return 0;
 }
 
+/* decoder class of the 8-bit LLR path (turbodecoder.c:392-406, AVX2 build): 32 / 16 sub-blocks run in int8 arithmetic,
+ * 8 / 0 fall back to the 16-bit decoders on widened inputs (turbodecoder.c:408-452) */
+int orc_subblocks8(int K)
+{
+  if (!(K % 32) && K > 2048) return 32;
+  if (!(K % 16) && K > 800) return 16;
+  if (!(K % 8) && K > 400) return 8;
+  return 0;
+}
+
 int orc_cbsegm(uint32_t tbs, uint32_t *o)
 {   /* cbsegm.c:58-108; o = {F,C,K1,K2,K1_idx,K2_idx,C1,C2,tbs} */
   memset(o, 0, 9 * sizeof(uint32_t));
@@ -303,6 +313,94 @@ static void map_windowed(int K, int P, const int16_t *in, const int16_t *app, co
   }
 }
 
+/* ---- 8-bit windowed decoders tdec_win{sse8,avx8}_dec (turbodecoder_win.h:97-178 for the parameter
+ * set): int8 saturating arithmetic, INF = 0 (all start states 0), normalisation after EVERY step k != 0 by the maximum of
+ * the 8 states (normalize_max, normalize_period 1, :244-254), output (m1 - m0) >> 1 per byte (divide_output, :565-567),
+ * tail trellis with the scalar add that saturates upwards only (:236-243). Values are int8 carried in int16. ---- */
+static inline int16_t sat8(int v) { return (int16_t)(v > 127 ? 127 : (v < -128 ? -128 : v)); }
+static inline int16_t adds8(int16_t a, int16_t b) { return sat8((int)a + (int)b); }
+static inline int16_t subs8(int16_t a, int16_t b) { return sat8((int)a - (int)b); }
+static inline int16_t sadd8_tail(int16_t x, int16_t y) { int z = x + y; return (int16_t)(z > 127 ? 127 : (int8_t)z); }
+
+static void win8_beta_step(int16_t o[8], int16_t x, int16_t y, int tail)
+{
+  int16_t xy, m[8], n[8];
+#define A8(a, b) (tail ? sadd8_tail(a, b) : adds8(a, b))
+  xy = A8(x, y);
+  m[0] = A8(o[4], xy); m[1] = o[4];         m[2] = A8(o[5], y);  m[3] = A8(o[5], x);
+  m[4] = A8(o[6], x);  m[5] = A8(o[6], y);  m[6] = o[7];         m[7] = A8(o[7], xy);
+  n[0] = o[0];         n[1] = A8(o[0], xy); n[2] = A8(o[1], x);  n[3] = A8(o[1], y);
+  n[4] = A8(o[2], y);  n[5] = A8(o[2], x);  n[6] = A8(o[3], xy); n[7] = o[3];
+#undef A8
+  for (int i = 0; i < 8; i++) o[i] = maxs(m[i], n[i]);
+}
+
+static void win8_alpha_branches(const int16_t o[8], int16_t x, int16_t y, int16_t m[8], int16_t n[8])
+{
+  int16_t xy = adds8(x, y);
+  m[0] = o[0];            m[1] = adds8(o[3], y); m[2] = adds8(o[4], y); m[3] = o[7];
+  m[4] = o[1];            m[5] = adds8(o[2], y); m[6] = adds8(o[5], y); m[7] = o[6];
+  n[0] = adds8(o[1], xy); n[1] = adds8(o[2], x); n[2] = adds8(o[5], x); n[3] = adds8(o[6], xy);
+  n[4] = adds8(o[0], xy); n[5] = adds8(o[3], x); n[6] = adds8(o[4], x); n[7] = adds8(o[7], xy);
+}
+
+static inline void win8_normalize(int k, int16_t o[8])
+{
+  if (k != 0) {
+    int16_t m = o[0];
+    for (int i = 1; i < 8; i++) m = maxs(m, o[i]);
+    for (int i = 0; i < 8; i++) o[i] = subs8(o[i], m);
+  }
+}
+
+static void map_windowed8(int K, int P, const int16_t *in, const int16_t *app, const int16_t *par,
+                          const int16_t *tail_x, const int16_t *tail_p, int16_t *out)
+{
+  const int L = K / P, W = 40;
+  static __thread int16_t X[ORC_MAX_K];
+  static __thread int16_t B[32][ORC_MAX_K / 16 + 1][8];
+  int16_t warm[32][8], o[8], m[8], n[8];
+  for (int i = 0; i < K; i++) X[i] = app ? adds8(app[i], in[i]) : in[i];
+  for (int d = 0; d < P; d++) {                 /* beta warm-up over the first 40 symbols of every sub-block (:321-384) */
+    memset(o, 0, sizeof(o));
+    for (int k = W - 1; k >= 0; k--) { win8_beta_step(o, X[d * L + k], par[d * L + k], 0); win8_normalize(k, o); }
+    memcpy(warm[d], o, sizeof(o));
+  }
+  for (int d = 0; d < P; d++) {
+    if (d < P - 1) memcpy(o, warm[d + 1], sizeof(o));
+    else { memset(o, 0, sizeof(o)); for (int k = 2; k >= 0; k--) win8_beta_step(o, tail_x[k], tail_p[k], 1); }
+    memcpy(B[d][L], o, sizeof(o));
+    for (int k = L - 1; k >= 0; k--) {
+      win8_beta_step(o, X[d * L + k], par[d * L + k], 0);
+      memcpy(B[d][k], o, sizeof(o));            /* stored before normalisation (:419-432) */
+      win8_normalize(k, o);
+    }
+  }
+  for (int d = 0; d < P; d++) {                 /* alpha warm-up over the last 40 symbols (:459-506) */
+    memset(o, 0, sizeof(o));
+    for (int k = 0; k < W; k++) {
+      int idx = d * L + L - W + k;
+      win8_alpha_branches(o, X[idx], par[idx], m, n);
+      for (int i = 0; i < 8; i++) o[i] = maxs(m[i], n[i]);
+      win8_normalize(k, o);
+    }
+    memcpy(warm[d], o, sizeof(o));
+  }
+  for (int d = 0; d < P; d++) {
+    if (d > 0) memcpy(o, warm[d - 1], sizeof(o)); else memset(o, 0, sizeof(o));   /* known state: (0, -INF x 7) with INF = 0 */
+    for (int k = 0; k < L; k++) {
+      int idx = d * L + k;
+      win8_alpha_branches(o, X[idx], par[idx], m, n);
+      const int16_t *b = B[d][k + 1];
+      int16_t m0 = adds8(b[0], m[0]), m1 = adds8(b[0], n[0]);
+      for (int i = 1; i < 8; i++) { m0 = maxs(m0, adds8(b[i], m[i])); m1 = maxs(m1, adds8(b[i], n[i])); }
+      out[idx] = (int16_t)(subs8(m1, m0) >> 1);
+      for (int i = 0; i < 8; i++) o[i] = maxs(m[i], n[i]);
+      win8_normalize(k, o);
+    }
+  }
+}
+
 /* non-windowed SSE decoder, wrapping int16 (turbodecoder_sse.c:105-206,211-297,300-353) */
 static void map_sse(int K, const int16_t *in, const int16_t *app, const int16_t *par,
                     const int16_t *tail_x, const int16_t *tail_p, int16_t *out)
@@ -359,8 +457,21 @@ static int tdec_setup(orc_tdec_t *h, int K)
 {
   int idx = orc_cb_index(K);
   if (K > ORC_MAX_K || idx < 0 || orc_cb_size(idx) != K) return -1;
-  h->K = K; h->P = orc_subblocks(K); h->n_iter = 0;
+  h->K = K; h->P = orc_subblocks(K); h->n_iter = 0; h->llr8 = 0;
   return orc_qpp(K, h->fwd, h->rev);
+}
+
+/* srslte_vec_sub_bbb as the 8-bit iteration driver calls it (vector_simd.c:165-192, aligned buffers, AVX2): saturating in
+ * blocks of 32 array elements, the K mod 32 elements behind the last full block by the scalar (wrapping) loop. The arrays
+ * are in sub-block order: natural bit (d, k) sits at k*P + d. */
+static void vec_sub8(const orc_tdec_t *h, int16_t *z, const int16_t *x, const int16_t *y)
+{
+  const int K = h->K, L = K / h->P, full = K - (K % 32);
+  for (int d = 0; d < h->P; d++)
+    for (int k = 0; k < L; k++) {
+      int i = d * L + k, pos = k * h->P + d;
+      z[i] = pos < full ? subs8(x[i], y[i]) : (int16_t)(int8_t)(x[i] - y[i]);
+    }
 }
 
 static void tdec_tails(orc_tdec_t *h, const int16_t *t)
@@ -394,7 +505,17 @@ int orc_tdec_new_cb_soft(orc_tdec_t *h, int K, const int16_t *soft)
 void orc_tdec_iteration(orc_tdec_t *h, uint8_t *out_bytes, int16_t *llr_nat)
 {   /* run_tdec_iteration_16bit (turbodecoder_iter.h:73-147) + tdec_decision_byte (turbodecoder.c:353-360) */
   const int K = h->K, n = h->n_iter;
-  if ((n % 2) == 0) {
+  if (h->llr8) {     /* run_tdec_iteration_8bit: same driver, int8 decoders and saturating vector subtraction */
+    if ((n % 2) == 0) {
+      if (n) vec_sub8(h, h->app1, h->app1, h->ext1);
+      map_windowed8(K, h->P, h->syst, n ? h->app1 : NULL, h->p0, h->t_syst, h->t_p0, h->ext1);
+    } else {
+      if (n > 1) vec_sub8(h, h->ext1, h->ext1, h->app1);
+      for (int i = 0; i < K; i++) h->app2[h->rev[i]] = h->ext1[i];
+      map_windowed8(K, h->P, h->app2, NULL, h->p1, h->t_app2, h->t_p1, h->ext2);
+      for (int i = 0; i < K; i++) h->app1[h->fwd[i]] = h->ext2[i];
+    }
+  } else if ((n % 2) == 0) {
     if (n) for (int i = 0; i < K; i++) h->app1[i] = wrap16(h->app1[i] - h->ext1[i]);
     orc_map(K, h->P, h->syst, n ? h->app1 : NULL, h->p0, h->t_syst, h->t_p0, h->ext1);
   } else {
@@ -420,6 +541,63 @@ int orc_tdec_halfits(int K, const int16_t *in_nat, int nof, uint8_t *out_bytes, 
     orc_tdec_iteration(h, out_bytes + (size_t)n * (K / 8), llr_nat ? llr_nat + (size_t)n * K : NULL);
   free(h);
   return r;
+}
+
+/* 8-bit LLR entry points (srslte_tdec_iteration_8bit, turbodecoder.c:408-452,536-543): sub-block classes 32 / 16 decode
+ * in int8; classes 8 / 0 widen the input to int16 once (convert_8_to_16) and run the 16-bit decoders of that class. */
+static void tdec8_class(orc_tdec_t *h)
+{
+  h->P = orc_subblocks8(h->K);
+  h->llr8 = h->P >= 16;
+}
+
+int orc_tdec8_new_cb_natural(orc_tdec_t *h, int K, const int8_t *in)
+{
+  if (tdec_setup(h, K)) return -1;
+  tdec8_class(h);
+  int16_t t[12];
+  for (int i = 0; i < K; i++) { h->syst[i] = in[3 * i]; h->p0[i] = in[3 * i + 1]; h->p1[i] = in[3 * i + 2]; }
+  for (int i = 0; i < 12; i++) t[i] = in[3 * K + i];
+  tdec_tails(h, t);
+  return 0;
+}
+
+int orc_tdec8_new_cb_soft(orc_tdec_t *h, int K, const int8_t *soft)
+{
+  if (tdec_setup(h, K)) return -1;
+  tdec8_class(h);
+  if (h->P == 0) return orc_tdec8_new_cb_natural(h, K, soft);
+  int16_t t[12];
+  for (int x = 0; x < K; x++) {
+    int pos = orc_sb_pos(x, K, h->P);
+    h->syst[x] = soft[pos]; h->p0[x] = soft[K + 32 + pos]; h->p1[x] = soft[2 * (K + 32) + pos];
+  }
+  for (int i = 0; i < 12; i++) t[i] = soft[3 * (K + 32) + i];
+  tdec_tails(h, t);
+  return 0;
+}
+
+int orc_tdec_halfits8(int K, const int8_t *in_nat, int nof, uint8_t *out_bytes, int16_t *llr_nat)
+{
+  orc_tdec_t *h = malloc(sizeof(*h));
+  int r = orc_tdec8_new_cb_natural(h, K, in_nat);
+  for (int n = 0; n < nof && !r; n++)
+    orc_tdec_iteration(h, out_bytes + (size_t)n * (K / 8), llr_nat ? llr_nat + (size_t)n * K : NULL);
+  free(h);
+  return r;
+}
+
+int orc_rm_rx8(const int8_t *in, int E, int K, int rv, int sb_layout, int8_t *soft)
+{   /* soft[deinter[i % (3K+12)]] += e[i], wrapping int8, table of the 8-bit decoder class (rm_turbo.c:432-469,543-631) */
+  static __thread uint16_t tab[3 * ORC_MAX_K + 12];
+  if (rv < 0 || rv > 3 || orc_cb_index(K) < 0 || orc_cb_size(orc_cb_index(K)) != K) return -2;
+  orc_rm_table(K, rv, tab);
+  int P = sb_layout ? orc_subblocks8(K) : 0, n = 3 * K + 12;
+  for (int i = 0; i < E; i++) {
+    int pos = orc_rm_soft_index(tab[i % n], K, P);
+    soft[pos] = (int8_t)(soft[pos] + in[i]);
+  }
+  return 0;
 }
 
 static int decode_cb_h(orc_tdec_t *h, int max_its, int crc_type, int crc_bits, uint8_t *out_bytes, int *nits)
@@ -462,10 +640,12 @@ void orc_tb_get_soft(void *p, int cb, int16_t *out) { memcpy(out, ((orc_tb_t *)p
 
 /* decode_tb + decode_tb_cb (sch.c:307-498). Returns 0 OK, -1 CRC fail, -2 invalid. data needs
  * tbs/8 + 3 bytes plus K/8 slack for the last CB's write. */
-int orc_tb_decode(void *p, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits, const int16_t *e_bits,
-                  uint32_t max_its, uint8_t *data, uint8_t *cb_crc_out, uint32_t *cb_its)
+static int tb_decode_any(void *p, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits, const void *e_any, int llr8,
+                         uint32_t max_its, uint8_t *data, uint8_t *cb_crc_out, uint32_t *cb_its)
 {
   orc_tb_t *t = p;
+  const int16_t *e_bits = e_any;
+  const int8_t *e_bits_b = e_any;
   uint32_t s[9];
   if (!t || !data || !e_bits) return -2;
   if (orc_cbsegm(tbs, s)) return -2;
@@ -480,8 +660,13 @@ int orc_tb_decode(void *p, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_
     if (!t->sb.cb_crc[cb]) {
       uint32_t Gp = nof_e_bits / Qm, gamma = Gp % C, n_e = Qm * (Gp / C), rp = cb * n_e, E = n_e;
       if (cb > C - gamma) { E = n_e + Qm; rp = (C - gamma) * n_e + (cb - (C - gamma)) * E; }   /* sch.c:339 quirk */
-      if (orc_rm_rx(e_bits + rp, (int)E, (int)K, (int)rv, 1, t->sb.soft[cb])) return -1;
-      orc_tdec_new_cb_soft(&t->dec, (int)K, t->sb.soft[cb]);
+      if (llr8) {      /* the soft buffer's memory holds int8 values (sch.c:344-348,362-364) */
+        if (orc_rm_rx8(e_bits_b + rp, (int)E, (int)K, (int)rv, 1, (int8_t *)t->sb.soft[cb])) return -1;
+        orc_tdec8_new_cb_soft(&t->dec, (int)K, (const int8_t *)t->sb.soft[cb]);
+      } else {
+        if (orc_rm_rx(e_bits + rp, (int)E, (int)K, (int)rv, 1, t->sb.soft[cb])) return -1;
+        orc_tdec_new_cb_soft(&t->dec, (int)K, t->sb.soft[cb]);
+      }
       int nits = 0;
       int ok = decode_cb_h(&t->dec, (int)max_its, C > 1 ? 1 : 0, C > 1 ? (int)K : (int)tbs + 24, &data[cb * rlen / 8], &nits);
       if (ok) t->sb.cb_crc[cb] = 1;
@@ -502,6 +687,19 @@ int orc_tb_decode(void *p, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_
   uint32_t par_rx = orc_crc(0, data, (int)tbs);
   uint32_t par_tx = ((uint32_t)data[tbs / 8] << 16) | ((uint32_t)data[tbs / 8 + 1] << 8) | data[tbs / 8 + 2];
   return (par_rx == par_tx && par_rx) ? 0 : -1;
+}
+
+int orc_tb_decode(void *p, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits, const int16_t *e_bits,
+                  uint32_t max_its, uint8_t *data, uint8_t *cb_crc_out, uint32_t *cb_its)
+{
+  return tb_decode_any(p, tbs, Qm, rv, nof_e_bits, e_bits, 0, max_its, data, cb_crc_out, cb_its);
+}
+
+/* the same with q->llr_is_8bit set: int8 LLRs, int8 soft buffers, srslte_tdec_iteration_8bit */
+int orc_tb_decode8(void *p, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits, const int8_t *e_bits,
+                   uint32_t max_its, uint8_t *data, uint8_t *cb_crc_out, uint32_t *cb_its)
+{
+  return tb_decode_any(p, tbs, Qm, rv, nof_e_bits, e_bits, 1, max_its, data, cb_crc_out, cb_its);
 }
 
 /* ------------------------------------------------------------------ multithreaded timing harness ---- */

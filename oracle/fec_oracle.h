@@ -47,7 +47,7 @@ void orc_map(int K, int P, const int16_t *x, const int16_t *app, const int16_t *
              const int16_t *tail_x, const int16_t *tail_p, int16_t *out);
 
 typedef struct {
-  int      K, P, n_iter;
+  int      K, P, n_iter, llr8;   /* llr8: int8 decoders of the 8-bit LLR path (values carried in int16) */
   int16_t  syst[ORC_MAX_K + 4], p0[ORC_MAX_K + 4], p1[ORC_MAX_K + 4];
   int16_t  t_syst[3], t_p0[3], t_app2[3], t_p1[3];
   int16_t  app1[ORC_MAX_K], app2[ORC_MAX_K], ext1[ORC_MAX_K], ext2[ORC_MAX_K];
@@ -59,6 +59,12 @@ int  orc_tdec_new_cb_soft(orc_tdec_t *h, int K, const int16_t *soft);           
 void orc_tdec_iteration(orc_tdec_t *h, uint8_t *out_bytes, int16_t *llr_nat);     /* turbodecoder_iter.h:73-147 */
 int  orc_tdec_halfits(int K, const int16_t *in_nat, int nof, uint8_t *out_bytes, int16_t *llr_nat);
 int  orc_decode_cb(const int16_t *soft, int K, int max_its, int crc_type, uint8_t *out_bytes, int *nits);
+/* 8-bit LLR path */
+int  orc_subblocks8(int K);                                                         /* turbodecoder.c:392-406 */
+int  orc_tdec8_new_cb_natural(orc_tdec_t *h, int K, const int8_t *in_nat);
+int  orc_tdec8_new_cb_soft(orc_tdec_t *h, int K, const int8_t *soft);
+int  orc_tdec_halfits8(int K, const int8_t *in_nat, int nof, uint8_t *out_bytes, int16_t *llr_nat);
+int  orc_rm_rx8(const int8_t *in, int E, int K, int rv, int sb_layout, int8_t *soft);   /* rm_turbo.c:432-469 */
 
 typedef struct {
   int      max_cb;
@@ -73,6 +79,8 @@ void  orc_tb_free(void *p);
 void  orc_tb_reset(void *p, uint32_t tbs);                                        /* softbuffer.c:128-151 */
 int   orc_tb_decode(void *p, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits, const int16_t *e_bits,
                     uint32_t max_its, uint8_t *data, uint8_t *cb_crc_out, uint32_t *cb_its); /* sch.c:307-498 */
+int   orc_tb_decode8(void *p, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits, const int8_t *e_bits,
+                     uint32_t max_its, uint8_t *data, uint8_t *cb_crc_out, uint32_t *cb_its);
 void  orc_tb_get_soft(void *p, int cb, int16_t *out);
 
 /* front end in front of decode_tb: see the section header in fec_oracle.c */

@@ -14,7 +14,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "tests"))
-from _libs import ALL_K, P, int_awgn_llr, int_gauss, ref  # noqa: E402
+from _libs import ALL_K, P, aligned, int_awgn_llr, int_gauss, ref  # noqa: E402
 
 R = ref()
 assert R is not None, "needs oracle/_ref (make -C oracle ref)"
@@ -198,10 +198,97 @@ def gen_frontend():
     np.savez_compressed(os.path.join(OUT, "frontend.npz"), **out)
 
 
+def llr8_input(coded, sigma_milli, seed, amp=24):
+    """int8 LLRs as the 8-bit demodulator scale delivers them: amp*(2b-1) + noise, clipped to int8"""
+    return np.clip(int_awgn_llr(coded, sigma_milli, seed, amp=amp), -128, 127).astype(np.int8)
+
+
+def soft8_crc(s8, K, P8):
+    if P8 == 0:
+        return crc32(s8[:3 * K + 12])
+    return crc32(np.concatenate([s8[0:K], s8[K + 32:2 * K + 32], s8[2 * K + 64:3 * K + 64], s8[3 * K + 96:3 * K + 108]]))
+
+
+def gen_llr8():
+    """8-bit LLR path: srslte_tdec_iteration_8bit snapshots on natural-layout int8 inputs (all four decoder
+    classes: avx8 P=32, sse8 P=16, and the 16-bit fallbacks P=8 / 0) and srslte_dlsch_decode sequences with llr_is_8bit.
+    Transport blocks whose code blocks fall to the P=8 fallback are left out: in soft-buffer layout the reference widens only
+    the first 3K+12 of the 3K+108 entries (turbodecoder.c:427-431,455-459) and decodes stale memory behind them."""
+    out = {}
+    cases = []
+    for K, kind, par, nof in [(40, "awgn", 700, 6), (400, "awgn", 800, 6), (408, "awgn", 750, 8), (800, "awgn", 800, 8),
+                              (816, "awgn", 700, 8), (1008, "awgn", 750, 8), (1024, "rand", 127, 8), (2048, "awgn", 650, 8),
+                              (2112, "awgn", 700, 8), (3136, "rand", 60, 8), (5824, "awgn", 600, 8), (6144, "awgn", 700, 8),
+                              (6144, "rand", 127, 6)]:
+        i = len(cases)
+        seed = 9000 + i
+        if kind == "awgn":
+            bits = (int_gauss(K, seed) & 1).astype(np.uint8)
+            coded = np.zeros(3 * K + 12, np.uint8)
+            R.ref_encode_cb(K, P(bits), P(coded))
+            inp = llr8_input(coded, par, seed + 1)
+            out[f"coded_{i}"] = np.packbits(coded)
+        else:
+            inp = (int_gauss(3 * K + 12, seed) % (2 * par + 1) - par).astype(np.int8)
+        ob = np.zeros((nof, K // 8), np.uint8)
+        ol = np.zeros((nof, K), np.int16)
+        assert R.ref_tdec_halfits8(K, P(inp), nof, P(ob), P(ol)) == 0
+        out[f"bytes_{i}"] = ob
+        out[f"llrcrc_{i}"] = np.array([crc32(ol[n]) for n in range(nof)], np.uint32)
+        out[f"incrc_{i}"] = np.array([crc32(inp)], np.uint32)
+        cases.append((K, 0 if kind == "awgn" else 1, par, nof, seed))
+    out["cases"] = np.array(cases, np.int64)
+    tbc = []
+    for tbs, Qm, nbits, sigma, max_its, ntx in [(75376, 6, 90000, 450, 8, 1), (75376, 6, 90000, 620, 8, 4), (36696, 4, 57600, 600, 8, 2),
+                                                (6200, 6, 14400, 700, 8, 2), (1000, 4, 1600, 550, 8, 2), (1800, 2, 3000, 900, 8, 3),
+                                                (256, 2, 600, 700, 10, 2), (12960, 2, 20000, 800, 8, 4)]:
+        ci = len(tbc)
+        seed = 9500 + 10 * ci
+        t = C.c_void_p(R.ref_tb_new(100))
+        data = np.zeros(tbs // 8 + 3 + 1024, np.uint8)
+        data[: tbs // 8] = (int_gauss(tbs // 8, seed) & 255).astype(np.uint8)
+        R.ref_tb_reset(t, tbs)
+        seg = np.zeros(9, np.uint32)
+        R.ref_cbsegm(tbs, P(seg))
+        assert R.ref_subblocks8(int(seg[2])) != 8 and (int(seg[7]) == 0 or R.ref_subblocks8(int(seg[3])) != 8)
+        done = 0
+        for tx, rv in enumerate([0, 2, 3, 1][:ntx]):
+            e = np.zeros(nbits, np.uint8)
+            assert R.ref_tb_encode(t, tbs, Qm, rv, nbits, P(data), P(e)) == 0
+            llr = aligned(nbits + 64, np.int8)
+            llr[:nbits] = llr8_input(e, sigma, seed + 1 + tx)
+            d = np.zeros(tbs // 8 + 3 + 1024, np.uint8)
+            crc, avg = np.zeros(13, np.uint8), np.zeros(1, np.uint32)
+            ret = R.ref_tb_decode8(t, tbs, Qm, rv, nbits, P(llr), max_its, P(d), P(crc), P(avg))
+            out[f"tb_e_{ci}_{tx}"] = np.packbits(e)
+            out[f"tb_data_{ci}_{tx}"] = d[: tbs // 8 + 3].copy()
+            out[f"tb_crc_{ci}_{tx}"] = crc
+            out[f"tb_ret_{ci}_{tx}"] = np.array([ret, int(avg[0])], np.int64)
+            sc = []
+            for cb in range(int(seg[1])):
+                s = np.zeros(18600, np.int16)
+                R.ref_tb_get_soft(t, cb, P(s))
+                K = int(seg[2]) if cb < int(seg[6]) else int(seg[3])
+                sc.append(soft8_crc(s.view(np.int8), K, R.ref_subblocks8(K)))
+            out[f"tb_softcrc_{ci}_{tx}"] = np.array(sc, np.uint32)
+            done += 1
+            if ret == 0:
+                break
+        out[f"tb_payload_{ci}"] = data[: tbs // 8].copy()
+        tbc.append((tbs, Qm, nbits, sigma, max_its, done, seed))
+        R.ref_tb_free(t)
+    out["tb_cases"] = np.array(tbc, np.int64)
+    np.savez_compressed(os.path.join(OUT, "llr8.npz"), **out)
+
+
 if __name__ == "__main__":
-    gen_frontend()
-    gen_tdec()
-    gen_tables()
-    gen_tb()
+    if "llr8" in sys.argv[1:]:        # only the 8-bit fixtures (the others stay byte-identical)
+        gen_llr8()
+    else:
+        gen_frontend()
+        gen_tdec()
+        gen_tables()
+        gen_tb()
+        gen_llr8()
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))

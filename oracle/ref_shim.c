@@ -139,6 +139,42 @@ int ref_tdec_halfits(int K, const int16_t *in_nat, int nof, int mode, uint8_t *o
   return r;
 }
 
+/* ---- 8-bit LLR path ---- */
+int ref_subblocks8(int K) { return (int)srslte_tdec_autoimp_get_subblocks_8bit((uint32_t)K); }
+
+int ref_rm_rx8(const int8_t *in, int E, int cb_idx, int rv, int8_t *soft)
+{
+  return srslte_rm_turbo_rx_lut_8bit((int8_t *)in, soft, (uint32_t)E, (uint32_t)cb_idx, (uint32_t)rv);
+}
+
+/* nof half-iterations through srslte_tdec_new_cb + srslte_tdec_iteration_8bit on a NATURAL-layout int8 input
+ * (force_not_sb). Snapshots per half-iteration: out_bytes[nof][K/8], llr_nat[nof][K] (int16, may be NULL). */
+int ref_tdec_halfits8(int K, const int8_t *in_nat, int nof, uint8_t *out_bytes, int16_t *llr_nat)
+{
+  srslte_tdec_t *h = &g_tdec;
+  srslte_tdec_force_not_sb(h);
+  int8_t *in = srslte_vec_malloc(3 * K + 12 + 64);
+  memcpy(in, in_nat, 3 * K + 12);
+  int r = srslte_tdec_new_cb(h, (uint32_t)K);
+  if (!r) {
+    for (int n = 0; n < nof; n++) {
+      srslte_tdec_iteration_8bit(h, in, out_bytes + (size_t)n * (K / 8));
+      if (llr_nat) {
+        int16_t *o = llr_nat + (size_t)n * K;
+        if (h->current_llr_type == SRSLTE_TDEC_16) llr_natural(h, K, o);
+        else {
+          int8_t *A = (h->n_iter % 2) ? (int8_t *)h->ext1 : (int8_t *)h->app1;
+          int P = ref_subblocks8(K), L = K / P;
+          for (int x = 0; x < K; x++) o[x] = A[(x % L) * P + x / L];
+        }
+      }
+    }
+  }
+  free(in);
+  h->force_not_sb = false;
+  return r;
+}
+
 /* Decode ONE code block from a soft buffer as sch.c:356-391 does (sb layout when P>0), CRC early stop.
  * crc_type 0 = CRC24A, 1 = CRC24B. soft is modified in place exactly as the reference does (trap 7).
  * Returns 1 if CRC OK else 0; *nits = half-iterations run. */
@@ -232,6 +268,21 @@ int ref_tb_decode(void *p, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_
   if (fill_cfg(t, tbs, Qm, rv, nof_e_bits)) return -2;
   srslte_sch_set_max_noi(&t->sch, max_its);
   int r = srslte_dlsch_decode(&t->sch, &t->cfg, &t->rx, e_bits, data);
+  for (uint32_t i = 0; i < t->cfg.cb_segm[0].C && cb_crc_out; i++) cb_crc_out[i] = t->rx.cb_crc[i];
+  if (avg_its) *avg_its = srslte_sch_last_noi(&t->sch);
+  return r;
+}
+
+/* srslte_dlsch_decode with q->llr_is_8bit set: int8 e_bits, the soft buffers hold int8 */
+int ref_tb_decode8(void *p, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits, int8_t *e_bits,
+                   uint32_t max_its, uint8_t *data, uint8_t *cb_crc_out, uint32_t *avg_its)
+{
+  ref_tb_t *t = p;
+  if (fill_cfg(t, tbs, Qm, rv, nof_e_bits)) return -2;
+  srslte_sch_set_max_noi(&t->sch, max_its);
+  t->sch.llr_is_8bit = true;
+  int r = srslte_dlsch_decode(&t->sch, &t->cfg, &t->rx, (int16_t *)e_bits, data);
+  t->sch.llr_is_8bit = false;
   for (uint32_t i = 0; i < t->cfg.cb_segm[0].C && cb_crc_out; i++) cb_crc_out[i] = t->rx.cb_crc[i];
   if (avg_its) *avg_its = srslte_sch_last_noi(&t->sch);
   return r;

@@ -88,3 +88,42 @@ def fe_ul_cases():
                    ack_pos=[int(v) for v in z[f"ul_ack_{i}"]], ri_pos=[int(v) for v in z[f"ul_ri_{i}"]],
                    crc_q=int(z[f"ul_crc_{i}"][0]), crc_g=int(z[f"ul_crc_{i}"][1]), g0=z[f"ul_g0_{i}"],
                    id=f"ul-qm{mod}-prb{prb}-ack{int(nack)}-ri{int(nri)}")
+
+
+def llr8_input(coded, sigma_milli, seed, amp=24):
+    """int8 LLRs of the 8-bit fixtures (same generator as oracle/gen_golden.py)"""
+    return np.clip(int_awgn_llr(coded, sigma_milli, seed, amp=amp), -128, 127).astype(np.int8)
+
+
+def soft8_view(s8, K, P8):
+    """the entries of an int8 reference soft buffer that carry data (sub-block layout leaves 32-entry gaps)"""
+    if P8 == 0:
+        return s8[:3 * K + 12]
+    return np.concatenate([s8[0:K], s8[K + 32:2 * K + 32], s8[2 * K + 64:3 * K + 64], s8[3 * K + 96:3 * K + 108]])
+
+
+def tdec8_cases():
+    """8-bit decoder snapshots: dict(K, inp int8[3K+12], nof, bytes[nof][K/8], llrcrc[nof])"""
+    z = np.load(os.path.join(GOLD, "llr8.npz"))
+    for i, (K, kind, par, nof, seed) in enumerate(z["cases"]):
+        K, par, nof, seed = int(K), int(par), int(nof), int(seed)
+        if kind == 0:
+            inp = llr8_input(np.unpackbits(z[f"coded_{i}"])[: 3 * K + 12], par, seed + 1)
+        else:
+            inp = (int_gauss(3 * K + 12, seed) % (2 * par + 1) - par).astype(np.int8)
+        assert crc32(inp) == int(z[f"incrc_{i}"][0]), "input generator drifted"
+        yield dict(K=K, inp=inp, nof=nof, bytes=z[f"bytes_{i}"], llrcrc=z[f"llrcrc_{i}"], id=f"K{K}-{'awgn' if kind == 0 else 'rand'}{par}")
+
+
+def tb8_cases():
+    """8-bit transport-block sequences: dict(tbs,Qm,nbits,max_its, tx=[dict(rv, llr int8, data, crc, ret, avg_its, softcrc)], payload)"""
+    z = np.load(os.path.join(GOLD, "llr8.npz"))
+    for ci, (tbs, Qm, nbits, sigma, max_its, ntx, seed) in enumerate(z["tb_cases"]):
+        tbs, Qm, nbits, sigma, max_its, ntx, seed = (int(v) for v in (tbs, Qm, nbits, sigma, max_its, ntx, seed))
+        txs = []
+        for tx in range(ntx):
+            e = np.unpackbits(z[f"tb_e_{ci}_{tx}"])[:nbits]
+            txs.append(dict(rv=[0, 2, 3, 1][tx], llr=llr8_input(e, sigma, seed + 1 + tx), data=z[f"tb_data_{ci}_{tx}"],
+                            crc=z[f"tb_crc_{ci}_{tx}"], ret=int(z[f"tb_ret_{ci}_{tx}"][0]), avg_its=int(z[f"tb_ret_{ci}_{tx}"][1]),
+                            softcrc=z[f"tb_softcrc_{ci}_{tx}"]))
+        yield dict(tbs=tbs, Qm=Qm, nbits=nbits, max_its=max_its, tx=txs, payload=z[f"tb_payload_{ci}"], id=f"tbs{tbs}-s{sigma}")

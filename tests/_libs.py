@@ -32,6 +32,7 @@ def oracle():
         lib.orc_tb_reset.argtypes = [C.c_void_p, C.c_uint32]
         lib.orc_tb_decode.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p,
                                       C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.orc_tb_decode8.argtypes = lib.orc_tb_decode.argtypes
         lib.orc_tb_get_soft.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         lib.orc_crc.restype = C.c_uint32
         lib.orc_crc.argtypes = [C.c_int, C.c_void_p, C.c_int]
@@ -73,6 +74,8 @@ def ref():
         lib.ref_tb_decode.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p,
                                       C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]
         lib.ref_tb_decode_detail.argtypes = lib.ref_tb_decode.argtypes
+        if hasattr(lib, "ref_tb_decode8"):
+            lib.ref_tb_decode8.argtypes = lib.ref_tb_decode.argtypes
         lib.ref_tb_get_soft.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         lib.ref_tb_set_soft.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         lib.ref_crc.restype = C.c_uint32
