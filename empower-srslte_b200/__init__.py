@@ -93,6 +93,7 @@ def load():
         lib.fec_cuda_cbsegm.argtypes = [C.c_uint32, C.POINTER(C.c_uint32)]
         lib.fec_cuda_last_phase_ms.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
         lib.fec_cuda_last_path_counts.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
+        lib.fec_cuda_set_llr_8bit.argtypes = [C.c_void_p, C.c_int]
         lib.fec_cuda_encode_tbs.argtypes = [C.c_void_p, C.POINTER(TxTbDesc), C.c_uint32, C.c_uint32]
         lib.fec_cuda_decode_syms.argtypes = [C.c_void_p, C.POINTER(TbDesc), C.POINTER(SymDesc), C.c_uint32, C.c_uint32]
         lib.fec_cuda_submit_syms.argtypes = [C.c_void_p, C.POINTER(TbDesc), C.POINTER(SymDesc), C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64)]
@@ -188,6 +189,12 @@ class FecCuda:
         d[0].data, d[0].e_bits = a.ctypes.data, o.ctypes.data
         self.encode_tbs(d)
         return int(d[0].ret), o
+
+    def set_llr_8bit(self, on):
+        """srslte_sch_t.llr_is_8bit: e_bits of the following decode calls are int8, the 8-bit rate de-matcher and decoders run"""
+        rc = self.lib.fec_cuda_set_llr_8bit(self.h, 1 if on else 0)
+        if rc:
+            raise RuntimeError(f"fec_cuda_set_llr_8bit: {rc}")
 
     def last_path_counts(self):
         """code blocks of the last decode call handed (to the certificate variant of the packed kernel, on to the exact kernel)"""

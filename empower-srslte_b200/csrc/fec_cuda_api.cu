@@ -46,6 +46,8 @@ struct fec_cuda_ctx {
   uint64_t      launches;
   uint32_t      max_tbs;
   ktab_t        ktab[FEC_NOF_K];
+  ktab_t        ktab8[FEC_NOF_K];   /* the same per-K tables in the geometry of the 8-bit LLR path (P = 32 for K > 2048) */
+  int           llr8;               /* srslte_sch_t.llr_is_8bit: e_bits are int8, int8 combining and decoders (sch.c:344-348,362-364) */
   uint32_t     *d_r24a, *d_r24b;
   sbchunk_t    *chunks;
   uint32_t      nchunks, next_id;
@@ -176,9 +178,10 @@ extern "C" void fec_cuda_destroy(fec_cuda_ctx_t *ctx)
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
-  for (int i = 0; i < FEC_NOF_K; i++) if (ctx->ktab[i].ready) {
-    cudaFree(ctx->ktab[i].d_step); cudaFree(ctx->ktab[i].d_rank); cudaFree(ctx->ktab[i].d_pair_addr); cudaFree(ctx->ktab[i].d_txsrc);
-    cudaFree(ctx->ktab[i].d_pair_crc[0]); cudaFree(ctx->ktab[i].d_pair_crc[1]);
+  for (int i = 0; i < 2 * FEC_NOF_K; i++) if ((i < FEC_NOF_K ? ctx->ktab[i] : ctx->ktab8[i - FEC_NOF_K]).ready) {
+    ktab_t *kt = i < FEC_NOF_K ? &ctx->ktab[i] : &ctx->ktab8[i - FEC_NOF_K];
+    cudaFree(kt->d_step); cudaFree(kt->d_rank); cudaFree(kt->d_pair_addr); cudaFree(kt->d_txsrc);
+    cudaFree(kt->d_pair_crc[0]); cudaFree(kt->d_pair_crc[1]);
   }
   cudaFree(ctx->d_softmax); cudaFree(ctx->d_exact); cudaFree(ctx->d_econt); cudaFreeHost(ctx->h_queue);
   for (uint32_t i = 0; i < ctx->nchunks; i++) { cudaFree(ctx->chunks[i].d_soft); cudaFree(ctx->chunks[i].d_cache); free(ctx->chunks[i].cb_crc); }
@@ -191,6 +194,15 @@ extern "C" void fec_cuda_destroy(fec_cuda_ctx_t *ctx)
   pipes_destroy(ctx);
   cudaStreamDestroy(ctx->stream);
   free(ctx);
+}
+
+/* srslte_sch_t.llr_is_8bit (sch.h:60): from here on e_bits are int8 and the 8-bit rate de-matcher and decoders run. Soft
+ * buffers written in one mode cannot be continued in the other (as in the reference): reset them when switching. */
+extern "C" int fec_cuda_set_llr_8bit(fec_cuda_ctx_t *ctx, int on)
+{
+  if (!ctx) return FEC_CUDA_EINVAL;
+  ctx->llr8 = on ? 1 : 0;
+  return 0;
 }
 
 extern "C" const char *fec_cuda_last_error(fec_cuda_ctx_t *ctx) { return ctx ? ctx->err : "null context"; }
@@ -229,9 +241,9 @@ static int ktab_get(fec_cuda_ctx_t *ctx, uint32_t K, ktab_t **out)
 {
   int idx = fec_k_index(K);
   if (idx < 0 || fec_k_size(idx) != (int)K) return fail(ctx, FEC_CUDA_EINVAL, "K=%u is not an LTE code block size", K);
-  ktab_t *t = &ctx->ktab[idx];
+  ktab_t *t = ctx->llr8 ? &ctx->ktab8[idx] : &ctx->ktab[idx];
   if (!t->ready) {
-    fec_geom(K, &t->g);
+    if (ctx->llr8) fec_geom_p(K, fec_k_subblocks8(K), &t->g); else fec_geom(K, &t->g);
     const size_t nstep = 2 * (size_t)t->g.SS, nrank = 3 * (size_t)t->g.SS + 16;
     uint32_t *step = (uint32_t *)malloc(nstep * 4);
     uint16_t *rank = (uint16_t *)malloc(nrank * 2);
@@ -325,14 +337,15 @@ extern "C" int fec_cuda_softbuffer_read_ref_layout(fec_cuda_ctx_t *ctx, uint32_t
 static void fill_decode_args(fec_cuda_ctx_t *ctx, int k, FecDecodeArgs *a, const FecCbDesc *cbd_dev, FecCbStatus *status_dev,
                              unsigned int *queue3, const uint32_t *softmax, uint32_t *exact, uint32_t *trk, uint32_t *econt, uint32_t off, uint32_t cnt, int16_t *dbg)
 {
-  const ktab_t *t = &ctx->ktab[k];
+  const ktab_t *t = ctx->llr8 ? &ctx->ktab8[k] : &ctx->ktab[k];
   memset(a, 0, sizeof(*a));
+  a->llr8 = ctx->llr8 && t->g.P >= 16;     /* classes 8 / 0 of the 8-bit path run the 16-bit decoders on the widened values */
   a->g = t->g; a->step_tab = t->d_step; a->crcpow[0] = ctx->d_r24a; a->crcpow[1] = ctx->d_r24b;
   a->cbs = cbd_dev + off; a->status = status_dev;
   a->queue = queue3 + 2 * k; a->ncb = cnt; a->slots = t->slots; a->dbg_llr = dbg;
   a->pair_addr = t->d_pair_addr; a->pair_crc[0] = t->d_pair_crc[0]; a->pair_crc[1] = t->d_pair_crc[1];
   a->soft_max = softmax; a->status_off = off;
-  if (t->g.P && !ctx->force_exact && !dbg) {
+  if (t->g.P && !ctx->force_exact && !dbg && !a->llr8) {
     a->exact_list = exact + off; a->exact_count = queue3 + 2 * FEC_NOF_K + k;
     a->trk_list = trk + off; a->trk_queue = queue3 + 3 * FEC_NOF_K + k; a->trk_count = queue3 + 4 * FEC_NOF_K + k;
     /* hand-over in mid-decode: continuation words behind the two lists, extrinsic scratch slots shared by the K groups of the
@@ -462,6 +475,8 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
                        cudaStream_t sc)
 {
   const int dev_io = (flags & FEC_CUDA_F_DEVICE_IO) != 0;
+  const size_t esz = ctx->llr8 ? 1 : 2;        /* bytes per LLR of e_bits */
+  if (syms && ctx->llr8) return fail(ctx, FEC_CUDA_EINVAL, "the symbol front end produces int16 LLRs: not available in 8-bit LLR mode");
   if (pp->plan_cap < n) { free(pp->plan); pp->plan = (tbplan_t *)malloc(sizeof(tbplan_t) * n); pp->plan_cap = n; }
   tbplan_t *plan = pp->plan;
   memset(plan, 0, sizeof(tbplan_t) * n);
@@ -520,7 +535,7 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
    * synchronises the device, so it must stop after the first calls */
   size_t need[16] = { sizeof(FecCbDesc) * (ncb + 1), sizeof(FecRmDesc) * (ncb + 1), sizeof(FecTbDesc) * (ntb + 1), sizeof(FecCbStatus) * (ncb + 1),
                       sizeof(int32_t) * (ntb + 1), (size_t)(ncb + 1) * CB_BYTES, (size_t)(ncb + 1) * 4,
-                      dev_io ? 0 : (syms ? sym_total : e_total * 2), dev_io ? 0 : data_total,
+                      dev_io ? 0 : (syms ? sym_total : e_total * esz), dev_io ? 0 : data_total,
                       /* front end */ sizeof(FecFeDesc) * nfe, syms ? e_total * 2 : 0, lst_total * 4, (dev_io || !syms) ? 0 : uci_total * 2, sizeof(float) * nfe, 0, 0 };
   for (int i = 0; i < 16; i++) { if (need[i] > ctx->hw[i]) ctx->hw[i] = need[i]; need[i] = ctx->hw[i]; }
   if (stage_reserve(ctx, &pp->st_cbd, need[0]) || stage_reserve(ctx, &pp->st_rmd, need[1]) ||
@@ -576,8 +591,8 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
     uint8_t *crc = p->chunk->cb_crc + (size_t)p->local * FEC_CUDA_MAX_CB;
     int16_t *soft0 = p->chunk->d_soft + (size_t)p->local * FEC_CUDA_MAX_CB * FEC_CUDA_SOFT_SLOT;
     uint8_t *cache0 = p->chunk->d_cache + (size_t)p->local * FEC_CUDA_MAX_CB * CB_BYTES;
-    const int16_t *e_dev = syms ? pp->d_llr + p->e_off + syms[i].nof_cqi_bits        /* g_bits + Q'_cqi*Qm, sch.c:963-973 */
-                                : dev_io ? t->e_bits : (const int16_t *)pp->st_e.d + p->e_off;
+    const char *e_dev = syms ? (const char *)(pp->d_llr + p->e_off + syms[i].nof_cqi_bits)        /* g_bits + Q'_cqi*Qm, sch.c:963-973 */
+                             : dev_io ? (const char *)t->e_bits : (const char *)pp->st_e.d + p->e_off * esz;
     FecTbDesc *td = &tbd[itb];
     memset(td, 0, sizeof(*td));
     td->data = dev_io ? t->data : (uint8_t *)pp->st_data.d + p->data_off;
@@ -595,7 +610,7 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
       if (cb > C - gamma) { E = n_e + t->Qm; rp = (C - gamma) * n_e + (cb - (C - gamma)) * E; }   /* sch.c:339 off-by-one kept */
       const uint32_t slot = grp_off[kt->g.idx] + grp_fill[kt->g.idx]++;
       FecRmDesc *r = &rmd[slot];
-      r->e = e_dev + rp; r->soft = soft0 + (size_t)cb * FEC_CUDA_SOFT_SLOT; r->rank = kt->d_rank;
+      r->e = (const int16_t *)(e_dev + (size_t)rp * esz); r->soft = soft0 + (size_t)cb * FEC_CUDA_SOFT_SLOT; r->rank = kt->d_rank;
       r->E = E; r->N = 3 * K + 12; r->off = kt->off[t->rv]; r->n_out = 3 * kt->g.SS + 16; r->new_data = t->new_data ? 1 : 0; r->slot = slot;
       if (r->n_out > max_n_out) max_n_out = r->n_out;
       FecCbDesc *d = &cbd[slot];
@@ -608,7 +623,7 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
       cudaPointerAttributes pa;
       p->pinned = (cudaPointerGetAttributes(&pa, t->e_bits) == cudaSuccess && pa.type == cudaMemoryTypeHost);
       cudaGetLastError();
-      if (!p->pinned) memcpy((int16_t *)pp->st_e.h + p->e_off, t->e_bits, (size_t)t->nof_e_bits * 2);
+      if (!p->pinned) memcpy((char *)pp->st_e.h + p->e_off * esz, t->e_bits, (size_t)t->nof_e_bits * esz);
     }
     itb++;
   }
@@ -654,14 +669,14 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
     while (i < n) {
       if (!plan[i].valid) { i++; continue; }
       const int pinned = plan[i].pinned;
-      const char *src0 = pinned ? (const char *)tbs[i].e_bits : (const char *)((int16_t *)pp->st_e.h + plan[i].e_off);
-      const size_t dst0 = plan[i].e_off * 2;
-      size_t len = (size_t)tbs[i].nof_e_bits * 2;
+      const char *src0 = pinned ? (const char *)tbs[i].e_bits : (const char *)pp->st_e.h + plan[i].e_off * esz;
+      const size_t dst0 = plan[i].e_off * esz;
+      size_t len = (size_t)tbs[i].nof_e_bits * esz;
       uint32_t j = i + 1;
       for (; j < n; j++) {
-        if (!plan[j].valid || plan[j].pinned != pinned || plan[j].e_off * 2 != dst0 + len) break;
+        if (!plan[j].valid || plan[j].pinned != pinned || plan[j].e_off * esz != dst0 + len) break;
         if (pinned && (const char *)tbs[j].e_bits != src0 + len) break;
-        len += (size_t)tbs[j].nof_e_bits * 2;
+        len += (size_t)tbs[j].nof_e_bits * esz;
       }
       CU(cudaMemcpyAsync((char *)pp->st_e.d + dst0, src0, len, cudaMemcpyHostToDevice, sin));
       i = j;
@@ -686,7 +701,7 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
     ctx->launches += (fe_kinds == 3 ? 2 : 1) + (any_csi ? 1 : 0) + (any_uci ? 1 : 0);
   }
   CU(cudaEventRecord(pp->ev[0], srm));
-  if (ncb) { CU(fec_launch_rm((const FecRmDesc *)pp->st_rmd.d, pp->d_softmax, ncb, max_n_out, srm)); ctx->launches++; }
+  if (ncb) { CU(fec_launch_rm((const FecRmDesc *)pp->st_rmd.d, pp->d_softmax, ncb, max_n_out, srm, ctx->llr8)); ctx->launches++; }
   CU(cudaEventRecord(pp->ev[1], srm));
   if (srm != sc) CU(cudaStreamWaitEvent(sc, pp->ev[1], 0));
   /* the certificate kernel follows the first kernel at once only while recent sub-batches needed it; otherwise pipe_finish

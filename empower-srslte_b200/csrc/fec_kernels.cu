@@ -23,19 +23,28 @@
 
 __device__ __forceinline__ int sadd(int u, int g) { return __viaddmin_s32_relu(u, g, 65535); }
 __device__ __forceinline__ int sat16(int v) { return max(min(v, 32767), -32768); }
+/* B8 = true: the int8 decoders of the 8-bit LLR path (tdec_win{sse8,avx8}, turbodecoder_win.h:97-178): the same biased
+ * representation with bias 128 and the clamp at 255, i.e. _mm_adds_epi8 in one instruction */
+template <bool B8> __device__ __forceinline__ int saddT(int u, int g) { return __viaddmin_s32_relu(u, g, B8 ? 255 : 65535); }
+template <bool B8> __device__ __forceinline__ int satT(int v) { return B8 ? max(min(v, 127), -128) : max(min(v, 32767), -32768); }
+#define BIAS_T(B8)   ((B8) ? 128 : BIAS)
+#define NEGINF_T(B8) ((B8) ? 128 : NEGINF)          /* INF = 0 in the int8 decoders (turbodecoder_win.h:128,160) */
 __device__ __forceinline__ int max8(const int *v)
 {
   return max(__vimax3_s32(v[0], v[1], v[2]), __vimax3_s32(__vimax3_s32(v[3], v[4], v[5]), v[6], v[7]));
 }
 
-/* pack 8 biased metrics as 8 true int16 (u ^ 0x8000 is the two's-complement int16 of u-32768) */
+/* pack 8 biased metrics as 8 true int16 (u ^ 0x8000 is the two's-complement int16 of u-32768); int8 decoders: the biased
+ * values 0..255 as they are */
+template <bool B8>
 __device__ __forceinline__ uint4 pack8(const int *o)
 {
+  const uint32_t x = B8 ? 0u : 0x80008000u;
   uint4 r;
-  r.x = __byte_perm(o[0], o[1], 0x5410) ^ 0x80008000u;
-  r.y = __byte_perm(o[2], o[3], 0x5410) ^ 0x80008000u;
-  r.z = __byte_perm(o[4], o[5], 0x5410) ^ 0x80008000u;
-  r.w = __byte_perm(o[6], o[7], 0x5410) ^ 0x80008000u;
+  r.x = __byte_perm(o[0], o[1], 0x5410) ^ x;
+  r.y = __byte_perm(o[2], o[3], 0x5410) ^ x;
+  r.z = __byte_perm(o[4], o[5], 0x5410) ^ x;
+  r.w = __byte_perm(o[6], o[7], 0x5410) ^ x;
   return r;
 }
 /* sign-extend the low int16 of a word: PRMT with the sign-replicate selector bit (__byte_perm masks it off) */
@@ -46,18 +55,34 @@ __device__ __forceinline__ int sext_lo(uint32_t w)
   return r;
 }
 /* unpack to TRUE signed values */
+template <bool B8>
 __device__ __forceinline__ void unpack8_true(uint4 p, int *b)
 {
-  b[0] = sext_lo(p.x); b[1] = ((int)p.x) >> 16;
-  b[2] = sext_lo(p.y); b[3] = ((int)p.y) >> 16;
-  b[4] = sext_lo(p.z); b[5] = ((int)p.z) >> 16;
-  b[6] = sext_lo(p.w); b[7] = ((int)p.w) >> 16;
+  if (B8) {
+    b[0] = (int)(p.x & 0xFFFFu) - 128; b[1] = (int)(p.x >> 16) - 128;
+    b[2] = (int)(p.y & 0xFFFFu) - 128; b[3] = (int)(p.y >> 16) - 128;
+    b[4] = (int)(p.z & 0xFFFFu) - 128; b[5] = (int)(p.z >> 16) - 128;
+    b[6] = (int)(p.w & 0xFFFFu) - 128; b[7] = (int)(p.w >> 16) - 128;
+  } else {
+    b[0] = sext_lo(p.x); b[1] = ((int)p.x) >> 16;
+    b[2] = sext_lo(p.y); b[3] = ((int)p.y) >> 16;
+    b[4] = sext_lo(p.z); b[5] = ((int)p.z) >> 16;
+    b[6] = sext_lo(p.w); b[7] = ((int)p.w) >> 16;
+  }
 }
 
-/* turbodecoder_win.h:244-261 (normalize_period 2): every even k != 0, subtract state 0, saturating */
+/* turbodecoder_win.h:244-261. 16-bit (normalize_period 2): every even k != 0, subtract state 0, saturating.
+ * int8 (normalize_max, normalize_period 1): every k != 0, subtract the maximum of the 8 states from all of them */
+template <bool B8>
 __device__ __forceinline__ void win_norm(int k, int *o)
 {
-  if (((k & 1) == 0) && k != 0) {
+  if (B8) {
+    if (k != 0) {
+      const int t = 128 - max8(o);
+#pragma unroll
+      for (int i = 0; i < 8; i++) o[i] = saddT<true>(o[i], t);
+    }
+  } else if (((k & 1) == 0) && k != 0) {
     const int t = BIAS - o[0];
 #pragma unroll
     for (int i = 1; i < 8; i++) o[i] = sadd(o[i], t);
@@ -66,30 +91,32 @@ __device__ __forceinline__ void win_norm(int k, int *o)
 }
 
 /* backward step (turbodecoder_win.h:397-418); x,y,xy are TRUE signed branch metrics */
+template <bool B8>
 __device__ __forceinline__ void win_beta_step(int *o, int x, int y)
 {
-  const int xy = sat16(x + y);
+  const int xy = satT<B8>(x + y);
   int n[8];
-  n[0] = max(sadd(o[4], xy), o[0]);
-  n[1] = max(o[4], sadd(o[0], xy));
-  n[2] = max(sadd(o[5], y), sadd(o[1], x));
-  n[3] = max(sadd(o[5], x), sadd(o[1], y));
-  n[4] = max(sadd(o[6], x), sadd(o[2], y));
-  n[5] = max(sadd(o[6], y), sadd(o[2], x));
-  n[6] = max(o[7], sadd(o[3], xy));
-  n[7] = max(sadd(o[7], xy), o[3]);
+  n[0] = max(saddT<B8>(o[4], xy), o[0]);
+  n[1] = max(o[4], saddT<B8>(o[0], xy));
+  n[2] = max(saddT<B8>(o[5], y), saddT<B8>(o[1], x));
+  n[3] = max(saddT<B8>(o[5], x), saddT<B8>(o[1], y));
+  n[4] = max(saddT<B8>(o[6], x), saddT<B8>(o[2], y));
+  n[5] = max(saddT<B8>(o[6], y), saddT<B8>(o[2], x));
+  n[6] = max(o[7], saddT<B8>(o[3], xy));
+  n[7] = max(saddT<B8>(o[7], xy), o[3]);
 #pragma unroll
   for (int i = 0; i < 8; i++) o[i] = n[i];
 }
 
 /* forward branches (turbodecoder_win.h:521-539): m = bit 0 hypothesis, n = bit 1 hypothesis */
+template <bool B8>
 __device__ __forceinline__ void win_alpha_branches(const int *o, int x, int y, int *m, int *n)
 {
-  const int xy = sat16(x + y);
-  m[0] = o[0];           m[1] = sadd(o[3], y); m[2] = sadd(o[4], y); m[3] = o[7];
-  m[4] = o[1];           m[5] = sadd(o[2], y); m[6] = sadd(o[5], y); m[7] = o[6];
-  n[0] = sadd(o[1], xy); n[1] = sadd(o[2], x); n[2] = sadd(o[5], x); n[3] = sadd(o[6], xy);
-  n[4] = sadd(o[0], xy); n[5] = sadd(o[3], x); n[6] = sadd(o[4], x); n[7] = sadd(o[7], xy);
+  const int xy = satT<B8>(x + y);
+  m[0] = o[0];                  m[1] = saddT<B8>(o[3], y); m[2] = saddT<B8>(o[4], y); m[3] = o[7];
+  m[4] = o[1];                  m[5] = saddT<B8>(o[2], y); m[6] = saddT<B8>(o[5], y); m[7] = o[6];
+  n[0] = saddT<B8>(o[1], xy);   n[1] = saddT<B8>(o[2], x); n[2] = saddT<B8>(o[5], x); n[3] = saddT<B8>(o[6], xy);
+  n[4] = saddT<B8>(o[0], xy);   n[5] = saddT<B8>(o[3], x); n[6] = saddT<B8>(o[4], x); n[7] = saddT<B8>(o[7], xy);
 }
 
 struct WinLane {           /* per-lane view of one half-iteration */
@@ -104,13 +131,14 @@ struct WinLane {           /* per-lane view of one half-iteration */
 /* int16 offset of (lane d, step k) inside one stream of the device layout (fec_tables.h) */
 __device__ __forceinline__ int win_widx(const WinLane &w, int k) { return 2 * ((((k >> 2) * w.tpc + w.dj) << 2) + (k & 3)) + w.dh; }
 
+template <bool B8>
 __device__ __forceinline__ void win_load_xy(const WinLane &w, int k, int &x, int &y)
 {
   const uint32_t t = __ldg(w.T + k);
   const int e = w.E[t & 0xFFFFu];
   const int wi = win_widx(w, k);
   const int s = (int)__ldg(w.S + wi) & w.smask;
-  x = sat16(s + e);
+  x = satT<B8>(s + e);
   y = (int)__ldg(w.Y + wi);
 }
 
@@ -134,7 +162,7 @@ uint32_t fec_win_pick_slots(const fec_geom_t *g)
   return s;
 }
 
-template <int P>
+template <int P, bool B8>
 __global__ void __launch_bounds__(FEC_WIN_THREADS, 1) fec_tdec_win_kernel(const FecDecodeArgs a)
 {
   extern __shared__ __align__(16) unsigned char smem[];
@@ -194,8 +222,8 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 1) fec_tdec_win_kernel(const 
       int o[8], x, y;
       /* ---- beta warm-up over the first 40 symbols of this sub-block (turbodecoder_win.h:321-384) ---- */
 #pragma unroll
-      for (int i = 0; i < 8; i++) o[i] = NEGINF;
-      for (int k = 39; k >= 0; k--) { win_load_xy(w, k, x, y); win_beta_step(o, x, y); win_norm(k, o); }
+      for (int i = 0; i < 8; i++) o[i] = NEGINF_T(B8);
+      for (int k = 39; k >= 0; k--) { win_load_xy<B8>(w, k, x, y); win_beta_step<B8>(o, x, y); win_norm<B8>(k, o); }
       /* lane shift: sub-block d starts from the estimate of sub-block d+1 (:347-355) */
 #pragma unroll
       for (int i = 0; i < 8; i++) o[i] = __shfl_down_sync(lane_mask, o[i], 1, P);
@@ -203,53 +231,56 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 1) fec_tdec_win_kernel(const 
         int t[8];
         t[0] = 0;
 #pragma unroll
-        for (int i = 1; i < 8; i++) t[i] = -10000;
+        for (int i = 1; i < 8; i++) t[i] = B8 ? 0 : -10000;
         for (int k = 2; k >= 0; k--) {
           const int tx = tail[2 * k], ty = tail[2 * k + 1];
-          const int txy = (short)(tx + ty);
+          /* int8: the scalar add of the tail trellis saturates upwards only, z > 127 ? 127 : (int8_t) z (:236-243) */
+#define TADD(a, b) (B8 ? (((a) + (b)) > 127 ? 127 : (int)(signed char)((a) + (b))) : (int)(short)((a) + (b)))
+          const int txy = TADD(tx, ty);
           int nn[8];
-          nn[0] = max((int)(short)(t[4] + txy), t[0]);
-          nn[1] = max(t[4], (int)(short)(t[0] + txy));
-          nn[2] = max((int)(short)(t[5] + ty), (int)(short)(t[1] + tx));
-          nn[3] = max((int)(short)(t[5] + tx), (int)(short)(t[1] + ty));
-          nn[4] = max((int)(short)(t[6] + tx), (int)(short)(t[2] + ty));
-          nn[5] = max((int)(short)(t[6] + ty), (int)(short)(t[2] + tx));
-          nn[6] = max(t[7], (int)(short)(t[3] + txy));
-          nn[7] = max((int)(short)(t[7] + txy), t[3]);
+          nn[0] = max(TADD(t[4], txy), t[0]);
+          nn[1] = max(t[4], TADD(t[0], txy));
+          nn[2] = max(TADD(t[5], ty), TADD(t[1], tx));
+          nn[3] = max(TADD(t[5], tx), TADD(t[1], ty));
+          nn[4] = max(TADD(t[6], tx), TADD(t[2], ty));
+          nn[5] = max(TADD(t[6], ty), TADD(t[2], tx));
+          nn[6] = max(t[7], TADD(t[3], txy));
+          nn[7] = max(TADD(t[7], txy), t[3]);
+#undef TADD
 #pragma unroll
           for (int i = 0; i < 8; i++) t[i] = nn[i];
         }
 #pragma unroll
-        for (int i = 0; i < 8; i++) o[i] = t[i] + BIAS;
+        for (int i = 0; i < 8; i++) o[i] = t[i] + BIAS_T(B8);
       }
       /* ---- beta main pass, checkpoint every S_CH steps (store is pre-normalisation, :419-432) ---- */
-      ckpt[tid] = pack8(o);
+      ckpt[tid] = pack8<B8>(o);
       {
         int c = 1, knext = L - S_CH;
         for (int k = L - 1; k >= 0; k--) {
-          win_load_xy(w, k, x, y);
-          win_beta_step(o, x, y);
-          if (k == knext && c < nck) { ckpt[c * nthr + tid] = pack8(o); c++; knext -= S_CH; }
-          win_norm(k, o);
+          win_load_xy<B8>(w, k, x, y);
+          win_beta_step<B8>(o, x, y);
+          if (k == knext && c < nck) { ckpt[c * nthr + tid] = pack8<B8>(o); c++; knext -= S_CH; }
+          win_norm<B8>(k, o);
         }
       }
       /* ---- alpha warm-up over the last 40 symbols (:459-506) ---- */
       int m[8], nb[8];
 #pragma unroll
-      for (int i = 0; i < 8; i++) o[i] = NEGINF;
+      for (int i = 0; i < 8; i++) o[i] = NEGINF_T(B8);
       for (int k = 0; k < 40; k++) {
-        win_load_xy(w, L - 40 + k, x, y);
-        win_alpha_branches(o, x, y, m, nb);
+        win_load_xy<B8>(w, L - 40 + k, x, y);
+        win_alpha_branches<B8>(o, x, y, m, nb);
 #pragma unroll
         for (int i = 0; i < 8; i++) o[i] = max(m[i], nb[i]);
-        win_norm(k, o);
+        win_norm<B8>(k, o);
       }
 #pragma unroll
       for (int i = 0; i < 8; i++) o[i] = __shfl_up_sync(lane_mask, o[i], 1, P);
       if (d == 0) {
-        o[0] = BIAS;
+        o[0] = BIAS_T(B8);
 #pragma unroll
-        for (int i = 1; i < 8; i++) o[i] = NEGINF;
+        for (int i = 1; i < 8; i++) o[i] = NEGINF_T(B8);
       }
       /* ---- alpha main pass: per chunk, recompute beta from its checkpoint, then alpha + LLR ---- */
       uint32_t crc = 0, wbits = 0;
@@ -258,37 +289,44 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 1) fec_tdec_win_kernel(const 
         const uint4 ck = ckpt[c * nthr + tid];
         {
           int b[8];
-          unpack8_true(ck, b);
+          unpack8_true<B8>(ck, b);
 #pragma unroll
-          for (int i = 0; i < 8; i++) b[i] += BIAS;
-          if (c > 0) win_norm(khi, b);
+          for (int i = 0; i < 8; i++) b[i] += BIAS_T(B8);
+          if (c > 0) win_norm<B8>(khi, b);
           for (int k = khi - 1; k > klo; k--) {
-            win_load_xy(w, k, x, y);
-            win_beta_step(b, x, y);
-            chunk[(k - klo - 1) * nthr + tid] = pack8(b);
-            win_norm(k, b);
+            win_load_xy<B8>(w, k, x, y);
+            win_beta_step<B8>(b, x, y);
+            chunk[(k - klo - 1) * nthr + tid] = pack8<B8>(b);
+            win_norm<B8>(k, b);
           }
         }
         for (int k = klo; k < khi; k++) {
           const uint32_t t = __ldg(w.T + k);
           const int ea = t & 0xFFFFu, nat = t >> 16;
           const int e = w.E[ea];
-          x = sat16(((int)__ldg(w.S + win_widx(w, k)) & w.smask) + e);
+          x = satT<B8>(((int)__ldg(w.S + win_widx(w, k)) & w.smask) + e);
           y = (int)__ldg(w.Y + win_widx(w, k));
-          win_alpha_branches(o, x, y, m, nb);
+          win_alpha_branches<B8>(o, x, y, m, nb);
           int b[8], v0[8], v1[8];
-          unpack8_true((k == khi - 1) ? ck : chunk[(k - klo) * nthr + tid], b);
+          unpack8_true<B8>((k == khi - 1) ? ck : chunk[(k - klo) * nthr + tid], b);
 #pragma unroll
-          for (int i = 0; i < 8; i++) { v0[i] = sadd(m[i], b[i]); v1[i] = sadd(nb[i], b[i]); }
-          int r = sat16(max8(v1) - max8(v0));
-          if (P == 8) r >>= 1;                       /* divide_output: sse16 only (turbodecoder_win.h:61,565) */
+          for (int i = 0; i < 8; i++) { v0[i] = saddT<B8>(m[i], b[i]); v1[i] = saddT<B8>(nb[i], b[i]); }
+          int r = satT<B8>(max8(v1) - max8(v0));
+          if (P == 8 || B8) r >>= 1;                 /* divide_output: sse16 and the int8 decoders (turbodecoder_win.h:61,127,159,565) */
+          if (B8) {
+            /* srslte_vec_sub_bbb (vector_simd.c:165-192): saturating in blocks of 32 array elements, the K mod 32 elements
+             * behind the last block by the scalar wrapping loop; the arrays are in sub-block order of the NATURAL bit
+             * (element k*P + d), so those are the bits at step L-1 of every lane when K mod 32 == 16 */
+            const bool wrap = (K & 31) && ((par ? nat - (nat / L) * L : k) == L - 1);
+            w.E[ea] = (int16_t)(wrap ? (int)(signed char)(r - e) : satT<true>(r - e));
+          } else
           w.E[ea] = (int16_t)(r - e);                /* next apriori = LLR - (what this decoder was given), wrapping */
           if (a.dbg_llr) a.dbg_llr[(size_t)desc.status * FEC_MAX_K + nat] = (int16_t)r;
           if (r > 0) { crc ^= __ldg(R + (K - 1 - nat)); wbits |= 1u << (k & 31); }
           if ((k & 31) == 31 || k == L - 1) { bitsw[(k >> 5) * nthr + tid] = wbits; wbits = 0; }
 #pragma unroll
           for (int i = 0; i < 8; i++) o[i] = max(m[i], nb[i]);
-          win_norm(k, o);
+          win_norm<B8>(k, o);
         }
       }
       /* ---- CRC over the K hard decisions of this half-iteration: XOR-reduce over the P lanes ---- */
@@ -365,7 +403,7 @@ __global__ void fec_tdec_small_kernel(const FecDecodeArgs a)
         int tmp[8];
 #pragma unroll
         for (int i = 0; i < 8; i++) tmp[i] = al[i] + BIAS;
-        A[tid] = pack8(tmp);
+        A[tid] = pack8<false>(tmp);
       }
       for (int k = 0; k < K; k++) {
         const uint32_t t = __ldg(T + k);
@@ -385,7 +423,7 @@ __global__ void fec_tdec_small_kernel(const FecDecodeArgs a)
         int tmp[8];
 #pragma unroll
         for (int i = 0; i < 8; i++) { al[i] = nx[i]; tmp[i] = nx[i] + BIAS; }
-        A[(k + 1) * nthr + tid] = pack8(tmp);                       /* stored before normalisation */
+        A[(k + 1) * nthr + tid] = pack8<false>(tmp);                       /* stored before normalisation */
         if ((k & 3) == 3) {
           const int z = al[0];
 #pragma unroll
@@ -426,7 +464,7 @@ __global__ void fec_tdec_small_kernel(const FecDecodeArgs a)
         for (int i = 0; i < 8; i++) be[i] = max(sp[i], sn[i]);
         if (k < K) {
           int av[8];
-          unpack8_true(A[k * nthr + tid], av);
+          unpack8_true<false>(A[k * nthr + tid], av);
           int mp = W16(sp[0] + av[0]), mn = W16(sn[0] + av[0]);
 #pragma unroll
           for (int i = 1; i < 8; i++) { mp = max(mp, W16(sp[i] + av[i])); mn = max(mn, W16(sn[i] + av[i])); }
@@ -477,8 +515,8 @@ cudaError_t fec_launch_decode(const FecDecodeArgs &a, int sm_count, cudaStream_t
     const uint32_t slots = b.slots;
     const size_t smem = fec_win_smem_bytes(&b.g, slots);
     const int grid = sm_count;                     /* persistent; CTAs find the list empty and exit in the common case */
-    if (b.g.P == 16) fec_tdec_win_kernel<16><<<grid, slots * 16, smem, st>>>(b);
-    else             fec_tdec_win_kernel<8><<<grid, slots * 8, smem, st>>>(b);
+    if (b.g.P == 16) fec_tdec_win_kernel<16, false><<<grid, slots * 16, smem, st>>>(b);
+    else             fec_tdec_win_kernel<8, false><<<grid, slots * 8, smem, st>>>(b);
     return cudaGetLastError();
   }
   const uint32_t slots = a.slots;
@@ -487,8 +525,10 @@ cudaError_t fec_launch_decode(const FecDecodeArgs &a, int sm_count, cudaStream_t
   const int per_sm = (int)((220 * 1024) / (smem + 1024));
   const int cap = sm_count * (per_sm < 1 ? 1 : per_sm);
   if (grid > cap) grid = cap;
-  if (a.g.P == 16) fec_tdec_win_kernel<16><<<grid, slots * 16, smem, st>>>(a);
-  else             fec_tdec_win_kernel<8><<<grid, slots * 8, smem, st>>>(a);
+  if (a.llr8 && a.g.P == 32)      fec_tdec_win_kernel<32, true><<<grid, slots * 32, smem, st>>>(a);
+  else if (a.llr8 && a.g.P == 16) fec_tdec_win_kernel<16, true><<<grid, slots * 16, smem, st>>>(a);
+  else if (a.g.P == 16)           fec_tdec_win_kernel<16, false><<<grid, slots * 16, smem, st>>>(a);
+  else                            fec_tdec_win_kernel<8, false><<<grid, slots * 8, smem, st>>>(a);
   return cudaGetLastError();
 }
 
@@ -623,9 +663,58 @@ __global__ void __launch_bounds__(FEC_RM_THREADS) fec_rm_rx_kernel(const FecRmDe
   fec_softmax_commit(soft_max + d.slot, max(hi, -lo));
 }
 
-cudaError_t fec_launch_rm(const FecRmDesc *descs, uint32_t *soft_max, uint32_t n, uint32_t max_n_out, cudaStream_t st)
+/* 8-bit LLR path (srslte_rm_turbo_rx_lut_8bit, rm_turbo.c:432-469,543-631): int8 LLRs in, int8 wrapping accumulation.
+ * The soft buffer keeps its int16 slots; an entry holds the int8 value the reference's buffer would hold, sign-extended
+ * (wrapping int8 addition is addition mod 256, so sums may be formed wider and reduced once). Halves the ingest, not the
+ * soft-buffer traffic; same gather structure as above without the tuning. */
+__device__ __forceinline__ uint32_t rm_sext8x2(uint32_t v)
+{
+  return __vsub2((v & 0x00FF00FFu) ^ 0x00800080u, 0x00800080u);
+}
+
+__global__ void __launch_bounds__(FEC_RM_THREADS) fec_rm_rx8_kernel(const FecRmDesc *descs, uint32_t *soft_max)
+{
+  extern __shared__ __align__(16) int16_t rm_tile[];
+  const FecRmDesc d = descs[blockIdx.x];
+  const int8_t *e8 = reinterpret_cast<const int8_t *>(d.e);
+  const int tid = threadIdx.x;
+  for (uint32_t i = tid; i < d.N; i += FEC_RM_THREADS) {
+    int acc = 0;
+    for (uint32_t j = i; j < d.E; j += d.N) acc += (int)__ldg(e8 + j);
+    uint32_t p = i + d.off;
+    if (p >= d.N) p -= d.N;
+    rm_tile[p] = (int16_t)acc;
+  }
+  if (tid == 0) rm_tile[d.N] = 0;
+  __syncthreads();
+  const uint4 *rank4 = reinterpret_cast<const uint4 *>(d.rank);
+  uint4 *soft4 = reinterpret_cast<uint4 *>(d.soft);
+  const uint32_t tb = (uint32_t)__cvta_generic_to_shared(rm_tile);
+  uint32_t mx = 0, mn = 0;
+  for (int v = tid; v < (int)d.n_out / 8; v += FEC_RM_THREADS) {
+    const uint4 rk = __ldg(rank4 + v);
+    uint4 old = make_uint4(0, 0, 0, 0);
+    if (!d.new_data) old = soft4[v];
+    const uint32_t rw[4] = {rk.x, rk.y, rk.z, rk.w};
+    uint32_t ow[4] = {old.x, old.y, old.z, old.w};
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      ow[k] = rm_sext8x2(__vadd2(ow[k], __byte_perm(rm_lds_u16(tb + (rw[k] & 0xFFFFu)), rm_lds_u16(tb + (rw[k] >> 16)), 0x5410)));
+      mx = __vmaxs2(mx, ow[k]); mn = __vmins2(mn, ow[k]);
+    }
+    soft4[v] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+  }
+  const int hi = max((int)(short)(mx & 0xFFFFu), (int)(short)(mx >> 16)), lo = min((int)(short)(mn & 0xFFFFu), (int)(short)(mn >> 16));
+  fec_softmax_commit(soft_max + d.slot, max(hi, -lo));
+}
+
+cudaError_t fec_launch_rm(const FecRmDesc *descs, uint32_t *soft_max, uint32_t n, uint32_t max_n_out, cudaStream_t st, int llr8)
 {
   if (n == 0) return cudaSuccess;
+  if (llr8) {
+    fec_rm_rx8_kernel<<<n, FEC_RM_THREADS, (size_t)max_n_out * 2, st>>>(descs, soft_max);
+    return cudaGetLastError();
+  }
   fec_rm_rx_kernel<<<n, FEC_RM_THREADS, (size_t)max_n_out * 2, st>>>(descs, soft_max);   /* N = 3K+12 <= n_out */
   return cudaGetLastError();
 }
@@ -776,9 +865,13 @@ cudaError_t fec_kernels_init(void)
   cudaError_t e;
   e = fec_pk_init();
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(fec_tdec_win_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+  e = cudaFuncSetAttribute(fec_tdec_win_kernel<16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(fec_tdec_win_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+  e = cudaFuncSetAttribute(fec_tdec_win_kernel<16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(fec_tdec_win_kernel<32, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(fec_tdec_win_kernel<8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
   if (e != cudaSuccess) return e;
   return cudaFuncSetAttribute(fec_tdec_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
 }

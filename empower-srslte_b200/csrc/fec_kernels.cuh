@@ -53,6 +53,7 @@ struct FecDecodeArgs {
   uint32_t         *trk_cont;   /* per trk_list entry: 0 = decode from the soft buffer, else half-iterations done | G << 8 and ... */
   uint32_t         *econt;      /* ... the extrinsic array of the block in scratch slot [entry index] (Es words each) */
   uint32_t          econt_cap;  /* scratch slots */
+  int               llr8;       /* 1: int8 decoders of the 8-bit LLR path (P = 16 / 32, exact kernel only) */
   /* exact kernels: optional indirect work list (NULL = all ncb code blocks) */
   const uint32_t   *list;
   const unsigned int *list_count;
@@ -139,7 +140,7 @@ cudaError_t fec_launch_decode(const FecDecodeArgs &a, int sm_count, cudaStream_t
 cudaError_t fec_launch_decode_packed(const FecDecodeArgs &a, int sm_count, cudaStream_t st, int stages);
 size_t fec_pk_smem_bytes(const fec_geom_t *g);
 cudaError_t fec_pk_init(void);
-cudaError_t fec_launch_rm(const FecRmDesc *descs, uint32_t *soft_max, uint32_t n, uint32_t max_n_out, cudaStream_t st);
+cudaError_t fec_launch_rm(const FecRmDesc *descs, uint32_t *soft_max, uint32_t n, uint32_t max_n_out, cudaStream_t st, int llr8 = 0);
 cudaError_t fec_launch_extract(const FecExtractDesc *descs, uint32_t *soft_max, uint32_t n, cudaStream_t st);
 cudaError_t fec_launch_tb_assemble(const FecTbDesc *descs, const FecCbStatus *status, const uint32_t *r24a,
                                    uint32_t n, cudaStream_t st);

@@ -49,11 +49,21 @@ int fec_segm(uint32_t tbs, uint32_t *o)
   return 0;
 }
 
-int fec_geom(uint32_t K, fec_geom_t *g)
+int fec_k_subblocks8(uint32_t K)
+{   /* srslte_tdec_autoimp_get_subblocks_8bit, AVX2 build (turbodecoder.c:392-406) */
+  if (!(K % 32) && K > 2048) return 32;
+  if (!(K % 16) && K > 800) return 16;
+  if (!(K % 8) && K > 400) return 8;
+  return 0;
+}
+
+int fec_geom(uint32_t K, fec_geom_t *g) { return fec_geom_p(K, fec_k_subblocks(K), g); }
+
+int fec_geom_p(uint32_t K, int P, fec_geom_t *g)
 {
   int idx = fec_k_index(K);
   if (idx < 0 || lte_qpp_table[idx][0] != K) return -1;
-  g->K = (int)K; g->idx = idx; g->P = fec_k_subblocks(K);
+  g->K = (int)K; g->idx = idx; g->P = P;
   g->NL = g->P ? g->P : 1;
   g->L = g->K / g->NL;
   g->Lp = (g->L + 7) & ~7;

@@ -42,7 +42,9 @@ int  fec_k_index(uint32_t K);            /* first table index with K_i >= K, -1 
 int  fec_k_size(uint32_t idx);           /* K_i or -1 */
 int  fec_k_subblocks(uint32_t K);        /* 16 / 8 / 0 (turbodecoder.c:364-376, AVX2 build) */
 int  fec_segm(uint32_t tbs, uint32_t out9[9]);   /* cbsegm.c:58-108 */
+int  fec_k_subblocks8(uint32_t K);       /* 32 / 16 / 8 / 0: class of the 8-bit LLR path (turbodecoder.c:392-406, AVX2 build) */
 int  fec_geom(uint32_t K, fec_geom_t *g);        /* -1 if K is not an LTE size */
+int  fec_geom_p(uint32_t K, int P, fec_geom_t *g);   /* the same with the sub-block count given (8-bit path: P up to 32) */
 
 /* step table, 2 parities x NL x Lp entries of (natural_position << 16 | E_address); pads = 0 */
 void fec_gen_step_table(const fec_geom_t *g, uint32_t *tab);

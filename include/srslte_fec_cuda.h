@@ -92,6 +92,15 @@ int  fec_cuda_last_phase_ms(fec_cuda_ctx_t *ctx, float out3[3]);
  * run-time-certificate variant, handed on to the exact 32-bit kernel }; everything else stayed in the first kernel */
 int  fec_cuda_last_path_counts(fec_cuda_ctx_t *ctx, uint64_t out2[2]);
 
+/* 8-bit LLR mode, the counterpart of srslte_sch_t.llr_is_8bit (sch.h:60, sch.c:344-348,362-364; set by
+ * srslte_pdsch_init_ue / srslte_pusch_init_enb from the expert.*_8bit_decoder options). While on, fec_cuda_tb_t.e_bits point
+ * to int8 LLRs (half the ingest), HARQ combining wraps at int8 (srslte_rm_turbo_rx_lut_8bit, rm_turbo.c:432-469) and code
+ * blocks decode as srslte_tdec_iteration_8bit does (turbodecoder.c:392-452): K > 2048 in the 32-sub-block int8 decoder
+ * (avx8), 800 < K <= 2048 with K mod 16 == 0 in the 16-sub-block one (sse8), every other K in the 16-bit decoder of its
+ * class on the widened values. fec_cuda_cb_t.input stays int16 (values within int8). The symbol front end
+ * (fec_cuda_decode_syms) is not available in this mode. Soft buffers must be reset when the mode changes. */
+int  fec_cuda_set_llr_8bit(fec_cuda_ctx_t *ctx, int on);
+
 /* Pinned (page-locked) host memory for e_bits / data buffers: replaces srslte_vec_malloc
  * (lib/src/phy/utils/vector.c:125-132) for the buffers handed to the decode calls. Buffers obtained here (or
  * registered with cudaHostRegister) are DMA'd directly; any other host pointer is staged through a copy. */
