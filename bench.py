@@ -200,6 +200,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-worst-case", action="store_true")
     ap.add_argument("--no-uplink", action="store_true", help="skip the PUSCH leg of the symbol front end")
+    ap.add_argument("--no-llr8", action="store_true", help="skip the 8-bit LLR leg")
+    ap.add_argument("--sigma8", type=float, default=0.30, help="AWGN std of the 8-bit LLR leg")
     ap.add_argument("--sigma-ul", type=float, default=0.17, help="AWGN std per real dimension of the synthetic 16QAM PUSCH symbols")
     ap.add_argument("--no-tx", action="store_true", help="skip the transmit-side leg (turbo encoder + rate matching on the device)")
     ap.add_argument("--no-symbols", action="store_true", help="skip the leg that starts from equalised symbols (front end)")
@@ -250,16 +252,17 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(descs, flags, steps, phases=None):
+    def timed(descs, flags, steps, phases=None, f=None, st=None):
         """time exactly `steps` SYNCHRONOUS passes (one fec_cuda_decode_tbs call each); max over ranks"""
+        f, st = f or fec, st or stream
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(stream)
+        e0.record(st)
         for _ in range(steps):
-            fec.decode_tbs(descs, flags)
+            f.decode_tbs(descs, flags)
             if phases is not None:
-                phases.append(fec.last_phase_ms())
-        e1.record(stream)
+                phases.append(f.last_phase_ms())
+        e1.record(st)
         barrier()
         ms, _ = shard.reduce_job(dist if world > 1 else None, f"cuda:{local_rank}", e0.elapsed_time(e1))
         return ms
@@ -483,6 +486,58 @@ def main():
                   value=world * B * TBS * args.steps / (ms_tx / 1e3) / 1e9, unit="Gbit/s of transport-block bits", ms_per_step=ms_tx / args.steps,
                   cbs_per_s=world * B * C_CB * args.steps / (ms_tx / 1e3), checked="first 2 transport blocks bit-exact vs the numpy synthesiser (itself pinned to srslte_dlsch_encode)")
 
+    # ---- 8-bit LLR leg: the same transport blocks as int8 LLRs (amplitude 24, the scale of the reference's
+    #      8-bit demodulator output after its int8 clipping) through fec_cuda_set_llr_8bit: half the ingest bytes, int8
+    #      combining, the int8 decoders (P = 32 for K = 5824). The int8 decoders lose ~0.7 dB: quoted at sigma 0.3 ----
+    llr8 = None
+    if not args.no_llr8:
+        synth8 = importlib.import_module("empower-srslte_b200.synth")
+        f8 = pkg.FecCuda(local_rank, max_tbs=B)
+        f8.set_llr_8bit(True)
+        st8 = torch.cuda.ExternalStream(f8.stream, device=f"cuda:{local_rank}")
+        h8 = pkg.PinnedArray((B, NBITS), np.int8)
+        rng8 = np.random.default_rng(3000 + rank)
+        e8 = synth8.encode_tbs(payload, TBS, QM, RV, NBITS)
+        tmp = np.zeros((64, NBITS), np.int16)
+        for i0 in range(0, B, 64):
+            i1 = min(B, i0 + 64)
+            synth8.awgn_llr(e8[np.arange(i0, i1) % payload.shape[0]], args.sigma8, rng8, out=tmp[: i1 - i0])
+            h8.a[i0:i1] = np.clip(np.rint(tmp[: i1 - i0] * 0.24), -128, 127)
+        d8 = torch.from_numpy(h8.a).to(f"cuda:{local_rank}")
+        sb8 = f8.softbuffer_alloc(B)
+        dd8, hd8 = (pkg.TbDesc * B)(), (pkg.TbDesc * B)()
+        for i in range(B):
+            for dsc, ep, op in ((dd8, d8.data_ptr(), d_out[1].data_ptr()), (hd8, h8.a.ctypes.data, h_out2.a.ctypes.data)):
+                dsc[i].tbs, dsc[i].Qm, dsc[i].rv, dsc[i].nof_e_bits, dsc[i].max_its = TBS, QM, RV, NBITS, MAX_ITS
+                dsc[i].softbuffer, dsc[i].new_data = sb8 + i, 1
+                dsc[i].e_bits, dsc[i].data = ep + i * NBITS, op + i * DATA_STRIDE
+        for _ in range(3):
+            f8.decode_tbs(dd8, pkg.F_DEVICE_IO)
+        n8 = max(2, args.steps // 2)
+        ms8 = timed(dd8, pkg.F_DEVICE_IO, n8, f=f8, st=st8)
+        ok8 = sum(1 for i in range(B) if dd8[i].ret == 0)
+        its8 = sum(sum(dd8[i].cb_its[:C_CB]) for i in range(B))
+        o8 = d_out[1].cpu().numpy()
+        bad8 = sum(1 for i in range(B) if dd8[i].ret == 0 and not (o8[i, :TBS // 8] == payload[i % payload.shape[0]]).all())
+        if bad8:
+            raise SystemExit(f"bench.py: {bad8} CRC-passing transport blocks of the 8-bit leg differ from the transmitted payload")
+        ph8 = []
+        for _ in range(3):
+            f8.decode_tbs(dd8, pkg.F_DEVICE_IO | pkg.F_SERIAL)
+            ph8.append(f8.last_phase_ms())
+        for _ in range(6):                       # the pipes of the ring size their pinned staging on their first use
+            f8.decode_tbs(hd8, 0)
+        ms8e = timed(hd8, 0, n8, f=f8, st=st8)
+        ok8e = sum(1 for i in range(B) if hd8[i].ret == 0)
+        llr8 = dict(workload="the same transport blocks as int8 LLRs (amplitude 24, sigma %.2f), fec_cuda_set_llr_8bit" % args.sigma8,
+                    value=allsum(ok8) * TBS * n8 / (ms8 / 1e3) / 1e9, unit=UNIT, ms_per_step=ms8 / n8, tb_ok_frac=allsum(ok8) / (world * B),
+                    halfits_per_cb=allsum(its8) / (world * B * C_CB),
+                    phases_ms=dict(rate_dematch=sum(p[0] for p in ph8) / 3, turbo_decode=sum(p[1] for p in ph8) / 3, tb_assemble_crc24a=sum(p[2] for p in ph8) / 3),
+                    e2e=dict(value=allsum(ok8e) * TBS * n8 / (ms8e / 1e3) / 1e9, unit=UNIT, ms_per_step=ms8e / n8, h2d_bytes_per_step=B * NBITS + B * C_CB * (32 + 48) + B * 520,
+                             note="one blocking call per step (not the two-in-flight submission of the headline e2e)"),
+                    kernel="fec_tdec_win_kernel<32,true>: exact 32-bit-lane kernel, one sub-block per thread; not tuned")
+        f8.close()
+
     # ---- latency of the reference's call shape: ONE transport block per blocking call (srslte_dlsch_decode as pdsch.c:816
     #      makes it, level 2 of INTEGRATION.md), host buffers, everything inside the timed call ----
     lat = None
@@ -563,7 +618,7 @@ def main():
                     e2e=dict(value=e2e_val, unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h, ms_per_step=ms_e / args.steps,
                              sync_ms_per_step=ms_e_sync / args.steps),
                     sync_ms_per_step=ms_sync / args.steps,
-                    gpu_launches=launches, clocks=clocks, roofline=roof, worst_case_8_halfits=worst, frontend_symbols=front, transmit_side=tx, single_tb_latency=lat, cpu_baseline=cpu)
+                    gpu_launches=launches, clocks=clocks, roofline=roof, worst_case_8_halfits=worst, frontend_symbols=front, transmit_side=tx, llr_8bit=llr8, single_tb_latency=lat, cpu_baseline=cpu)
         print(json.dumps(line), flush=True)
     fec.close()
     if world > 1:

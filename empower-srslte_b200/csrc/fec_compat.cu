@@ -98,14 +98,8 @@ extern "C" int srslte_tdec_get_nof_iterations(srslte_tdec_t *h) { return h ? (in
 
 extern "C" uint32_t srslte_tdec_autoimp_get_subblocks(uint32_t nof_bits) { return (uint32_t)fec_k_subblocks(nof_bits); }
 
-/* sub-block count of the 8-bit decoders, AVX2 build (turbodecoder.c:392-406); only the mapping is provided, not the decoders */
-extern "C" uint32_t srslte_tdec_autoimp_get_subblocks_8bit(uint32_t nof_bits)
-{
-  if ((nof_bits % 32) == 0 && nof_bits > 2048) return 32;
-  if ((nof_bits % 16) == 0 && nof_bits > 800) return 16;
-  if ((nof_bits % 8) == 0 && nof_bits > 400) return 8;
-  return 0;
-}
+/* sub-block count of the 8-bit decoders, AVX2 build (turbodecoder.c:392-406) */
+extern "C" uint32_t srslte_tdec_autoimp_get_subblocks_8bit(uint32_t nof_bits) { return (uint32_t)fec_k_subblocks8(nof_bits); }
 
 /* the caller's input is in the sub-block layout of srslte_rm_turbo_rx_lut_(…, true) unless force_not_sb was set
  * or the block size has no windowed decoder (turbodecoder_iter.h:48,61-70,91-103): bring it to the natural layout */
@@ -120,12 +114,14 @@ static void compat_take_input(srslte_tdec_t *h, const int16_t *in)
 
 /* Runs the code block from its LLRs for (n_iter + 1) half-iterations: the device decoder is deterministic, so this
  * IS the state the reference reaches by its (n_iter+1)-th incremental call (turbodecoder_iter.h:73-147). */
-static int compat_run(srslte_tdec_t *h, uint8_t *output, uint32_t halfits)
+static int compat_run(srslte_tdec_t *h, uint8_t *output, uint32_t halfits, int llr8 = 0)
 {
   fec_cuda_cb_t cb;
   memset(&cb, 0, sizeof(cb));
   cb.K = h->fec_K; cb.max_its = halfits; cb.crc_type = 1; cb.llr = h->fec_input; cb.out = output;
+  fec_cuda_set_llr_8bit((fec_cuda_ctx_t *)h->fec_ctx, llr8);       /* the shared context is switched under g_mu */
   const int r = fec_cuda_decode_cbs((fec_cuda_ctx_t *)h->fec_ctx, &cb, 1, FEC_CUDA_F_NO_EARLY_STOP);
+  fec_cuda_set_llr_8bit((fec_cuda_ctx_t *)h->fec_ctx, 0);
   if (r) fprintf(stderr, "libsrslte_fec_cuda: %s\n", fec_cuda_last_error((fec_cuda_ctx_t *)h->fec_ctx));
   return r;
 }
@@ -150,14 +146,35 @@ extern "C" int srslte_tdec_run_all(srslte_tdec_t *h, int16_t *input, uint8_t *ou
   return SRSLTE_SUCCESS;
 }
 
-extern "C" void srslte_tdec_iteration_8bit(srslte_tdec_t *, int8_t *, uint8_t *)
+/* 8-bit entry points (turbodecoder.c:408-452,536-563): the int8 input is in the sub-block layout of
+ * srslte_rm_turbo_rx_lut_8bit for the 8-bit class of K (32 / 16 / 8 sub-blocks) unless force_not_sb was set or K <= 400 */
+static void compat_take_input8(srslte_tdec_t *h, const int8_t *in)
 {
-  fprintf(stderr, "srslte_tdec_iteration_8bit: the 8-bit LLR path is not provided by libsrslte_fec_cuda\n");
+  const uint32_t K = h->fec_K;
+  fec_geom_t g;
+  fec_geom_p(K, fec_k_subblocks8(K), &g);
+  const int sb = !(g.P == 0 || h->fec_force_not_sb);
+  for (uint32_t t = 0; t < 3 * K + 12; t++) h->fec_input[t] = in[sb ? fec_soft_offset_ref(&g, (int)t, 1) : (int)t];
 }
-extern "C" int srslte_tdec_run_all_8bit(srslte_tdec_t *, int8_t *, uint8_t *, uint32_t, uint32_t)
+
+extern "C" void srslte_tdec_iteration_8bit(srslte_tdec_t *h, int8_t *input, uint8_t *output)
 {
-  fprintf(stderr, "srslte_tdec_run_all_8bit: the 8-bit LLR path is not provided by libsrslte_fec_cuda\n");
-  return SRSLTE_ERROR;
+  if (!h || h->fec_magic != COMPAT_MAGIC || !h->fec_K || !input || !output) return;
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (h->n_iter == 0) compat_take_input8(h, input);
+  if (compat_run(h, output, h->n_iter + 1, 1) == 0) h->n_iter++;
+}
+
+extern "C" int srslte_tdec_run_all_8bit(srslte_tdec_t *h, int8_t *input, uint8_t *output, uint32_t nof_iterations, uint32_t long_cb)
+{
+  if (srslte_tdec_new_cb(h, long_cb)) return SRSLTE_ERROR;       /* turbodecoder.c:545-563 */
+  if (!input || !output) return SRSLTE_ERROR;
+  std::lock_guard<std::mutex> lk(g_mu);
+  compat_take_input8(h, input);
+  if (nof_iterations == 0) return SRSLTE_SUCCESS;
+  if (compat_run(h, output, nof_iterations, 1)) return SRSLTE_ERROR;
+  h->n_iter = nof_iterations;
+  return SRSLTE_SUCCESS;
 }
 
 /* ================================================================= rate de-matching (rm_turbo.c:267-430) ==== */
@@ -238,8 +255,8 @@ extern "C" void srslte_softbuffer_rx_reset_tbs(srslte_softbuffer_rx_t *q, uint32
 extern "C" void srslte_softbuffer_rx_reset(srslte_softbuffer_rx_t *q) { if (q) srslte_softbuffer_rx_reset_cb(q, q->max_cb); }
 
 /* ================================================================= decode_tb (sch.c:437-486) ==== */
-extern "C" int srslte_sch_decode_tb_cuda(srslte_softbuffer_rx_t *softbuffer, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits,
-                                         int16_t *e_bits, uint8_t *data, uint32_t max_iterations, uint32_t *nof_iterations)
+static int compat_decode_tb(srslte_softbuffer_rx_t *softbuffer, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits,
+                            const void *e_bits, int llr8, uint8_t *data, uint32_t max_iterations, uint32_t *nof_iterations)
 {
   compat_sb_t *s = compat_sb(softbuffer);
   if (!s || !data || !e_bits) return SRSLTE_ERROR_INVALID_INPUTS;          /* sch.c:444-448 */
@@ -257,8 +274,11 @@ extern "C" int srslte_sch_decode_tb_cuda(srslte_softbuffer_rx_t *softbuffer, uin
   fec_cuda_tb_t t;
   memset(&t, 0, sizeof(t));
   t.tbs = tbs; t.Qm = Qm; t.rv = rv; t.nof_e_bits = nof_e_bits; t.max_its = max_iterations; t.softbuffer = s->id;
-  t.new_data = s->pending_new; t.e_bits = e_bits; t.data = data;
-  if (fec_cuda_decode_tbs(ctx, &t, 1, 0)) { fprintf(stderr, "libsrslte_fec_cuda: %s\n", fec_cuda_last_error(ctx)); return SRSLTE_ERROR; }
+  t.new_data = s->pending_new; t.e_bits = (const int16_t *)e_bits; t.data = data;
+  fec_cuda_set_llr_8bit(ctx, llr8);                                            /* q->llr_is_8bit (sch.c:344-348,362-364) */
+  const int rc = fec_cuda_decode_tbs(ctx, &t, 1, 0);
+  fec_cuda_set_llr_8bit(ctx, 0);
+  if (rc) { fprintf(stderr, "libsrslte_fec_cuda: %s\n", fec_cuda_last_error(ctx)); return SRSLTE_ERROR; }
   s->pending_new = 0;
   for (uint32_t c = 0; c < seg[1] && c < softbuffer->max_cb; c++) softbuffer->cb_crc[c] = t.cb_crc[c] != 0;
   bool all = true;
@@ -266,6 +286,20 @@ extern "C" int srslte_sch_decode_tb_cuda(srslte_softbuffer_rx_t *softbuffer, uin
   softbuffer->tb_crc = all;                                                    /* sch.c:404-408 */
   if (nof_iterations) *nof_iterations = t.avg_its;                             /* sch.c:420 */
   return t.ret;
+}
+
+extern "C" int srslte_sch_decode_tb_cuda(srslte_softbuffer_rx_t *softbuffer, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits,
+                                         int16_t *e_bits, uint8_t *data, uint32_t max_iterations, uint32_t *nof_iterations)
+{
+  return compat_decode_tb(softbuffer, tbs, Qm, rv, nof_e_bits, e_bits, 0, data, max_iterations, nof_iterations);
+}
+
+/* the same for q->llr_is_8bit: int8 LLRs. A soft buffer must be reset between uses in the two modes (as in the reference,
+ * whose int8 and int16 views of buffer_f are incompatible). */
+extern "C" int srslte_sch_decode_tb_cuda_8bit(srslte_softbuffer_rx_t *softbuffer, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits,
+                                              int8_t *e_bits, uint8_t *data, uint32_t max_iterations, uint32_t *nof_iterations)
+{
+  return compat_decode_tb(softbuffer, tbs, Qm, rv, nof_e_bits, e_bits, 1, data, max_iterations, nof_iterations);
 }
 
 /* ================================================================= encode_tb_off (sch.c:188-296) ==== */

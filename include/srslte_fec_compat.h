@@ -9,7 +9,9 @@
  * everything else is private storage of this library.  A maintainer building inside the srsLTE tree includes the
  * reference headers instead (the prototypes are identical) and keeps the static asserts of csrc/fec_compat.cu.
  *
- * 16-bit LLR path only: the *_8bit entry points return SRSLTE_ERROR.
+ * 16-bit and 8-bit LLR paths: srslte_tdec_iteration_8bit / srslte_tdec_run_all_8bit and
+ * srslte_sch_decode_tb_cuda_8bit; srslte_rm_turbo_rx_lut_8bit on host buffers is not exported (the rate de-matcher of
+ * the 8-bit path runs inside the transport-block call).
  * No CPU fallback: without a usable CUDA device every init returns SRSLTE_ERROR and every decode returns -1.
  */
 #ifndef SRSLTE_FEC_COMPAT_H
@@ -50,8 +52,8 @@ uint32_t srslte_tdec_autoimp_get_subblocks(uint32_t nof_bits);
 uint32_t srslte_tdec_autoimp_get_subblocks_8bit(uint32_t nof_bits);
 void     srslte_tdec_iteration(srslte_tdec_t *h, int16_t *input, uint8_t *output);
 int      srslte_tdec_run_all(srslte_tdec_t *h, int16_t *input, uint8_t *output, uint32_t nof_iterations, uint32_t long_cb);
-void     srslte_tdec_iteration_8bit(srslte_tdec_t *h, int8_t *input, uint8_t *output);                       /* not provided: no-op */
-int      srslte_tdec_run_all_8bit(srslte_tdec_t *h, int8_t *input, uint8_t *output, uint32_t nof_iterations, uint32_t long_cb); /* -1 */
+void     srslte_tdec_iteration_8bit(srslte_tdec_t *h, int8_t *input, uint8_t *output);                       /* turbodecoder.c:536-543 */
+int      srslte_tdec_run_all_8bit(srslte_tdec_t *h, int8_t *input, uint8_t *output, uint32_t nof_iterations, uint32_t long_cb); /* turbodecoder.c:545-563 */
 
 /* ---- rate de-matching: lib/include/srslte/phy/fec/rm_turbo.h:51-94 ---- */
 void srslte_rm_turbo_gentables(void);                     /* tables are built per K on first use: nothing to do */
@@ -80,6 +82,10 @@ void srslte_softbuffer_rx_reset_cb(srslte_softbuffer_rx_t *q, uint32_t nof_cb);
  * q->max_iterations, *nof_iterations receives q->nof_iterations (sch.c:420).  Returns 0 / -1 / -2 like decode_tb. */
 int  srslte_sch_decode_tb_cuda(srslte_softbuffer_rx_t *softbuffer, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits,
                                int16_t *e_bits, uint8_t *data, uint32_t max_iterations, uint32_t *nof_iterations);
+
+/* decode_tb with q->llr_is_8bit (sch.c:344-348,362-364): e_bits are int8 */
+int  srslte_sch_decode_tb_cuda_8bit(srslte_softbuffer_rx_t *softbuffer, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits,
+                                    int8_t *e_bits, uint8_t *data, uint32_t max_iterations, uint32_t *nof_iterations);
 
 /* ---- encode_tb_off (sch.c:188-296): the body a patched sch.c calls on the transmit side. data = NULL (the reference
  * re-reads its tx soft buffer for a retransmission) is not supported: pass the transport block again. w_offset = 0. */

@@ -33,6 +33,10 @@ def lib():
     l.srslte_softbuffer_rx_reset_tbs.argtypes = [C.c_void_p, C.c_uint32]
     l.srslte_sch_decode_tb_cuda.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p,
                                             C.c_uint32, C.c_void_p]
+    l.srslte_tdec_iteration_8bit.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    l.srslte_tdec_iteration_8bit.restype = None
+    l.srslte_tdec_run_all_8bit.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]
+    l.srslte_sch_decode_tb_cuda_8bit.argtypes = l.srslte_sch_decode_tb_cuda.argtypes
     return l
 
 
@@ -142,3 +146,65 @@ def test_encode_tb_wrapper_golden(lib):
             assert lib.srslte_sch_encode_tb_cuda(c["tbs"], c["Qm"], t["rv"], c["nbits"], P(data), P(e)) == 0
             assert (np.unpackbits(e)[: c["nbits"]] == np.unpackbits(z[f"e_{ci}_{tx}"])[: c["nbits"]]).all(), (c["id"], tx)
     assert lib.srslte_sch_encode_tb_cuda(75376, 6, 0, 90000, None, P(np.zeros(8, np.uint8))) == -2
+
+
+@pytest.mark.parametrize("case", list(G.tdec8_cases()), ids=lambda c: c["id"])
+def test_tdec_8bit_run_all_and_iteration_golden(lib, case):
+    """srslte_tdec_run_all_8bit / srslte_tdec_iteration_8bit (turbodecoder.c:536-563) on natural-layout int8 input with
+    force_not_sb: the golden bytes after every half-iteration of the reference's 8-bit decoders"""
+    K = case["K"]
+    h = _tdec(lib)
+    lib.srslte_tdec_force_not_sb(h)
+    inp = np.ascontiguousarray(case["inp"])
+    out = np.zeros(K // 8, np.uint8)
+    assert lib.srslte_tdec_run_all_8bit(h, P(inp), P(out), case["nof"], K) == 0
+    assert lib.srslte_tdec_get_nof_iterations(h) == case["nof"]
+    assert (out == case["bytes"][case["nof"] - 1]).all()
+    assert lib.srslte_tdec_new_cb(h, K) == 0
+    for n in range(case["nof"]):
+        lib.srslte_tdec_iteration_8bit(h, P(inp), P(out))
+        assert (out == case["bytes"][n]).all(), (K, n)
+    lib.srslte_tdec_free(h)
+
+
+def test_tdec_8bit_sb_layout_input_vs_oracle(lib, orc):
+    """without force_not_sb the int8 input is in the sub-block layout of srslte_rm_turbo_rx_lut_8bit for the 8-bit class of K"""
+    for K in (408, 1024, 2112, 6144):
+        E = 3 * K + 12 + 300
+        e = (int_gauss(E, 37 * K) % 101 - 50).astype(np.int8)
+        soft = np.zeros(2 * 18600, np.int8)
+        assert orc.orc_rm_rx8(P(e), E, K, 0, 1, P(soft)) == 0
+        want = np.zeros((3, K // 8), np.uint8)
+        t = orc.orc_tb_new()
+        orc.orc_tb_free(t)
+        nat = np.zeros(3 * K + 12, np.int8)
+        P8 = orc.orc_subblocks8(K)
+        for tt in range(3 * K + 12):
+            nat[tt] = soft[orc.orc_rm_soft_index(tt, K, P8)]
+        assert orc.orc_tdec_halfits8(K, P(nat), 3, P(want), None) == 0
+        h = _tdec(lib)
+        out = np.zeros(K // 8, np.uint8)
+        assert lib.srslte_tdec_run_all_8bit(h, P(soft), P(out), 3, K) == 0
+        assert (out == want[2]).all(), K
+        lib.srslte_tdec_free(h)
+
+
+@pytest.mark.parametrize("case", list(G.tb8_cases()), ids=lambda c: c["id"])
+def test_decode_tb_8bit_with_reference_softbuffer_calls(lib, case):
+    """decode_tb with q->llr_is_8bit: one srslte_sch_decode_tb_cuda_8bit per (re)transmission of the golden sequences"""
+    tbs = case["tbs"]
+    nC = importlib.import_module("empower-srslte_b200").cbsegm(tbs)["C"]
+    q = C.create_string_buffer(40)
+    assert lib.srslte_softbuffer_rx_init(q, 100) == 0
+    lib.srslte_softbuffer_rx_reset_tbs(q, tbs)
+    for tx in case["tx"]:
+        data = np.zeros(tbs // 8 + 3 + 768, np.uint8)
+        noi = C.c_uint32(0)
+        llr = np.ascontiguousarray(tx["llr"])
+        ret = lib.srslte_sch_decode_tb_cuda_8bit(q, tbs, case["Qm"], tx["rv"], case["nbits"], P(llr), P(data), case["max_its"], C.byref(noi))
+        assert ret == tx["ret"] and noi.value == tx["avg_its"]
+        if ret == 0:
+            assert (data[: tbs // 8 + 3] == tx["data"][: tbs // 8 + 3]).all()
+        crc = (C.c_bool * 13).from_address(C.c_void_p.from_buffer(q, 24).value)
+        assert [bool(crc[i]) for i in range(nC)] == [bool(v) for v in tx["crc"][:nC]]
+    lib.srslte_softbuffer_rx_free(q)

@@ -23,3 +23,8 @@ if t:
 l = j.get("single_tb_latency")
 if l:
     print("single-TB call latency: median %.0f us, p90 %.0f us, min %.0f us" % (l["median_us"], l["p90_us"], l["min_us"]))
+q = j.get("llr_8bit")
+if q:
+    print("8-bit LLR leg: value %.2f Gbps step %.3f ms ok %.3f its %.2f | e2e %.2f Gbps (%.2f ms) | phases %s" % (
+        q["value"], q["ms_per_step"], q["tb_ok_frac"], q["halfits_per_cb"], q["e2e"]["value"], q["e2e"]["ms_per_step"],
+        {k: round(v, 3) for k, v in q["phases_ms"].items()}))
