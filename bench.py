@@ -511,7 +511,7 @@ def main():
                 dsc[i].tbs, dsc[i].Qm, dsc[i].rv, dsc[i].nof_e_bits, dsc[i].max_its = TBS, QM, RV, NBITS, MAX_ITS
                 dsc[i].softbuffer, dsc[i].new_data = sb8 + i, 1
                 dsc[i].e_bits, dsc[i].data = ep + i * NBITS, op + i * DATA_STRIDE
-        for _ in range(3):
+        for _ in range(8):                       # every pipe of the ring sizes its scratch on first use
             f8.decode_tbs(dd8, pkg.F_DEVICE_IO)
         n8 = max(2, args.steps // 2)
         ms8 = timed(dd8, pkg.F_DEVICE_IO, n8, f=f8, st=st8)

@@ -142,6 +142,61 @@ __device__ __forceinline__ void win_load_xy(const WinLane &w, int k, int &x, int
   y = (int)__ldg(w.Y + wi);
 }
 
+/* Four trellis steps of a lane in three 16-byte loads: the device layout keeps steps 4b..4b+3 of a lane PAIR in one 16-byte
+ * group per stream, and the step table is contiguous per lane. The loops below walk the sub-block in such groups and fetch
+ * group b-1 / b+1 while group b is computed: with one sub-block per thread and a handful of warps per SM the kernel is bound
+ * by the latency of these loads, not by their bandwidth (measured: ~970 cycles per step with one load triple per step). */
+struct WinBlk { uint4 s, y, t; };
+
+__device__ __forceinline__ WinBlk win_fetch(const WinLane &w, int kb)
+{
+  WinBlk b;
+  const int g = kb * w.tpc + w.dj;
+  b.s = w.smask ? __ldg(reinterpret_cast<const uint4 *>(w.S) + g) : make_uint4(0, 0, 0, 0);
+  b.y = __ldg(reinterpret_cast<const uint4 *>(w.Y) + g);
+  b.t = __ldg(reinterpret_cast<const uint4 *>(w.T) + kb);
+  return b;
+}
+__device__ __forceinline__ uint32_t win_comp(const uint4 &v, int j) { return j == 0 ? v.x : j == 1 ? v.y : j == 2 ? v.z : v.w; }
+__device__ __forceinline__ int win_half(uint32_t v, int dh) { return (int)(short)(dh ? v >> 16 : v); }
+
+/* k = khi-1 down to klo: f(k, s, y, t) with s, y the TRUE systematic (0 for decoder 2) and parity values, t the step-table word */
+template <typename F>
+__device__ __forceinline__ void win_for_desc(const WinLane &w, int khi, int klo, F &&f)
+{
+  if (khi <= klo) return;
+  const int b_lo = klo >> 2;
+  int kb = (khi - 1) >> 2;
+  WinBlk cur = win_fetch(w, kb), nxt = cur;
+  for (; kb >= b_lo; kb--) {
+    if (kb > b_lo) nxt = win_fetch(w, kb - 1);
+#pragma unroll
+    for (int j = 3; j >= 0; j--) {
+      const int k = 4 * kb + j;
+      if (k < khi && k >= klo) f(k, win_half(win_comp(cur.s, j), w.dh), win_half(win_comp(cur.y, j), w.dh), win_comp(cur.t, j));
+    }
+    cur = nxt;
+  }
+}
+/* k = klo up to khi-1 */
+template <typename F>
+__device__ __forceinline__ void win_for_asc(const WinLane &w, int klo, int khi, F &&f)
+{
+  if (khi <= klo) return;
+  const int b_hi = (khi - 1) >> 2;
+  int kb = klo >> 2;
+  WinBlk cur = win_fetch(w, kb), nxt = cur;
+  for (; kb <= b_hi; kb++) {
+    if (kb < b_hi) nxt = win_fetch(w, kb + 1);
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int k = 4 * kb + j;
+      if (k < khi && k >= klo) f(k, win_half(win_comp(cur.s, j), w.dh), win_half(win_comp(cur.y, j), w.dh), win_comp(cur.t, j));
+    }
+    cur = nxt;
+  }
+}
+
 size_t fec_win_smem_bytes(const fec_geom_t *g, uint32_t slots)
 {
   const size_t nthr = (size_t)slots * g->P;
@@ -219,11 +274,13 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 1) fec_tdec_win_kernel(const 
       const int16_t *tail = desc.soft + 3 * SS + (par ? 6 : 0);   /* x at [0,2,4], parity at [1,3,5] */
       const uint32_t *R = a.crcpow[desc.crc_sel];
 
-      int o[8], x, y;
+      int o[8];
       /* ---- beta warm-up over the first 40 symbols of this sub-block (turbodecoder_win.h:321-384) ---- */
 #pragma unroll
       for (int i = 0; i < 8; i++) o[i] = NEGINF_T(B8);
-      for (int k = 39; k >= 0; k--) { win_load_xy<B8>(w, k, x, y); win_beta_step<B8>(o, x, y); win_norm<B8>(k, o); }
+      win_for_desc(w, 40, 0, [&](int k, int sv, int yv, uint32_t t) {
+        win_beta_step<B8>(o, satT<B8>(sv + (int)w.E[t & 0xFFFFu]), yv); win_norm<B8>(k, o);
+      });
       /* lane shift: sub-block d starts from the estimate of sub-block d+1 (:347-355) */
 #pragma unroll
       for (int i = 0; i < 8; i++) o[i] = __shfl_down_sync(lane_mask, o[i], 1, P);
@@ -257,24 +314,22 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 1) fec_tdec_win_kernel(const 
       ckpt[tid] = pack8<B8>(o);
       {
         int c = 1, knext = L - S_CH;
-        for (int k = L - 1; k >= 0; k--) {
-          win_load_xy<B8>(w, k, x, y);
-          win_beta_step<B8>(o, x, y);
+        win_for_desc(w, L, 0, [&](int k, int sv, int yv, uint32_t t) {
+          win_beta_step<B8>(o, satT<B8>(sv + (int)w.E[t & 0xFFFFu]), yv);
           if (k == knext && c < nck) { ckpt[c * nthr + tid] = pack8<B8>(o); c++; knext -= S_CH; }
           win_norm<B8>(k, o);
-        }
+        });
       }
       /* ---- alpha warm-up over the last 40 symbols (:459-506) ---- */
       int m[8], nb[8];
 #pragma unroll
       for (int i = 0; i < 8; i++) o[i] = NEGINF_T(B8);
-      for (int k = 0; k < 40; k++) {
-        win_load_xy<B8>(w, L - 40 + k, x, y);
-        win_alpha_branches<B8>(o, x, y, m, nb);
+      win_for_asc(w, L - 40, L, [&](int k, int sv, int yv, uint32_t t) {
+        win_alpha_branches<B8>(o, satT<B8>(sv + (int)w.E[t & 0xFFFFu]), yv, m, nb);
 #pragma unroll
         for (int i = 0; i < 8; i++) o[i] = max(m[i], nb[i]);
-        win_norm<B8>(k, o);
-      }
+        win_norm<B8>(k - (L - 40), o);
+      });
 #pragma unroll
       for (int i = 0; i < 8; i++) o[i] = __shfl_up_sync(lane_mask, o[i], 1, P);
       if (d == 0) {
@@ -293,20 +348,16 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 1) fec_tdec_win_kernel(const 
 #pragma unroll
           for (int i = 0; i < 8; i++) b[i] += BIAS_T(B8);
           if (c > 0) win_norm<B8>(khi, b);
-          for (int k = khi - 1; k > klo; k--) {
-            win_load_xy<B8>(w, k, x, y);
-            win_beta_step<B8>(b, x, y);
+          win_for_desc(w, khi, klo + 1, [&](int k, int sv, int yv, uint32_t t) {
+            win_beta_step<B8>(b, satT<B8>(sv + (int)w.E[t & 0xFFFFu]), yv);
             chunk[(k - klo - 1) * nthr + tid] = pack8<B8>(b);
             win_norm<B8>(k, b);
-          }
+          });
         }
-        for (int k = klo; k < khi; k++) {
-          const uint32_t t = __ldg(w.T + k);
+        win_for_asc(w, klo, khi, [&](int k, int sv, int yv, uint32_t t) {
           const int ea = t & 0xFFFFu, nat = t >> 16;
           const int e = w.E[ea];
-          x = satT<B8>(((int)__ldg(w.S + win_widx(w, k)) & w.smask) + e);
-          y = (int)__ldg(w.Y + win_widx(w, k));
-          win_alpha_branches<B8>(o, x, y, m, nb);
+          win_alpha_branches<B8>(o, satT<B8>(sv + e), yv, m, nb);
           int b[8], v0[8], v1[8];
           unpack8_true<B8>((k == khi - 1) ? ck : chunk[(k - klo) * nthr + tid], b);
 #pragma unroll
@@ -327,7 +378,7 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 1) fec_tdec_win_kernel(const 
 #pragma unroll
           for (int i = 0; i < 8; i++) o[i] = max(m[i], nb[i]);
           win_norm<B8>(k, o);
-        }
+        });
       }
       /* ---- CRC over the K hard decisions of this half-iteration: XOR-reduce over the P lanes ---- */
 #pragma unroll
