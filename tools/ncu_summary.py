@@ -1,48 +1,21 @@
-#!/usr/bin/env python
-"""Summarise ncu outputs into small text files for profiles/ (run in the build container, no GPU needed).
-   python tools/ncu_summary.py launches gpurun_out/launches.csv   -> per-kernel launch count / total / mean us / share
-   python tools/ncu_summary.py full gpurun_out/prof.ncu-rep        -> key counters of each captured launch"""
-import csv
-import subprocess
-import sys
-from collections import defaultdict
-
-KEYS = ["gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "launch__registers_per_thread", "launch__shared_mem_per_block",
-        "launch__occupancy_limit", "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__issue_active.avg.pct_of_peak_sustained_active",
-        "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active",
-        "sm__inst_executed_pipe_fmaheavy", "sm__inst_executed_pipe_lsu.avg.pct", "sm__inst_executed_pipe_xu.avg.pct", "sm__inst_executed_pipe_uniform",
-        "smsp__inst_executed.sum", "sm__throughput.avg.pct_of_peak_sustained_elapsed", "dram__bytes_read.sum", "dram__bytes_write.sum",
-        "dram__throughput.avg.pct_of_peak_sustained_elapsed", "lts__t_bytes.sum", "lts__t_sector_hit_rate.pct", "l1tex__t_bytes.sum",
-        "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum",
-        "smsp__average_warps_issue_stalled", "smsp__average_warp_latency_per_inst_issued", "sm__cycles_elapsed.avg ", "sm__cycles_active.avg",
-        "smsp__cycles_active.avg", "lts__throughput.avg.pct_of_peak_sustained_elapsed", "l1tex__throughput.avg.pct_of_peak_sustained_elapsed"]
-
-
-def launches(path):
-    rows = [r for r in csv.reader(l for l in open(path) if l.startswith('"'))]
-    h = rows[0]
-    ki, vi, ui = h.index("Kernel Name"), h.index("Metric Value"), h.index("Metric Unit")
-    agg = defaultdict(list)
-    for r in rows[1:]:
-        v = float(r[vi].replace(",", ""))
-        v = v / 1e3 if r[ui] in ("ns", "nsecond") else v
-        agg[r[ki].split("(")[0]].append(v)
-    tot = sum(sum(v) for v in agg.values())
-    print(f"{'kernel':60s} {'launches':>8s} {'total_us':>12s} {'mean_us':>10s} {'share':>7s}")
-    for k, v in sorted(agg.items(), key=lambda kv: -sum(kv[1])):
-        print(f"{k[:60]:60s} {len(v):8d} {sum(v):12.1f} {sum(v) / len(v):10.1f} {sum(v) / tot:7.3f}")
-
-
-def full(path):
-    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
-    rows = list(csv.reader(out.splitlines()))
-    h, units = rows[0], rows[1]
-    for r in rows[2:]:
-        print("==", r[h.index("Kernel Name")])
-        for i, c in enumerate(h):
-            if any(c.startswith(k.strip()) for k in KEYS):
-                print(f"  {c} = {r[i]} {units[i]}")
-
-
-if __name__ == "__main__":
-    {"launches": launches, "full": full}[sys.argv[1]](sys.argv[2])
+"""print the metrics of an ncu report that the profiles/ summaries quote: python tools/ncu_summary.py file.ncu-rep"""
+import csv, subprocess, sys
+out = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+rows = list(csv.reader(out.splitlines()))
+hdr, vals = rows[0], rows[-1]
+d = dict(zip(hdr, vals))
+print("kernel:", d.get("Kernel Name"))
+keys = ["gpu__time_duration.sum", "launch__registers_per_thread", "launch__grid_size", "launch__block_size", "launch__occupancy_limit",
+        "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__issue_active.avg.pct", "sm__inst_executed_pipe_alu",
+        "sm__inst_executed_pipe_fma", "sm__inst_executed_pipe_lsu", "dram__bytes_read.sum", "dram__bytes_write.sum", "smsp__inst_executed.sum",
+        "l1tex__data_bank_conflicts_pipe_lsu_mem_shared", "sm__throughput.avg.pct_of_peak_sustained_elapsed", "dram__throughput.avg.pct",
+        "launch__shared_mem_per_block", "smsp__warps_eligible.avg.per_cycle_active", "lts__t_sector_hit_rate"]
+for k in hdr:
+    if any(k.startswith(x) for x in keys):
+        print(k, d[k])
+    elif "smsp__average_warp" in k and "issue_stalled" in k and "not_issued" not in k and k.endswith(".ratio"):
+        try:
+            if float(d[k].replace(",", "")) >= 0.1:
+                print(k, d[k])
+        except ValueError:
+            pass
