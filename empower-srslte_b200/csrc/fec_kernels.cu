@@ -729,12 +729,41 @@ __global__ void __launch_bounds__(FEC_RM_THREADS) fec_rm_rx8_kernel(const FecRmD
   const FecRmDesc d = descs[blockIdx.x];
   const int8_t *e8 = reinterpret_cast<const int8_t *>(d.e);
   const int tid = threadIdx.x;
-  for (uint32_t i = tid; i < d.N; i += FEC_RM_THREADS) {
-    int acc = 0;
-    for (uint32_t j = i; j < d.E; j += d.N) acc += (int)__ldg(e8 + j);
-    uint32_t p = i + d.off;
-    if (p >= d.N) p -= d.N;
-    rm_tile[p] = (int16_t)acc;
+  if (d.E <= d.N) {
+    /* no repetition: a rotated copy, read as 32-bit words (4 LLRs) behind a head that brings the slice to 4-byte alignment,
+     * 4 independent loads in flight per thread; entries never transmitted are 0 */
+    const uint32_t head = min((uint32_t)((4 - (reinterpret_cast<size_t>(e8) & 3)) & 3), d.E);
+    const uint32_t nq = (d.E - head) >> 2;
+    const uint32_t *e32 = reinterpret_cast<const uint32_t *>(e8 + head);
+    for (uint32_t q0 = tid; q0 < nq; q0 += 4 * FEC_RM_THREADS) {
+      uint32_t v[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) { const uint32_t q = q0 + u * FEC_RM_THREADS; v[u] = q < nq ? __ldg(e32 + q) : 0u; }
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const uint32_t q = q0 + u * FEC_RM_THREADS;
+        if (q < nq) {
+          uint32_t p = head + 4 * q + d.off;
+          if (p >= d.N) p -= d.N;
+#pragma unroll
+          for (int b = 0; b < 4; b++) { rm_tile[p] = (int16_t)(int8_t)(v[u] >> (8 * b)); if (++p == d.N) p = 0; }
+        }
+      }
+    }
+    for (uint32_t i = tid; i < d.N; i += FEC_RM_THREADS) {
+      if (i >= head && i < head + 4 * nq) continue;
+      uint32_t p = i + d.off;
+      if (p >= d.N) p -= d.N;
+      rm_tile[p] = i < d.E ? (int16_t)__ldg(e8 + i) : (int16_t)0;
+    }
+  } else {
+    for (uint32_t i = tid; i < d.N; i += FEC_RM_THREADS) {
+      int acc = 0;
+      for (uint32_t j = i; j < d.E; j += d.N) acc += (int)__ldg(e8 + j);    /* repeats accumulate when E > 3K+12 */
+      uint32_t p = i + d.off;
+      if (p >= d.N) p -= d.N;
+      rm_tile[p] = (int16_t)acc;
+    }
   }
   if (tid == 0) rm_tile[d.N] = 0;
   __syncthreads();
