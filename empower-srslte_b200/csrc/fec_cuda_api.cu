@@ -267,7 +267,7 @@ static int ktab_get(fec_cuda_ctx_t *ctx, uint32_t K, ktab_t **out)
       }
       free(pa); free(pc);
     }
-    t->slots = t->g.P ? fec_win_pick_slots(&t->g) : 0;
+    t->slots = t->g.P ? fec_win_pick_slots(&t->g, ctx->llr8 && t->g.P >= 16) : 0;
     t->ready = 1;
   }
   *out = t;

@@ -123,7 +123,7 @@ struct WinLane {           /* per-lane view of one half-iteration */
   const int16_t  *S;       /* systematic stream of this lane (ignored when smask == 0) */
   const int16_t  *Y;       /* parity stream of this lane */
   const uint32_t *T;       /* step table of this lane and parity */
-  int16_t        *E;       /* extrinsic array of this code block (shared memory) */
+  void           *E;       /* extrinsic array of this code block (shared memory): int16, int8 in the int8 decoders */
   int             smask;   /* -1: x = sat(S + E) (decoder 1);  0: x = E (decoder 2) */
   int             tpc, dj, dh; /* pairs per code block, pair index and half of this lane */
 };
@@ -131,16 +131,38 @@ struct WinLane {           /* per-lane view of one half-iteration */
 /* int16 offset of (lane d, step k) inside one stream of the device layout (fec_tables.h) */
 __device__ __forceinline__ int win_widx(const WinLane &w, int k) { return 2 * ((((k >> 2) * w.tpc + w.dj) << 2) + (k & 3)) + w.dh; }
 
-template <bool B8>
-__device__ __forceinline__ void win_load_xy(const WinLane &w, int k, int &x, int &y)
+template <bool B8> __device__ __forceinline__ int win_e(const WinLane &w, uint32_t idx)
 {
-  const uint32_t t = __ldg(w.T + k);
-  const int e = w.E[t & 0xFFFFu];
-  const int wi = win_widx(w, k);
-  const int s = (int)__ldg(w.S + wi) & w.smask;
-  x = satT<B8>(s + e);
-  y = (int)__ldg(w.Y + wi);
+  return B8 ? (int)static_cast<const int8_t *>(w.E)[idx] : (int)static_cast<const int16_t *>(w.E)[idx];
 }
+template <bool B8> __device__ __forceinline__ void win_e_store(const WinLane &w, uint32_t idx, int v)
+{
+  if (B8) static_cast<int8_t *>(w.E)[idx] = (int8_t)v; else static_cast<int16_t *>(w.E)[idx] = (int16_t)v;
+}
+
+/* beta checkpoint / chunk entries: 8 state metrics of one lane. 16-bit decoders: 8 x int16 (16 bytes); int8 decoders: the
+ * biased values 0..255 as 8 bytes, which with the int8 extrinsic array halves the CTA's shared memory (4 CTAs per SM) */
+template <bool B8> struct WinCk;
+template <> struct WinCk<false> {
+  typedef uint4 type;
+  static __device__ __forceinline__ uint4 pack(const int *o) { return pack8<false>(o); }
+  static __device__ __forceinline__ void unpack_true(uint4 p, int *b) { unpack8_true<false>(p, b); }
+};
+template <> struct WinCk<true> {
+  typedef uint2 type;
+  static __device__ __forceinline__ uint2 pack(const int *o)
+  {
+    uint2 r;
+    r.x = __byte_perm(__byte_perm(o[0], o[1], 0x4040), __byte_perm(o[2], o[3], 0x4040), 0x5410);
+    r.y = __byte_perm(__byte_perm(o[4], o[5], 0x4040), __byte_perm(o[6], o[7], 0x4040), 0x5410);
+    return r;
+  }
+  static __device__ __forceinline__ void unpack_true(uint2 p, int *b)
+  {
+    b[0] = (int)(p.x & 0xFFu) - 128; b[1] = (int)((p.x >> 8) & 0xFFu) - 128; b[2] = (int)((p.x >> 16) & 0xFFu) - 128; b[3] = (int)(p.x >> 24) - 128;
+    b[4] = (int)(p.y & 0xFFu) - 128; b[5] = (int)((p.y >> 8) & 0xFFu) - 128; b[6] = (int)((p.y >> 16) & 0xFFu) - 128; b[7] = (int)(p.y >> 24) - 128;
+  }
+};
 
 /* Four trellis steps of a lane in three 16-byte loads: the device layout keeps steps 4b..4b+3 of a lane PAIR in one 16-byte
  * group per stream, and the step table is contiguous per lane. The loops below walk the sub-block in such groups and fetch
@@ -197,28 +219,29 @@ __device__ __forceinline__ void win_for_asc(const WinLane &w, int klo, int khi, 
   }
 }
 
-size_t fec_win_smem_bytes(const fec_geom_t *g, uint32_t slots)
+size_t fec_win_smem_bytes(const fec_geom_t *g, uint32_t slots, int llr8)
 {
   const size_t nthr = (size_t)slots * g->P;
   const size_t nck = (g->L + S_CH - 1) / S_CH, nw = (g->L + 31) / 32;
+  const size_t esz = llr8 ? 1 : 2, cksz = llr8 ? 8 : 16;
   size_t b = 0;
-  b += (((size_t)slots * g->P * g->LpE * 2) + 15) & ~(size_t)15;   /* E */
-  b += nck * nthr * 16;                                            /* beta checkpoints */
-  b += (size_t)(S_CH - 1) * nthr * 16;                             /* beta chunk buffer */
+  b += (((size_t)slots * g->P * g->LpE * esz) + 15) & ~(size_t)15; /* E */
+  b += nck * nthr * cksz;                                          /* beta checkpoints */
+  b += (size_t)(S_CH - 1) * nthr * cksz;                           /* beta chunk buffer */
   b += nw * nthr * 4;                                              /* decision words per lane */
   b += (size_t)slots * ((g->K + 31) / 32) * 4;                     /* output assembly */
   return b;
 }
 
-uint32_t fec_win_pick_slots(const fec_geom_t *g)
+uint32_t fec_win_pick_slots(const fec_geom_t *g, int llr8)
 {
   uint32_t s = FEC_WIN_THREADS / g->P;
-  while (s > 1 && fec_win_smem_bytes(g, s) > 220 * 1024) s--;
+  while (s > 1 && fec_win_smem_bytes(g, s, llr8) > 220 * 1024) s--;
   return s;
 }
 
 template <int P, bool B8>
-__global__ void __launch_bounds__(FEC_WIN_THREADS, 1) fec_tdec_win_kernel(const FecDecodeArgs a)
+__global__ void __launch_bounds__(FEC_WIN_THREADS, B8 ? 3 : 1) fec_tdec_win_kernel(const FecDecodeArgs a)
 {
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ int s_cb[FEC_WIN_THREADS / 8], s_n[FEC_WIN_THREADS / 8], s_fresh[FEC_WIN_THREADS / 8];
@@ -230,11 +253,13 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 1) fec_tdec_win_kernel(const 
   const int nck = (L + S_CH - 1) / S_CH, nw = (L + 31) / 32, kw = (K + 31) / 32;
   const unsigned lane_mask = (P == 32) ? 0xFFFFFFFFu : (((1u << P) - 1u) << ((tid & 31) & ~(P - 1)));
 
+  typedef typename WinCk<B8>::type ck_t;
+  constexpr int ESZ = B8 ? 1 : 2;
   size_t off = 0;
-  int16_t *E = (int16_t *)smem + (size_t)slot * P * LpE;
-  off += (((size_t)slots * P * LpE * 2) + 15) & ~(size_t)15;
-  uint4 *ckpt = (uint4 *)(smem + off);  off += (size_t)nck * nthr * 16;
-  uint4 *chunk = (uint4 *)(smem + off); off += (size_t)(S_CH - 1) * nthr * 16;
+  unsigned char *E = smem + (size_t)slot * P * LpE * ESZ;
+  off += (((size_t)slots * P * LpE * ESZ) + 15) & ~(size_t)15;
+  ck_t *ckpt = (ck_t *)(smem + off);  off += (size_t)nck * nthr * sizeof(ck_t);
+  ck_t *chunk = (ck_t *)(smem + off); off += (size_t)(S_CH - 1) * nthr * sizeof(ck_t);
   uint32_t *bitsw = (uint32_t *)(smem + off); off += (size_t)nw * nthr * 4;
   uint32_t *outw = (uint32_t *)(smem + off) + (size_t)slot * kw;
 
@@ -255,7 +280,7 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 1) fec_tdec_win_kernel(const 
     if (!__syncthreads_or(cb >= 0)) break;
     if (cb >= 0 && s_fresh[slot]) {               /* apriori = 0 before the first half-iteration */
       uint32_t *e32 = (uint32_t *)E;
-      for (int i = d; i < P * LpE / 2; i += P) e32[i] = 0;
+      for (int i = d; i < P * LpE * ESZ / 4; i += P) e32[i] = 0;
     }
     __syncthreads();
     if (d == 0) s_fresh[slot] = 0;
@@ -279,7 +304,7 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 1) fec_tdec_win_kernel(const 
 #pragma unroll
       for (int i = 0; i < 8; i++) o[i] = NEGINF_T(B8);
       win_for_desc(w, 40, 0, [&](int k, int sv, int yv, uint32_t t) {
-        win_beta_step<B8>(o, satT<B8>(sv + (int)w.E[t & 0xFFFFu]), yv); win_norm<B8>(k, o);
+        win_beta_step<B8>(o, satT<B8>(sv + win_e<B8>(w, t & 0xFFFFu)), yv); win_norm<B8>(k, o);
       });
       /* lane shift: sub-block d starts from the estimate of sub-block d+1 (:347-355) */
 #pragma unroll
@@ -311,12 +336,12 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 1) fec_tdec_win_kernel(const 
         for (int i = 0; i < 8; i++) o[i] = t[i] + BIAS_T(B8);
       }
       /* ---- beta main pass, checkpoint every S_CH steps (store is pre-normalisation, :419-432) ---- */
-      ckpt[tid] = pack8<B8>(o);
+      ckpt[tid] = WinCk<B8>::pack(o);
       {
         int c = 1, knext = L - S_CH;
         win_for_desc(w, L, 0, [&](int k, int sv, int yv, uint32_t t) {
-          win_beta_step<B8>(o, satT<B8>(sv + (int)w.E[t & 0xFFFFu]), yv);
-          if (k == knext && c < nck) { ckpt[c * nthr + tid] = pack8<B8>(o); c++; knext -= S_CH; }
+          win_beta_step<B8>(o, satT<B8>(sv + win_e<B8>(w, t & 0xFFFFu)), yv);
+          if (k == knext && c < nck) { ckpt[c * nthr + tid] = WinCk<B8>::pack(o); c++; knext -= S_CH; }
           win_norm<B8>(k, o);
         });
       }
@@ -325,7 +350,7 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 1) fec_tdec_win_kernel(const 
 #pragma unroll
       for (int i = 0; i < 8; i++) o[i] = NEGINF_T(B8);
       win_for_asc(w, L - 40, L, [&](int k, int sv, int yv, uint32_t t) {
-        win_alpha_branches<B8>(o, satT<B8>(sv + (int)w.E[t & 0xFFFFu]), yv, m, nb);
+        win_alpha_branches<B8>(o, satT<B8>(sv + win_e<B8>(w, t & 0xFFFFu)), yv, m, nb);
 #pragma unroll
         for (int i = 0; i < 8; i++) o[i] = max(m[i], nb[i]);
         win_norm<B8>(k - (L - 40), o);
@@ -341,25 +366,25 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 1) fec_tdec_win_kernel(const 
       uint32_t crc = 0, wbits = 0;
       for (int c = nck - 1; c >= 0; c--) {
         const int khi = L - c * S_CH, klo = max(0, khi - S_CH);
-        const uint4 ck = ckpt[c * nthr + tid];
+        const ck_t ck = ckpt[c * nthr + tid];
         {
           int b[8];
-          unpack8_true<B8>(ck, b);
+          WinCk<B8>::unpack_true(ck, b);
 #pragma unroll
           for (int i = 0; i < 8; i++) b[i] += BIAS_T(B8);
           if (c > 0) win_norm<B8>(khi, b);
           win_for_desc(w, khi, klo + 1, [&](int k, int sv, int yv, uint32_t t) {
-            win_beta_step<B8>(b, satT<B8>(sv + (int)w.E[t & 0xFFFFu]), yv);
-            chunk[(k - klo - 1) * nthr + tid] = pack8<B8>(b);
+            win_beta_step<B8>(b, satT<B8>(sv + win_e<B8>(w, t & 0xFFFFu)), yv);
+            chunk[(k - klo - 1) * nthr + tid] = WinCk<B8>::pack(b);
             win_norm<B8>(k, b);
           });
         }
         win_for_asc(w, klo, khi, [&](int k, int sv, int yv, uint32_t t) {
           const int ea = t & 0xFFFFu, nat = t >> 16;
-          const int e = w.E[ea];
+          const int e = win_e<B8>(w, ea);
           win_alpha_branches<B8>(o, satT<B8>(sv + e), yv, m, nb);
           int b[8], v0[8], v1[8];
-          unpack8_true<B8>((k == khi - 1) ? ck : chunk[(k - klo) * nthr + tid], b);
+          WinCk<B8>::unpack_true((k == khi - 1) ? ck : chunk[(k - klo) * nthr + tid], b);
 #pragma unroll
           for (int i = 0; i < 8; i++) { v0[i] = saddT<B8>(m[i], b[i]); v1[i] = saddT<B8>(nb[i], b[i]); }
           int r = satT<B8>(max8(v1) - max8(v0));
@@ -369,9 +394,9 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 1) fec_tdec_win_kernel(const 
              * behind the last block by the scalar wrapping loop; the arrays are in sub-block order of the NATURAL bit
              * (element k*P + d), so those are the bits at step L-1 of every lane when K mod 32 == 16 */
             const bool wrap = (K & 31) && ((par ? nat - (nat / L) * L : k) == L - 1);
-            w.E[ea] = (int16_t)(wrap ? (int)(signed char)(r - e) : satT<true>(r - e));
+            win_e_store<B8>(w, ea, wrap ? (int)(signed char)(r - e) : satT<true>(r - e));
           } else
-          w.E[ea] = (int16_t)(r - e);                /* next apriori = LLR - (what this decoder was given), wrapping */
+          win_e_store<B8>(w, ea, r - e);             /* next apriori = LLR - (what this decoder was given), wrapping */
           if (a.dbg_llr) a.dbg_llr[(size_t)desc.status * FEC_MAX_K + nat] = (int16_t)r;
           if (r > 0) { crc ^= __ldg(R + (K - 1 - nat)); wbits |= 1u << (k & 31); }
           if ((k & 31) == 31 || k == L - 1) { bitsw[(k >> 5) * nthr + tid] = wbits; wbits = 0; }
@@ -564,14 +589,14 @@ cudaError_t fec_launch_decode(const FecDecodeArgs &a, int sm_count, cudaStream_t
     FecDecodeArgs b = a;
     b.list = a.exact_list; b.list_count = a.exact_count; b.queue = a.queue + 1;
     const uint32_t slots = b.slots;
-    const size_t smem = fec_win_smem_bytes(&b.g, slots);
+    const size_t smem = fec_win_smem_bytes(&b.g, slots, 0);
     const int grid = sm_count;                     /* persistent; CTAs find the list empty and exit in the common case */
     if (b.g.P == 16) fec_tdec_win_kernel<16, false><<<grid, slots * 16, smem, st>>>(b);
     else             fec_tdec_win_kernel<8, false><<<grid, slots * 8, smem, st>>>(b);
     return cudaGetLastError();
   }
   const uint32_t slots = a.slots;
-  const size_t smem = fec_win_smem_bytes(&a.g, slots);
+  const size_t smem = fec_win_smem_bytes(&a.g, slots, a.llr8);
   int grid = (int)((a.ncb + slots - 1) / slots);
   const int per_sm = (int)((220 * 1024) / (smem + 1024));
   const int cap = sm_count * (per_sm < 1 ? 1 : per_sm);

@@ -109,8 +109,8 @@ cudaError_t fec_launch_frontend(const FecFeDesc *descs, float *csi_max, const ui
                                 uint32_t ntb, uint32_t max_re, int any_csi, int any_uci, int kinds /* 1: DL present, 2: UL present */, cudaStream_t st);
 extern "C" void fec_gen_gold_tables(uint32_t *x2_masks, uint32_t *x1_states);
 
-size_t fec_win_smem_bytes(const fec_geom_t *g, uint32_t slots);
-uint32_t fec_win_pick_slots(const fec_geom_t *g);
+size_t fec_win_smem_bytes(const fec_geom_t *g, uint32_t slots, int llr8);
+uint32_t fec_win_pick_slots(const fec_geom_t *g, int llr8);
 /* ---- transmit side (fec_tx.cu) ---- */
 #define FEC_TX_W 194              /* words per d-stream in shared memory: K + 4 <= 6148 bits */
 struct FecTxTbDesc { const uint8_t *data; uint32_t tbs; uint8_t *crc3; uint32_t *e_out; uint32_t e_words; };   /* e_out: zeroed by the CRC kernel */
