@@ -236,12 +236,23 @@ size_t fec_win_smem_bytes(const fec_geom_t *g, uint32_t slots, int llr8)
 uint32_t fec_win_pick_slots(const fec_geom_t *g, int llr8)
 {
   uint32_t s = FEC_WIN_THREADS / g->P;
+  if (llr8) {
+    /* the int8 kernel is latency-bound: take the CTA size that keeps most code blocks resident per SM (shared memory
+     * 227 KB with 1 KB reserved per CTA; 128 registers per thread -> 512 threads) */
+    uint32_t best = 1, best_cbs = 0;
+    for (uint32_t t = s; t >= 1; t--) {
+      uint32_t ctas = (uint32_t)((227 * 1024) / (fec_win_smem_bytes(g, t, 1) + 1024));
+      if (ctas * t * g->P > 512) ctas = 512 / (t * g->P);
+      if (ctas * t > best_cbs) { best_cbs = ctas * t; best = t; }
+    }
+    return best;
+  }
   while (s > 1 && fec_win_smem_bytes(g, s, llr8) > 220 * 1024) s--;
   return s;
 }
 
 template <int P, bool B8>
-__global__ void __launch_bounds__(FEC_WIN_THREADS, B8 ? 3 : 1) fec_tdec_win_kernel(const FecDecodeArgs a)
+__global__ void __launch_bounds__(FEC_WIN_THREADS, B8 ? 4 : 1) fec_tdec_win_kernel(const FecDecodeArgs a)
 {
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ int s_cb[FEC_WIN_THREADS / 8], s_n[FEC_WIN_THREADS / 8], s_fresh[FEC_WIN_THREADS / 8];
@@ -598,7 +609,7 @@ cudaError_t fec_launch_decode(const FecDecodeArgs &a, int sm_count, cudaStream_t
   const uint32_t slots = a.slots;
   const size_t smem = fec_win_smem_bytes(&a.g, slots, a.llr8);
   int grid = (int)((a.ncb + slots - 1) / slots);
-  const int per_sm = (int)((220 * 1024) / (smem + 1024));
+  const int per_sm = (int)(((a.llr8 ? 227 : 220) * 1024) / (smem + 1024));
   const int cap = sm_count * (per_sm < 1 ? 1 : per_sm);
   if (grid > cap) grid = cap;
   if (a.llr8 && a.g.P == 32)      fec_tdec_win_kernel<32, true><<<grid, slots * 32, smem, st>>>(a);
