@@ -676,8 +676,24 @@ __device__ PK_EPI_INLINE void pk_finish_block(int par, uint32_t Eb, const uint16
 /* A code block that leaves the a-priori range in mid-decode continues in the certificate kernel where it stands: its state
  * is the extrinsic array E (shared memory) and the half-iteration count. E goes to a scratch slot indexed like the hand-over
  * list entry; blocks beyond the scratch capacity restart from their soft buffer (cont = 0). Cold path, kept out of line. */
+#ifndef PK_HO_INLINE
+#define PK_HO_INLINE 0
+#endif
+#ifndef PK_HO_REFILL_CALL
+#define PK_HO_REFILL_CALL 0    /* 1: the refill loop also goes through pk_hand_over — measured 3 % slower on the headline workload
+                                  (MAP kernel 1.455 vs 1.412 ms, tools/experiments/ab_handover.sh): a second call site in the
+                                  refill loop costs the hot path registers although it never runs there */
+#endif
+#ifndef PK_HO_CONT
+#define PK_HO_CONT 1
+#endif
+#if PK_HO_INLINE
+#define PK_HO_ATTR __forceinline__
+#else
+#define PK_HO_ATTR __noinline__
+#endif
 template <int TPC>
-__device__ __noinline__ void pk_hand_over(unsigned int *trk_count, uint32_t *trk_list, uint32_t *trk_cont, uint32_t *econt, uint32_t econt_cap,
+__device__ PK_HO_ATTR void pk_hand_over(unsigned int *trk_count, uint32_t *trk_list, uint32_t *trk_cont, uint32_t *econt, uint32_t econt_cap,
                                           uint32_t cb, const uint32_t *Eslot, int Es, uint32_t n1, uint32_t G, int j, int g, unsigned gmask)
 {
   uint32_t idx = 0;
@@ -791,7 +807,11 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
       }
       if (!TRK && 2 * M + M / 2 > FEC_PK_GMAX) {    /* outside the a-priori range now or (decoder 1: G = 2M + max|extrinsic|) certain to
                                                        leave it with the second iteration: certificate kernel from the start */
+#if PK_HO_REFILL_CALL
         pk_hand_over<TPC>(a.trk_count, a.trk_list, a.trk_cont, a.econt, a.econt_cap, q, Eslot, Es, 0u, 0u, j, g, gmask);
+#else
+        if (j == 0) { const uint32_t idx = atomicAdd(a.trk_count, 1u); a.trk_list[idx] = q; a.trk_cont[idx] = 0; }
+#endif
         continue;
       }
       cb = (int)q; n = 0; G = 2 * M;
@@ -876,7 +896,11 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
           if (j == 0) a.exact_list[atomicAdd(a.exact_count, 1u)] = (uint32_t)cb;   /* re-decoded from scratch by the exact kernel */
           cb = -1;
         } else if (!TRK && G > FEC_PK_GMAX) {
+#if PK_HO_CONT
           pk_hand_over<TPC>(a.trk_count, a.trk_list, a.trk_cont, a.econt, a.econt_cap, (uint32_t)cb, Eslot, Es, (uint32_t)n1, G, j, g, gmask);   /* the certificate kernel goes on from here */
+#else
+          if (j == 0) { const uint32_t idx = atomicAdd(a.trk_count, 1u); a.trk_list[idx] = (uint32_t)cb; a.trk_cont[idx] = 0; }
+#endif
           cb = -1;
         } else n = n1;
       }
