@@ -924,9 +924,15 @@ __global__ void __launch_bounds__(256) fec_tb_assemble_kernel(const FecTbDesc *d
                                                               const uint32_t *r24a)
 {
   const FecTbDesc &d = descs[blockIdx.x];
-  __shared__ uint32_t s_red[8];
+  __shared__ uint32_t s_red[8], s_tab[256];
   __shared__ int s_ok;
   const int tid = threadIdx.x;
+  {
+    uint32_t c = (uint32_t)tid << 16;              /* (tid * x^24) mod g, g = 0x1864CFB */
+#pragma unroll
+    for (int i = 0; i < 8; i++) c = ((c << 1) ^ ((c & 0x800000u) ? 0x864CFBu : 0u)) & 0xFFFFFFu;
+    s_tab[tid] = c;
+  }
   if (tid == 0) {
     int ok = 1;
     for (uint32_t c = 0; c < d.C; c++) if (d.st_idx[c] >= 0 && !status[d.st_idx[c]].crc_ok) ok = 0;
@@ -944,15 +950,23 @@ __global__ void __launch_bounds__(256) fec_tb_assemble_kernel(const FecTbDesc *d
   }
   int ret = -1;
   if (s_ok) {
+    /* CRC-24A of the tbs bits (crc.c:144-158): every thread runs the byte-table CRC over its own contiguous run of bytes (one
+     * shared-memory lookup per byte), then moves its 24-bit remainder to its place, remainder(x) * x^(bits behind the run) mod g,
+     * through the power table r24a[m] = x^(m+24) mod g (one lookup per set remainder bit); the XOR of all is the CRC */
     uint32_t acc = 0;
-    const uint32_t nbytes = d.tbs / 8;
-    for (uint32_t b = tid; b < nbytes; b += blockDim.x) {
-      uint32_t v = d.data[b];
-      while (v) {
-        const int hb = 31 - __clz(v);            /* bit value 1<<hb is stream bit 8b + (7-hb) */
-        acc ^= r24a[d.tbs - 1 - (8 * b + (7 - hb))];
-        v &= ~(1u << hb);
-      }
+    const uint32_t nbytes = d.tbs / 8, per = (nbytes + blockDim.x - 1) / blockDim.x;
+    const uint32_t b0 = min(nbytes, tid * per), b1 = min(nbytes, b0 + per);
+    if (b1 > b0) {
+      uint32_t c = 0;
+      for (uint32_t b = b0; b < b1; b++) c = ((c << 8) ^ s_tab[((c >> 16) ^ d.data[b]) & 0xFFu]) & 0xFFFFFFu;
+      const uint32_t nshift = 8 * (nbytes - b1);
+      if (nshift == 0) acc = c;
+      else
+        while (c) {
+          const uint32_t hb = 31 - __clz(c), e = hb + nshift;
+          acc ^= e >= 24 ? r24a[e - 24] : (1u << e);
+          c &= ~(1u << hb);
+        }
     }
 #pragma unroll
     for (int s = 16; s > 0; s >>= 1) acc ^= __shfl_xor_sync(0xFFFFFFFFu, acc, s);
