@@ -240,9 +240,10 @@ uint32_t fec_win_pick_slots(const fec_geom_t *g, int llr8)
     /* the int8 kernel is latency-bound: take the CTA size that keeps most code blocks resident per SM (shared memory
      * 227 KB with 1 KB reserved per CTA; 128 registers per thread -> 512 threads) */
     uint32_t best = 1, best_cbs = 0;
+    s = FEC_WIN_THREADS / (g->P / 2);             /* two lanes per thread (fec_tdec_win8p_kernel) */
     for (uint32_t t = s; t >= 1; t--) {
       uint32_t ctas = (uint32_t)((227 * 1024) / (fec_win_smem_bytes(g, t, 1) + 1024));
-      if (ctas * t * g->P > 512) ctas = 512 / (t * g->P);
+      if (ctas * t * (g->P / 2) > 512) ctas = 512 / (t * (g->P / 2));
       if (ctas * t > best_cbs) { best_cbs = ctas * t; best = t; }
     }
     return best;
@@ -445,6 +446,320 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, B8 ? 4 : 1) fec_tdec_win_kern
 }
 
 /* =====================================================================================================
+ * int8 decoders, two sub-blocks per thread: the same arithmetic as fec_tdec_win_kernel<P, true> with the lane pair (2j, 2j+1)
+ * of the device layout in the two 16-bit halves of a register. State metrics are biased by 128 per half; the saturating
+ * int8 add of the reference is VIADDMNMX.S16x2.RELU with the clamp 0x00FF00FF (max(min(u + g, 255), 0) per half), so one
+ * instruction serves two lanes: half the instruction count of the one-lane kernel, which is bound by exactly that.
+ * Shared memory per code block is unchanged (int8 extrinsics, 8 bytes per lane and checkpoint).
+ * ===================================================================================================== */
+#define P2_CLAMP 0x00FF00FFu
+#define P2_BIAS  0x00800080u
+__device__ __forceinline__ uint32_t p2_sadd(uint32_t u, uint32_t g) { return __viaddmin_s16x2_relu(u, g, P2_CLAMP); }
+__device__ __forceinline__ uint32_t p2_sat8(uint32_t v) { return __vmins2(__vmaxs2(v, 0xFF80FF80u), 0x007F007Fu); }
+__device__ __forceinline__ uint32_t p2_addsat8(uint32_t a, uint32_t b) { return __vmins2(__viaddmax_s16x2(a, b, 0xFF80FF80u), 0x007F007Fu); }
+__device__ __forceinline__ uint32_t p2_max8(const uint32_t *v)
+{
+  return __vmaxs2(__vimax3_s16x2(v[0], v[1], v[2]), __vimax3_s16x2(__vimax3_s16x2(v[3], v[4], v[5]), v[6], v[7]));
+}
+__device__ __forceinline__ void p2_norm(int k, uint32_t *o)
+{
+  if (k != 0) {
+    const uint32_t t = __vsub2(P2_BIAS, p2_max8(o));
+#pragma unroll
+    for (int i = 0; i < 8; i++) o[i] = p2_sadd(o[i], t);
+  }
+}
+__device__ __forceinline__ void p2_beta_step(uint32_t *o, uint32_t x, uint32_t y)
+{
+  const uint32_t xy = p2_addsat8(x, y);
+  uint32_t n[8];
+  n[0] = __vmaxs2(p2_sadd(o[4], xy), o[0]);
+  n[1] = __vmaxs2(o[4], p2_sadd(o[0], xy));
+  n[2] = __vmaxs2(p2_sadd(o[5], y), p2_sadd(o[1], x));
+  n[3] = __vmaxs2(p2_sadd(o[5], x), p2_sadd(o[1], y));
+  n[4] = __vmaxs2(p2_sadd(o[6], x), p2_sadd(o[2], y));
+  n[5] = __vmaxs2(p2_sadd(o[6], y), p2_sadd(o[2], x));
+  n[6] = __vmaxs2(o[7], p2_sadd(o[3], xy));
+  n[7] = __vmaxs2(p2_sadd(o[7], xy), o[3]);
+#pragma unroll
+  for (int i = 0; i < 8; i++) o[i] = n[i];
+}
+__device__ __forceinline__ void p2_alpha_branches(const uint32_t *o, uint32_t x, uint32_t y, uint32_t *m, uint32_t *n)
+{
+  const uint32_t xy = p2_addsat8(x, y);
+  m[0] = o[0];              m[1] = p2_sadd(o[3], y); m[2] = p2_sadd(o[4], y); m[3] = o[7];
+  m[4] = o[1];              m[5] = p2_sadd(o[2], y); m[6] = p2_sadd(o[5], y); m[7] = o[6];
+  n[0] = p2_sadd(o[1], xy); n[1] = p2_sadd(o[2], x); n[2] = p2_sadd(o[5], x); n[3] = p2_sadd(o[6], xy);
+  n[4] = p2_sadd(o[0], xy); n[5] = p2_sadd(o[3], x); n[6] = p2_sadd(o[4], x); n[7] = p2_sadd(o[7], xy);
+}
+/* 8 packed state words (two biased bytes each) <-> 16 bytes: word i/2 = [o_i.lo, o_i.hi, o_i+1.lo, o_i+1.hi] */
+__device__ __forceinline__ uint4 p2_pack(const uint32_t *o)
+{
+  return make_uint4(__byte_perm(o[0], o[1], 0x6420), __byte_perm(o[2], o[3], 0x6420), __byte_perm(o[4], o[5], 0x6420), __byte_perm(o[6], o[7], 0x6420));
+}
+__device__ __forceinline__ void p2_unpack(uint4 p, uint32_t *b)     /* biased */
+{
+  b[0] = __byte_perm(p.x, 0, 0x4140); b[1] = __byte_perm(p.x, 0, 0x4342);
+  b[2] = __byte_perm(p.y, 0, 0x4140); b[3] = __byte_perm(p.y, 0, 0x4342);
+  b[4] = __byte_perm(p.z, 0, 0x4140); b[5] = __byte_perm(p.z, 0, 0x4342);
+  b[6] = __byte_perm(p.w, 0, 0x4140); b[7] = __byte_perm(p.w, 0, 0x4342);
+}
+
+struct P2Lane {
+  const uint4 *S, *Y;        /* systematic / parity stream of the code block (16-byte groups of 4 steps per lane pair) */
+  const uint4 *T0, *T1;      /* step tables of lanes 2j and 2j+1 */
+  const int8_t *E;           /* extrinsic array (shared memory) */
+  int smask, tpc, j;
+};
+struct P2Blk { uint4 s, y, t0, t1; };
+__device__ __forceinline__ P2Blk p2_fetch(const P2Lane &w, int kb)
+{
+  P2Blk b;
+  const int g = kb * w.tpc + w.j;
+  b.s = w.smask ? __ldg(w.S + g) : make_uint4(0, 0, 0, 0);
+  b.y = __ldg(w.Y + g);
+  b.t0 = __ldg(w.T0 + kb);
+  b.t1 = __ldg(w.T1 + kb);
+  return b;
+}
+/* f(k, s, y, t0, t1): packed true systematic and parity values of the two lanes, their step-table words */
+template <typename F>
+__device__ __forceinline__ void p2_for_desc(const P2Lane &w, int khi, int klo, F &&f)
+{
+  if (khi <= klo) return;
+  const int b_lo = klo >> 2;
+  int kb = (khi - 1) >> 2;
+  P2Blk cur = p2_fetch(w, kb), nxt = cur;
+  for (; kb >= b_lo; kb--) {
+    if (kb > b_lo) nxt = p2_fetch(w, kb - 1);
+#pragma unroll
+    for (int q = 3; q >= 0; q--) {
+      const int k = 4 * kb + q;
+      if (k < khi && k >= klo) f(k, win_comp(cur.s, q), win_comp(cur.y, q), win_comp(cur.t0, q), win_comp(cur.t1, q));
+    }
+    cur = nxt;
+  }
+}
+template <typename F>
+__device__ __forceinline__ void p2_for_asc(const P2Lane &w, int klo, int khi, F &&f)
+{
+  if (khi <= klo) return;
+  const int b_hi = (khi - 1) >> 2;
+  int kb = klo >> 2;
+  P2Blk cur = p2_fetch(w, kb), nxt = cur;
+  for (; kb <= b_hi; kb++) {
+    if (kb < b_hi) nxt = p2_fetch(w, kb + 1);
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+      const int k = 4 * kb + q;
+      if (k < khi && k >= klo) f(k, win_comp(cur.s, q), win_comp(cur.y, q), win_comp(cur.t0, q), win_comp(cur.t1, q));
+    }
+    cur = nxt;
+  }
+}
+/* x of the two lanes: sat8(systematic + a-priori), the a-priori values gathered from the int8 extrinsic array */
+__device__ __forceinline__ uint32_t p2_x(const P2Lane &w, uint32_t s, uint32_t t0, uint32_t t1, uint32_t &e)
+{
+  e = __byte_perm((uint32_t)(int)w.E[t0 & 0xFFFFu], (uint32_t)(int)w.E[t1 & 0xFFFFu], 0x5410);
+  return p2_addsat8(s, e);
+}
+
+template <int P>
+__global__ void __launch_bounds__(FEC_WIN_THREADS, 4) fec_tdec_win8p_kernel(const FecDecodeArgs a)
+{
+  constexpr int TPC = P / 2;
+  extern __shared__ __align__(16) unsigned char smem[];
+  __shared__ int s_cb[FEC_WIN_THREADS / 8], s_n[FEC_WIN_THREADS / 8], s_fresh[FEC_WIN_THREADS / 8];
+  __shared__ int s_empty;
+
+  const int tid = threadIdx.x, nthr = blockDim.x;
+  const int slot = tid / TPC, j = tid % TPC, slots = nthr / TPC, nlane = slots * P;
+  const int K = a.g.K, L = a.g.L, Lp = a.g.Lp, LpE = a.g.LpE, SS = a.g.SS;
+  const int nck = (L + S_CH - 1) / S_CH, nw = (L + 31) / 32, kw = (K + 31) / 32;
+  const unsigned lane_mask = (((1u << TPC) - 1u) << ((tid & 31) & ~(TPC - 1)));
+
+  size_t off = 0;
+  int8_t *E = reinterpret_cast<int8_t *>(smem) + (size_t)slot * P * LpE;
+  off += (((size_t)slots * P * LpE) + 15) & ~(size_t)15;
+  uint4 *ckpt = (uint4 *)(smem + off);  off += (size_t)nck * nthr * 16;
+  uint4 *chunk = (uint4 *)(smem + off); off += (size_t)(S_CH - 1) * nthr * 16;
+  uint32_t *bitsw = (uint32_t *)(smem + off); off += (size_t)nw * nlane * 4;
+  uint32_t *outw = (uint32_t *)(smem + off) + (size_t)slot * kw;
+  const int l0 = slot * P + 2 * j;                /* lane ids of this thread inside the CTA: l0, l0 + 1 */
+
+  if (j == 0) { s_cb[slot] = -1; s_fresh[slot] = 0; }
+  if (tid == 0) s_empty = 0;
+  __syncthreads();
+
+  for (;;) {
+    if (j == 0 && s_cb[slot] < 0 && !s_empty) {
+      const unsigned q = atomicAdd(a.queue, 1u);
+      const unsigned total = a.list ? *a.list_count : a.ncb;
+      if (q < total) { s_cb[slot] = a.list ? (int)a.list[q] : (int)q; s_n[slot] = 0; s_fresh[slot] = 1; }
+      else s_empty = 1;
+    }
+    __syncthreads();
+    const int cb = s_cb[slot];
+    if (!__syncthreads_or(cb >= 0)) break;
+    if (cb >= 0 && s_fresh[slot]) {
+      uint32_t *e32 = (uint32_t *)E;
+      for (int i = j; i < P * LpE / 4; i += TPC) e32[i] = 0;
+    }
+    __syncthreads();
+    if (j == 0) s_fresh[slot] = 0;
+
+    int done = 0;
+    if (cb >= 0) {
+      const FecCbDesc desc = a.cbs[cb];
+      const int n = s_n[slot], par = n & 1;
+      P2Lane w;
+      w.S = reinterpret_cast<const uint4 *>(desc.soft);
+      w.Y = reinterpret_cast<const uint4 *>(desc.soft + (1 + par) * SS);
+      w.T0 = reinterpret_cast<const uint4 *>(a.step_tab + par * SS + (2 * j) * Lp);
+      w.T1 = reinterpret_cast<const uint4 *>(a.step_tab + par * SS + (2 * j + 1) * Lp);
+      w.E = E; w.smask = par ? 0 : -1; w.tpc = TPC; w.j = j;
+      const int16_t *tail = desc.soft + 3 * SS + (par ? 6 : 0);
+      const uint32_t *R = a.crcpow[desc.crc_sel];
+      const uint32_t *T0s = a.step_tab + par * SS + (2 * j) * Lp, *T1s = T0s + Lp;
+
+      uint32_t o[8], e;
+      /* ---- beta warm-up (turbodecoder_win.h:321-384), INF = 0: all states start at 0 ---- */
+#pragma unroll
+      for (int i = 0; i < 8; i++) o[i] = P2_BIAS;
+      p2_for_desc(w, 40, 0, [&](int k, uint32_t s, uint32_t y, uint32_t t0, uint32_t t1) {
+        p2_beta_step(o, p2_x(w, s, t0, t1, e), y); p2_norm(k, o);
+      });
+      /* lane shift: lane d starts from the estimate of lane d+1: low half <- own high half, high half <- neighbour's low half */
+#pragma unroll
+      for (int i = 0; i < 8; i++) o[i] = __byte_perm(o[i], __shfl_down_sync(lane_mask, o[i], 1, TPC), 0x5432);
+      if (j == TPC - 1) {   /* last lane: known end state through the 3 tail steps (:263-307), scalar add saturating upwards only (:236-243) */
+        int t[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) t[i] = 0;
+        for (int k = 2; k >= 0; k--) {
+          const int tx = tail[2 * k], ty = tail[2 * k + 1];
+#define TADD(a, b) (((a) + (b)) > 127 ? 127 : (int)(signed char)((a) + (b)))
+          const int txy = TADD(tx, ty);
+          int nn[8];
+          nn[0] = max(TADD(t[4], txy), t[0]);
+          nn[1] = max(t[4], TADD(t[0], txy));
+          nn[2] = max(TADD(t[5], ty), TADD(t[1], tx));
+          nn[3] = max(TADD(t[5], tx), TADD(t[1], ty));
+          nn[4] = max(TADD(t[6], tx), TADD(t[2], ty));
+          nn[5] = max(TADD(t[6], ty), TADD(t[2], tx));
+          nn[6] = max(t[7], TADD(t[3], txy));
+          nn[7] = max(TADD(t[7], txy), t[3]);
+#undef TADD
+#pragma unroll
+          for (int i = 0; i < 8; i++) t[i] = nn[i];
+        }
+#pragma unroll
+        for (int i = 0; i < 8; i++) o[i] = (o[i] & 0xFFFFu) | ((uint32_t)(t[i] + 128) << 16);
+      }
+      /* ---- beta main pass, checkpoint every S_CH steps (stored before normalisation, :419-432) ---- */
+      ckpt[tid] = p2_pack(o);
+      {
+        int c = 1, knext = L - S_CH;
+        p2_for_desc(w, L, 0, [&](int k, uint32_t s, uint32_t y, uint32_t t0, uint32_t t1) {
+          p2_beta_step(o, p2_x(w, s, t0, t1, e), y);
+          if (k == knext && c < nck) { ckpt[c * nthr + tid] = p2_pack(o); c++; knext -= S_CH; }
+          p2_norm(k, o);
+        });
+      }
+      /* ---- alpha warm-up over the last 40 symbols (:459-506) ---- */
+      uint32_t m[8], nb[8];
+#pragma unroll
+      for (int i = 0; i < 8; i++) o[i] = P2_BIAS;
+      p2_for_asc(w, L - 40, L, [&](int k, uint32_t s, uint32_t y, uint32_t t0, uint32_t t1) {
+        p2_alpha_branches(o, p2_x(w, s, t0, t1, e), y, m, nb);
+#pragma unroll
+        for (int i = 0; i < 8; i++) o[i] = __vmaxs2(m[i], nb[i]);
+        p2_norm(k - (L - 40), o);
+      });
+      /* lane d starts from the estimate of lane d-1: high half <- own low half, low half <- neighbour's high half; lane 0: known state */
+#pragma unroll
+      for (int i = 0; i < 8; i++) o[i] = __byte_perm(o[i], __shfl_up_sync(lane_mask, o[i], 1, TPC), 0x1076);
+      if (j == 0) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) o[i] = (o[i] & 0xFFFF0000u) | 0x0080u;
+      }
+      /* ---- alpha main pass: per chunk, recompute beta from its checkpoint, then alpha + LLR ---- */
+      uint32_t crc = 0, wb0 = 0, wb1 = 0;
+      for (int c = nck - 1; c >= 0; c--) {
+        const int khi = L - c * S_CH, klo = max(0, khi - S_CH);
+        const uint4 ck = ckpt[c * nthr + tid];
+        {
+          uint32_t b[8];
+          p2_unpack(ck, b);
+          if (c > 0) p2_norm(khi, b);
+          p2_for_desc(w, khi, klo + 1, [&](int k, uint32_t s, uint32_t y, uint32_t t0, uint32_t t1) {
+            p2_beta_step(b, p2_x(w, s, t0, t1, e), y);
+            chunk[(k - klo - 1) * nthr + tid] = p2_pack(b);
+            p2_norm(k, b);
+          });
+        }
+        p2_for_asc(w, klo, khi, [&](int k, uint32_t s, uint32_t y, uint32_t t0, uint32_t t1) {
+          const int ea0 = t0 & 0xFFFFu, ea1 = t1 & 0xFFFFu, nat0 = t0 >> 16, nat1 = t1 >> 16;
+          p2_alpha_branches(o, p2_x(w, s, t0, t1, e), y, m, nb);
+          uint32_t b[8], v0[8], v1[8];
+          p2_unpack((k == khi - 1) ? ck : chunk[(k - klo) * nthr + tid], b);
+#pragma unroll
+          for (int i = 0; i < 8; i++) {
+            const uint32_t bt = __vsub2(b[i], P2_BIAS);          /* true beta */
+            v0[i] = p2_sadd(m[i], bt); v1[i] = p2_sadd(nb[i], bt);
+          }
+          uint32_t r = p2_sat8(__vsub2(p2_max8(v1), p2_max8(v0)));
+          r = ((r >> 1) & 0x7FFF7FFFu) | (r & 0x80008000u);       /* divide_output: arithmetic >> 1 per lane (:127,159,565) */
+          const uint32_t dif = __vsub2(r, e);
+          uint32_t ne = p2_sat8(dif);
+          if (K & 31) {
+            /* srslte_vec_sub_bbb: the K mod 32 array elements behind the last block of 32 wrap (see fec_tdec_win_kernel) */
+            const bool w0 = (par ? nat0 - (nat0 / L) * L : k) == L - 1, w1 = (par ? nat1 - (nat1 / L) * L : k) == L - 1;
+            const uint32_t wr = __vsub2((dif & 0x00FF00FFu) ^ 0x00800080u, 0x00800080u);
+            const uint32_t msk = (w0 ? 0x0000FFFFu : 0u) | (w1 ? 0xFFFF0000u : 0u);
+            ne = (wr & msk) | (ne & ~msk);
+          }
+          E[ea0] = (int8_t)(ne & 0xFFu); E[ea1] = (int8_t)((ne >> 16) & 0xFFu);
+          const int r0 = (short)(r & 0xFFFFu), r1 = (short)(r >> 16);
+          if (a.dbg_llr) { a.dbg_llr[(size_t)desc.status * FEC_MAX_K + nat0] = (int16_t)r0; a.dbg_llr[(size_t)desc.status * FEC_MAX_K + nat1] = (int16_t)r1; }
+          if (r0 > 0) { crc ^= __ldg(R + (K - 1 - nat0)); wb0 |= 1u << (k & 31); }
+          if (r1 > 0) { crc ^= __ldg(R + (K - 1 - nat1)); wb1 |= 1u << (k & 31); }
+          if ((k & 31) == 31 || k == L - 1) { bitsw[(k >> 5) * nlane + l0] = wb0; bitsw[(k >> 5) * nlane + l0 + 1] = wb1; wb0 = wb1 = 0; }
+#pragma unroll
+          for (int i = 0; i < 8; i++) o[i] = __vmaxs2(m[i], nb[i]);
+          p2_norm(k, o);
+        });
+      }
+#pragma unroll
+      for (int s = TPC / 2; s > 0; s >>= 1) crc ^= __shfl_xor_sync(lane_mask, crc, s, TPC);
+      const int n1 = n + 1;
+      const int crc_ok = (crc == 0);
+      done = (crc_ok && !(desc.flags & FEC_F_NO_EARLY)) || (n1 >= (int)desc.max_its);
+      if (done) {
+        for (int i = j; i < kw; i += TPC) outw[i] = 0;
+        __syncwarp(lane_mask);
+        for (int h = 0; h < 2; h++) {
+          const uint32_t *Ts = h ? T1s : T0s;
+          for (int k = 0; k < L; k++) {
+            if ((bitsw[(k >> 5) * nlane + l0 + h] >> (k & 31)) & 1u) {
+              const int nat = __ldg(Ts + k) >> 16;
+              atomicOr(&outw[nat >> 5], 1u << (8 * ((nat >> 3) & 3) + 7 - (nat & 7)));
+            }
+          }
+        }
+        __syncwarp(lane_mask);
+        const uint8_t *ob = (const uint8_t *)outw;
+        for (int i = j; i < K / 8; i += TPC) desc.out[i] = ob[i];
+        if (j == 0) { a.status[desc.status].its = (uint32_t)n1; a.status[desc.status].crc_ok = (uint32_t)crc_ok; }
+      }
+      if (j == 0) s_n[slot] = n1;
+    }
+    __syncthreads();
+    if (j == 0 && done) s_cb[slot] = -1;
+  }
+}
+
+/* =====================================================================================================
  * Non-windowed decoder for K <= 400 (AUTO class 0): one thread per code block, wrapping int16
  * arithmetic (turbodecoder_sse.c). alpha is stored for every step, beta runs backward with the LLR.
  * ===================================================================================================== */
@@ -612,8 +927,8 @@ cudaError_t fec_launch_decode(const FecDecodeArgs &a, int sm_count, cudaStream_t
   const int per_sm = (int)(((a.llr8 ? 227 : 220) * 1024) / (smem + 1024));
   const int cap = sm_count * (per_sm < 1 ? 1 : per_sm);
   if (grid > cap) grid = cap;
-  if (a.llr8 && a.g.P == 32)      fec_tdec_win_kernel<32, true><<<grid, slots * 32, smem, st>>>(a);
-  else if (a.llr8 && a.g.P == 16) fec_tdec_win_kernel<16, true><<<grid, slots * 16, smem, st>>>(a);
+  if (a.llr8 && a.g.P == 32)      fec_tdec_win8p_kernel<32><<<grid, slots * 16, smem, st>>>(a);
+  else if (a.llr8 && a.g.P == 16) fec_tdec_win8p_kernel<16><<<grid, slots * 8, smem, st>>>(a);
   else if (a.g.P == 16)           fec_tdec_win_kernel<16, false><<<grid, slots * 16, smem, st>>>(a);
   else                            fec_tdec_win_kernel<8, false><<<grid, slots * 8, smem, st>>>(a);
   return cudaGetLastError();
@@ -1000,6 +1315,10 @@ cudaError_t fec_kernels_init(void)
   e = cudaFuncSetAttribute(fec_tdec_win_kernel<16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(fec_tdec_win_kernel<32, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(fec_tdec_win8p_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(fec_tdec_win8p_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(fec_tdec_win_kernel<8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
   if (e != cudaSuccess) return e;
