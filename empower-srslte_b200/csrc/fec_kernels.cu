@@ -375,7 +375,7 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, B8 ? 4 : 1) fec_tdec_win_kern
         for (int i = 1; i < 8; i++) o[i] = NEGINF_T(B8);
       }
       /* ---- alpha main pass: per chunk, recompute beta from its checkpoint, then alpha + LLR ---- */
-      uint32_t crc = 0, wbits = 0;
+      uint32_t crc = 0, wbits = 0, pend = 0;   /* CRC table word of step k is XORed in at step k+1: the lookup is off the critical path */
       for (int c = nck - 1; c >= 0; c--) {
         const int khi = L - c * S_CH, klo = max(0, khi - S_CH);
         const ck_t ck = ckpt[c * nthr + tid];
@@ -410,7 +410,9 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, B8 ? 4 : 1) fec_tdec_win_kern
           } else
           win_e_store<B8>(w, ea, r - e);             /* next apriori = LLR - (what this decoder was given), wrapping */
           if (a.dbg_llr) a.dbg_llr[(size_t)desc.status * FEC_MAX_K + nat] = (int16_t)r;
-          if (r > 0) { crc ^= __ldg(R + (K - 1 - nat)); wbits |= 1u << (k & 31); }
+          crc ^= pend;
+          pend = r > 0 ? __ldg(R + (K - 1 - nat)) : 0u;
+          wbits |= (uint32_t)(r > 0) << (k & 31);
           if ((k & 31) == 31 || k == L - 1) { bitsw[(k >> 5) * nthr + tid] = wbits; wbits = 0; }
 #pragma unroll
           for (int i = 0; i < 8; i++) o[i] = max(m[i], nb[i]);
@@ -418,6 +420,7 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, B8 ? 4 : 1) fec_tdec_win_kern
         });
       }
       /* ---- CRC over the K hard decisions of this half-iteration: XOR-reduce over the P lanes ---- */
+      crc ^= pend;
 #pragma unroll
       for (int s = P / 2; s > 0; s >>= 1) crc ^= __shfl_xor_sync(lane_mask, crc, s, P);
       const int n1 = n + 1;
@@ -684,7 +687,7 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 4) fec_tdec_win8p_kernel(cons
         for (int i = 0; i < 8; i++) o[i] = (o[i] & 0xFFFF0000u) | 0x0080u;
       }
       /* ---- alpha main pass: per chunk, recompute beta from its checkpoint, then alpha + LLR ---- */
-      uint32_t crc = 0, wb0 = 0, wb1 = 0;
+      uint32_t crc = 0, wb0 = 0, wb1 = 0, pend0 = 0, pend1 = 0;   /* CRC table words are XORed in one step late: the lookup is off the critical path */
       for (int c = nck - 1; c >= 0; c--) {
         const int khi = L - c * S_CH, klo = max(0, khi - S_CH);
         const uint4 ck = ckpt[c * nthr + tid];
@@ -722,14 +725,16 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 4) fec_tdec_win8p_kernel(cons
           E[ea0] = (int8_t)(ne & 0xFFu); E[ea1] = (int8_t)((ne >> 16) & 0xFFu);
           const int r0 = (short)(r & 0xFFFFu), r1 = (short)(r >> 16);
           if (a.dbg_llr) { a.dbg_llr[(size_t)desc.status * FEC_MAX_K + nat0] = (int16_t)r0; a.dbg_llr[(size_t)desc.status * FEC_MAX_K + nat1] = (int16_t)r1; }
-          if (r0 > 0) { crc ^= __ldg(R + (K - 1 - nat0)); wb0 |= 1u << (k & 31); }
-          if (r1 > 0) { crc ^= __ldg(R + (K - 1 - nat1)); wb1 |= 1u << (k & 31); }
+          crc ^= pend0 ^ pend1;
+          pend0 = r0 > 0 ? __ldg(R + (K - 1 - nat0)) : 0u; pend1 = r1 > 0 ? __ldg(R + (K - 1 - nat1)) : 0u;
+          wb0 |= (uint32_t)(r0 > 0) << (k & 31); wb1 |= (uint32_t)(r1 > 0) << (k & 31);
           if ((k & 31) == 31 || k == L - 1) { bitsw[(k >> 5) * nlane + l0] = wb0; bitsw[(k >> 5) * nlane + l0 + 1] = wb1; wb0 = wb1 = 0; }
 #pragma unroll
           for (int i = 0; i < 8; i++) o[i] = __vmaxs2(m[i], nb[i]);
           p2_norm(k, o);
         });
       }
+      crc ^= pend0 ^ pend1;
 #pragma unroll
       for (int s = TPC / 2; s > 0; s >>= 1) crc ^= __shfl_xor_sync(lane_mask, crc, s, TPC);
       const int n1 = n + 1;
