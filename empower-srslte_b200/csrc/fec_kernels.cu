@@ -17,6 +17,10 @@
 #include "fec_kernels.cuh"
 #include <stdio.h>
 
+#ifndef FEC_WIN8_TMEM
+#define FEC_WIN8_TMEM 1      /* int8 two-lane decoder: beta checkpoints in tensor memory (0: shared memory) */
+#endif
+#define FEC_WIN8_TCOLS 128   /* tensor-memory columns per CTA: (nck + S_CH - 1) * 4 <= 108 for every K of the int8 classes */
 #define BIAS   32768
 #define NEGINF (BIAS - 10000)
 #define S_CH   FEC_WIN_CHUNK
@@ -223,7 +227,7 @@ size_t fec_win_smem_bytes(const fec_geom_t *g, uint32_t slots, int llr8)
 {
   const size_t nthr = (size_t)slots * g->P;
   const size_t nck = (g->L + S_CH - 1) / S_CH, nw = (g->L + 31) / 32;
-  const size_t esz = llr8 ? 1 : 2, cksz = llr8 ? 8 : 16;
+  const size_t esz = llr8 ? 1 : 2, cksz = llr8 == 2 ? 0 : llr8 ? 8 : 16;    /* llr8 == 2: checkpoints and chunk buffer in tensor memory */
   size_t b = 0;
   b += (((size_t)slots * g->P * g->LpE * esz) + 15) & ~(size_t)15; /* E */
   b += nck * nthr * cksz;                                          /* beta checkpoints */
@@ -241,6 +245,7 @@ uint32_t fec_win_pick_slots(const fec_geom_t *g, int llr8)
      * 227 KB with 1 KB reserved per CTA; 128 registers per thread -> 512 threads) */
     uint32_t best = 1, best_cbs = 0;
     s = FEC_WIN_THREADS / (g->P / 2);             /* two lanes per thread (fec_tdec_win8p_kernel) */
+    if (FEC_WIN8_TMEM) return s;                   /* tensor-memory variant: full 128-thread CTAs (whole warps, 4 lane quarters) */
     for (uint32_t t = s; t >= 1; t--) {
       uint32_t ctas = (uint32_t)((227 * 1024) / (fec_win_smem_bytes(g, t, 1) + 1024));
       if (ctas * t * (g->P / 2) > 512) ctas = 512 / (t * (g->P / 2));
@@ -567,13 +572,32 @@ __device__ __forceinline__ uint32_t p2_x(const P2Lane &w, uint32_t s, uint32_t t
   return p2_addsat8(s, e);
 }
 
-template <int P>
+/* TM = true: beta checkpoints and the chunk buffer live in TENSOR MEMORY (tcgen05.st / ld, 32x32b.x4: 4 columns per entry,
+ * private to the thread's lane) instead of shared memory: shared memory per code block halves (extrinsics + decision bits
+ * only), so more code blocks are resident per SM, which is what this latency-bound kernel needs. The tcgen05 accesses are
+ * warp-collective (.aligned): idle slots run on code block 0's inputs with their results dropped, so that every warp of the
+ * CTA stays convergent. */
+__device__ __forceinline__ void p2_tm_store(uint32_t taddr, uint4 v)
+{
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" :: "r"(taddr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ void p2_tm_store_fence() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ uint4 p2_tm_load(uint32_t taddr)
+{
+  uint4 v;
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(taddr) : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(v.x), "+r"(v.y), "+r"(v.z), "+r"(v.w) :: "memory");
+  return v;
+}
+
+template <int P, bool TM>
 __global__ void __launch_bounds__(FEC_WIN_THREADS, 4) fec_tdec_win8p_kernel(const FecDecodeArgs a)
 {
   constexpr int TPC = P / 2;
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ int s_cb[FEC_WIN_THREADS / 8], s_n[FEC_WIN_THREADS / 8], s_fresh[FEC_WIN_THREADS / 8];
   __shared__ int s_empty;
+  __shared__ uint32_t s_tmem;
 
   const int tid = threadIdx.x, nthr = blockDim.x;
   const int slot = tid / TPC, j = tid % TPC, slots = nthr / TPC, nlane = slots * P;
@@ -584,15 +608,28 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 4) fec_tdec_win8p_kernel(cons
   size_t off = 0;
   int8_t *E = reinterpret_cast<int8_t *>(smem) + (size_t)slot * P * LpE;
   off += (((size_t)slots * P * LpE) + 15) & ~(size_t)15;
-  uint4 *ckpt = (uint4 *)(smem + off);  off += (size_t)nck * nthr * 16;
-  uint4 *chunk = (uint4 *)(smem + off); off += (size_t)(S_CH - 1) * nthr * 16;
+  uint4 *ckpt = (uint4 *)(smem + off);  if (!TM) off += (size_t)nck * nthr * 16;
+  uint4 *chunk = (uint4 *)(smem + off); if (!TM) off += (size_t)(S_CH - 1) * nthr * 16;
   uint32_t *bitsw = (uint32_t *)(smem + off); off += (size_t)nw * nlane * 4;
   uint32_t *outw = (uint32_t *)(smem + off) + (size_t)slot * kw;
   const int l0 = slot * P + 2 * j;                /* lane ids of this thread inside the CTA: l0, l0 + 1 */
 
   if (j == 0) { s_cb[slot] = -1; s_fresh[slot] = 0; }
   if (tid == 0) s_empty = 0;
+  uint32_t tck = 0, tch = 0;                     /* tensor-memory addresses of this thread's checkpoint / chunk entries */
+  if (TM) {
+    if ((tid >> 5) == 0) {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"((uint32_t)__cvta_generic_to_shared(&s_tmem)), "n"(FEC_WIN8_TCOLS) : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  }
   __syncthreads();
+  if (TM) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    tck = s_tmem + ((uint32_t)((tid >> 5) & 3) << 21);      /* lane field: 32 * (warp % 4) */
+    tch = tck + 4u * (uint32_t)nck;
+  }
 
   for (;;) {
     if (j == 0 && s_cb[slot] < 0 && !s_empty) {
@@ -612,8 +649,9 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 4) fec_tdec_win8p_kernel(cons
     if (j == 0) s_fresh[slot] = 0;
 
     int done = 0;
-    if (cb >= 0) {
-      const FecCbDesc desc = a.cbs[cb];
+    const bool active = cb >= 0;
+    if (TM || active) {
+      const FecCbDesc desc = a.cbs[active ? cb : 0];
       const int n = s_n[slot], par = n & 1;
       P2Lane w;
       w.S = reinterpret_cast<const uint4 *>(desc.soft);
@@ -660,15 +698,16 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 4) fec_tdec_win8p_kernel(cons
         for (int i = 0; i < 8; i++) o[i] = (o[i] & 0xFFFFu) | ((uint32_t)(t[i] + 128) << 16);
       }
       /* ---- beta main pass, checkpoint every S_CH steps (stored before normalisation, :419-432) ---- */
-      ckpt[tid] = p2_pack(o);
+      if (TM) p2_tm_store(tck, p2_pack(o)); else ckpt[tid] = p2_pack(o);
       {
         int c = 1, knext = L - S_CH;
         p2_for_desc(w, L, 0, [&](int k, uint32_t s, uint32_t y, uint32_t t0, uint32_t t1) {
           p2_beta_step(o, p2_x(w, s, t0, t1, e), y);
-          if (k == knext && c < nck) { ckpt[c * nthr + tid] = p2_pack(o); c++; knext -= S_CH; }
+          if (k == knext && c < nck) { if (TM) p2_tm_store(tck + 4u * c, p2_pack(o)); else ckpt[c * nthr + tid] = p2_pack(o); c++; knext -= S_CH; }
           p2_norm(k, o);
         });
       }
+      if (TM) p2_tm_store_fence();
       /* ---- alpha warm-up over the last 40 symbols (:459-506) ---- */
       uint32_t m[8], nb[8];
 #pragma unroll
@@ -690,22 +729,23 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 4) fec_tdec_win8p_kernel(cons
       uint32_t crc = 0, wb0 = 0, wb1 = 0, pend0 = 0, pend1 = 0;   /* CRC table words are XORed in one step late: the lookup is off the critical path */
       for (int c = nck - 1; c >= 0; c--) {
         const int khi = L - c * S_CH, klo = max(0, khi - S_CH);
-        const uint4 ck = ckpt[c * nthr + tid];
+        const uint4 ck = TM ? p2_tm_load(tck + 4u * c) : ckpt[c * nthr + tid];
         {
           uint32_t b[8];
           p2_unpack(ck, b);
           if (c > 0) p2_norm(khi, b);
           p2_for_desc(w, khi, klo + 1, [&](int k, uint32_t s, uint32_t y, uint32_t t0, uint32_t t1) {
             p2_beta_step(b, p2_x(w, s, t0, t1, e), y);
-            chunk[(k - klo - 1) * nthr + tid] = p2_pack(b);
+            if (TM) p2_tm_store(tch + 4u * (k - klo - 1), p2_pack(b)); else chunk[(k - klo - 1) * nthr + tid] = p2_pack(b);
             p2_norm(k, b);
           });
+          if (TM) p2_tm_store_fence();
         }
         p2_for_asc(w, klo, khi, [&](int k, uint32_t s, uint32_t y, uint32_t t0, uint32_t t1) {
           const int ea0 = t0 & 0xFFFFu, ea1 = t1 & 0xFFFFu, nat0 = t0 >> 16, nat1 = t1 >> 16;
           p2_alpha_branches(o, p2_x(w, s, t0, t1, e), y, m, nb);
           uint32_t b[8], v0[8], v1[8];
-          p2_unpack((k == khi - 1) ? ck : chunk[(k - klo) * nthr + tid], b);
+          p2_unpack((k == khi - 1) ? ck : (TM ? p2_tm_load(tch + 4u * (k - klo)) : chunk[(k - klo) * nthr + tid]), b);
 #pragma unroll
           for (int i = 0; i < 8; i++) {
             const uint32_t bt = __vsub2(b[i], P2_BIAS);          /* true beta */
@@ -724,7 +764,7 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 4) fec_tdec_win8p_kernel(cons
           }
           E[ea0] = (int8_t)(ne & 0xFFu); E[ea1] = (int8_t)((ne >> 16) & 0xFFu);
           const int r0 = (short)(r & 0xFFFFu), r1 = (short)(r >> 16);
-          if (a.dbg_llr) { a.dbg_llr[(size_t)desc.status * FEC_MAX_K + nat0] = (int16_t)r0; a.dbg_llr[(size_t)desc.status * FEC_MAX_K + nat1] = (int16_t)r1; }
+          if (a.dbg_llr && active) { a.dbg_llr[(size_t)desc.status * FEC_MAX_K + nat0] = (int16_t)r0; a.dbg_llr[(size_t)desc.status * FEC_MAX_K + nat1] = (int16_t)r1; }
           crc ^= pend0 ^ pend1;
           pend0 = r0 > 0 ? __ldg(R + (K - 1 - nat0)) : 0u; pend1 = r1 > 0 ? __ldg(R + (K - 1 - nat1)) : 0u;
           wb0 |= (uint32_t)(r0 > 0) << (k & 31); wb1 |= (uint32_t)(r1 > 0) << (k & 31);
@@ -739,7 +779,7 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 4) fec_tdec_win8p_kernel(cons
       for (int s = TPC / 2; s > 0; s >>= 1) crc ^= __shfl_xor_sync(lane_mask, crc, s, TPC);
       const int n1 = n + 1;
       const int crc_ok = (crc == 0);
-      done = (crc_ok && !(desc.flags & FEC_F_NO_EARLY)) || (n1 >= (int)desc.max_its);
+      done = active && ((crc_ok && !(desc.flags & FEC_F_NO_EARLY)) || (n1 >= (int)desc.max_its));
       if (done) {
         for (int i = j; i < kw; i += TPC) outw[i] = 0;
         __syncwarp(lane_mask);
@@ -761,6 +801,11 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 4) fec_tdec_win8p_kernel(cons
     }
     __syncthreads();
     if (j == 0 && done) s_cb[slot] = -1;
+  }
+  if (TM) {
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if ((tid >> 5) == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(s_tmem), "n"(FEC_WIN8_TCOLS) : "memory");
   }
 }
 
@@ -927,13 +972,14 @@ cudaError_t fec_launch_decode(const FecDecodeArgs &a, int sm_count, cudaStream_t
     return cudaGetLastError();
   }
   const uint32_t slots = a.slots;
-  const size_t smem = fec_win_smem_bytes(&a.g, slots, a.llr8);
+  const size_t smem = fec_win_smem_bytes(&a.g, slots, a.llr8 ? 1 + FEC_WIN8_TMEM : 0);
   int grid = (int)((a.ncb + slots - 1) / slots);
-  const int per_sm = (int)(((a.llr8 ? 227 : 220) * 1024) / (smem + 1024));
+  int per_sm = (int)(((a.llr8 ? 227 : 220) * 1024) / (smem + 1024));
+  if (a.llr8 && FEC_WIN8_TMEM && per_sm > 512 / FEC_WIN8_TCOLS) per_sm = 512 / FEC_WIN8_TCOLS;
   const int cap = sm_count * (per_sm < 1 ? 1 : per_sm);
   if (grid > cap) grid = cap;
-  if (a.llr8 && a.g.P == 32)      fec_tdec_win8p_kernel<32><<<grid, slots * 16, smem, st>>>(a);
-  else if (a.llr8 && a.g.P == 16) fec_tdec_win8p_kernel<16><<<grid, slots * 8, smem, st>>>(a);
+  if (a.llr8 && a.g.P == 32)      fec_tdec_win8p_kernel<32, FEC_WIN8_TMEM != 0><<<grid, slots * 16, smem, st>>>(a);
+  else if (a.llr8 && a.g.P == 16) fec_tdec_win8p_kernel<16, FEC_WIN8_TMEM != 0><<<grid, slots * 8, smem, st>>>(a);
   else if (a.g.P == 16)           fec_tdec_win_kernel<16, false><<<grid, slots * 16, smem, st>>>(a);
   else                            fec_tdec_win_kernel<8, false><<<grid, slots * 8, smem, st>>>(a);
   return cudaGetLastError();
@@ -1321,9 +1367,9 @@ cudaError_t fec_kernels_init(void)
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(fec_tdec_win_kernel<32, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(fec_tdec_win8p_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+  e = cudaFuncSetAttribute(fec_tdec_win8p_kernel<32, FEC_WIN8_TMEM != 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(fec_tdec_win8p_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+  e = cudaFuncSetAttribute(fec_tdec_win8p_kernel<16, FEC_WIN8_TMEM != 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(fec_tdec_win_kernel<8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
   if (e != cudaSuccess) return e;
