@@ -233,7 +233,7 @@ size_t fec_win_smem_bytes(const fec_geom_t *g, uint32_t slots, int llr8)
   b += nck * nthr * cksz;                                          /* beta checkpoints */
   b += (size_t)(S_CH - 1) * nthr * cksz;                           /* beta chunk buffer */
   b += nw * nthr * 4;                                              /* decision words per lane */
-  b += (size_t)slots * ((g->K + 31) / 32) * 4;                     /* output assembly */
+  if (llr8 != 2) b += (size_t)slots * ((g->K + 31) / 32) * 4;      /* output assembly (tensor-memory variant: inside E) */
   return b;
 }
 
@@ -582,6 +582,14 @@ __device__ __forceinline__ void p2_tm_store(uint32_t taddr, uint4 v)
   asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" :: "r"(taddr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 __device__ __forceinline__ void p2_tm_store_fence() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void p2_tm_load_issue(uint32_t taddr, uint4 &v)
+{
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void p2_tm_load_wait(uint4 &v)
+{   /* the registers are tied to the wait so that no use can be scheduled above it */
+  asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(v.x), "+r"(v.y), "+r"(v.z), "+r"(v.w) :: "memory");
+}
 __device__ __forceinline__ uint4 p2_tm_load(uint32_t taddr)
 {
   uint4 v;
@@ -611,7 +619,9 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 4) fec_tdec_win8p_kernel(cons
   uint4 *ckpt = (uint4 *)(smem + off);  if (!TM) off += (size_t)nck * nthr * 16;
   uint4 *chunk = (uint4 *)(smem + off); if (!TM) off += (size_t)(S_CH - 1) * nthr * 16;
   uint32_t *bitsw = (uint32_t *)(smem + off); off += (size_t)nw * nlane * 4;
-  uint32_t *outw = (uint32_t *)(smem + off) + (size_t)slot * kw;
+  /* output assembly words: a finished code block no longer needs its extrinsics, so in the tensor-memory variant they share
+   * the (larger) extrinsic array of the slot, which is zeroed again for the next code block */
+  uint32_t *outw = TM ? (uint32_t *)E : (uint32_t *)(smem + off) + (size_t)slot * kw;
   const int l0 = slot * P + 2 * j;                /* lane ids of this thread inside the CTA: l0, l0 + 1 */
 
   if (j == 0) { s_cb[slot] = -1; s_fresh[slot] = 0; }
@@ -741,11 +751,20 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 4) fec_tdec_win8p_kernel(cons
           });
           if (TM) p2_tm_store_fence();
         }
+        uint4 pref = ck;                           /* tensor memory: the chunk entry of the next step is fetched one step ahead */
+        if (TM && klo < khi - 1) p2_tm_load_issue(tch, pref);
         p2_for_asc(w, klo, khi, [&](int k, uint32_t s, uint32_t y, uint32_t t0, uint32_t t1) {
           const int ea0 = t0 & 0xFFFFu, ea1 = t1 & 0xFFFFu, nat0 = t0 >> 16, nat1 = t1 >> 16;
           p2_alpha_branches(o, p2_x(w, s, t0, t1, e), y, m, nb);
           uint32_t b[8], v0[8], v1[8];
-          p2_unpack((k == khi - 1) ? ck : (TM ? p2_tm_load(tch + 4u * (k - klo)) : chunk[(k - klo) * nthr + tid]), b);
+          if (TM) {
+            if (k == khi - 1) p2_unpack(ck, b);
+            else {
+              p2_tm_load_wait(pref);
+              p2_unpack(pref, b);
+              if (k + 1 < khi - 1) p2_tm_load_issue(tch + 4u * (k + 1 - klo), pref);
+            }
+          } else p2_unpack((k == khi - 1) ? ck : chunk[(k - klo) * nthr + tid], b);
 #pragma unroll
           for (int i = 0; i < 8; i++) {
             const uint32_t bt = __vsub2(b[i], P2_BIAS);          /* true beta */
