@@ -541,7 +541,7 @@ def main():
                     phases_ms=dict(rate_dematch=sum(p[0] for p in ph8) / 3, turbo_decode=sum(p[1] for p in ph8) / 3, tb_assemble_crc24a=sum(p[2] for p in ph8) / 3),
                     e2e=dict(value=allsum(ok8e) * TBS * n8 / (ms8e / 1e3) / 1e9, unit=UNIT, ms_per_step=ms8e / n8, sync_ms_per_step=ms8es / n8,
                              h2d_bytes_per_step=B * NBITS + B * C_CB * (32 + 48) + B * 520),
-                    kernel="fec_tdec_win_kernel<32,true>: 32-bit-lane int8 kernel, one sub-block per thread, ALU-pipe-bound (profiles/r1n_win8_kernel_ncu.txt)")
+                    kernel="fec_tdec_win8p_kernel<32,true>: two sub-blocks per thread in u16x2 lanes (VIADDMNMX.S16x2.RELU = saturating int8 add), beta checkpoints in tensor memory (profiles/r1o_win8p_kernel_ncu.txt)")
         f8.close()
 
     # ---- latency of the reference's call shape: ONE transport block per blocking call (srslte_dlsch_decode as pdsch.c:816

@@ -1382,10 +1382,8 @@ cudaError_t fec_kernels_init(void)
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(fec_tdec_win_kernel<16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(fec_tdec_win_kernel<16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
-  if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(fec_tdec_win_kernel<32, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
-  if (e != cudaSuccess) return e;
+  /* fec_tdec_win_kernel<P, true> (one lane per thread) is the first form of the int8 decoders; the launcher uses the
+   * two-lane fec_tdec_win8p_kernel, so it is not instantiated */
   e = cudaFuncSetAttribute(fec_tdec_win8p_kernel<32, FEC_WIN8_TMEM != 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(fec_tdec_win8p_kernel<16, FEC_WIN8_TMEM != 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
