@@ -194,6 +194,23 @@ extern "C" int srslte_rm_turbo_rx_lut_(int16_t *input, int16_t *output, uint32_t
   return r == 0 ? SRSLTE_SUCCESS : (r == FEC_CUDA_EINVAL ? SRSLTE_ERROR_INVALID_INPUTS : SRSLTE_ERROR);
 }
 
+/* rm_turbo.c:432-469: int8 LLRs into an int8 soft buffer (18600 entries as the reference sizes it), wrapping int8 adds, in the
+ * sub-block layout of the 8-bit decoder class of this K */
+extern "C" int srslte_rm_turbo_rx_lut_8bit(int8_t *input, int8_t *output, uint32_t in_len, uint32_t cb_idx, uint32_t rv_idx)
+{
+  if (!input || !output || rv_idx >= 4 || cb_idx >= FEC_NOF_K) {
+    fprintf(stderr, "Invalid inputs rv_idx=%d, cb_idx=%d\n", rv_idx, cb_idx);
+    return SRSLTE_ERROR_INVALID_INPUTS;
+  }
+  std::lock_guard<std::mutex> lk(g_mu);
+  fec_cuda_ctx_t *ctx = compat_ctx();
+  if (!ctx) return SRSLTE_ERROR;
+  fec_cuda_set_llr_8bit(ctx, 1);
+  const int r = fec_cuda_rm_rx(ctx, (const int16_t *)input, in_len, cb_idx, rv_idx, 1, (int16_t *)output);
+  fec_cuda_set_llr_8bit(ctx, 0);
+  return r == 0 ? SRSLTE_SUCCESS : (r == FEC_CUDA_EINVAL ? SRSLTE_ERROR_INVALID_INPUTS : SRSLTE_ERROR);
+}
+
 extern "C" int srslte_rm_turbo_rx_lut(int16_t *input, int16_t *output, uint32_t in_len, uint32_t cb_idx, uint32_t rv_idx)
 {
   return srslte_rm_turbo_rx_lut_(input, output, in_len, cb_idx, rv_idx, false);          /* rm_turbo.c:378-381 */

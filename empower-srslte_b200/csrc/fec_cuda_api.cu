@@ -1120,25 +1120,30 @@ extern "C" int fec_cuda_rm_rx(fec_cuda_ctx_t *ctx, const int16_t *in, uint32_t E
       stage_reserve(ctx, &ctx->st_data, 18600 * 2) ||
       dev_reserve(ctx, (void **)&ctx->d_softmax, &ctx->softmax_cap, 8) ||
       dev_reserve(ctx, (void **)&ctx->d_tmpsoft, &ctx->tmpsoft_cap, 2 * FEC_CUDA_SOFT_SLOT * sizeof(int16_t))) return FEC_CUDA_ENODEV;
-  memcpy(ctx->st_e.h, in, (size_t)E * 2);
-  memcpy(ctx->st_data.h, soft, 18600 * 2);
+  /* 8-bit LLR mode (srslte_rm_turbo_rx_lut_8bit): in and soft are int8 arrays; the soft buffer is widened for the device
+   * layout and narrowed on the way back (the int8 kernel keeps sign-extended int8 values in int16 slots) */
+  const size_t esz = ctx->llr8 ? 1 : 2;
+  memcpy(ctx->st_e.h, in, (size_t)E * esz);
+  if (ctx->llr8) for (int i = 0; i < 18600; i++) ((int16_t *)ctx->st_data.h)[i] = ((const int8_t *)soft)[i];
+  else memcpy(ctx->st_data.h, soft, 18600 * 2);
   FecRmDesc *r = (FecRmDesc *)ctx->st_rmd.h;
   r->e = (const int16_t *)ctx->st_e.d; r->soft = ctx->d_tmpsoft; r->rank = kt->d_rank; r->E = E; r->N = 3 * kt->g.K + 12;
   r->off = kt->off[rv]; r->n_out = 3 * kt->g.SS + 16; r->new_data = 0; r->slot = 0;
   cudaStream_t st = ctx->stream;
   /* the caller's soft buffer lives in host memory in the reference layout: bring it to the device layout, combine
    * there (wrapping int16 adds, rm_turbo.c:411-420), and hand the same layout back */
-  CUF(cudaMemcpyAsync(ctx->st_e.d, ctx->st_e.h, (size_t)E * 2, cudaMemcpyHostToDevice, st));
+  CUF(cudaMemcpyAsync(ctx->st_e.d, ctx->st_e.h, (size_t)E * esz, cudaMemcpyHostToDevice, st));
   CUF(cudaMemcpyAsync(ctx->st_data.d, ctx->st_data.h, 18600 * 2, cudaMemcpyHostToDevice, st));
   CUF(cudaMemcpyAsync(ctx->st_rmd.d, r, sizeof(FecRmDesc), cudaMemcpyHostToDevice, st));
   CUF(cudaMemsetAsync(ctx->d_softmax, 0, 8, st));
   CUF(fec_launch_ref_to_soft((const int16_t *)ctx->st_data.d, ctx->d_tmpsoft, kt->g, sb_layout, st));
-  CUF(fec_launch_rm((const FecRmDesc *)ctx->st_rmd.d, ctx->d_softmax, 1, r->n_out, st));
+  CUF(fec_launch_rm((const FecRmDesc *)ctx->st_rmd.d, ctx->d_softmax, 1, r->n_out, st, ctx->llr8));
   CUF(fec_launch_soft_to_ref(ctx->d_tmpsoft, (int16_t *)ctx->st_data.d, kt->g, sb_layout, 1, st));
   ctx->launches += 3;
   CUF(cudaMemcpyAsync(ctx->st_data.h, ctx->st_data.d, 18600 * 2, cudaMemcpyDeviceToHost, st));
   CUF(cudaStreamSynchronize(st));
-  memcpy(soft, ctx->st_data.h, 18600 * 2);
+  if (ctx->llr8) for (int i = 0; i < 18600; i++) ((int8_t *)soft)[i] = (int8_t)((const int16_t *)ctx->st_data.h)[i];
+  else memcpy(soft, ctx->st_data.h, 18600 * 2);
   return 0;
 }
 

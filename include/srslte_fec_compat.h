@@ -10,8 +10,7 @@
  * reference headers instead (the prototypes are identical) and keeps the static asserts of csrc/fec_compat.cu.
  *
  * 16-bit and 8-bit LLR paths: srslte_tdec_iteration_8bit / srslte_tdec_run_all_8bit and
- * srslte_sch_decode_tb_cuda_8bit; srslte_rm_turbo_rx_lut_8bit on host buffers is not exported (the rate de-matcher of
- * the 8-bit path runs inside the transport-block call).
+ * srslte_sch_decode_tb_cuda_8bit, srslte_rm_turbo_rx_lut_8bit.
  * No CPU fallback: without a usable CUDA device every init returns SRSLTE_ERROR and every decode returns -1.
  */
 #ifndef SRSLTE_FEC_COMPAT_H
@@ -60,6 +59,7 @@ void srslte_rm_turbo_gentables(void);                     /* tables are built pe
 void srslte_rm_turbo_free_tables(void);
 int  srslte_rm_turbo_rx_lut(int16_t *input, int16_t *output, uint32_t in_len, uint32_t cb_idx, uint32_t rv_idx);
 int  srslte_rm_turbo_rx_lut_(int16_t *input, int16_t *output, uint32_t in_len, uint32_t cb_idx, uint32_t rv_idx, bool enable_input_tdec);
+int  srslte_rm_turbo_rx_lut_8bit(int8_t *input, int8_t *output, uint32_t in_len, uint32_t cb_idx, uint32_t rv_idx);   /* rm_turbo.c:432-469 */
 
 /* ---- HARQ soft buffer: lib/include/srslte/phy/fec/softbuffer.h:42-48,57-75 (40 bytes, caller-allocated) ---- */
 typedef struct {

@@ -194,7 +194,8 @@ int  fec_cuda_encode_tbs(fec_cuda_ctx_t *ctx, fec_cuda_txtb_t *tbs, uint32_t n, 
 int  fec_cuda_decode_cbs(fec_cuda_ctx_t *ctx, fec_cuda_cb_t *cbs, uint32_t n, uint32_t flags);
 
 /* standalone rate de-matching into a HOST soft buffer in the reference layout — drop-in body of
- * srslte_rm_turbo_rx_lut_ (rm_turbo.c:378-430); computed on the device. */
+ * srslte_rm_turbo_rx_lut_ (rm_turbo.c:378-430); computed on the device. In 8-bit LLR mode (fec_cuda_set_llr_8bit) `in` and
+ * `soft18600` point to int8 arrays (E and 18600 entries): the body of srslte_rm_turbo_rx_lut_8bit (rm_turbo.c:432-469). */
 int  fec_cuda_rm_rx(fec_cuda_ctx_t *ctx, const int16_t *in, uint32_t E, uint32_t cb_idx, uint32_t rv,
                     int sb_layout, int16_t *soft18600);
 

@@ -37,6 +37,7 @@ def lib():
     l.srslte_tdec_iteration_8bit.restype = None
     l.srslte_tdec_run_all_8bit.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]
     l.srslte_sch_decode_tb_cuda_8bit.argtypes = l.srslte_sch_decode_tb_cuda.argtypes
+    l.srslte_rm_turbo_rx_lut_8bit.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32]
     return l
 
 
@@ -208,3 +209,21 @@ def test_decode_tb_8bit_with_reference_softbuffer_calls(lib, case):
         crc = (C.c_bool * 13).from_address(C.c_void_p.from_buffer(q, 24).value)
         assert [bool(crc[i]) for i in range(nC)] == [bool(v) for v in tx["crc"][:nC]]
     lib.srslte_softbuffer_rx_free(q)
+
+
+def test_rm_rx_lut_8bit_accumulates_like_reference(lib, orc):
+    """srslte_rm_turbo_rx_lut_8bit on host buffers: wrapping int8 accumulation into a non-empty soft buffer, every 8-bit
+    decoder class, E below / above 3K+12, then the decoder entry point on the result"""
+    rng = np.random.default_rng(77)
+    for K in (40, 408, 1024, 2112, 6144):
+        for rv, E in ((0, 3 * K + 12 + 333), (2, K + 7), (3, 2 * (3 * K + 12) + 5)):
+            e = rng.integers(-128, 128, E).astype(np.int8)
+            s0 = np.zeros(18600, np.int8)
+            s0[: 3 * K + 108] = rng.integers(-128, 128, 3 * K + 108)
+            got, want = s0.copy(), np.zeros(2 * 18600, np.int8)
+            want[:18600] = s0
+            assert lib.srslte_rm_turbo_rx_lut_8bit(P(e), P(got), E, ALL_K.index(K), rv) == 0
+            assert orc.orc_rm_rx8(P(e), E, K, rv, 1, P(want)) == 0
+            P8 = orc.orc_subblocks8(K)
+            assert (G.soft8_view(got, K, P8) == G.soft8_view(want, K, P8)).all(), (K, rv, E)
+    assert lib.srslte_rm_turbo_rx_lut_8bit(P(e), P(got), 10, 0, 4) == -2
