@@ -944,6 +944,11 @@ extern "C" int fec_cuda_decode_cbs(fec_cuda_ctx_t *ctx, fec_cuda_cb_t *cbs, uint
   for (uint32_t i = 0; i < n; i++) {
     ktab_t *kt;
     if (!cbs[i].llr || !cbs[i].out || ktab_get(ctx, cbs[i].K, &kt)) return FEC_CUDA_EINVAL;
+    if (ctx->llr8) {                           /* the reference's 8-bit entry points take int8_t: anything wider is a caller error */
+      const int16_t *v = cbs[i].llr;
+      for (uint32_t t = 0; t < 3 * cbs[i].K + 12; t++)
+        if (v[t] < -128 || v[t] > 127) return fail(ctx, FEC_CUDA_EINVAL, "8-bit LLR mode: code block %u has an LLR outside int8", i);
+    }
     grp_cnt[kt->g.idx]++;
     llr_total += ((size_t)3 * cbs[i].K + 12 + 7) & ~(size_t)7;
   }

@@ -183,3 +183,14 @@ def test_mode_switch_leaves_16bit_path_untouched(orc):
         assert (a == ob[2]).all() and (b == ob[2]).all()
     finally:
         f.close()
+
+
+def test_invalid_in_8bit_mode(fec8):
+    """LLRs wider than int8 through the int16 code-block entry point, and the symbol front end, are refused in 8-bit mode"""
+    K = 1024
+    bad = np.zeros(3 * K + 12, np.int16)
+    bad[5] = 200
+    with pytest.raises(RuntimeError):
+        fec8.decode_cbs([K], [bad], 2, early_stop=False)
+    ok = fec8.decode_cbs([K], [np.zeros(3 * K + 12, np.int16)], 1, early_stop=False)
+    assert not ok[0]["out"].any()
