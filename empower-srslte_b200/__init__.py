@@ -15,7 +15,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("FEC_CUDA_LIB") or os.path.join(HERE, "libsrslte_fec_cuda.so")   # FEC_CUDA_LIB: tuning builds (tools/variants.sh)
 CSRC = os.path.join(HERE, "csrc")
-SOURCES = ["fec_kernels.cu", "fec_tdec_packed.cu", "fec_frontend.cu", "fec_tx.cu", "fec_cuda_api.cu", "fec_compat.cu", "fec_tables.c"]
+SOURCES = ["fec_kernels.cu", "fec_tdec_packed.cu", "fec_frontend.cu", "fec_tx.cu", "fec_cuda_api.cu", "fec_compat.cu", "fec_noalloc.cu", "fec_tables.c"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-Xcompiler", "-fPIC", "-shared"]
 
 MAX_CB = 13
@@ -90,6 +90,7 @@ def load():
         lib.fec_cuda_wait.argtypes = [C.c_void_p, C.c_uint64]
         lib.fec_cuda_decode_cbs.argtypes = [C.c_void_p, C.POINTER(CbDesc), C.c_uint32, C.c_uint32]
         lib.fec_cuda_rm_rx.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p]
+        lib.fec_cuda_rm_rx_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p]
         lib.fec_cuda_cbsegm.argtypes = [C.c_uint32, C.POINTER(C.c_uint32)]
         lib.fec_cuda_last_phase_ms.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
         lib.fec_cuda_last_path_counts.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]

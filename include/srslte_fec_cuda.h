@@ -199,6 +199,20 @@ int  fec_cuda_decode_cbs(fec_cuda_ctx_t *ctx, fec_cuda_cb_t *cbs, uint32_t n, ui
 int  fec_cuda_rm_rx(fec_cuda_ctx_t *ctx, const int16_t *in, uint32_t E, uint32_t cb_idx, uint32_t rv,
                     int sb_layout, int16_t *soft18600);
 
+/* The same operation for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it). NO COUNTERPART IN THE REFERENCE. Takes a device
+ * ordinal instead of a context and allocates nothing, on the host or on the device: all device scratch (staged LLRs,
+ * the soft buffer in both layouts, the per-K rank table, the descriptor) is one static __device__ array of at most
+ * FEC_CUDA_NOALLOC_SCRATCH_BYTES that every GPU which loads the library holds until exit. Host pointers, 16-bit LLRs
+ * only; of `soft` only the extent the layout uses is read and written (sb_layout and K > 400: 3*(K+32)+12 entries, else
+ * 3K+12). E > FEC_CUDA_NOALLOC_MAX_E is rejected with FEC_CUDA_EINVAL and a message on stderr. Synchronous; calls are
+ * serialised by a mutex because they all share the array (it keeps the last call's contents; what must start at zero is
+ * cleared per call) — GPU work that overlaps a call on the same array by any other route would race. */
+#define FEC_CUDA_NOALLOC_MAX_E          32768u
+#define FEC_CUDA_NOALLOC_SCRATCH_BYTES  (176u * 1024u)
+int  fec_cuda_rm_rx_noalloc(int device, const int16_t *in, uint32_t E, uint32_t cb_idx, uint32_t rv,
+                            int sb_layout, int16_t *soft);
+
 /* ---- test hooks (LLR dump of the last half-iteration of fec_cuda_decode_cbs; not a product feature) ---- */
 int  fec_cuda_debug_llr_enable(fec_cuda_ctx_t *ctx, uint32_t n_code_blocks);
 int  fec_cuda_debug_llr_read(fec_cuda_ctx_t *ctx, int16_t *out /* n x 6144 */, uint32_t n);
