@@ -115,6 +115,14 @@ def make_llrs(batch, sigma, seed, out):
     return payload
 
 
+def fnv1a_rows(a):
+    """FNV-1a (32 bit) of every row of a uint8 matrix — the checksum the CPU arm computes over its decoded bytes"""
+    h = np.full(a.shape[0], 2166136261, np.uint64)
+    for j in range(a.shape[1]):
+        h = ((h ^ a[:, j].astype(np.uint64)) * np.uint64(16777619)) & np.uint64(0xFFFFFFFF)
+    return h.astype(np.uint32)
+
+
 def cpu_cores():
     try:
         return len(os.sched_getaffinity(0))
@@ -135,6 +143,8 @@ def cpu_arm(llr, ntb, budget_s):
     ntb = min(ntb, llr.shape[0])
     sample = np.ascontiguousarray(llr[:ntb])
     out = np.zeros(3, np.uint64)
+    res = np.zeros((ntb, 3), np.uint32)       # per TB of the last pass: return value, mean half-iterations (sch.c:420), FNV-1a of the output
+    (lib.ref_bench_set_results if kind == "reference" else lib.orc_bench_set_results)(P(res))
 
     def run(reps):
         if kind == "reference":
@@ -145,7 +155,8 @@ def cpu_arm(llr, ntb, budget_s):
     reps = max(1, min(2000, int(budget_s / max(t1, 1e-3))))
     t = run(reps)
     n_tb, n_ok, sum_its = int(out[0]), int(out[1]), int(out[2])
-    return dict(value=n_ok * TBS / t / 1e9, unit=UNIT, cores=cores, kind=kind, seconds=t,
+    (lib.ref_bench_set_results if kind == "reference" else lib.orc_bench_set_results)(None)
+    return dict(results=res, value=n_ok * TBS / t / 1e9, unit=UNIT, cores=cores, kind=kind, seconds=t,
                 tbs_per_s=n_tb / t, cbs_per_s=n_tb * C_CB / t, tb_ok=n_ok, tb_total=n_tb,
                 mean_halfits=sum_its / max(n_tb, 1),
                 sample=f"{ntb} of the step's TBs x {reps} passes, {cores} threads (one srslte_sch_t + soft buffers each), "
@@ -323,6 +334,10 @@ def main():
     ms_e_sync = timed(hd, 0, args.steps)
     clocks = sampler.stop()
     ok_e, _ = tally(hd)
+    n_par = min(max(cpu_cores() * 4, 32), B)     # the transport blocks the CPU arm decodes too (parity_in_bench)
+    gpu_par = np.stack([np.array([hd[i].ret & 0xFFFFFFFF for i in range(n_par)], np.uint32),
+                        np.array([hd[i].avg_its for i in range(n_par)], np.uint32),
+                        fnv1a_rows(h_out.a[:n_par, :TBS // 8 + 3])], axis=1)
     e2e_val = allsum(ok_e) * TBS * args.steps / (ms_e / 1e3) / 1e9
     h2d = B * NBITS * 2 + B * C_CB * (32 + 48) + B * 520
     d2h = B * (((TBS // 8 + 3 + 768 + 15) // 16) * 16) + B * C_CB * 8 + B * 4
@@ -605,11 +620,19 @@ def main():
                          peak_source=pk["src"],
                          rate_dematch_kernel_gbs=B * C_CB * (2 * (NBITS // C_CB) + 2 * (3 * K_CB + 12) + 2 * (3 * K_CB + 12)) / (rm_ms / 1e3) / 1e9))
 
-    cpu = None
+    cpu, parity = None, None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         c = cpu_arm(h_llr.a, max(cpu_cores() * 4, 32), 15.0)
         cpu = dict(value=c["value"], unit=UNIT, cores=c["cores"], kind=c["kind"], sample=c["sample"],
                    cbs_per_s=c["cbs_per_s"], mean_halfits=c["mean_halfits"], tb_ok=c["tb_ok"], tb_total=c["tb_total"])
+        # the CPU arm decoded the first n_par transport blocks of the step: the GPU's results for the same blocks (e2e arm, host
+        # buffers) must be the same — return value, mean half-iterations as srslte_sch_last_noi reports them, every output byte
+        n_cmp = min(n_par, c["results"].shape[0])
+        same = (c["results"][:n_cmp] == gpu_par[:n_cmp]).all(axis=1)
+        parity = dict(tbs=int(n_cmp), equal=int(same.sum()), checker=c["kind"], compared="decode_tb return value, mean half-iterations (sch.c:420), FNV-1a of TBS/8+3 output bytes")
+        if not same.all():
+            raise SystemExit(f"bench.py: parity_in_bench failed: {parity}, first mismatch TB {int(np.argmin(same))}: "
+                             f"cpu {c['results'][int(np.argmin(same))].tolist()} gpu {gpu_par[int(np.argmin(same))].tolist()}")
 
     if rank == 0:
         line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=args.warmup,
@@ -624,7 +647,7 @@ def main():
                     e2e=dict(value=e2e_val, unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h, ms_per_step=ms_e / args.steps,
                              sync_ms_per_step=ms_e_sync / args.steps),
                     sync_ms_per_step=ms_sync / args.steps,
-                    gpu_launches=launches, clocks=clocks, roofline=roof, worst_case_8_halfits=worst, frontend_symbols=front, transmit_side=tx, llr_8bit=llr8, single_tb_latency=lat, cpu_baseline=cpu)
+                    gpu_launches=launches, clocks=clocks, roofline=roof, worst_case_8_halfits=worst, frontend_symbols=front, transmit_side=tx, llr_8bit=llr8, single_tb_latency=lat, cpu_baseline=cpu, parity_in_bench=parity)
         print(json.dumps(line), flush=True)
     fec.close()
     if world > 1:

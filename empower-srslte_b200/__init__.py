@@ -52,14 +52,29 @@ class CbDesc(C.Structure):
                 ("llr", C.c_void_p), ("out", C.c_void_p), ("its", C.c_uint32), ("crc_ok", C.c_uint32)]
 
 
-def build(force=False):
-    """Compile every CUDA source for sm_100a into the in-tree shared library (nvcc cross-compiles on CPU)."""
+def build(force=False, extra_flags=()):
+    """Compile every CUDA source for sm_100a into the in-tree shared library (nvcc cross-compiles on CPU).
+    One object per source under csrc/_obj (stale ones only, in parallel), then one link."""
+    from concurrent.futures import ThreadPoolExecutor
     srcs = [os.path.join(CSRC, s) for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
-    deps = srcs + [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))]
-    deps.append(os.path.join(os.path.dirname(HERE), "include", "srslte_fec_cuda.h"))
-    if not force and os.path.exists(LIB_PATH) and all(os.path.getmtime(d) <= os.path.getmtime(LIB_PATH) for d in deps if os.path.exists(d)):
-        return LIB_PATH
-    subprocess.check_call(["nvcc"] + NVCC_FLAGS + ["-o", LIB_PATH] + srcs)
+    hdrs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))]
+    hdrs += [os.path.join(os.path.dirname(HERE), "include", f) for f in ("srslte_fec_cuda.h", "srslte_fec_compat.h", "srslte_fec_abi.h")]
+    hdr_t = max(os.path.getmtime(h) for h in hdrs if os.path.exists(h))
+    objdir = os.path.join(CSRC, "_obj")
+    os.makedirs(objdir, exist_ok=True)
+    cflags = [f for f in NVCC_FLAGS if f != "-shared"] + list(extra_flags)
+
+    def compile_one(src):
+        obj = os.path.join(objdir, os.path.basename(src) + ".o")
+        if force or extra_flags or not os.path.exists(obj) or os.path.getmtime(obj) < max(os.path.getmtime(src), hdr_t):
+            subprocess.check_call(["nvcc"] + cflags + ["-c", src, "-o", obj])
+            return obj, True
+        return obj, False
+
+    with ThreadPoolExecutor(max_workers=len(srcs)) as ex:
+        res = list(ex.map(compile_one, srcs))
+    if any(r[1] for r in res) or not os.path.exists(LIB_PATH) or any(os.path.getmtime(r[0]) > os.path.getmtime(LIB_PATH) for r in res):
+        subprocess.check_call(["nvcc"] + NVCC_FLAGS + ["-o", LIB_PATH] + [r[0] for r in res])
     return LIB_PATH
 
 
@@ -84,6 +99,8 @@ def load():
         lib.fec_cuda_launch_count.restype = C.c_uint64
         lib.fec_cuda_softbuffer_alloc.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_uint32)]
         lib.fec_cuda_softbuffer_reset.argtypes = [C.c_void_p, C.c_uint32]
+        lib.fec_cuda_softbuffer_free.argtypes = [C.c_void_p, C.c_uint32]
+        lib.fec_cuda_set_decoder_class.argtypes = [C.c_void_p, C.c_int]
         lib.fec_cuda_softbuffer_read_ref_layout.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]
         lib.fec_cuda_decode_tbs.argtypes = [C.c_void_p, C.POINTER(TbDesc), C.c_uint32, C.c_uint32]
         lib.fec_cuda_submit_tbs.argtypes = [C.c_void_p, C.POINTER(TbDesc), C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64)]
@@ -214,6 +231,15 @@ class FecCuda:
         if rc:
             raise RuntimeError(f"softbuffer_alloc: {rc} {self.error()}")
         return int(first.value)
+
+    def softbuffer_free(self, sb):
+        return self.lib.fec_cuda_softbuffer_free(self.h, sb)
+
+    def set_decoder_class(self, P):
+        """srslte_tdec_init_manual: force the non-windowed (0) / 8 / 16 sub-block 16-bit decoder for every K; -1 = AUTO"""
+        rc = self.lib.fec_cuda_set_decoder_class(self.h, P)
+        if rc:
+            raise RuntimeError(f"fec_cuda_set_decoder_class: {rc}")
 
     def softbuffer_reset(self, sb):
         return self.lib.fec_cuda_softbuffer_reset(self.h, sb)

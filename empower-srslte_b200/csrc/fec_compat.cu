@@ -2,11 +2,13 @@
  * fec_compat.cu — the reference's own C symbols for the decode path as batch-of-one wrappers over the batched
  * API (include/srslte_fec_compat.h).  Host code only; every computation goes through fec_cuda_* (device).
  *
- * One process-wide context (device FEC_CUDA_DEVICE, default 0) is created on first use and shared by all
- * objects; calls are serialised by a mutex.  The reference has no locks on this path and expects one object
- * per worker thread (SURVEY 8b "Threading"): serialising keeps that contract; throughput-minded callers use
- * the batched API directly.
+ * Threading (SURVEY 8b "Threading"): the reference has no locks on this path and expects one object per worker thread,
+ * with several workers decoding at once (the PDSCH co-worker decodes TB0 while the caller decodes TB1, pdsch.c:837-864).
+ * Here every calling THREAD gets its own decode context (streams, staging, per-K tables) on first use, so calls from
+ * different threads run concurrently and a 16-bit and an 8-bit object never share mode state; soft buffers live in the
+ * device-wide pool of fec_cuda_api.cu and can be decoded into from any thread. Device: FEC_CUDA_DEVICE (default 0).
  */
+#include <cstddef>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -14,54 +16,80 @@
 
 #include "../../include/srslte_fec_cuda.h"
 #include "../../include/srslte_fec_compat.h"
+#include "../../include/srslte_fec_abi.h"
 #include "fec_tables.h"
 
-static_assert(sizeof(srslte_tdec_t) == 18264, "srslte_tdec_t view must keep the reference size (SURVEY Appendix B)");
-static_assert(offsetof(srslte_tdec_t, n_iter) == 18256, "n_iter offset");
-static_assert(sizeof(srslte_softbuffer_rx_t) == 40, "srslte_softbuffer_rx_t view must keep the reference size");
-static_assert(offsetof(srslte_softbuffer_rx_t, buffer_f) == 8 && offsetof(srslte_softbuffer_rx_t, cb_crc) == 24 &&
-              offsetof(srslte_softbuffer_rx_t, tb_crc) == 32, "soft buffer field offsets");
+static_assert(sizeof(srslte_tdec_t) == FEC_ABI_SIZEOF_TDEC, "srslte_tdec_t view must keep the reference size (SURVEY Appendix B)");
+static_assert(offsetof(srslte_tdec_t, n_iter) == FEC_ABI_TDEC_N_ITER, "n_iter offset");
+static_assert(sizeof(srslte_softbuffer_rx_t) == FEC_ABI_SIZEOF_SOFTBUFFER_RX, "srslte_softbuffer_rx_t view must keep the reference size");
+static_assert(offsetof(srslte_softbuffer_rx_t, buffer_f) == FEC_ABI_SOFTBUFFER_RX_BUFFER_F && offsetof(srslte_softbuffer_rx_t, cb_crc) == FEC_ABI_SOFTBUFFER_RX_CB_CRC &&
+              offsetof(srslte_softbuffer_rx_t, tb_crc) == FEC_ABI_SOFTBUFFER_RX_TB_CRC, "soft buffer field offsets");
 
 #define COMPAT_MAGIC 0xFEC0B200u
 #define SRSLTE_SUCCESS 0
 #define SRSLTE_ERROR (-1)
 #define SRSLTE_ERROR_INVALID_INPUTS (-2)
 
-static std::mutex g_mu;
-static fec_cuda_ctx_t *g_ctx = NULL;
+static int compat_device(void) { const char *e = getenv("FEC_CUDA_DEVICE"); return e ? atoi(e) : 0; }
+
+/* one decode context per calling thread, destroyed when the thread ends */
+struct CompatThread {
+  fec_cuda_ctx_t *ctx = NULL;
+  ~CompatThread() { if (ctx) fec_cuda_destroy(ctx); }
+};
+static thread_local CompatThread tl_compat;
 
 static fec_cuda_ctx_t *compat_ctx(void)
 {
-  if (!g_ctx) {
-    const char *e = getenv("FEC_CUDA_DEVICE");
+  if (!tl_compat.ctx) {
     fec_cuda_ctx_t *c = NULL;
-    if (fec_cuda_create(&c, e ? atoi(e) : 0, 64) != 0) {
+    if (fec_cuda_create(&c, compat_device(), 64) != 0) {
       fprintf(stderr, "libsrslte_fec_cuda: no usable CUDA device (there is no CPU fallback)\n");
       return NULL;
     }
-    g_ctx = c;
+    tl_compat.ctx = c;
   }
-  return g_ctx;
+  return tl_compat.ctx;
+}
+
+/* soft buffers outlive the thread that allocates them (srsENB's MAC allocates per UE, PHY workers decode): they are taken
+ * from the pooled, process-lifetime part of the device pool through one home context that is never destroyed */
+static std::mutex g_home_mu;
+static fec_cuda_ctx_t *g_home = NULL;
+static fec_cuda_ctx_t *compat_home(void)
+{
+  std::lock_guard<std::mutex> lk(g_home_mu);
+  if (!g_home && fec_cuda_create(&g_home, compat_device(), 1) != 0) {
+    fprintf(stderr, "libsrslte_fec_cuda: no usable CUDA device (there is no CPU fallback)\n");
+    g_home = NULL;
+  }
+  return g_home;
 }
 
 /* ================================================================= turbo decoder (turbodecoder.c:133-533) ==== */
 extern "C" int srslte_tdec_init_manual(srslte_tdec_t *h, uint32_t max_long_cb, srslte_tdec_impl_type_t dec_type)
 {
   if (!h) return SRSLTE_ERROR_INVALID_INPUTS;
-  std::lock_guard<std::mutex> lk(g_mu);
   memset(h, 0, sizeof(*h));                                     /* turbodecoder.c:156 */
-  if (dec_type != SRSLTE_TDEC_AUTO) {
-    /* manual modes pick ONE arithmetic class for every K (turbodecoder.c:160-190); this library implements the AUTO
-     * mapping of an AVX2 build only */
-    fprintf(stderr, "srslte_tdec_init_manual: only SRSLTE_TDEC_AUTO is provided by libsrslte_fec_cuda\n");
+  /* manual modes pick ONE arithmetic class for every K (turbodecoder.c:160-190): the non-windowed decoder, 8 or 16
+   * sub-blocks in 16 bits. The generic decoder (a different algorithm: full-length recursions, turbodecoder_gen.c) and the
+   * manual 8-bit classes are not provided. */
+  int cls;
+  switch (dec_type) {
+  case SRSLTE_TDEC_AUTO:       cls = -1; break;
+  case SRSLTE_TDEC_SSE:        cls = 0;  break;
+  case SRSLTE_TDEC_SSE_WINDOW: cls = 8;  break;
+  case SRSLTE_TDEC_AVX_WINDOW: cls = 16; break;
+  default:
+    fprintf(stderr, "Error decoder %d not supported\n", (int)dec_type);               /* turbodecoder.c:191-193 */
     return SRSLTE_ERROR;
   }
   if (max_long_cb > FEC_CUDA_MAX_K) return SRSLTE_ERROR;
-  h->fec_ctx = compat_ctx();
-  if (!h->fec_ctx) return SRSLTE_ERROR;
+  if (!compat_ctx()) return SRSLTE_ERROR;
   h->fec_input = (int16_t *)malloc(sizeof(int16_t) * (3 * FEC_CUDA_MAX_K + 12));
   if (!h->fec_input) return SRSLTE_ERROR;
   h->max_long_cb = max_long_cb;
+  h->fec_manual_type = (uint32_t)(cls + 1);                     /* 0 = AUTO, else forced class + 1 */
   h->fec_magic = COMPAT_MAGIC;
   return SRSLTE_SUCCESS;
 }
@@ -89,6 +117,12 @@ extern "C" int srslte_tdec_new_cb(srslte_tdec_t *h, uint32_t long_cb)
     fprintf(stderr, "Invalid CB length %u\n", long_cb);
     return SRSLTE_ERROR;
   }
+  if (h->fec_manual_type > 1) {
+    /* a forced windowed class needs whole sub-blocks that cover its 40-step warm-ups (turbodecoder_win.h:321-384); the
+     * reference does not check and reads outside its arrays for the sizes refused here */
+    const uint32_t P = h->fec_manual_type - 1;
+    if (long_cb % P || long_cb / P <= 40) { fprintf(stderr, "CB length %u cannot run in %u sub-blocks\n", long_cb, P); return SRSLTE_ERROR; }
+  }
   h->n_iter = 0;
   h->fec_K = long_cb;
   return SRSLTE_SUCCESS;
@@ -107,7 +141,7 @@ static void compat_take_input(srslte_tdec_t *h, const int16_t *in)
 {
   const uint32_t K = h->fec_K;
   fec_geom_t g;
-  fec_geom(K, &g);
+  if (h->fec_manual_type) fec_geom_p(K, (int)h->fec_manual_type - 1, &g); else fec_geom(K, &g);
   if (g.P == 0 || h->fec_force_not_sb) { memcpy(h->fec_input, in, sizeof(int16_t) * (3 * K + 12)); return; }
   for (uint32_t t = 0; t < 3 * K + 12; t++) h->fec_input[t] = in[fec_soft_offset_ref(&g, (int)t, 1)];
 }
@@ -119,17 +153,20 @@ static int compat_run(srslte_tdec_t *h, uint8_t *output, uint32_t halfits, int l
   fec_cuda_cb_t cb;
   memset(&cb, 0, sizeof(cb));
   cb.K = h->fec_K; cb.max_its = halfits; cb.crc_type = 1; cb.llr = h->fec_input; cb.out = output;
-  fec_cuda_set_llr_8bit((fec_cuda_ctx_t *)h->fec_ctx, llr8);       /* the shared context is switched under g_mu */
-  const int r = fec_cuda_decode_cbs((fec_cuda_ctx_t *)h->fec_ctx, &cb, 1, FEC_CUDA_F_NO_EARLY_STOP);
-  fec_cuda_set_llr_8bit((fec_cuda_ctx_t *)h->fec_ctx, 0);
-  if (r) fprintf(stderr, "libsrslte_fec_cuda: %s\n", fec_cuda_last_error((fec_cuda_ctx_t *)h->fec_ctx));
+  fec_cuda_ctx_t *ctx = compat_ctx();                              /* this thread's context: nobody else switches its mode */
+  if (!ctx) return SRSLTE_ERROR;
+  fec_cuda_set_llr_8bit(ctx, llr8);
+  fec_cuda_set_decoder_class(ctx, llr8 ? -1 : (int)h->fec_manual_type - 1);
+  const int r = fec_cuda_decode_cbs(ctx, &cb, 1, FEC_CUDA_F_NO_EARLY_STOP);
+  fec_cuda_set_llr_8bit(ctx, 0);
+  fec_cuda_set_decoder_class(ctx, -1);
+  if (r) fprintf(stderr, "libsrslte_fec_cuda: %s\n", fec_cuda_last_error(ctx));
   return r;
 }
 
 extern "C" void srslte_tdec_iteration(srslte_tdec_t *h, int16_t *input, uint8_t *output)
 {
   if (!h || h->fec_magic != COMPAT_MAGIC || !h->fec_K || !input || !output) return;
-  std::lock_guard<std::mutex> lk(g_mu);
   if (h->n_iter == 0) compat_take_input(h, input);
   if (compat_run(h, output, h->n_iter + 1) == 0) h->n_iter++;
 }
@@ -138,7 +175,6 @@ extern "C" int srslte_tdec_run_all(srslte_tdec_t *h, int16_t *input, uint8_t *ou
 {
   if (srslte_tdec_new_cb(h, long_cb)) return SRSLTE_ERROR;       /* turbodecoder.c:510-533 */
   if (!input || !output) return SRSLTE_ERROR;
-  std::lock_guard<std::mutex> lk(g_mu);
   compat_take_input(h, input);
   if (nof_iterations == 0) return SRSLTE_SUCCESS;
   if (compat_run(h, output, nof_iterations)) return SRSLTE_ERROR;
@@ -160,7 +196,6 @@ static void compat_take_input8(srslte_tdec_t *h, const int8_t *in)
 extern "C" void srslte_tdec_iteration_8bit(srslte_tdec_t *h, int8_t *input, uint8_t *output)
 {
   if (!h || h->fec_magic != COMPAT_MAGIC || !h->fec_K || !input || !output) return;
-  std::lock_guard<std::mutex> lk(g_mu);
   if (h->n_iter == 0) compat_take_input8(h, input);
   if (compat_run(h, output, h->n_iter + 1, 1) == 0) h->n_iter++;
 }
@@ -169,7 +204,6 @@ extern "C" int srslte_tdec_run_all_8bit(srslte_tdec_t *h, int8_t *input, uint8_t
 {
   if (srslte_tdec_new_cb(h, long_cb)) return SRSLTE_ERROR;       /* turbodecoder.c:545-563 */
   if (!input || !output) return SRSLTE_ERROR;
-  std::lock_guard<std::mutex> lk(g_mu);
   compat_take_input8(h, input);
   if (nof_iterations == 0) return SRSLTE_SUCCESS;
   if (compat_run(h, output, nof_iterations, 1)) return SRSLTE_ERROR;
@@ -187,7 +221,6 @@ extern "C" int srslte_rm_turbo_rx_lut_(int16_t *input, int16_t *output, uint32_t
     fprintf(stderr, "Invalid inputs rv_idx=%d, cb_idx=%d\n", rv_idx, cb_idx);
     return SRSLTE_ERROR_INVALID_INPUTS;
   }
-  std::lock_guard<std::mutex> lk(g_mu);
   fec_cuda_ctx_t *ctx = compat_ctx();
   if (!ctx) return SRSLTE_ERROR;
   const int r = fec_cuda_rm_rx(ctx, input, in_len, cb_idx, rv_idx, enable_input_tdec ? 1 : 0, output);
@@ -202,7 +235,6 @@ extern "C" int srslte_rm_turbo_rx_lut_8bit(int8_t *input, int8_t *output, uint32
     fprintf(stderr, "Invalid inputs rv_idx=%d, cb_idx=%d\n", rv_idx, cb_idx);
     return SRSLTE_ERROR_INVALID_INPUTS;
   }
-  std::lock_guard<std::mutex> lk(g_mu);
   fec_cuda_ctx_t *ctx = compat_ctx();
   if (!ctx) return SRSLTE_ERROR;
   fec_cuda_set_llr_8bit(ctx, 1);
@@ -239,13 +271,14 @@ extern "C" int srslte_softbuffer_rx_init(srslte_softbuffer_rx_t *q, uint32_t nof
   if (!q) return SRSLTE_ERROR_INVALID_INPUTS;
   memset(q, 0, sizeof(*q));                                      /* softbuffer.c:50 */
   if (nof_prb < 1 || nof_prb > 110) return SRSLTE_ERROR;         /* srslte_ra_tbs_from_idx fails (softbuffer.c:52-53) */
-  std::lock_guard<std::mutex> lk(g_mu);
-  fec_cuda_ctx_t *ctx = compat_ctx();
+  fec_cuda_ctx_t *ctx = compat_home();
   if (!ctx) return SRSLTE_ERROR;
   compat_sb_t *s = (compat_sb_t *)calloc(1, sizeof(*s));
   q->max_cb = tbs_itbs26[nof_prb - 1] / (6144 - 24) + 1;
   q->cb_crc = (bool *)calloc(q->max_cb, sizeof(bool));
-  if (!s || !q->cb_crc || fec_cuda_softbuffer_alloc(ctx, 1, &s->id)) { free(s); free(q->cb_crc); memset(q, 0, sizeof(*q)); return SRSLTE_ERROR; }
+  int arc = -1;
+  if (s && q->cb_crc) { std::lock_guard<std::mutex> lk(g_home_mu); arc = fec_cuda_softbuffer_alloc(ctx, 1, &s->id); }
+  if (arc) { free(s); free(q->cb_crc); memset(q, 0, sizeof(*q)); return SRSLTE_ERROR; }
   s->magic = COMPAT_MAGIC; s->pending_new = 1;
   q->buffer_f = (int16_t **)s;
   return SRSLTE_SUCCESS;
@@ -254,8 +287,13 @@ extern "C" int srslte_softbuffer_rx_init(srslte_softbuffer_rx_t *q, uint32_t nof
 extern "C" void srslte_softbuffer_rx_free(srslte_softbuffer_rx_t *q)
 {
   if (!q) return;
-  /* device slots are pooled for the lifetime of the context (softbuffer ids are not recycled) */
-  if (compat_sb(q)) free(q->buffer_f);
+  /* the device buffer goes back to the pool's free list (zeroed for its next user) */
+  if (compat_sb(q)) {
+    fec_cuda_ctx_t *ctx = compat_home();
+    if (ctx) { std::lock_guard<std::mutex> lk(g_home_mu); fec_cuda_softbuffer_free(ctx, compat_sb(q)->id); }
+    compat_sb(q)->magic = 0;
+    free(q->buffer_f);
+  }
   if (q->cb_crc) free(q->cb_crc);
   memset(q, 0, sizeof(*q));
 }
@@ -285,7 +323,6 @@ static int compat_decode_tb(srslte_softbuffer_rx_t *softbuffer, uint32_t tbs, ui
     fprintf(stderr, "Error number of CB (%d) exceeds soft buffer size (%d CBs)\n", seg[1], softbuffer->max_cb);
     return SRSLTE_ERROR_INVALID_INPUTS;
   }
-  std::lock_guard<std::mutex> lk(g_mu);
   fec_cuda_ctx_t *ctx = compat_ctx();
   if (!ctx) return SRSLTE_ERROR;
   fec_cuda_tb_t t;
@@ -296,7 +333,10 @@ static int compat_decode_tb(srslte_softbuffer_rx_t *softbuffer, uint32_t tbs, ui
   const int rc = fec_cuda_decode_tbs(ctx, &t, 1, 0);
   fec_cuda_set_llr_8bit(ctx, 0);
   if (rc) { fprintf(stderr, "libsrslte_fec_cuda: %s\n", fec_cuda_last_error(ctx)); return SRSLTE_ERROR; }
-  s->pending_new = 0;
+  /* the deferred reset is spent only when the rate de-matcher ran with it; a transport block the library refused (-2)
+   * wrote nothing to the device buffer, so the next valid decode still has to start from zero */
+  if (t.ret != FEC_CUDA_EINVAL) s->pending_new = 0;
+  else return SRSLTE_ERROR_INVALID_INPUTS;
   for (uint32_t c = 0; c < seg[1] && c < softbuffer->max_cb; c++) softbuffer->cb_crc[c] = t.cb_crc[c] != 0;
   bool all = true;
   for (uint32_t c = 0; c < seg[1]; c++) all = all && t.cb_crc[c];
@@ -319,11 +359,36 @@ extern "C" int srslte_sch_decode_tb_cuda_8bit(srslte_softbuffer_rx_t *softbuffer
   return compat_decode_tb(softbuffer, tbs, Qm, rv, nof_e_bits, e_bits, 1, data, max_iterations, nof_iterations);
 }
 
+/* ================================================================= srslte_dlsch_decode[2] (sch.c:488-517) ==== */
+/* The reference's own DL-SCH entry points on the reference's own structs. Only the fields decode_tb reads are touched,
+ * through the offsets of include/srslte_fec_abi.h (asserted against the real headers by the ABI checker that is compiled with the link tests):
+ * q->max_iterations / nof_iterations / llr_is_8bit, cfg->cb_segm[tb].tbs, cfg->grant.Qm[tb] / tb_en[], cfg->rv[tb],
+ * cfg->nbits[tb].nof_bits, cfg->nof_layers. */
+template <typename T> static T &abi_at(void *base, size_t off) { return *(T *)((char *)base + off); }
+
+extern "C" int srslte_dlsch_decode2(void *q, void *cfg, srslte_softbuffer_rx_t *softbuffer, int16_t *e_bits, uint8_t *data, int tb_idx)
+{
+  if (!q || !cfg || tb_idx < 0 || tb_idx >= FEC_ABI_MAX_CODEWORDS) return SRSLTE_ERROR_INVALID_INPUTS;
+  const uint32_t ntb = (abi_at<bool>(cfg, FEC_ABI_PDSCH_CFG_GRANT + FEC_ABI_DL_GRANT_TB_EN) ? 1u : 0u) +
+                       (abi_at<bool>(cfg, FEC_ABI_PDSCH_CFG_GRANT + FEC_ABI_DL_GRANT_TB_EN + 1) ? 1u : 0u);       /* SRSLTE_RA_DL_GRANT_NOF_TB */
+  const uint32_t Nl = abi_at<uint32_t>(cfg, FEC_ABI_PDSCH_CFG_NOF_LAYERS) != ntb ? 2 : 1;                         /* sch.c:508-512 */
+  const uint32_t tbs = abi_at<uint32_t>(cfg, FEC_ABI_PDSCH_CFG_CB_SEGM + (size_t)tb_idx * FEC_ABI_SIZEOF_CBSEGM + FEC_ABI_CBSEGM_TBS);
+  const uint32_t Qm = abi_at<uint32_t>(cfg, FEC_ABI_PDSCH_CFG_GRANT + FEC_ABI_DL_GRANT_QM + 4 * (size_t)tb_idx) * Nl;
+  const uint32_t rv = abi_at<uint32_t>(cfg, FEC_ABI_PDSCH_CFG_RV + 4 * (size_t)tb_idx);
+  const uint32_t nbits = abi_at<uint32_t>(cfg, FEC_ABI_PDSCH_CFG_NBITS + (size_t)tb_idx * FEC_ABI_SIZEOF_RA_NBITS + FEC_ABI_RA_NBITS_NOF_BITS);
+  return compat_decode_tb(softbuffer, tbs, Qm, rv, nbits, e_bits, abi_at<bool>(q, FEC_ABI_SCH_LLR_IS_8BIT) ? 1 : 0, data,
+                          abi_at<uint32_t>(q, FEC_ABI_SCH_MAX_ITERATIONS), &abi_at<uint32_t>(q, FEC_ABI_SCH_NOF_ITERATIONS));
+}
+
+extern "C" int srslte_dlsch_decode(void *q, void *cfg, srslte_softbuffer_rx_t *softbuffer, int16_t *e_bits, uint8_t *data)
+{
+  return srslte_dlsch_decode2(q, cfg, softbuffer, e_bits, data, 0);
+}
+
 /* ================================================================= encode_tb_off (sch.c:188-296) ==== */
 extern "C" int srslte_sch_encode_tb_cuda(uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits, uint8_t *data, uint8_t *e_bits)
 {
   if (!e_bits || !data) return SRSLTE_ERROR_INVALID_INPUTS;                    /* sch.c:196-199 */
-  std::lock_guard<std::mutex> lk(g_mu);
   fec_cuda_ctx_t *ctx = compat_ctx();
   if (!ctx) return SRSLTE_ERROR;
   fec_cuda_txtb_t t;

@@ -13,6 +13,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <time.h>
+#include <pthread.h>
 
 #define CB_BYTES 768     /* 6144/8: per-CB decoded byte slot */
 
@@ -33,7 +34,25 @@ typedef struct {
   int16_t *d_soft;    /* n x 13 x FEC_CUDA_SOFT_SLOT */
   uint8_t *d_cache;   /* n x 13 x CB_BYTES */
   uint8_t *cb_crc;    /* host: n x 13 */
+  struct fec_cuda_ctx *owner;   /* context whose destruction releases the chunk; NULL: pooled single buffers, process lifetime */
 } sbchunk_t;
+
+/* HARQ soft buffers belong to the DEVICE, not to a context: the reference allocates them in one thread (MAC) and decodes
+ * into them from others (PHY workers, one srslte_sch_t each: SURVEY 8b "Threading"), so every context of a device must be
+ * able to decode into any of them. One pool per device; ids are unique per device. Bulk allocations (n > 1) are owned by
+ * the allocating context and die with it; single buffers (n == 1) come from pooled chunks of SB_POOL_N, are recycled
+ * through a free list (fec_cuda_softbuffer_free) and live as long as the process. */
+#define FEC_MAX_DEV 64
+#define SB_POOL_N   32
+typedef struct { int16_t *soft0; uint8_t *cache0; uint8_t *crc; } sbref_t;
+typedef struct {
+  pthread_rwlock_t lock;
+  sbchunk_t *chunks; uint32_t nchunks, next_id;
+  uint32_t  *free_ids; uint32_t nfree, free_cap;
+} sbpool_t;
+static sbpool_t g_pool[FEC_MAX_DEV];
+static pthread_once_t g_pool_once = PTHREAD_ONCE_INIT;
+static void pool_init_all(void) { for (int i = 0; i < FEC_MAX_DEV; i++) pthread_rwlock_init(&g_pool[i].lock, NULL); }
 
 typedef struct { void *h, *d; size_t cap; } stage_t;   /* pinned host + device mirror, grown on demand */
 #define FEC_NPIPE 8
@@ -47,10 +66,11 @@ struct fec_cuda_ctx {
   uint32_t      max_tbs;
   ktab_t        ktab[FEC_NOF_K];
   ktab_t        ktab8[FEC_NOF_K];   /* the same per-K tables in the geometry of the 8-bit LLR path (P = 32 for K > 2048) */
+  ktab_t        ktabm[3][FEC_NOF_K];/* ... and in a forced 16-bit class (srslte_tdec_init_manual): non-windowed, 8 and 16 sub-blocks */
+  int           force_p;            /* -1: the AUTO mapping; 0 / 8 / 16: that class for every code block size */
   int           llr8;               /* srslte_sch_t.llr_is_8bit: e_bits are int8, int8 combining and decoders (sch.c:344-348,362-364) */
   uint32_t     *d_r24a, *d_r24b;
-  sbchunk_t    *chunks;
-  uint32_t      nchunks, next_id;
+  sbpool_t     *pool;               /* the soft-buffer pool of this context's device */
   stage_t       st_e, st_data, st_cbd, st_rmd, st_tbd, st_status, st_ret, st_exd;
   stage_t       st_txin, st_txout, st_txtb, st_txcb;   /* transmit side: payloads, packed output, descriptors */
   uint8_t      *d_txcrc; size_t txcrc_cap;
@@ -84,6 +104,8 @@ struct fec_cuda_ctx {
 };
 
 static int pipes_create(fec_cuda_ctx_t *ctx);
+static int pipe_finish(fec_cuda_ctx_t *ctx, fec_pipe_t *pp);
+static void pipes_drain(fec_cuda_ctx_t *ctx);
 static double now_ms(void) { struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e3 + ts.tv_nsec / 1e6; }
 static void pipes_destroy(fec_cuda_ctx_t *ctx);
 
@@ -138,7 +160,11 @@ extern "C" int fec_cuda_create(fec_cuda_ctx_t **out, int device, uint32_t max_tb
     return fail(NULL, FEC_CUDA_ENODEV, "libsrslte_fec_cuda: no usable CUDA device %d (there is no CPU fallback)\n", device);
   fec_cuda_ctx_t *ctx = (fec_cuda_ctx_t *)calloc(1, sizeof(*ctx));
   if (!ctx) return FEC_CUDA_ERROR;
+  if (device >= FEC_MAX_DEV) { free(ctx); return FEC_CUDA_EINVAL; }
+  pthread_once(&g_pool_once, pool_init_all);
+  ctx->pool = &g_pool[device];
   ctx->device = device; ctx->max_tbs = max_tbs_per_call ? max_tbs_per_call : 1;
+  ctx->force_p = -1;
   cudaDeviceProp prop;
   if (cudaSetDevice(device) != cudaSuccess || cudaGetDeviceProperties(&prop, device) != cudaSuccess) { free(ctx); return FEC_CUDA_ENODEV; }
   if (prop.major < 10) { fprintf(stderr, "libsrslte_fec_cuda: built for sm_100a only, device is sm_%d%d\n", prop.major, prop.minor); free(ctx); return FEC_CUDA_ENODEV; }
@@ -178,14 +204,25 @@ extern "C" void fec_cuda_destroy(fec_cuda_ctx_t *ctx)
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
-  for (int i = 0; i < 2 * FEC_NOF_K; i++) if ((i < FEC_NOF_K ? ctx->ktab[i] : ctx->ktab8[i - FEC_NOF_K]).ready) {
-    ktab_t *kt = i < FEC_NOF_K ? &ctx->ktab[i] : &ctx->ktab8[i - FEC_NOF_K];
+  for (int i = 0; i < 5 * FEC_NOF_K; i++) {
+    ktab_t *kt = i < FEC_NOF_K ? &ctx->ktab[i] : i < 2 * FEC_NOF_K ? &ctx->ktab8[i - FEC_NOF_K] : &ctx->ktabm[i / FEC_NOF_K - 2][i % FEC_NOF_K];
+    if (!kt->ready) continue;
     cudaFree(kt->d_step); cudaFree(kt->d_rank); cudaFree(kt->d_pair_addr); cudaFree(kt->d_txsrc);
     cudaFree(kt->d_pair_crc[0]); cudaFree(kt->d_pair_crc[1]);
   }
   cudaFree(ctx->d_softmax); cudaFree(ctx->d_exact); cudaFree(ctx->d_econt); cudaFreeHost(ctx->h_queue);
-  for (uint32_t i = 0; i < ctx->nchunks; i++) { cudaFree(ctx->chunks[i].d_soft); cudaFree(ctx->chunks[i].d_cache); free(ctx->chunks[i].cb_crc); }
-  free(ctx->chunks);
+  pipes_drain(ctx);                              /* nothing in flight may touch the chunks */
+  {
+    sbpool_t *pl = ctx->pool;
+    pthread_rwlock_wrlock(&pl->lock);
+    uint32_t w = 0;
+    for (uint32_t i = 0; i < pl->nchunks; i++) {
+      if (pl->chunks[i].owner == ctx) { cudaFree(pl->chunks[i].d_soft); cudaFree(pl->chunks[i].d_cache); free(pl->chunks[i].cb_crc); }
+      else pl->chunks[w++] = pl->chunks[i];
+    }
+    pl->nchunks = w;
+    pthread_rwlock_unlock(&pl->lock);
+  }
   stage_free(&ctx->st_e); stage_free(&ctx->st_data); stage_free(&ctx->st_cbd); stage_free(&ctx->st_rmd);
   stage_free(&ctx->st_tbd); stage_free(&ctx->st_status); stage_free(&ctx->st_ret); stage_free(&ctx->st_exd);
   stage_free(&ctx->st_txin); stage_free(&ctx->st_txout); stage_free(&ctx->st_txtb); stage_free(&ctx->st_txcb); cudaFree(ctx->d_txcrc);
@@ -203,6 +240,23 @@ extern "C" int fec_cuda_set_llr_8bit(fec_cuda_ctx_t *ctx, int on)
   if (!ctx) return FEC_CUDA_EINVAL;
   ctx->llr8 = on ? 1 : 0;
   return 0;
+}
+
+/* srslte_tdec_init_manual (turbodecoder.c:153-190): one 16-bit arithmetic class for every code block size instead of the
+ * AUTO mapping — P = 0 the non-windowed decoder (SRSLTE_TDEC_SSE), 8 (SRSLTE_TDEC_SSE_WINDOW), 16 (SRSLTE_TDEC_AVX_WINDOW);
+ * -1 returns to AUTO. Forced classes run in the exact kernels. Applies to fec_cuda_decode_cbs (the srslte_tdec_* level). */
+extern "C" int fec_cuda_set_decoder_class(fec_cuda_ctx_t *ctx, int P)
+{
+  if (!ctx || !(P == -1 || P == 0 || P == 8 || P == 16)) return FEC_CUDA_EINVAL;
+  ctx->force_p = P;
+  return 0;
+}
+
+static ktab_t *ktab_of(fec_cuda_ctx_t *ctx, int idx)
+{
+  if (ctx->llr8) return &ctx->ktab8[idx];
+  if (ctx->force_p >= 0) return &ctx->ktabm[ctx->force_p == 0 ? 0 : ctx->force_p == 8 ? 1 : 2][idx];
+  return &ctx->ktab[idx];
 }
 
 extern "C" const char *fec_cuda_last_error(fec_cuda_ctx_t *ctx) { return ctx ? ctx->err : "null context"; }
@@ -241,9 +295,14 @@ static int ktab_get(fec_cuda_ctx_t *ctx, uint32_t K, ktab_t **out)
 {
   int idx = fec_k_index(K);
   if (idx < 0 || fec_k_size(idx) != (int)K) return fail(ctx, FEC_CUDA_EINVAL, "K=%u is not an LTE code block size", K);
-  ktab_t *t = ctx->llr8 ? &ctx->ktab8[idx] : &ctx->ktab[idx];
+  ktab_t *t = ktab_of(ctx, idx);
   if (!t->ready) {
-    if (ctx->llr8) fec_geom_p(K, fec_k_subblocks8(K), &t->g); else fec_geom(K, &t->g);
+    if (ctx->llr8) fec_geom_p(K, fec_k_subblocks8(K), &t->g);
+    else if (ctx->force_p >= 0) {
+      /* a windowed class needs whole sub-blocks that cover the 40-step warm-up of turbodecoder_win.h:321-384 */
+      if (ctx->force_p && (K % ctx->force_p || K / ctx->force_p <= 40)) return fail(ctx, FEC_CUDA_EINVAL, "K=%u cannot run in the forced class of %d sub-blocks", K, ctx->force_p);
+      fec_geom_p(K, ctx->force_p, &t->g);
+    } else fec_geom(K, &t->g);
     const size_t nstep = 2 * (size_t)t->g.SS, nrank = 3 * (size_t)t->g.SS + 16;
     uint32_t *step = (uint32_t *)malloc(nstep * 4);
     uint16_t *rank = (uint16_t *)malloc(nrank * 2);
@@ -275,59 +334,125 @@ static int ktab_get(fec_cuda_ctx_t *ctx, uint32_t K, ktab_t **out)
 }
 
 /* ---------------------------------------------------------------- soft buffers ---- */
-extern "C" int fec_cuda_softbuffer_alloc(fec_cuda_ctx_t *ctx, uint32_t n, uint32_t *first_id)
+/* new chunk of n buffers; the pool's write lock is held by the caller */
+static int pool_add_chunk(fec_cuda_ctx_t *ctx, sbpool_t *pl, uint32_t n, fec_cuda_ctx_t *owner, uint32_t *first_id)
 {
-  if (!ctx || !n || !first_id) return FEC_CUDA_EINVAL;
-  cudaSetDevice(ctx->device);
   sbchunk_t c;
   memset(&c, 0, sizeof(c));
-  c.first_id = ctx->next_id; c.n = n;
+  c.first_id = pl->next_id; c.n = n; c.owner = owner;
   CU(cudaMalloc(&c.d_soft, (size_t)n * FEC_CUDA_MAX_CB * FEC_CUDA_SOFT_SLOT * sizeof(int16_t)));
-  CU(cudaMalloc(&c.d_cache, (size_t)n * FEC_CUDA_MAX_CB * CB_BYTES));
+  if (cudaMalloc(&c.d_cache, (size_t)n * FEC_CUDA_MAX_CB * CB_BYTES) != cudaSuccess) { cudaFree(c.d_soft); return fail(ctx, FEC_CUDA_ENODEV, "soft buffers: out of device memory"); }
+  c.cb_crc = (uint8_t *)calloc((size_t)n * FEC_CUDA_MAX_CB, 1);
+  sbchunk_t *nc = (sbchunk_t *)realloc(pl->chunks, sizeof(sbchunk_t) * (pl->nchunks + 1));
+  if (!c.cb_crc || !nc) { cudaFree(c.d_soft); cudaFree(c.d_cache); free(c.cb_crc); if (nc) pl->chunks = nc; return fail(ctx, FEC_CUDA_ERROR, "soft buffers: out of host memory"); }
+  pl->chunks = nc;
   CU(cudaMemsetAsync(c.d_soft, 0, (size_t)n * FEC_CUDA_MAX_CB * FEC_CUDA_SOFT_SLOT * sizeof(int16_t), ctx->stream));
   CU(cudaMemsetAsync(c.d_cache, 0, (size_t)n * FEC_CUDA_MAX_CB * CB_BYTES, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));      /* decode calls run on several streams */
-  c.cb_crc = (uint8_t *)calloc((size_t)n * FEC_CUDA_MAX_CB, 1);
-  ctx->chunks = (sbchunk_t *)realloc(ctx->chunks, sizeof(sbchunk_t) * (ctx->nchunks + 1));
-  ctx->chunks[ctx->nchunks++] = c;
-  ctx->next_id += n;
+  pl->chunks[pl->nchunks++] = c;
+  pl->next_id += n;
   *first_id = c.first_id;
   return 0;
 }
 
-static sbchunk_t *sb_find(fec_cuda_ctx_t *ctx, uint32_t id, uint32_t *local)
+/* id -> device slot 0, decoded-CB cache and host cb_crc flags of that buffer (copied out under the read lock: the chunk
+ * array may be reallocated by another thread's allocation, the memory it points to stays until the owner is destroyed) */
+static int sb_lookup(fec_cuda_ctx_t *ctx, uint32_t id, sbref_t *out)
 {
-  for (uint32_t i = 0; i < ctx->nchunks; i++)
-    if (id >= ctx->chunks[i].first_id && id < ctx->chunks[i].first_id + ctx->chunks[i].n) {
-      *local = id - ctx->chunks[i].first_id;
-      return &ctx->chunks[i];
+  sbpool_t *pl = ctx->pool;
+  int found = 0;
+  pthread_rwlock_rdlock(&pl->lock);
+  for (uint32_t i = 0; i < pl->nchunks; i++) {
+    const sbchunk_t *c = &pl->chunks[i];
+    if (id >= c->first_id && id - c->first_id < c->n) {
+      const size_t l = id - c->first_id;
+      out->soft0 = c->d_soft + l * FEC_CUDA_MAX_CB * FEC_CUDA_SOFT_SLOT;
+      out->cache0 = c->d_cache + l * FEC_CUDA_MAX_CB * CB_BYTES;
+      out->crc = c->cb_crc + l * FEC_CUDA_MAX_CB;
+      found = 1;
+      break;
     }
-  return NULL;
+  }
+  pthread_rwlock_unlock(&pl->lock);
+  return found;
 }
 
-extern "C" int fec_cuda_softbuffer_reset(fec_cuda_ctx_t *ctx, uint32_t id)
+static int sb_zero(fec_cuda_ctx_t *ctx, const sbref_t *r)
 {
-  uint32_t l;
-  sbchunk_t *c = ctx ? sb_find(ctx, id, &l) : NULL;
-  if (!c) return FEC_CUDA_EINVAL;
-  cudaSetDevice(ctx->device);
-  memset(c->cb_crc + (size_t)l * FEC_CUDA_MAX_CB, 0, FEC_CUDA_MAX_CB);
-  CU(cudaMemsetAsync(c->d_soft + (size_t)l * FEC_CUDA_MAX_CB * FEC_CUDA_SOFT_SLOT, 0,
-                     (size_t)FEC_CUDA_MAX_CB * FEC_CUDA_SOFT_SLOT * sizeof(int16_t), ctx->stream));
+  memset(r->crc, 0, FEC_CUDA_MAX_CB);
+  CU(cudaMemsetAsync(r->soft0, 0, (size_t)FEC_CUDA_MAX_CB * FEC_CUDA_SOFT_SLOT * sizeof(int16_t), ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
   return 0;
 }
 
+extern "C" int fec_cuda_softbuffer_alloc(fec_cuda_ctx_t *ctx, uint32_t n, uint32_t *first_id)
+{
+  if (!ctx || !n || !first_id) return FEC_CUDA_EINVAL;
+  cudaSetDevice(ctx->device);
+  sbpool_t *pl = ctx->pool;
+  int rc = 0;
+  pthread_rwlock_wrlock(&pl->lock);
+  if (n > 1) rc = pool_add_chunk(ctx, pl, n, ctx, first_id);
+  else {
+    if (pl->nfree == 0) {
+      /* a pooled chunk: one id for the caller, the rest on the free list (softbuffer.c:46-100 allocates per UE on attach;
+       * one cudaMalloc pair per SB_POOL_N of them instead of per buffer) */
+      uint32_t f0 = 0;
+      rc = pool_add_chunk(ctx, pl, SB_POOL_N, NULL, &f0);
+      if (!rc && pl->free_cap < pl->nfree + SB_POOL_N) {
+        uint32_t *nf = (uint32_t *)realloc(pl->free_ids, sizeof(uint32_t) * (pl->nfree + SB_POOL_N + pl->free_cap));
+        if (nf) { pl->free_ids = nf; pl->free_cap = pl->nfree + SB_POOL_N + pl->free_cap; } else rc = FEC_CUDA_ERROR;
+      }
+      for (uint32_t i = 0; !rc && i < SB_POOL_N; i++) pl->free_ids[pl->nfree++] = f0 + SB_POOL_N - 1 - i;
+    }
+    if (!rc) *first_id = pl->free_ids[--pl->nfree];
+  }
+  pthread_rwlock_unlock(&pl->lock);
+  return rc;
+}
+
+/* srslte_softbuffer_rx_free (softbuffer.c:102-126): a single buffer (n == 1 allocation) goes back to the pool, zeroed for
+ * its next user; buffers of a bulk allocation are released with their context, freeing one of them is a no-op */
+extern "C" int fec_cuda_softbuffer_free(fec_cuda_ctx_t *ctx, uint32_t id)
+{
+  sbref_t r;
+  if (!ctx || !sb_lookup(ctx, id, &r)) return FEC_CUDA_EINVAL;
+  cudaSetDevice(ctx->device);
+  sbpool_t *pl = ctx->pool;
+  int pooled = 0, rc = 0;
+  pthread_rwlock_wrlock(&pl->lock);
+  for (uint32_t i = 0; i < pl->nchunks; i++)
+    if (id >= pl->chunks[i].first_id && id - pl->chunks[i].first_id < pl->chunks[i].n) pooled = pl->chunks[i].owner == NULL;
+  for (uint32_t i = 0; pooled && i < pl->nfree; i++) if (pl->free_ids[i] == id) pooled = 0;       /* double free */
+  if (pooled) {
+    if (pl->nfree == pl->free_cap) {
+      uint32_t *nf = (uint32_t *)realloc(pl->free_ids, sizeof(uint32_t) * (pl->free_cap + SB_POOL_N));
+      if (nf) { pl->free_ids = nf; pl->free_cap += SB_POOL_N; } else rc = FEC_CUDA_ERROR;
+    }
+    if (!rc) rc = sb_zero(ctx, &r);
+    if (!rc) pl->free_ids[pl->nfree++] = id;
+  }
+  pthread_rwlock_unlock(&pl->lock);
+  return rc;
+}
+
+extern "C" int fec_cuda_softbuffer_reset(fec_cuda_ctx_t *ctx, uint32_t id)
+{
+  sbref_t r;
+  if (!ctx || !sb_lookup(ctx, id, &r)) return FEC_CUDA_EINVAL;
+  cudaSetDevice(ctx->device);
+  return sb_zero(ctx, &r);
+}
+
 extern "C" int fec_cuda_softbuffer_read_ref_layout(fec_cuda_ctx_t *ctx, uint32_t id, uint32_t cb, uint32_t K, int16_t *out)
 {
-  uint32_t l;
-  sbchunk_t *c = ctx ? sb_find(ctx, id, &l) : NULL;
+  sbref_t r;
   ktab_t *t;
-  if (!c || cb >= FEC_CUDA_MAX_CB || !out) return FEC_CUDA_EINVAL;
+  if (!ctx || !sb_lookup(ctx, id, &r) || cb >= FEC_CUDA_MAX_CB || !out) return FEC_CUDA_EINVAL;
   cudaSetDevice(ctx->device);
   if (ktab_get(ctx, K, &t)) return FEC_CUDA_EINVAL;
   if (dev_reserve(ctx, (void **)&ctx->d_tmpsoft, &ctx->tmpsoft_cap, 2 * FEC_CUDA_SOFT_SLOT * sizeof(int16_t))) return FEC_CUDA_ENODEV;
-  CU(fec_launch_soft_to_ref(c->d_soft + ((size_t)l * FEC_CUDA_MAX_CB + cb) * FEC_CUDA_SOFT_SLOT, ctx->d_tmpsoft, t->g, 1, 0, ctx->stream));
+  CU(fec_launch_soft_to_ref(r.soft0 + (size_t)cb * FEC_CUDA_SOFT_SLOT, ctx->d_tmpsoft, t->g, 1, 0, ctx->stream));
   ctx->launches++;
   CU(cudaMemcpyAsync(out, ctx->d_tmpsoft, 18600 * sizeof(int16_t), cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
@@ -337,7 +462,7 @@ extern "C" int fec_cuda_softbuffer_read_ref_layout(fec_cuda_ctx_t *ctx, uint32_t
 static void fill_decode_args(fec_cuda_ctx_t *ctx, int k, FecDecodeArgs *a, const FecCbDesc *cbd_dev, FecCbStatus *status_dev,
                              unsigned int *queue3, const uint32_t *softmax, uint32_t *exact, uint32_t *trk, uint32_t *econt, uint32_t off, uint32_t cnt, int16_t *dbg)
 {
-  const ktab_t *t = ctx->llr8 ? &ctx->ktab8[k] : &ctx->ktab[k];
+  const ktab_t *t = ktab_of(ctx, k);
   memset(a, 0, sizeof(*a));
   a->llr8 = ctx->llr8 && t->g.P >= 16;     /* classes 8 / 0 of the 8-bit path run the 16-bit decoders on the widened values */
   a->g = t->g; a->step_tab = t->d_step; a->crcpow[0] = ctx->d_r24a; a->crcpow[1] = ctx->d_r24b;
@@ -345,7 +470,7 @@ static void fill_decode_args(fec_cuda_ctx_t *ctx, int k, FecDecodeArgs *a, const
   a->queue = queue3 + 2 * k; a->ncb = cnt; a->slots = t->slots; a->dbg_llr = dbg;
   a->pair_addr = t->d_pair_addr; a->pair_crc[0] = t->d_pair_crc[0]; a->pair_crc[1] = t->d_pair_crc[1];
   a->soft_max = softmax; a->status_off = off;
-  if (t->g.P && !ctx->force_exact && !dbg && !a->llr8) {
+  if (t->g.P && !ctx->force_exact && ctx->force_p < 0 && !dbg && !a->llr8) {
     a->exact_list = exact + off; a->exact_count = queue3 + 2 * FEC_NOF_K + k;
     a->trk_list = trk + off; a->trk_queue = queue3 + 3 * FEC_NOF_K + k; a->trk_count = queue3 + 4 * FEC_NOF_K + k;
     /* hand-over in mid-decode: continuation words behind the two lists, extrinsic scratch slots shared by the K groups of the
@@ -362,7 +487,7 @@ static void fill_decode_args(fec_cuda_ctx_t *ctx, int k, FecDecodeArgs *a, const
  * one of two compute streams, D2H on the output stream) the host builds the descriptors of sub-batch i+1 and
  * unpacks the results of sub-batch i-1. The call returns when every sub-batch is done. */
 typedef struct {
-  uint32_t seg[9]; sbchunk_t *chunk; uint32_t local; int valid, pinned; uint32_t ndec; size_t data_off, e_off; int kidx[2];
+  uint32_t seg[9]; sbref_t sb; int valid, pinned; uint32_t ndec; size_t data_off, e_off; int kidx[2];
   /* front end (symbols in): offsets into the pipe's symbol / list / control-information staging */
   int fe_valid, sym_pinned; size_t sym_off, csi_off, lst_off, uci_off; uint32_t nack_u, nri_u, nuci, last_ri_pos;
 } tbplan_t;
@@ -448,7 +573,18 @@ static int fe_check(const fec_cuda_tb_t *t, const fec_cuda_sym_t *sy)
   for (uint32_t i = 0; i < sy->nof_ack_pos; i++) if (sy->ack_pos[i] >= nb) return 0;
   for (uint32_t i = 0; i < sy->nof_ri_pos; i++) if (sy->ri_pos[i] >= nb) return 0;
   if (sy->nof_cqi_bits > nb) return 0;
-  return t->tbs == 0 || (uint64_t)t->nof_e_bits + sy->nof_cqi_bits <= nb;
+  if (t->tbs == 0) return 1;
+  /* the de-interleaved stream is shorter than the q stream by the RI positions taken out of it (sch.c:860-881): decode_tb
+   * must not be asked to read behind its end (the pipelined path does not zero the LLR scratch) */
+  uint32_t nri_u = 0;
+  if (sy->nof_ri_pos) {
+    uint32_t *tmp = (uint32_t *)malloc(sizeof(uint32_t) * sy->nof_ri_pos);
+    if (!tmp) return 0;
+    memcpy(tmp, sy->ri_pos, sizeof(uint32_t) * sy->nof_ri_pos);
+    nri_u = sort_unique(tmp, sy->nof_ri_pos);
+    free(tmp);
+  }
+  return (uint64_t)t->nof_e_bits + sy->nof_cqi_bits + nri_u <= nb;
 }
 
 /* UL position lists of one transport block: 2*(nack+nri) words at lst (host) / dl (its device mirror):
@@ -500,8 +636,7 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
     const int decode = !(t->tbs == 0 || p->seg[1] == 0);
     if (decode) {
       if (p->seg[0] || p->seg[1] > FEC_CUDA_MAX_CB) continue;            /* filler bits / too many CBs */
-      p->chunk = sb_find(ctx, t->softbuffer, &p->local);
-      if (!p->chunk) continue;
+      if (!sb_lookup(ctx, t->softbuffer, &p->sb)) continue;
     }
     if (sy) {
       /* the front end runs for every transport block whose symbols are usable, also for control-only PUSCH (tbs == 0) */
@@ -517,7 +652,7 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
       p->e_off = e_total; e_total += ((size_t)sy->nof_re * sy->mod_bits + 7) & ~(size_t)7;
     }
     if (!decode) { t->ret = 0; continue; }
-    uint8_t *crc = p->chunk->cb_crc + (size_t)p->local * FEC_CUDA_MAX_CB;
+    uint8_t *crc = p->sb.crc;
     if (t->new_data) memset(crc, 0, FEC_CUDA_MAX_CB);
     p->kidx[0] = (int)p->seg[4]; p->kidx[1] = (int)p->seg[5];
     p->valid = 1; p->ndec = 0;
@@ -588,9 +723,9 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
     tbplan_t *p = &plan[i];
     if (!p->valid) continue;
     const uint32_t C = p->seg[1], C1 = p->seg[6];
-    uint8_t *crc = p->chunk->cb_crc + (size_t)p->local * FEC_CUDA_MAX_CB;
-    int16_t *soft0 = p->chunk->d_soft + (size_t)p->local * FEC_CUDA_MAX_CB * FEC_CUDA_SOFT_SLOT;
-    uint8_t *cache0 = p->chunk->d_cache + (size_t)p->local * FEC_CUDA_MAX_CB * CB_BYTES;
+    uint8_t *crc = p->sb.crc;
+    int16_t *soft0 = p->sb.soft0;
+    uint8_t *cache0 = p->sb.cache0;
     const char *e_dev = syms ? (const char *)(pp->d_llr + p->e_off + syms[i].nof_cqi_bits)        /* g_bits + Q'_cqi*Qm, sch.c:963-973 */
                              : dev_io ? (const char *)t->e_bits : (const char *)pp->st_e.d + p->e_off * esz;
     FecTbDesc *td = &tbd[itb];
@@ -693,6 +828,9 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
   cudaStream_t srm = (flags & FEC_CUDA_F_SERIAL) ? sc : ctx->s_rm;
   CU(cudaMemsetAsync(pp->d_queue, 0, sizeof(unsigned int) * FEC_NQUEUE * FEC_NOF_K, srm));
   if (ncb) CU(cudaMemsetAsync(pp->d_softmax, 0, (size_t)ncb * 4, srm));
+  /* status entries of code blocks that are handed over stay unwritten until the deferred pass: they must not carry the
+   * verdicts of the pipe's previous sub-batch into the first assembly (which refreshes the decoded-CB cache) */
+  if (ncb) CU(cudaMemsetAsync(pp->st_status.d, 0, sizeof(FecCbStatus) * ncb, srm));
   CU(cudaStreamWaitEvent(srm, pp->ev_in, 0));
   CU(cudaEventRecord(pp->ev_fe, srm));
   if (nfe) {
@@ -756,6 +894,7 @@ static int pipe_finish(fec_cuda_ctx_t *ctx, fec_pipe_t *pp)
        * complete, so its work-queue counter and its list start again from zero */
       cudaStream_t sc = ctx->s_comp[0];
       ctx->path_cnt[1] += nexact;
+      CU(cudaEventRecord(pp->ev[0], sc));                  /* the events of the first pass have been read above */
       for (int g = 0; g < pp->ngrp; g++) {
         const int k = pp->grp[g].k;
         CU(cudaMemsetAsync(pp->d_queue + 2 * k + 1, 0, sizeof(unsigned int), sc));
@@ -766,12 +905,17 @@ static int pipe_finish(fec_cuda_ctx_t *ctx, fec_pipe_t *pp)
         CU(fec_launch_decode(a, ctx->sm_count, sc, FEC_ST_B | FEC_ST_C));
         ctx->launches += 2;
       }
+      CU(cudaEventRecord(pp->ev[1], sc));
       if (pp->ntb) { CU(fec_launch_tb_assemble((const FecTbDesc *)pp->st_tbd.d, (const FecCbStatus *)pp->st_status.d, ctx->d_r24a, pp->ntb, sc)); ctx->launches++; }
+      CU(cudaEventRecord(pp->ev[2], sc));
       CU(cudaMemcpyAsync(pp->st_status.h, pp->st_status.d, sizeof(FecCbStatus) * pp->ncb, cudaMemcpyDeviceToHost, sc));
       if (pp->ntb) CU(cudaMemcpyAsync(pp->st_ret.h, pp->st_ret.d, sizeof(int32_t) * pp->ntb, cudaMemcpyDeviceToHost, sc));
       CU(cudaMemcpyAsync(pp->h_queue, pp->d_queue, sizeof(unsigned int) * FEC_NQUEUE * FEC_NOF_K, cudaMemcpyDeviceToHost, sc));
       if (!pp->dev_io && pp->data_total) CU(cudaMemcpyAsync(pp->st_data.h, pp->st_data.d, pp->data_total, cudaMemcpyDeviceToHost, sc));
       CU(cudaStreamSynchronize(sc));
+      /* the deferred certificate / exact kernels and the second assembly belong to the phases of this call too */
+      { float ms = 0; if (cudaEventElapsedTime(&ms, pp->ev[0], pp->ev[1]) == cudaSuccess) ctx->phase_ms[1] += ms;
+        if (cudaEventElapsedTime(&ms, pp->ev[1], pp->ev[2]) == cudaSuccess) ctx->phase_ms[2] += ms; }
     }
     /* launch policy of the next sub-batches */
     if (ntrk) ctx->eager_ttl = 16; else if (ctx->eager_ttl > 0) ctx->eager_ttl--;
@@ -799,7 +943,7 @@ static int pipe_finish(fec_cuda_ctx_t *ctx, fec_pipe_t *pp)
     tbplan_t *p = &pp->plan[i];
     if (!p->valid) continue;
     const FecTbDesc *td = &tbd[itb];
-    uint8_t *crc = p->chunk->cb_crc + (size_t)p->local * FEC_CUDA_MAX_CB;
+    uint8_t *crc = p->sb.crc;
     uint32_t sum = 0;
     for (uint32_t cb = 0; cb < p->seg[1]; cb++) {
       if (td->st_idx[cb] >= 0) {
@@ -838,6 +982,11 @@ static int pipes_create(fec_cuda_ctx_t *ctx)
   ctx->trace = sb ? atoi(sb) : 0;
   CU(cudaEventCreate(&ctx->ev_call));
   return 0;
+}
+
+static void pipes_drain(fec_cuda_ctx_t *ctx)
+{
+  for (int i = 0; i < FEC_NPIPE && ctx->pipes; i++) if (ctx->pipes[i].busy) pipe_finish(ctx, &ctx->pipes[i]);
 }
 
 static void pipes_destroy(fec_cuda_ctx_t *ctx)
@@ -1128,9 +1277,12 @@ extern "C" int fec_cuda_rm_rx(fec_cuda_ctx_t *ctx, const int16_t *in, uint32_t E
   /* 8-bit LLR mode (srslte_rm_turbo_rx_lut_8bit): in and soft are int8 arrays; the soft buffer is widened for the device
    * layout and narrowed on the way back (the int8 kernel keeps sign-extended int8 values in int16 slots) */
   const size_t esz = ctx->llr8 ? 1 : 2;
+  /* only the extent of the caller's array that the layout uses is read and written back: the reference touches nothing
+   * else (rm_turbo.c:250-264,411-420), and its own tests pass arrays of exactly 3K+12 entries (rm_turbo_test.c:52,186) */
+  const size_t next = (sb_layout && kt->g.P) ? 3 * ((size_t)kt->g.K + 32) + 12 : 3 * (size_t)kt->g.K + 12;
   memcpy(ctx->st_e.h, in, (size_t)E * esz);
-  if (ctx->llr8) for (int i = 0; i < 18600; i++) ((int16_t *)ctx->st_data.h)[i] = ((const int8_t *)soft)[i];
-  else memcpy(ctx->st_data.h, soft, 18600 * 2);
+  if (ctx->llr8) for (size_t i = 0; i < next; i++) ((int16_t *)ctx->st_data.h)[i] = ((const int8_t *)soft)[i];
+  else memcpy(ctx->st_data.h, soft, next * 2);
   FecRmDesc *r = (FecRmDesc *)ctx->st_rmd.h;
   r->e = (const int16_t *)ctx->st_e.d; r->soft = ctx->d_tmpsoft; r->rank = kt->d_rank; r->E = E; r->N = 3 * kt->g.K + 12;
   r->off = kt->off[rv]; r->n_out = 3 * kt->g.SS + 16; r->new_data = 0; r->slot = 0;
@@ -1138,17 +1290,17 @@ extern "C" int fec_cuda_rm_rx(fec_cuda_ctx_t *ctx, const int16_t *in, uint32_t E
   /* the caller's soft buffer lives in host memory in the reference layout: bring it to the device layout, combine
    * there (wrapping int16 adds, rm_turbo.c:411-420), and hand the same layout back */
   CUF(cudaMemcpyAsync(ctx->st_e.d, ctx->st_e.h, (size_t)E * esz, cudaMemcpyHostToDevice, st));
-  CUF(cudaMemcpyAsync(ctx->st_data.d, ctx->st_data.h, 18600 * 2, cudaMemcpyHostToDevice, st));
+  CUF(cudaMemcpyAsync(ctx->st_data.d, ctx->st_data.h, next * 2, cudaMemcpyHostToDevice, st));
   CUF(cudaMemcpyAsync(ctx->st_rmd.d, r, sizeof(FecRmDesc), cudaMemcpyHostToDevice, st));
   CUF(cudaMemsetAsync(ctx->d_softmax, 0, 8, st));
   CUF(fec_launch_ref_to_soft((const int16_t *)ctx->st_data.d, ctx->d_tmpsoft, kt->g, sb_layout, st));
   CUF(fec_launch_rm((const FecRmDesc *)ctx->st_rmd.d, ctx->d_softmax, 1, r->n_out, st, ctx->llr8));
   CUF(fec_launch_soft_to_ref(ctx->d_tmpsoft, (int16_t *)ctx->st_data.d, kt->g, sb_layout, 1, st));
   ctx->launches += 3;
-  CUF(cudaMemcpyAsync(ctx->st_data.h, ctx->st_data.d, 18600 * 2, cudaMemcpyDeviceToHost, st));
+  CUF(cudaMemcpyAsync(ctx->st_data.h, ctx->st_data.d, next * 2, cudaMemcpyDeviceToHost, st));
   CUF(cudaStreamSynchronize(st));
-  if (ctx->llr8) for (int i = 0; i < 18600; i++) ((int8_t *)soft)[i] = (int8_t)((const int16_t *)ctx->st_data.h)[i];
-  else memcpy(soft, ctx->st_data.h, 18600 * 2);
+  if (ctx->llr8) for (size_t i = 0; i < next; i++) ((int8_t *)soft)[i] = (int8_t)((const int16_t *)ctx->st_data.h)[i];
+  else memcpy(soft, ctx->st_data.h, next * 2);
   return 0;
 }
 

@@ -30,11 +30,11 @@ typedef enum { SRSLTE_TDEC_AUTO = 0, SRSLTE_TDEC_GENERIC, SRSLTE_TDEC_SSE, SRSLT
 typedef struct {
   uint32_t max_long_cb;          /* @0, as in the reference */
   uint32_t fec_magic;            /* private from here on */
-  void    *fec_ctx;              /* fec_cuda_ctx_t of this decoder */
+  void    *fec_reserved;         /* (decode contexts are per calling thread, not per object) */
   int16_t *fec_input;            /* private copy of the code block's LLRs, natural layout (taken at n_iter == 0) */
   uint32_t fec_K;                /* current code block size */
   uint32_t fec_force_not_sb;
-  uint32_t fec_manual_type;
+  uint32_t fec_manual_type;      /* 0: AUTO, else forced sub-block class + 1 (srslte_tdec_init_manual) */
   uint8_t  fec_private[18256 - 36];
   uint32_t n_iter;               /* @18256, as in the reference */
   uint32_t fec_pad;
@@ -86,6 +86,15 @@ int  srslte_sch_decode_tb_cuda(srslte_softbuffer_rx_t *softbuffer, uint32_t tbs,
 /* decode_tb with q->llr_is_8bit (sch.c:344-348,362-364): e_bits are int8 */
 int  srslte_sch_decode_tb_cuda_8bit(srslte_softbuffer_rx_t *softbuffer, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits,
                                     int8_t *e_bits, uint8_t *data, uint32_t max_iterations, uint32_t *nof_iterations);
+
+/* ---- srslte_dlsch_decode / srslte_dlsch_decode2 (sch.h:108-121, sch.c:488-517): the reference's DL-SCH entry points on the
+ * reference's own caller-allocated structs — q is a srslte_sch_t *, cfg a srslte_pdsch_cfg_t * (declared void * here because
+ * this header does not carry those types; same ABI). Only the fields decode_tb reads are touched, through the offsets of
+ * srslte_fec_abi.h. A build that takes these from the library compiles them out of sch.c (oracle/patch_sch.py shows how);
+ * srslte_ulsch_decode / srslte_ulsch_uci_decode stay in sch.c (they de-interleave and decode UCI first, sch.c:883-985) and
+ * reach the library through decode_tb -> srslte_sch_decode_tb_cuda. */
+int  srslte_dlsch_decode(void *q, void *cfg, srslte_softbuffer_rx_t *softbuffer, int16_t *e_bits, uint8_t *data);
+int  srslte_dlsch_decode2(void *q, void *cfg, srslte_softbuffer_rx_t *softbuffer, int16_t *e_bits, uint8_t *data, int tb_idx);
 
 /* ---- encode_tb_off (sch.c:188-296): the body a patched sch.c calls on the transmit side. data = NULL (the reference
  * re-reads its tx soft buffer for a retransmission) is not supported: pass the transport block again. w_offset = 0. */

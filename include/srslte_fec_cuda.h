@@ -101,6 +101,13 @@ int  fec_cuda_last_path_counts(fec_cuda_ctx_t *ctx, uint64_t out2[2]);
  * (fec_cuda_decode_syms) is not available in this mode. Soft buffers must be reset when the mode changes. */
 int  fec_cuda_set_llr_8bit(fec_cuda_ctx_t *ctx, int on);
 
+/* srslte_tdec_init_manual (turbodecoder.c:153-190): force ONE 16-bit arithmetic class on every code block size instead of
+ * the AUTO mapping of turbodecoder.c:364-376 — P = 0 the non-windowed decoder (SRSLTE_TDEC_SSE), 8 (SRSLTE_TDEC_SSE_WINDOW),
+ * 16 (SRSLTE_TDEC_AVX_WINDOW); -1 returns to AUTO. Applies to fec_cuda_decode_cbs (the srslte_tdec_* level, what
+ * turbodecoder_test -d N exercises); forced classes run in the exact kernels. A windowed class needs K mod P == 0 and
+ * K / P > 40 (its warm-up length; the reference itself corrupts its heap at K / P = 40), else the code block is refused with FEC_CUDA_EINVAL. */
+int  fec_cuda_set_decoder_class(fec_cuda_ctx_t *ctx, int P);
+
 /* Pinned (page-locked) host memory for e_bits / data buffers: replaces srslte_vec_malloc
  * (lib/src/phy/utils/vector.c:125-132) for the buffers handed to the decode calls. Buffers obtained here (or
  * registered with cudaHostRegister) are DMA'd directly; any other host pointer is staged through a copy. */
@@ -111,6 +118,11 @@ void  fec_cuda_host_free(void *p);
 /* allocates n TB soft buffers (13 code-block slots each) in HBM; ids are first_id .. first_id+n-1 */
 int  fec_cuda_softbuffer_alloc(fec_cuda_ctx_t *ctx, uint32_t n, uint32_t *first_id);
 int  fec_cuda_softbuffer_reset(fec_cuda_ctx_t *ctx, uint32_t id);           /* srslte_softbuffer_rx_reset */
+/* srslte_softbuffer_rx_free (softbuffer.c:102-126). Soft buffers belong to the DEVICE, not to the context: any context of
+ * the device can decode into any id (the reference allocates them in the MAC thread and decodes from PHY worker threads,
+ * one srslte_sch_t each). A single buffer (n == 1 allocation) returns to a free list and lives as long as the process;
+ * buffers of a bulk allocation (n > 1) are released when the allocating context is destroyed — freeing one is a no-op. */
+int  fec_cuda_softbuffer_free(fec_cuda_ctx_t *ctx, uint32_t id);
 /* debugging / parity: copy one CB slot out in the REFERENCE soft-buffer layout (18600 int16, rm_turbo.c:250-264) */
 int  fec_cuda_softbuffer_read_ref_layout(fec_cuda_ctx_t *ctx, uint32_t id, uint32_t cb, uint32_t K, int16_t *out18600);
 
@@ -195,9 +207,11 @@ int  fec_cuda_decode_cbs(fec_cuda_ctx_t *ctx, fec_cuda_cb_t *cbs, uint32_t n, ui
 
 /* standalone rate de-matching into a HOST soft buffer in the reference layout — drop-in body of
  * srslte_rm_turbo_rx_lut_ (rm_turbo.c:378-430); computed on the device. In 8-bit LLR mode (fec_cuda_set_llr_8bit) `in` and
- * `soft18600` point to int8 arrays (E and 18600 entries): the body of srslte_rm_turbo_rx_lut_8bit (rm_turbo.c:432-469). */
+ * `soft` point to int8 arrays: the body of srslte_rm_turbo_rx_lut_8bit (rm_turbo.c:432-469). Of `soft` only the extent
+ * the layout uses is read and written: 3*(K+32)+12 entries with sb_layout and K > 400, else 3K+12 (what the reference's own
+ * rm_turbo_test.c:52,186 allocates). */
 int  fec_cuda_rm_rx(fec_cuda_ctx_t *ctx, const int16_t *in, uint32_t E, uint32_t cb_idx, uint32_t rv,
-                    int sb_layout, int16_t *soft18600);
+                    int sb_layout, int16_t *soft);
 
 /* The same operation for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
  * harnesses that forbid it). NO COUNTERPART IN THE REFERENCE. Takes a device

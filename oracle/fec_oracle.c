@@ -712,6 +712,12 @@ typedef struct {
   struct timespec t0, t1;
 } orc_mt_t;
 
+/* optional per-TB results of the last pass, 3 words per TB: return value, sum of half-iterations / C (sch.c:420), FNV-1a of
+ * the tbs/8 + 3 output bytes (NULL: off) */
+static uint32_t *g_mt_results;
+void orc_bench_set_results(uint32_t *buf) { g_mt_results = buf; }
+static uint32_t orc_fnv1a(const uint8_t *p, size_t n) { uint32_t h = 2166136261u; for (size_t i = 0; i < n; i++) { h ^= p[i]; h *= 16777619u; } return h; }
+
 static void *orc_mt_worker(void *a_)
 {
   orc_mt_t *a = a_;
@@ -725,7 +731,12 @@ static void *orc_mt_worker(void *a_)
       orc_tb_reset(tb, a->tbs);
       int ret = orc_tb_decode(tb, a->tbs, a->Qm, a->rv, a->nof_e_bits, a->e + (size_t)i * a->nof_e_bits, a->max_its, data, crc, its);
       a->n_tb++; if (ret == 0) a->n_ok++;
-      for (int c = 0; c < ORC_MAX_CB; c++) a->its += its[c];
+      uint32_t sum = 0, nz = 0;
+      for (int c = 0; c < ORC_MAX_CB; c++) { a->its += its[c]; sum += its[c]; }
+      if (g_mt_results) {
+        uint32_t seg[9]; orc_cbsegm(a->tbs, seg); nz = seg[1] ? seg[1] : 1;
+        g_mt_results[3 * i] = (uint32_t)ret; g_mt_results[3 * i + 1] = sum / nz; g_mt_results[3 * i + 2] = orc_fnv1a(data, a->tbs / 8 + 3);
+      }
     }
   clock_gettime(CLOCK_MONOTONIC, &a->t1);
   free(data); orc_tb_free(tb);

@@ -13,6 +13,7 @@ import zlib
 import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 from _libs import ALL_K, P, aligned, int_awgn_llr, int_gauss, ref  # noqa: E402
 
@@ -281,10 +282,37 @@ def gen_llr8():
     np.savez_compressed(os.path.join(OUT, "llr8.npz"), **out)
 
 
+def gen_bler():
+    """row g1 (north_star: "against turbodecoder_gen ... matching BER/BLER within stated tolerance on the same AWGN vectors"):
+    block / bit error counts of the reference's generic full-length int16 decoder (srslte_tdec_init_manual(...,
+    SRSLTE_TDEC_GENERIC), turbodecoder.c:173, turbodecoder_gen.c:59-203) and of its AUTO SSE/AVX decoders after 8
+    half-iterations, 2000 seeded code blocks per point, sigma across the waterfall of each K"""
+    import _golden as G
+    GENERIC = 1                                   # srslte_tdec_impl_type_t, turbodecoder_impl.h:33-42
+    rows = []
+    grid = {504: (1000, 1050, 1100, 1150, 1200), 2048: (1050, 1075, 1100, 1125, 1150), 5824: (1075, 1100, 1125), 6144: (1075, 1100, 1125)}
+    for K, sms in grid.items():
+        for sm in sms:
+            n, seed, nof = 2000, 900000 + K * 10 + sm, 8
+            bits, llr = G.bler_vectors(K, sm, n, seed)
+            cnt = []
+            for mode in (GENERIC, 0):
+                ob = np.zeros((n, K // 8), np.uint8)
+                assert R.ref_tdec_batch(K, P(llr), n, nof, mode, P(ob)) == 0
+                err = np.unpackbits(ob, axis=1) != bits
+                cnt += [int(err.any(axis=1).sum()), int(err.sum())]
+            rows.append((K, sm, n, seed, nof, crc32(llr)) + tuple(cnt))
+            print("bler", rows[-1], flush=True)
+    np.savez_compressed(os.path.join(OUT, "bler_gen.npz"), cases=np.array(rows, np.int64))
+
+
 if __name__ == "__main__":
     if "llr8" in sys.argv[1:]:        # only the 8-bit fixtures (the others stay byte-identical)
         gen_llr8()
+    elif "bler" in sys.argv[1:]:      # only the BLER statistics against the generic decoder
+        gen_bler()
     else:
+        gen_bler()
         gen_frontend()
         gen_tdec()
         gen_tables()

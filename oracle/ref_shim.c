@@ -139,6 +139,29 @@ int ref_tdec_halfits(int K, const int16_t *in_nat, int nof, int mode, uint8_t *o
   return r;
 }
 
+/* n code blocks of one size through ONE decoder object (mode as above: 0 AUTO, SRSLTE_TDEC_GENERIC = 1 the full-length
+ * int16 max-log-MAP of turbodecoder_gen.c:59-203, ...), nof half-iterations each via srslte_tdec_run_all; natural-layout
+ * inputs in_all[n][3K+12], decisions out_bytes[n][K/8]. For BER/BLER statistics (tests/golden/bler_gen.npz). */
+int ref_tdec_batch(int K, const int16_t *in_all, int n, int nof, int mode, uint8_t *out_bytes)
+{
+  srslte_tdec_t local, *h = &g_tdec;
+  if (mode != 0) {
+    if (srslte_tdec_init_manual(&local, 6144, (srslte_tdec_impl_type_t)mode)) return -1;
+    h = &local;
+  }
+  srslte_tdec_force_not_sb(h);
+  int16_t *in = srslte_vec_malloc(sizeof(int16_t) * (3 * K + 12 + 64));
+  int r = 0;
+  for (int i = 0; i < n && !r; i++) {
+    memcpy(in, in_all + (size_t)i * (3 * K + 12), sizeof(int16_t) * (3 * K + 12));
+    r = srslte_tdec_run_all(h, in, out_bytes + (size_t)i * (K / 8), (uint32_t)nof, (uint32_t)K);
+  }
+  free(in);
+  h->force_not_sb = false;
+  if (mode != 0) srslte_tdec_free(&local);
+  return r;
+}
+
 /* ---- 8-bit LLR path ---- */
 int ref_subblocks8(int K) { return (int)srslte_tdec_autoimp_get_subblocks_8bit((uint32_t)K); }
 
@@ -354,6 +377,12 @@ typedef struct {
   struct timespec t0, t1;
 } mt_arg_t;
 
+/* optional per-TB results of the last pass, 3 words per TB: decode_tb return value, srslte_sch_last_noi, FNV-1a of the
+ * tbs/8 + 3 output bytes — so that a bench can compare what it decoded with what the reference decodes (NULL: off) */
+static uint32_t *g_mt_results;
+void ref_bench_set_results(uint32_t *buf) { g_mt_results = buf; }
+static uint32_t fnv1a(const uint8_t *p, size_t n) { uint32_t h = 2166136261u; for (size_t i = 0; i < n; i++) { h ^= p[i]; h *= 16777619u; } return h; }
+
 static void *mt_worker(void *a_)
 {
   mt_arg_t *a = a_;
@@ -371,6 +400,7 @@ static void *mt_worker(void *a_)
       int ret = ref_tb_decode(a->tb, a->tbs, a->Qm, a->rv, a->nof_e_bits, e, a->max_its, data, crc, &avg);
       a->n_tb++; a->sum_avg_its += avg;
       if (ret == 0) a->n_ok++;
+      if (g_mt_results) { g_mt_results[3 * i] = (uint32_t)ret; g_mt_results[3 * i + 1] = avg; g_mt_results[3 * i + 2] = fnv1a(data, a->tbs / 8 + 3); }
     }
   }
   clock_gettime(CLOCK_MONOTONIC, &a->t1);

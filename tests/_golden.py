@@ -127,3 +127,32 @@ def tb8_cases():
                             crc=z[f"tb_crc_{ci}_{tx}"], ret=int(z[f"tb_ret_{ci}_{tx}"][0]), avg_its=int(z[f"tb_ret_{ci}_{tx}"][1]),
                             softcrc=z[f"tb_softcrc_{ci}_{tx}"]))
         yield dict(tbs=tbs, Qm=Qm, nbits=nbits, max_its=max_its, tx=txs, payload=z[f"tb_payload_{ci}"], id=f"tbs{tbs}-s{sigma}")
+
+
+def bler_vectors(K, sigma_milli, n, seed):
+    """n random code blocks of size K, turbo-encoded at rate 1/3 (natural layout [s p p'] x K + 12 tail) and sent over an
+    integer AWGN channel: LLR = 100*(2b-1) + 100*sigma*g, g = sum of twelve 16-bit uniforms (Irwin-Hall, std 65536) from
+    numpy's PCG64 integer stream. Returns (bits[n,K], llr[n,3K+12] int16). Same generator in oracle/gen_golden.py (fixture
+    bler_gen.npz, which records crc32(llr) so that a drifting generator is noticed) and in the GPU test."""
+    import importlib
+    synth = importlib.import_module("empower-srslte_b200.synth")
+    rng = np.random.Generator(np.random.PCG64(seed))
+    bits = rng.integers(0, 2, size=(n, K), dtype=np.uint8)
+    coded = synth.turbo_encode(bits)
+    g = np.zeros(coded.shape, np.int64)
+    for _ in range(12):
+        g += rng.integers(0, 65536, size=coded.shape, dtype=np.uint16)
+    g -= 6 * 65535
+    noise = (100 * sigma_milli * g) // (1000 * 65536)
+    llr = np.clip(100 * (2 * coded.astype(np.int64) - 1) + noise, -32768, 32767).astype(np.int16)
+    return bits, llr
+
+
+def bler_cases():
+    """rows of tests/golden/bler_gen.npz: dict(K, sigma_milli, n, seed, nof, llrcrc, gen=(block errors, bit errors) of the
+    reference's full-length int16 max-log-MAP (SRSLTE_TDEC_GENERIC, turbodecoder_gen.c:59-203), auto=(...) of its AUTO
+    SSE/AVX decoders, both after nof half-iterations on these vectors)"""
+    z = np.load(os.path.join(GOLD, "bler_gen.npz"))
+    for K, sm, n, seed, nof, crc, gb, gbit, ab, abit in z["cases"]:
+        yield dict(K=int(K), sigma_milli=int(sm), n=int(n), seed=int(seed), nof=int(nof), llrcrc=int(crc),
+                   gen=(int(gb), int(gbit)), auto=(int(ab), int(abit)), id=f"K{int(K)}-s{int(sm)}")

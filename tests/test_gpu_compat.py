@@ -227,3 +227,94 @@ def test_rm_rx_lut_8bit_accumulates_like_reference(lib, orc):
             P8 = orc.orc_subblocks8(K)
             assert (G.soft8_view(got, K, P8) == G.soft8_view(want, K, P8)).all(), (K, rv, E)
     assert lib.srslte_rm_turbo_rx_lut_8bit(P(e), P(got), 10, 0, 4) == -2
+
+
+def _tb_case(name_tbs):
+    return [c for c in G.tb_cases() if c["tbs"] == name_tbs][0]
+
+
+def test_reset_then_refused_call_then_valid_call(lib, orc):
+    """a decode_tb the library refuses (-2: rv out of range) writes nothing to the device buffer, so it must not spend the
+    deferred reset of srslte_softbuffer_rx_reset*: the next valid decode starts from zero like the reference's, whose
+    reset zeroed the memory (softbuffer.c:138-151)"""
+    case = _tb_case(6200)
+    tbs, tx = case["tbs"], case["tx"][0]
+    llr = np.ascontiguousarray(tx["llr"])
+    q = C.create_string_buffer(40)
+    assert lib.srslte_softbuffer_rx_init(q, 100) == 0
+    data, noi = np.zeros(tbs // 8 + 3 + 768, np.uint8), C.c_uint32(0)
+    # fill the device buffer with something that would break a later combine
+    junk = (int_gauss(llr.size, 99) % 1601 - 800).astype(np.int16)
+    lib.srslte_softbuffer_rx_reset_tbs(q, tbs)
+    lib.srslte_sch_decode_tb_cuda(q, tbs, case["Qm"], 0, case["nbits"], P(junk), P(data), case["max_its"], C.byref(noi))
+    lib.srslte_softbuffer_rx_reset_tbs(q, tbs)
+    assert lib.srslte_sch_decode_tb_cuda(q, tbs, case["Qm"], 7, case["nbits"], P(llr), P(data), case["max_its"], C.byref(noi)) == -2
+    ret = lib.srslte_sch_decode_tb_cuda(q, tbs, case["Qm"], tx["rv"], case["nbits"], P(llr), P(data), case["max_its"], C.byref(noi))
+    assert ret == tx["ret"]
+    if ret == 0:
+        assert (data[: tbs // 8 + 3] == tx["data"][: tbs // 8 + 3]).all()
+    lib.srslte_softbuffer_rx_free(q)
+
+
+def test_softbuffer_free_recycles_device_buffers(lib):
+    """srsENB creates and frees soft buffers per UE on attach / detach: freed buffers return to the pool (and come back
+    zeroed), device memory does not grow"""
+    import torch
+    case = _tb_case(6200)
+    tbs, tx = case["tbs"], case["tx"][0]
+    llr = np.ascontiguousarray(tx["llr"])
+    qs = [C.create_string_buffer(40) for _ in range(3)]
+    for q in qs:                                     # make sure the pooled chunk exists before measuring
+        assert lib.srslte_softbuffer_rx_init(q, 100) == 0
+    for q in qs:
+        lib.srslte_softbuffer_rx_free(q)
+    torch.cuda.synchronize()
+    free0 = torch.cuda.mem_get_info()[0]
+    for it in range(200):
+        q = C.create_string_buffer(40)
+        assert lib.srslte_softbuffer_rx_init(q, 100) == 0
+        if it % 50 == 0:
+            data, noi = np.zeros(tbs // 8 + 3 + 768, np.uint8), C.c_uint32(0)
+            lib.srslte_softbuffer_rx_reset_tbs(q, tbs)
+            ret = lib.srslte_sch_decode_tb_cuda(q, tbs, case["Qm"], tx["rv"], case["nbits"], P(llr), P(data), case["max_its"], C.byref(noi))
+            assert ret == tx["ret"]
+        lib.srslte_softbuffer_rx_free(q)
+    torch.cuda.synchronize()
+    assert free0 - torch.cuda.mem_get_info()[0] < (8 << 20), "device memory grew across 200 init/free cycles"
+
+
+def test_two_worker_threads_decode_concurrently(lib):
+    """SURVEY 8b "Threading": one object per worker thread, workers run at once (pdsch.c:837-864), and a 16-bit and an 8-bit
+    object may overlap. Each thread gets its own decode context; results must equal the golden ones of the single-threaded
+    runs, in both modes, while the other thread is busy"""
+    import threading
+    c16 = _tb_case(6200)
+    c8 = [c for c in G.tb8_cases()][0]
+    errs = []
+
+    def worker(case, fn, reps):
+        try:
+            tbs = case["tbs"]
+            q = C.create_string_buffer(40)
+            assert lib.srslte_softbuffer_rx_init(q, 100) == 0
+            for _ in range(reps):
+                lib.srslte_softbuffer_rx_reset_tbs(q, tbs)
+                for tx in case["tx"]:
+                    data, noi = np.zeros(tbs // 8 + 3 + 768, np.uint8), C.c_uint32(0)
+                    llr = np.ascontiguousarray(tx["llr"])
+                    ret = fn(q, tbs, case["Qm"], tx["rv"], case["nbits"], P(llr), P(data), case["max_its"], C.byref(noi))
+                    assert ret == tx["ret"], (ret, tx["ret"])
+                    if ret == 0:
+                        assert (data[: tbs // 8 + 3] == tx["data"][: tbs // 8 + 3]).all()
+            lib.srslte_softbuffer_rx_free(q)
+        except Exception as e:                       # noqa: BLE001
+            errs.append(repr(e))
+
+    th = [threading.Thread(target=worker, args=(c16, lib.srslte_sch_decode_tb_cuda, 40)),
+          threading.Thread(target=worker, args=(c8, lib.srslte_sch_decode_tb_cuda_8bit, 40)),
+          threading.Thread(target=worker, args=(c16, lib.srslte_sch_decode_tb_cuda, 40))]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    assert not errs, errs

@@ -124,15 +124,18 @@ def test_config4_all_k_with_crc_early_stop(fec, orc):
     assert min(its) <= 2 and max(its) >= 6, "the sweep should cover early and late stops"
 
 
-def test_config2_full_shape_properties(fec):
-    """MCS28 / 100 PRB (TBS 75376, 90000 LLRs, 13 x K=5824) on 148 transport blocks: every CRC-passing block returns
-    the transmitted payload, the call is deterministic, and host and device buffers give identical results"""
+def test_config2_full_shape_vs_oracle(fec, orc):
+    """MCS28 / 100 PRB (TBS 75376, 90000 LLRs, 13 x K=5824) on 148 transport blocks, every one of them against the oracle's
+    decode_tb (return value, per-CB CRC flags, per-CB half-iteration counts, all TBS/8+3 bytes); and: every CRC-passing
+    block returns the transmitted payload, the call is deterministic, host and device buffers give identical results"""
     import torch
     tbs, Qm, nbits, n = 75376, 6, 90000, 148
     rng = np.random.default_rng(2)
     payload = rng.integers(0, 256, (n, tbs // 8), dtype=np.uint8)
     llr = synth.awgn_llr(synth.encode_tbs(payload, tbs, Qm, 0, nbits), 0.47, rng)
     sb0 = fec.softbuffer_alloc(n)
+
+    crcs = []
 
     def run(dev):
         d = (pkg.TbDesc * n)()
@@ -147,12 +150,22 @@ def test_config2_full_shape_properties(fec):
             d[i].data = do[i].data_ptr() if dev else do[i].ctypes.data
         fec.decode_tbs(d, pkg.F_DEVICE_IO if dev else 0)
         out = do.cpu().numpy() if dev else do
+        crcs.append([list(d[i].cb_crc) for i in range(n)])
         return [d[i].ret for i in range(n)], [list(d[i].cb_its) for i in range(n)], out
 
     r1, i1, o1 = run(False)
     r2, i2, o2 = run(False)
     r3, i3, o3 = run(True)
     assert r1 == r2 == r3 and i1 == i2 == i3
+    ot = C.c_void_p(orc.orc_tb_new())
+    bad = []
+    for i in range(n):
+        orc.orc_tb_reset(ot, tbs)
+        ret, dd, crc, its = _oracle_tb(orc, ot, tbs, Qm, 0, nbits, llr[i], 8)
+        if r1[i] != ret or i1[i] != list(its) or crcs[0][i] != list(crc) or not (o1[i, : tbs // 8 + 3] == dd[: tbs // 8 + 3]).all():
+            bad.append((i, r1[i], ret, i1[i], list(its)))
+    orc.orc_tb_free(ot)
+    assert not bad, bad[:5]
     ok = [i for i in range(n) if r1[i] == 0]
     assert 0.5 * n < len(ok), "operating point should decode most blocks"
     for i in ok:

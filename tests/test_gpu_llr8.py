@@ -113,6 +113,28 @@ def test_tb8_golden(fec8, orc, c):
         orc.orc_tb_free(to)
 
 
+def test_rm_rx8_all_k_vs_oracle(fec8, orc):
+    """the int8 rate de-matcher (srslte_rm_turbo_rx_lut_8bit, rm_turbo.c:432-469) for every one of the 188 sizes x 4 rv,
+    lengths below and above 3K+12, accumulating with int8 wrap-around into a non-empty buffer; checker: the oracle, which
+    tests/test_oracle_llr8.py pins to the compiled reference on the same grid"""
+    rng = np.random.default_rng(88)
+    bad = []
+    for K in ALL_K:
+        P8 = orc.orc_subblocks8(K)
+        for rv in range(4):
+            E = int(rng.choice([K + 7, 3 * K + 12, 3 * K + 12 + 333, 2 * (3 * K + 12) + 5]))
+            e = rng.integers(-128, 128, E).astype(np.int8)
+            s0 = np.zeros(18600, np.int8)
+            s0[: 3 * K + 108] = rng.integers(-128, 128, 3 * K + 108)
+            got, want = s0.copy(), np.zeros(2 * 18600, np.int8)
+            want[:18600] = s0
+            assert fec8.lib.fec_cuda_rm_rx(fec8.h, P(e), E, ALL_K.index(K), rv, 1, P(got)) == 0
+            assert orc.orc_rm_rx8(P(e), E, K, rv, 1, P(want)) == 0
+            if not (G.soft8_view(got, K, P8) == G.soft8_view(want, K, P8)).all():
+                bad.append((K, rv, E))
+    assert not bad, bad[:20]
+
+
 def test_tb8_round_trip_full_shape(fec8, orc):
     """BASELINE configs[1] shape, 296 transport blocks: encode on the GPU, int8 LLRs with noise, decode in 8-bit mode: every
     payload comes back at low noise; at high noise a retransmission combines into the int8 soft buffers and rescues blocks;

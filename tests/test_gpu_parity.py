@@ -172,16 +172,28 @@ def test_tdec_continues_in_certificate_kernel_vs_oracle(fec, orc):
     print("mid-decode hand-overs: %d over 6 runs of %d blocks; early-stop half-iterations %s" % (tot_trk, len(cases), exp_its))
 
 
-def test_rm_rx_golden_subset(fec):
+def test_rm_rx_golden_all_rows(fec):
+    """every row of the fixture the unmodified reference produced (oracle/gen_golden.py:71-81): 188 K x 4 rv x {natural,
+    sub-block layout} x 3 lengths E (below, at and above 3K+12). The per-K rank table is where a gather breaks (ND, R, the
+    wrap at k0), so all of them — the scope of rm_turbo_test.c:140-193. The buffer is exactly the extent the layout uses,
+    between canaries (the reference's own test allocates 3K+12 entries, rm_turbo_test.c:52,186)."""
     z = G.tables()
-    rows = [r for r in z["rm"] if int(r[0]) in (40, 104, 400, 408, 800, 816, 1024, 3136, 5824, 6144)]
-    for K, rv, sb, E, c in rows:
+    assert len(z["rm"]) == 188 * 4 * 2 * 3
+    bad = []
+    for K, rv, sb, E, c in z["rm"]:
         K, rv, sb, E = int(K), int(rv), int(sb), int(E)
         e = (int_gauss(E, K * 8 + rv) % 2001 - 1000).astype(np.int16)
         s = (int_gauss(18600, K) % 20001 - 10000).astype(np.int16)
-        # the reference scatter only touches LUT-addressed positions; so does the drop-in
-        assert fec.rm_rx(e, ALL_K.index(K), rv, s, bool(sb)) == 0
-        assert G.crc32(s) == int(c), (K, rv, sb, E)
+        ext = 3 * (K + 32) + 12 if sb and K > 400 else 3 * K + 12
+        buf = np.full(ext + 128, 0x5A5A, np.int16)
+        buf[64:64 + ext] = s[:ext]
+        rc = fec.lib.fec_cuda_rm_rx(fec.h, P(e), E, ALL_K.index(K), rv, sb, C.c_void_p(buf.ctypes.data + 128))
+        assert rc == 0
+        assert (buf[:64] == 0x5A5A).all() and (buf[64 + ext:] == 0x5A5A).all(), ("wrote outside the extent", K, rv, sb, E)
+        s[:ext] = buf[64:64 + ext]
+        if G.crc32(s) != int(c):
+            bad.append((K, rv, sb, E))
+    assert not bad, bad[:20]
 
 
 def test_rm_rx_invalid(fec):

@@ -131,3 +131,19 @@ def test_tb_encode_golden(orc):
             assert (np.unpackbits(got)[: c["nbits"]] == np.unpackbits(want)[: c["nbits"]]).all(), (c["id"], tx)
             n += 1
     assert n >= 4
+
+
+def test_oracle_bler_point_matches_reference_auto_decoder(orc):
+    """one point of tests/golden/bler_gen.npz (K = 504, the size where the windowed decoder departs most from the generic
+    one): the oracle's block / bit error counts on the seeded vectors equal those of the reference's AUTO decoder"""
+    case = [c for c in G.bler_cases() if c["K"] == 504 and c["sigma_milli"] == 1050][0]
+    K = case["K"]
+    bits, llr = G.bler_vectors(K, case["sigma_milli"], case["n"], case["seed"])
+    assert G.crc32(llr) == case["llrcrc"]
+    ob = np.zeros((case["nof"], K // 8), np.uint8)
+    blk = bit = 0
+    for i in range(case["n"]):
+        assert orc.orc_tdec_halfits(K, P(np.ascontiguousarray(llr[i])), case["nof"], P(ob), None) == 0
+        e = np.unpackbits(ob[-1]) != bits[i]
+        blk += int(e.any()); bit += int(e.sum())
+    assert (blk, bit) == case["auto"]
