@@ -171,6 +171,68 @@ __device__ __forceinline__ void pk_alpha_branches(const uint32_t *o, uint32_t x,
   n[4] = pk_add(o[0], xy); n[5] = pk_add(o[3], x); n[6] = pk_add(o[4], x); n[7] = pk_add(o[7], xy);
 }
 
+/* ---- mixed-form arithmetic of the a-priori-range kernel (PK_MIX) --------------------------------------------------
+ * The packed add / add-max instructions exist on the ALU pipe only and take two issue cycles per warp (64 lanes per clock
+ * and SM, profiles/r1_pipe_mix.txt); a plain 32-bit add issues at full rate or goes to the otherwise idle FMA pipe as IMAD.
+ * Two int16 lanes (v_hi, v_lo) therefore travel in one of three forms:
+ *   P form  two's complement halves, as in memory                       (branch metrics for the fused add-max, LLRs, extrinsics)
+ *   I form  the integer v_hi * 65536 + v_lo                              (branch metrics for plain 32-bit adds)
+ *   S form  I + 0x80008000: both halves offset-binary                    (state metrics alpha / beta)
+ * While every lane stays inside int16 — the range condition this kernel runs under anyway — S + I is a 32-bit add giving S,
+ * S (+) P a packed add giving S (VIADDMNMX.U16x2 fuses it with the unsigned per-lane max), S (+) S a packed add giving P
+ * (the two offsets cancel mod 2^16: the LLR sums alpha-branch + beta, reduced by the signed fused add-max as before), and
+ * S - S a 32-bit subtract giving I (normalisation). Same integers in every lane as the P-form code, so still bit-exact with
+ * the reference; per trellis step about 20 packed adds leave the ALU pipe. The certificate (TRK) variant keeps the P form:
+ * its extremes are tracked with signed packed min / max. */
+#ifndef PK_MIX
+#define PK_MIX 0         /* measured on B200 (tools/experiments/README.md): bit-exact, ALU-pipe cycles per step 150 -> 118, but 6 % SLOWER —
+                            with one warp per scheduler the loops are issue-bound and the form conversions add instructions */
+#endif
+#define PK_C 0x80008000u
+__device__ __forceinline__ uint32_t pk_to_i(uint32_t p) { return p - 2u * (p & 0x8000u); }
+__device__ __forceinline__ uint32_t pk_addmax_u(uint32_t a, uint32_t b, uint32_t c) { return __viaddmax_u16x2(a, b, c); }
+__device__ __forceinline__ uint32_t pk_max_u(uint32_t a, uint32_t b) { return __vmaxu2(a, b); }
+
+struct PkGam { uint32_t xP, yP, xyP, xI, yI; };
+__device__ __forceinline__ PkGam pk_gammas(uint32_t x, uint32_t y)
+{
+  PkGam g;
+  g.xP = x; g.yP = y; g.xyP = pk_add(x, y); g.xI = pk_to_i(x); g.yI = pk_to_i(y);
+  return g;
+}
+/* S-form state: subtract state 0 from all, state 0 := 0 */
+__device__ __forceinline__ void pk_norm_s(uint32_t *o)
+{
+  const uint32_t c = PK_C - o[0];
+#pragma unroll
+  for (int i = 1; i < 8; i++) o[i] += c;
+  o[0] = PK_C;
+}
+/* backward step on S-form states: 4 plain adds + 8 fused unsigned add-max */
+__device__ __forceinline__ void pk_beta_s(uint32_t *o, const PkGam &g)
+{
+  uint32_t n[8];
+  n[0] = pk_addmax_u(o[4], g.xyP, o[0]);
+  n[1] = pk_addmax_u(o[0], g.xyP, o[4]);
+  n[2] = pk_addmax_u(o[1], g.xP, o[5] + g.yI);
+  n[3] = pk_addmax_u(o[1], g.yP, o[5] + g.xI);
+  n[4] = pk_addmax_u(o[2], g.yP, o[6] + g.xI);
+  n[5] = pk_addmax_u(o[2], g.xP, o[6] + g.yI);
+  n[6] = pk_addmax_u(o[3], g.xyP, o[7]);
+  n[7] = pk_addmax_u(o[7], g.xyP, o[3]);
+#pragma unroll
+  for (int i = 0; i < 8; i++) o[i] = n[i];
+}
+/* forward branches on S-form states with I-form branch metrics: 12 plain adds */
+__device__ __forceinline__ void pk_alpha_branches_s(const uint32_t *o, uint32_t xI, uint32_t yI, uint32_t *m, uint32_t *n)
+{
+  const uint32_t xyI = xI + yI;
+  m[0] = o[0];       m[1] = o[3] + yI; m[2] = o[4] + yI; m[3] = o[7];
+  m[4] = o[1];       m[5] = o[2] + yI; m[6] = o[5] + yI; m[7] = o[6];
+  n[0] = o[1] + xyI; n[1] = o[2] + xI; n[2] = o[5] + xI; n[3] = o[6] + xyI;
+  n[4] = o[0] + xyI; n[5] = o[3] + xI; n[6] = o[4] + xI; n[7] = o[7] + xyI;
+}
+
 /* ---------------------------------------------------------------- tensor-memory checkpoint store ---- */
 #if FEC_PK_TMEM
 __device__ __forceinline__ void pk_ck_store(uint32_t taddr, const uint32_t *o)
@@ -230,21 +292,21 @@ __device__ __forceinline__ void pk_load_raw(const PkView &v, int k0, int i0, PkR
   }
 }
 
-/* CRC syndrome words of the chunk */
-template <bool FULL, bool VEC>
+/* CRC syndrome words of the chunk. Step k sits at uint2 index (k>>1)*2*TPC + (k&1): with k0 even (VEC: L % 4 == 0, so every
+ * chunk base is) the 8 steps are 4 pairs 128 bytes apart — one base pointer per chunk and constant offsets, instead of
+ * one 64-bit address computation per load (5 instructions each in the SASS of the first version) */
+template <bool FULL, bool VEC, int TPC>
 __device__ __forceinline__ void pk_load_crc(const PkView &v, int k0, int i0, uint2 *rr)
 {
-  if (FULL && VEC && !PK_CRC64) {
+  if (FULL && VEC) {
+    const uint2 *base = v.Rrow + (k0 >> 1) * (2 * TPC);
 #pragma unroll
-    for (int i = 0; i < 8; i += 2) {
-      const uint4 t = pk_ldg128(v.Rrow + ((k0 + i) >> 1) * (v.tpc4 >> 1));
-      rr[i] = make_uint2(t.x, t.y); rr[i + 1] = make_uint2(t.z, t.w);
-    }
+    for (int i = 0; i < 8; i++) rr[i] = pk_ldg64(base + (i >> 1) * (2 * TPC) + (i & 1));
   } else {
 #pragma unroll
     for (int i = 0; i < 8; i++) {
       rr[i] = make_uint2(0, 0);
-      if (FULL || i >= i0) { const int k = k0 + i; rr[i] = pk_ldg64(v.Rrow + (k >> 1) * (v.tpc4 >> 1) + (k & 1)); }
+      if (FULL || i >= i0) { const int k = k0 + i; rr[i] = pk_ldg64(v.Rrow + (k >> 1) * (2 * TPC) + (k & 1)); }
     }
   }
 }
@@ -282,14 +344,14 @@ __device__ __forceinline__ void pk_finish_chunk(const PkView &v, int k0, int i0,
  * with this schedule every sum stays within max(13 G, 10000 + 10 G). */
 
 /* 8 backward steps of the main pass (i = 7..0); the checkpoint is the NORMALISED state after step i = 0 */
-template <bool FULL>
+template <bool FULL, bool MIX>
 __device__ __forceinline__ void pk_beta_chunk(uint32_t *o, const uint32_t *xs, const uint32_t *ys, int i0, uint32_t ck_addr)
 {
 #pragma unroll
   for (int i = 7; i >= 0; i--) {
     if (FULL || i >= i0) {
-      pk_beta(o, xs[i], ys[i]);
-      if ((i & 3) == 0) pk_norm(o);
+      if (MIX) { pk_beta_s(o, pk_gammas(xs[i], ys[i])); if ((i & 3) == 0) pk_norm_s(o); }
+      else { pk_beta(o, xs[i], ys[i]); if ((i & 3) == 0) pk_norm(o); }
       if (FULL && i == 0) pk_ck_store(ck_addr, o);
     }
   }
@@ -311,12 +373,12 @@ struct PkAcc { uint32_t crc, emx, emn, wlo, whi; uint32_t vmx, vmn, rb; PkTrk ta
 
 /* one chunk of the forward pass: recompute the inner betas from the checkpoint `ck` (= normalised beta at k0+8),
  * then alpha recursion + LLR + extrinsic write-back + CRC syndrome + decision bits for steps i = i0..7 */
-template <bool FULL, bool SHIFT, bool TRK>
+template <bool FULL, bool SHIFT, bool TRK, bool MIX>
 __device__ __forceinline__ void pk_alpha_chunk(const PkView &v, int k0, uint32_t *o, const uint32_t *ck, int i0,
                                                const uint32_t *xs, const uint32_t *ys, const uint32_t *es,
                                                const uint2 *rr, PkAcc &acc, const uint32_t *ka, int kpar = 0, bool top = false)
 {
-  uint32_t b[8], bb[8][8], m[8], n[8];
+  uint32_t b[8], bb[8][8], m[8], n[8], xi[8], yi[8];
 #pragma unroll
   for (int s = 0; s < 8; s++) b[s] = ck[s];
   if (TRK) {
@@ -327,6 +389,15 @@ __device__ __forceinline__ void pk_alpha_chunk(const PkView &v, int k0, uint32_t
 #pragma unroll
   for (int i = 7; i >= 1; i--) {
     if (FULL || i >= i0 + 1) {
+      if (MIX) {
+        const PkGam g = pk_gammas(xs[i], ys[i]);
+        xi[i] = g.xI; yi[i] = g.yI;                     /* the forward pass below needs the I forms only */
+        pk_beta_s(b, g);
+        if (i == 4) pk_norm_s(b);
+#pragma unroll
+        for (int s = 0; s < 8; s++) bb[i][s] = b[s];
+        continue;
+      }
       pk_beta(b, xs[i], ys[i]);
       if (TRK) {
 #pragma unroll
@@ -342,29 +413,44 @@ __device__ __forceinline__ void pk_alpha_chunk(const PkView &v, int k0, uint32_t
 #pragma unroll
   for (int i = 0; i < 8; i++) {
     if (FULL || i >= i0) {
-      pk_alpha_branches(o, xs[i], ys[i], m, n);
+      if (MIX) {
+        if (i == 0 || (!FULL && i == i0)) { xi[i] = pk_to_i(xs[i]); yi[i] = pk_to_i(ys[i]); }   /* the step the backward loop did not visit */
+        pk_alpha_branches_s(o, xi[i], yi[i], m, n);
+      } else pk_alpha_branches(o, xs[i], ys[i], m, n);
       const uint32_t *bn = (i == 7) ? ck : bb[(i + 1) & 7];
       uint32_t m0 = pk_add(bn[0], m[0]), m1 = pk_add(bn[0], n[0]);
 #pragma unroll
       for (int s = 1; s < 8; s++) { m0 = pk_addmax(bn[s], m[s], m0); m1 = pk_addmax(bn[s], n[s], m1); }
       if (TRK) { acc.vmx = __vimax3_s16x2(acc.vmx, m0, m1); acc.vmn = __vimin3_s16x2(acc.vmn, m0, m1); }
-      uint32_t r = pk_sub(m1, m0);
-      if (SHIFT) r = ((r >> 1) & 0x7FFF7FFFu) | (r & 0x80008000u);        /* divide_output, sse16 only (:61,565) */
-      const uint32_t en = pk_sub(r, es[i]);                                /* next apriori = LLR - what this decoder was given */
+      /* LLR r = m1 - m0, next apriori en = r - (what this decoder was given). A packed subtract is NOT + add + add 1; the sign
+       * test wants r - 1 = m1 + ~m0 anyway, so r itself is never formed (unless it has to be halved): en = (r - 1) + ~es + 2 */
+      uint32_t rm1, en;
+      if (SHIFT) {
+        uint32_t r = pk_sub(m1, m0);
+        r = ((r >> 1) & 0x7FFF7FFFu) | (r & 0x80008000u);                  /* divide_output, sse16 only (:61,565) */
+        en = pk_sub(r, es[i]);
+        rm1 = pk_add(r, 0xFFFFFFFFu);
+      } else {
+        rm1 = pk_add(m1, ~m0);
+        en = pk_add(pk_add(rm1, ~es[i]), 0x00020002u);
+      }
       uint32_t alo, ahi;
       if (PK_KEEP_ADDR) { alo = ka[2 * i]; ahi = ka[2 * i + 1]; } else pk_eaddr(v, k0 + i, alo, ahi);
       pk_sts_u16(alo, en);
       pk_sts_u16(ahi, en >> 16);
       acc.emx = pk_max(acc.emx, en); acc.emn = pk_min(acc.emn, en);
-      const uint32_t nr = pk_sub(0u, r);                                   /* sign set <=> LLR > 0 <=> bit 1 */
-      const uint32_t mlo = pk_prmt(nr, 0u, 0x9999u), mhi = pk_prmt(nr, 0u, 0xBBBBu);
-      acc.crc ^= (mlo & rr[i].x) ^ (mhi & rr[i].y);
-      acc.wlo = __funnelshift_l(mlo, acc.wlo, 1); acc.whi = __funnelshift_l(mhi, acc.whi, 1);
+      /* decision: bit 1 <=> LLR > 0 <=> r - 1 >= 0. The masks below are all-ones for a ZERO bit (sign of r - 1: one packed add
+       * with an immediate instead of the two-instruction negation); the CRC takes them inverted inside its LOP3, the decision
+       * words collect w <- 2 w + mask (an IMAD on the otherwise idle FMA pipe instead of a funnel shift on the ALU pipe):
+       * after the 32 steps of a word w = -(inverted bits), so the decisions are ~(-w) = w - 1 (taken at the stores) */
+      const uint32_t zlo = pk_prmt(rm1, 0u, 0x9999u), zhi = pk_prmt(rm1, 0u, 0xBBBBu);
+      acc.crc ^= (~zlo & rr[i].x) ^ (~zhi & rr[i].y);
+      acc.wlo = acc.wlo * 2u + zlo; acc.whi = acc.whi * 2u + zhi;
 #pragma unroll
-      for (int s = 0; s < 8; s++) o[s] = pk_max(m[s], n[s]);
+      for (int s = 0; s < 8; s++) o[s] = MIX ? pk_max_u(m[s], n[s]) : pk_max(m[s], n[s]);
       if (TRK) { if ((((i + kpar) & 1) == 0) && (k0 + i != 0)) pk_norm_trk(o, acc.ta); }
-      else if ((i & 3) == 3) pk_norm(o);
-    } else { acc.wlo <<= 1; acc.whi <<= 1; }
+      else if ((i & 3) == 3) { if (MIX) pk_norm_s(o); else pk_norm(o); }
+    } else { acc.wlo = acc.wlo * 2u + 0xFFFFFFFFu; acc.whi = acc.whi * 2u + 0xFFFFFFFFu; }   /* a zero bit for a step that does not exist */
   }
 }
 
@@ -393,6 +479,7 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
 {
   const int nfull = L >> 3, rem = L & 7;
   const int kpar = VEC ? 0 : (L & 1);               /* parity of every chunk base k0 (chunks are 8 steps, aligned to L) */
+  constexpr bool MIX = PK_MIX && !TRK;              /* S / I / P forms (see pk_beta_s) instead of P form throughout */
   uint32_t o[8], xs[8], es[8], ka[16];
   PkRaw raw, nraw;
   PkTrk tb;                                         /* TRK: extremes of the beta recursion (warm-up + main pass) */
@@ -413,7 +500,7 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
 
   /* ---- beta warm-up over the first 40 symbols of both sub-blocks (turbodecoder_win.h:321-384) ---- */
 #pragma unroll
-  for (int i = 0; i < 8; i++) o[i] = 0;            /* the reference starts from 8 equal metrics (-10000): only differences matter */
+  for (int i = 0; i < 8; i++) o[i] = MIX ? PK_C : 0u;   /* the reference starts from 8 equal metrics (-10000): only differences matter */
   /* every loop below has the shape  { issue the loads of the NEXT chunk; PK_PIN; work on this chunk; rotate }  and
    * starts with a load-only iteration: no load is in flight when a loop is entered, so the only scoreboard
    * wait on global loads sits at the rotation, a whole chunk after their issue */
@@ -425,6 +512,7 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
       pk_finish_chunk<true>(v, 8 * c, 0, raw, xs, es);
 #pragma unroll
       for (int i = 7; i >= 0; i--) {
+        if (MIX) { pk_beta_s(o, pk_gammas(xs[i], raw.y[i])); if ((i & 3) == 0) pk_norm_s(o); continue; }
         pk_beta(o, xs[i], raw.y[i]);
         if (TRK) { if (!(i & 1) && (i != 0 || c != 0)) pk_norm_trk(o, tb); }     /* even k != 0 (:244-261) */
         else if ((i & 3) == 0) pk_norm(o);
@@ -457,9 +545,10 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
 #pragma unroll
     for (int i = 0; i < 8; i++) {
       const uint32_t w = __shfl_down_sync(gmask, o[i], 1, TPC);
-      o[i] = (j == TPC - 1) ? ((o[i] >> 16) | ((uint32_t)t[i] << 16)) : pk_prmt(o[i], w, 0x5432u);
+      o[i] = (j == TPC - 1) ? ((o[i] >> 16) | ((uint32_t)(t[i] + (MIX ? 32768 : 0)) << 16)) : pk_prmt(o[i], w, 0x5432u);
     }
     if (TRK) pk_trk8(tb, o);                          /* the reference starts the main pass from this state as it is */
+    else if (MIX) pk_norm_s(o);
     else pk_norm(o);
   }
   /* ---- beta main pass, chunks aligned from the top; checkpoint c = normalised beta at k = L-8c ---- */
@@ -474,7 +563,7 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
       PK_PIN();
       pk_finish_chunk<true>(v, L - PK_CH, 0, raw, xs, es);
       if (TRK) pk_beta_chunk_trk(o, xs, raw.y, tbase + 8, kpar, L != PK_CH, tb);
-      else pk_beta_chunk<true>(o, xs, raw.y, 0, tbase + 8);
+      else pk_beta_chunk<true, MIX>(o, xs, raw.y, 0, tbase + 8);
     }
 #pragma unroll 1
     for (int c = c0 - 2; c < nfull; c += 2) {
@@ -484,10 +573,10 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
       if (c >= c0) {
         pk_finish_chunk<true>(v, k0, 0, raw, xs, es);
         if (TRK) pk_beta_chunk_trk(o, xs, raw.y, tbase + 8 * (c + 1), kpar, true, tb);
-        else pk_beta_chunk<true>(o, xs, raw.y, 0, tbase + 8 * (c + 1));
+        else pk_beta_chunk<true, MIX>(o, xs, raw.y, 0, tbase + 8 * (c + 1));
         pk_finish_chunk<true>(v, k0 - PK_CH, 0, rawB, xs, es);
         if (TRK) pk_beta_chunk_trk(o, xs, rawB.y, tbase + 8 * (c + 2), kpar, k0 != PK_CH, tb);
-        else pk_beta_chunk<true>(o, xs, rawB.y, 0, tbase + 8 * (c + 2));
+        else pk_beta_chunk<true, MIX>(o, xs, rawB.y, 0, tbase + 8 * (c + 2));
       }
       raw = nraw; rawB = nrawB;
     }
@@ -499,7 +588,7 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
   {
     uint32_t m[8], n[8];
 #pragma unroll
-    for (int i = 0; i < 8; i++) o[i] = 0;
+    for (int i = 0; i < 8; i++) o[i] = MIX ? PK_C : 0u;
 #pragma unroll 1
     for (int c = -1; c < 5; c++) {
       if (c < 4) pk_load_raw<true, VEC>(v, L - 40 + 8 * (c + 1), 0, nraw);
@@ -508,6 +597,13 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
         pk_finish_chunk<true>(v, L - 40 + 8 * c, 0, raw, xs, es);
 #pragma unroll
         for (int i = 0; i < 8; i++) {
+          if (MIX) {
+            pk_alpha_branches_s(o, pk_to_i(xs[i]), pk_to_i(raw.y[i]), m, n);
+#pragma unroll
+            for (int s = 0; s < 8; s++) o[s] = pk_max_u(m[s], n[s]);
+            if ((i & 3) == 3) pk_norm_s(o);
+            continue;
+          }
           pk_alpha_branches(o, xs[i], raw.y[i], m, n);
 #pragma unroll
           for (int s = 0; s < 8; s++) o[s] = pk_max(m[s], n[s]);
@@ -521,7 +617,7 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
 #pragma unroll
   for (int i = 0; i < 8; i++) {
     const uint32_t w = __shfl_up_sync(gmask, o[i], 1, TPC);
-    const uint32_t first = (i == 0) ? 0u : 0xD8F0u;
+    const uint32_t first = MIX ? ((i == 0) ? 0x8000u : 0x58F0u) : ((i == 0) ? 0u : 0xD8F0u);   /* 0 / -10000, offset-binary in S form */
     o[i] = (j == 0) ? (first | (o[i] << 16)) : pk_prmt(w, o[i], 0x5432u);
   }
   if (TRK) {
@@ -531,7 +627,8 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
 #pragma unroll
     for (int i = 0; i < 8; i++) tv[i] = (j == 0) ? (o[i] & 0xFFFF0000u) : o[i];
     pk_trk8(acc.ta, tv);
-  } else pk_norm(o);
+  } else if (MIX) pk_norm_s(o);
+  else pk_norm(o);
   /* ---- alpha main pass, ascending k: bottom partial chunk (if any), then the full chunks ---- */
   acc.wlo = 0; acc.whi = 0;
   int wi = 0, cc = 0;
@@ -541,29 +638,29 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
     const int k0 = rem - PK_CH, i0 = PK_CH - rem;
     pk_ck_load_issue(tbase + 8 * nfull, ck);
     pk_load_raw<false, VEC>(v, k0, i0, raw);
-    pk_load_crc<false, VEC>(v, k0, i0, rr);
+    pk_load_crc<false, VEC, TPC>(v, k0, i0, rr);
     PK_PIN();
     pk_finish_chunk<false>(v, k0, i0, raw, xs, es, ka);
     pk_ck_load_wait(ck);
-    pk_alpha_chunk<false, SHIFT, TRK>(v, k0, o, ck, i0, xs, raw.y, es, rr, acc, ka, kpar, false);
+    pk_alpha_chunk<false, SHIFT, TRK, MIX>(v, k0, o, ck, i0, xs, raw.y, es, rr, acc, ka, kpar, false);
     cc = 1;
   }
 #pragma unroll 1
   for (int c = nfull; c >= 0; c--) {                 /* iteration c works on steps [k0, k0+8), k0 = rem + 8(nfull-1-c) */
     const int k0 = rem + PK_CH * (nfull - 1 - c);
     if (c > 0) pk_load_raw<true, VEC>(v, k0 + PK_CH, 0, nraw);
-    if (c < nfull) { pk_ck_load_issue(tbase + 8 * c, ck); pk_load_crc<true, VEC>(v, k0, 0, rr); }
+    if (c < nfull) { pk_ck_load_issue(tbase + 8 * c, ck); pk_load_crc<true, VEC, TPC>(v, k0, 0, rr); }
     PK_PIN();
     if (c < nfull) {
       pk_finish_chunk<true>(v, k0, 0, raw, xs, es, ka);
       pk_ck_load_wait(ck);
-      pk_alpha_chunk<true, SHIFT, TRK>(v, k0, o, ck, 0, xs, raw.y, es, rr, acc, ka, kpar, c == 0);
-      if ((cc & 3) == 3) { bits_lo[wi] = acc.wlo; bits_hi[wi] = acc.whi; wi++; }
+      pk_alpha_chunk<true, SHIFT, TRK, MIX>(v, k0, o, ck, 0, xs, raw.y, es, rr, acc, ka, kpar, c == 0);
+      if ((cc & 3) == 3) { bits_lo[wi] = acc.wlo - 1u; bits_hi[wi] = acc.whi - 1u; wi++; }
       cc++;
     }
     raw = nraw;
   }
-  if (cc & 3) { const int sh = 32 - 8 * (cc & 3); bits_lo[wi] = acc.wlo << sh; bits_hi[wi] = acc.whi << sh; }
+  if (cc & 3) { const int sh = 32 - 8 * (cc & 3); bits_lo[wi] = (acc.wlo - 1u) << sh; bits_hi[wi] = (acc.whi - 1u) << sh; }
 #if PK_PF_L1
   /* the next half-iteration starts with the first 40 steps of the other decoder's rows (10 lines per stream):
    * pull them into L1 while the CRC is reduced and the slot decides how to go on */
