@@ -210,7 +210,11 @@ def main():
     ap.add_argument("--sigma", type=float, default=0.45, help="AWGN std of the synthetic LLRs (0.45 = operating point)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-worst-case", action="store_true")
-    ap.add_argument("--no-uplink", action="store_true", help="skip the PUSCH leg of the symbol front end")
+    ap.add_argument("--no-uplink", action="store_true", help="skip the 64-cell PUSCH leg (BASELINE configs[4])")
+    ap.add_argument("--ul-subframes", type=int, default=37, help="subframes per cell and step of the 64-cell PUSCH leg (64 x 37 = 2368 TBs)")
+    ap.add_argument("--no-harq", action="store_true", help="skip the HARQ leg (BASELINE configs[2])")
+    ap.add_argument("--sigma-harq", type=float, default=0.50, help="AWGN std of the HARQ leg (rv 0 mostly fails)")
+    ap.add_argument("--sustain", type=float, default=2.0, help="seconds of the sustained leg (0 = skip)")
     ap.add_argument("--no-llr8", action="store_true", help="skip the 8-bit LLR leg")
     ap.add_argument("--sigma8", type=float, default=0.30, help="AWGN std of the 8-bit LLR leg")
     ap.add_argument("--sigma-ul", type=float, default=0.17, help="AWGN std per real dimension of the synthetic 16QAM PUSCH symbols")
@@ -344,7 +348,7 @@ def main():
 
     # ---- front-end leg: the same transport blocks given as equalised 64QAM symbols (8 B per resource element
     #      instead of 12 B of LLRs); soft demodulation + descrambling run in the fused front-end kernel on the device ----
-    front = None
+    front, ulsch5 = None, None
     if not args.no_symbols:
         synth = importlib.import_module("empower-srslte_b200.synth")
         nre = NBITS // QM
@@ -414,35 +418,46 @@ def main():
         #      srsENB grants, phch_worker.cc:598-601), 96 PRB, TBS 36696 = 6 x K=6144, HARQ-ACK / RI / CQI multiplexed: soft
         #      demodulation, ACK zeroing, descrambling, channel de-interleaver with RI removal, then decode_tb on g_bits ----
         if not args.no_uplink:
+            # BASELINE configs[4]: "multi-cell eNB UL-SCH decode: 64 cells x 20 MHz ... sharded across 1/2/4/8 B200". The 64 cells
+            # are placed with shard.owner (cell-affine: every HARQ process of a cell lives on ONE GPU, no soft buffer ever moves,
+            # no collective); this rank decodes args.ul_subframes subframes of each of ITS cells per step. Strong scaling: the
+            # job (64 cells) is fixed, the per-rank share shrinks with N.
             ACK_COLS, RI_COLS, uci_positions = synth.ACK_COLS, synth.RI_COLS, synth.uci_positions
-            U_TBS, U_MOD, U_PRB, U_COLS, U_CQI = 36696, 4, 96, 12, 32
+            U_TBS, U_MOD, U_PRB, U_COLS, U_CQI, U_C, N_CELLS = 36696, 4, 96, 12, 32, 6, 64
             u_rows, u_nre = 12 * U_PRB, 12 * U_PRB * U_COLS
             ack_pos = np.array(uci_positions(8, U_MOD, u_rows, ACK_COLS), np.uint32)
             ri_pos = np.array(uci_positions(4, U_MOD, u_rows, RI_COLS), np.uint32)
             U_G = u_nre * U_MOD - ri_pos.size - U_CQI
-            u_ncw = 16
-            u_pay = np.random.default_rng(7000 + rank).integers(0, 256, (u_ncw, U_TBS // 8), dtype=np.uint8)
-            u_e = synth.encode_tbs(u_pay, U_TBS, U_MOD, 0, U_G)
-            u_cq = rng.integers(0, 2, (u_ncw, U_CQI)).astype(u_e.dtype)
+            keys = [(c, 0) for c in range(N_CELLS)]
+            my_cells = [keys[i][0] for i in shard.partition(keys, rank, world)]
+            nsf = args.ul_subframes
+            nU = len(my_cells) * nsf                                  # transport blocks of this rank per step
+            u_pay = np.random.default_rng(7000).integers(0, 256, (N_CELLS, U_TBS // 8), dtype=np.uint8)     # one codeword per cell
+            u_e = synth.encode_tbs(u_pay[my_cells], U_TBS, U_MOD, 0, U_G)
+            u_cq = np.random.default_rng(7001).integers(0, 2, (N_CELLS, U_CQI)).astype(u_e.dtype)[my_cells]
             u_q = synth.ulsch_interleave(np.concatenate([u_cq, u_e], axis=1), U_MOD, U_COLS, list(ri_pos))
-            u_ci = [synth.cinit_pusch(0x46 + k, 2 * (k % 10), 1 + k % 64) for k in range(u_ncw)]
-            u_clean = np.stack([synth.modulate(u_q[k] ^ synth.gold_sequence(u_ci[k], u_nre * U_MOD), U_MOD) for k in range(u_ncw)])
-            hu_sym = pkg.PinnedArray((B, u_nre, 2), np.float32)
-            for i0 in range(0, B, 64):
-                i1 = min(B, i0 + 64)
-                hu_sym.a[i0:i1] = synth.awgn_symbols(u_clean[np.arange(i0, i1) % u_ncw], args.sigma_ul, rng)
+            u_ci = [synth.cinit_pusch(0x46 + c, 2 * (c % 10), 1 + c) for c in my_cells]                     # cell id = c + 1
+            u_clean = np.stack([synth.modulate(u_q[k] ^ synth.gold_sequence(u_ci[k], u_nre * U_MOD), U_MOD) for k in range(len(my_cells))])
+            hu_sym = pkg.PinnedArray((nU, u_nre, 2), np.float32)
+            rng_u = np.random.default_rng(7100 + rank)
+            cell_of = np.repeat(np.arange(len(my_cells)), nsf)        # TB i belongs to this rank's cell cell_of[i]
+            for i0 in range(0, nU, 64):
+                i1 = min(nU, i0 + 64)
+                hu_sym.a[i0:i1] = synth.awgn_symbols(u_clean[cell_of[i0:i1]], args.sigma_ul, rng_u)
             du_sym = torch.from_numpy(hu_sym.a).to(f"cuda:{local_rank}")
             n_uci = ack_pos.size + ri_pos.size + U_CQI
-            du_uci = torch.zeros((2, B, (n_uci + 7) & ~7), dtype=torch.int16, device=f"cuda:{local_rank}")
+            du_uci = torch.zeros((2, nU, (n_uci + 7) & ~7), dtype=torch.int16, device=f"cuda:{local_rank}")
+            du_out = torch.zeros((2, nU, DATA_STRIDE), dtype=torch.uint8, device=f"cuda:{local_rank}")
+            sbu = fec.softbuffer_alloc(2 * nU)                        # per (cell, subframe) HARQ entity, two sets in flight
             u_tb, u_sy = [], []
             for s_ in range(2):
-                t_ = (pkg.TbDesc * B)()
-                y_ = (pkg.SymDesc * B)()
-                for i in range(B):
+                t_ = (pkg.TbDesc * nU)()
+                y_ = (pkg.SymDesc * nU)()
+                for i in range(nU):
                     t_[i].tbs, t_[i].Qm, t_[i].rv, t_[i].nof_e_bits, t_[i].max_its = U_TBS, U_MOD, 0, U_G, 8
-                    t_[i].softbuffer, t_[i].new_data = sb0 + s_ * B + i, 1
-                    t_[i].data = d_out[s_].data_ptr() + i * DATA_STRIDE
-                    y_[i].symbols, y_[i].nof_re, y_[i].mod_bits, y_[i].c_init = du_sym.data_ptr() + i * u_nre * 8, u_nre, U_MOD, u_ci[i % u_ncw]
+                    t_[i].softbuffer, t_[i].new_data = sbu + s_ * nU + i, 1
+                    t_[i].data = du_out[s_, i].data_ptr()
+                    y_[i].symbols, y_[i].nof_re, y_[i].mod_bits, y_[i].c_init = du_sym.data_ptr() + i * u_nre * 8, u_nre, U_MOD, u_ci[cell_of[i]]
                     y_[i].nof_symb = U_COLS
                     y_[i].ack_pos, y_[i].ri_pos, y_[i].nof_ack_pos, y_[i].nof_ri_pos = ack_pos.ctypes.data, ri_pos.ctypes.data, ack_pos.size, ri_pos.size
                     y_[i].nof_cqi_bits = U_CQI
@@ -451,24 +466,124 @@ def main():
             for i in range(6):
                 fec.decode_syms(u_tb[i & 1], u_sy[i & 1], pkg.F_DEVICE_IO)
             ms_ul = timed_syms(u_tb, u_sy, pkg.F_DEVICE_IO, args.steps)
-            ok_u, its_u = tally(u_tb[0])
-            out_host = d_out[0].cpu().numpy()
-            bad = sum(1 for i in range(B) if u_tb[0][i].ret == 0 and not (out_host[i, :U_TBS // 8] == u_pay[i % u_ncw]).all())
+            ok_u = sum(1 for i in range(nU) if u_tb[0][i].ret == 0)
+            its_u = sum(sum(u_tb[0][i].cb_its[:U_C]) for i in range(nU))
+            out_host = du_out[0].cpu().numpy()
+            bad = sum(1 for i in range(nU) if u_tb[0][i].ret == 0 and not (out_host[i, :U_TBS // 8] == u_pay[my_cells[cell_of[i]]]).all())
             if bad:
                 raise SystemExit(f"bench.py: {bad} CRC-passing transport blocks of the uplink leg differ from the transmitted payload")
             fec.decode_syms(u_tb[0], u_sy[0], pkg.F_DEVICE_IO | pkg.F_SERIAL)
             path_u = fec.last_path_counts()
-            U_C = 6
-            front["uplink"] = dict(workload="PUSCH 16QAM 96 PRB, TBS 36696 (6 x K=6144), 32 HARQ-ACK + 16 RI positions + 32 CQI bits multiplexed; "
-                                            "symbols in, device-resident", sigma_sym=args.sigma_ul,
-                                   value=allsum(ok_u) * U_TBS * args.steps / (ms_ul / 1e3) / 1e9, unit=UNIT, ms_per_step=ms_ul / args.steps,
-                                   tb_ok_frac=allsum(ok_u) / (world * B), halfits_per_cb=allsum(its_u) / (world * B * U_C),
-                                   cbs_per_s=world * B * U_C * args.steps / (ms_ul / 1e3),
-                                   code_blocks_by_kernel=dict(total=B * U_C, certificate_variant=path_u[0], exact=path_u[1]),
-                                   serial_phases_ms=dict(zip(("rate_dematch", "turbo_decode", "tb_assemble_crc24a"), fec.last_phase_ms()),
-                                                         frontend=fec.last_frontend_ms()))
+            tot_u = allsum(nU)
+            ulsch5 = dict(workload="BASELINE configs[4]: 64 cells x PUSCH 16QAM 96 PRB, TBS 36696 (6 x K=6144), 32 HARQ-ACK + 16 RI positions + 32 CQI bits "
+                                   "multiplexed; equalised symbols in (device-resident), UL front end + decode_tb", scaling="strong",
+                          placement="shard.partition: cell c on rank c mod N with all of its HARQ soft buffers; no collective on the data path",
+                          cells=N_CELLS, cells_this_rank=len(my_cells), subframes_per_cell_per_step=nsf, tbs_per_step=tot_u, sigma_sym=args.sigma_ul,
+                          value=allsum(ok_u) * U_TBS * args.steps / (ms_ul / 1e3) / 1e9, unit=UNIT, ms_per_step=ms_ul / args.steps,
+                          tb_ok_frac=allsum(ok_u) / tot_u, halfits_per_cb=allsum(its_u) / (tot_u * U_C),
+                          cbs_per_s=tot_u * U_C * args.steps / (ms_ul / 1e3), payload_check="every CRC-passing TB of set 0 equals its cell's transmitted payload",
+                          code_blocks_by_kernel_rank0=dict(total=nU * U_C, certificate_variant=path_u[0], exact=path_u[1]),
+                          serial_phases_ms_rank0=dict(zip(("rate_dematch", "turbo_decode", "tb_assemble_crc24a"), fec.last_phase_ms()),
+                                                      frontend=fec.last_frontend_ms()))
+            del du_sym, du_uci, du_out
+            hu_sym.free()
         # the LLR legs below reuse dd / hd: put the soft buffers back into the state of the LLR workload
         fec.decode_tbs(dd, pkg.F_DEVICE_IO)
+
+    # ---- HARQ leg (BASELINE configs[2]: TM4 2-codeword shape, 8-process HARQ soft combining): TBS 75376 in 86400 LLRs (rate 0.876),
+    #      13 x K=5824, rv sequence 0,2,3,1; noise so that rv 0 mostly fails. One step = one whole HARQ cycle of B/2 processes:
+    #      round 0 decodes all of them (new data), every later round only the NACKed ones with new_data = 0 — the read-modify-write
+    #      combine (softbuffer.c:128-151 state, rm_turbo.c:411-420), the cb_crc skip and the cached-CB copy (sch.c:396-418) are
+    #      inside the timed region. Rounds of one process are sequential by nature (same soft buffer), so the calls are blocking.
+    harq = None
+    if not args.no_harq:
+        synth_h = importlib.import_module("empower-srslte_b200.synth")
+        H_NBITS, Bh = 86400, max(8, B // 2)
+        rng_h = np.random.default_rng(9000 + rank)
+        ncw = payload.shape[0]
+        d_h = []
+        tmp_h = np.empty((64, H_NBITS), np.int16)
+        for rv in (0, 2, 3, 1):
+            e_h = synth_h.encode_tbs(payload, TBS, QM, rv, H_NBITS)
+            dev = torch.empty((Bh, H_NBITS), dtype=torch.int16, device=f"cuda:{local_rank}")
+            for i0 in range(0, Bh, 64):
+                i1 = min(Bh, i0 + 64)
+                synth_h.awgn_llr(e_h[np.arange(i0, i1) % ncw], args.sigma_harq, rng_h, out=tmp_h[: i1 - i0])
+                dev[i0:i1] = torch.from_numpy(tmp_h[: i1 - i0]).to(dev.device)
+            d_h.append(dev)
+
+        def harq_round(r, live):
+            d_ = (pkg.TbDesc * len(live))()
+            for s_, i in enumerate(live):
+                d_[s_].tbs, d_[s_].Qm, d_[s_].rv, d_[s_].nof_e_bits, d_[s_].max_its = TBS, QM, (0, 2, 3, 1)[r], H_NBITS, MAX_ITS
+                d_[s_].softbuffer, d_[s_].new_data = sb0 + i, int(r == 0)
+                d_[s_].e_bits, d_[s_].data = d_h[r].data_ptr() + i * H_NBITS * 2, d_out[0].data_ptr() + i * DATA_STRIDE
+            return d_
+
+        # discovery pass (untimed): which processes are still NACKed after each round — deterministic, the timed passes repeat it
+        rounds, live = [], list(range(Bh))
+        for r in range(4):
+            if not live:
+                break
+            d_ = harq_round(r, live)
+            fec.decode_tbs(d_, pkg.F_DEVICE_IO)
+            rounds.append((d_, list(live), [d_[s_].ret for s_ in range(len(live))]))
+            live = [i for s_, i in enumerate(live) if d_[s_].ret != 0]
+        fec.decode_tbs(rounds[0][0], pkg.F_DEVICE_IO)          # warm
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(args.steps):
+            for d_, _, _ in rounds:
+                fec.decode_tbs(d_, pkg.F_DEVICE_IO)
+        e1.record(stream)
+        barrier()
+        ms_h = shard.reduce_job(dist if world > 1 else None, f"cuda:{local_rank}", e0.elapsed_time(e1))[0]
+        out_host = d_out[0].cpu().numpy()
+        acked, ntx, skipped, per_round = 0, 0, 0, []
+        for r, (d_, lv, ret0) in enumerate(rounds):
+            if [d_[s_].ret for s_ in range(len(lv))] != ret0:
+                raise SystemExit("bench.py: the HARQ leg is not deterministic across steps")
+            ok_r = [i for s_, i in enumerate(lv) if d_[s_].ret == 0]
+            bad = sum(1 for i in ok_r if not (out_host[i, :TBS // 8] == payload[i % ncw]).all())
+            if bad:
+                raise SystemExit(f"bench.py: {bad} ACKed transport blocks of the HARQ leg differ from the transmitted payload")
+            sk = sum(sum(1 for c in range(C_CB) if d_[s_].cb_its[c] == 0) for s_ in range(len(lv))) if r else 0
+            acked += len(ok_r); ntx += len(lv); skipped += sk
+            per_round.append(dict(rv=(0, 2, 3, 1)[r], tbs=len(lv), acked=len(ok_r), code_blocks_skipped_already_ok=sk))
+        # the rate de-matcher in its read-modify-write case: the first retransmission round, serialised
+        rmw = None
+        if len(rounds) > 1:
+            for d_, _, _ in rounds[:2]:
+                fec.decode_tbs(d_, pkg.F_DEVICE_IO | pkg.F_SERIAL)
+            ph = fec.last_phase_ms()
+            d1, lv1 = rounds[1][0], rounds[1][1]
+            ncb1 = sum(sum(1 for c in range(C_CB) if d1[s_].cb_its[c] > 0) for s_ in range(len(lv1)))
+            Eh = H_NBITS // C_CB
+            byt = ncb1 * (2 * Eh + 2 * 2 * (3 * 5888 + 16))       # LLRs in, slot read + slot written (3*SS+16 int16, SS = 16*368)
+            rmw = dict(code_blocks=ncb1, ms=ph[0], algorithmic_bytes=byt, achieved=byt / (ph[0] / 1e3) / 1e9, unit="GB/s", peak=peaks()["hbm_gbs"],
+                       frac=byt / (ph[0] / 1e3) / 1e9 / peaks()["hbm_gbs"], bytes_per_cb="2E + 2 x 2 x (3*SS+16)")
+        harq = dict(workload="BASELINE configs[2] shape: TBS 75376 in 86400 LLRs (13 x K=5824, E = 6642/6648), rv 0,2,3,1, "
+                             "new_data only in round 0; later rounds combine into the soft buffers, skip code blocks that are already OK and copy their cached bytes",
+                    sigma=args.sigma_harq, harq_processes=allsum(Bh), value=allsum(acked) * TBS * args.steps / (ms_h / 1e3) / 1e9, unit=UNIT + " of ACKed bits",
+                    ms_per_cycle=ms_h / args.steps, mean_transmissions_per_tb=allsum(ntx) / allsum(Bh), acked_frac=allsum(acked) / allsum(Bh),
+                    rounds_rank0=per_round, rate_dematch_read_modify_write_rank0=rmw,
+                    payload_check="every ACKed transport block equals the transmitted payload; return codes identical in every cycle")
+        del d_h
+        fec.decode_tbs(dd, pkg.F_DEVICE_IO)
+
+    # ---- sustained leg: the headline step looped for args.sustain seconds (the timed region of `value` is tens of milliseconds) ----
+    sustained = None
+    if args.sustain > 0:
+        n_s = max(args.steps, int(args.sustain * 1e3 / (ms / args.steps)) + 1)
+        smp = ClockSampler(local_rank)
+        smp.start()
+        time.sleep(0.2)
+        ms_s = timed_pipelined(dd_ab, pkg.F_DEVICE_IO, n_s)
+        ck = smp.stop()
+        ok_s2, _ = tally(dd)
+        sustained = dict(seconds=ms_s / 1e3, steps=n_s, value=allsum(ok_s2) * TBS * n_s / (ms_s / 1e3) / 1e9, unit=UNIT, ms_per_step=ms_s / n_s,
+                         sm_mhz_median=ck["sm_mhz"], power_w_max=ck["power_w_max"], reasons=ck["reasons"])
 
     # ---- transmit side: the same transport blocks through CRC + segmentation + turbo encoding + rate matching
     #      on the device (fec_cuda_encode_tbs, device-resident payloads and packed output), checked against the oracle ----
@@ -618,7 +733,11 @@ def main():
                 hbm=dict(bound="hbm", algorithmic_bytes_per_step=hbm_bytes, achieved=hbm_bytes / (ms / args.steps / 1e3) / 1e9,
                          peak=pk["hbm_gbs"], unit="GB/s", frac=hbm_bytes / (ms / args.steps / 1e3) / 1e9 / pk["hbm_gbs"],
                          peak_source=pk["src"],
-                         rate_dematch_kernel_gbs=B * C_CB * (2 * (NBITS // C_CB) + 2 * (3 * K_CB + 12) + 2 * (3 * K_CB + 12)) / (rm_ms / 1e3) / 1e9))
+                         # the rate de-matcher alone, new data: E LLRs in, the slot (3*SS+16 int16, SS = P*Lp) written once
+                         rate_dematch_kernel=dict(ms_per_launch=rm_ms, bytes_per_cb=2 * (NBITS // C_CB) + 2 * (3 * P_CB * ((K_CB // P_CB + 7) // 8 * 8) + 16),
+                                                  achieved=B * C_CB * (2 * (NBITS // C_CB) + 2 * (3 * P_CB * ((K_CB // P_CB + 7) // 8 * 8) + 16)) / (rm_ms / 1e3) / 1e9,
+                                                  unit="GB/s", peak=pk["hbm_gbs"],
+                                                  frac=B * C_CB * (2 * (NBITS // C_CB) + 2 * (3 * P_CB * ((K_CB // P_CB + 7) // 8 * 8) + 16)) / (rm_ms / 1e3) / 1e9 / pk["hbm_gbs"])))
 
     cpu, parity = None, None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -647,7 +766,7 @@ def main():
                     e2e=dict(value=e2e_val, unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h, ms_per_step=ms_e / args.steps,
                              sync_ms_per_step=ms_e_sync / args.steps),
                     sync_ms_per_step=ms_sync / args.steps,
-                    gpu_launches=launches, clocks=clocks, roofline=roof, worst_case_8_halfits=worst, frontend_symbols=front, transmit_side=tx, llr_8bit=llr8, single_tb_latency=lat, cpu_baseline=cpu, parity_in_bench=parity)
+                    gpu_launches=launches, clocks=clocks, roofline=roof, worst_case_8_halfits=worst, frontend_symbols=front, ulsch_config5=ulsch5, harq_config3=harq, sustained=sustained, transmit_side=tx, llr_8bit=llr8, single_tb_latency=lat, cpu_baseline=cpu, parity_in_bench=parity)
         print(json.dumps(line), flush=True)
     fec.close()
     if world > 1:
