@@ -123,6 +123,41 @@ def fnv1a_rows(a):
     return h.astype(np.uint32)
 
 
+def bind_to_gpu_cpus(index):
+    """sched_setaffinity to the CPUs NVML reports as local to GPU `index` (nvmlDeviceGetCpuAffinity); returns what was done"""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = {64 * w + b for w, v in enumerate(words) for b in range(64) if (int(v) >> b) & 1}
+        allowed = os.sched_getaffinity(0)
+        use = sorted(cpus & allowed)
+        if not use:
+            return dict(bound=False, why="no NVML-local CPU in the allowed set", allowed=len(allowed))
+        os.sched_setaffinity(0, use)
+        return dict(bound=True, cpus=f"{use[0]}-{use[-1]}", n_cpus=len(use), allowed_before=len(allowed))
+    except Exception as e:                       # noqa: BLE001
+        return dict(bound=False, why=repr(e)[:120])
+
+
+def h2d_link_peak(torch, device, barrier, mb=256, reps=8):
+    """what the host delivers to THIS GPU while every rank does the same: pinned 256 MB buffers, cudaMemcpyAsync H2D back to back
+    (tools/h2d_peak.cu is the standalone version). GB/s; the denominator of the end-to-end figures."""
+    h = torch.empty(mb << 20, dtype=torch.uint8, pin_memory=True)
+    d = torch.empty(mb << 20, dtype=torch.uint8, device=device)
+    d.copy_(h, non_blocking=True)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        d.copy_(h, non_blocking=True)
+    e1.record()
+    e1.synchronize()
+    barrier()
+    return (mb << 20) * reps / (e0.elapsed_time(e1) / 1e3) / 1e9
+
+
 def cpu_cores():
     try:
         return len(os.sched_getaffinity(0))
@@ -209,11 +244,12 @@ def main():
     ap.add_argument("--batch", type=int, default=1184, help="transport blocks per GPU per step (default 8 per SM)")
     ap.add_argument("--sigma", type=float, default=0.45, help="AWGN std of the synthetic LLRs (0.45 = operating point)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-bind", action="store_true", help="do not bind the rank to the CPUs local to its GPU")
     ap.add_argument("--no-worst-case", action="store_true")
     ap.add_argument("--no-uplink", action="store_true", help="skip the 64-cell PUSCH leg (BASELINE configs[4])")
     ap.add_argument("--ul-subframes", type=int, default=37, help="subframes per cell and step of the 64-cell PUSCH leg (64 x 37 = 2368 TBs)")
     ap.add_argument("--no-harq", action="store_true", help="skip the HARQ leg (BASELINE configs[2])")
-    ap.add_argument("--sigma-harq", type=float, default=0.50, help="AWGN std of the HARQ leg (rv 0 mostly fails)")
+    ap.add_argument("--sigma-harq", type=float, default=0.47, help="AWGN std of the HARQ leg (rv 0 mostly fails)")
     ap.add_argument("--sustain", type=float, default=2.0, help="seconds of the sustained leg (0 = skip)")
     ap.add_argument("--no-llr8", action="store_true", help="skip the 8-bit LLR leg")
     ap.add_argument("--sigma8", type=float, default=0.30, help="AWGN std of the 8-bit LLR leg")
@@ -239,6 +275,9 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     pkg = importlib.import_module("empower-srslte_b200")
     shard = importlib.import_module("empower-srslte_b200.shard")
+    # run this rank (and first-touch its pinned staging) on the CPUs next to its GPU: with 8 ranks pulling 50 GB/s each out of
+    # host memory the NUMA placement of the pinned buffers is part of the end-to-end figure
+    affinity = bind_to_gpu_cpus(local_rank) if not args.no_bind else None
     fec = pkg.FecCuda(local_rank, max_tbs=args.batch)
     B = args.batch
 
@@ -343,6 +382,9 @@ def main():
                         np.array([hd[i].avg_its for i in range(n_par)], np.uint32),
                         fnv1a_rows(h_out.a[:n_par, :TBS // 8 + 3])], axis=1)
     e2e_val = allsum(ok_e) * TBS * args.steps / (ms_e / 1e3) / 1e9
+    link = h2d_link_peak(torch, f"cuda:{local_rank}", barrier)
+    link_min = -shard.reduce_job(dist if world > 1 else None, f"cuda:{local_rank}", -link)[0]      # slowest rank's link (MAX of the negated rates)
+    link_sum = allsum(link)
     h2d = B * NBITS * 2 + B * C_CB * (32 + 48) + B * 520
     d2h = B * (((TBS // 8 + 3 + 768 + 15) // 16) * 16) + B * C_CB * 8 + B * 4
 
@@ -409,7 +451,8 @@ def main():
                      sigma_sym=args.sigma_sym, value=allsum(ok_s) * TBS * args.steps / (ms_sd / 1e3) / 1e9, unit=UNIT,
                      ms_per_step=ms_sd / args.steps, tb_ok_frac=allsum(ok_s) / (world * B), halfits_per_cb=allsum(its_s) / (world * B * C_CB),
                      e2e=dict(value=allsum(ok_sh) * TBS * args.steps / (ms_sh / 1e3) / 1e9, unit=UNIT, ms_per_step=ms_sh / args.steps,
-                              h2d_bytes_per_step=B * nre * 8 + B * C_CB * (32 + 48) + B * (520 + 80), d2h_bytes_per_step=d2h),
+                              h2d_bytes_per_step=B * nre * 8 + B * C_CB * (32 + 48) + B * (520 + 80), d2h_bytes_per_step=d2h,
+                              frac_of_h2d_link=(B * nre * 8 + B * C_CB * (32 + 48) + B * (520 + 80)) / (ms_sh / args.steps / 1e3) / 1e9 / link_min),
                      code_blocks_by_kernel=dict(total=B * C_CB, certificate_variant=path_s[0], exact=path_s[1]),
                      serial_phases_ms=dict(frontend=fe_ms, rate_dematch=ph_s[0], turbo_decode=ph_s[1], tb_assemble_crc24a=ph_s[2]),
                      frontend_kernel=dict(ms_per_launch=fe_ms, algorithmic_bytes=fe_bytes, achieved=fe_bytes / (fe_ms / 1e3) / 1e9,
@@ -670,7 +713,8 @@ def main():
                     halfits_per_cb=allsum(its8) / (world * B * C_CB),
                     phases_ms=dict(rate_dematch=sum(p[0] for p in ph8) / 3, turbo_decode=sum(p[1] for p in ph8) / 3, tb_assemble_crc24a=sum(p[2] for p in ph8) / 3),
                     e2e=dict(value=allsum(ok8e) * TBS * n8 / (ms8e / 1e3) / 1e9, unit=UNIT, ms_per_step=ms8e / n8, sync_ms_per_step=ms8es / n8,
-                             h2d_bytes_per_step=B * NBITS + B * C_CB * (32 + 48) + B * 520),
+                             h2d_bytes_per_step=B * NBITS + B * C_CB * (32 + 48) + B * 520,
+                             frac_of_h2d_link=(B * NBITS + B * C_CB * (32 + 48) + B * 520) / (ms8e / n8 / 1e3) / 1e9 / link_min),
                     kernel="fec_tdec_win8p_kernel<32,true>: two sub-blocks per thread in u16x2 lanes (VIADDMNMX.S16x2.RELU = saturating int8 add), beta checkpoints in tensor memory (profiles/r1o_win8p_kernel_ncu.txt)")
         f8.close()
 
@@ -764,7 +808,11 @@ def main():
                                 l2="inputs larger than L2: %.0f MB LLRs + %.0f MB soft buffers per step" % (B * NBITS * 2 / 1e6, B * C_CB * 18464 * 2 / 1e6)),
                     cbs_per_s=cbs_per_s, tb_ok_frac=ok_all / (world * B), halfits_per_cb=its_all / (world * B * C_CB),
                     e2e=dict(value=e2e_val, unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h, ms_per_step=ms_e / args.steps,
-                             sync_ms_per_step=ms_e_sync / args.steps),
+                             sync_ms_per_step=ms_e_sync / args.steps,
+                             # the ingest is link-bound by construction: the same ranks copying pinned 256 MB buffers at the same time
+                             h2d_link=dict(gbs_slowest_rank=link_min, gbs_all_ranks=link_sum, how="pinned 256 MB x 8 cudaMemcpyAsync per rank, all ranks at once (tools/h2d_peak.cu standalone)",
+                                           achieved_gbs_per_rank=h2d / (ms_e / args.steps / 1e3) / 1e9, frac=h2d / (ms_e / args.steps / 1e3) / 1e9 / link_min),
+                             cpu_binding=affinity),
                     sync_ms_per_step=ms_sync / args.steps,
                     gpu_launches=launches, clocks=clocks, roofline=roof, worst_case_8_halfits=worst, frontend_symbols=front, ulsch_config5=ulsch5, harq_config3=harq, sustained=sustained, transmit_side=tx, llr_8bit=llr8, single_tb_latency=lat, cpu_baseline=cpu, parity_in_bench=parity)
         print(json.dumps(line), flush=True)
