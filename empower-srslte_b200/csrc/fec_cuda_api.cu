@@ -22,6 +22,7 @@ typedef struct {
   fec_geom_t g;
   uint32_t  *d_step;
   uint16_t  *d_rank;
+  uint16_t  *d_ranki[4];      /* the rank table re-based to the start of each redundancy version (16-bit rate de-matcher), built on first use */
   uint32_t   off[4];
   uint32_t   slots;
   uint32_t  *d_pair_addr;     /* packed kernel: decoder-2 address words */
@@ -193,6 +194,7 @@ extern "C" int fec_cuda_create(fec_cuda_ctx_t **out, int device, uint32_t max_tb
     free(m);
   }
   { const char *fe = getenv("FEC_CUDA_FORCE_EXACT"); ctx->force_exact = fe && fe[0] == '1'; }
+  cudaStreamSynchronize(cudaStreamLegacy);       /* the table copies above are in place, not just staged */
   if (pipes_create(ctx)) { free(ctx); return FEC_CUDA_ENODEV; }
   if (cudaGetLastError() != cudaSuccess) { free(ctx); return FEC_CUDA_ENODEV; }
   *out = ctx;
@@ -208,6 +210,7 @@ extern "C" void fec_cuda_destroy(fec_cuda_ctx_t *ctx)
     ktab_t *kt = i < FEC_NOF_K ? &ctx->ktab[i] : i < 2 * FEC_NOF_K ? &ctx->ktab8[i - FEC_NOF_K] : &ctx->ktabm[i / FEC_NOF_K - 2][i % FEC_NOF_K];
     if (!kt->ready) continue;
     cudaFree(kt->d_step); cudaFree(kt->d_rank); cudaFree(kt->d_pair_addr); cudaFree(kt->d_txsrc);
+    for (int r = 0; r < 4; r++) cudaFree(kt->d_ranki[r]);
     cudaFree(kt->d_pair_crc[0]); cudaFree(kt->d_pair_crc[1]);
   }
   cudaFree(ctx->d_softmax); cudaFree(ctx->d_exact); cudaFree(ctx->d_econt); cudaFreeHost(ctx->h_queue);
@@ -327,9 +330,34 @@ static int ktab_get(fec_cuda_ctx_t *ctx, uint32_t K, ktab_t **out)
       free(pa); free(pc);
     }
     t->slots = t->g.P ? fec_win_pick_slots(&t->g, ctx->llr8 && t->g.P >= 16) : 0;
+    /* cudaMemcpy from pageable memory returns when the data is STAGED, not when it is in place, and the kernels that read
+     * these tables run on non-blocking streams, which the legacy stream does not order: wait for the DMA itself */
+    CU(cudaStreamSynchronize(cudaStreamLegacy));
     t->ready = 1;
   }
   *out = t;
+  return 0;
+}
+
+/* table the rate de-matcher gathers through for redundancy version rv: in 8-bit mode the rank table itself (its kernel
+ * rotates while staging), else the table re-based to the first LLR of that rv (bulk-copy staging, fec_rm_rx_kernel) */
+static int ktab_rank(fec_cuda_ctx_t *ctx, ktab_t *t, uint32_t rv, const uint16_t **out)
+{
+  if (ctx->llr8) { *out = t->d_rank; return 0; }
+  if (!t->d_ranki[rv]) {
+    const size_t n = 3 * (size_t)t->g.SS + 16;
+    uint16_t *rank = (uint16_t *)malloc(n * 2), *ri = (uint16_t *)malloc(n * 2);
+    uint32_t off[4];
+    if (!rank || !ri) { free(rank); free(ri); return fail(ctx, FEC_CUDA_ERROR, "out of host memory"); }
+    fec_gen_rm_rank(&t->g, rank, off);
+    fec_rm_rank_rebase(&t->g, rank, off[rv], ri);
+    cudaError_t e = cudaMalloc(&t->d_ranki[rv], n * 2);
+    if (e == cudaSuccess) e = cudaMemcpy(t->d_ranki[rv], ri, n * 2, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(cudaStreamLegacy);      /* in place before a non-blocking stream reads it (see ktab_get) */
+    free(rank); free(ri);
+    if (e != cudaSuccess) { cudaFree(t->d_ranki[rv]); t->d_ranki[rv] = NULL; return fail(ctx, FEC_CUDA_ENODEV, "rank table: %s", cudaGetErrorString(e)); }
+  }
+  *out = t->d_ranki[rv];
   return 0;
 }
 
@@ -734,18 +762,19 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
     td->C = C; td->tbs = t->tbs; td->all_ok = 1; td->ret = (int32_t *)pp->st_ret.d + itb;
     const uint32_t Gp = t->nof_e_bits / t->Qm, gamma = Gp % C, n_e = t->Qm * (Gp / C);
     ktab_t *kts[2] = {NULL, NULL};
+    const uint16_t *rks[2] = {NULL, NULL};
     for (uint32_t cb = 0; cb < C; cb++) {
       const int which = cb < C1 ? 0 : 1;
       const uint32_t K = which ? p->seg[3] : p->seg[2];
       td->K[cb] = K; td->rlen[cb] = C == 1 ? K : K - 24; td->cache[cb] = cache0 + (size_t)cb * CB_BYTES;
       if (crc[cb]) { td->st_idx[cb] = -1; td->cb_bytes[cb] = td->cache[cb]; continue; }
-      if (!kts[which] && ktab_get(ctx, K, &kts[which])) return FEC_CUDA_EINVAL;
+      if (!kts[which] && (ktab_get(ctx, K, &kts[which]) || ktab_rank(ctx, kts[which], t->rv, &rks[which]))) return FEC_CUDA_EINVAL;
       ktab_t *kt = kts[which];
       uint32_t rp = cb * n_e, E = n_e;
       if (cb > C - gamma) { E = n_e + t->Qm; rp = (C - gamma) * n_e + (cb - (C - gamma)) * E; }   /* sch.c:339 off-by-one kept */
       const uint32_t slot = grp_off[kt->g.idx] + grp_fill[kt->g.idx]++;
       FecRmDesc *r = &rmd[slot];
-      r->e = (const int16_t *)(e_dev + (size_t)rp * esz); r->soft = soft0 + (size_t)cb * FEC_CUDA_SOFT_SLOT; r->rank = kt->d_rank;
+      r->e = (const int16_t *)(e_dev + (size_t)rp * esz); r->soft = soft0 + (size_t)cb * FEC_CUDA_SOFT_SLOT; r->rank = rks[which];
       r->E = E; r->N = 3 * K + 12; r->off = kt->off[t->rv]; r->n_out = 3 * kt->g.SS + 16; r->new_data = t->new_data ? 1 : 0; r->slot = slot;
       if (r->n_out > max_n_out) max_n_out = r->n_out;
       FecCbDesc *d = &cbd[slot];
@@ -1220,7 +1249,8 @@ extern "C" int fec_cuda_encode_tbs(fec_cuda_ctx_t *ctx, fec_cuda_txtb_t *tbs, ui
           const size_t N = 3 * (size_t)K + 12;
           uint16_t *src = (uint16_t *)malloc(N * 2);
           fec_gen_rm_txsrc(&kt->g, 32 * FEC_TX_W, src);
-          if (cudaMalloc(&kt->d_txsrc, N * 2) != cudaSuccess || cudaMemcpy(kt->d_txsrc, src, N * 2, cudaMemcpyHostToDevice) != cudaSuccess) rc = FEC_CUDA_ENODEV;
+          if (cudaMalloc(&kt->d_txsrc, N * 2) != cudaSuccess || cudaMemcpy(kt->d_txsrc, src, N * 2, cudaMemcpyHostToDevice) != cudaSuccess ||
+              cudaStreamSynchronize(cudaStreamLegacy) != cudaSuccess) rc = FEC_CUDA_ENODEV;
           free(src);
           if (rc) break;
         }
@@ -1268,7 +1298,8 @@ extern "C" int fec_cuda_rm_rx(fec_cuda_ctx_t *ctx, const int16_t *in, uint32_t E
   if (!ctx || !in || !soft || rv > 3 || fec_k_size(cb_idx) < 0) return FEC_CUDA_EINVAL;   /* rm_turbo.c:395,426-429 */
   cudaSetDevice(ctx->device);
   ktab_t *kt;
-  if (ktab_get(ctx, (uint32_t)fec_k_size(cb_idx), &kt)) return FEC_CUDA_EINVAL;
+  const uint16_t *rk;
+  if (ktab_get(ctx, (uint32_t)fec_k_size(cb_idx), &kt) || ktab_rank(ctx, kt, rv, &rk)) return FEC_CUDA_EINVAL;
   void *plan = NULL;
   if (stage_reserve(ctx, &ctx->st_e, ((size_t)E + 8) * 2) || stage_reserve(ctx, &ctx->st_rmd, sizeof(FecRmDesc)) ||
       stage_reserve(ctx, &ctx->st_data, 18600 * 2) ||
@@ -1284,7 +1315,7 @@ extern "C" int fec_cuda_rm_rx(fec_cuda_ctx_t *ctx, const int16_t *in, uint32_t E
   if (ctx->llr8) for (size_t i = 0; i < next; i++) ((int16_t *)ctx->st_data.h)[i] = ((const int8_t *)soft)[i];
   else memcpy(ctx->st_data.h, soft, next * 2);
   FecRmDesc *r = (FecRmDesc *)ctx->st_rmd.h;
-  r->e = (const int16_t *)ctx->st_e.d; r->soft = ctx->d_tmpsoft; r->rank = kt->d_rank; r->E = E; r->N = 3 * kt->g.K + 12;
+  r->e = (const int16_t *)ctx->st_e.d; r->soft = ctx->d_tmpsoft; r->rank = rk; r->E = E; r->N = 3 * kt->g.K + 12;
   r->off = kt->off[rv]; r->n_out = 3 * kt->g.SS + 16; r->new_data = 0; r->slot = 0;
   cudaStream_t st = ctx->stream;
   /* the caller's soft buffer lives in host memory in the reference layout: bring it to the device layout, combine

@@ -1032,71 +1032,63 @@ __device__ __forceinline__ uint32_t rm_lds_u16(uint32_t addr)
   return r;
 }
 
+/* Phase 1 (staging) by the bulk-copy engine: the tile is e[] IN THE ORDER RECEIVED (entry i = e[i], entries E..N zero; the per-rv
+ * table d.rank maps every soft position to 2i), so the whole slice arrives with ONE cp.async.bulk (UBLKCP) signalled on an
+ * mbarrier while the threads zero the tail: no LDG / STS instruction is spent on staging. Bulk copies want 16-byte aligned
+ * addresses and sizes: the tile starts (e & 15) bytes into shared memory so that source and destination are congruent, the
+ * 16-byte aligned interior goes by bulk copy and the ragged head / tail (< 8 LLRs each) by plain loads. */
 __global__ void __launch_bounds__(FEC_RM_THREADS) fec_rm_rx_kernel(const FecRmDesc *descs, uint32_t *soft_max)
 {
-  extern __shared__ __align__(16) int16_t rm_tile[];
+  extern __shared__ __align__(16) unsigned char rm_smem[];
+  __shared__ __align__(8) unsigned long long rm_mbar;
   const FecRmDesc d = descs[blockIdx.x];
   const int tid = threadIdx.x;
+  const size_t ea = reinterpret_cast<size_t>(d.e);
+  const uint32_t delta = (uint32_t)(ea & 15);
+  int16_t *rm_tile = reinterpret_cast<int16_t *>(rm_smem + delta);
+  const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(rm_smem), mb = (uint32_t)__cvta_generic_to_shared(&rm_mbar);
   if (d.E <= d.N) {
-    /* the common case (no repetition): a rotated copy. Entry i lands at p = i + off (mod N). LLR pairs are read as
-     * 32-bit words when the slice is 4-byte aligned (it is for every even Qm), 8 independent loads in flight per thread */
-    const uint32_t wrap = d.N - d.off;                 /* entries i >= wrap land at p = i - wrap */
-    const bool al = ((reinterpret_cast<size_t>(d.e) & 3) == 0);
-    if (al) {
-      const uint32_t *e32 = reinterpret_cast<const uint32_t *>(d.e);
-      const uint32_t npair = d.E >> 1;
-      for (uint32_t q0 = tid; q0 < npair; q0 += 8 * FEC_RM_THREADS) {
-        uint32_t v[8];
-#pragma unroll
-        for (int u = 0; u < 8; u++) { const uint32_t q = q0 + u * FEC_RM_THREADS; v[u] = q < npair ? __ldg(e32 + q) : 0u; }
-#pragma unroll
-        for (int u = 0; u < 8; u++) {
-          const uint32_t q = q0 + u * FEC_RM_THREADS, i = 2 * q;
-          if (q < npair) {
-            const uint32_t p0 = i < wrap ? i + d.off : i - wrap, p1 = i + 1 < wrap ? i + 1 + d.off : i + 1 - wrap;
-            if (p1 == p0 + 1 && !(p0 & 1)) *reinterpret_cast<uint32_t *>(rm_tile + p0) = v[u];
-            else { rm_tile[p0] = (int16_t)(v[u] & 0xFFFFu); rm_tile[p1] = (int16_t)(v[u] >> 16); }
-          }
-        }
-      }
-      if ((d.E & 1) && tid == 0) { const uint32_t i = d.E - 1; rm_tile[i < wrap ? i + d.off : i - wrap] = __ldg(d.e + i); }
-    } else {
-      for (uint32_t i0 = tid; i0 < d.E; i0 += 8 * FEC_RM_THREADS) {
-        int16_t v[8];
-#pragma unroll
-        for (int u = 0; u < 8; u++) { const uint32_t i = i0 + u * FEC_RM_THREADS; v[u] = i < d.E ? __ldg(d.e + i) : (int16_t)0; }
-#pragma unroll
-        for (int u = 0; u < 8; u++) { const uint32_t i = i0 + u * FEC_RM_THREADS; if (i < d.E) rm_tile[i < wrap ? i + d.off : i - wrap] = v[u]; }
+    /* the common case (no repetition) */
+    const size_t a0 = (ea + 15) & ~(size_t)15, a1 = (ea + 2 * (size_t)d.E) & ~(size_t)15;
+    const bool bulk = a1 > a0;
+    const uint32_t nb = bulk ? (uint32_t)(a1 - a0) : 0u;
+    if (tid == 0) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(mb));
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      if (bulk) {
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(mb), "r"(nb) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     :: "r"(sbase + delta + (uint32_t)(a0 - ea)), "l"(a0), "r"(nb), "r"(mb) : "memory");
       }
     }
-    /* entries never transmitted: p in [E + off, N + off) mod N, one or two contiguous runs, zeroed 16 bytes at a time */
+    /* ragged head and tail of the slice */
+    const uint32_t h = bulk ? (uint32_t)(a0 - ea) >> 1 : d.E, t0 = bulk ? (uint32_t)(a1 - ea) >> 1 : d.E;
+    if ((uint32_t)tid < h) rm_tile[tid] = __ldg(d.e + tid);
+    if (t0 + tid < d.E) rm_tile[t0 + tid] = __ldg(d.e + t0 + tid);
+    /* entries never transmitted, E .. N (entry N is what the table's "no coded bit here" offsets point at): zeroed 16 bytes at
+     * a time between a scalar head and tail */
     {
-      const uint32_t a0 = d.E + d.off;                 /* first untransmitted p, before the wrap */
-      uint32_t lo[2], hi[2];
-      if (a0 >= d.N) { lo[0] = a0 - d.N; hi[0] = d.off; lo[1] = hi[1] = 0; }
-      else           { lo[0] = a0; hi[0] = d.N; lo[1] = 0; hi[1] = d.off; }
-#pragma unroll
-      for (int r = 0; r < 2; r++) {
-        const uint32_t l8 = (lo[r] + 7) & ~7u, h8 = hi[r] & ~7u;
-        if (l8 >= h8) { for (uint32_t p = lo[r] + tid; p < hi[r]; p += FEC_RM_THREADS) rm_tile[p] = 0; }
-        else {
-          for (uint32_t p = lo[r] + tid; p < l8; p += FEC_RM_THREADS) rm_tile[p] = 0;
-          for (uint32_t p = l8 + 8 * tid; p < h8; p += 8 * FEC_RM_THREADS) *reinterpret_cast<uint4 *>(rm_tile + p) = make_uint4(0, 0, 0, 0);
-          for (uint32_t p = h8 + tid; p < hi[r]; p += FEC_RM_THREADS) rm_tile[p] = 0;
-        }
-      }
+      const uint32_t lo = d.E, hi = d.N + 1;
+      const uint32_t l8 = min(hi, lo + ((16u - ((delta + 2u * lo) & 15u)) & 15u) / 2u), h8 = l8 + ((hi - l8) & ~7u);
+      for (uint32_t p = lo + tid; p < l8; p += FEC_RM_THREADS) rm_tile[p] = 0;
+      for (uint32_t p = l8 + 8 * tid; p < h8; p += 8 * FEC_RM_THREADS) *reinterpret_cast<uint4 *>(rm_tile + p) = make_uint4(0, 0, 0, 0);
+      for (uint32_t p = h8 + tid; p < hi; p += FEC_RM_THREADS) rm_tile[p] = 0;
+    }
+    __syncthreads();                                   /* the barrier object is initialised for everybody */
+    if (bulk) {
+      uint32_t ok = 0;
+      while (!ok)
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }" : "=r"(ok) : "r"(mb) : "memory");
     }
   } else {
     for (uint32_t i = tid; i < d.N; i += FEC_RM_THREADS) {
       int acc = 0;
       for (uint32_t j = i; j < d.E; j += d.N) acc += (int)__ldg(d.e + j);    /* repeats accumulate when E > 3K+12 */
-      uint32_t p = i + d.off;
-      if (p >= d.N) p -= d.N;
-      rm_tile[p] = (int16_t)acc;
+      rm_tile[i] = (int16_t)acc;
     }
+    if (tid == 0) rm_tile[d.N] = 0;
+    __syncthreads();
   }
-  if (tid == 0) rm_tile[d.N] = 0;                      /* the entry the table's "no coded bit here" offsets point at */
-  __syncthreads();
   /* the rank table holds byte offsets into the tile: per soft value one 16-bit shared-memory load, per pair one PRMT, one
    * packed wrapping add (rm_turbo.c:411-420 adds int16 with wrap-around) when combining, and a packed min / max for max|soft| */
   const uint4 *rank4 = reinterpret_cast<const uint4 *>(d.rank);
@@ -1216,7 +1208,7 @@ cudaError_t fec_launch_rm(const FecRmDesc *descs, uint32_t *soft_max, uint32_t n
     fec_rm_rx8_kernel<<<n, FEC_RM_THREADS, (size_t)max_n_out * 2, st>>>(descs, soft_max);
     return cudaGetLastError();
   }
-  fec_rm_rx_kernel<<<n, FEC_RM_THREADS, (size_t)max_n_out * 2, st>>>(descs, soft_max);   /* N = 3K+12 <= n_out */
+  fec_rm_rx_kernel<<<n, FEC_RM_THREADS, (size_t)max_n_out * 2 + 32, st>>>(descs, soft_max);   /* N + 1 entries + up to 14 bytes of shift */
   return cudaGetLastError();
 }
 

@@ -23,7 +23,7 @@
 
 #define NA_ALIGN(x)        (((x) + 255u) & ~(size_t)255u)
 #define NA_OFF_IN          0
-#define NA_OFF_REF         (NA_OFF_IN + NA_ALIGN((size_t)FEC_CUDA_NOALLOC_MAX_E * 2))
+#define NA_OFF_REF         (NA_OFF_IN + NA_ALIGN((size_t)FEC_CUDA_NOALLOC_MAX_E * 2 + 16))
 #define NA_OFF_SOFT        (NA_OFF_REF + NA_ALIGN((size_t)18600 * 2))
 #define NA_OFF_RANK        (NA_OFF_SOFT + NA_ALIGN((size_t)FEC_CUDA_SOFT_SLOT * 2))
 #define NA_OFF_DESC        (NA_OFF_RANK + NA_ALIGN((size_t)FEC_CUDA_SOFT_SLOT * 2))
@@ -35,10 +35,10 @@ static __device__ __align__(256) unsigned char fec_noalloc_scratch[NA_SCRATCH_BY
 
 static pthread_mutex_t g_na_mu = PTHREAD_MUTEX_INITIALIZER;
 static unsigned char  *g_na_ptr[NA_MAX_DEV];     /* device address of the array on each device, looked up on first use */
-static int             g_na_K[NA_MAX_DEV];       /* code-block size whose rank table the array holds */
+static int             g_na_K[NA_MAX_DEV];       /* code-block size and redundancy version (K * 4 + rv) whose table the array holds */
 static uint32_t        g_na_off[NA_MAX_DEV][4];
 /* host-side staging of the rank table and the descriptor (plain static memory, copied with cudaMemcpyAsync) */
-static uint16_t        g_na_rank[FEC_CUDA_SOFT_SLOT];
+static uint16_t        g_na_rank[FEC_CUDA_SOFT_SLOT], g_na_rank0[FEC_CUDA_SOFT_SLOT];
 static FecRmDesc       g_na_desc;
 
 static int na_fail(int code, const char *what, cudaError_t e)
@@ -80,12 +80,13 @@ extern "C" int fec_cuda_rm_rx_noalloc(int device, const int16_t *in, uint32_t E,
   uint32_t *d_max = (uint32_t *)(sc + NA_OFF_MAX);
   cudaStream_t st = cudaStreamPerThread;
 
-  if (g_na_K[device] != g.K) {
+  if (g_na_K[device] != g.K * 4 + (int)rv) {
     g_na_K[device] = 0;
-    fec_gen_rm_rank(&g, g_na_rank, g_na_off[device]);
+    fec_gen_rm_rank(&g, g_na_rank0, g_na_off[device]);
+    fec_rm_rank_rebase(&g, g_na_rank0, g_na_off[device][rv], g_na_rank);        /* the table of this rv, as fec_cuda_rm_rx uses it */
     NA(cudaMemcpyAsync(d_rank, g_na_rank, (3 * (size_t)g.SS + 16) * 2, cudaMemcpyHostToDevice, st));
     NA(cudaStreamSynchronize(st));       /* g_na_rank is reusable, the table is in place */
-    g_na_K[device] = g.K;
+    g_na_K[device] = g.K * 4 + (int)rv;
   }
   memset(&g_na_desc, 0, sizeof(g_na_desc));
   g_na_desc.e = d_in; g_na_desc.soft = d_soft; g_na_desc.rank = d_rank; g_na_desc.E = E; g_na_desc.N = 3 * (uint32_t)g.K + 12;

@@ -166,6 +166,18 @@ void fec_gen_rm_rank(const fec_geom_t *g, uint16_t *rank, uint32_t off[4])
   }
 }
 
+/* The same table re-based to the start of one redundancy version: entry = 2 x (index i of the received LLR e[i] that lands on
+ * this soft position, i in [0, 3K+12) for the first pass through the circular buffer), pad entries stay at 2 x (3K+12).
+ * With it the rate de-matcher's tile is simply e[] in the order received (one bulk copy) followed by zeros. */
+void fec_rm_rank_rebase(const fec_geom_t *g, const uint16_t *rank, uint32_t off, uint16_t *out)
+{
+  const uint32_t N = 3 * (uint32_t)g->K + 12;
+  for (int i = 0; i < 3 * g->SS + 16; i++) {
+    const uint32_t c = rank[i] / 2u;
+    out[i] = (uint16_t)(c >= N ? 2 * N : 2 * ((c + N - off) % N));
+  }
+}
+
 void fec_gen_rm_txsrc(const fec_geom_t *g, uint32_t stream_bits, uint16_t *src)
 {
   const int D = g->K + 4, R = (D - 1) / 32 + 1, KP = 32 * R, ND = KP - D, NCB = 3 * KP;

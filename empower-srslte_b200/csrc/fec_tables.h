@@ -58,6 +58,8 @@ void fec_gen_pair_crc_table(const fec_geom_t *g, uint32_t poly, uint32_t *tab);
 /* rate-matching rank table in device soft-buffer layout (3*SS+16 entries of 2 x rank, pad = 2 x (3K+12)) and the 4 rv
  * start ranks: transmitted index of soft position o for rv is (rank[o] - off[rv]) mod (3K+12). */
 void fec_gen_rm_rank(const fec_geom_t *g, uint16_t *rank, uint32_t off[4]);
+/* rank table re-based to the start rank `off` of one redundancy version: 2 x index of the received LLR, pad = 2 x (3K+12) */
+void fec_rm_rank_rebase(const fec_geom_t *g, const uint16_t *rank, uint32_t off, uint16_t *out);
 /* natural coded position t (0..3K+11) -> device soft-buffer offset, and -> reference soft-buffer offset */
 /* transmit side: NULL-free circular-buffer position (counted from w[0], as rank) -> stream * stream_bits + index in d_stream,
  * index < K + 4 (36.212 5.1.4.1.1-2); n = 3K + 12 entries */

@@ -297,15 +297,15 @@ def test_two_worker_threads_decode_concurrently(lib):
             tbs = case["tbs"]
             q = C.create_string_buffer(40)
             assert lib.srslte_softbuffer_rx_init(q, 100) == 0
-            for _ in range(reps):
+            for rep in range(reps):
                 lib.srslte_softbuffer_rx_reset_tbs(q, tbs)
-                for tx in case["tx"]:
+                for txi, tx in enumerate(case["tx"]):
                     data, noi = np.zeros(tbs // 8 + 3 + 768, np.uint8), C.c_uint32(0)
                     llr = np.ascontiguousarray(tx["llr"])
                     ret = fn(q, tbs, case["Qm"], tx["rv"], case["nbits"], P(llr), P(data), case["max_its"], C.byref(noi))
-                    assert ret == tx["ret"], (ret, tx["ret"])
+                    assert ret == tx["ret"], (fn.__name__, rep, txi, ret, tx["ret"])
                     if ret == 0:
-                        assert (data[: tbs // 8 + 3] == tx["data"][: tbs // 8 + 3]).all()
+                        assert (data[: tbs // 8 + 3] == tx["data"][: tbs // 8 + 3]).all(), (fn.__name__, rep, txi)
             lib.srslte_softbuffer_rx_free(q)
         except Exception as e:                       # noqa: BLE001
             errs.append(repr(e))
