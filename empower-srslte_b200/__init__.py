@@ -292,7 +292,7 @@ class FecCuda:
             raise RuntimeError(f"fec_cuda_last_frontend_ms: {rc}")
         return float(o.value)
 
-    def frontend(self, symbols, mod_bits, c_init, csi=None, nof_symb=0, ack_pos=(), ri_pos=(), nof_cqi_bits=0):
+    def frontend(self, symbols, mod_bits, c_init, csi=None, nof_symb=0, ack_pos=(), ri_pos=(), nof_cqi_bits=0, llr8=False):
         """symbols -> LLRs as decode_tb receives them (demodulation, descrambling, CSI weights / UL de-interleaver).
         symbols: float32 pairs (re, im). Returns (llr int16[nof_re*mod_bits], uci int16[nack+nri+ncqi])"""
         sym = np.ascontiguousarray(symbols, dtype=np.float32).reshape(-1)
@@ -312,7 +312,7 @@ class FecCuda:
         uci = np.zeros(ack.size + ri.size + nof_cqi_bits + 1, np.int16)
         d.ack_pos, d.ri_pos, d.nof_ack_pos, d.nof_ri_pos, d.nof_cqi_bits = ack.ctypes.data, ri.ctypes.data, ack.size, ri.size, nof_cqi_bits
         d.uci_out = uci.ctypes.data
-        out = np.zeros(n * mod_bits, np.int16)
+        out = np.zeros(n * mod_bits, np.int8 if llr8 else np.int16)      # llr8: the context is in 8-bit LLR mode (set_llr_8bit)
         rc = self.lib.fec_cuda_frontend(self.h, C.byref(d), out.ctypes.data_as(C.c_void_p))
         if rc:
             raise RuntimeError(f"fec_cuda_frontend: {rc} {self.error()}")

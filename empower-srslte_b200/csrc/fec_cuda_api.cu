@@ -640,7 +640,6 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
 {
   const int dev_io = (flags & FEC_CUDA_F_DEVICE_IO) != 0;
   const size_t esz = ctx->llr8 ? 1 : 2;        /* bytes per LLR of e_bits */
-  if (syms && ctx->llr8) return fail(ctx, FEC_CUDA_EINVAL, "the symbol front end produces int16 LLRs: not available in 8-bit LLR mode");
   if (pp->plan_cap < n) { free(pp->plan); pp->plan = (tbplan_t *)malloc(sizeof(tbplan_t) * n); pp->plan_cap = n; }
   tbplan_t *plan = pp->plan;
   memset(plan, 0, sizeof(tbplan_t) * n);
@@ -659,7 +658,7 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
     memset(t->cb_crc, 0, sizeof(t->cb_crc)); memset(t->cb_its, 0, sizeof(t->cb_its));
     const fec_cuda_sym_t *sy = syms ? &syms[i] : NULL;
     if ((!sy && !t->e_bits) || (!t->data && t->tbs) || t->rv > 3 || t->Qm == 0) continue;
-    if (sy && !fe_check(t, sy)) continue;
+    if (sy && (!fe_check(t, sy) || (ctx->llr8 && sy->nof_symb))) continue;     /* 8-bit LLR mode: the downlink front end only */
     if (fec_segm(t->tbs, p->seg)) continue;
     const int decode = !(t->tbs == 0 || p->seg[1] == 0);
     if (decode) {
@@ -677,7 +676,7 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
       p->nuci = sy->nof_ack_pos + sy->nof_ri_pos;
       p->uci_off = uci_total; uci_total += ((size_t)p->nuci + sy->nof_cqi_bits + 7) & ~(size_t)7;
       if (p->nuci + sy->nof_cqi_bits) any_uci = 1;
-      p->e_off = e_total; e_total += ((size_t)sy->nof_re * sy->mod_bits + 7) & ~(size_t)7;
+      p->e_off = e_total; e_total += ((size_t)sy->nof_re * sy->mod_bits + 15) & ~(size_t)15;    /* 16-byte lines also for int8 LLRs */
     }
     if (!decode) { t->ret = 0; continue; }
     uint8_t *crc = p->sb.crc;
@@ -699,7 +698,7 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
   size_t need[16] = { sizeof(FecCbDesc) * (ncb + 1), sizeof(FecRmDesc) * (ncb + 1), sizeof(FecTbDesc) * (ntb + 1), sizeof(FecCbStatus) * (ncb + 1),
                       sizeof(int32_t) * (ntb + 1), (size_t)(ncb + 1) * CB_BYTES, (size_t)(ncb + 1) * 4,
                       dev_io ? 0 : (syms ? sym_total : e_total * esz), dev_io ? 0 : data_total,
-                      /* front end */ sizeof(FecFeDesc) * nfe, syms ? e_total * 2 : 0, lst_total * 4, (dev_io || !syms) ? 0 : uci_total * 2, sizeof(float) * nfe, 0, 0 };
+                      /* front end */ sizeof(FecFeDesc) * nfe, syms ? e_total * esz : 0, lst_total * 4, (dev_io || !syms) ? 0 : uci_total * 2, sizeof(float) * nfe, 0, 0 };
   for (int i = 0; i < 16; i++) { if (need[i] > ctx->hw[i]) ctx->hw[i] = need[i]; need[i] = ctx->hw[i]; }
   if (stage_reserve(ctx, &pp->st_cbd, need[0]) || stage_reserve(ctx, &pp->st_rmd, need[1]) ||
       stage_reserve(ctx, &pp->st_tbd, need[2]) || stage_reserve(ctx, &pp->st_status, need[3]) ||
@@ -738,7 +737,7 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
       if (!p->sym_pinned) memcpy((char *)pp->st_e.h + p->sym_off, sy->symbols, (size_t)sy->nof_re * 8);
       if (sy->csi) memcpy((char *)pp->st_e.h + p->csi_off, sy->csi, (size_t)sy->nof_re * 4);
     }
-    f->e = pp->d_llr + p->e_off;
+    f->e = (int16_t *)((char *)pp->d_llr + p->e_off * esz);     /* int8 entries in 8-bit LLR mode */
     f->nof_re = sy->nof_re; f->mod = mod; f->c_init = sy->c_init & 0x7FFFFFFFu;
     f->cols = sy->nof_symb; f->rows = sy->nof_symb ? sy->nof_re / sy->nof_symb : 0;
     f->n_cqi = sy->nof_cqi_bits; f->nuci = p->nuci;
@@ -754,7 +753,7 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
     uint8_t *crc = p->sb.crc;
     int16_t *soft0 = p->sb.soft0;
     uint8_t *cache0 = p->sb.cache0;
-    const char *e_dev = syms ? (const char *)(pp->d_llr + p->e_off + syms[i].nof_cqi_bits)        /* g_bits + Q'_cqi*Qm, sch.c:963-973 */
+    const char *e_dev = syms ? (const char *)pp->d_llr + (p->e_off + syms[i].nof_cqi_bits) * esz   /* g_bits + Q'_cqi*Qm, sch.c:963-973 */
                              : dev_io ? (const char *)t->e_bits : (const char *)pp->st_e.d + p->e_off * esz;
     FecTbDesc *td = &tbd[itb];
     memset(td, 0, sizeof(*td));
@@ -864,8 +863,8 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
   CU(cudaEventRecord(pp->ev_fe, srm));
   if (nfe) {
     /* symbols -> LLRs in decode_tb order: soft demodulation, descrambling, CSI weights / UL channel de-interleaver */
-    CU(fec_launch_frontend((const FecFeDesc *)pp->st_fed.d, pp->d_csimax, ctx->d_x2masks, ctx->d_x1states, nfe, max_re, any_csi, any_uci, fe_kinds, srm));
-    ctx->launches += (fe_kinds == 3 ? 2 : 1) + (any_csi ? 1 : 0) + (any_uci ? 1 : 0);
+    CU(fec_launch_frontend((const FecFeDesc *)pp->st_fed.d, pp->d_csimax, ctx->d_x2masks, ctx->d_x1states, nfe, max_re, any_csi, any_uci, fe_kinds, srm, ctx->llr8));
+    ctx->launches += ctx->llr8 ? 1 + (any_csi ? 1 : 0) : (fe_kinds == 3 ? 2 : 1) + (any_csi ? 1 : 0) + (any_uci ? 1 : 0);
   }
   CU(cudaEventRecord(pp->ev[0], srm));
   if (ncb) { CU(fec_launch_rm((const FecRmDesc *)pp->st_rmd.d, pp->d_softmax, ncb, max_n_out, srm, ctx->llr8)); ctx->launches++; }
@@ -1350,12 +1349,13 @@ extern "C" int fec_cuda_frontend(fec_cuda_ctx_t *ctx, const fec_cuda_sym_t *sy, 
   if (!ctx || !sy || !llr_out) return FEC_CUDA_EINVAL;
   fec_cuda_tb_t none;
   memset(&none, 0, sizeof(none));
-  if (!fe_check(&none, sy)) return FEC_CUDA_EINVAL;
+  if (!fe_check(&none, sy) || (ctx->llr8 && sy->nof_symb)) return FEC_CUDA_EINVAL;       /* 8-bit LLR mode: downlink only */
+  const size_t esz = ctx->llr8 ? 1 : 2;               /* llr_out points to int8 LLRs in 8-bit mode */
   cudaSetDevice(ctx->device);
   const uint32_t mod = sy->mod_bits, nb = sy->nof_re * mod, nuci = sy->nof_ack_pos + sy->nof_ri_pos;
   const size_t symb = ((size_t)sy->nof_re * 8 + 15) & ~(size_t)15, csib = sy->csi ? (((size_t)sy->nof_re * 4 + 15) & ~(size_t)15) : 0;
   const size_t lstb = ((size_t)2 * nuci * 4 + 15) & ~(size_t)15, ucib = (((size_t)nuci + sy->nof_cqi_bits) * 2 + 15) & ~(size_t)15;
-  const size_t outb = ((size_t)nb * 2 + 15) & ~(size_t)15;
+  const size_t outb = ((size_t)nb * esz + 15) & ~(size_t)15;
   void *plan = NULL;
   /* one staging block: [symbols | csi | lists | descriptor] in, [LLRs | control-information LLRs | csi max] out */
   if (stage_reserve(ctx, &ctx->st_e, symb + csib + lstb + sizeof(FecFeDesc)) || stage_reserve(ctx, &ctx->st_data, outb + ucib + 16)) return FEC_CUDA_ENODEV;
@@ -1374,11 +1374,11 @@ extern "C" int fec_cuda_frontend(fec_cuda_ctx_t *ctx, const fec_cuda_sym_t *sy, 
   CUF(cudaMemcpyAsync(d, h, symb + csib + lstb + sizeof(FecFeDesc), cudaMemcpyHostToDevice, st));
   CUF(cudaMemsetAsync(od, 0, outb, st));       /* UL: the positions behind the last de-interleaved LLR are not written */
   CUF(fec_launch_frontend((const FecFeDesc *)(d + symb + csib + lstb), (float *)(od + outb + ucib), ctx->d_x2masks, ctx->d_x1states,
-                          1, sy->nof_re, sy->csi != NULL, f->uci_out != NULL, sy->nof_symb ? 2 : 1, st));
+                          1, sy->nof_re, sy->csi != NULL, f->uci_out != NULL, sy->nof_symb ? 2 : 1, st, ctx->llr8));
   ctx->launches += 1 + (sy->csi ? 1 : 0) + (f->uci_out ? 1 : 0);
   CUF(cudaMemcpyAsync(ctx->st_data.h, od, outb + ucib, cudaMemcpyDeviceToHost, st));
   CUF(cudaStreamSynchronize(st));
-  memcpy(llr_out, ctx->st_data.h, (size_t)nb * 2);
+  memcpy(llr_out, ctx->st_data.h, (size_t)nb * esz);
   if (f->uci_out) memcpy(sy->uci_out, (char *)ctx->st_data.h + outb, ((size_t)nuci + sy->nof_cqi_bits) * 2);
   return 0;
 }

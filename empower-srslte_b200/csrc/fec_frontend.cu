@@ -426,6 +426,116 @@ fec_fe_dl_kernel(const FecFeDesc *descs, const float *csi_max, const uint32_t *x
   }
 }
 
+/* ---- 8-bit LLR mode (q->llr_is_8bit, pdsch.c:795-813): srslte_demod_soft_demodulate_b (demod_soft.c:458-478: SSE bodies
+ * over 8 symbols — 16 values for QPSK — with two saturating packs, scalar tails with C conversions), srslte_scrambling_sb_offset
+ * (psignb: wrapping int8 negate) and the scalar int8 branch of csi_correction (pdsch.c:707-714). Downlink only. One byte per
+ * LLR leaves for HBM, so this is not the bandwidth-critical form of the kernel: one symbol per thread and pass, the LLR bytes
+ * staged in shared memory so that the stores are 16-byte lines. ---- */
+__device__ __forceinline__ int fe_wrap8(int v) { return (int)(signed char)v; }
+__device__ __forceinline__ int fe_abs8(int v) { return fe_wrap8(v < 0 ? -v : v); }        /* pabsb */
+__device__ __forceinline__ int fe_sat8(int v16) { return max(-128, min(127, v16)); }      /* packsswb on a packssdw result */
+__device__ __forceinline__ int fe_c8(double v)                                             /* cvttsd2si to 32 bits, low byte kept */
+{
+  if (!(v > -2147483649.0 && v < 2147483648.0)) return 0;
+  return (int)(signed char)__double2int_rz(v);
+}
+struct FeConst8 { float qpsk_scale; double sqrt2, off16, off64a, off64b; int ioff16, ioff64a, ioff64b; };
+
+template <int mod>
+__device__ __forceinline__ void fe_demod8(float re, float im, bool body, bool body_im, const FeConst8 &c, int *v)
+{
+  if (mod == 6) {
+    if (body) {
+      const int yr = fe_sat8(fe_sat16_rn(__fmul_rn(re, -40.0f))), yi = fe_sat8(fe_sat16_rn(__fmul_rn(im, -40.0f)));
+      const int ar = fe_wrap8(fe_abs8(yr) - c.ioff64a), ai = fe_wrap8(fe_abs8(yi) - c.ioff64a);
+      v[0] = yr; v[1] = yi; v[2] = ar; v[3] = ai;
+      v[4] = fe_wrap8(fe_abs8(ar) - c.ioff64b); v[5] = fe_wrap8(fe_abs8(ai) - c.ioff64b);
+    } else {
+      const int yr = fe_c8((double)__fmul_rn(40.0f, re)), yi = fe_c8((double)__fmul_rn(40.0f, im));
+      v[0] = fe_c8(-(double)yr); v[1] = fe_c8(-(double)yi);
+      v[2] = fe_c8((double)abs(yr) - c.off64a); v[3] = fe_c8((double)abs(yi) - c.off64a);
+      v[4] = fe_c8((double)abs(v[2]) - c.off64b); v[5] = fe_c8((double)abs(v[3]) - c.off64b);
+    }
+  } else if (mod == 4) {
+    if (body) {
+      const int yr = fe_sat8(fe_sat16_rn(__fmul_rn(re, -30.0f))), yi = fe_sat8(fe_sat16_rn(__fmul_rn(im, -30.0f)));
+      v[0] = yr; v[1] = yi;
+      v[2] = fe_wrap8(fe_abs8(yr) - c.ioff16); v[3] = fe_wrap8(fe_abs8(yi) - c.ioff16);
+    } else {
+      const int yr = fe_c8((double)__fmul_rn(30.0f, re)), yi = fe_c8((double)__fmul_rn(30.0f, im));
+      v[0] = fe_wrap8(-yr); v[1] = fe_wrap8(-yi);
+      v[2] = fe_c8((double)abs(yr) - c.off16); v[3] = fe_c8((double)abs(yi) - c.off16);
+    }
+  } else if (mod == 2) {
+    const float pr = __fmul_rn(re, c.qpsk_scale), pi = __fmul_rn(im, c.qpsk_scale);
+    v[0] = body ? fe_sat8(fe_sat16_rz(pr)) : fe_c8((double)pr);
+    v[1] = body_im ? fe_sat8(fe_sat16_rz(pi)) : fe_c8((double)pi);
+  } else {
+    const float s = __fmul_rn(-20.0f, __fadd_rn(re, im));
+    v[0] = fe_c8((double)s / c.sqrt2);
+  }
+}
+
+template <int MOD>
+__device__ __forceinline__ void fe_tile_dl8(const FecFeDesc &d, uint32_t s0, float cmax, const uint32_t *x2_masks,
+                                            const uint32_t *x1_states, const FeConst8 &kc, uint32_t *cw, signed char *tile)
+{
+  constexpr uint32_t mod = MOD;
+  const uint32_t nsym = min((uint32_t)FE_SEG, d.nof_re - s0);
+  const uint32_t nbits = nsym * mod, p0 = s0 * mod;
+  const uint32_t body_end = (mod == 2) ? 16 * ((2 * d.nof_re) / 16) : 8 * (d.nof_re / 8);     /* values (QPSK) / symbols */
+  {
+    const uint32_t nblk = (nbits + FE_BLK_BITS - 1) / FE_BLK_BITS;
+    if (threadIdx.x < nblk) {
+      uint32_t s1, s2;
+      fe_block_states(x2_masks, x1_states, p0 / FE_BLK_BITS + threadIdx.x, d.c_init, s1, s2);
+#pragma unroll
+      for (int w = 0; w < FE_BLK_BITS / 32; w++) cw[threadIdx.x * (FE_BLK_BITS / 32) + w] = fe_x1_next32(s1) ^ fe_x2_next32(s2);
+    }
+  }
+  __syncthreads();
+  for (uint32_t ls = threadIdx.x; ls < nsym; ls += FE_THREADS) {
+    const uint32_t sh = s0 + ls;
+    const float2 q = d.sym[sh];
+    const bool body = mod == 2 ? 2 * sh < body_end : sh < body_end;
+    const bool body_im = mod == 2 ? 2 * sh + 1 < body_end : body;
+    int v[6];
+    fe_demod8<MOD>(q.x, q.y, body, body_im, kc, v);
+    const float w = d.csi ? __fdiv_rn(d.csi[sh], cmax) : 1.f;
+#pragma unroll
+    for (uint32_t k = 0; k < mod; k++) {
+      const uint32_t b = ls * mod + k;
+      int val = v[k];
+      if ((cw[b >> 5] >> (b & 31)) & 1) val = fe_wrap8(-val);
+      if (d.csi) val = fe_c8((double)__fmul_rn((float)val, w));
+      tile[b] = (signed char)val;
+    }
+  }
+  __syncthreads();
+  /* tile -> HBM: p0 bytes is a multiple of 16 (p0 = 2048*mod*blockIdx.x) */
+  signed char *dst = reinterpret_cast<signed char *>(d.e) + p0;
+  const uint32_t n16 = nbits / 16;
+  for (uint32_t i = threadIdx.x; i < n16; i += FE_THREADS) reinterpret_cast<uint4 *>(dst)[i] = reinterpret_cast<const uint4 *>(tile)[i];
+  for (uint32_t i = n16 * 16 + threadIdx.x; i < nbits; i += FE_THREADS) dst[i] = tile[i];
+}
+
+__global__ void __launch_bounds__(FE_THREADS)
+fec_fe_dl8_kernel(const FecFeDesc *descs, const float *csi_max, const uint32_t *x2_masks, const uint32_t *x1_states, FeConst8 kc)
+{
+  const FecFeDesc d = descs[blockIdx.y];
+  const uint32_t s0 = blockIdx.x * FE_SEG;
+  if (d.cols || s0 >= d.nof_re) return;
+  __shared__ uint32_t cw[FE_SEG * 6 / 32 + 1];
+  __shared__ __align__(16) signed char tile[FE_SEG * 6];
+  const float cmax = d.csi ? csi_max[blockIdx.y] : 1.f;
+  switch (d.mod) {
+  case 6: fe_tile_dl8<6>(d, s0, cmax, x2_masks, x1_states, kc, cw, tile); break;
+  case 4: fe_tile_dl8<4>(d, s0, cmax, x2_masks, x1_states, kc, cw, tile); break;
+  case 2: fe_tile_dl8<2>(d, s0, cmax, x2_masks, x1_states, kc, cw, tile); break;
+  default: fe_tile_dl8<1>(d, s0, cmax, x2_masks, x1_states, kc, cw, tile); break;
+  }
+}
+
 __global__ void __launch_bounds__(FE_THREADS)
 fec_fe_ul_kernel(const FecFeDesc *descs, const uint32_t *x2_masks, const uint32_t *x1_states, FeConst kc)
 {
@@ -471,9 +581,21 @@ __global__ void __launch_bounds__(FE_THREADS) fec_fe_uci_kernel(const FecFeDesc 
 }
 
 cudaError_t fec_launch_frontend(const FecFeDesc *descs, float *csi_max, const uint32_t *x2_masks, const uint32_t *x1_states,
-                                uint32_t ntb, uint32_t max_re, int any_csi, int any_uci, int kinds, cudaStream_t st)
+                                uint32_t ntb, uint32_t max_re, int any_csi, int any_uci, int kinds, cudaStream_t st, int llr8)
 {
   if (!ntb || !max_re) return cudaSuccess;
+  if (llr8) {
+    /* 8-bit LLR mode: downlink only (the caller has refused uplink transport blocks) */
+    FeConst8 k8;
+    k8.qpsk_scale = (float)(-20 * sqrt(2.0));
+    k8.sqrt2 = sqrt(2.0);
+    k8.off16 = 2 * 30 / sqrt(10.0); k8.off64a = 4 * 40 / sqrt(42.0); k8.off64b = 2 * 40 / sqrt(42.0);
+    k8.ioff16 = (signed char)k8.off16; k8.ioff64a = (signed char)k8.off64a; k8.ioff64b = (signed char)k8.off64b;
+    if (any_csi) fec_fe_csimax_kernel<<<ntb, FE_THREADS, 0, st>>>(descs, csi_max);
+    dim3 g8((max_re + FE_SEG - 1) / FE_SEG, ntb);
+    fec_fe_dl8_kernel<<<g8, FE_THREADS, 0, st>>>(descs, csi_max, x2_masks, x1_states, k8);
+    return cudaGetLastError();
+  }
   FeConst kc;
   kc.qpsk_scale = (float)(-100 * sqrt(2.0));
   kc.sqrt2 = sqrt(2.0);

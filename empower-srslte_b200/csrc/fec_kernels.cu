@@ -1321,7 +1321,9 @@ __global__ void __launch_bounds__(256) fec_tb_assemble_kernel(const FecTbDesc *d
     const int fresh = d.st_idx[c] >= 0;
     const uint32_t nby = fresh ? d.K[c] / 8 : d.rlen[c] / 8, base = c * d.rlen[c] / 8;
     for (uint32_t i = tid; i < nby; i += blockDim.x) d.data[base + i] = d.cb_bytes[c][i];
-    if (fresh && status[d.st_idx[c]].crc_ok)
+    /* "If TB CRC failed, save correct CB for next retransmission" (sch.c:409-417): the cache is refreshed only while some
+     * code block of the transport block is still wrong — a (pointless) retransmission after an ACK finds it as it was */
+    if (fresh && !s_ok && status[d.st_idx[c]].crc_ok)
       for (uint32_t i = tid; i < d.rlen[c] / 8; i += blockDim.x) d.cache[c][i] = d.cb_bytes[c][i];
     __syncthreads();
   }

@@ -106,7 +106,8 @@ struct FecFeDesc {
   uint32_t        pad;
 };
 cudaError_t fec_launch_frontend(const FecFeDesc *descs, float *csi_max, const uint32_t *x2_masks, const uint32_t *x1_states,
-                                uint32_t ntb, uint32_t max_re, int any_csi, int any_uci, int kinds /* 1: DL present, 2: UL present */, cudaStream_t st);
+                                uint32_t ntb, uint32_t max_re, int any_csi, int any_uci, int kinds /* 1: DL present, 2: UL present */, cudaStream_t st,
+                                int llr8 = 0 /* 1: int8 LLRs out (srslte_demod_soft_demodulate_b chain, downlink only) */);
 extern "C" void fec_gen_gold_tables(uint32_t *x2_masks, uint32_t *x1_states);
 
 size_t fec_win_smem_bytes(const fec_geom_t *g, uint32_t slots, int llr8);

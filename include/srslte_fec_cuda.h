@@ -98,7 +98,10 @@ int  fec_cuda_last_path_counts(fec_cuda_ctx_t *ctx, uint64_t out2[2]);
  * blocks decode as srslte_tdec_iteration_8bit does (turbodecoder.c:392-452): K > 2048 in the 32-sub-block int8 decoder
  * (avx8), 800 < K <= 2048 with K mod 16 == 0 in the 16-sub-block one (sse8), every other K in the 16-bit decoder of its
  * class on the widened values. fec_cuda_cb_t.input stays int16 (values within int8). The symbol front end
- * (fec_cuda_decode_syms) is not available in this mode. Soft buffers must be reset when the mode changes. */
+ * (fec_cuda_decode_syms / fec_cuda_frontend) then runs the reference's 8-bit chain — srslte_demod_soft_demodulate_b
+ * (demod_soft.c:458-478), srslte_scrambling_sb_offset (scrambling.c:53-56), the int8 branch of csi_correction
+ * (pdsch.c:707-714) — for DOWNLINK transport blocks; uplink ones (nof_symb != 0) are refused in this mode. Soft buffers
+ * must be reset when the mode changes. */
 int  fec_cuda_set_llr_8bit(fec_cuda_ctx_t *ctx, int on);
 
 /* srslte_tdec_init_manual (turbodecoder.c:153-190): force ONE 16-bit arithmetic class on every code block size instead of
@@ -150,7 +153,8 @@ int  fec_cuda_wait(fec_cuda_ctx_t *ctx, uint64_t ticket);
  *       (sch.c:913-916), descrambling, ulsch_deinterleave (sch.c:860-881), decode_tb on g_bits + Q'_cqi*Qm.
  * One fused kernel writes the int16 LLRs to HBM; the host ships 8 bytes per resource element instead of 2*Qm. The
  * LLRs are bit-identical with the reference's AVX2 build (rounding of its SIMD bodies and scalar tails, the CSI weights
- * of its SSE loop, g[0] overwritten by the last RI position). 16-bit LLRs only (llr_is_8bit = false). */
+ * of its SSE loop, g[0] overwritten by the last RI position). In 8-bit LLR mode (fec_cuda_set_llr_8bit) the downlink
+ * chain is the reference's int8 one and the LLRs are int8. */
 typedef struct {
   const void     *symbols;      /* nof_re complex floats (cf_t), 16-byte aligned: q->d[cw] (pdsch.c:797) / q->d (pusch.c:620);
                                    host, or device with FEC_CUDA_F_DEVICE_IO */
@@ -178,8 +182,8 @@ int  fec_cuda_submit_syms(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, const fec_cud
                           uint64_t *ticket);
 /* device time of the front-end kernels of the last call (ms) */
 int  fec_cuda_last_frontend_ms(fec_cuda_ctx_t *ctx, float *ms);
-/* front end alone: LLRs as decode_tb would receive them (e_bits for DL, g_bits for UL), nof_re*mod_bits int16, host
- * pointers; drop-in body of srslte_demod_soft_demodulate_s + srslte_scrambling_s_offset (+ csi / de-interleaver) */
+/* front end alone: LLRs as decode_tb would receive them (e_bits for DL, g_bits for UL), nof_re*mod_bits int16 (int8 in
+ * 8-bit LLR mode: llr_out then points to int8_t), host pointers; drop-in body of srslte_demod_soft_demodulate_s + srslte_scrambling_s_offset (+ csi / de-interleaver) */
 int  fec_cuda_frontend(fec_cuda_ctx_t *ctx, const fec_cuda_sym_t *sym, int16_t *llr_out);
 uint32_t fec_cuda_cinit_pdsch(uint32_t rnti, uint32_t codeword, uint32_t nslot, uint32_t cell_id);   /* sequences.c:64-66 */
 uint32_t fec_cuda_cinit_pusch(uint32_t rnti, uint32_t nslot, uint32_t cell_id);                       /* sequences.c:71-73 */

@@ -996,6 +996,99 @@ void orc_csi_s(int mod_bits, int16_t *e, const float *csi, uint32_t nof_bits)
 #undef CSI_MULHI
 }
 
+/* ---- 8-bit LLR front end (q->llr_is_8bit: pdsch.c:795-813, 707-714) ---------------------------------------------------- */
+/* C conversion float/double -> int8_t as gcc emits it on x86-64: cvttss2si / cvttsd2si to 32 bits, low byte kept */
+static int8_t fe_cvt_c8(double v)
+{
+  if (!(v > -2147483649.0 && v < 2147483648.0)) return 0;
+  return (int8_t)(int32_t)v;
+}
+/* cvtps2dq (nearest even) or cvttps2dq, then packssdw and packsswb: saturation to int16, then to int8 */
+static int8_t fe_cvt_sat8(float v, int truncate)
+{
+  const int16_t w = fe_cvt_sat16(v, truncate);
+  return (int8_t)(w > 127 ? 127 : w < -128 ? -128 : w);
+}
+static int8_t fe_abs8(int8_t v) { return (int8_t)(v < 0 ? -v : v); }        /* pabsb: |-128| = -128 */
+
+/* srslte_demod_soft_demodulate_b (demod_soft.c:458-478) -> demod_{bpsk,qpsk,16qam,64qam}_lte_b (:49-53,67-69,136-187,209-224,
+ * 305-372,397-413): SSE bodies over 8 symbols (16 values for QPSK), scalar tails */
+int orc_demod_b(int mod_bits, const float *sym, int8_t *llr, int nsym)
+{
+  switch (mod_bits) {
+  case 1:
+    for (int i = 0; i < nsym; i++) {
+      const float s = (float)(int8_t)-20 * (sym[2 * i] + sym[2 * i + 1]);
+      llr[i] = fe_cvt_c8((double)s / sqrt(2));
+    }
+    return 0;
+  case 2: {
+    /* srslte_vec_convert_fb_simd (vector_simd.c:433-496): 16 values per SSE step, truncation + two saturating packs */
+    const float scale = (float)(-20 * sqrt(2));
+    const int len = 2 * nsym;
+    int i = 0;
+    for (; i < len - 16 + 1; i += 16)
+      for (int k = 0; k < 16; k++) llr[i + k] = fe_cvt_sat8(sym[i + k] * scale, 1);
+    for (; i < len; i++) llr[i] = fe_cvt_c8(sym[i] * scale);
+    return 0;
+  }
+  case 4: {
+    const int8_t off = (int8_t)(2 * 30 / sqrt(10));
+    int i = 0;
+    for (; i < 8 * (nsym / 8); i++)
+      for (int c = 0; c < 2; c++) {
+        const int8_t y = fe_cvt_sat8(sym[2 * i + c] * -30.0f, 0);
+        llr[4 * i + c] = y; llr[4 * i + 2 + c] = (int8_t)(fe_abs8(y) - off);
+      }
+    for (; i < nsym; i++)
+      for (int c = 0; c < 2; c++) {
+        const short y = fe_cvt_c8(30 * sym[2 * i + c]);
+        llr[4 * i + c] = (int8_t)-y;
+        llr[4 * i + 2 + c] = fe_cvt_c8(abs(y) - 2 * 30 / sqrt(10));
+      }
+    return 0;
+  }
+  case 6: {
+    const int8_t off1 = (int8_t)(4 * 40 / sqrt(42)), off2 = (int8_t)(2 * 40 / sqrt(42));
+    int i = 0;
+    for (; i < 8 * (nsym / 8); i++)
+      for (int c = 0; c < 2; c++) {
+        const int8_t y = fe_cvt_sat8(sym[2 * i + c] * -40.0f, 0);
+        const int8_t a1 = (int8_t)(fe_abs8(y) - off1);
+        llr[6 * i + c] = y; llr[6 * i + 2 + c] = a1; llr[6 * i + 4 + c] = (int8_t)(fe_abs8(a1) - off2);
+      }
+    for (; i < nsym; i++)
+      for (int c = 0; c < 2; c++) {
+        const float y = fe_cvt_c8(40 * sym[2 * i + c]);
+        llr[6 * i + c] = fe_cvt_c8(-y);
+        llr[6 * i + 2 + c] = fe_cvt_c8(abs((int)y) - 4 * 40 / sqrt(42));
+        llr[6 * i + 4 + c] = fe_cvt_c8(abs(llr[6 * i + 2 + c]) - 2 * 40 / sqrt(42));
+      }
+    return 0;
+  }
+  default:
+    return -1;
+  }
+}
+
+/* srslte_scrambling_sb_offset (scrambling.c:53-56) -> srslte_vec_neg_bbb (vector_simd.c:252-279): psignb with +-1, wrapping */
+void orc_descramble_b(const uint8_t *c, int8_t *llr, uint32_t len)
+{
+  for (uint32_t i = 0; i < len; i++) if (c[i]) llr[i] = (int8_t)-llr[i];
+}
+
+/* csi_correction, 8-bit branch (pdsch.c:707-714): scalar throughout */
+void orc_csi_b(int mod_bits, int8_t *e, const float *csi, uint32_t nof_bits)
+{
+  const uint32_t qm = (uint32_t)mod_bits, nsym = nof_bits / qm;
+  float csi_max = 1.0f;
+  if (nsym) { csi_max = -INFINITY; for (uint32_t i = 0; i < nsym; i++) if (csi[i] > csi_max) csi_max = csi[i]; }
+  for (uint32_t i = 0; i < nsym; i++) {
+    const float w = csi[i] / csi_max;
+    for (uint32_t k = 0; k < qm; k++) e[qm * i + k] = fe_cvt_c8((float)e[qm * i + k] * w);
+  }
+}
+
 /* ulsch_deinterleave (sch.c:860-881) = ulsch_interleave_gen (:550-568) + srslte_vec_lut_sis (vector.c:119-123): q is
  * column-major (cols SC-FDMA symbols x rows), g row-major without the RI positions; RI positions get lut 0, so g[0]
  * ends up holding the LAST RI position's value (scatter in ascending q order). g must be pre-filled by the caller if the

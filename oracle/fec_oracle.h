@@ -101,4 +101,8 @@ int      orc_tb_encode(uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bi
 /* multithreaded timing harness for bench.py's cpu_baseline leg ("port") */
 double orc_bench_tb_mt(int nthreads, int ntb, uint32_t tbs, uint32_t Qm, uint32_t rv, uint32_t nof_e_bits,
                        const int16_t *e_bits_all, uint32_t max_its, int reps, uint64_t *out3);
+/* 8-bit LLR front end (pdsch.c:795-813 with q->llr_is_8bit) */
+int      orc_demod_b(int mod_bits, const float *sym, int8_t *llr, int nsym);
+void     orc_descramble_b(const uint8_t *c, int8_t *llr, uint32_t len);
+void     orc_csi_b(int mod_bits, int8_t *e, const float *csi, uint32_t nof_bits);
 #endif

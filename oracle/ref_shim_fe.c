@@ -91,6 +91,34 @@ int ref_csi_s(int mod_bits, int16_t *llr, float *csi, uint32_t nof_bits)
   return 0;
 }
 
+/* ---- the 8-bit LLR variants of the three stages (q->llr_is_8bit, pdsch.c:795-813) ---- */
+int ref_demod_b(int mod_bits, const float *sym, int8_t *llr, int nsym)
+{
+  return srslte_demod_soft_demodulate_b(mod_of(mod_bits), (const cf_t *)sym, llr, nsym);
+}
+
+int ref_descramble_b(uint32_t c_init, int8_t *llr, uint32_t len)
+{
+  srslte_sequence_t s;
+  memset(&s, 0, sizeof(s));
+  if (srslte_sequence_LTE_pr(&s, len, c_init)) return -1;
+  srslte_scrambling_sb_offset(&s, llr, 0, (int)len);
+  srslte_sequence_free(&s);
+  return 0;
+}
+
+int ref_csi_b(int mod_bits, int8_t *llr, float *csi, uint32_t nof_bits)
+{
+  static srslte_pdsch_t q;
+  static srslte_pdsch_cfg_t cfg;
+  memset(&q, 0, sizeof(q)); memset(&cfg, 0, sizeof(cfg));
+  q.csi[0] = csi; q.llr_is_8bit = true; q.csi_enabled = true;
+  cfg.grant.mcs[0].mod = mod_of(mod_bits);
+  cfg.nbits[0].nof_bits = nof_bits;
+  csi_correction(&q, &cfg, 0, 0, llr);
+  return 0;
+}
+
 /* ---- the whole PDSCH codeword decode: srslte_pdsch_codeword_decode (pdsch.c:778-834) ---- */
 typedef struct {
   srslte_pdsch_t          q;

@@ -41,6 +41,11 @@ def oracle():
                                         C.c_uint32, C.c_int, C.c_void_p]
         lib.orc_map.argtypes = [C.c_int, C.c_int] + [C.c_void_p] * 6
         lib.orc_demod_s.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+        lib.orc_demod_b.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+        lib.orc_descramble_b.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
+        lib.orc_descramble_b.restype = None
+        lib.orc_csi_b.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32]
+        lib.orc_csi_b.restype = None
         lib.orc_sequence.argtypes = [C.c_uint32, C.c_uint32, C.c_void_p]
         lib.orc_sequence.restype = None
         lib.orc_descramble_s.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
@@ -101,6 +106,10 @@ def ref():
             lib.ref_sequence.argtypes = [C.c_uint32, C.c_uint32, C.c_void_p]
             lib.ref_descramble_s.argtypes = [C.c_uint32, C.c_void_p, C.c_uint32]
             lib.ref_csi_s.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32]
+            if hasattr(lib, "ref_demod_b"):
+                lib.ref_demod_b.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+                lib.ref_descramble_b.argtypes = [C.c_uint32, C.c_void_p, C.c_uint32]
+                lib.ref_csi_b.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32]
             lib.ref_cinit_pdsch.restype = C.c_uint32
             lib.ref_cinit_pusch.restype = C.c_uint32
             lib.ref_ulsch_deinterleave.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32]

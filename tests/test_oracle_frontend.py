@@ -204,3 +204,54 @@ def test_ul_chain_vs_reference(orc, reflib, tbs, mod, prb, cols, uci):
     assert ret == r and (d2[: tbs // 8 + 3] == data[: tbs // 8 + 3]).all() and (crc == crc_ref).all()
     assert r == 0 and (data[: tbs // 8] == payload[0]).all()
     reflib.ref_ul_free(ul)
+
+
+# ---- 8-bit LLR front end (q->llr_is_8bit: srslte_demod_soft_demodulate_b, srslte_scrambling_sb_offset, int8 CSI weighting) ----
+@pytest.mark.parametrize("mod", [1, 2, 4, 6])
+def test_demod8_matches_reference(orc, reflib, mod):
+    """int8 demodulators: SSE bodies over 8 symbols (16 values for QPSK) with rounding / truncation and two saturating packs,
+    scalar tails with C conversions; lengths that leave 0..7 symbols to the tails, rounding ties, saturation"""
+    rng = np.random.default_rng(40 + mod)
+    for n in (1, 3, 7, 8, 9, 15, 16, 17, 33, 250, 1001, 15000):
+        for big in (False, True):
+            sym = _symbols(n, rng, big)
+            if not big:
+                sym[: min(2 * n, 40)] = (np.arange(min(2 * n, 40)) - 20.5) / 80.0          # x.5 / 40: exact rounding ties at 64QAM
+            a, b = aligned(mod * n + 64, np.int8), aligned(mod * n + 64, np.int8)
+            assert reflib.ref_demod_b(mod, P(sym), P(a), n) == 0
+            assert orc.orc_demod_b(mod, P(sym), P(b), n) == 0
+            if big:
+                # out-of-range float -> int8 conversions in the reference's scalar loops are undefined C: SIMD bodies only
+                m = 16 * ((2 * n) // 16) if mod == 2 else 0 if mod == 1 else mod * 8 * (n // 8)
+                assert (a[:m] == b[:m]).all(), (mod, n, np.nonzero(a[:m] != b[:m])[0][:8])
+            else:
+                assert (a == b).all(), (mod, n, np.nonzero(a != b)[0][:8])
+
+
+def test_descramble8(orc, reflib):
+    rng = np.random.default_rng(46)
+    for n in (5, 31, 32, 33, 90000):
+        x = aligned(n, np.int8)
+        x[:] = rng.integers(-128, 128, n)
+        x[0] = -128
+        y = x.copy()
+        c = np.zeros(n, np.uint8)
+        orc.orc_sequence(777, n, P(c))
+        assert reflib.ref_descramble_b(777, P(x), n) == 0
+        orc.orc_descramble_b(P(c), P(y), n)
+        assert (x == y).all()
+
+
+@pytest.mark.parametrize("mod", [2, 4, 6])
+def test_csi_weighting8(orc, reflib, mod):
+    rng = np.random.default_rng(50 + mod)
+    for nsym in (2, 3, 5, 100, 101, 15000):
+        e = aligned(mod * nsym, np.int8)
+        e[:] = rng.integers(-128, 128, mod * nsym)
+        csi = aligned(nsym + 8, np.float32)
+        csi[:nsym] = rng.uniform(0.05, 2.0, nsym).astype(np.float32)
+        a, b = e.copy(), e.copy()
+        a2 = aligned(mod * nsym, np.int8); a2[:] = a
+        assert reflib.ref_csi_b(mod, P(a2), P(csi), mod * nsym) == 0
+        orc.orc_csi_b(mod, P(b), P(csi), mod * nsym)
+        assert (a2 == b).all(), (mod, nsym, np.nonzero(a2 != b)[0][:8])
