@@ -241,7 +241,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=1184, help="transport blocks per GPU per step (default 8 per SM)")
+    ap.add_argument("--batch", type=int, default=4736, help="transport blocks per GPU per step (default 32 per SM = 61 568 code blocks)")
     ap.add_argument("--sigma", type=float, default=0.45, help="AWGN std of the synthetic LLRs (0.45 = operating point)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-bind", action="store_true", help="do not bind the rank to the CPUs local to its GPU")
@@ -252,6 +252,7 @@ def main():
     ap.add_argument("--sigma-harq", type=float, default=0.47, help="AWGN std of the HARQ leg (rv 0 mostly fails)")
     ap.add_argument("--sustain", type=float, default=2.0, help="seconds of the sustained leg (0 = skip)")
     ap.add_argument("--no-llr8", action="store_true", help="skip the 8-bit LLR leg")
+    ap.add_argument("--no-grid", action="store_true", help="skip the sigma grid (int16 and int8 paths at sigma 0.30 / 0.40 / 0.45)")
     ap.add_argument("--sigma8", type=float, default=0.30, help="AWGN std of the 8-bit LLR leg")
     ap.add_argument("--sigma-ul", type=float, default=0.17, help="AWGN std per real dimension of the synthetic 16QAM PUSCH symbols")
     ap.add_argument("--no-tx", action="store_true", help="skip the transmit-side leg (turbo encoder + rate matching on the device)")
@@ -415,18 +416,19 @@ def main():
                 sets.append(sd)
             sy_ab.append(sets)
 
-        def timed_syms(tb_sets, sym_sets, flags, steps):
+        def timed_syms(tb_sets, sym_sets, flags, steps, f=None, st=None):
+            f, st = f or fec, st or stream
             barrier()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record(stream)
+            e0.record(st)
             prev = None
             for i in range(steps):
-                t = fec.submit_syms(tb_sets[i & 1], sym_sets[i & 1], flags)
+                t = f.submit_syms(tb_sets[i & 1], sym_sets[i & 1], flags)
                 if prev is not None:
-                    fec.wait(prev)
+                    f.wait(prev)
                 prev = t
-            fec.wait(prev)
-            e1.record(stream)
+            f.wait(prev)
+            e1.record(st)
             barrier()
             return shard.reduce_job(dist if world > 1 else None, f"cuda:{local_rank}", e0.elapsed_time(e1))[0]
 
@@ -716,6 +718,67 @@ def main():
                              h2d_bytes_per_step=B * NBITS + B * C_CB * (32 + 48) + B * 520,
                              frac_of_h2d_link=(B * NBITS + B * C_CB * (32 + 48) + B * 520) / (ms8e / n8 / 1e3) / 1e9 / link_min),
                     kernel="fec_tdec_win8p_kernel<32,true>: two sub-blocks per thread in u16x2 lanes (VIADDMNMX.S16x2.RELU = saturating int8 add), beta checkpoints in tensor memory (profiles/r1o_win8p_kernel_ncu.txt)")
+        # ---- the 8-bit path fed with equalised symbols (8 B per resource element): int8 soft demodulation
+        #      (srslte_demod_soft_demodulate_b), int8 descrambling, int8 rate de-matching, int8 decoders ----
+        if front is not None:
+            for i in range(6):
+                f8.decode_syms([dd8, dd8b][i & 1], sy_ab[0][i & 1], pkg.F_DEVICE_IO)
+            ms8y = timed_syms([dd8, dd8b], sy_ab[0], pkg.F_DEVICE_IO, n8, f=f8, st=st8)
+            ok8y = sum(1 for i in range(B) if dd8[i].ret == 0)
+            its8y = sum(sum(dd8[i].cb_its[:C_CB]) for i in range(B))
+            o8 = d_out[1].cpu().numpy()
+            if any(dd8[i].ret == 0 and not (o8[i, :TBS // 8] == payload[i % payload.shape[0]]).all() for i in range(B)):
+                raise SystemExit("bench.py: a CRC-passing transport block of the 8-bit symbol leg differs from the transmitted payload")
+            f8.decode_syms(dd8, sy_ab[0][0], pkg.F_DEVICE_IO | pkg.F_SERIAL)
+            fe8_ms = f8.last_frontend_ms()
+            for i in range(6):
+                f8.decode_syms([hd8, hd8b][i & 1], sy_ab[1][i & 1], 0)
+            ms8yh = timed_syms([hd8, hd8b], sy_ab[1], 0, n8, f=f8, st=st8)
+            ok8yh = sum(1 for i in range(B) if hd8[i].ret == 0)
+            hb = B * (NBITS // QM) * 8 + B * C_CB * (32 + 48) + B * (520 + 80)
+            llr8["symbols_in"] = dict(workload="same TBs as 64QAM symbols (sigma_sym %.3f), int8 front end + 8-bit path" % args.sigma_sym,
+                                      value=allsum(ok8y) * TBS * n8 / (ms8y / 1e3) / 1e9, unit=UNIT, ms_per_step=ms8y / n8,
+                                      tb_ok_frac=allsum(ok8y) / (world * B), halfits_per_cb=allsum(its8y) / (world * B * C_CB), frontend_ms=fe8_ms,
+                                      e2e=dict(value=allsum(ok8yh) * TBS * n8 / (ms8yh / 1e3) / 1e9, unit=UNIT, ms_per_step=ms8yh / n8,
+                                               h2d_bytes_per_step=hb, frac_of_h2d_link=hb / (ms8yh / n8 / 1e3) / 1e9 / link_min))
+        # ---- sigma grid: the int16 path and the int8 path on the SAME transport blocks at the same noise levels, with the
+        #      half-iterations per code block beside each value (296 distinct noisy TBs per point, tiled to the batch) ----
+        if not args.no_grid:
+            G = min(B, 296)
+            g16 = np.zeros((G, NBITS), np.int16)
+            d_g16 = torch.empty((B, NBITS), dtype=torch.int16, device=f"cuda:{local_rank}")
+            gsets = []
+            for s_ in range(2):
+                d_ = (pkg.TbDesc * B)()
+                fill_descs(pkg, d_, B, d_g16.data_ptr(), d_out[s_].data_ptr(), sb0 + s_ * B)
+                gsets.append(d_)
+            rows = np.arange(B) % G
+            idx = torch.from_numpy(rows).to(f"cuda:{local_rank}")
+            grid = []
+            for sg in (0.30, 0.40, 0.45):
+                rng_g = np.random.default_rng(7000 + rank)
+                for i0 in range(0, G, 64):
+                    i1 = min(G, i0 + 64)
+                    synth8.awgn_llr(e8[np.arange(i0, i1) % payload.shape[0]], sg, rng_g, out=g16[i0:i1])
+                t16 = torch.from_numpy(g16).to(f"cuda:{local_rank}")
+                d_g16.copy_(t16[idx])
+                d8.copy_(torch.from_numpy(np.clip(np.rint(g16 * 0.24), -128, 127).astype(np.int8)).to(f"cuda:{local_rank}")[idx])
+                torch.cuda.synchronize()
+                row = dict(sigma=sg)
+                for name, ff, sets, stx in (("int16", fec, gsets, stream), ("int8", f8, [dd8, dd8b], st8)):
+                    for d_ in sets:
+                        ff.decode_tbs(d_, pkg.F_DEVICE_IO)
+                    ms_g = timed_pipelined(sets, pkg.F_DEVICE_IO, n8, f=ff, st=stx)
+                    okg = sum(1 for i in range(B) if sets[0][i].ret == 0)
+                    itg = sum(sum(sets[0][i].cb_its[:C_CB]) for i in range(B))
+                    og = d_out[1 if name == "int8" else 0].cpu().numpy()
+                    if any(sets[0][i].ret == 0 and not (og[i, :TBS // 8] == payload[rows[i] % payload.shape[0]]).all() for i in range(B)):
+                        raise SystemExit(f"bench.py: sigma grid {name} sigma {sg}: a CRC-passing transport block differs from the transmitted payload")
+                    row[name] = dict(value=allsum(okg) * TBS * n8 / (ms_g / 1e3) / 1e9, unit=UNIT, ms_per_step=ms_g / n8,
+                                     tb_ok_frac=allsum(okg) / (world * B), halfits_per_cb=allsum(itg) / (world * B * C_CB))
+                grid.append(row)
+            llr8["sigma_grid"] = dict(note="device-resident, 2 batches in flight; value counts ACKed bits only; int8 LLRs = clip(rint(0.24 * int16 LLRs))", points=grid)
+            del d_g16
         f8.close()
 
     # ---- latency of the reference's call shape: ONE transport block per blocking call (srslte_dlsch_decode as pdsch.c:816

@@ -802,12 +802,25 @@ __global__ void __launch_bounds__(FEC_WIN_THREADS, 4) fec_tdec_win8p_kernel(cons
       if (done) {
         for (int i = j; i < kw; i += TPC) outw[i] = 0;
         __syncwarp(lane_mask);
+        /* natural positions from the step tables, 4 steps per load (the rows are Lp >= L words, 16-byte aligned) and 4 loads in
+         * flight: one dependent 4-byte load per step made this stage as long as a third of a half-iteration */
         for (int h = 0; h < 2; h++) {
-          const uint32_t *Ts = h ? T1s : T0s;
-          for (int k = 0; k < L; k++) {
-            if ((bitsw[(k >> 5) * nlane + l0 + h] >> (k & 31)) & 1u) {
-              const int nat = __ldg(Ts + k) >> 16;
-              atomicOr(&outw[nat >> 5], 1u << (8 * ((nat >> 3) & 3) + 7 - (nat & 7)));
+          const uint4 *T4 = reinterpret_cast<const uint4 *>(h ? T1s : T0s);
+          const int nq = (L + 3) >> 2;
+          for (int q0 = 0; q0 < nq; q0 += 4) {
+            uint4 t[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) t[u] = (q0 + u < nq) ? __ldg(T4 + q0 + u) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+#pragma unroll
+              for (int c = 0; c < 4; c++) {
+                const int k = 4 * (q0 + u) + c;
+                if (k < L && ((bitsw[(k >> 5) * nlane + l0 + h] >> (k & 31)) & 1u)) {
+                  const int nat = (int)(win_comp(t[u], c) >> 16);
+                  atomicOr(&outw[nat >> 5], 1u << (8 * ((nat >> 3) & 3) + 7 - (nat & 7)));
+                }
+              }
             }
           }
         }
@@ -1065,15 +1078,10 @@ __global__ void __launch_bounds__(FEC_RM_THREADS) fec_rm_rx_kernel(const FecRmDe
     const uint32_t h = bulk ? (uint32_t)(a0 - ea) >> 1 : d.E, t0 = bulk ? (uint32_t)(a1 - ea) >> 1 : d.E;
     if ((uint32_t)tid < h) rm_tile[tid] = __ldg(d.e + tid);
     if (t0 + tid < d.E) rm_tile[t0 + tid] = __ldg(d.e + t0 + tid);
-    /* entries never transmitted, E .. N (entry N is what the table's "no coded bit here" offsets point at): zeroed 16 bytes at
-     * a time between a scalar head and tail */
-    {
-      const uint32_t lo = d.E, hi = d.N + 1;
-      const uint32_t l8 = min(hi, lo + ((16u - ((delta + 2u * lo) & 15u)) & 15u) / 2u), h8 = l8 + ((hi - l8) & ~7u);
-      for (uint32_t p = lo + tid; p < l8; p += FEC_RM_THREADS) rm_tile[p] = 0;
-      for (uint32_t p = l8 + 8 * tid; p < h8; p += 8 * FEC_RM_THREADS) *reinterpret_cast<uint4 *>(rm_tile + p) = make_uint4(0, 0, 0, 0);
-      for (uint32_t p = h8 + tid; p < hi; p += FEC_RM_THREADS) rm_tile[p] = 0;
-    }
+    /* entries never transmitted (E .. N; entry N is what the table's "no coded bit here" offsets point at) all read the ONE
+     * zero behind the slice: the gather clamps its offsets to it, so the tile is E + 1 entries, not N + 1 (at the bench shape
+     * 14 KB instead of 35 KB: more CTAs per SM, and no zero-fill pass) */
+    if (tid == 0) rm_tile[d.E] = 0;
     __syncthreads();                                   /* the barrier object is initialised for everybody */
     if (bulk) {
       uint32_t ok = 0;
@@ -1094,12 +1102,13 @@ __global__ void __launch_bounds__(FEC_RM_THREADS) fec_rm_rx_kernel(const FecRmDe
   const uint4 *rank4 = reinterpret_cast<const uint4 *>(d.rank);
   uint4 *soft4 = reinterpret_cast<uint4 *>(d.soft);
   const uint32_t tb = (uint32_t)__cvta_generic_to_shared(rm_tile);
+  const uint32_t lim = 2u * min(d.E, d.N) * 0x00010001u;        /* byte offset of the zero entry, in both halves */
   uint32_t mx = 0, mn = 0;
   if (d.new_data) {
 #pragma unroll kRmUnroll
     for (int v = tid; v < (int)d.n_out / 8; v += FEC_RM_THREADS) {
       const uint4 rk = __ldg(rank4 + v);
-      const uint32_t rw[4] = {rk.x, rk.y, rk.z, rk.w};
+      const uint32_t rw[4] = {__vminu2(rk.x, lim), __vminu2(rk.y, lim), __vminu2(rk.z, lim), __vminu2(rk.w, lim)};
       uint32_t ow[4];
 #pragma unroll
       for (int k = 0; k < 4; k++) {
@@ -1113,7 +1122,7 @@ __global__ void __launch_bounds__(FEC_RM_THREADS) fec_rm_rx_kernel(const FecRmDe
     for (int v = tid; v < (int)d.n_out / 8; v += FEC_RM_THREADS) {
       const uint4 rk = __ldg(rank4 + v);
       const uint4 old = soft4[v];
-      const uint32_t rw[4] = {rk.x, rk.y, rk.z, rk.w};
+      const uint32_t rw[4] = {__vminu2(rk.x, lim), __vminu2(rk.y, lim), __vminu2(rk.z, lim), __vminu2(rk.w, lim)};
       uint32_t ow[4] = {old.x, old.y, old.z, old.w};
 #pragma unroll
       for (int k = 0; k < 4; k++) {
@@ -1201,14 +1210,16 @@ __global__ void __launch_bounds__(FEC_RM_THREADS) fec_rm_rx8_kernel(const FecRmD
   fec_softmax_commit(soft_max + d.slot, max(hi, -lo));
 }
 
-cudaError_t fec_launch_rm(const FecRmDesc *descs, uint32_t *soft_max, uint32_t n, uint32_t max_n_out, cudaStream_t st, int llr8)
+/* max_tile: the largest min(E, N) + 1 of the launch (0: not known, the slot size bounds it) */
+cudaError_t fec_launch_rm(const FecRmDesc *descs, uint32_t *soft_max, uint32_t n, uint32_t max_n_out, cudaStream_t st, int llr8, uint32_t max_tile)
 {
   if (n == 0) return cudaSuccess;
   if (llr8) {
     fec_rm_rx8_kernel<<<n, FEC_RM_THREADS, (size_t)max_n_out * 2, st>>>(descs, soft_max);
     return cudaGetLastError();
   }
-  fec_rm_rx_kernel<<<n, FEC_RM_THREADS, (size_t)max_n_out * 2 + 32, st>>>(descs, soft_max);   /* N + 1 entries + up to 14 bytes of shift */
+  if (max_tile == 0 || max_tile > max_n_out) max_tile = max_n_out;
+  fec_rm_rx_kernel<<<n, FEC_RM_THREADS, (size_t)max_tile * 2 + 32, st>>>(descs, soft_max);   /* the tile + up to 14 bytes of shift */
   return cudaGetLastError();
 }
 
@@ -1384,5 +1395,7 @@ cudaError_t fec_kernels_init(void)
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(fec_tdec_win_kernel<8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
   if (e != cudaSuccess) return e;
-  return cudaFuncSetAttribute(fec_tdec_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+  e = cudaFuncSetAttribute(fec_tdec_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+  if (e != cudaSuccess) return e;
+  return cudaSuccess;
 }

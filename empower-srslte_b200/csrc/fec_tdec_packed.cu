@@ -857,12 +857,19 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
   uint32_t *rows = reinterpret_cast<uint32_t *>(smem) + TPC * Lw + nslots * Es + slot * (P * nw1);
   const unsigned gmask = (TPC == 32) ? 0xFFFFFFFFu : (((1u << TPC) - 1u) << (g * TPC));
 
-  for (int i = tid; i < TPC * L; i += blockDim.x) {
-    const int r = i / L, k = i - r * L;
-    const uint32_t w = a.pair_addr[r * Lp + k];
-    Tlo[r * Lw + k] = (uint16_t)((w & 0xFFFFu) * 2u);
-    Thi[r * Lw + k] = (uint16_t)((w >> 16) * 2u);
-  }
+  /* the decoder-2 address table of this K into shared memory, 4 independent loads in flight per thread (one load per
+   * iteration had every thread wait out 23 global-memory latencies before the CTA's first code block) */
+  for (int r = 0; r < TPC; r++)
+    for (int k0 = tid; k0 < L; k0 += 4 * FEC_PK_WARPS * 32) {
+      uint32_t w[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) { const int k = k0 + u * FEC_PK_WARPS * 32; w[u] = k < L ? a.pair_addr[r * Lp + k] : 0u; }
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const int k = k0 + u * FEC_PK_WARPS * 32;
+        if (k < L) { Tlo[r * Lw + k] = (uint16_t)((w[u] & 0xFFFFu) * 2u); Thi[r * Lw + k] = (uint16_t)((w[u] >> 16) * 2u); }
+      }
+    }
   if (warp == 0) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" :: "r"((uint32_t)__cvta_generic_to_shared(&s_tmem)) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
