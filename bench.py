@@ -35,7 +35,7 @@ METRIC = "decoded DL-SCH Gbps & code blocks/s per B200 (20MHz MCS28, 8 it)"
 UNIT = "Gbit/s"
 
 
-NCU_DRAM_BYTES_PER_CB = 42534          # measured, see roofline.traffic_source
+NCU_DRAM_BYTES_PER_CB = 47705          # measured, see roofline.traffic_source
 
 
 def ops_per_halfit(K, P):
@@ -360,6 +360,10 @@ def main():
     ms = timed_pipelined(dd_ab, pkg.F_DEVICE_IO, args.steps)
     launches = fec.launches - l0
     ms_sync = timed(dd, pkg.F_DEVICE_IO, args.steps)
+    t0 = time.perf_counter()                     # host side of one step: argument checks, segmentation, descriptors, launches
+    tk_ = fec.submit_tbs(dd, pkg.F_DEVICE_IO)
+    host_submit_ms = (time.perf_counter() - t0) * 1e3
+    fec.wait(tk_)
     ok, its = tally(dd)
     # parity spot check of what was decoded: payload bytes of every CRC-passing TB
     out_host = d_out[0].cpu().numpy()
@@ -511,6 +515,10 @@ def main():
             for i in range(6):
                 fec.decode_syms(u_tb[i & 1], u_sy[i & 1], pkg.F_DEVICE_IO)
             ms_ul = timed_syms(u_tb, u_sy, pkg.F_DEVICE_IO, args.steps)
+            t0 = time.perf_counter()                                  # host side of one step: descriptors, position lists, launches
+            tk_ = fec.submit_syms(u_tb[0], u_sy[0], pkg.F_DEVICE_IO)
+            host_submit_ul_ms = (time.perf_counter() - t0) * 1e3
+            fec.wait(tk_)
             ok_u = sum(1 for i in range(nU) if u_tb[0][i].ret == 0)
             its_u = sum(sum(u_tb[0][i].cb_its[:U_C]) for i in range(nU))
             out_host = du_out[0].cpu().numpy()
@@ -528,6 +536,7 @@ def main():
                           tb_ok_frac=allsum(ok_u) / tot_u, halfits_per_cb=allsum(its_u) / (tot_u * U_C),
                           cbs_per_s=tot_u * U_C * args.steps / (ms_ul / 1e3), payload_check="every CRC-passing TB of set 0 equals its cell's transmitted payload",
                           code_blocks_by_kernel_rank0=dict(total=nU * U_C, certificate_variant=path_u[0], exact=path_u[1]),
+                          host_submit_ms_rank0=host_submit_ul_ms,
                           serial_phases_ms_rank0=dict(zip(("rate_dematch", "turbo_decode", "tb_assemble_crc24a"), fec.last_phase_ms()),
                                                       frontend=fec.last_frontend_ms()))
             del du_sym, du_uci, du_out
@@ -717,7 +726,7 @@ def main():
                     e2e=dict(value=allsum(ok8e) * TBS * n8 / (ms8e / 1e3) / 1e9, unit=UNIT, ms_per_step=ms8e / n8, sync_ms_per_step=ms8es / n8,
                              h2d_bytes_per_step=B * NBITS + B * C_CB * (32 + 48) + B * 520,
                              frac_of_h2d_link=(B * NBITS + B * C_CB * (32 + 48) + B * 520) / (ms8e / n8 / 1e3) / 1e9 / link_min),
-                    kernel="fec_tdec_win8p_kernel<32,true>: two sub-blocks per thread in u16x2 lanes (VIADDMNMX.S16x2.RELU = saturating int8 add), beta checkpoints in tensor memory (profiles/r1o_win8p_kernel_ncu.txt)")
+                    kernel="fec_tdec_win8p_kernel<32,true>: two sub-blocks per thread in u16x2 lanes (VIADDMNMX.S16x2.RELU = saturating int8 add), beta checkpoints in tensor memory (profiles/r2_win8p_kernel_ncu.txt)")
         # ---- the 8-bit path fed with equalised symbols (8 B per resource element): int8 soft demodulation
         #      (srslte_demod_soft_demodulate_b), int8 descrambling, int8 rate de-matching, int8 decoders ----
         if front is not None:
@@ -827,14 +836,15 @@ def main():
     hbm_bytes = B * C_CB * algorithmic_bytes_per_cb(K_CB, NBITS // C_CB)
     roof = dict(bound="alu_int16", kernel="fec_tdec_pk_kernel<16,true>", achieved=achieved, peak=peak_nom, unit="Tops/s",
                 frac=achieved / peak_nom, frac_at_sustained_clock=achieved / peak_run, peak_source=peak_src + f" @ {pk['sm_max_mhz']:.0f} MHz",
-                traffic=NCU_DRAM_BYTES_PER_CB * B * C_CB, traffic_source="ncu --set full of one 7696-CB launch (profiles/r1f_map_kernel_ncu.txt): "
-                "dram__bytes_read.sum + dram__bytes_write.sum = 327.3 MB = 42.5 KB per code block, scaled to this launch",
+                traffic=NCU_DRAM_BYTES_PER_CB * B * C_CB, traffic_source="ncu --set full of one 30 784-CB launch (profiles/r2_map_kernel_ncu.txt): "
+                "dram__bytes_read.sum + dram__bytes_write.sum = 1443.8 + 24.7 MB = 47.7 KB per code block, scaled to this launch",
                 ops_per_launch=ops, ms_per_launch=dec_ms,
                 # the packed add / add-max instructions only exist on the ALU pipe (half rate: 64 lanes/clk/SM); the peak above also
                 # counts the FMA pipe (IMAD), which this instruction mix cannot use. Against the ALU pipe alone:
                 alu_pipe_only=dict(peak=peak_nom * 64.0 / 124.3, frac=achieved / (peak_nom * 64.0 / 124.3),
-                                   ncu="profiles/r1f_map_kernel_ncu.txt: issue slots 46.6 % busy, 47 % of stall samples issuing + 24 % the second "
-                                       "cycle of a half-rate instruction = 70 % ALU-pipe occupancy; rest: 8 % global loads, 7 % final barrier (ragged tail)"),
+                                   ncu="profiles/r2_map_kernel_ncu.txt (30 784-CB launch): sm__inst_executed_pipe_alu 41 % of peak, issue slots 47.5 % busy; "
+                                       "stall samples: 47.6 % issuing, 25.6 % fixed-latency wait (dependent issue, second cycle of the half-rate packed "
+                                       "instructions), 8.8 % global loads, 5.5 % instruction fetch, 4.8 % dispatch, 3.9 % shared-memory loads, 1.6 % final barrier"),
                 share_of_step=dec_ms / (rm_ms + dec_ms + asm_ms), serial_step_ms=rm_ms + dec_ms + asm_ms,
                 phases_ms=dict(rate_dematch=rm_ms, turbo_decode=dec_ms, tb_assemble_crc24a=asm_ms),
                 hbm=dict(bound="hbm", algorithmic_bytes_per_step=hbm_bytes, achieved=hbm_bytes / (ms / args.steps / 1e3) / 1e9,
@@ -876,7 +886,7 @@ def main():
                              h2d_link=dict(gbs_slowest_rank=link_min, gbs_all_ranks=link_sum, how="pinned 256 MB x 8 cudaMemcpyAsync per rank, all ranks at once (tools/h2d_peak.cu standalone)",
                                            achieved_gbs_per_rank=h2d / (ms_e / args.steps / 1e3) / 1e9, frac=h2d / (ms_e / args.steps / 1e3) / 1e9 / link_min),
                              cpu_binding=affinity),
-                    sync_ms_per_step=ms_sync / args.steps,
+                    sync_ms_per_step=ms_sync / args.steps, host_submit_ms_per_step=host_submit_ms,
                     gpu_launches=launches, clocks=clocks, roofline=roof, worst_case_8_halfits=worst, frontend_symbols=front, ulsch_config5=ulsch5, harq_config3=harq, sustained=sustained, transmit_side=tx, llr_8bit=llr8, single_tb_latency=lat, cpu_baseline=cpu, parity_in_bench=parity)
         print(json.dumps(line), flush=True)
     fec.close()
