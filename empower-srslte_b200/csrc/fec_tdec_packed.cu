@@ -74,6 +74,9 @@ __device__ __forceinline__ void pk_sts_u16(uint32_t addr, uint32_t val)
 #ifndef PK_LATE_ZERO
 #define PK_LATE_ZERO 1
 #endif
+#ifndef PK_PF_BETA
+#define PK_PF_BETA 0
+#endif
 #ifndef PK_PF_L1
 #define PK_PF_L1 1
 #endif
@@ -289,6 +292,18 @@ __device__ __forceinline__ void pk_load_raw(const PkView &v, int k0, int i0, PkR
         r.y[i] = pk_ldg32(v.Yrow + w); if (!v.par) r.s[i] = pk_ldg32(v.Srow + w);
       }
     }
+  }
+}
+
+/* the lines pk_load_raw<true, true> will read for chunk k0, asked into L1 ahead of time (no register is tied up) */
+__device__ __forceinline__ void pk_prefetch_raw(const PkView &v, int k0)
+{
+  const int w0 = (k0 >> 2) * v.tpc4;
+  asm volatile("prefetch.global.L1 [%0];" :: "l"(v.Yrow + w0));
+  asm volatile("prefetch.global.L1 [%0];" :: "l"(v.Yrow + w0 + v.tpc4));
+  if (!v.par) {
+    asm volatile("prefetch.global.L1 [%0];" :: "l"(v.Srow + w0));
+    asm volatile("prefetch.global.L1 [%0];" :: "l"(v.Srow + w0 + v.tpc4));
   }
 }
 
@@ -569,6 +584,12 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
     for (int c = c0 - 2; c < nfull; c += 2) {
       const int k0 = L - PK_CH * (c + 1);
       if (c + 2 < nfull) { pk_load_raw<true, VEC>(v, k0 - 2 * PK_CH, 0, nraw); pk_load_raw<true, VEC>(v, k0 - 3 * PK_CH, 0, nrawB); }
+#if PK_PF_BETA
+      /* the L2 round trip under load is longer than the 16 steps the register loads are issued ahead (3.7 % of the kernel's
+       * warp-cycles waited at the rotation below): the lines of the iteration after the next go to L1 now. Measured: decode
+       * phase -1 % with early stop, +1.3 % with all 8 half-iterations, pipelined step unchanged — off (tools/experiments/README.md) */
+      if (VEC && c + 4 < nfull) { pk_prefetch_raw(v, k0 - 4 * PK_CH); pk_prefetch_raw(v, k0 - 5 * PK_CH); }
+#endif
       PK_PIN();
       if (c >= c0) {
         pk_finish_chunk<true>(v, k0, 0, raw, xs, es);
