@@ -231,3 +231,37 @@ def test_decode_syms_ul_with_control(fec, orc, tbs, mod, prb, n_ack_sym, n_ri_sy
         assert (outs[i][: tbs // 8 + 3] == data[: tbs // 8 + 3]).all()
         if n_ack_sym <= 8:
             assert ret == 0 and (outs[i][: tbs // 8] == payload[i]).all()
+
+
+def test_decode_syms_ul_mixed_control_layouts_in_one_batch(fec, orc):
+    """the host pass reuses the sorted position lists of an allocation for the following allocations with the same layout
+    (fe_same_uci, csrc/fec_cuda_api.cu): one batch that alternates between three layouts (also one without any control
+    information, and equal layouts given through different arrays) must decode every block as the oracle does"""
+    tbs, mod, prb, cols = 15264, 4, 40, 12
+    rows = 12 * prb
+    rng = np.random.default_rng(4242)
+    layouts = {"A": (8, 4, 0), "B": (0, 0, 0), "C": (12, 0, 64), "D": (8, 4, 32)}       # D: A's positions, other CQI length
+    order = ["A", "A", "B", "A", "C", "C", "B", "D", "A", "D"]
+    c_init = synth.cinit_pusch(0x51, 4, 3)
+    payload = rng.integers(0, 256, (len(order), tbs // 8), dtype=np.uint8)
+    items, want = [], []
+    for i, key in enumerate(order):
+        n_ack_sym, n_ri_sym, n_cqi = layouts[key]
+        ack_pos = _fe.uci_positions(n_ack_sym, mod, rows, _fe.ACK_COLS)
+        ri_pos = _fe.uci_positions(n_ri_sym, mod, rows, _fe.RI_COLS)
+        sym, G = _fe.make_ul(payload[i:i + 1], tbs, mod, 0, prb, cols, c_init, 0.16, rng, ri_pos, n_cqi)
+        items.append(dict(sym=sym[0], mod=mod, c_init=c_init, nof_symb=cols, ack_pos=list(ack_pos), ri_pos=list(ri_pos), n_cqi=n_cqi, nof_e_bits=G, rv=0))
+        want.append((ack_pos, ri_pos, n_cqi, G))
+    sb0 = fec.softbuffer_alloc(len(order))
+    d, outs, ucis = _run_syms(fec, tbs, mod, items, True, sb0)
+    for i, (ack_pos, ri_pos, n_cqi, G) in enumerate(want):
+        g, raw = _fe.oracle_frontend(orc, items[i]["sym"], mod, c_init, None, cols, ack_pos, ri_pos)
+        assert (ucis[i][: raw.size] == raw).all(), (i, order[i])
+        assert (ucis[i][raw.size: raw.size + n_cqi] == g[:n_cqi]).all(), (i, order[i])
+        ot = C.c_void_p(orc.orc_tb_new())
+        orc.orc_tb_reset(ot, tbs)
+        ret, data, crc, its = _oracle_decode(orc, ot, tbs, mod, 0, g[n_cqi: n_cqi + G])
+        orc.orc_tb_free(ot)
+        assert d[i].ret == ret and list(d[i].cb_its) == list(its) and list(d[i].cb_crc) == list(crc), (i, order[i])
+        assert (outs[i][: tbs // 8 + 3] == data[: tbs // 8 + 3]).all(), (i, order[i])
+        assert ret == 0 and (outs[i][: tbs // 8] == payload[i]).all(), (i, order[i])
