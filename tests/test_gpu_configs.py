@@ -173,3 +173,67 @@ def test_config2_full_shape_vs_oracle(fec, orc):
     assert (o1[:, : tbs // 8 + 3] == o2[:, : tbs // 8 + 3]).all() and (o1[:, : tbs // 8 + 3] == o3[:, : tbs // 8 + 3]).all()
     spread = {v for row in i1 for v in row[:13]}
     assert len(spread) >= 3, "half-iteration counts should vary across code blocks (early stop)"
+
+
+def test_device_call_cut_into_two_sub_batches_and_calls_in_flight(orc):
+    """a device-resident call is cut into two sub-batches of at least 592 transport blocks (csrc/fec_cuda_api.cu submit_common):
+    1301 small transport blocks in one call must give what the host-buffer call (sub-batches of 296) gives and what the
+    oracle gives; then four calls in flight on a fresh context (every pipe of the ring is used before its first wait)"""
+    import torch
+    tbs, Qm, nbits, n = 1000, 2, 1440, 1301
+    rng = np.random.default_rng(31)
+    payload = rng.integers(0, 256, (n, tbs // 8), dtype=np.uint8)
+    llr = synth.awgn_llr(synth.encode_tbs(payload, tbs, Qm, 0, nbits), 0.62, rng)
+    f = pkg.FecCuda(0, max_tbs=64)                      # deliberately small: the staging grows with the first call
+    try:
+        sb0 = f.softbuffer_alloc(4 * n)
+        dl = torch.from_numpy(llr).cuda()
+        stride = tbs // 8 + 3 + 768
+
+        def descs(dev, out, sb):
+            d = (pkg.TbDesc * n)()
+            for i in range(n):
+                d[i].tbs, d[i].Qm, d[i].rv, d[i].nof_e_bits, d[i].max_its, d[i].softbuffer, d[i].new_data = tbs, Qm, 0, nbits, 8, sb + i, 1
+                d[i].e_bits = dl[i].data_ptr() if dev else llr[i].ctypes.data
+                d[i].data = out[i].data_ptr() if dev else out[i].ctypes.data
+            return d
+
+        oh = np.zeros((n, stride), np.uint8)
+        dh = descs(False, oh, sb0)
+        f.decode_tbs(dh, 0)
+        od = torch.zeros((n, stride), dtype=torch.uint8, device="cuda")
+        dd = descs(True, od, sb0 + n)
+        f.decode_tbs(dd, pkg.F_DEVICE_IO)
+        o2 = od.cpu().numpy()
+        assert [dh[i].ret for i in range(n)] == [dd[i].ret for i in range(n)]
+        assert [list(dh[i].cb_its) for i in range(n)] == [list(dd[i].cb_its) for i in range(n)]
+        assert (oh[:, : tbs // 8 + 3] == o2[:, : tbs // 8 + 3]).all()
+        ot = C.c_void_p(orc.orc_tb_new())
+        for i in list(range(0, 8)) + list(range(646, 656)) + [n - 1]:      # both sides of the cut
+            orc.orc_tb_reset(ot, tbs)
+            ret, data, crc, its = _oracle_tb(orc, ot, tbs, Qm, 0, nbits, llr[i], 8)
+            assert dd[i].ret == ret and list(dd[i].cb_its) == list(its), i
+            assert (o2[i, : tbs // 8 + 3] == data[: tbs // 8 + 3]).all(), i
+        orc.orc_tb_free(ot)
+        assert sum(1 for i in range(n) if dd[i].ret == 0) > n // 2
+    finally:
+        f.close()
+    g = pkg.FecCuda(0, max_tbs=64)
+    try:
+        sb0 = g.softbuffer_alloc(4 * n)
+        outs = [torch.zeros((n, stride), dtype=torch.uint8, device="cuda") for _ in range(4)]
+        sets = []
+        for k in range(4):
+            d = (pkg.TbDesc * n)()
+            for i in range(n):
+                d[i].tbs, d[i].Qm, d[i].rv, d[i].nof_e_bits, d[i].max_its, d[i].softbuffer, d[i].new_data = tbs, Qm, 0, nbits, 8, sb0 + k * n + i, 1
+                d[i].e_bits, d[i].data = dl[i].data_ptr(), outs[k][i].data_ptr()
+            sets.append(d)
+        tickets = [g.submit_tbs(d, pkg.F_DEVICE_IO) for d in sets]
+        for t in tickets:
+            g.wait(t)
+        for k in range(4):
+            assert [sets[k][i].ret for i in range(n)] == [dd[i].ret for i in range(n)], k
+            assert (outs[k].cpu().numpy()[:, : tbs // 8 + 3] == o2[:, : tbs // 8 + 3]).all(), k
+    finally:
+        g.close()
