@@ -23,6 +23,7 @@ typedef struct {
   uint32_t  *d_step;
   uint16_t  *d_rank;
   uint16_t  *d_ranki[4];      /* the rank table re-based to the start of each redundancy version (16-bit rate de-matcher), built on first use */
+  uint16_t  *d_ranki8[4];     /* the same with byte offsets into an int8 tile (8-bit rate de-matcher) */
   uint32_t   off[4];
   uint32_t   slots;
   uint32_t  *d_pair_addr;     /* packed kernel: decoder-2 address words */
@@ -219,7 +220,7 @@ extern "C" void fec_cuda_destroy(fec_cuda_ctx_t *ctx)
     ktab_t *kt = i < FEC_NOF_K ? &ctx->ktab[i] : i < 2 * FEC_NOF_K ? &ctx->ktab8[i - FEC_NOF_K] : &ctx->ktabm[i / FEC_NOF_K - 2][i % FEC_NOF_K];
     if (!kt->ready) continue;
     cudaFree(kt->d_step); cudaFree(kt->d_rank); cudaFree(kt->d_pair_addr); cudaFree(kt->d_txsrc);
-    for (int r = 0; r < 4; r++) cudaFree(kt->d_ranki[r]);
+    for (int r = 0; r < 4; r++) { cudaFree(kt->d_ranki[r]); cudaFree(kt->d_ranki8[r]); }
     cudaFree(kt->d_pair_crc[0]); cudaFree(kt->d_pair_crc[1]);
   }
   cudaFree(ctx->d_softmax); cudaFree(ctx->d_exact); cudaFree(ctx->d_econt); cudaFreeHost(ctx->h_queue);
@@ -352,21 +353,22 @@ static int ktab_get(fec_cuda_ctx_t *ctx, uint32_t K, ktab_t **out)
  * rotates while staging), else the table re-based to the first LLR of that rv (bulk-copy staging, fec_rm_rx_kernel) */
 static int ktab_rank(fec_cuda_ctx_t *ctx, ktab_t *t, uint32_t rv, const uint16_t **out)
 {
-  if (ctx->llr8) { *out = t->d_rank; return 0; }
-  if (!t->d_ranki[rv]) {
+  uint16_t **slot = ctx->llr8 ? &t->d_ranki8[rv] : &t->d_ranki[rv];
+  if (!*slot) {
     const size_t n = 3 * (size_t)t->g.SS + 16;
     uint16_t *rank = (uint16_t *)malloc(n * 2), *ri = (uint16_t *)malloc(n * 2);
     uint32_t off[4];
     if (!rank || !ri) { free(rank); free(ri); return fail(ctx, FEC_CUDA_ERROR, "out of host memory"); }
     fec_gen_rm_rank(&t->g, rank, off);
     fec_rm_rank_rebase(&t->g, rank, off[rv], ri);
-    cudaError_t e = cudaMalloc(&t->d_ranki[rv], n * 2);
-    if (e == cudaSuccess) e = cudaMemcpy(t->d_ranki[rv], ri, n * 2, cudaMemcpyHostToDevice);
+    if (ctx->llr8) for (size_t i = 0; i < n; i++) ri[i] >>= 1;              /* one byte per LLR in the tile */
+    cudaError_t e = cudaMalloc(slot, n * 2);
+    if (e == cudaSuccess) e = cudaMemcpy(*slot, ri, n * 2, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaStreamSynchronize(cudaStreamLegacy);      /* in place before a non-blocking stream reads it (see ktab_get) */
     free(rank); free(ri);
-    if (e != cudaSuccess) { cudaFree(t->d_ranki[rv]); t->d_ranki[rv] = NULL; return fail(ctx, FEC_CUDA_ENODEV, "rank table: %s", cudaGetErrorString(e)); }
+    if (e != cudaSuccess) { cudaFree(*slot); *slot = NULL; return fail(ctx, FEC_CUDA_ENODEV, "rank table: %s", cudaGetErrorString(e)); }
   }
-  *out = t->d_ranki[rv];
+  *out = *slot;
   return 0;
 }
 

@@ -21,7 +21,9 @@
 #include "fec_kernels.cuh"
 #include <math.h>
 
+#ifndef FE_SEG
 #define FE_SEG      2048          /* symbols per CTA */
+#endif
 #define FE_THREADS  256
 #define FE_BLK_BITS 256           /* scrambling bits produced per jump-table entry */
 

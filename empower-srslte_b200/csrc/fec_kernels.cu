@@ -1145,63 +1145,75 @@ __device__ __forceinline__ uint32_t rm_sext8x2(uint32_t v)
   return __vsub2((v & 0x00FF00FFu) ^ 0x00800080u, 0x00800080u);
 }
 
+__device__ __forceinline__ uint32_t rm_lds_s8(uint32_t addr)
+{
+  uint32_t r;
+  asm volatile("ld.shared.s8 %0, [%1];" : "=r"(r) : "r"(addr));
+  return r;
+}
+
+/* Same structure as fec_rm_rx_kernel on an int8 tile: the slice e[0..E) in the order received behind one bulk copy, one zero
+ * byte behind it, the per-(K, rv) table holding byte offsets into it (ktab_rank halves them). Repeats (E > N) are summed
+ * mod 256 into the tile, which is all the wrapping int8 accumulation keeps of them. */
 __global__ void __launch_bounds__(FEC_RM_THREADS) fec_rm_rx8_kernel(const FecRmDesc *descs, uint32_t *soft_max)
 {
-  extern __shared__ __align__(16) int16_t rm_tile[];
+  extern __shared__ __align__(16) unsigned char rm_smem[];
+  __shared__ __align__(8) unsigned long long rm_mbar;
   const FecRmDesc d = descs[blockIdx.x];
   const int8_t *e8 = reinterpret_cast<const int8_t *>(d.e);
   const int tid = threadIdx.x;
+  const size_t ea = reinterpret_cast<size_t>(e8);
+  const uint32_t delta = (uint32_t)(ea & 15);
+  int8_t *tile = reinterpret_cast<int8_t *>(rm_smem + delta);
+  const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(rm_smem), mb = (uint32_t)__cvta_generic_to_shared(&rm_mbar);
   if (d.E <= d.N) {
-    /* no repetition: a rotated copy, read as 32-bit words (4 LLRs) behind a head that brings the slice to 4-byte alignment,
-     * 4 independent loads in flight per thread; entries never transmitted are 0 */
-    const uint32_t head = min((uint32_t)((4 - (reinterpret_cast<size_t>(e8) & 3)) & 3), d.E);
-    const uint32_t nq = (d.E - head) >> 2;
-    const uint32_t *e32 = reinterpret_cast<const uint32_t *>(e8 + head);
-    for (uint32_t q0 = tid; q0 < nq; q0 += 4 * FEC_RM_THREADS) {
-      uint32_t v[4];
-#pragma unroll
-      for (int u = 0; u < 4; u++) { const uint32_t q = q0 + u * FEC_RM_THREADS; v[u] = q < nq ? __ldg(e32 + q) : 0u; }
-#pragma unroll
-      for (int u = 0; u < 4; u++) {
-        const uint32_t q = q0 + u * FEC_RM_THREADS;
-        if (q < nq) {
-          uint32_t p = head + 4 * q + d.off;
-          if (p >= d.N) p -= d.N;
-#pragma unroll
-          for (int b = 0; b < 4; b++) { rm_tile[p] = (int16_t)(int8_t)(v[u] >> (8 * b)); if (++p == d.N) p = 0; }
-        }
+    const size_t a0 = (ea + 15) & ~(size_t)15, a1 = (ea + (size_t)d.E) & ~(size_t)15;
+    const bool bulk = a1 > a0;
+    const uint32_t nb = bulk ? (uint32_t)(a1 - a0) : 0u;
+    if (tid == 0) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(mb));
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      if (bulk) {
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(mb), "r"(nb) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     :: "r"(sbase + delta + (uint32_t)(a0 - ea)), "l"(a0), "r"(nb), "r"(mb) : "memory");
       }
+      tile[d.E] = 0;
     }
-    for (uint32_t i = tid; i < d.N; i += FEC_RM_THREADS) {
-      if (i >= head && i < head + 4 * nq) continue;
-      uint32_t p = i + d.off;
-      if (p >= d.N) p -= d.N;
-      rm_tile[p] = i < d.E ? (int16_t)__ldg(e8 + i) : (int16_t)0;
+    const uint32_t h = bulk ? (uint32_t)(a0 - ea) : d.E, t0 = bulk ? (uint32_t)(a1 - ea) : d.E;      /* ragged head / tail: < 16 LLRs each */
+    for (uint32_t i = tid; i < h; i += FEC_RM_THREADS) tile[i] = __ldg(e8 + i);
+    for (uint32_t i = t0 + tid; i < d.E; i += FEC_RM_THREADS) tile[i] = __ldg(e8 + i);
+    __syncthreads();
+    if (bulk) {
+      uint32_t ok = 0;
+      while (!ok)
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }" : "=r"(ok) : "r"(mb) : "memory");
     }
   } else {
     for (uint32_t i = tid; i < d.N; i += FEC_RM_THREADS) {
       int acc = 0;
       for (uint32_t j = i; j < d.E; j += d.N) acc += (int)__ldg(e8 + j);    /* repeats accumulate when E > 3K+12 */
-      uint32_t p = i + d.off;
-      if (p >= d.N) p -= d.N;
-      rm_tile[p] = (int16_t)acc;
+      tile[i] = (int8_t)acc;
     }
+    if (tid == 0) tile[d.N] = 0;
+    __syncthreads();
   }
-  if (tid == 0) rm_tile[d.N] = 0;
-  __syncthreads();
   const uint4 *rank4 = reinterpret_cast<const uint4 *>(d.rank);
   uint4 *soft4 = reinterpret_cast<uint4 *>(d.soft);
-  const uint32_t tb = (uint32_t)__cvta_generic_to_shared(rm_tile);
+  const uint32_t tb = (uint32_t)__cvta_generic_to_shared(tile);
+  const uint32_t lim = min(d.E, d.N) * 0x00010001u;           /* offset of the zero byte, in both halves */
   uint32_t mx = 0, mn = 0;
+#pragma unroll 2
   for (int v = tid; v < (int)d.n_out / 8; v += FEC_RM_THREADS) {
     const uint4 rk = __ldg(rank4 + v);
     uint4 old = make_uint4(0, 0, 0, 0);
     if (!d.new_data) old = soft4[v];
-    const uint32_t rw[4] = {rk.x, rk.y, rk.z, rk.w};
+    const uint32_t rw[4] = {__vminu2(rk.x, lim), __vminu2(rk.y, lim), __vminu2(rk.z, lim), __vminu2(rk.w, lim)};
     uint32_t ow[4] = {old.x, old.y, old.z, old.w};
 #pragma unroll
     for (int k = 0; k < 4; k++) {
-      ow[k] = rm_sext8x2(__vadd2(ow[k], __byte_perm(rm_lds_u16(tb + (rw[k] & 0xFFFFu)), rm_lds_u16(tb + (rw[k] >> 16)), 0x5410)));
+      const uint32_t in = __byte_perm(rm_lds_s8(tb + (rw[k] & 0xFFFFu)), rm_lds_s8(tb + (rw[k] >> 16)), 0x5410);
+      ow[k] = d.new_data ? in : rm_sext8x2(__vadd2(ow[k], in));
       mx = __vmaxs2(mx, ow[k]); mn = __vmins2(mn, ow[k]);
     }
     soft4[v] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
@@ -1214,11 +1226,11 @@ __global__ void __launch_bounds__(FEC_RM_THREADS) fec_rm_rx8_kernel(const FecRmD
 cudaError_t fec_launch_rm(const FecRmDesc *descs, uint32_t *soft_max, uint32_t n, uint32_t max_n_out, cudaStream_t st, int llr8, uint32_t max_tile)
 {
   if (n == 0) return cudaSuccess;
+  if (max_tile == 0 || max_tile > max_n_out) max_tile = max_n_out;
   if (llr8) {
-    fec_rm_rx8_kernel<<<n, FEC_RM_THREADS, (size_t)max_n_out * 2, st>>>(descs, soft_max);
+    fec_rm_rx8_kernel<<<n, FEC_RM_THREADS, (size_t)max_tile + 32, st>>>(descs, soft_max);       /* one byte per LLR */
     return cudaGetLastError();
   }
-  if (max_tile == 0 || max_tile > max_n_out) max_tile = max_n_out;
   fec_rm_rx_kernel<<<n, FEC_RM_THREADS, (size_t)max_tile * 2 + 32, st>>>(descs, soft_max);   /* the tile + up to 14 bytes of shift */
   return cudaGetLastError();
 }
