@@ -1105,8 +1105,16 @@ static int submit_common(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, const fec_cuda
    * with two calls) still let rate de-matching and assembly of one overlap the decoder of another. Measured, headline shape,
    * Gbit/s at 1184 / 2368 / 4736 transport blocks per call: sub-batch 592: 57.5 / 58.2 / 57.4; half the call: 57.5 / 62.7 /
    * 66.1; the whole call: 56.1 / 59.2 / 61.0 */
-  /* host buffers: sub-batches are sized by what crosses the link — int8 LLRs are half the bytes per transport block */
-  uint32_t sub = (ctx->llr8 && !syms) ? 2 * ctx->sub_tbs : ctx->sub_tbs;
+  /* host buffers: sub-batches are sized by what crosses the link (FEC_CUDA_SUB_TBS transport blocks of the headline shape,
+   * 90 000 int16 LLRs each = 53 MB by default): int8 LLRs are half the bytes per transport block, 64QAM symbols two thirds */
+  uint32_t sub = ctx->sub_tbs;
+  if (!(flags & FEC_CUDA_F_DEVICE_IO)) {
+    const uint64_t per_tb = syms ? (uint64_t)syms[0].nof_re * (syms[0].csi ? 12 : 8) : (uint64_t)tbs[0].nof_e_bits * (ctx->llr8 ? 1 : 2);
+    if (per_tb) {
+      const uint64_t want = (uint64_t)ctx->sub_tbs * 180000u / per_tb;
+      sub = (uint32_t)(want < 64 ? 64 : want > 8192 ? 8192 : want);
+    }
+  }
   if (flags & FEC_CUDA_F_DEVICE_IO) { sub = ctx->sub_tbs_dev ? ctx->sub_tbs_dev : (n + 1) / 2; if (!ctx->sub_tbs_dev && sub < 592) sub = 592; }
   int rc = 0;
   uint32_t s = 0, off = 0;
