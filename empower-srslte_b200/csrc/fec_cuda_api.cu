@@ -70,7 +70,7 @@ typedef struct { void *h, *d; size_t cap; } stage_t;   /* pinned host + device m
 typedef struct fec_pipe fec_pipe_t;
 
 struct fec_cuda_ctx {
-  int           device, sm_count;
+  int           device, sm_count, grid_sms;   /* grid_sms: CTAs of a pipelined decoder launch (FEC_CUDA_GRID_DIV, experiment) */
   cudaStream_t  stream;
   char          err[256];
   uint64_t      launches;
@@ -180,6 +180,7 @@ extern "C" int fec_cuda_create(fec_cuda_ctx_t **out, int device, uint32_t max_tb
   if (cudaSetDevice(device) != cudaSuccess || cudaGetDeviceProperties(&prop, device) != cudaSuccess) { free(ctx); return FEC_CUDA_ENODEV; }
   if (prop.major < 10) { fprintf(stderr, "libsrslte_fec_cuda: built for sm_100a only, device is sm_%d%d\n", prop.major, prop.minor); free(ctx); return FEC_CUDA_ENODEV; }
   ctx->sm_count = prop.multiProcessorCount;
+  { const char *gd = getenv("FEC_CUDA_GRID_DIV"); const int dv = gd ? atoi(gd) : 1; ctx->grid_sms = ctx->sm_count / (dv > 0 ? dv : 1); if (ctx->grid_sms < 1) ctx->grid_sms = 1; }
   if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { free(ctx); return FEC_CUDA_ENODEV; }
   cudaError_t e = fec_kernels_init();
   if (e != cudaSuccess) { fprintf(stderr, "libsrslte_fec_cuda: kernel image unusable: %s\n", cudaGetErrorString(e)); free(ctx); return FEC_CUDA_ENODEV; }
@@ -934,15 +935,18 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
    * launches it when it sees hand-over counts. Measured on the bench workload (nothing handed over, tools/variants.sh A/B
    * on one box): first + exact kernel 1.69 ms per step, first + certificate + exact 1.78 ms, first alone 1.72-1.78 ms — a
    * third persistent full-shared-memory grid between the sub-batches of the two compute streams costs 4 % even when it
-   * finds nothing to do, while the (empty) exact-kernel launch happens to pace the two streams well and stays */
-  pp->stages = FEC_ST_A | FEC_ST_C | (ctx->eager_ttl > 0 ? FEC_ST_B : 0);
+   * finds nothing to do. Round 2 (CTA timeline, tools/experiments/timeline.py): the empty exact-kernel launch is no better — its
+   * 148 CTAs ask for a whole SM's shared memory each, so on a busy GPU they run only when the decoder of the OTHER stream
+   * starts to drain, and the next decoder launch of this stream, queued behind them and the assembly, came 0.2-0.45 ms late
+   * to fill that tail. Both follow-up kernels are now launched only while recent sub-batches needed them */
+  pp->stages = FEC_ST_A | (ctx->eager_ttl > 0 ? FEC_ST_B | FEC_ST_C : 0);
   pp->ngrp = 0;
   for (int k = 0; k < FEC_NOF_K; k++) {
     if (!grp_cnt[k]) continue;
     FecDecodeArgs a;
     fill_decode_args(ctx, k, &a, (const FecCbDesc *)pp->st_cbd.d, (FecCbStatus *)pp->st_status.d, pp->d_queue, pp->d_softmax, pp->d_exact, pp->d_exact + pp->exact_cap / 12, pp->d_econt,
                      grp_off[k], grp_cnt[k], NULL);
-    CU(fec_launch_decode(a, ctx->sm_count, sc, pp->stages));
+    CU(fec_launch_decode(a, ctx->grid_sms, sc, pp->stages));
     ctx->launches += a.exact_list ? 1 + ((pp->stages & FEC_ST_B) != 0) + ((pp->stages & FEC_ST_C) != 0) : 1;
     if (a.exact_list) { pp->grp[pp->ngrp].k = k; pp->grp[pp->ngrp].off = grp_off[k]; pp->grp[pp->ngrp].cnt = grp_cnt[k]; pp->ngrp++; }
   }
@@ -977,21 +981,27 @@ static int pipe_finish(fec_cuda_ctx_t *ctx, fec_pipe_t *pp)
     /* hand-over counts of the kernels launched so far: run the stages that were left out and turn out to be needed */
     uint64_t ntrk = 0, nexact = 0;
     for (int g = 0; g < pp->ngrp; g++) { ntrk += pp->h_queue[4 * FEC_NOF_K + pp->grp[g].k]; nexact += pp->h_queue[2 * FEC_NOF_K + pp->grp[g].k]; }
-    if (ntrk && !(pp->stages & FEC_ST_B)) {
-      /* certificate kernel now, then the exact kernel once more for what the certificate cannot cover: its first run is
-       * complete, so its work-queue counter and its list start again from zero */
+    const int did_b = (pp->stages & FEC_ST_B) != 0, did_c = (pp->stages & FEC_ST_C) != 0;
+    const int need_b = ntrk && !did_b, need_c = need_b || (nexact && !did_c);
+    if (need_c) {
+      /* certificate kernel now (if it was left out and is needed), then the exact kernel for what neither packed variant
+       * covers. If the exact kernel already ran in the first pass, that run is complete: its work-queue counter and its list
+       * start again from zero; if it was left out, its list holds the first kernel's hand-overs and the certificate kernel
+       * appends to it */
       cudaStream_t sc = ctx->s_comp[0];
-      ctx->path_cnt[1] += nexact;
+      if (did_c) ctx->path_cnt[1] += nexact;
       CU(cudaEventRecord(pp->ev[0], sc));                  /* the events of the first pass have been read above */
       for (int g = 0; g < pp->ngrp; g++) {
         const int k = pp->grp[g].k;
-        CU(cudaMemsetAsync(pp->d_queue + 2 * k + 1, 0, sizeof(unsigned int), sc));
-        CU(cudaMemsetAsync(pp->d_queue + 2 * FEC_NOF_K + k, 0, sizeof(unsigned int), sc));
+        if (did_c) {
+          CU(cudaMemsetAsync(pp->d_queue + 2 * k + 1, 0, sizeof(unsigned int), sc));
+          CU(cudaMemsetAsync(pp->d_queue + 2 * FEC_NOF_K + k, 0, sizeof(unsigned int), sc));
+        }
         FecDecodeArgs a;
         fill_decode_args(ctx, k, &a, (const FecCbDesc *)pp->st_cbd.d, (FecCbStatus *)pp->st_status.d, pp->d_queue, pp->d_softmax, pp->d_exact,
                          pp->d_exact + pp->exact_cap / 12, pp->d_econt, pp->grp[g].off, pp->grp[g].cnt, NULL);
-        CU(fec_launch_decode(a, ctx->sm_count, sc, FEC_ST_B | FEC_ST_C));
-        ctx->launches += 2;
+        CU(fec_launch_decode(a, ctx->sm_count, sc, (need_b ? FEC_ST_B : 0) | FEC_ST_C));
+        ctx->launches += 1 + need_b;
       }
       CU(cudaEventRecord(pp->ev[1], sc));
       if (pp->ntb) { CU(fec_launch_tb_assemble((const FecTbDesc *)pp->st_tbd.d, (const FecCbStatus *)pp->st_status.d, ctx->d_r24a, pp->ntb, sc)); ctx->launches++; }
@@ -1006,7 +1016,7 @@ static int pipe_finish(fec_cuda_ctx_t *ctx, fec_pipe_t *pp)
         if (cudaEventElapsedTime(&ms, pp->ev[1], pp->ev[2]) == cudaSuccess) ctx->phase_ms[2] += ms; }
     }
     /* launch policy of the next sub-batches */
-    if (ntrk) ctx->eager_ttl = 16; else if (ctx->eager_ttl > 0) ctx->eager_ttl--;
+    if (ntrk || nexact) ctx->eager_ttl = 16; else if (ctx->eager_ttl > 0) ctx->eager_ttl--;
   }
   if (pp->ncb) path_count_add(ctx, pp->h_queue);
   if (pp->syms && !pp->dev_io)

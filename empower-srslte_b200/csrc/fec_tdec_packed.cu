@@ -74,6 +74,9 @@ __device__ __forceinline__ void pk_sts_u16(uint32_t addr, uint32_t val)
 #ifndef PK_LATE_ZERO
 #define PK_LATE_ZERO 1
 #endif
+#ifndef PK_TIMELINE
+#define PK_TIMELINE 0
+#endif
 #ifndef PK_PF_BETA
 #define PK_PF_BETA 0
 #endif
@@ -850,6 +853,24 @@ __device__ __forceinline__ bool pk_certificate(uint32_t ahi, uint32_t alo, uint3
   return 2 * R + 6 * G <= 32767 && Ra + Rb + 5 * G <= 32767 && 10000 + Rb + 5 * G <= 32767 && max(v0, v1) <= 32767;
 }
 
+#if PK_TIMELINE
+/* diagnosis build only (tools/experiments/timeline.py): start / queue-empty / end time of every CTA of the first kernel */
+__device__ unsigned long long pk_tl_buf[6 * 16384];
+__device__ unsigned int pk_tl_n;
+__device__ __forceinline__ unsigned long long pk_gtime() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+extern "C" int fec_cuda_debug_timeline(unsigned long long *out, unsigned int cap)
+{
+  unsigned int n = 0;
+  cudaMemcpyFromSymbol(&n, pk_tl_n, sizeof(n));
+  if (n > 16384) n = 16384;
+  if (n > cap) n = cap;
+  cudaMemcpyFromSymbol(out, pk_tl_buf, sizeof(unsigned long long) * 6 * n);
+  unsigned int z = 0;
+  cudaMemcpyToSymbol(pk_tl_n, &z, sizeof(z));
+  return (int)n;
+}
+#endif
+
 /* ---------------------------------------------------------------- the kernel ---- */
 /* shared memory: [Tlo, Thi: TPC*Lw halfwords each][E: nslots x (TPC*Lw+1) words][bit rows: nslots x P x nw1 words] */
 size_t fec_pk_smem_bytes(const fec_geom_t *g)
@@ -865,6 +886,9 @@ template <int P, bool VEC, bool TRK>
 __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const FecDecodeArgs a)
 {
   if (TRK) { if (*a.list_count == 0) return; }
+#if PK_TIMELINE
+  unsigned long long tl0 = pk_gtime(), tl1 = 0;
+#endif
   constexpr int TPC = P / 2, CPW = 32 / TPC;
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ uint32_t s_tmem;
@@ -911,7 +935,13 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
       unsigned q = 0;
       if (j == 0) q = atomicAdd(a.queue, 1u);
       q = __shfl_sync(gmask, q, g * TPC);
-      if (q >= (TRK ? *a.list_count : a.ncb)) { exhausted = true; break; }
+      if (q >= (TRK ? *a.list_count : a.ncb)) {
+        exhausted = true;
+#if PK_TIMELINE
+        if (!tl1) tl1 = pk_gtime();
+#endif
+        break;
+      }
       const unsigned qi = q;
       if (TRK) q = a.list[q];
 #if PK_OPT_DESC
@@ -1035,6 +1065,16 @@ __global__ void __launch_bounds__(FEC_PK_WARPS * 32, 1) fec_tdec_pk_kernel(const
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" :: "r"(s_tmem) : "memory");
+#if PK_TIMELINE
+  if (!TRK && tid == 0) {
+    unsigned smid; asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+    const unsigned i = atomicAdd(&pk_tl_n, 1u);
+    if (i < 16384) {
+      unsigned long long *r = pk_tl_buf + 6 * (size_t)i;
+      r[0] = (unsigned long long)(size_t)a.queue; r[1] = smid; r[2] = tl0; r[3] = tl1; r[4] = pk_gtime(); r[5] = blockIdx.x;
+    }
+  }
+#endif
 }
 
 template <int P, bool TRK>
