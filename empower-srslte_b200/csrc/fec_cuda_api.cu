@@ -107,6 +107,7 @@ struct fec_cuda_ctx {
   uint32_t     *d_x2masks, *d_x1states;   /* front end: scrambling-sequence jump tables (fec_frontend.cu) */
   float         fe_ms;          /* device time of the front-end kernels of the last call */
   uint64_t      path_cnt[2];    /* last call: code blocks handed to the certificate kernel / to the exact kernel */
+  int           eager_c_ttl;    /* the same for the exact kernel behind both */
   int           eager_ttl;      /* > 0: recent sub-batches handed blocks to the certificate kernel: launch it right behind the first
                                    kernel instead of after the host has seen the hand-over counts (pipe_finish) */
   unsigned int *h_queue;        /* pinned mirror of d_queue (fec_cuda_decode_cbs) */
@@ -939,7 +940,7 @@ static int pipe_submit(fec_cuda_ctx_t *ctx, fec_pipe_t *pp, fec_cuda_tb_t *tbs, 
    * 148 CTAs ask for a whole SM's shared memory each, so on a busy GPU they run only when the decoder of the OTHER stream
    * starts to drain, and the next decoder launch of this stream, queued behind them and the assembly, came 0.2-0.45 ms late
    * to fill that tail. Both follow-up kernels are now launched only while recent sub-batches needed them */
-  pp->stages = FEC_ST_A | (ctx->eager_ttl > 0 ? FEC_ST_B | FEC_ST_C : 0);
+  pp->stages = FEC_ST_A | (ctx->eager_ttl > 0 ? FEC_ST_B : 0) | (ctx->eager_c_ttl > 0 ? FEC_ST_C : 0);
   pp->ngrp = 0;
   for (int k = 0; k < FEC_NOF_K; k++) {
     if (!grp_cnt[k]) continue;
@@ -1016,7 +1017,8 @@ static int pipe_finish(fec_cuda_ctx_t *ctx, fec_pipe_t *pp)
         if (cudaEventElapsedTime(&ms, pp->ev[1], pp->ev[2]) == cudaSuccess) ctx->phase_ms[2] += ms; }
     }
     /* launch policy of the next sub-batches */
-    if (ntrk || nexact) ctx->eager_ttl = 16; else if (ctx->eager_ttl > 0) ctx->eager_ttl--;
+    if (ntrk) ctx->eager_ttl = 16; else if (ctx->eager_ttl > 0) ctx->eager_ttl--;
+    if (nexact) ctx->eager_c_ttl = 16; else if (ctx->eager_c_ttl > 0) ctx->eager_c_ttl--;
   }
   if (pp->ncb) path_count_add(ctx, pp->h_queue);
   if (pp->syms && !pp->dev_io)
@@ -1111,10 +1113,11 @@ static int submit_common(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, const fec_cuda
   /* host buffers: small sub-batches so that the PCIe copy of one overlaps the kernels of the previous (the copy is
    * the longer of the two); device buffers: nothing to overlap but host-side descriptor work, so few, large ones */
   /* device buffers: a decoder launch ends with a tail in which each CTA waits for the slowest of its 16 code blocks (about
-   * 0.2 ms whatever the launch size), so launches are as large as possible while two sub-batches per call (four in flight
-   * with two calls) still let rate de-matching and assembly of one overlap the decoder of another. Measured, headline shape,
-   * Gbit/s at 1184 / 2368 / 4736 transport blocks per call: sub-batch 592: 57.5 / 58.2 / 57.4; half the call: 57.5 / 62.7 /
-   * 66.1; the whole call: 56.1 / 59.2 / 61.0 */
+   * 0.2 ms of SM time whatever the launch size; the next launch fills the SMs as they are released, but the slots of a
+   * draining CTA idle), so launches are large: two sub-batches per call of at least 1184 transport blocks each — two rather
+   * than one so that a single blocking call still overlaps the rate de-matching of its second half with the decoder of the
+   * first. Measured, headline shape, Gbit/s with two calls in flight at 1184 / 4736 transport blocks per call: sub-batches
+   * of 296: 55.6 / -; 592: 61.5 / 63.6; 1184: 64.5 / 67.5; 2368: - / 69.0; 4736: - / 68.9 */
   /* host buffers: sub-batches are sized by what crosses the link (FEC_CUDA_SUB_TBS transport blocks of the headline shape,
    * 90 000 int16 LLRs each = 53 MB by default): int8 LLRs are half the bytes per transport block, 64QAM symbols two thirds */
   uint32_t sub = ctx->sub_tbs;
@@ -1125,7 +1128,7 @@ static int submit_common(fec_cuda_ctx_t *ctx, fec_cuda_tb_t *tbs, const fec_cuda
       sub = (uint32_t)(want < 64 ? 64 : want > 8192 ? 8192 : want);
     }
   }
-  if (flags & FEC_CUDA_F_DEVICE_IO) { sub = ctx->sub_tbs_dev ? ctx->sub_tbs_dev : (n + 1) / 2; if (!ctx->sub_tbs_dev && sub < 592) sub = 592; }
+  if (flags & FEC_CUDA_F_DEVICE_IO) { sub = ctx->sub_tbs_dev ? ctx->sub_tbs_dev : (n + 1) / 2; if (!ctx->sub_tbs_dev && sub < 1184) sub = 1184; }
   int rc = 0;
   uint32_t s = 0, off = 0;
   while (off < n && !rc) {

@@ -78,7 +78,7 @@ typedef struct {
 /* device: CUDA ordinal. max_tbs_per_call bounds the staging buffers (pinned host + device).
  * Environment read at creation (tuning and diagnosis, none is needed): FEC_CUDA_SUB_TBS = transport blocks per pipelined
  * sub-batch of a call with host buffers (default 296; twice that for int8 LLRs: sub-batches are sized by what crosses the
- * link); FEC_CUDA_SUB_TBS_DEV = the same with FEC_CUDA_F_DEVICE_IO (default: two sub-batches per call, at least 592 each —
+ * link); FEC_CUDA_SUB_TBS_DEV = the same with FEC_CUDA_F_DEVICE_IO (default: two sub-batches per call, at least 1184 each —
  * decoder launches as large as possible); FEC_CUDA_TRACE=1 prints the device timeline of every sub-batch to
  * stderr; FEC_CUDA_FORCE_EXACT=1 sends every code block to the exact 32-bit kernels. */
 int  fec_cuda_create(fec_cuda_ctx_t **ctx, int device, uint32_t max_tbs_per_call);
