@@ -238,7 +238,7 @@ def fill_descs(pkg, d, n, e_ptr0, data_ptr0, sb0, new_data=1):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=None, help="timed steps (default 40; 10 for --impl reference, whose step is ~4.6 s of CPU work)")
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=4736, help="transport blocks per GPU per step (default 32 per SM = 61 568 code blocks)")
@@ -260,6 +260,8 @@ def main():
     ap.add_argument("--sigma-sym", type=float, default=0.062, help="AWGN std per real dimension of the synthetic 64QAM symbols")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.steps is None:
+        args.steps = 10 if args.impl == "reference" else 40
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
