@@ -1038,6 +1038,19 @@ __device__ __forceinline__ void fec_softmax_commit(uint32_t *dst, int amax)
 #define RM_UNROLL 2
 #endif
 constexpr int kRmUnroll = RM_UNROLL;
+#ifndef RM_STREAM_ST
+#define RM_STREAM_ST 1
+#endif
+/* the slot leaves with a streaming store (evict-first in L2): it is read again only when its code block's turn comes in the
+ * decoder, long after 1 GB of other slots has gone by — until then it should not push the running decoder's rows out of L2 */
+__device__ __forceinline__ void rm_store_slot(uint4 *p, uint4 v)
+{
+#if RM_STREAM_ST
+  asm volatile("st.global.cs.v4.u32 [%0], {%1, %2, %3, %4};" :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+#else
+  *p = v;
+#endif
+}
 __device__ __forceinline__ uint32_t rm_lds_u16(uint32_t addr)
 {
   uint32_t r;
@@ -1115,7 +1128,7 @@ __global__ void __launch_bounds__(FEC_RM_THREADS) fec_rm_rx_kernel(const FecRmDe
         ow[k] = __byte_perm(rm_lds_u16(tb + (rw[k] & 0xFFFFu)), rm_lds_u16(tb + (rw[k] >> 16)), 0x5410);
         mx = __vmaxs2(mx, ow[k]); mn = __vmins2(mn, ow[k]);
       }
-      soft4[v] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+      rm_store_slot(soft4 + v, make_uint4(ow[0], ow[1], ow[2], ow[3]));
     }
   } else {
 #pragma unroll 2
@@ -1129,7 +1142,7 @@ __global__ void __launch_bounds__(FEC_RM_THREADS) fec_rm_rx_kernel(const FecRmDe
         ow[k] = __vadd2(ow[k], __byte_perm(rm_lds_u16(tb + (rw[k] & 0xFFFFu)), rm_lds_u16(tb + (rw[k] >> 16)), 0x5410));
         mx = __vmaxs2(mx, ow[k]); mn = __vmins2(mn, ow[k]);
       }
-      soft4[v] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+      rm_store_slot(soft4 + v, make_uint4(ow[0], ow[1], ow[2], ow[3]));
     }
   }
   const int hi = max((int)(short)(mx & 0xFFFFu), (int)(short)(mx >> 16)), lo = min((int)(short)(mn & 0xFFFFu), (int)(short)(mn >> 16));
@@ -1216,7 +1229,7 @@ __global__ void __launch_bounds__(FEC_RM_THREADS) fec_rm_rx8_kernel(const FecRmD
       ow[k] = d.new_data ? in : rm_sext8x2(__vadd2(ow[k], in));
       mx = __vmaxs2(mx, ow[k]); mn = __vmins2(mn, ow[k]);
     }
-    soft4[v] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+    rm_store_slot(soft4 + v, make_uint4(ow[0], ow[1], ow[2], ow[3]));
   }
   const int hi = max((int)(short)(mx & 0xFFFFu), (int)(short)(mx >> 16)), lo = min((int)(short)(mn & 0xFFFFu), (int)(short)(mn >> 16));
   fec_softmax_commit(soft_max + d.slot, max(hi, -lo));
