@@ -74,6 +74,9 @@ __device__ __forceinline__ void pk_sts_u16(uint32_t addr, uint32_t val)
 #ifndef PK_LATE_ZERO
 #define PK_LATE_ZERO 1
 #endif
+#ifndef PK_DIAG_NOLOAD
+#define PK_DIAG_NOLOAD 0
+#endif
 #ifndef PK_TIMELINE
 #define PK_TIMELINE 0
 #endif
@@ -279,6 +282,13 @@ struct PkRaw { uint32_t s[8], y[8]; };
 template <bool FULL, bool VEC>
 __device__ __forceinline__ void pk_load_raw(const PkView &v, int k0, int i0, PkRaw &r)
 {
+#if PK_DIAG_NOLOAD      /* timing diagnosis only: what would the kernel cost if the stream loads were free (results are garbage) */
+  if (FULL && VEC) {
+#pragma unroll
+    for (int i = 0; i < 8; i++) { r.y[i] = (uint32_t)((k0 + i) & 3) * 0x00010001u; r.s[i] = (uint32_t)((k0 + 2 * i) & 3) * 0x00010001u; }
+    return;
+  }
+#endif
   if (FULL && VEC) {
     const int w0 = (k0 >> 2) * v.tpc4;
     const uint4 y0 = pk_ldg128(v.Yrow + w0), y1 = pk_ldg128(v.Yrow + w0 + v.tpc4);
