@@ -237,3 +237,39 @@ def test_device_call_cut_into_two_sub_batches_and_calls_in_flight(orc):
             assert (outs[k].cpu().numpy()[:, : tbs // 8 + 3] == o2[:, : tbs // 8 + 3]).all(), k
     finally:
         g.close()
+
+
+def test_tb_path_exact_kernel_deferred_then_eager(orc):
+    """LLR amplitudes beyond the reach of both packed kernels (max|soft| > 2250): every code block ends up in the exact
+    kernel. On a fresh context the exact kernel is not launched with the sub-batch (nothing needed it recently): the host
+    launches it when the hand-over counts come back, then eagerly for the following calls. Both ways must give the oracle's
+    bits, iteration counts and return codes; a last call with ordinary amplitudes takes the fast path again."""
+    tbs, Qm, nbits, n = 6200, 2, 7200, 6
+    rng = np.random.default_rng(77)
+    payload = rng.integers(0, 256, (n, tbs // 8), dtype=np.uint8)
+    e = synth.encode_tbs(payload, tbs, Qm, 0, nbits)
+    f = pkg.FecCuda(0, max_tbs=16)
+    try:
+        sb0 = f.softbuffer_alloc(n)
+        ot = C.c_void_p(orc.orc_tb_new())
+        for call, amp in enumerate((3000.0, 3000.0, 2600.0, 100.0)):
+            llr = synth.awgn_llr(e, 0.8, rng, amp=amp)
+            out = np.zeros((n, tbs // 8 + 3 + 768), np.uint8)
+            d = (pkg.TbDesc * n)()
+            for i in range(n):
+                d[i].tbs, d[i].Qm, d[i].rv, d[i].nof_e_bits, d[i].max_its, d[i].softbuffer, d[i].new_data = tbs, Qm, 0, nbits, 8, sb0 + i, 1
+                d[i].e_bits, d[i].data = llr[i].ctypes.data, out[i].ctypes.data
+            f.decode_tbs(d, 0)
+            paths = f.last_path_counts()
+            if amp > 2500:
+                assert paths[1] > 0, (call, paths)          # the exact kernel did the work
+            else:
+                assert paths == (0, 0) or list(paths) == [0, 0], (call, paths)
+            for i in range(n):
+                orc.orc_tb_reset(ot, tbs)
+                ret, dd, crc, its = _oracle_tb(orc, ot, tbs, Qm, 0, nbits, llr[i], 8)
+                assert d[i].ret == ret and list(d[i].cb_its) == list(its) and list(d[i].cb_crc) == list(crc), (call, i)
+                assert (out[i, : tbs // 8 + 3] == dd[: tbs // 8 + 3]).all(), (call, i)
+        orc.orc_tb_free(ot)
+    finally:
+        f.close()
