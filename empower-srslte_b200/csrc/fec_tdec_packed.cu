@@ -74,6 +74,9 @@ __device__ __forceinline__ void pk_sts_u16(uint32_t addr, uint32_t val)
 #ifndef PK_LATE_ZERO
 #define PK_LATE_ZERO 1
 #endif
+#ifndef PK_NORM8
+#define PK_NORM8 0
+#endif
 #ifndef PK_DIAG_NOLOAD
 #define PK_DIAG_NOLOAD 0
 #endif
@@ -379,7 +382,7 @@ __device__ __forceinline__ void pk_beta_chunk(uint32_t *o, const uint32_t *xs, c
   for (int i = 7; i >= 0; i--) {
     if (FULL || i >= i0) {
       if (MIX) { pk_beta_s(o, pk_gammas(xs[i], ys[i])); if ((i & 3) == 0) pk_norm_s(o); }
-      else { pk_beta(o, xs[i], ys[i]); if ((i & 3) == 0) pk_norm(o); }
+      else { pk_beta(o, xs[i], ys[i]); if (PK_NORM8 ? i == 0 : (i & 3) == 0) pk_norm(o); }
       if (FULL && i == 0) pk_ck_store(ck_addr, o);
     }
   }
@@ -432,7 +435,7 @@ __device__ __forceinline__ void pk_alpha_chunk(const PkView &v, int k0, uint32_t
         for (int s = 0; s < 8; s++) bb[i][s] = b[s];                      /* beta[k0+i] as the reference stores it */
         if (((i + kpar) & 1) == 0) pk_norm(b);
       } else {
-        if (i == 4) pk_norm(b);
+        if (!PK_NORM8 && i == 4) pk_norm(b);
 #pragma unroll
         for (int s = 0; s < 8; s++) bb[i][s] = b[s];
       }
@@ -477,7 +480,7 @@ __device__ __forceinline__ void pk_alpha_chunk(const PkView &v, int k0, uint32_t
 #pragma unroll
       for (int s = 0; s < 8; s++) o[s] = MIX ? pk_max_u(m[s], n[s]) : pk_max(m[s], n[s]);
       if (TRK) { if ((((i + kpar) & 1) == 0) && (k0 + i != 0)) pk_norm_trk(o, acc.ta); }
-      else if ((i & 3) == 3) { if (MIX) pk_norm_s(o); else pk_norm(o); }
+      else if (PK_NORM8 && !MIX ? i == 7 : (i & 3) == 3) { if (MIX) pk_norm_s(o); else pk_norm(o); }
     } else { acc.wlo = acc.wlo * 2u + 0xFFFFFFFFu; acc.whi = acc.whi * 2u + 0xFFFFFFFFu; }   /* a zero bit for a step that does not exist */
   }
 }
