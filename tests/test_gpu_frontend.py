@@ -265,3 +265,34 @@ def test_decode_syms_ul_mixed_control_layouts_in_one_batch(fec, orc):
         assert d[i].ret == ret and list(d[i].cb_its) == list(its) and list(d[i].cb_crc) == list(crc), (i, order[i])
         assert (outs[i][: tbs // 8 + 3] == data[: tbs // 8 + 3]).all(), (i, order[i])
         assert ret == 0 and (outs[i][: tbs // 8] == payload[i]).all(), (i, order[i])
+
+
+@pytest.mark.parametrize("cols,ack_cols,ri_cols", [(11, (2, 3, 8, 9), (1, 4, 7, 10)),      # normal CP, last symbol taken by SRS
+                                                    (10, (1, 2, 6, 7), (0, 3, 5, 8)),      # extended CP (uci.c:499-546)
+                                                    (9, (1, 2, 6, 7), (0, 3, 5, 8))])      # extended CP with SRS
+def test_decode_syms_ul_other_column_counts(fec, orc, cols, ack_cols, ri_cols):
+    """the UL tile is FE_SEG / cols whole rows of the channel interleaver: every column count LTE has, not only the 12 of the
+    bench (rows per tile, run lengths of the scrambling words and the transpose all depend on it)"""
+    tbs, mod, prb, n_ack_sym, n_ri_sym, n_cqi = 15264, 4, 50, 8, 4, 24
+    rows = 12 * prb
+    rng = np.random.default_rng(100 + cols)
+    ack_pos = _fe.uci_positions(n_ack_sym, mod, rows, ack_cols)
+    ri_pos = _fe.uci_positions(n_ri_sym, mod, rows, ri_cols)
+    c_init = synth.cinit_pusch(0x77, 8, 5)
+    ntb = 3
+    payload = rng.integers(0, 256, (ntb, tbs // 8), dtype=np.uint8)
+    sym, G = _fe.make_ul(payload, tbs, mod, 0, prb, cols, c_init, 0.14, rng, ri_pos, n_cqi)
+    sb0 = fec.softbuffer_alloc(ntb)
+    items = [dict(sym=sym[i], mod=mod, c_init=c_init, nof_symb=cols, ack_pos=ack_pos, ri_pos=ri_pos, n_cqi=n_cqi, nof_e_bits=G, rv=0) for i in range(ntb)]
+    d, outs, ucis = _run_syms(fec, tbs, mod, items, True, sb0)
+    for i in range(ntb):
+        g, raw = _fe.oracle_frontend(orc, sym[i], mod, c_init, None, cols, ack_pos, ri_pos)
+        assert (ucis[i][: raw.size] == raw).all(), i
+        assert (ucis[i][raw.size: raw.size + n_cqi] == g[:n_cqi]).all(), i
+        ot = C.c_void_p(orc.orc_tb_new())
+        orc.orc_tb_reset(ot, tbs)
+        ret, data, crc, its = _oracle_decode(orc, ot, tbs, mod, 0, g[n_cqi: n_cqi + G])
+        orc.orc_tb_free(ot)
+        assert d[i].ret == ret and list(d[i].cb_its) == list(its) and list(d[i].cb_crc) == list(crc)
+        assert (outs[i][: tbs // 8 + 3] == data[: tbs // 8 + 3]).all()
+        assert ret == 0 and (outs[i][: tbs // 8] == payload[i]).all()
