@@ -74,6 +74,9 @@ __device__ __forceinline__ void pk_sts_u16(uint32_t addr, uint32_t val)
 #ifndef PK_LATE_ZERO
 #define PK_LATE_ZERO 1
 #endif
+#ifndef PK_TAIL_EARLY
+#define PK_TAIL_EARLY 1
+#endif
 #ifndef PK_NORM8
 #define PK_NORM8 0
 #endif
@@ -517,6 +520,13 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
   tb.hi = 0; tb.lo = 0;
   if (TRK) { acc.ta.hi = 0; acc.ta.lo = 0; acc.vmx = 0x80008000u; acc.vmn = 0x7FFF7FFFu; }
 
+#if PK_TAIL_EARLY
+  /* the 3 tail steps' (x, y) pairs, 12 bytes behind the streams (4-byte aligned): asked for now, used after the beta warm-up
+   * (loaded where they are used, every half-iteration waited out a global-memory latency there: 0.6 % of the kernel) */
+  uint32_t tw[3];
+#pragma unroll
+  for (int k = 0; k < 3; k++) tw[k] = pk_ldg32(reinterpret_cast<const uint32_t *>(tail) + k);
+#endif
   /* pull this half-iteration's rows (first touch comes from HBM) and the next one's towards L2 */
   for (int off = j * 28; off < L * TPC; off += TPC * 32) {      /* each of the TPC threads takes every TPC-th 128-byte line */
     asm volatile("prefetch.global.L2 [%0];" :: "l"(v.Yrow + off));
@@ -558,8 +568,13 @@ __device__ __forceinline__ void pk_half_iteration(const PkView &v, int L, uint32
     t[0] = 0;
 #pragma unroll
     for (int i = 1; i < 8; i++) t[i] = -10000;
+#pragma unroll
     for (int k = 2; k >= 0; k--) {
+#if PK_TAIL_EARLY
+      const int tx = (short)(tw[k] & 0xFFFFu), ty = (short)(tw[k] >> 16);
+#else
       const int tx = tail[2 * k], ty = tail[2 * k + 1];
+#endif
       const int txy = (short)(tx + ty);
       int nn[8];
       nn[0] = max((int)(short)(t[4] + txy), t[0]);
