@@ -206,7 +206,7 @@ def reference_main(args, rank, world):
     ntb = max(cpu_cores() * 4, 32)
     llr = np.empty((ntb, NBITS), np.int16)
     make_llrs(ntb, args.sigma, 1234, llr)
-    per_step_budget = min(20.0, 150.0 / max(args.steps + args.warmup, 1))
+    per_step_budget = min(20.0, args.ref_seconds / max(args.steps + args.warmup, 1))
     vals = []
     last = None
     for s in range(args.warmup + args.steps):
@@ -251,6 +251,7 @@ def main():
     ap.add_argument("--no-harq", action="store_true", help="skip the HARQ leg (BASELINE configs[2])")
     ap.add_argument("--sigma-harq", type=float, default=0.47, help="AWGN std of the HARQ leg (rv 0 mostly fails)")
     ap.add_argument("--sustain", type=float, default=2.0, help="seconds of the sustained leg (0 = skip)")
+    ap.add_argument("--ref-seconds", type=float, default=150.0, help="--impl reference: CPU time budget of the whole run (bounded samples per step)")
     ap.add_argument("--no-llr8", action="store_true", help="skip the 8-bit LLR leg")
     ap.add_argument("--no-grid", action="store_true", help="skip the sigma grid (int16 and int8 paths at sigma 0.30 / 0.40 / 0.45)")
     ap.add_argument("--sigma8", type=float, default=0.30, help="AWGN std of the 8-bit LLR leg")
