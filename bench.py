@@ -396,428 +396,6 @@ def main():
     h2d = B * NBITS * 2 + B * C_CB * (32 + 48) + B * 520
     d2h = B * (((TBS // 8 + 3 + 768 + 15) // 16) * 16) + B * C_CB * 8 + B * 4
 
-    # ---- front-end leg: the same transport blocks given as equalised 64QAM symbols (8 B per resource element
-    #      instead of 12 B of LLRs); soft demodulation + descrambling run in the fused front-end kernel on the device ----
-    front, ulsch5 = None, None
-    if not args.no_symbols:
-        synth = importlib.import_module("empower-srslte_b200.synth")
-        nre = NBITS // QM
-        h_sym = pkg.PinnedArray((B, nre, 2), np.float32)
-        rng = np.random.default_rng(5000 + rank)
-        ncw = payload.shape[0]
-        c_inits = [synth.cinit_pdsch(0x1000 + k, 0, 2 * (k % 10), 1) for k in range(ncw)]
-        e = synth.encode_tbs(payload, TBS, QM, RV, NBITS)
-        cw_sym = np.stack([synth.modulate(e[k] ^ synth.gold_sequence(c_inits[k], NBITS), QM) for k in range(ncw)])
-        for i0 in range(0, B, 64):
-            i1 = min(B, i0 + 64)
-            h_sym.a[i0:i1] = synth.awgn_symbols(cw_sym[np.arange(i0, i1) % ncw], args.sigma_sym, rng)
-        d_sym = torch.from_numpy(h_sym.a).to(f"cuda:{local_rank}")
-        sy_ab = []
-        for dev in (True, False):
-            sets = []
-            for s_ in range(2):
-                sd = (pkg.SymDesc * B)()
-                base = d_sym.data_ptr() if dev else h_sym.a.ctypes.data
-                for i in range(B):
-                    sd[i].symbols, sd[i].nof_re, sd[i].mod_bits, sd[i].c_init = base + i * nre * 8, nre, QM, c_inits[i % ncw]
-                sets.append(sd)
-            sy_ab.append(sets)
-
-        def timed_syms(tb_sets, sym_sets, flags, steps, f=None, st=None):
-            f, st = f or fec, st or stream
-            barrier()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record(st)
-            prev = None
-            for i in range(steps):
-                t = f.submit_syms(tb_sets[i & 1], sym_sets[i & 1], flags)
-                if prev is not None:
-                    f.wait(prev)
-                prev = t
-            f.wait(prev)
-            e1.record(st)
-            barrier()
-            return shard.reduce_job(dist if world > 1 else None, f"cuda:{local_rank}", e0.elapsed_time(e1))[0]
-
-        for i in range(6):
-            fec.decode_syms(dd_ab[i & 1], sy_ab[0][i & 1], pkg.F_DEVICE_IO)
-        ms_sd = timed_syms(dd_ab, sy_ab[0], pkg.F_DEVICE_IO, args.steps)
-        ok_s, its_s = tally(dd)
-        fec.decode_syms(dd, sy_ab[0][0], pkg.F_DEVICE_IO | pkg.F_SERIAL)
-        fe_ms = fec.last_frontend_ms()
-        ph_s = fec.last_phase_ms()
-        path_s = fec.last_path_counts()
-        out_host = d_out[0].cpu().numpy()
-        bad = sum(1 for i in range(B) if dd[i].ret == 0 and not (out_host[i, :TBS // 8] == payload[i % ncw]).all())
-        if bad:
-            raise SystemExit(f"bench.py: {bad} CRC-passing transport blocks of the symbol leg differ from the transmitted payload")
-        for i in range(6):
-            fec.decode_syms(hd_ab[i & 1], sy_ab[1][i & 1], 0)
-        ms_sh = timed_syms(hd_ab, sy_ab[1], 0, args.steps)
-        ok_sh, _ = tally(hd)
-        fe_bytes = B * (nre * 8 + NBITS * 2)
-        front = dict(workload="same TBs as 64QAM symbols (15000 RE), soft demodulation + descrambling on the device",
-                     sigma_sym=args.sigma_sym, value=allsum(ok_s) * TBS * args.steps / (ms_sd / 1e3) / 1e9, unit=UNIT,
-                     ms_per_step=ms_sd / args.steps, tb_ok_frac=allsum(ok_s) / (world * B), halfits_per_cb=allsum(its_s) / (world * B * C_CB),
-                     e2e=dict(value=allsum(ok_sh) * TBS * args.steps / (ms_sh / 1e3) / 1e9, unit=UNIT, ms_per_step=ms_sh / args.steps,
-                              h2d_bytes_per_step=B * nre * 8 + B * C_CB * (32 + 48) + B * (520 + 80), d2h_bytes_per_step=d2h,
-                              frac_of_h2d_link=(B * nre * 8 + B * C_CB * (32 + 48) + B * (520 + 80)) / (ms_sh / args.steps / 1e3) / 1e9 / link_min),
-                     code_blocks_by_kernel=dict(total=B * C_CB, certificate_variant=path_s[0], exact=path_s[1]),
-                     serial_phases_ms=dict(frontend=fe_ms, rate_dematch=ph_s[0], turbo_decode=ph_s[1], tb_assemble_crc24a=ph_s[2]),
-                     frontend_kernel=dict(ms_per_launch=fe_ms, algorithmic_bytes=fe_bytes, achieved=fe_bytes / (fe_ms / 1e3) / 1e9,
-                                          peak=peaks()["hbm_gbs"], unit="GB/s", frac=fe_bytes / (fe_ms / 1e3) / 1e9 / peaks()["hbm_gbs"], bound="hbm"))
-        # ---- uplink leg (BASELINE configs[4] shape per cell-subframe): PUSCH from the demodulator on — 16QAM (what
-        #      srsENB grants, phch_worker.cc:598-601), 96 PRB, TBS 36696 = 6 x K=6144, HARQ-ACK / RI / CQI multiplexed: soft
-        #      demodulation, ACK zeroing, descrambling, channel de-interleaver with RI removal, then decode_tb on g_bits ----
-        if not args.no_uplink:
-            # BASELINE configs[4]: "multi-cell eNB UL-SCH decode: 64 cells x 20 MHz ... sharded across 1/2/4/8 B200". The 64 cells
-            # are placed with shard.owner (cell-affine: every HARQ process of a cell lives on ONE GPU, no soft buffer ever moves,
-            # no collective); this rank decodes args.ul_subframes subframes of each of ITS cells per step. Strong scaling: the
-            # job (64 cells) is fixed, the per-rank share shrinks with N.
-            ACK_COLS, RI_COLS, uci_positions = synth.ACK_COLS, synth.RI_COLS, synth.uci_positions
-            U_TBS, U_MOD, U_PRB, U_COLS, U_CQI, U_C, N_CELLS = 36696, 4, 96, 12, 32, 6, 64
-            u_rows, u_nre = 12 * U_PRB, 12 * U_PRB * U_COLS
-            ack_pos = np.array(uci_positions(8, U_MOD, u_rows, ACK_COLS), np.uint32)
-            ri_pos = np.array(uci_positions(4, U_MOD, u_rows, RI_COLS), np.uint32)
-            U_G = u_nre * U_MOD - ri_pos.size - U_CQI
-            keys = [(c, 0) for c in range(N_CELLS)]
-            my_cells = [keys[i][0] for i in shard.partition(keys, rank, world)]
-            nsf = args.ul_subframes
-            nU = len(my_cells) * nsf                                  # transport blocks of this rank per step
-            u_pay = np.random.default_rng(7000).integers(0, 256, (N_CELLS, U_TBS // 8), dtype=np.uint8)     # one codeword per cell
-            u_e = synth.encode_tbs(u_pay[my_cells], U_TBS, U_MOD, 0, U_G)
-            u_cq = np.random.default_rng(7001).integers(0, 2, (N_CELLS, U_CQI)).astype(u_e.dtype)[my_cells]
-            u_q = synth.ulsch_interleave(np.concatenate([u_cq, u_e], axis=1), U_MOD, U_COLS, list(ri_pos))
-            u_ci = [synth.cinit_pusch(0x46 + c, 2 * (c % 10), 1 + c) for c in my_cells]                     # cell id = c + 1
-            u_clean = np.stack([synth.modulate(u_q[k] ^ synth.gold_sequence(u_ci[k], u_nre * U_MOD), U_MOD) for k in range(len(my_cells))])
-            hu_sym = pkg.PinnedArray((nU, u_nre, 2), np.float32)
-            rng_u = np.random.default_rng(7100 + rank)
-            cell_of = np.repeat(np.arange(len(my_cells)), nsf)        # TB i belongs to this rank's cell cell_of[i]
-            for i0 in range(0, nU, 64):
-                i1 = min(nU, i0 + 64)
-                hu_sym.a[i0:i1] = synth.awgn_symbols(u_clean[cell_of[i0:i1]], args.sigma_ul, rng_u)
-            du_sym = torch.from_numpy(hu_sym.a).to(f"cuda:{local_rank}")
-            n_uci = ack_pos.size + ri_pos.size + U_CQI
-            du_uci = torch.zeros((2, nU, (n_uci + 7) & ~7), dtype=torch.int16, device=f"cuda:{local_rank}")
-            du_out = torch.zeros((2, nU, DATA_STRIDE), dtype=torch.uint8, device=f"cuda:{local_rank}")
-            sbu = fec.softbuffer_alloc(2 * nU)                        # per (cell, subframe) HARQ entity, two sets in flight
-            u_tb, u_sy = [], []
-            for s_ in range(2):
-                t_ = (pkg.TbDesc * nU)()
-                y_ = (pkg.SymDesc * nU)()
-                for i in range(nU):
-                    t_[i].tbs, t_[i].Qm, t_[i].rv, t_[i].nof_e_bits, t_[i].max_its = U_TBS, U_MOD, 0, U_G, 8
-                    t_[i].softbuffer, t_[i].new_data = sbu + s_ * nU + i, 1
-                    t_[i].data = du_out[s_, i].data_ptr()
-                    y_[i].symbols, y_[i].nof_re, y_[i].mod_bits, y_[i].c_init = du_sym.data_ptr() + i * u_nre * 8, u_nre, U_MOD, u_ci[cell_of[i]]
-                    y_[i].nof_symb = U_COLS
-                    y_[i].ack_pos, y_[i].ri_pos, y_[i].nof_ack_pos, y_[i].nof_ri_pos = ack_pos.ctypes.data, ri_pos.ctypes.data, ack_pos.size, ri_pos.size
-                    y_[i].nof_cqi_bits = U_CQI
-                    y_[i].uci_out = du_uci[s_, i].data_ptr()
-                u_tb.append(t_); u_sy.append(y_)
-            for i in range(6):
-                fec.decode_syms(u_tb[i & 1], u_sy[i & 1], pkg.F_DEVICE_IO)
-            ms_ul = timed_syms(u_tb, u_sy, pkg.F_DEVICE_IO, args.steps)
-            t0 = time.perf_counter()                                  # host side of one step: descriptors, position lists, launches
-            tk_ = fec.submit_syms(u_tb[0], u_sy[0], pkg.F_DEVICE_IO)
-            host_submit_ul_ms = (time.perf_counter() - t0) * 1e3
-            fec.wait(tk_)
-            ok_u = sum(1 for i in range(nU) if u_tb[0][i].ret == 0)
-            its_u = sum(sum(u_tb[0][i].cb_its[:U_C]) for i in range(nU))
-            out_host = du_out[0].cpu().numpy()
-            bad = sum(1 for i in range(nU) if u_tb[0][i].ret == 0 and not (out_host[i, :U_TBS // 8] == u_pay[my_cells[cell_of[i]]]).all())
-            if bad:
-                raise SystemExit(f"bench.py: {bad} CRC-passing transport blocks of the uplink leg differ from the transmitted payload")
-            fec.decode_syms(u_tb[0], u_sy[0], pkg.F_DEVICE_IO | pkg.F_SERIAL)
-            path_u = fec.last_path_counts()
-            tot_u = allsum(nU)
-            ulsch5 = dict(workload="BASELINE configs[4]: 64 cells x PUSCH 16QAM 96 PRB, TBS 36696 (6 x K=6144), 32 HARQ-ACK + 16 RI positions + 32 CQI bits "
-                                   "multiplexed; equalised symbols in (device-resident), UL front end + decode_tb", scaling="strong",
-                          placement="shard.partition: cell c on rank c mod N with all of its HARQ soft buffers; no collective on the data path",
-                          cells=N_CELLS, cells_this_rank=len(my_cells), subframes_per_cell_per_step=nsf, tbs_per_step=tot_u, sigma_sym=args.sigma_ul,
-                          value=allsum(ok_u) * U_TBS * args.steps / (ms_ul / 1e3) / 1e9, unit=UNIT, ms_per_step=ms_ul / args.steps,
-                          tb_ok_frac=allsum(ok_u) / tot_u, halfits_per_cb=allsum(its_u) / (tot_u * U_C),
-                          cbs_per_s=tot_u * U_C * args.steps / (ms_ul / 1e3), payload_check="every CRC-passing TB of set 0 equals its cell's transmitted payload",
-                          code_blocks_by_kernel_rank0=dict(total=nU * U_C, certificate_variant=path_u[0], exact=path_u[1]),
-                          host_submit_ms_rank0=host_submit_ul_ms,
-                          serial_phases_ms_rank0=dict(zip(("rate_dematch", "turbo_decode", "tb_assemble_crc24a"), fec.last_phase_ms()),
-                                                      frontend=fec.last_frontend_ms()))
-            del du_sym, du_uci, du_out
-            hu_sym.free()
-        # the LLR legs below reuse dd / hd: put the soft buffers back into the state of the LLR workload
-        fec.decode_tbs(dd, pkg.F_DEVICE_IO)
-
-    # ---- HARQ leg (BASELINE configs[2]: TM4 2-codeword shape, 8-process HARQ soft combining): TBS 75376 in 86400 LLRs (rate 0.876),
-    #      13 x K=5824, rv sequence 0,2,3,1; noise so that rv 0 mostly fails. One step = one whole HARQ cycle of B/2 processes:
-    #      round 0 decodes all of them (new data), every later round only the NACKed ones with new_data = 0 — the read-modify-write
-    #      combine (softbuffer.c:128-151 state, rm_turbo.c:411-420), the cb_crc skip and the cached-CB copy (sch.c:396-418) are
-    #      inside the timed region. Rounds of one process are sequential by nature (same soft buffer), so the calls are blocking.
-    harq = None
-    if not args.no_harq:
-        synth_h = importlib.import_module("empower-srslte_b200.synth")
-        H_NBITS, Bh = 86400, max(8, B // 2)
-        rng_h = np.random.default_rng(9000 + rank)
-        ncw = payload.shape[0]
-        d_h = []
-        tmp_h = np.empty((64, H_NBITS), np.int16)
-        for rv in (0, 2, 3, 1):
-            e_h = synth_h.encode_tbs(payload, TBS, QM, rv, H_NBITS)
-            dev = torch.empty((Bh, H_NBITS), dtype=torch.int16, device=f"cuda:{local_rank}")
-            for i0 in range(0, Bh, 64):
-                i1 = min(Bh, i0 + 64)
-                synth_h.awgn_llr(e_h[np.arange(i0, i1) % ncw], args.sigma_harq, rng_h, out=tmp_h[: i1 - i0])
-                dev[i0:i1] = torch.from_numpy(tmp_h[: i1 - i0]).to(dev.device)
-            d_h.append(dev)
-
-        def harq_round(r, live):
-            d_ = (pkg.TbDesc * len(live))()
-            for s_, i in enumerate(live):
-                d_[s_].tbs, d_[s_].Qm, d_[s_].rv, d_[s_].nof_e_bits, d_[s_].max_its = TBS, QM, (0, 2, 3, 1)[r], H_NBITS, MAX_ITS
-                d_[s_].softbuffer, d_[s_].new_data = sb0 + i, int(r == 0)
-                d_[s_].e_bits, d_[s_].data = d_h[r].data_ptr() + i * H_NBITS * 2, d_out[0].data_ptr() + i * DATA_STRIDE
-            return d_
-
-        # discovery pass (untimed): which processes are still NACKed after each round — deterministic, the timed passes repeat it
-        rounds, live = [], list(range(Bh))
-        for r in range(4):
-            if not live:
-                break
-            d_ = harq_round(r, live)
-            fec.decode_tbs(d_, pkg.F_DEVICE_IO)
-            rounds.append((d_, list(live), [d_[s_].ret for s_ in range(len(live))]))
-            live = [i for s_, i in enumerate(live) if d_[s_].ret != 0]
-        fec.decode_tbs(rounds[0][0], pkg.F_DEVICE_IO)          # warm
-        barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(stream)
-        for _ in range(args.steps):
-            for d_, _, _ in rounds:
-                fec.decode_tbs(d_, pkg.F_DEVICE_IO)
-        e1.record(stream)
-        barrier()
-        ms_h = shard.reduce_job(dist if world > 1 else None, f"cuda:{local_rank}", e0.elapsed_time(e1))[0]
-        out_host = d_out[0].cpu().numpy()
-        acked, ntx, skipped, per_round = 0, 0, 0, []
-        for r, (d_, lv, ret0) in enumerate(rounds):
-            if [d_[s_].ret for s_ in range(len(lv))] != ret0:
-                raise SystemExit("bench.py: the HARQ leg is not deterministic across steps")
-            ok_r = [i for s_, i in enumerate(lv) if d_[s_].ret == 0]
-            bad = sum(1 for i in ok_r if not (out_host[i, :TBS // 8] == payload[i % ncw]).all())
-            if bad:
-                raise SystemExit(f"bench.py: {bad} ACKed transport blocks of the HARQ leg differ from the transmitted payload")
-            sk = sum(sum(1 for c in range(C_CB) if d_[s_].cb_its[c] == 0) for s_ in range(len(lv))) if r else 0
-            acked += len(ok_r); ntx += len(lv); skipped += sk
-            per_round.append(dict(rv=(0, 2, 3, 1)[r], tbs=len(lv), acked=len(ok_r), code_blocks_skipped_already_ok=sk))
-        # the rate de-matcher in its read-modify-write case: the first retransmission round, serialised
-        rmw = None
-        if len(rounds) > 1:
-            for d_, _, _ in rounds[:2]:
-                fec.decode_tbs(d_, pkg.F_DEVICE_IO | pkg.F_SERIAL)
-            ph = fec.last_phase_ms()
-            d1, lv1 = rounds[1][0], rounds[1][1]
-            ncb1 = sum(sum(1 for c in range(C_CB) if d1[s_].cb_its[c] > 0) for s_ in range(len(lv1)))
-            Eh = H_NBITS // C_CB
-            byt = ncb1 * (2 * Eh + 2 * 2 * (3 * 5888 + 16))       # LLRs in, slot read + slot written (3*SS+16 int16, SS = 16*368)
-            rmw = dict(code_blocks=ncb1, ms=ph[0], algorithmic_bytes=byt, achieved=byt / (ph[0] / 1e3) / 1e9, unit="GB/s", peak=peaks()["hbm_gbs"],
-                       frac=byt / (ph[0] / 1e3) / 1e9 / peaks()["hbm_gbs"], bytes_per_cb="2E + 2 x 2 x (3*SS+16)")
-        harq = dict(workload="BASELINE configs[2] shape: TBS 75376 in 86400 LLRs (13 x K=5824, E = 6642/6648), rv 0,2,3,1, "
-                             "new_data only in round 0; later rounds combine into the soft buffers, skip code blocks that are already OK and copy their cached bytes",
-                    sigma=args.sigma_harq, harq_processes=allsum(Bh), value=allsum(acked) * TBS * args.steps / (ms_h / 1e3) / 1e9, unit=UNIT + " of ACKed bits",
-                    ms_per_cycle=ms_h / args.steps, mean_transmissions_per_tb=allsum(ntx) / allsum(Bh), acked_frac=allsum(acked) / allsum(Bh),
-                    rounds_rank0=per_round, rate_dematch_read_modify_write_rank0=rmw,
-                    payload_check="every ACKed transport block equals the transmitted payload; return codes identical in every cycle")
-        del d_h
-        fec.decode_tbs(dd, pkg.F_DEVICE_IO)
-
-    # ---- sustained leg: the headline step looped for args.sustain seconds (the timed region of `value` is tens of milliseconds) ----
-    sustained = None
-    if args.sustain > 0:
-        n_s = max(args.steps, int(args.sustain * 1e3 / (ms / args.steps)) + 1)
-        smp = ClockSampler(local_rank)
-        smp.start()
-        time.sleep(0.2)
-        ms_s = timed_pipelined(dd_ab, pkg.F_DEVICE_IO, n_s)
-        ck = smp.stop()
-        ok_s2, _ = tally(dd)
-        sustained = dict(seconds=ms_s / 1e3, steps=n_s, value=allsum(ok_s2) * TBS * n_s / (ms_s / 1e3) / 1e9, unit=UNIT, ms_per_step=ms_s / n_s,
-                         sm_mhz_median=ck["sm_mhz"], power_w_max=ck["power_w_max"], reasons=ck["reasons"])
-
-    # ---- transmit side: the same transport blocks through CRC + segmentation + turbo encoding + rate matching
-    #      on the device (fec_cuda_encode_tbs, device-resident payloads and packed output), checked against the oracle ----
-    tx = None
-    if not args.no_tx:
-        ncw = payload.shape[0]
-        d_pay = torch.from_numpy(np.ascontiguousarray(payload[np.arange(B) % ncw])).to(f"cuda:{local_rank}")
-        EST = (NBITS // 8 + 15) & ~15
-        d_e = torch.zeros((B, EST), dtype=torch.uint8, device=f"cuda:{local_rank}")
-        td = (pkg.TxTbDesc * B)()
-        for i in range(B):
-            td[i].tbs, td[i].Qm, td[i].rv, td[i].nof_e_bits = TBS, QM, RV, NBITS
-            td[i].data, td[i].e_bits = d_pay.data_ptr() + i * (TBS // 8), d_e.data_ptr() + i * EST
-        for _ in range(3):
-            fec.encode_tbs(td, pkg.F_DEVICE_IO)
-        barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(stream)
-        for _ in range(args.steps):
-            fec.encode_tbs(td, pkg.F_DEVICE_IO)
-        e1.record(stream)
-        barrier()
-        ms_tx = shard.reduce_job(dist if world > 1 else None, f"cuda:{local_rank}", e0.elapsed_time(e1))[0]
-        if rank == 0:
-            synth_ = importlib.import_module("empower-srslte_b200.synth")
-            want = np.packbits(synth_.encode_tbs(payload[:2], TBS, QM, RV, NBITS), axis=1)
-            got = d_e[:2].cpu().numpy()
-            if not (got[:, : NBITS // 8] == want).all():
-                raise SystemExit("bench.py: the device encoder's bits differ from the host synthesiser's")
-        tx = dict(workload="the same transport blocks encoded: CRC-24A, segmentation, CRC-24B, turbo encoder, rate matching",
-                  value=world * B * TBS * args.steps / (ms_tx / 1e3) / 1e9, unit="Gbit/s of transport-block bits", ms_per_step=ms_tx / args.steps,
-                  cbs_per_s=world * B * C_CB * args.steps / (ms_tx / 1e3), checked="first 2 transport blocks bit-exact vs the numpy synthesiser (itself pinned to srslte_dlsch_encode)")
-
-    # ---- 8-bit LLR leg: the same transport blocks as int8 LLRs (amplitude 24, the scale of the reference's
-    #      8-bit demodulator output after its int8 clipping) through fec_cuda_set_llr_8bit: half the ingest bytes, int8
-    #      combining, the int8 decoders (P = 32 for K = 5824). The int8 decoders lose ~0.7 dB: quoted at sigma 0.3 ----
-    llr8 = None
-    if not args.no_llr8:
-        synth8 = importlib.import_module("empower-srslte_b200.synth")
-        f8 = pkg.FecCuda(local_rank, max_tbs=B)
-        f8.set_llr_8bit(True)
-        st8 = torch.cuda.ExternalStream(f8.stream, device=f"cuda:{local_rank}")
-        h8 = pkg.PinnedArray((B, NBITS), np.int8)
-        rng8 = np.random.default_rng(3000 + rank)
-        e8 = synth8.encode_tbs(payload, TBS, QM, RV, NBITS)
-        tmp = np.zeros((64, NBITS), np.int16)
-        for i0 in range(0, B, 64):
-            i1 = min(B, i0 + 64)
-            synth8.awgn_llr(e8[np.arange(i0, i1) % payload.shape[0]], args.sigma8, rng8, out=tmp[: i1 - i0])
-            h8.a[i0:i1] = np.clip(np.rint(tmp[: i1 - i0] * 0.24), -128, 127)
-        d8 = torch.from_numpy(h8.a).to(f"cuda:{local_rank}")
-        sb8 = f8.softbuffer_alloc(2 * B)
-        dd8, hd8, dd8b, hd8b = (pkg.TbDesc * B)(), (pkg.TbDesc * B)(), (pkg.TbDesc * B)(), (pkg.TbDesc * B)()
-        for i in range(B):
-            for dsc, ep, op, sbx in ((dd8, d8.data_ptr(), d_out[1].data_ptr(), sb8), (hd8, h8.a.ctypes.data, h_out2.a.ctypes.data, sb8),
-                                     (dd8b, d8.data_ptr(), d_out[0].data_ptr(), sb8 + B), (hd8b, h8.a.ctypes.data, h_out.a.ctypes.data, sb8 + B)):
-                dsc[i].tbs, dsc[i].Qm, dsc[i].rv, dsc[i].nof_e_bits, dsc[i].max_its = TBS, QM, RV, NBITS, MAX_ITS
-                dsc[i].softbuffer, dsc[i].new_data = sbx + i, 1
-                dsc[i].e_bits, dsc[i].data = ep + i * NBITS, op + i * DATA_STRIDE
-        for _ in range(8):                       # every pipe of the ring sizes its scratch on first use
-            f8.decode_tbs(dd8, pkg.F_DEVICE_IO)
-        n8 = max(2, args.steps // 2)
-        f8.decode_tbs(dd8b, pkg.F_DEVICE_IO)
-        ms8 = timed_pipelined([dd8, dd8b], pkg.F_DEVICE_IO, n8, f=f8, st=st8)
-        ms8s = timed(dd8, pkg.F_DEVICE_IO, n8, f=f8, st=st8)
-        ok8 = sum(1 for i in range(B) if dd8[i].ret == 0)
-        its8 = sum(sum(dd8[i].cb_its[:C_CB]) for i in range(B))
-        o8 = d_out[1].cpu().numpy()
-        bad8 = sum(1 for i in range(B) if dd8[i].ret == 0 and not (o8[i, :TBS // 8] == payload[i % payload.shape[0]]).all())
-        if bad8:
-            raise SystemExit(f"bench.py: {bad8} CRC-passing transport blocks of the 8-bit leg differ from the transmitted payload")
-        ph8 = []
-        for _ in range(3):
-            f8.decode_tbs(dd8, pkg.F_DEVICE_IO | pkg.F_SERIAL)
-            ph8.append(f8.last_phase_ms())
-        for _ in range(6):                       # the pipes of the ring size their pinned staging on their first use
-            f8.decode_tbs(hd8, 0)
-            f8.decode_tbs(hd8b, 0)
-        ms8e = timed_pipelined([hd8, hd8b], 0, n8, f=f8, st=st8)
-        ms8es = timed(hd8, 0, n8, f=f8, st=st8)
-        ok8e = sum(1 for i in range(B) if hd8[i].ret == 0)
-        llr8 = dict(workload="the same transport blocks as int8 LLRs (amplitude 24, sigma %.2f), fec_cuda_set_llr_8bit" % args.sigma8,
-                    value=allsum(ok8) * TBS * n8 / (ms8 / 1e3) / 1e9, unit=UNIT, ms_per_step=ms8 / n8, sync_ms_per_step=ms8s / n8, tb_ok_frac=allsum(ok8) / (world * B),
-                    halfits_per_cb=allsum(its8) / (world * B * C_CB),
-                    phases_ms=dict(rate_dematch=sum(p[0] for p in ph8) / 3, turbo_decode=sum(p[1] for p in ph8) / 3, tb_assemble_crc24a=sum(p[2] for p in ph8) / 3),
-                    e2e=dict(value=allsum(ok8e) * TBS * n8 / (ms8e / 1e3) / 1e9, unit=UNIT, ms_per_step=ms8e / n8, sync_ms_per_step=ms8es / n8,
-                             h2d_bytes_per_step=B * NBITS + B * C_CB * (32 + 48) + B * 520,
-                             frac_of_h2d_link=(B * NBITS + B * C_CB * (32 + 48) + B * 520) / (ms8e / n8 / 1e3) / 1e9 / link_min),
-                    kernel="fec_tdec_win8p_kernel<32,true>: two sub-blocks per thread in u16x2 lanes (VIADDMNMX.S16x2.RELU = saturating int8 add), beta checkpoints in tensor memory (profiles/r2_win8p_kernel_ncu.txt)")
-        # ---- the 8-bit path fed with equalised symbols (8 B per resource element): int8 soft demodulation
-        #      (srslte_demod_soft_demodulate_b), int8 descrambling, int8 rate de-matching, int8 decoders ----
-        if front is not None:
-            for i in range(6):
-                f8.decode_syms([dd8, dd8b][i & 1], sy_ab[0][i & 1], pkg.F_DEVICE_IO)
-            ms8y = timed_syms([dd8, dd8b], sy_ab[0], pkg.F_DEVICE_IO, n8, f=f8, st=st8)
-            ok8y = sum(1 for i in range(B) if dd8[i].ret == 0)
-            its8y = sum(sum(dd8[i].cb_its[:C_CB]) for i in range(B))
-            o8 = d_out[1].cpu().numpy()
-            if any(dd8[i].ret == 0 and not (o8[i, :TBS // 8] == payload[i % payload.shape[0]]).all() for i in range(B)):
-                raise SystemExit("bench.py: a CRC-passing transport block of the 8-bit symbol leg differs from the transmitted payload")
-            f8.decode_syms(dd8, sy_ab[0][0], pkg.F_DEVICE_IO | pkg.F_SERIAL)
-            fe8_ms = f8.last_frontend_ms()
-            for i in range(6):
-                f8.decode_syms([hd8, hd8b][i & 1], sy_ab[1][i & 1], 0)
-            ms8yh = timed_syms([hd8, hd8b], sy_ab[1], 0, n8, f=f8, st=st8)
-            ok8yh = sum(1 for i in range(B) if hd8[i].ret == 0)
-            hb = B * (NBITS // QM) * 8 + B * C_CB * (32 + 48) + B * (520 + 80)
-            llr8["symbols_in"] = dict(workload="same TBs as 64QAM symbols (sigma_sym %.3f), int8 front end + 8-bit path" % args.sigma_sym,
-                                      value=allsum(ok8y) * TBS * n8 / (ms8y / 1e3) / 1e9, unit=UNIT, ms_per_step=ms8y / n8,
-                                      tb_ok_frac=allsum(ok8y) / (world * B), halfits_per_cb=allsum(its8y) / (world * B * C_CB), frontend_ms=fe8_ms,
-                                      e2e=dict(value=allsum(ok8yh) * TBS * n8 / (ms8yh / 1e3) / 1e9, unit=UNIT, ms_per_step=ms8yh / n8,
-                                               h2d_bytes_per_step=hb, frac_of_h2d_link=hb / (ms8yh / n8 / 1e3) / 1e9 / link_min))
-        # ---- sigma grid: the int16 path and the int8 path on the SAME transport blocks at the same noise levels, with the
-        #      half-iterations per code block beside each value (296 distinct noisy TBs per point, tiled to the batch) ----
-        if not args.no_grid:
-            G = min(B, 296)
-            g16 = np.zeros((G, NBITS), np.int16)
-            d_g16 = torch.empty((B, NBITS), dtype=torch.int16, device=f"cuda:{local_rank}")
-            gsets = []
-            for s_ in range(2):
-                d_ = (pkg.TbDesc * B)()
-                fill_descs(pkg, d_, B, d_g16.data_ptr(), d_out[s_].data_ptr(), sb0 + s_ * B)
-                gsets.append(d_)
-            rows = np.arange(B) % G
-            idx = torch.from_numpy(rows).to(f"cuda:{local_rank}")
-            grid = []
-            for sg in (0.30, 0.40, 0.45):
-                rng_g = np.random.default_rng(7000 + rank)
-                for i0 in range(0, G, 64):
-                    i1 = min(G, i0 + 64)
-                    synth8.awgn_llr(e8[np.arange(i0, i1) % payload.shape[0]], sg, rng_g, out=g16[i0:i1])
-                t16 = torch.from_numpy(g16).to(f"cuda:{local_rank}")
-                d_g16.copy_(t16[idx])
-                d8.copy_(torch.from_numpy(np.clip(np.rint(g16 * 0.24), -128, 127).astype(np.int8)).to(f"cuda:{local_rank}")[idx])
-                torch.cuda.synchronize()
-                row = dict(sigma=sg)
-                for name, ff, sets, stx in (("int16", fec, gsets, stream), ("int8", f8, [dd8, dd8b], st8)):
-                    for d_ in sets:
-                        ff.decode_tbs(d_, pkg.F_DEVICE_IO)
-                    ms_g = timed_pipelined(sets, pkg.F_DEVICE_IO, n8, f=ff, st=stx)
-                    okg = sum(1 for i in range(B) if sets[0][i].ret == 0)
-                    itg = sum(sum(sets[0][i].cb_its[:C_CB]) for i in range(B))
-                    og = d_out[1 if name == "int8" else 0].cpu().numpy()
-                    if any(sets[0][i].ret == 0 and not (og[i, :TBS // 8] == payload[rows[i] % payload.shape[0]]).all() for i in range(B)):
-                        raise SystemExit(f"bench.py: sigma grid {name} sigma {sg}: a CRC-passing transport block differs from the transmitted payload")
-                    row[name] = dict(value=allsum(okg) * TBS * n8 / (ms_g / 1e3) / 1e9, unit=UNIT, ms_per_step=ms_g / n8,
-                                     tb_ok_frac=allsum(okg) / (world * B), halfits_per_cb=allsum(itg) / (world * B * C_CB))
-                grid.append(row)
-            llr8["sigma_grid"] = dict(note="device-resident, 2 batches in flight; value counts ACKed bits only; int8 LLRs = clip(rint(0.24 * int16 LLRs))", points=grid)
-            del d_g16
-        f8.close()
-
-    # ---- latency of the reference's call shape: ONE transport block per blocking call (srslte_dlsch_decode as pdsch.c:816
-    #      makes it, level 2 of INTEGRATION.md), host buffers, everything inside the timed call ----
-    lat = None
-    if rank == 0:
-        one = (pkg.TbDesc * 1)()
-        ts = []
-        for i in range(64):
-            fill_descs(pkg, one, 1, h_llr.a.ctypes.data + (i % B) * NBITS * 2, h_out.a.ctypes.data, sb0)
-            t0 = time.perf_counter()
-            fec.decode_tbs(one, 0)
-            ts.append((time.perf_counter() - t0) * 1e6)
-        ts = sorted(ts[8:])
-        lat = dict(call="fec_cuda_decode_tbs(n=1), 13 code blocks, host LLRs in, payload out", median_us=ts[len(ts) // 2], p90_us=ts[int(len(ts) * 0.9)],
-                   min_us=ts[0])
-
-    # ---- worst case: all 8 half-iterations for every code block (no early stop), same inputs ----
-    worst = None
-    if not args.no_worst_case:
-        fec.decode_tbs(dd, pkg.F_DEVICE_IO | pkg.F_NO_EARLY_STOP)
-        ms_w = timed(dd, pkg.F_DEVICE_IO | pkg.F_NO_EARLY_STOP, max(2, args.steps // 3))
-        ok_w, its_w = tally(dd)
-        nst = max(2, args.steps // 3)
-        worst = dict(gbps=allsum(ok_w) * TBS * nst / (ms_w / 1e3) / 1e9, cbs_per_s=world * B * C_CB * nst / (ms_w / 1e3),
-                     halfits_per_cb=allsum(its_w) / (world * B * C_CB), ms_per_step=ms_w / nst)
-
     # ---- roofline of the dominant kernel (turbo MAP decoder), per launch: the same step un-pipelined (one launch per
     #      kernel, FEC_CUDA_F_SERIAL), so that the CUDA events around each kernel do not overlap with a neighbour ----
     pk = peaks()
@@ -873,6 +451,439 @@ def main():
             raise SystemExit(f"bench.py: parity_in_bench failed: {parity}, first mismatch TB {int(np.argmin(same))}: "
                              f"cpu {c['results'][int(np.argmin(same))].tolist()} gpu {gpu_par[int(np.argmin(same))].tolist()}")
 
+    # ---- the other legs. A failure in one of them (allocation, a driver hiccup) must not cost the run its headline: the error is
+    #      reported in the line (`aux_error`); a payload or parity mismatch is a SystemExit and still ends the run ----
+    front = ulsch5 = harq = sustained = tx = llr8 = lat = worst = None
+    aux_error = None
+    try:
+        # ---- front-end leg: the same transport blocks given as equalised 64QAM symbols (8 B per resource element
+        #      instead of 12 B of LLRs); soft demodulation + descrambling run in the fused front-end kernel on the device ----
+        front, ulsch5 = None, None
+        if not args.no_symbols:
+            synth = importlib.import_module("empower-srslte_b200.synth")
+            nre = NBITS // QM
+            h_sym = pkg.PinnedArray((B, nre, 2), np.float32)
+            rng = np.random.default_rng(5000 + rank)
+            ncw = payload.shape[0]
+            c_inits = [synth.cinit_pdsch(0x1000 + k, 0, 2 * (k % 10), 1) for k in range(ncw)]
+            e = synth.encode_tbs(payload, TBS, QM, RV, NBITS)
+            cw_sym = np.stack([synth.modulate(e[k] ^ synth.gold_sequence(c_inits[k], NBITS), QM) for k in range(ncw)])
+            for i0 in range(0, B, 64):
+                i1 = min(B, i0 + 64)
+                h_sym.a[i0:i1] = synth.awgn_symbols(cw_sym[np.arange(i0, i1) % ncw], args.sigma_sym, rng)
+            d_sym = torch.from_numpy(h_sym.a).to(f"cuda:{local_rank}")
+            sy_ab = []
+            for dev in (True, False):
+                sets = []
+                for s_ in range(2):
+                    sd = (pkg.SymDesc * B)()
+                    base = d_sym.data_ptr() if dev else h_sym.a.ctypes.data
+                    for i in range(B):
+                        sd[i].symbols, sd[i].nof_re, sd[i].mod_bits, sd[i].c_init = base + i * nre * 8, nre, QM, c_inits[i % ncw]
+                    sets.append(sd)
+                sy_ab.append(sets)
+
+            def timed_syms(tb_sets, sym_sets, flags, steps, f=None, st=None):
+                f, st = f or fec, st or stream
+                barrier()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(st)
+                prev = None
+                for i in range(steps):
+                    t = f.submit_syms(tb_sets[i & 1], sym_sets[i & 1], flags)
+                    if prev is not None:
+                        f.wait(prev)
+                    prev = t
+                f.wait(prev)
+                e1.record(st)
+                barrier()
+                return shard.reduce_job(dist if world > 1 else None, f"cuda:{local_rank}", e0.elapsed_time(e1))[0]
+
+            for i in range(6):
+                fec.decode_syms(dd_ab[i & 1], sy_ab[0][i & 1], pkg.F_DEVICE_IO)
+            ms_sd = timed_syms(dd_ab, sy_ab[0], pkg.F_DEVICE_IO, args.steps)
+            ok_s, its_s = tally(dd)
+            fec.decode_syms(dd, sy_ab[0][0], pkg.F_DEVICE_IO | pkg.F_SERIAL)
+            fe_ms = fec.last_frontend_ms()
+            ph_s = fec.last_phase_ms()
+            path_s = fec.last_path_counts()
+            out_host = d_out[0].cpu().numpy()
+            bad = sum(1 for i in range(B) if dd[i].ret == 0 and not (out_host[i, :TBS // 8] == payload[i % ncw]).all())
+            if bad:
+                raise SystemExit(f"bench.py: {bad} CRC-passing transport blocks of the symbol leg differ from the transmitted payload")
+            for i in range(6):
+                fec.decode_syms(hd_ab[i & 1], sy_ab[1][i & 1], 0)
+            ms_sh = timed_syms(hd_ab, sy_ab[1], 0, args.steps)
+            ok_sh, _ = tally(hd)
+            fe_bytes = B * (nre * 8 + NBITS * 2)
+            front = dict(workload="same TBs as 64QAM symbols (15000 RE), soft demodulation + descrambling on the device",
+                         sigma_sym=args.sigma_sym, value=allsum(ok_s) * TBS * args.steps / (ms_sd / 1e3) / 1e9, unit=UNIT,
+                         ms_per_step=ms_sd / args.steps, tb_ok_frac=allsum(ok_s) / (world * B), halfits_per_cb=allsum(its_s) / (world * B * C_CB),
+                         e2e=dict(value=allsum(ok_sh) * TBS * args.steps / (ms_sh / 1e3) / 1e9, unit=UNIT, ms_per_step=ms_sh / args.steps,
+                                  h2d_bytes_per_step=B * nre * 8 + B * C_CB * (32 + 48) + B * (520 + 80), d2h_bytes_per_step=d2h,
+                                  frac_of_h2d_link=(B * nre * 8 + B * C_CB * (32 + 48) + B * (520 + 80)) / (ms_sh / args.steps / 1e3) / 1e9 / link_min),
+                         code_blocks_by_kernel=dict(total=B * C_CB, certificate_variant=path_s[0], exact=path_s[1]),
+                         serial_phases_ms=dict(frontend=fe_ms, rate_dematch=ph_s[0], turbo_decode=ph_s[1], tb_assemble_crc24a=ph_s[2]),
+                         frontend_kernel=dict(ms_per_launch=fe_ms, algorithmic_bytes=fe_bytes, achieved=fe_bytes / (fe_ms / 1e3) / 1e9,
+                                              peak=peaks()["hbm_gbs"], unit="GB/s", frac=fe_bytes / (fe_ms / 1e3) / 1e9 / peaks()["hbm_gbs"], bound="hbm"))
+            # ---- uplink leg (BASELINE configs[4] shape per cell-subframe): PUSCH from the demodulator on — 16QAM (what
+            #      srsENB grants, phch_worker.cc:598-601), 96 PRB, TBS 36696 = 6 x K=6144, HARQ-ACK / RI / CQI multiplexed: soft
+            #      demodulation, ACK zeroing, descrambling, channel de-interleaver with RI removal, then decode_tb on g_bits ----
+            if not args.no_uplink:
+                # BASELINE configs[4]: "multi-cell eNB UL-SCH decode: 64 cells x 20 MHz ... sharded across 1/2/4/8 B200". The 64 cells
+                # are placed with shard.owner (cell-affine: every HARQ process of a cell lives on ONE GPU, no soft buffer ever moves,
+                # no collective); this rank decodes args.ul_subframes subframes of each of ITS cells per step. Strong scaling: the
+                # job (64 cells) is fixed, the per-rank share shrinks with N.
+                ACK_COLS, RI_COLS, uci_positions = synth.ACK_COLS, synth.RI_COLS, synth.uci_positions
+                U_TBS, U_MOD, U_PRB, U_COLS, U_CQI, U_C, N_CELLS = 36696, 4, 96, 12, 32, 6, 64
+                u_rows, u_nre = 12 * U_PRB, 12 * U_PRB * U_COLS
+                ack_pos = np.array(uci_positions(8, U_MOD, u_rows, ACK_COLS), np.uint32)
+                ri_pos = np.array(uci_positions(4, U_MOD, u_rows, RI_COLS), np.uint32)
+                U_G = u_nre * U_MOD - ri_pos.size - U_CQI
+                keys = [(c, 0) for c in range(N_CELLS)]
+                my_cells = [keys[i][0] for i in shard.partition(keys, rank, world)]
+                nsf = args.ul_subframes
+                nU = len(my_cells) * nsf                                  # transport blocks of this rank per step
+                u_pay = np.random.default_rng(7000).integers(0, 256, (N_CELLS, U_TBS // 8), dtype=np.uint8)     # one codeword per cell
+                u_e = synth.encode_tbs(u_pay[my_cells], U_TBS, U_MOD, 0, U_G)
+                u_cq = np.random.default_rng(7001).integers(0, 2, (N_CELLS, U_CQI)).astype(u_e.dtype)[my_cells]
+                u_q = synth.ulsch_interleave(np.concatenate([u_cq, u_e], axis=1), U_MOD, U_COLS, list(ri_pos))
+                u_ci = [synth.cinit_pusch(0x46 + c, 2 * (c % 10), 1 + c) for c in my_cells]                     # cell id = c + 1
+                u_clean = np.stack([synth.modulate(u_q[k] ^ synth.gold_sequence(u_ci[k], u_nre * U_MOD), U_MOD) for k in range(len(my_cells))])
+                hu_sym = pkg.PinnedArray((nU, u_nre, 2), np.float32)
+                rng_u = np.random.default_rng(7100 + rank)
+                cell_of = np.repeat(np.arange(len(my_cells)), nsf)        # TB i belongs to this rank's cell cell_of[i]
+                for i0 in range(0, nU, 64):
+                    i1 = min(nU, i0 + 64)
+                    hu_sym.a[i0:i1] = synth.awgn_symbols(u_clean[cell_of[i0:i1]], args.sigma_ul, rng_u)
+                du_sym = torch.from_numpy(hu_sym.a).to(f"cuda:{local_rank}")
+                n_uci = ack_pos.size + ri_pos.size + U_CQI
+                du_uci = torch.zeros((2, nU, (n_uci + 7) & ~7), dtype=torch.int16, device=f"cuda:{local_rank}")
+                du_out = torch.zeros((2, nU, DATA_STRIDE), dtype=torch.uint8, device=f"cuda:{local_rank}")
+                sbu = fec.softbuffer_alloc(2 * nU)                        # per (cell, subframe) HARQ entity, two sets in flight
+                u_tb, u_sy = [], []
+                for s_ in range(2):
+                    t_ = (pkg.TbDesc * nU)()
+                    y_ = (pkg.SymDesc * nU)()
+                    for i in range(nU):
+                        t_[i].tbs, t_[i].Qm, t_[i].rv, t_[i].nof_e_bits, t_[i].max_its = U_TBS, U_MOD, 0, U_G, 8
+                        t_[i].softbuffer, t_[i].new_data = sbu + s_ * nU + i, 1
+                        t_[i].data = du_out[s_, i].data_ptr()
+                        y_[i].symbols, y_[i].nof_re, y_[i].mod_bits, y_[i].c_init = du_sym.data_ptr() + i * u_nre * 8, u_nre, U_MOD, u_ci[cell_of[i]]
+                        y_[i].nof_symb = U_COLS
+                        y_[i].ack_pos, y_[i].ri_pos, y_[i].nof_ack_pos, y_[i].nof_ri_pos = ack_pos.ctypes.data, ri_pos.ctypes.data, ack_pos.size, ri_pos.size
+                        y_[i].nof_cqi_bits = U_CQI
+                        y_[i].uci_out = du_uci[s_, i].data_ptr()
+                    u_tb.append(t_); u_sy.append(y_)
+                for i in range(6):
+                    fec.decode_syms(u_tb[i & 1], u_sy[i & 1], pkg.F_DEVICE_IO)
+                ms_ul = timed_syms(u_tb, u_sy, pkg.F_DEVICE_IO, args.steps)
+                t0 = time.perf_counter()                                  # host side of one step: descriptors, position lists, launches
+                tk_ = fec.submit_syms(u_tb[0], u_sy[0], pkg.F_DEVICE_IO)
+                host_submit_ul_ms = (time.perf_counter() - t0) * 1e3
+                fec.wait(tk_)
+                ok_u = sum(1 for i in range(nU) if u_tb[0][i].ret == 0)
+                its_u = sum(sum(u_tb[0][i].cb_its[:U_C]) for i in range(nU))
+                out_host = du_out[0].cpu().numpy()
+                bad = sum(1 for i in range(nU) if u_tb[0][i].ret == 0 and not (out_host[i, :U_TBS // 8] == u_pay[my_cells[cell_of[i]]]).all())
+                if bad:
+                    raise SystemExit(f"bench.py: {bad} CRC-passing transport blocks of the uplink leg differ from the transmitted payload")
+                fec.decode_syms(u_tb[0], u_sy[0], pkg.F_DEVICE_IO | pkg.F_SERIAL)
+                path_u = fec.last_path_counts()
+                tot_u = allsum(nU)
+                ulsch5 = dict(workload="BASELINE configs[4]: 64 cells x PUSCH 16QAM 96 PRB, TBS 36696 (6 x K=6144), 32 HARQ-ACK + 16 RI positions + 32 CQI bits "
+                                       "multiplexed; equalised symbols in (device-resident), UL front end + decode_tb", scaling="strong",
+                              placement="shard.partition: cell c on rank c mod N with all of its HARQ soft buffers; no collective on the data path",
+                              cells=N_CELLS, cells_this_rank=len(my_cells), subframes_per_cell_per_step=nsf, tbs_per_step=tot_u, sigma_sym=args.sigma_ul,
+                              value=allsum(ok_u) * U_TBS * args.steps / (ms_ul / 1e3) / 1e9, unit=UNIT, ms_per_step=ms_ul / args.steps,
+                              tb_ok_frac=allsum(ok_u) / tot_u, halfits_per_cb=allsum(its_u) / (tot_u * U_C),
+                              cbs_per_s=tot_u * U_C * args.steps / (ms_ul / 1e3), payload_check="every CRC-passing TB of set 0 equals its cell's transmitted payload",
+                              code_blocks_by_kernel_rank0=dict(total=nU * U_C, certificate_variant=path_u[0], exact=path_u[1]),
+                              host_submit_ms_rank0=host_submit_ul_ms,
+                              serial_phases_ms_rank0=dict(zip(("rate_dematch", "turbo_decode", "tb_assemble_crc24a"), fec.last_phase_ms()),
+                                                          frontend=fec.last_frontend_ms()))
+                del du_sym, du_uci, du_out
+                hu_sym.free()
+            # the LLR legs below reuse dd / hd: put the soft buffers back into the state of the LLR workload
+            fec.decode_tbs(dd, pkg.F_DEVICE_IO)
+
+        # ---- HARQ leg (BASELINE configs[2]: TM4 2-codeword shape, 8-process HARQ soft combining): TBS 75376 in 86400 LLRs (rate 0.876),
+        #      13 x K=5824, rv sequence 0,2,3,1; noise so that rv 0 mostly fails. One step = one whole HARQ cycle of B/2 processes:
+        #      round 0 decodes all of them (new data), every later round only the NACKed ones with new_data = 0 — the read-modify-write
+        #      combine (softbuffer.c:128-151 state, rm_turbo.c:411-420), the cb_crc skip and the cached-CB copy (sch.c:396-418) are
+        #      inside the timed region. Rounds of one process are sequential by nature (same soft buffer), so the calls are blocking.
+        harq = None
+        if not args.no_harq:
+            synth_h = importlib.import_module("empower-srslte_b200.synth")
+            H_NBITS, Bh = 86400, max(8, B // 2)
+            rng_h = np.random.default_rng(9000 + rank)
+            ncw = payload.shape[0]
+            d_h = []
+            tmp_h = np.empty((64, H_NBITS), np.int16)
+            for rv in (0, 2, 3, 1):
+                e_h = synth_h.encode_tbs(payload, TBS, QM, rv, H_NBITS)
+                dev = torch.empty((Bh, H_NBITS), dtype=torch.int16, device=f"cuda:{local_rank}")
+                for i0 in range(0, Bh, 64):
+                    i1 = min(Bh, i0 + 64)
+                    synth_h.awgn_llr(e_h[np.arange(i0, i1) % ncw], args.sigma_harq, rng_h, out=tmp_h[: i1 - i0])
+                    dev[i0:i1] = torch.from_numpy(tmp_h[: i1 - i0]).to(dev.device)
+                d_h.append(dev)
+
+            def harq_round(r, live):
+                d_ = (pkg.TbDesc * len(live))()
+                for s_, i in enumerate(live):
+                    d_[s_].tbs, d_[s_].Qm, d_[s_].rv, d_[s_].nof_e_bits, d_[s_].max_its = TBS, QM, (0, 2, 3, 1)[r], H_NBITS, MAX_ITS
+                    d_[s_].softbuffer, d_[s_].new_data = sb0 + i, int(r == 0)
+                    d_[s_].e_bits, d_[s_].data = d_h[r].data_ptr() + i * H_NBITS * 2, d_out[0].data_ptr() + i * DATA_STRIDE
+                return d_
+
+            # discovery pass (untimed): which processes are still NACKed after each round — deterministic, the timed passes repeat it
+            rounds, live = [], list(range(Bh))
+            for r in range(4):
+                if not live:
+                    break
+                d_ = harq_round(r, live)
+                fec.decode_tbs(d_, pkg.F_DEVICE_IO)
+                rounds.append((d_, list(live), [d_[s_].ret for s_ in range(len(live))]))
+                live = [i for s_, i in enumerate(live) if d_[s_].ret != 0]
+            fec.decode_tbs(rounds[0][0], pkg.F_DEVICE_IO)          # warm
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _ in range(args.steps):
+                for d_, _, _ in rounds:
+                    fec.decode_tbs(d_, pkg.F_DEVICE_IO)
+            e1.record(stream)
+            barrier()
+            ms_h = shard.reduce_job(dist if world > 1 else None, f"cuda:{local_rank}", e0.elapsed_time(e1))[0]
+            out_host = d_out[0].cpu().numpy()
+            acked, ntx, skipped, per_round = 0, 0, 0, []
+            for r, (d_, lv, ret0) in enumerate(rounds):
+                if [d_[s_].ret for s_ in range(len(lv))] != ret0:
+                    raise SystemExit("bench.py: the HARQ leg is not deterministic across steps")
+                ok_r = [i for s_, i in enumerate(lv) if d_[s_].ret == 0]
+                bad = sum(1 for i in ok_r if not (out_host[i, :TBS // 8] == payload[i % ncw]).all())
+                if bad:
+                    raise SystemExit(f"bench.py: {bad} ACKed transport blocks of the HARQ leg differ from the transmitted payload")
+                sk = sum(sum(1 for c in range(C_CB) if d_[s_].cb_its[c] == 0) for s_ in range(len(lv))) if r else 0
+                acked += len(ok_r); ntx += len(lv); skipped += sk
+                per_round.append(dict(rv=(0, 2, 3, 1)[r], tbs=len(lv), acked=len(ok_r), code_blocks_skipped_already_ok=sk))
+            # the rate de-matcher in its read-modify-write case: the first retransmission round, serialised
+            rmw = None
+            if len(rounds) > 1:
+                for d_, _, _ in rounds[:2]:
+                    fec.decode_tbs(d_, pkg.F_DEVICE_IO | pkg.F_SERIAL)
+                ph = fec.last_phase_ms()
+                d1, lv1 = rounds[1][0], rounds[1][1]
+                ncb1 = sum(sum(1 for c in range(C_CB) if d1[s_].cb_its[c] > 0) for s_ in range(len(lv1)))
+                Eh = H_NBITS // C_CB
+                byt = ncb1 * (2 * Eh + 2 * 2 * (3 * 5888 + 16))       # LLRs in, slot read + slot written (3*SS+16 int16, SS = 16*368)
+                rmw = dict(code_blocks=ncb1, ms=ph[0], algorithmic_bytes=byt, achieved=byt / (ph[0] / 1e3) / 1e9, unit="GB/s", peak=peaks()["hbm_gbs"],
+                           frac=byt / (ph[0] / 1e3) / 1e9 / peaks()["hbm_gbs"], bytes_per_cb="2E + 2 x 2 x (3*SS+16)")
+            harq = dict(workload="BASELINE configs[2] shape: TBS 75376 in 86400 LLRs (13 x K=5824, E = 6642/6648), rv 0,2,3,1, "
+                                 "new_data only in round 0; later rounds combine into the soft buffers, skip code blocks that are already OK and copy their cached bytes",
+                        sigma=args.sigma_harq, harq_processes=allsum(Bh), value=allsum(acked) * TBS * args.steps / (ms_h / 1e3) / 1e9, unit=UNIT + " of ACKed bits",
+                        ms_per_cycle=ms_h / args.steps, mean_transmissions_per_tb=allsum(ntx) / allsum(Bh), acked_frac=allsum(acked) / allsum(Bh),
+                        rounds_rank0=per_round, rate_dematch_read_modify_write_rank0=rmw,
+                        payload_check="every ACKed transport block equals the transmitted payload; return codes identical in every cycle")
+            del d_h
+            fec.decode_tbs(dd, pkg.F_DEVICE_IO)
+
+        # ---- sustained leg: the headline step looped for args.sustain seconds (the timed region of `value` is tens of milliseconds) ----
+        sustained = None
+        if args.sustain > 0:
+            n_s = max(args.steps, int(args.sustain * 1e3 / (ms / args.steps)) + 1)
+            smp = ClockSampler(local_rank)
+            smp.start()
+            time.sleep(0.2)
+            ms_s = timed_pipelined(dd_ab, pkg.F_DEVICE_IO, n_s)
+            ck = smp.stop()
+            ok_s2, _ = tally(dd)
+            sustained = dict(seconds=ms_s / 1e3, steps=n_s, value=allsum(ok_s2) * TBS * n_s / (ms_s / 1e3) / 1e9, unit=UNIT, ms_per_step=ms_s / n_s,
+                             sm_mhz_median=ck["sm_mhz"], power_w_max=ck["power_w_max"], reasons=ck["reasons"])
+
+        # ---- transmit side: the same transport blocks through CRC + segmentation + turbo encoding + rate matching
+        #      on the device (fec_cuda_encode_tbs, device-resident payloads and packed output), checked against the oracle ----
+        tx = None
+        if not args.no_tx:
+            ncw = payload.shape[0]
+            d_pay = torch.from_numpy(np.ascontiguousarray(payload[np.arange(B) % ncw])).to(f"cuda:{local_rank}")
+            EST = (NBITS // 8 + 15) & ~15
+            d_e = torch.zeros((B, EST), dtype=torch.uint8, device=f"cuda:{local_rank}")
+            td = (pkg.TxTbDesc * B)()
+            for i in range(B):
+                td[i].tbs, td[i].Qm, td[i].rv, td[i].nof_e_bits = TBS, QM, RV, NBITS
+                td[i].data, td[i].e_bits = d_pay.data_ptr() + i * (TBS // 8), d_e.data_ptr() + i * EST
+            for _ in range(3):
+                fec.encode_tbs(td, pkg.F_DEVICE_IO)
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _ in range(args.steps):
+                fec.encode_tbs(td, pkg.F_DEVICE_IO)
+            e1.record(stream)
+            barrier()
+            ms_tx = shard.reduce_job(dist if world > 1 else None, f"cuda:{local_rank}", e0.elapsed_time(e1))[0]
+            if rank == 0:
+                synth_ = importlib.import_module("empower-srslte_b200.synth")
+                want = np.packbits(synth_.encode_tbs(payload[:2], TBS, QM, RV, NBITS), axis=1)
+                got = d_e[:2].cpu().numpy()
+                if not (got[:, : NBITS // 8] == want).all():
+                    raise SystemExit("bench.py: the device encoder's bits differ from the host synthesiser's")
+            tx = dict(workload="the same transport blocks encoded: CRC-24A, segmentation, CRC-24B, turbo encoder, rate matching",
+                      value=world * B * TBS * args.steps / (ms_tx / 1e3) / 1e9, unit="Gbit/s of transport-block bits", ms_per_step=ms_tx / args.steps,
+                      cbs_per_s=world * B * C_CB * args.steps / (ms_tx / 1e3), checked="first 2 transport blocks bit-exact vs the numpy synthesiser (itself pinned to srslte_dlsch_encode)")
+
+        # ---- 8-bit LLR leg: the same transport blocks as int8 LLRs (amplitude 24, the scale of the reference's
+        #      8-bit demodulator output after its int8 clipping) through fec_cuda_set_llr_8bit: half the ingest bytes, int8
+        #      combining, the int8 decoders (P = 32 for K = 5824). The int8 decoders lose ~0.7 dB: quoted at sigma 0.3 ----
+        llr8 = None
+        if not args.no_llr8:
+            synth8 = importlib.import_module("empower-srslte_b200.synth")
+            f8 = pkg.FecCuda(local_rank, max_tbs=B)
+            f8.set_llr_8bit(True)
+            st8 = torch.cuda.ExternalStream(f8.stream, device=f"cuda:{local_rank}")
+            h8 = pkg.PinnedArray((B, NBITS), np.int8)
+            rng8 = np.random.default_rng(3000 + rank)
+            e8 = synth8.encode_tbs(payload, TBS, QM, RV, NBITS)
+            tmp = np.zeros((64, NBITS), np.int16)
+            for i0 in range(0, B, 64):
+                i1 = min(B, i0 + 64)
+                synth8.awgn_llr(e8[np.arange(i0, i1) % payload.shape[0]], args.sigma8, rng8, out=tmp[: i1 - i0])
+                h8.a[i0:i1] = np.clip(np.rint(tmp[: i1 - i0] * 0.24), -128, 127)
+            d8 = torch.from_numpy(h8.a).to(f"cuda:{local_rank}")
+            sb8 = f8.softbuffer_alloc(2 * B)
+            dd8, hd8, dd8b, hd8b = (pkg.TbDesc * B)(), (pkg.TbDesc * B)(), (pkg.TbDesc * B)(), (pkg.TbDesc * B)()
+            for i in range(B):
+                for dsc, ep, op, sbx in ((dd8, d8.data_ptr(), d_out[1].data_ptr(), sb8), (hd8, h8.a.ctypes.data, h_out2.a.ctypes.data, sb8),
+                                         (dd8b, d8.data_ptr(), d_out[0].data_ptr(), sb8 + B), (hd8b, h8.a.ctypes.data, h_out.a.ctypes.data, sb8 + B)):
+                    dsc[i].tbs, dsc[i].Qm, dsc[i].rv, dsc[i].nof_e_bits, dsc[i].max_its = TBS, QM, RV, NBITS, MAX_ITS
+                    dsc[i].softbuffer, dsc[i].new_data = sbx + i, 1
+                    dsc[i].e_bits, dsc[i].data = ep + i * NBITS, op + i * DATA_STRIDE
+            for _ in range(8):                       # every pipe of the ring sizes its scratch on first use
+                f8.decode_tbs(dd8, pkg.F_DEVICE_IO)
+            n8 = max(2, args.steps // 2)
+            f8.decode_tbs(dd8b, pkg.F_DEVICE_IO)
+            ms8 = timed_pipelined([dd8, dd8b], pkg.F_DEVICE_IO, n8, f=f8, st=st8)
+            ms8s = timed(dd8, pkg.F_DEVICE_IO, n8, f=f8, st=st8)
+            ok8 = sum(1 for i in range(B) if dd8[i].ret == 0)
+            its8 = sum(sum(dd8[i].cb_its[:C_CB]) for i in range(B))
+            o8 = d_out[1].cpu().numpy()
+            bad8 = sum(1 for i in range(B) if dd8[i].ret == 0 and not (o8[i, :TBS // 8] == payload[i % payload.shape[0]]).all())
+            if bad8:
+                raise SystemExit(f"bench.py: {bad8} CRC-passing transport blocks of the 8-bit leg differ from the transmitted payload")
+            ph8 = []
+            for _ in range(3):
+                f8.decode_tbs(dd8, pkg.F_DEVICE_IO | pkg.F_SERIAL)
+                ph8.append(f8.last_phase_ms())
+            for _ in range(6):                       # the pipes of the ring size their pinned staging on their first use
+                f8.decode_tbs(hd8, 0)
+                f8.decode_tbs(hd8b, 0)
+            ms8e = timed_pipelined([hd8, hd8b], 0, n8, f=f8, st=st8)
+            ms8es = timed(hd8, 0, n8, f=f8, st=st8)
+            ok8e = sum(1 for i in range(B) if hd8[i].ret == 0)
+            llr8 = dict(workload="the same transport blocks as int8 LLRs (amplitude 24, sigma %.2f), fec_cuda_set_llr_8bit" % args.sigma8,
+                        value=allsum(ok8) * TBS * n8 / (ms8 / 1e3) / 1e9, unit=UNIT, ms_per_step=ms8 / n8, sync_ms_per_step=ms8s / n8, tb_ok_frac=allsum(ok8) / (world * B),
+                        halfits_per_cb=allsum(its8) / (world * B * C_CB),
+                        phases_ms=dict(rate_dematch=sum(p[0] for p in ph8) / 3, turbo_decode=sum(p[1] for p in ph8) / 3, tb_assemble_crc24a=sum(p[2] for p in ph8) / 3),
+                        e2e=dict(value=allsum(ok8e) * TBS * n8 / (ms8e / 1e3) / 1e9, unit=UNIT, ms_per_step=ms8e / n8, sync_ms_per_step=ms8es / n8,
+                                 h2d_bytes_per_step=B * NBITS + B * C_CB * (32 + 48) + B * 520,
+                                 frac_of_h2d_link=(B * NBITS + B * C_CB * (32 + 48) + B * 520) / (ms8e / n8 / 1e3) / 1e9 / link_min),
+                        kernel="fec_tdec_win8p_kernel<32,true>: two sub-blocks per thread in u16x2 lanes (VIADDMNMX.S16x2.RELU = saturating int8 add), beta checkpoints in tensor memory (profiles/r2_win8p_kernel_ncu.txt)")
+            # ---- the 8-bit path fed with equalised symbols (8 B per resource element): int8 soft demodulation
+            #      (srslte_demod_soft_demodulate_b), int8 descrambling, int8 rate de-matching, int8 decoders ----
+            if front is not None:
+                for i in range(6):
+                    f8.decode_syms([dd8, dd8b][i & 1], sy_ab[0][i & 1], pkg.F_DEVICE_IO)
+                ms8y = timed_syms([dd8, dd8b], sy_ab[0], pkg.F_DEVICE_IO, n8, f=f8, st=st8)
+                ok8y = sum(1 for i in range(B) if dd8[i].ret == 0)
+                its8y = sum(sum(dd8[i].cb_its[:C_CB]) for i in range(B))
+                o8 = d_out[1].cpu().numpy()
+                if any(dd8[i].ret == 0 and not (o8[i, :TBS // 8] == payload[i % payload.shape[0]]).all() for i in range(B)):
+                    raise SystemExit("bench.py: a CRC-passing transport block of the 8-bit symbol leg differs from the transmitted payload")
+                f8.decode_syms(dd8, sy_ab[0][0], pkg.F_DEVICE_IO | pkg.F_SERIAL)
+                fe8_ms = f8.last_frontend_ms()
+                for i in range(6):
+                    f8.decode_syms([hd8, hd8b][i & 1], sy_ab[1][i & 1], 0)
+                ms8yh = timed_syms([hd8, hd8b], sy_ab[1], 0, n8, f=f8, st=st8)
+                ok8yh = sum(1 for i in range(B) if hd8[i].ret == 0)
+                hb = B * (NBITS // QM) * 8 + B * C_CB * (32 + 48) + B * (520 + 80)
+                llr8["symbols_in"] = dict(workload="same TBs as 64QAM symbols (sigma_sym %.3f), int8 front end + 8-bit path" % args.sigma_sym,
+                                          value=allsum(ok8y) * TBS * n8 / (ms8y / 1e3) / 1e9, unit=UNIT, ms_per_step=ms8y / n8,
+                                          tb_ok_frac=allsum(ok8y) / (world * B), halfits_per_cb=allsum(its8y) / (world * B * C_CB), frontend_ms=fe8_ms,
+                                          e2e=dict(value=allsum(ok8yh) * TBS * n8 / (ms8yh / 1e3) / 1e9, unit=UNIT, ms_per_step=ms8yh / n8,
+                                                   h2d_bytes_per_step=hb, frac_of_h2d_link=hb / (ms8yh / n8 / 1e3) / 1e9 / link_min))
+            # ---- sigma grid: the int16 path and the int8 path on the SAME transport blocks at the same noise levels, with the
+            #      half-iterations per code block beside each value (296 distinct noisy TBs per point, tiled to the batch) ----
+            if not args.no_grid:
+                G = min(B, 296)
+                g16 = np.zeros((G, NBITS), np.int16)
+                d_g16 = torch.empty((B, NBITS), dtype=torch.int16, device=f"cuda:{local_rank}")
+                gsets = []
+                for s_ in range(2):
+                    d_ = (pkg.TbDesc * B)()
+                    fill_descs(pkg, d_, B, d_g16.data_ptr(), d_out[s_].data_ptr(), sb0 + s_ * B)
+                    gsets.append(d_)
+                rows = np.arange(B) % G
+                idx = torch.from_numpy(rows).to(f"cuda:{local_rank}")
+                grid = []
+                for sg in (0.30, 0.40, 0.45):
+                    rng_g = np.random.default_rng(7000 + rank)
+                    for i0 in range(0, G, 64):
+                        i1 = min(G, i0 + 64)
+                        synth8.awgn_llr(e8[np.arange(i0, i1) % payload.shape[0]], sg, rng_g, out=g16[i0:i1])
+                    t16 = torch.from_numpy(g16).to(f"cuda:{local_rank}")
+                    d_g16.copy_(t16[idx])
+                    d8.copy_(torch.from_numpy(np.clip(np.rint(g16 * 0.24), -128, 127).astype(np.int8)).to(f"cuda:{local_rank}")[idx])
+                    torch.cuda.synchronize()
+                    row = dict(sigma=sg)
+                    for name, ff, sets, stx in (("int16", fec, gsets, stream), ("int8", f8, [dd8, dd8b], st8)):
+                        for d_ in sets:
+                            ff.decode_tbs(d_, pkg.F_DEVICE_IO)
+                        ms_g = timed_pipelined(sets, pkg.F_DEVICE_IO, n8, f=ff, st=stx)
+                        okg = sum(1 for i in range(B) if sets[0][i].ret == 0)
+                        itg = sum(sum(sets[0][i].cb_its[:C_CB]) for i in range(B))
+                        og = d_out[1 if name == "int8" else 0].cpu().numpy()
+                        if any(sets[0][i].ret == 0 and not (og[i, :TBS // 8] == payload[rows[i] % payload.shape[0]]).all() for i in range(B)):
+                            raise SystemExit(f"bench.py: sigma grid {name} sigma {sg}: a CRC-passing transport block differs from the transmitted payload")
+                        row[name] = dict(value=allsum(okg) * TBS * n8 / (ms_g / 1e3) / 1e9, unit=UNIT, ms_per_step=ms_g / n8,
+                                         tb_ok_frac=allsum(okg) / (world * B), halfits_per_cb=allsum(itg) / (world * B * C_CB))
+                    grid.append(row)
+                llr8["sigma_grid"] = dict(note="device-resident, 2 batches in flight; value counts ACKed bits only; int8 LLRs = clip(rint(0.24 * int16 LLRs))", points=grid)
+                del d_g16
+            f8.close()
+
+        # ---- latency of the reference's call shape: ONE transport block per blocking call (srslte_dlsch_decode as pdsch.c:816
+        #      makes it, level 2 of INTEGRATION.md), host buffers, everything inside the timed call ----
+        lat = None
+        if rank == 0:
+            one = (pkg.TbDesc * 1)()
+            ts = []
+            for i in range(64):
+                fill_descs(pkg, one, 1, h_llr.a.ctypes.data + (i % B) * NBITS * 2, h_out.a.ctypes.data, sb0)
+                t0 = time.perf_counter()
+                fec.decode_tbs(one, 0)
+                ts.append((time.perf_counter() - t0) * 1e6)
+            ts = sorted(ts[8:])
+            lat = dict(call="fec_cuda_decode_tbs(n=1), 13 code blocks, host LLRs in, payload out", median_us=ts[len(ts) // 2], p90_us=ts[int(len(ts) * 0.9)],
+                       min_us=ts[0])
+
+        # ---- worst case: all 8 half-iterations for every code block (no early stop), same inputs ----
+        worst = None
+        if not args.no_worst_case:
+            fec.decode_tbs(dd, pkg.F_DEVICE_IO | pkg.F_NO_EARLY_STOP)
+            ms_w = timed(dd, pkg.F_DEVICE_IO | pkg.F_NO_EARLY_STOP, max(2, args.steps // 3))
+            ok_w, its_w = tally(dd)
+            nst = max(2, args.steps // 3)
+            worst = dict(gbps=allsum(ok_w) * TBS * nst / (ms_w / 1e3) / 1e9, cbs_per_s=world * B * C_CB * nst / (ms_w / 1e3),
+                         halfits_per_cb=allsum(its_w) / (world * B * C_CB), ms_per_step=ms_w / nst)
+
+    except Exception as ex:            # noqa: BLE001 — reported, not swallowed
+        if world > 1:
+            raise                      # the other ranks wait in the legs' reductions: fail the job rather than hang it
+        import traceback
+        aux_error = repr(ex) + " | " + traceback.format_exc(limit=3).replace("\n", " / ")
+
     if rank == 0:
         line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=args.warmup,
                     ms_per_step=ms / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None, dtype="int16",
@@ -890,7 +901,7 @@ def main():
                                            achieved_gbs_per_rank=h2d / (ms_e / args.steps / 1e3) / 1e9, frac=h2d / (ms_e / args.steps / 1e3) / 1e9 / link_min),
                              cpu_binding=affinity),
                     sync_ms_per_step=ms_sync / args.steps, host_submit_ms_per_step=host_submit_ms,
-                    gpu_launches=launches, clocks=clocks, roofline=roof, worst_case_8_halfits=worst, frontend_symbols=front, ulsch_config5=ulsch5, harq_config3=harq, sustained=sustained, transmit_side=tx, llr_8bit=llr8, single_tb_latency=lat, cpu_baseline=cpu, parity_in_bench=parity)
+                    gpu_launches=launches, clocks=clocks, roofline=roof, worst_case_8_halfits=worst, frontend_symbols=front, ulsch_config5=ulsch5, harq_config3=harq, sustained=sustained, transmit_side=tx, llr_8bit=llr8, single_tb_latency=lat, cpu_baseline=cpu, parity_in_bench=parity, aux_error=aux_error)
         print(json.dumps(line), flush=True)
     fec.close()
     if world > 1:
