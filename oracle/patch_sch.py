@@ -2,7 +2,7 @@
 """Level-2 integration patch of INTEGRATION.md, applied to a COPY of the reference's lib/src/phy/phch/sch.c (test
 infrastructure: nothing of the reference is committed here, the edit is made by anchor, not by diff).
 
-    python oracle/patch_sch.py /root/reference/lib/src/phy/phch/sch.c oracle/_ref/link/sch_cuda.c
+    python oracle/patch_sch.py /root/reference/lib/src/phy/phch/sch.c <out.c>      (oracle/Makefile compiles the copy and removes it)
 
 Two edits, both behind -DSRSLTE_FEC_CUDA:
  1. decode_tb (sch.c:437-486) hands the whole transport block to libsrslte_fec_cuda (srslte_sch_decode_tb_cuda[_8bit]) as its
