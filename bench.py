@@ -637,28 +637,54 @@ def main():
                     d_[s_].e_bits, d_[s_].data = d_h[r].data_ptr() + i * H_NBITS * 2, d_out[0].data_ptr() + i * DATA_STRIDE
                 return d_
 
-            # discovery pass (untimed): which processes are still NACKed after each round — deterministic, the timed passes repeat it
-            rounds, live = [], list(range(Bh))
-            for r in range(4):
-                if not live:
-                    break
-                d_ = harq_round(r, live)
-                fec.decode_tbs(d_, pkg.F_DEVICE_IO)
-                rounds.append((d_, list(live), [d_[s_].ret for s_ in range(len(live))]))
-                live = [i for s_, i in enumerate(live) if d_[s_].ret != 0]
-            fec.decode_tbs(rounds[0][0], pkg.F_DEVICE_IO)          # warm
+            # discovery pass (untimed): which processes are still NACKed after each round — deterministic, the timed passes repeat it.
+            # The processes form two groups (a process never changes group): the rounds of ONE group are sequential by nature, the
+            # other group's round is in flight meanwhile, as the PHY workers of an eNB overlap the HARQ processes of different UEs
+            groups = []
+            for g_ in range(2):
+                rounds_g, live = [], list(range(g_ * (Bh // 2), Bh if g_ else Bh // 2))
+                for r in range(4):
+                    if not live:
+                        break
+                    d_ = harq_round(r, live)
+                    fec.decode_tbs(d_, pkg.F_DEVICE_IO)
+                    rounds_g.append((d_, list(live), [d_[s_].ret for s_ in range(len(live))]))
+                    live = [i for s_, i in enumerate(live) if d_[s_].ret != 0]
+                groups.append(rounds_g)
+            seq_g = [(g_, groups[g_][r]) for r in range(4) for g_ in range(2) if r < len(groups[g_])]      # G0 r0, G1 r0, G0 r1, G1 r1, ...
+            seq = [it for _, it in seq_g]
+            rounds = seq
+            for d_, _, _ in seq[:2]:
+                fec.decode_tbs(d_, pkg.F_DEVICE_IO)                # warm
+            # blocking reference figure: one call after the other
             barrier()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record(stream)
-            for _ in range(args.steps):
-                for d_, _, _ in rounds:
+            for _ in range(max(2, args.steps // 4)):
+                for d_, _, _ in seq:
                     fec.decode_tbs(d_, pkg.F_DEVICE_IO)
+            e1.record(stream)
+            barrier()
+            ms_h_block = shard.reduce_job(dist if world > 1 else None, f"cuda:{local_rank}", e0.elapsed_time(e1))[0] / max(2, args.steps // 4)
+            # timed: round r + 1 of a group is submitted only after its round r has been collected; the other group's call is in
+            # flight meanwhile
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            pend = {}
+            for _ in range(args.steps):
+                for g_, (d_, _, _) in seq_g:
+                    if g_ in pend:
+                        fec.wait(pend.pop(g_))                     # this group's previous round: its NACK list is what this call decodes
+                    pend[g_] = fec.submit_tbs(d_, pkg.F_DEVICE_IO)
+            for t_ in pend.values():
+                fec.wait(t_)
             e1.record(stream)
             barrier()
             ms_h = shard.reduce_job(dist if world > 1 else None, f"cuda:{local_rank}", e0.elapsed_time(e1))[0]
             out_host = d_out[0].cpu().numpy()
             acked, ntx, skipped, per_round = 0, 0, 0, []
-            for r, (d_, lv, ret0) in enumerate(rounds):
+            for (g_, (d_, lv, ret0)), r in zip(seq_g, [r_ for r_ in range(4) for g2 in range(2) if r_ < len(groups[g2])]):
                 if [d_[s_].ret for s_ in range(len(lv))] != ret0:
                     raise SystemExit("bench.py: the HARQ leg is not deterministic across steps")
                 ok_r = [i for s_, i in enumerate(lv) if d_[s_].ret == 0]
@@ -667,14 +693,14 @@ def main():
                     raise SystemExit(f"bench.py: {bad} ACKed transport blocks of the HARQ leg differ from the transmitted payload")
                 sk = sum(sum(1 for c in range(C_CB) if d_[s_].cb_its[c] == 0) for s_ in range(len(lv))) if r else 0
                 acked += len(ok_r); ntx += len(lv); skipped += sk
-                per_round.append(dict(rv=(0, 2, 3, 1)[r], tbs=len(lv), acked=len(ok_r), code_blocks_skipped_already_ok=sk))
+                per_round.append(dict(group=g_, rv=(0, 2, 3, 1)[r], tbs=len(lv), acked=len(ok_r), code_blocks_skipped_already_ok=sk))
             # the rate de-matcher in its read-modify-write case: the first retransmission round, serialised
             rmw = None
-            if len(rounds) > 1:
-                for d_, _, _ in rounds[:2]:
+            if len(groups[0]) > 1:
+                for d_, _, _ in groups[0][:2]:
                     fec.decode_tbs(d_, pkg.F_DEVICE_IO | pkg.F_SERIAL)
                 ph = fec.last_phase_ms()
-                d1, lv1 = rounds[1][0], rounds[1][1]
+                d1, lv1 = groups[0][1][0], groups[0][1][1]
                 ncb1 = sum(sum(1 for c in range(C_CB) if d1[s_].cb_its[c] > 0) for s_ in range(len(lv1)))
                 Eh = H_NBITS // C_CB
                 byt = ncb1 * (2 * Eh + 2 * 2 * (3 * 5888 + 16))       # LLRs in, slot read + slot written (3*SS+16 int16, SS = 16*368)
@@ -683,7 +709,9 @@ def main():
             harq = dict(workload="BASELINE configs[2] shape: TBS 75376 in 86400 LLRs (13 x K=5824, E = 6642/6648), rv 0,2,3,1, "
                                  "new_data only in round 0; later rounds combine into the soft buffers, skip code blocks that are already OK and copy their cached bytes",
                         sigma=args.sigma_harq, harq_processes=allsum(Bh), value=allsum(acked) * TBS * args.steps / (ms_h / 1e3) / 1e9, unit=UNIT + " of ACKed bits",
-                        ms_per_cycle=ms_h / args.steps, mean_transmissions_per_tb=allsum(ntx) / allsum(Bh), acked_frac=allsum(acked) / allsum(Bh),
+                        ms_per_cycle=ms_h / args.steps, blocking_ms_per_cycle=ms_h_block,
+                        pipelining="two groups of processes: a group's round r + 1 is submitted after its round r was collected, the other group's call is in flight meanwhile",
+                        mean_transmissions_per_tb=allsum(ntx) / allsum(Bh), acked_frac=allsum(acked) / allsum(Bh),
                         rounds_rank0=per_round, rate_dematch_read_modify_write_rank0=rmw,
                         payload_check="every ACKed transport block equals the transmitted payload; return codes identical in every cycle")
             del d_h
